@@ -1,0 +1,266 @@
+"""TEST INFRASTRUCTURE ONLY: ctypes loader for the oracle libraries.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may import
+this module.  Nothing under ol_dsp_b200/ does.
+
+  oracle()     -> oracle/libolb_oracle.so   our CPU restatement (built from oracle/olb_oracle.cpp)
+  reference()  -> oracle/_ref/libolref.so   the reference's own headers + verb.cpp (built in the dev
+                                            container from /root/reference; the .so travels to the GPU box)
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+EV_MIDI_CC, EV_HW_CC, EV_NOTE_ON, EV_NOTE_OFF, EV_INIT, EV_SET_FREQ, EV_GATE_ON, EV_GATE_OFF = range(8)
+KIND_BIQUAD, KIND_PORT, KIND_LPF = 0, 1, 2
+MODE_EXACT, MODE_FMA = 0, 1
+LAYOUT_FRAMES, LAYOUT_PLANAR = 0, 1
+
+
+class Event(C.Structure):
+    _fields_ = [("frame", C.c_uint32), ("kind", C.c_uint32), ("a", C.c_uint32), ("v", C.c_float), ("voice", C.c_int32)]
+
+
+def events(lst):
+    """lst of (frame, kind, a, v[, voice]) -> (ctypes array, n)"""
+    arr = (Event * max(1, len(lst)))()
+    for i, e in enumerate(sorted(lst, key=lambda e: e[0])):
+        arr[i].frame, arr[i].kind, arr[i].a, arr[i].v = int(e[0]), int(e[1]), int(e[2]), float(e[3])
+        arr[i].voice = int(e[4]) if len(e) > 4 else -1
+    return arr, len(lst)
+
+
+def _fp(a):
+    return a.ctypes.data_as(C.POINTER(C.c_float))
+
+
+def build(force=False):
+    """(Re)build libolb_oracle.so, and _ref/libolref.so when the reference tree is present."""
+    so = os.path.join(HERE, "libolb_oracle.so")
+    src = os.path.join(HERE, "olb_oracle.cpp")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-s", "-C", HERE, "libolb_oracle.so"])
+    subprocess.check_call(["make", "-s", "-C", HERE, "ref"])
+
+
+_EVP = C.POINTER(Event)
+_F = C.POINTER(C.c_float)
+_RUN_SIG = [C.c_int, C.c_float, _EVP, C.c_size_t, _F, _F, C.c_size_t]
+
+
+class _Fx:
+    """Shared wrapper shape for the per-unit run functions of either library."""
+
+    def __init__(self, lib, prefix):
+        self.lib, self.prefix = lib, prefix
+        for name in ("filterfx", "delayfx", "reverbfx", "fxrack"):
+            f = getattr(lib, f"{prefix}_{name}_run")
+            f.argtypes, f.restype = _RUN_SIG, C.c_int
+        sc = getattr(lib, f"{prefix}_scale")
+        sc.argtypes, sc.restype = [C.c_float] * 6, C.c_float
+        d = getattr(lib, f"{prefix}_dattorro_run")
+        d.argtypes, d.restype = [_F, _F, _F, _F, C.c_size_t], C.c_int
+
+    def scale(self, *a):
+        return getattr(self.lib, f"{self.prefix}_scale")(*[float(x) for x in a])
+
+    def _run(self, name, x, sr, ev, prefill=0.0):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        n = 1 if x.ndim == 1 else x.shape[1]
+        out = np.full_like(x, prefill)
+        arr, n_ev = events(ev or [])
+        rc = getattr(self.lib, f"{self.prefix}_{name}_run")(n, sr, arr, n_ev, _fp(x), _fp(out), x.shape[0])
+        assert rc == 0
+        return out
+
+    def filterfx(self, x, sr=48000.0, ev=None, prefill=0.0):
+        return self._run("filterfx", x, sr, ev, prefill)
+
+    def delayfx(self, x, sr=48000.0, ev=None):
+        return self._run("delayfx", x, sr, ev)
+
+    def reverbfx(self, x, sr=48000.0, ev=None):
+        return self._run("reverbfx", x, sr, ev)
+
+    def fxrack(self, x, sr=48000.0, ev=None):
+        return self._run("fxrack", x, sr, ev)
+
+    def dattorro(self, x, params=None):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        l, r = np.empty_like(x), np.empty_like(x)
+        p = None
+        if params is not None:
+            p = np.ascontiguousarray(params, dtype=np.float32)
+            assert p.shape == (7,)
+        rc = getattr(self.lib, f"{self.prefix}_dattorro_run")(_fp(p) if p is not None else None, _fp(x), _fp(l), _fp(r), x.shape[0])
+        assert rc == 0
+        return l, r
+
+
+class Oracle(_Fx):
+    def __init__(self):
+        build()
+        lib = C.CDLL(os.path.join(HERE, "libolb_oracle.so"))
+        super().__init__(lib, "orc")
+        lib.orc_noise_fill.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint64, C.c_uint64, C.c_float, _F, C.c_uint64, C.c_uint64]
+        lib.orc_noise_fill.restype = None
+        lib.orc_biquad_run.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_void_p, _F, _F, _F, _F, C.c_uint64, C.c_int]
+        lib.orc_biquad_run.restype = C.c_int
+        lib.orc_biquad_run_f64.argtypes = [C.c_uint32, C.c_uint32, C.c_void_p, _F, _F, C.POINTER(C.c_double), C.c_uint64]
+        lib.orc_biquad_run_f64.restype = C.c_int
+        lib.orc_biquad_fma_coefs.argtypes = [C.c_int, _F, _F]
+        lib.orc_rbj.argtypes = [C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, _F]
+        lib.orc_rbj.restype = None
+        lib.orc_voice_run.argtypes = [C.c_float, _F, _EVP, C.c_size_t, _F, _F, C.c_size_t]
+        lib.orc_voice_run.restype = C.c_int
+        lib.orc_polyvoice_run.argtypes = [C.c_int, C.c_float, _F, _EVP, C.c_size_t, _F, C.c_size_t]
+        lib.orc_polyvoice_run.restype = C.c_int
+        lib.orc_dattorro_slab_floats.restype = C.c_uint32
+        lib.orc_biquad_bench.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_void_p, _F, C.c_uint64, C.c_uint32, C.c_int, C.POINTER(C.c_double)]
+        lib.orc_biquad_bench.restype = C.c_double
+
+    def noise(self, seed, first_channel, channels, first_frame, frames, scale=1.0, planar=False):
+        """Philox white noise in [-1,1): [frames][channels] (or [channels][frames] when planar)."""
+        if planar:
+            out = np.empty((channels, frames), dtype=np.float32)
+            self.lib.orc_noise_fill(seed, first_channel, channels, first_frame, frames, scale, _fp(out), 1, frames)
+        else:
+            out = np.empty((frames, channels), dtype=np.float32)
+            self.lib.orc_noise_fill(seed, first_channel, channels, first_frame, frames, scale, _fp(out), channels, 1)
+        return out
+
+    def rbj(self, typ, fs, f0, q, gain_db=0.0):
+        out = np.empty(5, dtype=np.float32)
+        self.lib.orc_rbj(typ, fs, f0, q, gain_db, _fp(out))
+        return out
+
+    def biquad(self, x, coefs, kinds=None, mode=MODE_EXACT, state=None, planar=False):
+        """x: [T][C] (or [C][T] when planar); coefs: [C][S][5]; state: [C][S][4] updated in place."""
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        coefs = np.ascontiguousarray(coefs, dtype=np.float32)
+        ch, sec = coefs.shape[0], coefs.shape[1]
+        frames = x.shape[1] if planar else x.shape[0]
+        assert (x.shape[0] if planar else x.shape[1]) == ch
+        out = np.empty_like(x)
+        k = None
+        if kinds is not None:
+            k = np.ascontiguousarray(kinds, dtype=np.uint8)
+            assert k.shape == (sec,)
+        if state is not None:
+            assert state.dtype == np.float32 and state.shape == (ch, sec, 4) and state.flags.c_contiguous
+        rc = self.lib.orc_biquad_run(mode, ch, sec, k.ctypes.data if k is not None else None, _fp(coefs),
+                                     _fp(state) if state is not None else None, _fp(x), _fp(out), frames,
+                                     LAYOUT_PLANAR if planar else LAYOUT_FRAMES)
+        assert rc == 0
+        return out
+
+    def biquad_f64(self, x, coefs, kinds=None):
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        coefs = np.ascontiguousarray(coefs, dtype=np.float32)
+        out = np.empty(x.shape, dtype=np.float64)
+        k = np.ascontiguousarray(kinds, dtype=np.uint8) if kinds is not None else None
+        rc = self.lib.orc_biquad_run_f64(coefs.shape[0], coefs.shape[1], k.ctypes.data if k is not None else None,
+                                         _fp(coefs), _fp(x), out.ctypes.data_as(C.POINTER(C.c_double)), x.shape[0])
+        assert rc == 0
+        return out
+
+    def fma_coefs(self, kind, c5):
+        a = np.ascontiguousarray(c5, dtype=np.float32)
+        out = np.empty(5, dtype=np.float32)
+        self.lib.orc_biquad_fma_coefs(kind, _fp(a), _fp(out))
+        return out
+
+    def voice(self, frames, sr=48000.0, config=None, ev=None, trace=False):
+        out = np.empty(frames, dtype=np.float32)
+        tr = np.empty((frames, 4), dtype=np.float32) if trace else None
+        cfg = np.ascontiguousarray(config, dtype=np.float32) if config is not None else None
+        arr, n_ev = events(ev or [])
+        rc = self.lib.orc_voice_run(sr, _fp(cfg) if cfg is not None else None, arr, n_ev, _fp(out),
+                                    _fp(tr) if tr is not None else None, frames)
+        assert rc == 0
+        return (out, tr) if trace else out
+
+    def polyvoice(self, n, frames, sr=48000.0, config=None, ev=None):
+        out = np.empty(frames, dtype=np.float32)
+        cfg = np.ascontiguousarray(config, dtype=np.float32) if config is not None else None
+        arr, n_ev = events(ev or [])
+        rc = self.lib.orc_polyvoice_run(n, sr, _fp(cfg) if cfg is not None else None, arr, n_ev, _fp(out), frames)
+        assert rc == 0
+        return out
+
+    def biquad_bench(self, coefs, kinds, frames, seed, threads, mode=MODE_EXACT):
+        coefs = np.ascontiguousarray(coefs, dtype=np.float32)
+        k = np.ascontiguousarray(kinds, dtype=np.uint8) if kinds is not None else None
+        chk = C.c_double(0)
+        dt = self.lib.orc_biquad_bench(mode, coefs.shape[0], coefs.shape[1], k.ctypes.data if k is not None else None,
+                                       _fp(coefs), frames, seed, threads, C.byref(chk))
+        return dt, chk.value
+
+
+class Reference(_Fx):
+    def __init__(self, path):
+        lib = C.CDLL(path)
+        super().__init__(lib, "ref")
+        lib.ref_voice_run.argtypes = [C.c_float, _F, _EVP, C.c_size_t, _F, C.c_size_t]
+        lib.ref_voice_run.restype = C.c_int
+        lib.ref_polyvoice_run.argtypes = [C.c_int, C.c_float, _F, _EVP, C.c_size_t, _F, C.c_size_t]
+        lib.ref_polyvoice_run.restype = C.c_int
+        lib.ref_test_fx_delay.argtypes = [_F]
+        lib.ref_test_fx_delay.restype = C.c_int
+        lib.ref_test_synth_voice.argtypes = [_F]
+        lib.ref_test_synth_voice.restype = C.c_int
+        lib.ref_describe.restype = C.c_char_p
+
+    def voice(self, frames, sr=48000.0, config=None, ev=None):
+        out = np.empty(frames, dtype=np.float32)
+        cfg = np.ascontiguousarray(config, dtype=np.float32) if config is not None else None
+        arr, n_ev = events(ev or [])
+        rc = self.lib.ref_voice_run(sr, _fp(cfg) if cfg is not None else None, arr, n_ev, _fp(out), frames)
+        assert rc == 0
+        return out
+
+    def polyvoice(self, n, frames, sr=48000.0, config=None, ev=None):
+        out = np.empty(frames, dtype=np.float32)
+        cfg = np.ascontiguousarray(config, dtype=np.float32) if config is not None else None
+        arr, n_ev = events(ev or [])
+        rc = self.lib.ref_polyvoice_run(n, sr, _fp(cfg) if cfg is not None else None, arr, n_ev, _fp(out), frames)
+        assert rc == 0
+        return out
+
+    def test_fx_delay(self):
+        out = np.empty(48000, dtype=np.float32)
+        return self.lib.ref_test_fx_delay(_fp(out)), out
+
+    def test_synth_voice(self):
+        fr = np.empty(4, dtype=np.float32)
+        return self.lib.ref_test_synth_voice(_fp(fr)), fr
+
+
+_oracle = None
+_reference = None
+
+
+def oracle():
+    global _oracle
+    if _oracle is None:
+        _oracle = Oracle()
+    return _oracle
+
+
+def reference():
+    """The compiled reference, or None when oracle/_ref/libolref.so has not been built."""
+    global _reference
+    if _reference is None:
+        path = os.path.join(HERE, "_ref", "libolref.so")
+        if not os.path.exists(path):
+            try:
+                build()
+            except Exception:
+                pass
+        if os.path.exists(path):
+            _reference = Reference(path)
+    return _reference
