@@ -1,0 +1,114 @@
+/* olbank.h -- C ABI of libolbank.so: banks of independent audio-DSP units on one B200 (sm_100a).
+ *
+ * This is the drop-in boundary for the hot path of oletizi/ol_dsp.  The reference
+ * has no FFI layer: its operator API is the duck-typed method set
+ *     Init(sample_rate) / Process(frame_in, frame_out) / Update*Control(cc, value)
+ * on header-only C++ classes.  Every entry point below names the reference interface it replaces
+ * (file:line under the reference tree).  The C++ wrappers in include/ol_gpu/ keep the reference's
+ * method names on top of these calls; INTEGRATION.md shows the binding a maintainer would add.
+ *
+ * Conventions
+ *   - every function returns 0 (OLB_OK) or a negative OLB_E_* code; olb_last_error() gives the text
+ *     (the reference returns void everywhere and never throws: Fx.h:38,88,194; SoundSource.h:9-11)
+ *   - audio buffers named *_dev are caller-owned DEVICE pointers on the bank's GPU; *_host are host
+ *     pointers (pinned memory makes the copies asynchronous); handles own all other device memory
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream)
+ *   - a bank keeps its recurrence state on the device between process calls, exactly as a reference
+ *     object keeps it between Process() calls; *_init() resets it (re-Init: test/fx_test.cpp:32,42)
+ *   - there is no CPU fallback: without a usable sm_100 device every create call fails
+ */
+#ifndef OLBANK_H
+#define OLBANK_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define OLB_OK 0
+#define OLB_E_ARG (-1)   /* bad argument (NULL handle, size 0, unsupported layout ...) */
+#define OLB_E_CUDA (-2)  /* a CUDA runtime/driver call failed; see olb_last_error() */
+#define OLB_E_NCCL (-3)  /* reserved for the voice-bus reduce */
+#define OLB_E_STATE (-4) /* call not valid in the handle's current state */
+
+/* Audio layouts.  A reference frame is N consecutive floats (Fx.h:38); a bank frame is one float per
+ * unit, so the frame-interleaved block [frames][units] is the bank analogue of the reference's
+ * "for each frame: Process(in, out)" loop (ol_daisy/app/synth/main.cpp:74-90). */
+#define OLB_LAYOUT_FRAMES 0 /* [frames][units]  unit index fastest  (coalesced; the fast path) */
+#define OLB_LAYOUT_PLANAR 1 /* [units][frames]  one contiguous timeline per unit */
+
+/* Library / device ------------------------------------------------------------------------------ */
+const char *olb_last_error(void);
+const char *olb_version(void);
+int olb_device_count(int *count);
+/* Pinned host memory for the *_host entry points (cudaHostAlloc / cudaFreeHost). */
+int olb_host_alloc(void **ptr, size_t bytes);
+int olb_host_free(void *ptr);
+/* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
+uint64_t olb_launch_count(void);
+
+/* Replayable white noise: Philox4x32-10, key (seed, 0x01D5B200), counter
+ * (frame/4 lo, frame/4 hi, channel, 0); x = (u >> 8) * 2^-23 - 1 in [-1, 1), times `scale`.
+ * Fills units [first_unit, first_unit+units) x frames [first_frame, first_frame+frames) of a buffer in
+ * `layout`.  The CPU oracle replays the same stream. */
+int olb_noise_fill(float *out_dev, uint32_t seed, uint32_t first_unit, uint32_t units, uint64_t first_frame,
+                   uint64_t frames, float scale, int layout, void *stream);
+
+/* (a1) Biquad / one-pole cascade bank ------------------------------------------------------------
+ * No class of this name exists in the reference; the bank follows the
+ * reference's object conventions and reproduces its two one-pole forms as section kinds:
+ *   OLB_KIND_BIQUAD  y = b0*x + (((b1*x1 + b2*x2) - a2*y2) - a1*y1)          direct form 1
+ *   OLB_KIND_PORT    z = x + c*(z - x)      daisysp::Port::Process, modules/synthlib/Portamento.h:29-32
+ *   OLB_KIND_LPF     o = o + (x - o)*f      LowPassFilter_process, libs/dattorro-verb/verb.cpp:131-134
+ * Modes:
+ *   OLB_MODE_EXACT   every product and sum rounded separately, in the order written above
+ *                    (bit-exact against the scalar oracle built with -ffp-contract=off)
+ *   OLB_MODE_FMA     p = fma(b2,x2, b1*x1); p = fma(-a2,y2,p); p = fma(-a1,y1,p); y = fma(b0,x,p);
+ *                    one-pole kinds are rewritten as biquads first (PORT: b0=1-c, a1=-c;
+ *                    LPF: b0=f, a1=-(1-f)).  The throughput tier; within 1e-5 of full scale of EXACT. */
+#define OLB_KIND_BIQUAD 0
+#define OLB_KIND_PORT 1
+#define OLB_KIND_LPF 2
+#define OLB_MODE_EXACT 0
+#define OLB_MODE_FMA 1
+#define OLB_BIQUAD_MAX_SECTIONS 16
+
+typedef struct olb_biquad olb_biquad;
+
+/* default-construct + Init(sample_rate)  (lifecycle of every reference unit, e.g. Fx.h:83-86).
+ * All coefficients start as the identity section (b0 = 1), kinds as OLB_KIND_BIQUAD, mode EXACT. */
+int olb_biquad_create(int device, uint32_t channels, uint32_t sections, float sample_rate, olb_biquad **out);
+int olb_biquad_destroy(olb_biquad *h);
+/* Init(sample_rate): zeroes the recurrence state, keeps parameters (Fx.h:83-86 keeps cutoff etc.). */
+int olb_biquad_init(olb_biquad *h, float sample_rate);
+/* kinds: one uint8 per section, shared by every channel of the bank. */
+int olb_biquad_set_kinds(olb_biquad *h, const uint8_t *kinds, uint32_t sections);
+int olb_biquad_set_mode(olb_biquad *h, int mode);
+/* Parameter setter: coefs_host is [count][sections][5] = b0 b1 b2 a1 a2 for channels
+ * [first, first+count).  Takes effect at the next process call (setters in the reference take
+ * effect at the next Process(): Fx.h:110-114). */
+int olb_biquad_set_coeffs(olb_biquad *h, uint32_t first, uint32_t count, const float *coefs_host);
+/* RBJ-cookbook designer in the reference's "setter computes coefficients on the host" style
+ * (the Svf setters do the same: SURVEY.md section 2.3).  type: 0 low-pass, 1 high-pass,
+ * 2 peaking (gain_db), 3 one-pole low-pass as a biquad.  Computed in double, rounded to float. */
+int olb_biquad_design(int type, double sample_rate, double f0, double q, double gain_db, float *coefs5);
+/* Block form of "for each frame: Process(in, out)".  in_dev == out_dev is allowed (the reference is
+ * called in place: main.cpp:82-85).  frames == 1 is the per-frame call. */
+int olb_biquad_process(olb_biquad *h, const float *in_dev, float *out_dev, uint64_t frames, int layout, void *stream);
+/* Same with host buffers: chunks the block in time, overlaps H2D / kernel / D2H on internal
+ * streams, returns when out_host is complete. */
+int olb_biquad_process_host(olb_biquad *h, const float *in_host, float *out_host, uint64_t frames, int layout);
+/* State as the oracle lays it out: [channels][sections][4] = x1 x2 y1 y2 (host pointers). */
+int olb_biquad_get_state(olb_biquad *h, float *state_host);
+int olb_biquad_set_state(olb_biquad *h, const float *state_host);
+/* Diagnostics for bench.py: which kernel variant the last process call used, and kernel selection
+ * override (0 = automatic). */
+const char *olb_biquad_last_kernel(olb_biquad *h);
+int olb_biquad_set_variant(olb_biquad *h, int variant);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OLBANK_H */

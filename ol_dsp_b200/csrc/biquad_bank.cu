@@ -1,0 +1,707 @@
+// biquad_bank.cu -- (a1) biquad / one-pole cascade bank.
+//
+// The reference has no biquad class; the bank follows the reference's object
+// conventions (Init / setters / Process) and reproduces its two one-pole forms bit-exactly:
+//   daisysp::Port::Process      modules/synthlib/Portamento.h:29-32     z = x + c*(z - x)
+//   LowPassFilter_process       libs/dattorro-verb/verb.cpp:131-134     o = o + (x - o)*f
+//
+// Data layout in HBM
+//   audio    [frames][channels] fp32 (OLB_LAYOUT_FRAMES; channel fastest) or [channels][frames]
+//   coef     [sections][5][channels]   b0 b1 b2 -a1 -a2   (negation is exact; channel fastest so a warp's
+//                                                          prologue loads are coalesced)
+//   hist     [sections+1][2][channels] the last two samples at every node of the cascade: node 0 is the
+//            input, node s+1 the output of section s.  In a direct-form-1 cascade the y-history of
+//            section s IS the x-history of section s+1, so 2(S+1) floats per channel replace 4S.
+//
+// Kernels (all: one time-sequential recurrence per channel, state and coefficients in registers)
+//   k_bq_tma     the throughput kernel.  One thread = two adjacent channels in packed fp32x2 (FFMA2);
+//                one warp = 64 channels with its OWN TMA pipeline: [TB frames][64 ch] tiles arrive by
+//                cp.async.bulk.tensor into a per-warp shared-memory ring (mbarrier complete_tx), are
+//                filtered in place and leave by TMA store.  No block-wide barrier exists in the kernel.
+//   k_bq_direct  one channel per thread, plain coalesced loads, register double-buffering; handles any
+//                channel count / alignment, one-pole kinds in EXACT mode, and runtime section counts.
+//   k_bq_planar  [channels][frames] input: a warp transposes 32x32 tiles through shared memory.
+#include <math.h>
+
+#include <vector>
+
+#include "common.cuh"
+#include "tmap.h"
+
+namespace olb {
+
+constexpr int kMaxS = OLB_BIQUAD_MAX_SECTIONS;
+
+struct Kinds {
+    uint8_t k[kMaxS];
+};
+
+// ------------------------------------------------------------------------------------------------
+// One cascade step, scalar.  Op order follows the oracle (oracle/olb_oracle.cpp:131-147).
+template <int MODE>
+__device__ __forceinline__ float section_biquad(float x, float x1, float x2, float y1, float y2, float b0, float b1, float b2,
+                                                float na1, float na2) {
+    if (MODE == OLB_MODE_FMA) {
+        float p = __fmul_rn(b1, x1);
+        p = __fmaf_rn(b2, x2, p);
+        p = __fmaf_rn(na2, y2, p);
+        p = __fmaf_rn(na1, y1, p);
+        return __fmaf_rn(b0, x, p);
+    } else {
+        float p = __fadd_rn(__fmul_rn(b1, x1), __fmul_rn(b2, x2));
+        p = __fadd_rn(p, __fmul_rn(na2, y2));
+        p = __fadd_rn(p, __fmul_rn(na1, y1));
+        return __fadd_rn(__fmul_rn(b0, x), p);
+    }
+}
+
+// h[n][0] = newest, h[n][1] = the one before, for node n.  GENERIC: honour one-pole kinds (EXACT only).
+template <int S, int MODE, bool GENERIC>
+__device__ __forceinline__ float cascade_step(float v, float (&h)[S + 1][2], const float (&k)[S][5], const Kinds &kinds) {
+#pragma unroll
+    for (int s = 0; s < S; s++) {
+        float y;
+        const int kind = GENERIC ? kinds.k[s] : OLB_KIND_BIQUAD;
+        if (GENERIC && kind == OLB_KIND_PORT) {
+            y = __fadd_rn(v, __fmul_rn(k[s][0], __fsub_rn(h[s + 1][0], v)));
+        } else if (GENERIC && kind == OLB_KIND_LPF) {
+            y = __fadd_rn(h[s + 1][0], __fmul_rn(__fsub_rn(v, h[s + 1][0]), k[s][0]));
+        } else {
+            y = section_biquad<MODE>(v, h[s][0], h[s][1], h[s + 1][0], h[s + 1][1], k[s][0], k[s][1], k[s][2], k[s][3], k[s][4]);
+        }
+        h[s][1] = h[s][0];
+        h[s][0] = v;
+        v = y;
+    }
+    h[S][1] = h[S][0];
+    h[S][0] = v;
+    return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_bq_direct: one channel per thread, U frames of register double-buffering.
+template <int S, int MODE, bool GENERIC, int U>
+__global__ void __launch_bounds__(128) k_bq_direct(const float *in, float *out, uint64_t frames, uint32_t C, const float *coef,
+                                                   float *hist, Kinds kinds) {
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    float k[S][5], h[S + 1][2];
+#pragma unroll
+    for (int s = 0; s < S; s++)
+#pragma unroll
+        for (int j = 0; j < 5; j++) k[s][j] = coef[(size_t) (s * 5 + j) * C + c];
+#pragma unroll
+    for (int n = 0; n <= S; n++) {
+        h[n][0] = hist[(size_t) (n * 2 + 0) * C + c];
+        h[n][1] = hist[(size_t) (n * 2 + 1) * C + c];
+    }
+    const float *pi = in + c;
+    float *po = out + c;
+    uint64_t t = 0;
+    if (frames >= (uint64_t) U) {
+        float xb[U], xn[U];
+#pragma unroll
+        for (int i = 0; i < U; i++) xb[i] = pi[(size_t) i * C];
+        pi += (size_t) U * C;
+        for (; t + 2 * U <= frames; t += U) {
+#pragma unroll
+            for (int i = 0; i < U; i++) xn[i] = pi[(size_t) i * C];
+            pi += (size_t) U * C;
+#pragma unroll
+            for (int i = 0; i < U; i++) po[(size_t) i * C] = cascade_step<S, MODE, GENERIC>(xb[i], h, k, kinds);
+            po += (size_t) U * C;
+#pragma unroll
+            for (int i = 0; i < U; i++) xb[i] = xn[i];
+        }
+#pragma unroll
+        for (int i = 0; i < U; i++) po[(size_t) i * C] = cascade_step<S, MODE, GENERIC>(xb[i], h, k, kinds);
+        po += (size_t) U * C;
+        t += U;
+    }
+    for (; t < frames; t++) {
+        *po = cascade_step<S, MODE, GENERIC>(*pi, h, k, kinds);
+        pi += C;
+        po += C;
+    }
+#pragma unroll
+    for (int n = 0; n <= S; n++) {
+        hist[(size_t) (n * 2 + 0) * C + c] = h[n][0];
+        hist[(size_t) (n * 2 + 1) * C + c] = h[n][1];
+    }
+}
+
+// Runtime section count (9..16 sections, or as a last resort): state lives in local arrays.
+template <int MODE>
+__global__ void __launch_bounds__(128) k_bq_runtime(const float *in, float *out, uint64_t frames, uint32_t C, int S,
+                                                    const float *coef, float *hist, Kinds kinds, int layout) {
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    float k[kMaxS][5], h[kMaxS + 1][2];
+    for (int s = 0; s < S; s++)
+        for (int j = 0; j < 5; j++) k[s][j] = coef[(size_t) (s * 5 + j) * C + c];
+    for (int n = 0; n <= S; n++) {
+        h[n][0] = hist[(size_t) (n * 2 + 0) * C + c];
+        h[n][1] = hist[(size_t) (n * 2 + 1) * C + c];
+    }
+    const size_t base = layout == OLB_LAYOUT_FRAMES ? c : (size_t) c * frames;
+    const size_t stride = layout == OLB_LAYOUT_FRAMES ? C : 1;
+    for (uint64_t t = 0; t < frames; t++) {
+        float v = in[base + t * stride];
+        for (int s = 0; s < S; s++) {
+            float y;
+            const int kind = MODE == OLB_MODE_FMA ? OLB_KIND_BIQUAD : kinds.k[s];
+            if (kind == OLB_KIND_PORT) y = __fadd_rn(v, __fmul_rn(k[s][0], __fsub_rn(h[s + 1][0], v)));
+            else if (kind == OLB_KIND_LPF) y = __fadd_rn(h[s + 1][0], __fmul_rn(__fsub_rn(v, h[s + 1][0]), k[s][0]));
+            else y = section_biquad<MODE>(v, h[s][0], h[s][1], h[s + 1][0], h[s + 1][1], k[s][0], k[s][1], k[s][2], k[s][3], k[s][4]);
+            h[s][1] = h[s][0];
+            h[s][0] = v;
+            v = y;
+        }
+        h[S][1] = h[S][0];
+        h[S][0] = v;
+        out[base + t * stride] = v;
+    }
+    for (int n = 0; n <= S; n++) {
+        hist[(size_t) (n * 2 + 0) * C + c] = h[n][0];
+        hist[(size_t) (n * 2 + 1) * C + c] = h[n][1];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_bq_planar: [channels][frames].  One warp = 32 channels; 32x32 tiles are read with lane = frame
+// (coalesced 128 B per channel row), transposed through padded shared memory, filtered with
+// lane = channel, and written back the same way.
+template <int S, int MODE, bool GENERIC>
+__global__ void __launch_bounds__(128) k_bq_planar(const float *in, float *out, uint64_t frames, uint32_t C, const float *coef,
+                                                   float *hist, Kinds kinds) {
+    __shared__ float tile_all[4][32][33];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    float(*tile)[33] = tile_all[warp];
+    const uint32_t c0 = (blockIdx.x * 4 + warp) * 32;
+    if (c0 >= C) return;
+    const uint32_t c = c0 + lane;
+    const bool live = c < C;
+    const uint32_t cc = live ? c : C - 1;  // dead lanes shadow a valid channel and never store
+    float k[S][5], h[S + 1][2];
+#pragma unroll
+    for (int s = 0; s < S; s++)
+#pragma unroll
+        for (int j = 0; j < 5; j++) k[s][j] = coef[(size_t) (s * 5 + j) * C + cc];
+#pragma unroll
+    for (int n = 0; n <= S; n++) {
+        h[n][0] = hist[(size_t) (n * 2 + 0) * C + cc];
+        h[n][1] = hist[(size_t) (n * 2 + 1) * C + cc];
+    }
+    const uint32_t nch = min(32u, C - c0);
+    for (uint64_t t0 = 0; t0 < frames; t0 += 32) {
+        const uint32_t nt = (uint32_t) min((uint64_t) 32, frames - t0);
+        for (uint32_t r = 0; r < nch; r++)
+            if ((uint32_t) lane < nt) tile[r][lane] = in[(size_t) (c0 + r) * frames + t0 + lane];
+        __syncwarp();
+        for (uint32_t i = 0; i < nt; i++) {
+            const float y = cascade_step<S, MODE, GENERIC>(tile[lane][i], h, k, kinds);
+            tile[lane][i] = y;
+        }
+        __syncwarp();
+        for (uint32_t r = 0; r < nch; r++)
+            if ((uint32_t) lane < nt) out[(size_t) (c0 + r) * frames + t0 + lane] = tile[r][lane];
+        __syncwarp();
+    }
+    if (live) {
+#pragma unroll
+        for (int n = 0; n <= S; n++) {
+            hist[(size_t) (n * 2 + 0) * C + c] = h[n][0];
+            hist[(size_t) (n * 2 + 1) * C + c] = h[n][1];
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_bq_tma: packed two-channel threads, per-warp TMA pipelines.
+template <int MODE>
+__device__ __forceinline__ u64 section_biquad2(u64 x, u64 x1, u64 x2, u64 y1, u64 y2, u64 b0, u64 b1, u64 b2, u64 na1, u64 na2,
+                                               u64 one, u64 negzero) {
+    if (MODE == OLB_MODE_FMA) {
+        u64 p = fmul2(b1, x1);
+        p = ffma2(b2, x2, p);
+        p = ffma2(na2, y2, p);
+        p = ffma2(na1, y1, p);
+        return ffma2(b0, x, p);
+    } else {
+        // separately rounded products and sums from FFMA2 with opaque constants (see common.cuh)
+        u64 p = ffma2(ffma2(b1, x1, negzero), one, ffma2(b2, x2, negzero));
+        p = ffma2(p, one, ffma2(na2, y2, negzero));
+        p = ffma2(p, one, ffma2(na1, y1, negzero));
+        return ffma2(ffma2(b0, x, negzero), one, p);
+    }
+}
+
+template <int S, int MODE>
+__device__ __forceinline__ u64 cascade_step2(u64 v, u64 (&h)[S + 1][2], const u64 (&k)[S][5], u64 one, u64 negzero) {
+#pragma unroll
+    for (int s = 0; s < S; s++) {
+        const u64 y = section_biquad2<MODE>(v, h[s][0], h[s][1], h[s + 1][0], h[s + 1][1], k[s][0], k[s][1], k[s][2], k[s][3],
+                                            k[s][4], one, negzero);
+        h[s][1] = h[s][0];
+        h[s][0] = v;
+        v = y;
+    }
+    h[S][1] = h[S][0];
+    h[S][0] = v;
+    return v;
+}
+
+constexpr int kTmaCh = 64;  // channels per warp (2 per lane)
+
+template <int S, int MODE, int TB, int STAGES, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32) k_bq_tma(const __grid_constant__ TensorMap tm_in, const __grid_constant__ TensorMap tm_out,
+                                                       uint32_t frames, uint32_t C, const float *__restrict__ coef, float *hist,
+                                                       u64 one, u64 negzero) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t group = blockIdx.x * WARPS + warp;
+    const uint32_t ch0 = group * kTmaCh;
+    if (ch0 >= C) return;
+    float *tiles = reinterpret_cast<float *>(smem_raw) + (size_t) warp * STAGES * TB * kTmaCh;
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + (size_t) WARPS * STAGES * TB * kTmaCh * sizeof(float)) + warp * STAGES;
+
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; s++) mbar_init(&full[s], 1);
+        mbar_fence_init();
+    }
+    __syncwarp();
+
+    constexpr uint32_t kTileBytes = TB * kTmaCh * sizeof(float);
+    const uint32_t ntiles = (frames + TB - 1) / TB;
+    if (lane == 0) {
+        for (uint32_t j = 0; j < (uint32_t) (STAGES - 1) && j < ntiles; j++) {
+            mbar_arrive_expect_tx(&full[j], kTileBytes);
+            tma_load_2d(tiles + (size_t) j * TB * kTmaCh, &tm_in, (int) ch0, (int) (j * TB), &full[j]);
+        }
+    }
+
+    // coefficients and history for channels (c, c+1); lanes past the end of the bank idle on zeros
+    const uint32_t c = ch0 + 2 * lane;
+    const bool live = c < C;  // C is a multiple of 4 on this path, so a live lane owns two live channels
+    u64 k[S][5], h[S + 1][2];
+#pragma unroll
+    for (int s = 0; s < S; s++)
+#pragma unroll
+        for (int j = 0; j < 5; j++) k[s][j] = live ? *reinterpret_cast<const u64 *>(coef + (size_t) (s * 5 + j) * C + c) : 0ull;
+#pragma unroll
+    for (int n = 0; n <= S; n++) {
+        h[n][0] = live ? *reinterpret_cast<const u64 *>(hist + (size_t) (n * 2 + 0) * C + c) : 0ull;
+        h[n][1] = live ? *reinterpret_cast<const u64 *>(hist + (size_t) (n * 2 + 1) * C + c) : 0ull;
+    }
+
+    for (uint32_t i = 0; i < ntiles; i++) {
+        const uint32_t st = i % STAGES, par = (i / STAGES) & 1;
+        mbar_wait(&full[st], par);
+        u64 *col = reinterpret_cast<u64 *>(tiles + (size_t) st * TB * kTmaCh) + lane;
+        const uint32_t rows = min((uint32_t) TB, frames - i * TB);
+        if (rows == TB) {
+#pragma unroll 4
+            for (int r = 0; r < TB; r++) col[r * (kTmaCh / 2)] = cascade_step2<S, MODE>(col[r * (kTmaCh / 2)], h, k, one, negzero);
+        } else {
+            for (uint32_t r = 0; r < rows; r++) col[r * (kTmaCh / 2)] = cascade_step2<S, MODE>(col[r * (kTmaCh / 2)], h, k, one, negzero);
+        }
+        fence_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+            tma_store_2d(&tm_out, (int) ch0, (int) (i * TB), tiles + (size_t) st * TB * kTmaCh);
+            tma_commit();
+            const uint32_t nxt = i + STAGES - 1;  // goes into the stage tile i-1 was stored from
+            if (nxt < ntiles) {
+                tma_wait_read<1>();
+                const uint32_t ns = nxt % STAGES;
+                mbar_arrive_expect_tx(&full[ns], kTileBytes);
+                tma_load_2d(tiles + (size_t) ns * TB * kTmaCh, &tm_in, (int) ch0, (int) (nxt * TB), &full[ns]);
+            }
+        }
+    }
+    if (lane == 0) tma_wait_all<0>();
+    if (live) {
+#pragma unroll
+        for (int n = 0; n <= S; n++) {
+            *reinterpret_cast<u64 *>(hist + (size_t) (n * 2 + 0) * C + c) = h[n][0];
+            *reinterpret_cast<u64 *>(hist + (size_t) (n * 2 + 1) * C + c) = h[n][1];
+        }
+    }
+}
+
+}  // namespace olb
+
+using namespace olb;
+
+// ================================================================================================
+// Host side
+struct olb_biquad {
+    int device = 0;
+    uint32_t C = 0, S = 0;
+    float sample_rate = 0.f;
+    int mode = OLB_MODE_EXACT;
+    int variant = 0;  // 0 auto, 1 direct, 2 tma
+    Kinds kinds{};
+    bool all_biquad = true;
+    std::vector<float> coefs_host;  // [C][S][5] as the caller set them
+    float *d_coef = nullptr;        // [S][5][C] effective
+    float *d_hist = nullptr;        // [S+1][2][C]
+    bool coef_dirty = true;
+    const char *last_kernel = "none";
+    // host-buffer path
+    float *d_stage[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};  // [slot][in/out]
+    size_t stage_elems = 0;
+    cudaStream_t s_h2d = nullptr, s_run = nullptr, s_d2h = nullptr;
+    cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_run[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
+};
+
+static void effective_coefs(const olb_biquad *h, const float *in5, int s, float *out5) {
+    const int kind = h->kinds.k[s];
+    if (h->mode == OLB_MODE_FMA && kind == OLB_KIND_PORT) {
+        out5[0] = 1.0f - in5[0]; out5[1] = 0.f; out5[2] = 0.f; out5[3] = in5[0]; out5[4] = -0.f;  // -a1 = c, -a2 = -0
+    } else if (h->mode == OLB_MODE_FMA && kind == OLB_KIND_LPF) {
+        out5[0] = in5[0]; out5[1] = 0.f; out5[2] = 0.f; out5[3] = 1.0f - in5[0]; out5[4] = -0.f;
+    } else {
+        out5[0] = in5[0]; out5[1] = in5[1]; out5[2] = in5[2]; out5[3] = -in5[3]; out5[4] = -in5[4];
+    }
+}
+
+// Rebuild the device table for channels [first, first+count) from the host copy.
+static int upload_coefs(olb_biquad *h, uint32_t first, uint32_t count) {
+    const uint32_t S = h->S;
+    std::vector<float> stage((size_t) S * 5 * count);
+    for (uint32_t i = 0; i < count; i++)
+        for (uint32_t s = 0; s < S; s++) {
+            float e[5];
+            effective_coefs(h, &h->coefs_host[((size_t) (first + i) * S + s) * 5], (int) s, e);
+            for (int j = 0; j < 5; j++) stage[(size_t) (s * 5 + j) * count + i] = e[j];
+        }
+    OLB_CUDA(cudaMemcpy2D(h->d_coef + first, (size_t) h->C * sizeof(float), stage.data(), (size_t) count * sizeof(float),
+                          (size_t) count * sizeof(float), (size_t) S * 5, cudaMemcpyHostToDevice));
+    return OLB_OK;
+}
+
+OLB_API int olb_biquad_create(int device, uint32_t channels, uint32_t sections, float sample_rate, olb_biquad **out) {
+    OLB_ARG(out, "olb_biquad_create: out is NULL");
+    *out = nullptr;
+    OLB_ARG(channels > 0, "olb_biquad_create: channels must be > 0");
+    OLB_ARG(sections >= 1 && sections <= (uint32_t) kMaxS, "olb_biquad_create: sections must be in 1..%d", kMaxS);
+    int rc = require_sm100(device);
+    if (rc) return rc;
+    DeviceGuard g(device);
+    olb_biquad *h = new olb_biquad();
+    h->device = device;
+    h->C = channels;
+    h->S = sections;
+    h->sample_rate = sample_rate;
+    h->coefs_host.assign((size_t) channels * sections * 5, 0.f);
+    for (size_t i = 0; i < (size_t) channels * sections; i++) h->coefs_host[i * 5] = 1.0f;
+    cudaError_t e = cudaMalloc(&h->d_coef, (size_t) sections * 5 * channels * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_hist, (size_t) (sections + 1) * 2 * channels * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemset(h->d_hist, 0, (size_t) (sections + 1) * 2 * channels * sizeof(float));
+    if (e != cudaSuccess) {
+        cudaFree(h->d_coef);
+        cudaFree(h->d_hist);
+        delete h;
+        return fail_cuda(e, "allocating bank tables", __FILE__, __LINE__);
+    }
+    *out = h;
+    return OLB_OK;
+}
+
+OLB_API int olb_biquad_destroy(olb_biquad *h) {
+    if (!h) return OLB_OK;
+    DeviceGuard g(h->device);
+    cudaFree(h->d_coef);
+    cudaFree(h->d_hist);
+    for (int i = 0; i < 2; i++) {
+        cudaFree(h->d_stage[i][0]);
+        cudaFree(h->d_stage[i][1]);
+        if (h->ev_in[i]) cudaEventDestroy(h->ev_in[i]);
+        if (h->ev_run[i]) cudaEventDestroy(h->ev_run[i]);
+        if (h->ev_out[i]) cudaEventDestroy(h->ev_out[i]);
+    }
+    if (h->s_h2d) cudaStreamDestroy(h->s_h2d);
+    if (h->s_run) cudaStreamDestroy(h->s_run);
+    if (h->s_d2h) cudaStreamDestroy(h->s_d2h);
+    delete h;
+    return OLB_OK;
+}
+
+OLB_API int olb_biquad_init(olb_biquad *h, float sample_rate) {
+    OLB_ARG(h, "olb_biquad_init: NULL handle");
+    DeviceGuard g(h->device);
+    h->sample_rate = sample_rate;
+    OLB_CUDA(cudaMemset(h->d_hist, 0, (size_t) (h->S + 1) * 2 * h->C * sizeof(float)));
+    return OLB_OK;
+}
+
+OLB_API int olb_biquad_set_kinds(olb_biquad *h, const uint8_t *kinds, uint32_t sections) {
+    OLB_ARG(h && kinds, "olb_biquad_set_kinds: NULL argument");
+    OLB_ARG(sections == h->S, "olb_biquad_set_kinds: bank has %u sections, got %u", h->S, sections);
+    bool all = true;
+    for (uint32_t s = 0; s < sections; s++) {
+        OLB_ARG(kinds[s] <= OLB_KIND_LPF, "olb_biquad_set_kinds: unknown kind %u at section %u", kinds[s], s);
+        h->kinds.k[s] = kinds[s];
+        all = all && kinds[s] == OLB_KIND_BIQUAD;
+    }
+    h->all_biquad = all;
+    h->coef_dirty = true;
+    return OLB_OK;
+}
+
+OLB_API int olb_biquad_set_mode(olb_biquad *h, int mode) {
+    OLB_ARG(h, "olb_biquad_set_mode: NULL handle");
+    OLB_ARG(mode == OLB_MODE_EXACT || mode == OLB_MODE_FMA, "olb_biquad_set_mode: unknown mode %d", mode);
+    if (mode != h->mode) h->coef_dirty = true;
+    h->mode = mode;
+    return OLB_OK;
+}
+
+OLB_API int olb_biquad_set_variant(olb_biquad *h, int variant) {
+    OLB_ARG(h, "olb_biquad_set_variant: NULL handle");
+    OLB_ARG(variant >= 0 && variant <= 2, "olb_biquad_set_variant: unknown variant %d", variant);
+    h->variant = variant;
+    return OLB_OK;
+}
+
+OLB_API const char *olb_biquad_last_kernel(olb_biquad *h) { return h ? h->last_kernel : "none"; }
+
+OLB_API int olb_biquad_set_coeffs(olb_biquad *h, uint32_t first, uint32_t count, const float *coefs_host) {
+    OLB_ARG(h && coefs_host, "olb_biquad_set_coeffs: NULL argument");
+    OLB_ARG((uint64_t) first + count <= h->C, "olb_biquad_set_coeffs: range [%u, %u) exceeds %u channels", first, first + count, h->C);
+    if (count == 0) return OLB_OK;
+    memcpy(&h->coefs_host[(size_t) first * h->S * 5], coefs_host, (size_t) count * h->S * 5 * sizeof(float));
+    if (!h->coef_dirty) {
+        DeviceGuard g(h->device);
+        return upload_coefs(h, first, count);
+    }
+    return OLB_OK;
+}
+
+OLB_API int olb_biquad_design(int type, double fs, double f0, double q, double gain_db, float *c5) {
+    OLB_ARG(c5, "olb_biquad_design: coefs5 is NULL");
+    OLB_ARG(type >= 0 && type <= 3, "olb_biquad_design: unknown type %d", type);
+    OLB_ARG(fs > 0 && f0 > 0 && f0 < fs / 2 && q > 0, "olb_biquad_design: need 0 < f0 < fs/2 and q > 0");
+    const double w0 = 2.0 * M_PI * f0 / fs, cw = cos(w0), sw = sin(w0), alpha = sw / (2.0 * q);
+    double b0, b1, b2, a0, a1, a2;
+    switch (type) {
+        case 0: b1 = 1 - cw; b0 = b2 = b1 / 2; a0 = 1 + alpha; a1 = -2 * cw; a2 = 1 - alpha; break;
+        case 1: b0 = b2 = (1 + cw) / 2; b1 = -(1 + cw); a0 = 1 + alpha; a1 = -2 * cw; a2 = 1 - alpha; break;
+        case 2: {
+            const double A = pow(10.0, gain_db / 40.0);
+            b0 = 1 + alpha * A; b1 = -2 * cw; b2 = 1 - alpha * A; a0 = 1 + alpha / A; a1 = -2 * cw; a2 = 1 - alpha / A;
+            break;
+        }
+        default: {
+            const double p = exp(-w0);
+            b0 = 1 - p; b1 = 0; b2 = 0; a0 = 1; a1 = -p; a2 = 0;
+        }
+    }
+    c5[0] = (float) (b0 / a0); c5[1] = (float) (b1 / a0); c5[2] = (float) (b2 / a0);
+    c5[3] = (float) (a1 / a0); c5[4] = (float) (a2 / a0);
+    return OLB_OK;
+}
+
+// ---- state in the oracle's layout [C][S][4] = x1 x2 y1 y2 ---------------------------------------
+// Sections that never touch a slot (one-pole kinds in EXACT mode keep only y1) report 0 there, as a
+// freshly Init()ed oracle would.
+OLB_API int olb_biquad_get_state(olb_biquad *h, float *state_host) {
+    OLB_ARG(h && state_host, "olb_biquad_get_state: NULL argument");
+    DeviceGuard g(h->device);
+    const uint32_t C = h->C, S = h->S;
+    std::vector<float> hist((size_t) (S + 1) * 2 * C);
+    OLB_CUDA(cudaMemcpy(hist.data(), h->d_hist, hist.size() * sizeof(float), cudaMemcpyDeviceToHost));
+    for (uint32_t c = 0; c < C; c++)
+        for (uint32_t s = 0; s < S; s++) {
+            const bool full = h->mode == OLB_MODE_FMA || h->kinds.k[s] == OLB_KIND_BIQUAD;
+            float *o = state_host + ((size_t) c * S + s) * 4;
+            o[0] = full ? hist[(size_t) (s * 2 + 0) * C + c] : 0.f;
+            o[1] = full ? hist[(size_t) (s * 2 + 1) * C + c] : 0.f;
+            o[2] = hist[(size_t) ((s + 1) * 2 + 0) * C + c];
+            o[3] = full ? hist[(size_t) ((s + 1) * 2 + 1) * C + c] : 0.f;
+        }
+    return OLB_OK;
+}
+
+OLB_API int olb_biquad_set_state(olb_biquad *h, const float *state_host) {
+    OLB_ARG(h && state_host, "olb_biquad_set_state: NULL argument");
+    DeviceGuard g(h->device);
+    const uint32_t C = h->C, S = h->S;
+    std::vector<float> hist((size_t) (S + 1) * 2 * C, 0.f);
+    auto full = [&](uint32_t s) { return h->mode == OLB_MODE_FMA || h->kinds.k[s] == OLB_KIND_BIQUAD; };
+    for (uint32_t c = 0; c < C; c++) {
+        const float *st = state_host + (size_t) c * S * 4;
+        hist[(size_t) 0 * C + c] = st[0];
+        hist[(size_t) 1 * C + c] = st[1];
+        for (uint32_t s = 0; s < S; s++) {
+            const float *o = st + (size_t) s * 4;
+            hist[(size_t) ((s + 1) * 2 + 0) * C + c] = o[2];
+            float h2 = 0.f;
+            if (full(s)) h2 = o[3];
+            else if (s + 1 < S && full(s + 1)) h2 = st[(size_t) (s + 1) * 4 + 1];
+            hist[(size_t) ((s + 1) * 2 + 1) * C + c] = h2;
+        }
+    }
+    OLB_CUDA(cudaMemcpy(h->d_hist, hist.data(), hist.size() * sizeof(float), cudaMemcpyHostToDevice));
+    return OLB_OK;
+}
+
+// ---- launch -------------------------------------------------------------------------------------
+constexpr int kTB = 32, kStages = 4, kWarps = 4;
+constexpr size_t kTmaSmem = (size_t) kWarps * kStages * kTB * kTmaCh * sizeof(float) + (size_t) kWarps * kStages * sizeof(uint64_t);
+
+template <int S, int MODE>
+static int launch_tma(olb_biquad *h, const float *in, float *out, uint32_t frames, cudaStream_t st) {
+    TensorMap tin, tout;
+    int rc = make_tmap_frames(&tin, in, frames, h->C, kTmaCh, kTB);
+    if (rc) return rc;
+    rc = make_tmap_frames(&tout, out, frames, h->C, kTmaCh, kTB);
+    if (rc) return rc;
+    auto kern = k_bq_tma<S, MODE, kTB, kStages, kWarps>;
+    OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kTmaSmem));  // per device, cheap
+    const uint32_t groups = (h->C + kTmaCh - 1) / kTmaCh;
+    const float onef = 1.0f, nzf = -0.0f;
+    uint32_t ob, nb;
+    memcpy(&ob, &onef, 4);
+    memcpy(&nb, &nzf, 4);
+    const u64 one = ((u64) ob << 32) | ob, negzero = ((u64) nb << 32) | nb;
+    kern<<<(groups + kWarps - 1) / kWarps, kWarps * 32, kTmaSmem, st>>>(tin, tout, frames, h->C, h->d_coef, h->d_hist, one, negzero);
+    OLB_LAUNCHED();
+    return OLB_OK;
+}
+
+template <int S, int MODE, bool GENERIC>
+static int launch_direct(olb_biquad *h, const float *in, float *out, uint64_t frames, int layout, cudaStream_t st) {
+    if (layout == OLB_LAYOUT_FRAMES) {
+        k_bq_direct<S, MODE, GENERIC, 8><<<(h->C + 127) / 128, 128, 0, st>>>(in, out, frames, h->C, h->d_coef, h->d_hist, h->kinds);
+    } else {
+        k_bq_planar<S, MODE, GENERIC><<<(h->C + 127) / 128, 128, 0, st>>>(in, out, frames, h->C, h->d_coef, h->d_hist, h->kinds);
+    }
+    OLB_LAUNCHED();
+    return OLB_OK;
+}
+
+template <int S>
+static int dispatch_s(olb_biquad *h, const float *in, float *out, uint64_t frames, int layout, bool tma, cudaStream_t st) {
+    if (tma) {
+        return h->mode == OLB_MODE_FMA ? launch_tma<S, OLB_MODE_FMA>(h, in, out, (uint32_t) frames, st)
+                                       : launch_tma<S, OLB_MODE_EXACT>(h, in, out, (uint32_t) frames, st);
+    }
+    if (h->mode == OLB_MODE_FMA) return launch_direct<S, OLB_MODE_FMA, false>(h, in, out, frames, layout, st);
+    if (h->all_biquad) return launch_direct<S, OLB_MODE_EXACT, false>(h, in, out, frames, layout, st);
+    return launch_direct<S, OLB_MODE_EXACT, true>(h, in, out, frames, layout, st);
+}
+
+static int process_dev(olb_biquad *h, const float *in, float *out, uint64_t frames, int layout, cudaStream_t st) {
+    if (h->coef_dirty) {
+        int rc = upload_coefs(h, 0, h->C);
+        if (rc) return rc;
+        h->coef_dirty = false;
+    }
+    const uint32_t S = h->S;
+    if (S > 8) {
+        h->last_kernel = "k_bq_runtime";
+        if (h->mode == OLB_MODE_FMA)
+            k_bq_runtime<OLB_MODE_FMA><<<(h->C + 127) / 128, 128, 0, st>>>(in, out, frames, h->C, (int) S, h->d_coef, h->d_hist, h->kinds, layout);
+        else
+            k_bq_runtime<OLB_MODE_EXACT><<<(h->C + 127) / 128, 128, 0, st>>>(in, out, frames, h->C, (int) S, h->d_coef, h->d_hist, h->kinds, layout);
+        OLB_LAUNCHED();
+        return OLB_OK;
+    }
+    const bool tma_ok = layout == OLB_LAYOUT_FRAMES && (h->mode == OLB_MODE_FMA || h->all_biquad) && (h->C % 4) == 0 &&
+                        (((uintptr_t) in | (uintptr_t) out) & 15) == 0 && frames < (1ull << 31);
+    bool tma = tma_ok && h->variant != 1;
+    if (h->variant == 2 && !tma_ok) {
+        set_error("olb_biquad_process: the TMA variant needs FRAMES layout, channels %% 4 == 0, 16-byte aligned buffers and biquad-only kinds in EXACT mode");
+        return OLB_E_ARG;
+    }
+    // few channels: the packed kernel would leave most SMs without a warp; one channel per thread spreads wider
+    if (h->variant == 0 && tma && h->C < 64 * 148) tma = false;
+    h->last_kernel = tma ? "k_bq_tma" : (layout == OLB_LAYOUT_FRAMES ? "k_bq_direct" : "k_bq_planar");
+    switch (S) {
+        case 1: return dispatch_s<1>(h, in, out, frames, layout, tma, st);
+        case 2: return dispatch_s<2>(h, in, out, frames, layout, tma, st);
+        case 3: return dispatch_s<3>(h, in, out, frames, layout, tma, st);
+        case 4: return dispatch_s<4>(h, in, out, frames, layout, tma, st);
+        case 5: return dispatch_s<5>(h, in, out, frames, layout, tma, st);
+        case 6: return dispatch_s<6>(h, in, out, frames, layout, tma, st);
+        case 7: return dispatch_s<7>(h, in, out, frames, layout, tma, st);
+        default: return dispatch_s<8>(h, in, out, frames, layout, tma, st);
+    }
+}
+
+OLB_API int olb_biquad_process(olb_biquad *h, const float *in_dev, float *out_dev, uint64_t frames, int layout, void *stream) {
+    OLB_ARG(h, "olb_biquad_process: NULL handle");
+    OLB_ARG(layout == OLB_LAYOUT_FRAMES || layout == OLB_LAYOUT_PLANAR, "olb_biquad_process: bad layout %d", layout);
+    if (frames == 0) return OLB_OK;
+    OLB_ARG(in_dev && out_dev, "olb_biquad_process: NULL buffer");
+    DeviceGuard g(h->device);
+    return process_dev(h, in_dev, out_dev, frames, layout, (cudaStream_t) stream);
+}
+
+// Host buffers: the block is cut in time into chunks; chunk k+1 is copied in while chunk k is
+// filtered and chunk k-1 is copied out (three streams, two staging slots).  PLANAR chunks are
+// strided 2-D copies.  State flows from chunk to chunk on the device.
+OLB_API int olb_biquad_process_host(olb_biquad *h, const float *in_host, float *out_host, uint64_t frames, int layout) {
+    OLB_ARG(h, "olb_biquad_process_host: NULL handle");
+    OLB_ARG(layout == OLB_LAYOUT_FRAMES || layout == OLB_LAYOUT_PLANAR, "olb_biquad_process_host: bad layout %d", layout);
+    if (frames == 0) return OLB_OK;
+    OLB_ARG(in_host && out_host, "olb_biquad_process_host: NULL buffer");
+    DeviceGuard g(h->device);
+    const uint64_t C = h->C;
+    // ~64 MiB per staging buffer, whole frames, multiple of the TMA tile height
+    uint64_t chunk = (64ull << 20) / (C * sizeof(float));
+    chunk = chunk < 32 ? 32 : (chunk / 32) * 32;
+    if (chunk > frames) chunk = frames;
+    if (!h->s_h2d) {
+        OLB_CUDA(cudaStreamCreateWithFlags(&h->s_h2d, cudaStreamNonBlocking));
+        OLB_CUDA(cudaStreamCreateWithFlags(&h->s_run, cudaStreamNonBlocking));
+        OLB_CUDA(cudaStreamCreateWithFlags(&h->s_d2h, cudaStreamNonBlocking));
+        for (int i = 0; i < 2; i++) {
+            OLB_CUDA(cudaEventCreateWithFlags(&h->ev_in[i], cudaEventDisableTiming));
+            OLB_CUDA(cudaEventCreateWithFlags(&h->ev_run[i], cudaEventDisableTiming));
+            OLB_CUDA(cudaEventCreateWithFlags(&h->ev_out[i], cudaEventDisableTiming));
+        }
+    }
+    if (h->stage_elems < chunk * C) {
+        for (int i = 0; i < 2; i++)
+            for (int j = 0; j < 2; j++) {
+                cudaFree(h->d_stage[i][j]);
+                h->d_stage[i][j] = nullptr;
+                OLB_CUDA(cudaMalloc(&h->d_stage[i][j], chunk * C * sizeof(float)));
+            }
+        h->stage_elems = chunk * C;
+    }
+    uint64_t k = 0;
+    for (uint64_t t0 = 0; t0 < frames; t0 += chunk, k++) {
+        const uint64_t n = frames - t0 < chunk ? frames - t0 : chunk;
+        const int slot = (int) (k & 1);
+        float *din = h->d_stage[slot][0], *dout = h->d_stage[slot][1];
+        if (k >= 2) {
+            OLB_CUDA(cudaStreamWaitEvent(h->s_h2d, h->ev_run[slot], 0));  // kernel k-2 has consumed din
+        }
+        if (layout == OLB_LAYOUT_FRAMES)
+            OLB_CUDA(cudaMemcpyAsync(din, in_host + t0 * C, n * C * sizeof(float), cudaMemcpyHostToDevice, h->s_h2d));
+        else
+            OLB_CUDA(cudaMemcpy2DAsync(din, n * sizeof(float), in_host + t0, frames * sizeof(float), n * sizeof(float), C,
+                                       cudaMemcpyHostToDevice, h->s_h2d));
+        OLB_CUDA(cudaEventRecord(h->ev_in[slot], h->s_h2d));
+        OLB_CUDA(cudaStreamWaitEvent(h->s_run, h->ev_in[slot], 0));
+        if (k >= 2) OLB_CUDA(cudaStreamWaitEvent(h->s_run, h->ev_out[slot], 0));  // copy-out k-2 has drained dout
+        int rc = process_dev(h, din, dout, n, layout, h->s_run);
+        if (rc) return rc;
+        OLB_CUDA(cudaEventRecord(h->ev_run[slot], h->s_run));
+        OLB_CUDA(cudaStreamWaitEvent(h->s_d2h, h->ev_run[slot], 0));
+        if (layout == OLB_LAYOUT_FRAMES)
+            OLB_CUDA(cudaMemcpyAsync(out_host + t0 * C, dout, n * C * sizeof(float), cudaMemcpyDeviceToHost, h->s_d2h));
+        else
+            OLB_CUDA(cudaMemcpy2DAsync(out_host + t0, frames * sizeof(float), dout, n * sizeof(float), n * sizeof(float), C,
+                                       cudaMemcpyDeviceToHost, h->s_d2h));
+        OLB_CUDA(cudaEventRecord(h->ev_out[slot], h->s_d2h));
+    }
+    OLB_CUDA(cudaStreamSynchronize(h->s_d2h));
+    OLB_CUDA(cudaStreamSynchronize(h->s_run));
+    return OLB_OK;
+}

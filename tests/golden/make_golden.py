@@ -1,0 +1,105 @@
+"""Generates tests/golden/*.npz from the COMPILED REFERENCE (oracle/_ref/libolref.so, built from
+/root/reference by oracle/Makefile).  Run in the dev container only:
+
+    python tests/golden/make_golden.py
+
+The fixtures are small: short runs are stored whole, long runs as sha256 digests plus sparse samples.
+Inputs are the replayable Philox noise (seed in each file), so tests regenerate them.
+"""
+import hashlib
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from oracle import loader  # noqa: E402
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+NAN = float("nan")
+
+DATTORRO_CASES = {
+    # name: (params7 or None, seed, frames, scale)
+    "default_short": (None, 11, 4096, 0.25),
+    "default_wrap": (None, 12, 70000, 0.25),  # crosses the uint16 sample counter wrap and 34 excursion steps
+    "long_decay": ([0.3, 0.6, 0.7, 0.5, 0.9, 0.6, 0.8], 13, 20000, 0.25),
+    "short_predelay": ([0.0, NAN, NAN, NAN, 0.2, NAN, 0.5], 14, 6000, 0.5),
+}
+
+FX_EVENTS = [
+    (0, loader.EV_MIDI_CC, 35, 20),     # CC_DELAY_TIME -> 7559 samples
+    (0, loader.EV_MIDI_CC, 36, 90),     # CC_DELAY_FEEDBACK
+    (3000, loader.EV_MIDI_CC, 45, 40),  # CC_FX_FILTER_CUTOFF
+    (3000, loader.EV_HW_CC, 46, 0.6),   # CC_FX_FILTER_RESONANCE
+    (9000, loader.EV_MIDI_CC, 39, 80),  # CC_DELAY_BALANCE
+    (12000, loader.EV_MIDI_CC, 7, 100),  # CC_VOLUME
+]
+
+VOICE_EVENTS = [
+    (0, loader.EV_MIDI_CC, 41, 70), (0, loader.EV_MIDI_CC, 42, 30), (0, loader.EV_MIDI_CC, 73, 64),
+    (0, loader.EV_MIDI_CC, 75, 60), (0, loader.EV_MIDI_CC, 108, 10), (0, loader.EV_MIDI_CC, 111, 40),
+    (10, loader.EV_NOTE_ON, 60, 100), (2400, loader.EV_NOTE_OFF, 60, 0), (3000, loader.EV_NOTE_ON, 72, 90),
+    (3000, loader.EV_MIDI_CC, 5, 30), (5200, loader.EV_NOTE_OFF, 72, 0),
+]
+
+
+def sha(a):
+    return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def main():
+    ref = loader.reference()
+    orc = loader.oracle()
+    assert ref is not None, "oracle/_ref/libolref.so missing: run `make -C oracle` with /root/reference present"
+
+    out = {}
+    for name, (params, seed, frames, scale) in DATTORRO_CASES.items():
+        x = orc.noise(seed, 0, 1, 0, frames, scale)[:, 0]
+        l, r = ref.dattorro(x, params)
+        out[f"{name}_meta"] = np.array([seed, frames, scale], dtype=np.float64)
+        out[f"{name}_params"] = np.array(params if params is not None else [NAN] * 7, dtype=np.float32)
+        if frames <= 8192:
+            out[f"{name}_l"], out[f"{name}_r"] = l, r
+        else:
+            out[f"{name}_sha"] = np.array([sha(l), sha(r)])
+            out[f"{name}_tail_l"], out[f"{name}_tail_r"] = l[-256:], r[-256:]
+    np.savez_compressed(os.path.join(HERE, "dattorro.npz"), **out)
+
+    fx = {}
+    x = orc.noise(21, 0, 1, 0, 16000, 0.5)
+    fx["meta"] = np.array([21, 16000, 0.5], dtype=np.float64)
+    for name in ("filterfx", "delayfx", "reverbfx", "fxrack"):
+        y = getattr(ref, name)(x, 48000.0, FX_EVENTS)
+        fx[f"{name}_sha"] = np.array([sha(y)])
+        fx[f"{name}_head"] = y[:512, 0]
+        fx[f"{name}_tail"] = y[-512:, 0]
+    x2 = orc.noise(22, 0, 2, 0, 4000, 0.5)
+    fx["stereo_meta"] = np.array([22, 4000, 0.5], dtype=np.float64)
+    fx["fxrack2"] = ref.fxrack(x2, 44100.0, FX_EVENTS[:2])
+    rc, d = ref.test_fx_delay()
+    fx["test_fx_delay_nans"] = np.array([rc])
+    fx["test_fx_delay_sha"] = np.array([sha(d)])
+    fx["test_fx_delay_tail"] = d[-256:]
+    np.savez_compressed(os.path.join(HERE, "fx.npz"), **fx)
+
+    v = {}
+    y = ref.voice(6000, 48000.0, None, VOICE_EVENTS)
+    v["voice"] = y
+    p = ref.polyvoice(4, 3000, 48000.0, None,
+                      [(0, loader.EV_NOTE_ON, 48, 100), (5, loader.EV_NOTE_ON, 55, 100), (700, loader.EV_NOTE_ON, 64, 100),
+                       (1500, loader.EV_NOTE_OFF, 55, 0), (1600, loader.EV_NOTE_ON, 67, 100), (2500, loader.EV_NOTE_OFF, 48, 0)])
+    v["poly4"] = p
+    rc, fr = ref.test_synth_voice()
+    v["test_synth_voice_failed_mask"] = np.array([rc])
+    v["test_synth_voice_frames"] = fr
+    sc = [(64, 0, 127, 0, 20000, 1), (24, 0, 127, 0, 1, 1), (0.37, 0, 1, 0, 20000, 1.02), (90, 0, 127, 0, 20000, 2.5),
+          (30, 0, 127, 0, 1, 4), (-3, 0, 127, -1, 1, 3), (5, 5, 5, 0, 1, 1)]
+    v["scale_args"] = np.array(sc, dtype=np.float32)
+    v["scale_out"] = np.array([ref.scale(*a) for a in sc], dtype=np.float32)
+    np.savez_compressed(os.path.join(HERE, "synth.npz"), **v)
+    print("wrote", [f for f in os.listdir(HERE) if f.endswith(".npz")])
+
+
+if __name__ == "__main__":
+    main()
