@@ -22,6 +22,7 @@
 //                channel count / alignment, one-pole kinds in EXACT mode, and runtime section counts.
 //   k_bq_planar  [channels][frames] input: a warp transposes 32x32 tiles through shared memory.
 #include <math.h>
+#include <stdlib.h>
 
 #include <vector>
 
@@ -549,27 +550,59 @@ OLB_API int olb_biquad_set_state(olb_biquad *h, const float *state_host) {
 }
 
 // ---- launch -------------------------------------------------------------------------------------
-constexpr int kTB = 32, kStages = 4, kWarps = 4;
-constexpr size_t kTmaSmem = (size_t) kWarps * kStages * kTB * kTmaCh * sizeof(float) + (size_t) kWarps * kStages * sizeof(uint64_t);
+// k_bq_tma runs ONE warp per CTA: the warp is the scheduling unit, so the hardware block scheduler
+// spreads warp-groups of 64 channels over the 148 SMs by itself (65 536 channels = 1 024 CTAs = 6.9 per
+// SM, all resident in one wave).  Shared memory per CTA = STAGES x TB x 256 B (+ barriers).
+constexpr int kWarps = 1;
+struct TmaCfg {
+    int tb, stages;
+};
+// default tile shape; OLB_BQ_TMA_CFG="<TB>x<STAGES>" selects another compiled shape (tuning aid, S = 8 only)
+static TmaCfg tma_cfg() {
+    static TmaCfg cfg = [] {
+        TmaCfg c{32, 3};
+        if (const char *e = getenv("OLB_BQ_TMA_CFG")) {
+            int a = 0, b = 0;
+            if (sscanf(e, "%dx%d", &a, &b) == 2) c = TmaCfg{a, b};
+        }
+        return c;
+    }();
+    return cfg;
+}
 
-template <int S, int MODE>
-static int launch_tma(olb_biquad *h, const float *in, float *out, uint32_t frames, cudaStream_t st) {
+template <int S, int MODE, int TB, int STAGES>
+static int launch_tma_cfg(olb_biquad *h, const float *in, float *out, uint32_t frames, cudaStream_t st) {
+    constexpr size_t smem = (size_t) kWarps * STAGES * TB * kTmaCh * sizeof(float) + (size_t) kWarps * STAGES * sizeof(uint64_t);
     TensorMap tin, tout;
-    int rc = make_tmap_frames(&tin, in, frames, h->C, kTmaCh, kTB);
+    int rc = make_tmap_frames(&tin, in, frames, h->C, kTmaCh, TB);
     if (rc) return rc;
-    rc = make_tmap_frames(&tout, out, frames, h->C, kTmaCh, kTB);
+    rc = make_tmap_frames(&tout, out, frames, h->C, kTmaCh, TB);
     if (rc) return rc;
-    auto kern = k_bq_tma<S, MODE, kTB, kStages, kWarps>;
-    OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kTmaSmem));  // per device, cheap
+    auto kern = k_bq_tma<S, MODE, TB, STAGES, kWarps>;
+    OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));  // per device, cheap
+    OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     const uint32_t groups = (h->C + kTmaCh - 1) / kTmaCh;
     const float onef = 1.0f, nzf = -0.0f;
     uint32_t ob, nb;
     memcpy(&ob, &onef, 4);
     memcpy(&nb, &nzf, 4);
     const u64 one = ((u64) ob << 32) | ob, negzero = ((u64) nb << 32) | nb;
-    kern<<<(groups + kWarps - 1) / kWarps, kWarps * 32, kTmaSmem, st>>>(tin, tout, frames, h->C, h->d_coef, h->d_hist, one, negzero);
+    kern<<<(groups + kWarps - 1) / kWarps, kWarps * 32, smem, st>>>(tin, tout, frames, h->C, h->d_coef, h->d_hist, one, negzero);
     OLB_LAUNCHED();
     return OLB_OK;
+}
+
+template <int S, int MODE>
+static int launch_tma(olb_biquad *h, const float *in, float *out, uint32_t frames, cudaStream_t st) {
+    if (S == 8) {
+        const TmaCfg c = tma_cfg();
+        if (c.tb == 16 && c.stages == 4) return launch_tma_cfg<S, MODE, 16, 4>(h, in, out, frames, st);
+        if (c.tb == 32 && c.stages == 4) return launch_tma_cfg<S, MODE, 32, 4>(h, in, out, frames, st);
+        if (c.tb == 16 && c.stages == 6) return launch_tma_cfg<S, MODE, 16, 6>(h, in, out, frames, st);
+        if (c.tb == 8 && c.stages == 8) return launch_tma_cfg<S, MODE, 8, 8>(h, in, out, frames, st);
+        if (c.tb == 8 && c.stages == 4) return launch_tma_cfg<S, MODE, 8, 4>(h, in, out, frames, st);
+    }
+    return launch_tma_cfg<S, MODE, 32, 3>(h, in, out, frames, st);
 }
 
 template <int S, int MODE, bool GENERIC>
