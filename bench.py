@@ -34,7 +34,7 @@ def parse():
     p.add_argument("--channels", type=int, default=65536)
     p.add_argument("--sections", type=int, default=8)
     p.add_argument("--block-frames", type=int, default=24000, help="frames per step (0.5 s of audio at 48 kHz)")
-    p.add_argument("--mode", default="fma", choices=["fma", "exact"])
+    p.add_argument("--mode", default="fma", choices=["fast", "fma", "exact"])
     p.add_argument("--variant", type=int, default=0)
     p.add_argument("--e2e-frames", type=int, default=4800)
     p.add_argument("--e2e-steps", type=int, default=10)
@@ -101,7 +101,7 @@ def cpu_arm(args, target_seconds):
     from ol_dsp_b200 import c2_coefs
     orc = loader.oracle()
     threads = os.cpu_count() or 1
-    mode = loader.MODE_FMA if args.mode == "fma" else loader.MODE_EXACT
+    mode = {"fast": loader.MODE_FAST, "fma": loader.MODE_FMA, "exact": loader.MODE_EXACT}[args.mode]
     frames = 48000
     probe_ch = threads
     k = c2_coefs(max(probe_ch, 64))[:, :args.sections]
@@ -158,7 +158,7 @@ def run_olbank(args):
     import torch
     import torch.distributed as dist
 
-    from ol_dsp_b200 import MODE_EXACT, MODE_FMA, BiquadBank, _lib, c2_coefs, noise_device
+    from ol_dsp_b200 import MODE_EXACT, MODE_FAST, MODE_FMA, BiquadBank, _lib, c2_coefs, noise_device
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -174,7 +174,7 @@ def run_olbank(args):
 
     Cn, S, F = args.channels, args.sections, args.block_frames
     bank = BiquadBank(Cn, S, 48000.0, device=local)
-    bank.SetMode(MODE_FMA if args.mode == "fma" else MODE_EXACT)
+    bank.SetMode({"fast": MODE_FAST, "fma": MODE_FMA, "exact": MODE_EXACT}[args.mode])
     bank.SetVariant(args.variant)
     bank.SetCoeffs(c2_coefs(Cn)[:, :S])
     x = torch.empty((F, Cn), dtype=torch.float32, device="cuda")
@@ -253,7 +253,7 @@ def run_olbank(args):
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_launch": BYTES_PER_CHANNEL_SAMPLE * Cn * F,
-                         "fp32_lane_ops_per_channel_sample": 5 * S if args.mode == "fma" else 9 * S},
+                         "fp32_lane_ops_per_channel_sample": {"fast": 4 * S + 1, "fma": 5 * S, "exact": 9 * S}[args.mode]},
         }
         if e2e:
             line["e2e"] = e2e

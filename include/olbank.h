@@ -67,12 +67,21 @@ int olb_noise_fill(float *out_dev, uint32_t seed, uint32_t first_unit, uint32_t 
  *                    (bit-exact against the scalar oracle built with -ffp-contract=off)
  *   OLB_MODE_FMA     p = fma(b2,x2, b1*x1); p = fma(-a2,y2,p); p = fma(-a1,y1,p); y = fma(b0,x,p);
  *                    one-pole kinds are rewritten as biquads first (PORT: b0=1-c, a1=-c;
- *                    LPF: b0=f, a1=-(1-f)).  The throughput tier; within 1e-5 of full scale of EXACT. */
+ *                    LPF: b0=f, a1=-(1-f)).  Same operations as the oracle's FMA mode, so bit-exact to it.
+ *   OLB_MODE_FAST    the normalised fused cascade, 4 fused ops per section instead of 5 (the throughput tier):
+ *                    r1 = b1/b0, r2 = b2/b0 per section, G = prod(b0) per channel, all computed on the host in
+ *                    double and rounded to float;  v = G*x;  per section
+ *                    t = fma(r1,x1,v); t = fma(r2,x2,t); t = fma(-a2,y2,t); y = fma(-a1,y1,t).
+ *                    Bit-exact to the oracle's FAST mode; a tolerance tier against EXACT (DESIGN.md gives the
+ *                    measured error: it is as close to the float64 truth as EXACT is).  Node s of the cascade carries
+ *                    the signal times prod_{j>=s} b0_j and get/set_state speak that scaling.  A bank in which some
+ *                    channel has b0 == 0 (or a partial product outside [1e-30, 1e30]) runs the FMA arithmetic. */
 #define OLB_KIND_BIQUAD 0
 #define OLB_KIND_PORT 1
 #define OLB_KIND_LPF 2
 #define OLB_MODE_EXACT 0
 #define OLB_MODE_FMA 1
+#define OLB_MODE_FAST 2
 #define OLB_BIQUAD_MAX_SECTIONS 16
 
 typedef struct olb_biquad olb_biquad;

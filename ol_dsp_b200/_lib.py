@@ -14,7 +14,7 @@ HEADER_PATH = os.path.join(os.path.dirname(HERE), "include", "olbank.h")
 OK, E_ARG, E_CUDA, E_NCCL, E_STATE = 0, -1, -2, -3, -4
 LAYOUT_FRAMES, LAYOUT_PLANAR = 0, 1
 KIND_BIQUAD, KIND_PORT, KIND_LPF = 0, 1, 2
-MODE_EXACT, MODE_FMA = 0, 1
+MODE_EXACT, MODE_FMA, MODE_FAST = 0, 1, 2
 
 
 class OlbError(RuntimeError):

@@ -28,6 +28,7 @@
 
 #include "common.cuh"
 #include "tmap.h"
+#include "biquad_sys.cuh"
 
 namespace olb {
 
@@ -42,7 +43,12 @@ struct Kinds {
 template <int MODE>
 __device__ __forceinline__ float section_biquad(float x, float x1, float x2, float y1, float y2, float b0, float b1, float b2,
                                                 float na1, float na2) {
-    if (MODE == OLB_MODE_FMA) {
+    if (MODE == OLB_MODE_FAST) {  // b1, b2 hold r1 = b1/b0, r2 = b2/b0; x arrives pre-scaled (b0 slot unused)
+        float t = __fmaf_rn(b1, x1, x);
+        t = __fmaf_rn(b2, x2, t);
+        t = __fmaf_rn(na2, y2, t);
+        return __fmaf_rn(na1, y1, t);
+    } else if (MODE == OLB_MODE_FMA) {
         float p = __fmul_rn(b1, x1);
         p = __fmaf_rn(b2, x2, p);
         p = __fmaf_rn(na2, y2, p);
@@ -59,6 +65,7 @@ __device__ __forceinline__ float section_biquad(float x, float x1, float x2, flo
 // h[n][0] = newest, h[n][1] = the one before, for node n.  GENERIC: honour one-pole kinds (EXACT only).
 template <int S, int MODE, bool GENERIC>
 __device__ __forceinline__ float cascade_step(float v, float (&h)[S + 1][2], const float (&k)[S][5], const Kinds &kinds) {
+    if (MODE == OLB_MODE_FAST) v = __fmul_rn(k[0][0], v);  // G = prod(b0) sits in the b0 slot of section 0
 #pragma unroll
     for (int s = 0; s < S; s++) {
         float y;
@@ -148,9 +155,10 @@ __global__ void __launch_bounds__(128) k_bq_runtime(const float *in, float *out,
     const size_t stride = layout == OLB_LAYOUT_FRAMES ? C : 1;
     for (uint64_t t = 0; t < frames; t++) {
         float v = in[base + t * stride];
+        if (MODE == OLB_MODE_FAST) v = __fmul_rn(k[0][0], v);
         for (int s = 0; s < S; s++) {
             float y;
-            const int kind = MODE == OLB_MODE_FMA ? OLB_KIND_BIQUAD : kinds.k[s];
+            const int kind = MODE != OLB_MODE_EXACT ? OLB_KIND_BIQUAD : kinds.k[s];
             if (kind == OLB_KIND_PORT) y = __fadd_rn(v, __fmul_rn(k[s][0], __fsub_rn(h[s + 1][0], v)));
             else if (kind == OLB_KIND_LPF) y = __fadd_rn(h[s + 1][0], __fmul_rn(__fsub_rn(v, h[s + 1][0]), k[s][0]));
             else y = section_biquad<MODE>(v, h[s][0], h[s][1], h[s + 1][0], h[s + 1][1], k[s][0], k[s][1], k[s][2], k[s][3], k[s][4]);
@@ -222,7 +230,12 @@ __global__ void __launch_bounds__(128) k_bq_planar(const float *in, float *out, 
 template <int MODE>
 __device__ __forceinline__ u64 section_biquad2(u64 x, u64 x1, u64 x2, u64 y1, u64 y2, u64 b0, u64 b1, u64 b2, u64 na1, u64 na2,
                                                u64 one, u64 negzero) {
-    if (MODE == OLB_MODE_FMA) {
+    if (MODE == OLB_MODE_FAST) {
+        u64 t = ffma2(b1, x1, x);
+        t = ffma2(b2, x2, t);
+        t = ffma2(na2, y2, t);
+        return ffma2(na1, y1, t);
+    } else if (MODE == OLB_MODE_FMA) {
         u64 p = fmul2(b1, x1);
         p = ffma2(b2, x2, p);
         p = ffma2(na2, y2, p);
@@ -239,6 +252,7 @@ __device__ __forceinline__ u64 section_biquad2(u64 x, u64 x1, u64 x2, u64 y1, u6
 
 template <int S, int MODE>
 __device__ __forceinline__ u64 cascade_step2(u64 v, u64 (&h)[S + 1][2], const u64 (&k)[S][5], u64 one, u64 negzero) {
+    if (MODE == OLB_MODE_FAST) v = fmul2(k[0][0], v);
 #pragma unroll
     for (int s = 0; s < S; s++) {
         const u64 y = section_biquad2<MODE>(v, h[s][0], h[s][1], h[s + 1][0], h[s + 1][1], k[s][0], k[s][1], k[s][2], k[s][3],
@@ -341,8 +355,9 @@ struct olb_biquad {
     int device = 0;
     uint32_t C = 0, S = 0;
     float sample_rate = 0.f;
-    int mode = OLB_MODE_EXACT;
-    int variant = 0;  // 0 auto, 1 direct, 2 tma
+    int mode = OLB_MODE_EXACT;      // as set by the caller
+    int eff_mode = OLB_MODE_EXACT;  // arithmetic of the device table (FAST may drop to FMA, see upload_all)
+    int variant = 0;  // 0 auto, 1 direct, 2 tma (whole cascade per thread), 3 systolic (sections split over warps)
     Kinds kinds{};
     bool all_biquad = true;
     std::vector<float> coefs_host;  // [C][S][5] as the caller set them
@@ -357,30 +372,75 @@ struct olb_biquad {
     cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_run[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
 };
 
-static void effective_coefs(const olb_biquad *h, const float *in5, int s, float *out5) {
-    const int kind = h->kinds.k[s];
-    if (h->mode == OLB_MODE_FMA && kind == OLB_KIND_PORT) {
-        out5[0] = 1.0f - in5[0]; out5[1] = 0.f; out5[2] = 0.f; out5[3] = in5[0]; out5[4] = -0.f;  // -a1 = c, -a2 = -0
-    } else if (h->mode == OLB_MODE_FMA && kind == OLB_KIND_LPF) {
-        out5[0] = in5[0]; out5[1] = 0.f; out5[2] = 0.f; out5[3] = 1.0f - in5[0]; out5[4] = -0.f;
+// One-pole kinds as biquads (the FMA and FAST tiers run the biquad recurrence everywhere).
+static void as_biquad(int kind, const float *in5, float *k) {
+    if (kind == OLB_KIND_PORT) {
+        k[0] = 1.0f - in5[0]; k[1] = 0.f; k[2] = 0.f; k[3] = -in5[0]; k[4] = 0.f;
+    } else if (kind == OLB_KIND_LPF) {
+        k[0] = in5[0]; k[1] = 0.f; k[2] = 0.f; k[3] = -(1.0f - in5[0]); k[4] = 0.f;
     } else {
-        out5[0] = in5[0]; out5[1] = in5[1]; out5[2] = in5[2]; out5[3] = -in5[3]; out5[4] = -in5[4];
+        memcpy(k, in5, 5 * sizeof(float));
     }
 }
 
-// Rebuild the device table for channels [first, first+count) from the host copy.
+// FAST-tier table of one channel: out[s] = {G (s == 0 only), r1, r2, -a1, -a2}.  False when the channel cannot be
+// normalised (b0 == 0 / non-finite, or a node scale outside [1e-30, 1e30]).
+static bool fast_coefs(const olb_biquad *h, const float *chan, float *out) {
+    double g = 1.0;
+    for (uint32_t s = h->S; s-- > 0;) {
+        float k[5];
+        as_biquad(h->kinds.k[s], chan + 5 * s, k);
+        const double b0 = k[0];
+        if (!(b0 != 0.0) || !std::isfinite(b0)) return false;
+        g *= b0;
+        if (!(fabs(g) >= 1e-30 && fabs(g) <= 1e30)) return false;
+        out[5 * s + 0] = 0.f;
+        out[5 * s + 1] = (float) ((double) k[1] / b0);
+        out[5 * s + 2] = (float) ((double) k[2] / b0);
+        out[5 * s + 3] = -k[3];
+        out[5 * s + 4] = -k[4];
+    }
+    out[0] = (float) g;
+    return true;
+}
+
+static void effective_coefs(const olb_biquad *h, const float *in5, int s, float *out5) {
+    float k[5];
+    if (h->eff_mode != OLB_MODE_EXACT) as_biquad(h->kinds.k[s], in5, k);
+    else memcpy(k, in5, sizeof(k));
+    out5[0] = k[0]; out5[1] = k[1]; out5[2] = k[2]; out5[3] = -k[3]; out5[4] = -k[4];  // negation is exact
+}
+
+// Rebuild the device table for channels [first, first+count) from the host copy, in the arithmetic of h->eff_mode.
+// Returns OLB_E_STATE (without uploading) when eff_mode is FAST and one of the channels cannot be normalised.
 static int upload_coefs(olb_biquad *h, uint32_t first, uint32_t count) {
     const uint32_t S = h->S;
-    std::vector<float> stage((size_t) S * 5 * count);
-    for (uint32_t i = 0; i < count; i++)
-        for (uint32_t s = 0; s < S; s++) {
-            float e[5];
-            effective_coefs(h, &h->coefs_host[((size_t) (first + i) * S + s) * 5], (int) s, e);
-            for (int j = 0; j < 5; j++) stage[(size_t) (s * 5 + j) * count + i] = e[j];
+    std::vector<float> stage((size_t) S * 5 * count), e((size_t) S * 5);
+    for (uint32_t i = 0; i < count; i++) {
+        const float *chan = &h->coefs_host[(size_t) (first + i) * S * 5];
+        if (h->eff_mode == OLB_MODE_FAST) {
+            if (!fast_coefs(h, chan, e.data())) return OLB_E_STATE;
+        } else {
+            for (uint32_t s = 0; s < S; s++) effective_coefs(h, chan + 5 * s, (int) s, &e[5 * s]);
         }
+        for (uint32_t s = 0; s < S; s++)
+            for (int j = 0; j < 5; j++) stage[(size_t) (s * 5 + j) * count + i] = e[5 * s + j];
+    }
     OLB_CUDA(cudaMemcpy2D(h->d_coef + first, (size_t) h->C * sizeof(float), stage.data(), (size_t) count * sizeof(float),
                           (size_t) count * sizeof(float), (size_t) S * 5, cudaMemcpyHostToDevice));
     return OLB_OK;
+}
+
+// Full rebuild; a FAST bank with a channel that cannot be normalised drops to the FMA arithmetic.
+static int upload_all(olb_biquad *h) {
+    h->eff_mode = h->mode;
+    int rc = upload_coefs(h, 0, h->C);
+    if (rc == OLB_E_STATE && h->mode == OLB_MODE_FAST) {
+        h->eff_mode = OLB_MODE_FMA;
+        rc = upload_coefs(h, 0, h->C);
+    }
+    if (rc == OLB_OK) h->coef_dirty = false;
+    return rc;
 }
 
 OLB_API int olb_biquad_create(int device, uint32_t channels, uint32_t sections, float sample_rate, olb_biquad **out) {
@@ -454,7 +514,7 @@ OLB_API int olb_biquad_set_kinds(olb_biquad *h, const uint8_t *kinds, uint32_t s
 
 OLB_API int olb_biquad_set_mode(olb_biquad *h, int mode) {
     OLB_ARG(h, "olb_biquad_set_mode: NULL handle");
-    OLB_ARG(mode == OLB_MODE_EXACT || mode == OLB_MODE_FMA, "olb_biquad_set_mode: unknown mode %d", mode);
+    OLB_ARG(mode == OLB_MODE_EXACT || mode == OLB_MODE_FMA || mode == OLB_MODE_FAST, "olb_biquad_set_mode: unknown mode %d", mode);
     if (mode != h->mode) h->coef_dirty = true;
     h->mode = mode;
     return OLB_OK;
@@ -462,7 +522,7 @@ OLB_API int olb_biquad_set_mode(olb_biquad *h, int mode) {
 
 OLB_API int olb_biquad_set_variant(olb_biquad *h, int variant) {
     OLB_ARG(h, "olb_biquad_set_variant: NULL handle");
-    OLB_ARG(variant >= 0 && variant <= 2, "olb_biquad_set_variant: unknown variant %d", variant);
+    OLB_ARG(variant >= 0 && variant <= 3, "olb_biquad_set_variant: unknown variant %d", variant);
     h->variant = variant;
     return OLB_OK;
 }
@@ -476,7 +536,9 @@ OLB_API int olb_biquad_set_coeffs(olb_biquad *h, uint32_t first, uint32_t count,
     memcpy(&h->coefs_host[(size_t) first * h->S * 5], coefs_host, (size_t) count * h->S * 5 * sizeof(float));
     if (!h->coef_dirty) {
         DeviceGuard g(h->device);
-        return upload_coefs(h, first, count);
+        const int rc = upload_coefs(h, first, count);
+        if (rc != OLB_E_STATE) return rc;
+        h->coef_dirty = true;  // a FAST bank met a channel it cannot normalise: rebuild everything at the next process
     }
     return OLB_OK;
 }
@@ -516,7 +578,7 @@ OLB_API int olb_biquad_get_state(olb_biquad *h, float *state_host) {
     OLB_CUDA(cudaMemcpy(hist.data(), h->d_hist, hist.size() * sizeof(float), cudaMemcpyDeviceToHost));
     for (uint32_t c = 0; c < C; c++)
         for (uint32_t s = 0; s < S; s++) {
-            const bool full = h->mode == OLB_MODE_FMA || h->kinds.k[s] == OLB_KIND_BIQUAD;
+            const bool full = h->eff_mode != OLB_MODE_EXACT || h->kinds.k[s] == OLB_KIND_BIQUAD;
             float *o = state_host + ((size_t) c * S + s) * 4;
             o[0] = full ? hist[(size_t) (s * 2 + 0) * C + c] : 0.f;
             o[1] = full ? hist[(size_t) (s * 2 + 1) * C + c] : 0.f;
@@ -531,7 +593,7 @@ OLB_API int olb_biquad_set_state(olb_biquad *h, const float *state_host) {
     DeviceGuard g(h->device);
     const uint32_t C = h->C, S = h->S;
     std::vector<float> hist((size_t) (S + 1) * 2 * C, 0.f);
-    auto full = [&](uint32_t s) { return h->mode == OLB_MODE_FMA || h->kinds.k[s] == OLB_KIND_BIQUAD; };
+    auto full = [&](uint32_t s) { return h->eff_mode != OLB_MODE_EXACT || h->kinds.k[s] == OLB_KIND_BIQUAD; };
     for (uint32_t c = 0; c < C; c++) {
         const float *st = state_host + (size_t) c * S * 4;
         hist[(size_t) 0 * C + c] = st[0];
@@ -605,6 +667,72 @@ static int launch_tma(olb_biquad *h, const float *in, float *out, uint32_t frame
     return launch_tma_cfg<S, MODE, 32, 3>(h, in, out, frames, st);
 }
 
+// ---- k_bq_sys shapes ----------------------------------------------------------------------------
+// OLB_BQ_SYS_CFG="<SPW>x<TB>x<NST>x<PACK>" picks one of the compiled shapes (tuning aid).
+static bool sys_cfg_env(SysCfg *c) {
+    static int have = -1;
+    static SysCfg cfg{};
+    if (have < 0) {
+        have = 0;
+        if (const char *e = getenv("OLB_BQ_SYS_CFG"))
+            if (sscanf(e, "%dx%dx%dx%d", &cfg.spw, &cfg.tb, &cfg.nst, &cfg.pack) == 4) have = 1;
+    }
+    *c = cfg;
+    return have == 1;
+}
+
+// Automatic shape: packed lanes when that still gives every SM a CTA, scalar lanes below that.
+static SysCfg sys_cfg_auto(uint32_t C, uint32_t S) {
+    SysCfg c;
+    if (sys_cfg_env(&c)) return c;
+    if (C >= 64u * 148u) return SysCfg{S % 2 == 0 ? 2 : 1, 16, 7, 2};
+    // few channels: one section per warp, scalar lanes, and a DEEP ring -- a CTA must keep ~100 KiB of loads in flight
+    // to cover HBM latency on its own (profiles/r01_run7_small_banks.txt): 24 x 8 KiB stages with one CTA per SM,
+    // 24 x 4 KiB when two CTAs share an SM
+    if (S == 8) return C <= 32u * 148u ? SysCfg{1, 64, 24, 1} : SysCfg{1, 32, 24, 1};
+    return SysCfg{1, 16, 12, 1};
+}
+
+static bool sys_supported(uint32_t S) { return S == 2 || S == 4 || S == 6 || S == 8; }
+
+#define OLB_SYS_TRY(S_, SPW_, TB_, NST_, PACK_)                                                        \
+    if (S == S_ && c.spw == SPW_ && c.tb == TB_ && c.nst == NST_ && c.pack == PACK_)                   \
+        return launch_sys_cfg<S_, SPW_, MODE, TB_, NST_, PACK_>(h->C, h->d_coef, h->d_hist, in, out, frames, st);
+
+template <int MODE>
+static int launch_sys(olb_biquad *h, const float *in, float *out, uint32_t frames, cudaStream_t st) {
+    const uint32_t S = h->S;
+    SysCfg c = sys_cfg_auto(h->C, S);
+    if (S % c.spw) c.spw = 1;
+    OLB_SYS_TRY(8, 2, 16, 7, 2)
+    OLB_SYS_TRY(8, 2, 16, 6, 2)
+    OLB_SYS_TRY(8, 2, 8, 12, 2)
+    OLB_SYS_TRY(8, 2, 32, 6, 2)
+    OLB_SYS_TRY(8, 1, 8, 12, 2)
+    OLB_SYS_TRY(8, 1, 16, 12, 2)
+    OLB_SYS_TRY(8, 4, 16, 6, 2)
+    OLB_SYS_TRY(8, 4, 32, 3, 2)
+    OLB_SYS_TRY(8, 1, 16, 12, 1)
+    OLB_SYS_TRY(8, 1, 8, 16, 1)
+    OLB_SYS_TRY(8, 2, 16, 8, 1)
+    OLB_SYS_TRY(8, 1, 32, 24, 1)
+    OLB_SYS_TRY(8, 1, 64, 24, 1)
+    OLB_SYS_TRY(8, 1, 32, 48, 1)
+    OLB_SYS_TRY(8, 2, 64, 24, 1)
+    OLB_SYS_TRY(8, 1, 32, 24, 2)
+    OLB_SYS_TRY(8, 1, 32, 12, 2)
+    OLB_SYS_TRY(8, 2, 32, 24, 2)
+    OLB_SYS_TRY(8, 2, 16, 12, 1)
+    OLB_SYS_TRY(6, 2, 16, 7, 2)
+    OLB_SYS_TRY(6, 1, 16, 12, 1)
+    OLB_SYS_TRY(4, 2, 16, 7, 2)
+    OLB_SYS_TRY(4, 1, 16, 12, 1)
+    OLB_SYS_TRY(2, 2, 16, 7, 2)
+    OLB_SYS_TRY(2, 1, 16, 12, 1)
+    set_error("olb_biquad_process: no compiled systolic shape for S=%u spw=%d tb=%d nst=%d pack=%d", S, c.spw, c.tb, c.nst, c.pack);
+    return OLB_E_ARG;
+}
+
 template <int S, int MODE, bool GENERIC>
 static int launch_direct(olb_biquad *h, const float *in, float *out, uint64_t frames, int layout, cudaStream_t st) {
     if (layout == OLB_LAYOUT_FRAMES) {
@@ -618,40 +746,57 @@ static int launch_direct(olb_biquad *h, const float *in, float *out, uint64_t fr
 
 template <int S>
 static int dispatch_s(olb_biquad *h, const float *in, float *out, uint64_t frames, int layout, bool tma, cudaStream_t st) {
+    const int m = h->eff_mode;
     if (tma) {
-        return h->mode == OLB_MODE_FMA ? launch_tma<S, OLB_MODE_FMA>(h, in, out, (uint32_t) frames, st)
-                                       : launch_tma<S, OLB_MODE_EXACT>(h, in, out, (uint32_t) frames, st);
+        return m == OLB_MODE_FAST  ? launch_tma<S, OLB_MODE_FAST>(h, in, out, (uint32_t) frames, st)
+               : m == OLB_MODE_FMA ? launch_tma<S, OLB_MODE_FMA>(h, in, out, (uint32_t) frames, st)
+                                   : launch_tma<S, OLB_MODE_EXACT>(h, in, out, (uint32_t) frames, st);
     }
-    if (h->mode == OLB_MODE_FMA) return launch_direct<S, OLB_MODE_FMA, false>(h, in, out, frames, layout, st);
+    if (m == OLB_MODE_FAST) return launch_direct<S, OLB_MODE_FAST, false>(h, in, out, frames, layout, st);
+    if (m == OLB_MODE_FMA) return launch_direct<S, OLB_MODE_FMA, false>(h, in, out, frames, layout, st);
     if (h->all_biquad) return launch_direct<S, OLB_MODE_EXACT, false>(h, in, out, frames, layout, st);
     return launch_direct<S, OLB_MODE_EXACT, true>(h, in, out, frames, layout, st);
 }
 
 static int process_dev(olb_biquad *h, const float *in, float *out, uint64_t frames, int layout, cudaStream_t st) {
     if (h->coef_dirty) {
-        int rc = upload_coefs(h, 0, h->C);
+        int rc = upload_all(h);
         if (rc) return rc;
-        h->coef_dirty = false;
     }
     const uint32_t S = h->S;
     if (S > 8) {
         h->last_kernel = "k_bq_runtime";
-        if (h->mode == OLB_MODE_FMA)
+        if (h->eff_mode == OLB_MODE_FAST)
+            k_bq_runtime<OLB_MODE_FAST><<<(h->C + 127) / 128, 128, 0, st>>>(in, out, frames, h->C, (int) S, h->d_coef, h->d_hist, h->kinds, layout);
+        else if (h->eff_mode == OLB_MODE_FMA)
             k_bq_runtime<OLB_MODE_FMA><<<(h->C + 127) / 128, 128, 0, st>>>(in, out, frames, h->C, (int) S, h->d_coef, h->d_hist, h->kinds, layout);
         else
             k_bq_runtime<OLB_MODE_EXACT><<<(h->C + 127) / 128, 128, 0, st>>>(in, out, frames, h->C, (int) S, h->d_coef, h->d_hist, h->kinds, layout);
         OLB_LAUNCHED();
         return OLB_OK;
     }
-    const bool tma_ok = layout == OLB_LAYOUT_FRAMES && (h->mode == OLB_MODE_FMA || h->all_biquad) && (h->C % 4) == 0 &&
+    const bool tma_ok = layout == OLB_LAYOUT_FRAMES && (h->eff_mode != OLB_MODE_EXACT || h->all_biquad) && (h->C % 4) == 0 &&
                         (((uintptr_t) in | (uintptr_t) out) & 15) == 0 && frames < (1ull << 31);
-    bool tma = tma_ok && h->variant != 1;
-    if (h->variant == 2 && !tma_ok) {
-        set_error("olb_biquad_process: the TMA variant needs FRAMES layout, channels %% 4 == 0, 16-byte aligned buffers and biquad-only kinds in EXACT mode");
+    if (h->variant >= 2 && !tma_ok) {
+        set_error("olb_biquad_process: the TMA variants need FRAMES layout, channels %% 4 == 0, 16-byte aligned buffers and biquad-only kinds in EXACT mode");
         return OLB_E_ARG;
     }
-    // few channels: the packed kernel would leave most SMs without a warp; one channel per thread spreads wider
-    if (h->variant == 0 && tma && h->C < 64 * 148) tma = false;
+    if (h->variant == 3 && !sys_supported(S)) {
+        set_error("olb_biquad_process: the systolic variant is compiled for 2, 4, 6 and 8 sections");
+        return OLB_E_ARG;
+    }
+    // automatic choice (profiles/r01_run4_sys_sweep.txt): banks with a warp-group of 64 channels for every SM run the
+    // whole cascade per thread (k_bq_tma); smaller banks split the sections over the warps of a CTA (k_bq_sys, 8x the
+    // parallelism); tiny or unaligned ones run one channel per thread without TMA
+    bool tma = tma_ok && (h->variant == 2 || (h->variant == 0 && h->C >= 64u * 148u));
+    bool sys = !tma && tma_ok && sys_supported(S) && (h->variant == 3 || (h->variant == 0 && h->C >= 32u * 16u));
+    if (sys) {
+        h->last_kernel = "k_bq_sys";
+        const int m = h->eff_mode;
+        return m == OLB_MODE_FAST  ? launch_sys<OLB_MODE_FAST>(h, in, out, (uint32_t) frames, st)
+               : m == OLB_MODE_FMA ? launch_sys<OLB_MODE_FMA>(h, in, out, (uint32_t) frames, st)
+                                   : launch_sys<OLB_MODE_EXACT>(h, in, out, (uint32_t) frames, st);
+    }
     h->last_kernel = tma ? "k_bq_tma" : (layout == OLB_LAYOUT_FRAMES ? "k_bq_direct" : "k_bq_planar");
     switch (S) {
         case 1: return dispatch_s<1>(h, in, out, frames, layout, tma, st);

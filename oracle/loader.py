@@ -17,7 +17,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 
 EV_MIDI_CC, EV_HW_CC, EV_NOTE_ON, EV_NOTE_OFF, EV_INIT, EV_SET_FREQ, EV_GATE_ON, EV_GATE_OFF = range(8)
 KIND_BIQUAD, KIND_PORT, KIND_LPF = 0, 1, 2
-MODE_EXACT, MODE_FMA = 0, 1
+MODE_EXACT, MODE_FMA, MODE_FAST = 0, 1, 2
 LAYOUT_FRAMES, LAYOUT_PLANAR = 0, 1
 
 

@@ -125,7 +125,14 @@ ORC_API void orc_noise_fill(uint32_t seed, uint32_t first_channel, uint32_t chan
 //              p = fma(b2,x2, b1*x1); p = fma(-a2,y2,p); p = fma(-a1,y1,p); y = fma(b0,x,p)
 //            one-pole kinds are first rewritten as biquads:  PORT: b0 = 1-c, a1 = -c;  LPF: b0 = f, a1 = -(1-f)
 enum { ORC_KIND_BIQUAD = 0, ORC_KIND_PORT = 1, ORC_KIND_LPF = 2 };
-enum { ORC_MODE_EXACT = 0, ORC_MODE_FMA = 1 };
+//   2 FAST   the normalised fused cascade (the throughput tier; tolerance, not bit-equal to EXACT):
+//            one-pole kinds rewritten as in FMA; per section r1 = b1/b0, r2 = b2/b0 (double division, rounded to
+//            float); per channel G = prod(b0) (double product, rounded to float); v = G*x, then per section
+//              t = fma(r1,x1,v); t = fma(r2,x2,t); t = fma(-a2,y2,t); y = fma(-a1,y1,t)
+//            so node s of the cascade carries the true signal times prod_{j>=s} b0_j (state is kept in that scaling).
+//            Needs every b0 finite and non-zero and every partial product within [1e-30, 1e30]
+//            (orc_biquad_fast_coefs returns 0 otherwise and callers fall back to FMA).
+enum { ORC_MODE_EXACT = 0, ORC_MODE_FMA = 1, ORC_MODE_FAST = 2 };
 enum { ORC_LAYOUT_FRAMES = 0 /* [T][C] */, ORC_LAYOUT_PLANAR = 1 /* [C][T] */ };
 
 static inline float biquad_exact(const float *k, float *s, float x) {
@@ -156,13 +163,50 @@ ORC_API void orc_biquad_fma_coefs(int kind, const float *in5, float *out5) {
     }
 }
 
+// out: [sections][4] = r1 r2 -a1 -a2, *gain = G.  Returns 1 when the channel can run in FAST mode.
+ORC_API int orc_biquad_fast_coefs(uint32_t sections, const uint8_t *kinds, const float *coefs, float *out4, float *gain) {
+    double g = 1.0;
+    int ok = 1;
+    for (uint32_t s = sections; s-- > 0;) {  // partial products from the output side: the scale of node s
+        float k[5];
+        orc_biquad_fma_coefs(kinds ? kinds[s] : 0, coefs + 5 * s, k);
+        const double b0 = k[0];
+        if (!(b0 != 0.0) || !std::isfinite(b0)) { ok = 0; break; }
+        g *= b0;
+        if (!(fabs(g) >= 1e-30 && fabs(g) <= 1e30)) { ok = 0; break; }
+        out4[4 * s + 0] = (float) ((double) k[1] / b0);
+        out4[4 * s + 1] = (float) ((double) k[2] / b0);
+        out4[4 * s + 2] = -k[3];
+        out4[4 * s + 3] = -k[4];
+    }
+    *gain = (float) g;
+    return ok;
+}
+
+static inline float biquad_fast(const float *k4, float *s, float x) {
+    float t = __builtin_fmaf(k4[0], s[0], x);
+    t = __builtin_fmaf(k4[1], s[1], t);
+    t = __builtin_fmaf(k4[3], s[3], t);
+    float y = __builtin_fmaf(k4[2], s[2], t);
+    s[1] = s[0]; s[0] = x; s[3] = s[2]; s[2] = y;
+    return y;
+}
+
 static void biquad_channel(int mode, uint32_t sections, const uint8_t *kinds, const float *coefs, float *state,
                            const float *in, float *out, uint64_t frames, uint64_t stride) {
     float kf[64 * 5];
+    float gain = 1.f;
+    if (mode == ORC_MODE_FAST && !orc_biquad_fast_coefs(sections, kinds, coefs, kf, &gain)) mode = ORC_MODE_FMA;
     if (mode == ORC_MODE_FMA)
         for (uint32_t s = 0; s < sections; s++) orc_biquad_fma_coefs(kinds ? kinds[s] : 0, coefs + 5 * s, kf + 5 * s);
     for (uint64_t t = 0; t < frames; t++) {
         float v = in[t * stride];
+        if (mode == ORC_MODE_FAST) {
+            v = gain * v;
+            for (uint32_t s = 0; s < sections; s++) v = biquad_fast(kf + 4 * s, state + 4 * s, v);
+            out[t * stride] = v;
+            continue;
+        }
         for (uint32_t s = 0; s < sections; s++) {
             const float *k = coefs + 5 * s;
             float *st = state + 4 * s;
@@ -194,6 +238,11 @@ ORC_API int orc_biquad_run(int mode, uint32_t channels, uint32_t sections, const
                            float *state, const float *in, float *out, uint64_t frames, int layout) {
     if (sections > 64) return -1;
     std::vector<float> tmp(4 * (size_t) sections);
+    if (mode == ORC_MODE_FAST) {  // the decision is per BANK: one channel that cannot be normalised sends all to FMA
+        float k4[64 * 4], g;
+        for (uint32_t c = 0; c < channels && mode == ORC_MODE_FAST; c++)
+            if (!orc_biquad_fast_coefs(sections, kinds, coefs + (size_t) c * sections * 5, k4, &g)) mode = ORC_MODE_FMA;
+    }
     for (uint32_t c = 0; c < channels; c++) {
         float *st = state ? state + (size_t) c * sections * 4 : tmp.data();
         if (!state) memset(st, 0, sizeof(float) * 4 * sections);

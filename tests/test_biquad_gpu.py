@@ -6,12 +6,13 @@ import pytest
 import torch
 
 from oracle import loader
-from ol_dsp_b200 import (KIND_LPF, KIND_PORT, LAYOUT_FRAMES, LAYOUT_PLANAR, MODE_EXACT, MODE_FMA, BiquadBank, OlbError,
+from ol_dsp_b200 import (KIND_LPF, KIND_PORT, LAYOUT_FRAMES, LAYOUT_PLANAR, MODE_EXACT, MODE_FAST, MODE_FMA, BiquadBank, OlbError,
                          _lib, c2_coefs, noise_device)
 
 pytestmark = pytest.mark.gpu
 
-V_AUTO, V_DIRECT, V_TMA = 0, 1, 2
+V_AUTO, V_DIRECT, V_TMA, V_SYS = 0, 1, 2, 3
+KNAME = {V_DIRECT: "k_bq_direct", V_TMA: "k_bq_tma", V_SYS: "k_bq_sys"}
 
 
 def bits(a):
@@ -49,13 +50,14 @@ def test_noise_matches_oracle(orc):
 
 
 @pytest.mark.parametrize("mode", [MODE_EXACT, MODE_FMA])
-@pytest.mark.parametrize("variant,C", [(V_DIRECT, 256), (V_DIRECT, 77), (V_TMA, 256), (V_TMA, 68), (V_TMA, 4)])
+@pytest.mark.parametrize("variant,C", [(V_DIRECT, 256), (V_DIRECT, 77), (V_TMA, 256), (V_TMA, 68), (V_TMA, 4),
+                                       (V_SYS, 256), (V_SYS, 68), (V_SYS, 4), (V_SYS, 9600)])
 def test_c2_cascade_bit_exact(orc, mode, variant, C):
     T = 2051  # ragged: not a multiple of any tile height
     x = orc.noise(1, 0, C, 0, T)
     k = c2_coefs(C)
     y, name, st = run_bank(x, k, mode, variant)
-    assert name == ("k_bq_tma" if variant == V_TMA else "k_bq_direct")
+    assert name == KNAME[variant]
     ost = np.zeros((C, 8, 4), dtype=np.float32)
     want = orc.biquad(x, k, mode=mode, state=ost)
     assert np.array_equal(bits(y), bits(want))
@@ -88,7 +90,7 @@ def test_one_pole_kinds_reproduce_port_and_verb_lpf(orc, mode):
     assert np.array_equal(bits(st), bits(ost))
 
 
-@pytest.mark.parametrize("variant", [V_DIRECT, V_TMA])
+@pytest.mark.parametrize("variant", [V_DIRECT, V_TMA, V_SYS])
 def test_state_carries_across_calls_and_per_frame_process(orc, variant):
     C, T = 64, 300
     x = orc.noise(4, 0, C, 0, T)
@@ -175,6 +177,65 @@ def test_in_place_device_call_and_large_bank_properties(orc):
     torch.cuda.synchronize()
     assert torch.equal(out, dev)
     b.close()
+
+
+@pytest.mark.parametrize("S", [2, 4, 6, 8])
+@pytest.mark.parametrize("mode", [MODE_EXACT, MODE_FMA])
+@pytest.mark.parametrize("C", [132, 9600])
+def test_systolic_shapes_bit_exact(orc, S, mode, C):
+    """k_bq_sys: sections split over the warps of a CTA (scalar lanes below 9,472 channels, packed lanes
+    above); ragged frame count, two calls so the per-warp history hand-over is exercised."""
+    T = 777
+    x = orc.noise(21, 0, C, 0, T)
+    k = np.ascontiguousarray(c2_coefs(C)[:, :S])
+    y, name, st = run_bank(x, k, mode, V_SYS, chunks=[500, 277])
+    assert name == "k_bq_sys"
+    ost = np.zeros((C, S, 4), dtype=np.float32)
+    want = orc.biquad(x, k, mode=mode, state=ost)
+    assert np.array_equal(bits(y), bits(want))
+    assert np.array_equal(bits(st), bits(ost))
+
+
+@pytest.mark.parametrize("variant,C,S", [(V_DIRECT, 77, 8), (V_TMA, 260, 8), (V_SYS, 132, 8), (V_SYS, 9600, 8), (V_TMA, 64, 3),
+                                         (V_DIRECT, 64, 12), (V_SYS, 64, 4)])
+def test_fast_mode_bit_exact_to_oracle_fast_and_close_to_exact(orc, variant, C, S):
+    """OLB_MODE_FAST (normalised 4-op sections): same operations as the oracle's FAST mode -> bit-exact to it;
+    against EXACT it is a tolerance tier (bound measured in DESIGN.md; both are compared with the float64 cascade)."""
+    T = 1500
+    x = orc.noise(31, 0, C, 0, T)
+    k = np.ascontiguousarray(np.concatenate([c2_coefs(C), c2_coefs(C)[:, 4:]], axis=1)[:, :S])
+    y, name, st = run_bank(x, k, MODE_FAST, variant, chunks=[700, 800])
+    ost = np.zeros((C, S, 4), dtype=np.float32)
+    want = orc.biquad(x, k, mode=loader.MODE_FAST, state=ost)
+    assert np.array_equal(bits(y), bits(want)), name
+    assert np.array_equal(bits(st), bits(ost))
+    exact = orc.biquad(x, k, mode=MODE_EXACT)
+    truth = orc.biquad_f64(x, k)
+    # fp32 itself sits ~1e-4 from the float64 cascade on this coefficient set (30 Hz high-pass, pole radius 0.997):
+    # FAST must be no further from the truth than EXACT is (x2 slack), and within 1e-3 of EXACT
+    assert np.abs(y - truth).max() <= 2.0 * np.abs(exact - truth).max() + 1e-6
+    assert np.abs(y - exact).max() <= 1e-3
+
+
+def test_fast_mode_falls_back_to_fma_when_a_section_has_zero_b0(orc):
+    C, T = 64, 400
+    x = orc.noise(32, 0, C, 0, T)
+    k = c2_coefs(C).copy()
+    k[5, 3] = (0.0, 1.0, 0.0, 0.0, 0.0)  # a pure one-sample delay: b0 == 0 cannot be normalised
+    y, _, _ = run_bank(x, k, MODE_FAST)
+    assert np.array_equal(bits(y), bits(orc.biquad(x, k, mode=MODE_FMA)))
+
+
+def test_fast_mode_one_pole_kinds(orc):
+    C, T = 64, 600
+    x = orc.noise(33, 0, C, 0, T)
+    k = c2_coefs(C)[:, :4].copy()
+    k[:, 1, 0] = 0.85
+    k[:, 3, 0] = 0.999
+    kinds = np.array([0, KIND_LPF, 0, KIND_PORT], dtype=np.uint8)
+    y, _, _ = run_bank(x, k, MODE_FAST, kinds=kinds)
+    assert np.array_equal(bits(y), bits(orc.biquad(x, k, kinds=kinds, mode=loader.MODE_FAST)))
+    assert np.abs(y - orc.biquad(x, k, kinds=kinds, mode=MODE_EXACT)).max() <= 1e-3
 
 
 def test_errors():
