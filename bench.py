@@ -34,7 +34,8 @@ def parse():
     p.add_argument("--channels", type=int, default=65536)
     p.add_argument("--sections", type=int, default=8)
     p.add_argument("--block-frames", type=int, default=24000, help="frames per step (0.5 s of audio at 48 kHz)")
-    p.add_argument("--mode", default="fma", choices=["fast", "fma", "exact"])
+    p.add_argument("--mode", default="fast", choices=["fast", "fma", "exact"],
+                   help="fast: normalised 4-op sections (throughput tier); fma: fused 5-op; exact: separately rounded (bit-exact tier)")
     p.add_argument("--variant", type=int, default=0)
     p.add_argument("--e2e-frames", type=int, default=4800)
     p.add_argument("--e2e-steps", type=int, default=10)

@@ -50,3 +50,46 @@ def test_no_cpu_fallback_without_gpu():
         BiquadBank(64, 8)
     assert e.value.code == _lib.E_CUDA
     assert "no CPU fallback" in str(e.value)
+
+
+def test_cpp_host_mirror_builds_and_fails_loudly_without_gpu(tmp_path):
+    """include/ol_gpu/BiquadBank.hpp: a reference-style C++ caller links against the C ABI; without a GPU its
+    Init() reports the error instead of computing anything on the CPU."""
+    import os
+    import subprocess
+
+    import __graft_entry__ as g
+    g.build_cpp_hosts()
+    exe = os.path.join(g.ROOT, "tests", "cpp", "biquad_host")
+    assert os.path.exists(exe)
+    if _lib.device_count() > 0:
+        pytest.skip("a GPU is present")
+    x = np.zeros((4, 8), dtype=np.float32)
+    k = np.zeros((8, 8, 5), dtype=np.float32)
+    x.tofile(tmp_path / "in.f32")
+    k.tofile(tmp_path / "k.f32")
+    r = subprocess.run([exe, "8", "4", str(tmp_path / "in.f32"), str(tmp_path / "k.f32"), str(tmp_path / "out.f32"), "0"],
+                       capture_output=True, text=True)
+    assert r.returncode == 4 and "no CPU fallback" in r.stderr
+
+
+def test_product_never_touches_the_oracle():
+    """Nothing under ol_dsp_b200/ or include/ may import, link or load oracle/ (the oracle is test infrastructure)."""
+    import os
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    bad = []
+    for top in ("ol_dsp_b200", "include"):
+        for d, _, files in os.walk(os.path.join(root, top)):
+            if "build" in d.split(os.sep) or "__pycache__" in d:
+                continue
+            for f in files:
+                if f.endswith((".py", ".cu", ".cuh", ".h", ".hpp", "Makefile")):
+                    txt = open(os.path.join(d, f), errors="ignore").read()
+                    if re.search(r"(import|from)\s+oracle|oracle/|libolb_oracle|libolref", txt):
+                        # comments that merely CITE the oracle file for op order are allowed
+                        lines = [ln for ln in txt.splitlines() if re.search(r"oracle", ln) and not ln.lstrip().startswith(("//", "#", "*", "/*"))
+                                 and "//" not in ln.split("oracle")[0]]
+                        if lines:
+                            bad.append((f, lines[:2]))
+    assert not bad, bad

@@ -238,6 +238,27 @@ def test_fast_mode_one_pole_kinds(orc):
     assert np.abs(y - orc.biquad(x, k, kinds=kinds, mode=MODE_EXACT)).max() <= 1e-3
 
 
+@pytest.mark.parametrize("mode", [MODE_EXACT, MODE_FAST])
+def test_cpp_host_mirror_matches_oracle(orc, mode, tmp_path):
+    """A C++ caller written against include/ol_gpu/BiquadBank.hpp (Init -> SetCoeffs -> Process per frame -> ProcessBlock)."""
+    import os
+    import subprocess
+
+    import __graft_entry__ as g
+    g.build_cpp_hosts()
+    C, T = 256, 500
+    x = orc.noise(41, 0, C, 0, T)
+    k = c2_coefs(C)
+    x.tofile(tmp_path / "in.f32")
+    k.tofile(tmp_path / "k.f32")
+    exe = os.path.join(g.ROOT, "tests", "cpp", "biquad_host")
+    r = subprocess.run([exe, str(C), str(T), str(tmp_path / "in.f32"), str(tmp_path / "k.f32"), str(tmp_path / "out.f32"), str(mode)],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    y = np.fromfile(tmp_path / "out.f32", dtype=np.float32).reshape(T, C)
+    assert np.array_equal(bits(y), bits(orc.biquad(x, k, mode=mode)))
+
+
 def test_errors():
     b = BiquadBank(8, 2)
     with pytest.raises(OlbError):

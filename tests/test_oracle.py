@@ -147,3 +147,21 @@ def test_biquad_oracle_properties(orc):
     ye = orc.biquad(x, k2, kinds=kinds)
     yf2 = orc.biquad(x, k2, kinds=kinds, mode=loader.MODE_FMA)
     assert np.abs(ye - yf2).max() < 1e-3 and np.isfinite(ye).all()
+
+
+def test_biquad_tiers_error_budget(orc):
+    """The three arithmetic tiers over the FULL 10 s of the C2 workload (16 of its 64 coefficient sets), against the
+    float64 cascade.  float32 DF1 itself is ~3e-4 from the truth here (30 Hz high-pass, pole radius 0.997), so the
+    fast tiers are held to: no further from the truth than EXACT (x1.5 slack) and within 1e-3 of EXACT."""
+    from ol_dsp_b200 import c2_coefs  # host-side RBJ designer only; bit-equal to orc.rbj (tests/test_abi.py)
+    k = np.ascontiguousarray(c2_coefs(64)[::4])
+    C, T = k.shape[0], 480000
+    x = orc.noise(0x01D5B200, 0, C, 0, T)
+    truth = orc.biquad_f64(x, k)
+    e = orc.biquad(x, k, mode=loader.MODE_EXACT)
+    err_e = np.abs(e - truth).max()
+    assert 1e-5 < err_e < 1e-3
+    for mode in (loader.MODE_FMA, loader.MODE_FAST):
+        y = orc.biquad(x, k, mode=mode)
+        assert np.abs(y - truth).max() <= 1.5 * err_e
+        assert np.abs(y - e).max() <= 1e-3
