@@ -117,6 +117,36 @@ int olb_biquad_set_state(olb_biquad *h, const float *state_host);
 const char *olb_biquad_last_kernel(olb_biquad *h);
 int olb_biquad_set_variant(olb_biquad *h, int variant);
 
+/* (a7) Dattorro plate reverb bank -------------------------------------------------------------------
+ * Replaces libs/dattorro-verb/verb.h:5-26 for `instances` plates at once (mono in, stereo wet out):
+ *   DattorroVerb_create / initialize (verb.cpp:173-222, 225-232)  -> olb_dattorro_create, olb_dattorro_init
+ *   DattorroVerb_delete (verb.cpp:235-251)                         -> olb_dattorro_destroy
+ *   DattorroVerb_setPreDelay .. _setDamping (verb.cpp:136-170)     -> olb_dattorro_set_param(s)
+ *   DattorroVerb_process + _getLeft + _getRight (verb.cpp:258-326) -> olb_dattorro_process
+ * Every instance of a bank shares the reference's 16-bit sample counter `t` (they are created and ticked together).
+ * Results are bit-exact against verb.cpp compiled with -ffp-contract=off. */
+#define OLB_PLATE_PREDELAY 0         /* DattorroVerb_setPreDelay: fraction of 4 800 samples */
+#define OLB_PLATE_PREFILTER 1        /* DattorroVerb_setPreFilter */
+#define OLB_PLATE_INPUT_DIFFUSION1 2 /* DattorroVerb_setInputDiffusion1 */
+#define OLB_PLATE_INPUT_DIFFUSION2 3 /* DattorroVerb_setInputDiffusion2 */
+#define OLB_PLATE_DECAY 4            /* DattorroVerb_setDecay (also derives decay diffusion 2) */
+#define OLB_PLATE_DECAY_DIFFUSION 5  /* DattorroVerb_setDecayDiffusion */
+#define OLB_PLATE_DAMPING 6          /* DattorroVerb_setDamping */
+
+typedef struct olb_dattorro olb_dattorro;
+
+int olb_dattorro_create(int device, uint32_t instances, olb_dattorro **out);
+int olb_dattorro_destroy(olb_dattorro *h);
+/* initialize(): rings, filters, counter cleared; parameters back to the reference defaults (verb.cpp:215-221). */
+int olb_dattorro_init(olb_dattorro *h);
+/* One value for instances [first, first+count) / one value per instance (values[i * stride]).  Effective at the next
+ * process call. */
+int olb_dattorro_set_param(olb_dattorro *h, uint32_t first, uint32_t count, int param, float value);
+int olb_dattorro_set_params(olb_dattorro *h, uint32_t first, uint32_t count, int param, const float *values_host, uint32_t stride);
+/* For each frame: DattorroVerb_process(in); out_l = getLeft(); out_r = getRight().  Device buffers, all
+ * [frames][instances] (instance fastest). */
+int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *out_l_dev, float *out_r_dev, uint64_t frames, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -64,6 +64,12 @@ def lib():
         "olb_biquad_set_state": ([vp, _F], i32),
         "olb_biquad_last_kernel": ([vp], C.c_char_p),
         "olb_biquad_set_variant": ([vp, i32], i32),
+        "olb_dattorro_create": ([i32, u32, C.POINTER(vp)], i32),
+        "olb_dattorro_destroy": ([vp], i32),
+        "olb_dattorro_init": ([vp], i32),
+        "olb_dattorro_set_param": ([vp, u32, u32, i32, f32], i32),
+        "olb_dattorro_set_params": ([vp, u32, u32, i32, _F, u32], i32),
+        "olb_dattorro_process": ([vp, vp, vp, vp, u64, vp], i32),
     }
     for name, (args, res) in sig.items():
         f = getattr(L, name)

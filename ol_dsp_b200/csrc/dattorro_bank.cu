@@ -1,0 +1,304 @@
+// dattorro_bank.cu -- (a7) bank of Dattorro plate reverbs.
+//
+// Reference: libs/dattorro-verb/verb.cpp:258-326 (DattorroVerb_process / _getLeft / _getRight), ring sizes and
+// taps :173-222, setters :136-170, state libs/dattorro-verb/verb_structs.h:12-56.  One reference object = one
+// mono-in / stereo-out plate with 13 power-of-two ring buffers (42 368 floats), three one-pole low-passes and a
+// 16-bit sample counter `t` that also drives a +-16-sample excursion of two all-pass delays every 2 048 samples.
+//
+// Bank layout in HBM
+//   rings   [42 368 ring positions][instances]   instance fastest.  Every instance of a bank is created and ticked
+//           together, so they share `t` and therefore every ring index (only the pre-delay length is a per-instance
+//           parameter): a warp's 32 instances read and write 128 contiguous bytes per tap -> fully coalesced.
+//   lp      [3][instances]   pre-filter and the two damping one-poles
+//   par     [8][instances]   pre_filter in_diff1 in_diff2 decay_diff1 damping decay decay_diff2 pre_delay_offset
+//   audio   in [frames][instances], out_l / out_r [frames][instances]
+//
+// Kernel: one instance per thread, time-sequential, every float operation rounded separately in the reference's
+// order (bit-exact against verb.cpp compiled with -ffp-contract=off).  All 13 main-tap reads and 14 output-tap reads
+// of a sample are independent of that sample's arithmetic (every delay is >= 107 samples), so they are issued
+// together at the top of the iteration and the chain of filters then runs out of registers.
+#include <math.h>
+
+#include <vector>
+
+#include "common.cuh"
+
+namespace olb {
+
+enum { DV_PRE, DV_IN0, DV_IN1, DV_IN2, DV_IN3, DV_DD1A, DV_PDA, DV_DD2A, DV_POSTA, DV_DD1B, DV_PDB, DV_DD2B, DV_POSTB, DV_RINGS };
+
+struct PlateGeom {
+    uint32_t base[DV_RINGS];  // first ring position of each ring in the slab
+    uint32_t mask[DV_RINGS];
+    uint32_t off[DV_RINGS];   // main-tap read offset = size - delay (DD1A / DD1B: current excursion value)
+    uint32_t tap_l[7][2];     // {ring, read offset}, summed + + - + - - +  (verb.cpp:302-326)
+    uint32_t tap_r[7][2];
+};
+
+static const uint16_t kDelay[DV_RINGS] = {4800, 142, 107, 379, 277, 672, 4453, 1800, 3720, 908, 4217, 2656, 3163};
+static const uint16_t kTapL[7][2] = {{DV_PDB, 266}, {DV_PDB, 2974}, {DV_DD2B, 1913}, {DV_POSTB, 1996}, {DV_PDA, 1990}, {DV_DD2A, 187}, {DV_POSTA, 1066}};
+static const uint16_t kTapR[7][2] = {{DV_PDA, 353}, {DV_PDA, 3627}, {DV_DD2A, 1228}, {DV_POSTA, 2673}, {DV_PDB, 2111}, {DV_DD2B, 335}, {DV_POSTB, 121}};
+
+// buffer size = 2^(bit length of the delay)  (DelayBuffer_init, verb.cpp:67-81)
+static uint32_t ring_size(uint16_t delay) {
+    uint32_t bits = 0;
+    for (uint16_t x = delay; x; x >>= 1) bits++;
+    return 1u << bits;
+}
+
+#define RING(g, ring, idx) slab[(size_t) ((g).base[ring] + ((idx) & (g).mask[ring])) * I + inst]
+
+__device__ __forceinline__ float allpass(float delayed, float gain, float in, float &to_write) {  // verb.cpp:123-128
+    in = __fadd_rn(in, __fmul_rn(delayed, -gain));
+    to_write = in;
+    return __fadd_rn(delayed, __fmul_rn(in, gain));
+}
+__device__ __forceinline__ float lowpass(float &z, float f, float in) {  // verb.cpp:131-134
+    z = __fadd_rn(z, __fmul_rn(__fsub_rn(in, z), f));
+    return z;
+}
+
+__global__ void __launch_bounds__(64) k_dattorro(const float *__restrict__ in, float *__restrict__ out_l, float *__restrict__ out_r,
+                                                 uint32_t frames, uint32_t I, float *slab, float *lp, const float *__restrict__ par,
+                                                 const __grid_constant__ PlateGeom g0, uint32_t t0) {
+    const uint32_t inst = blockIdx.x * blockDim.x + threadIdx.x;
+    if (inst >= I) return;
+    const float pre_filter = par[0 * (size_t) I + inst], in_diff1 = par[1 * (size_t) I + inst], in_diff2 = par[2 * (size_t) I + inst];
+    const float decay_diff1 = par[3 * (size_t) I + inst], damping = par[4 * (size_t) I + inst], decay = par[5 * (size_t) I + inst];
+    const float decay_diff2 = par[6 * (size_t) I + inst];
+    const uint32_t pre_off = __float_as_uint(par[7 * (size_t) I + inst]);
+    float z_pre = lp[inst], z_a = lp[(size_t) I + inst], z_b = lp[2 * (size_t) I + inst];
+    uint32_t off_a = g0.off[DV_DD1A], off_b = g0.off[DV_DD1B];
+    uint32_t t = t0;  // 16-bit counter kept in 32 bits, wrapped explicitly
+    const bool pre_same = ((pre_off & g0.mask[DV_PRE]) == 0);  // pre-delay of 0 samples reads what was just written
+
+    for (uint32_t n = 0; n < frames; n++) {
+        if ((t & 0x07ffu) == 0) {  // excursion (verb.cpp:262-270); offsets are uint16 in the reference
+            if (t < (1u << 15)) { off_a = (off_a - 1) & 0xffffu; off_b = (off_b - 1) & 0xffffu; }
+            else { off_a = (off_a + 1) & 0xffffu; off_b = (off_b + 1) & 0xffffu; }
+        }
+        // ---- every read of this sample (none depends on this sample's writes, see header) ----
+        const float xin = in[(size_t) n * I + inst];
+        const float r_pre = RING(g0, DV_PRE, t + pre_off);
+        const float r_in0 = RING(g0, DV_IN0, t + g0.off[DV_IN0]), r_in1 = RING(g0, DV_IN1, t + g0.off[DV_IN1]);
+        const float r_in2 = RING(g0, DV_IN2, t + g0.off[DV_IN2]), r_in3 = RING(g0, DV_IN3, t + g0.off[DV_IN3]);
+        const float r_postb = RING(g0, DV_POSTB, t + g0.off[DV_POSTB]), r_posta = RING(g0, DV_POSTA, t + g0.off[DV_POSTA]);
+        const float r_dd1a = RING(g0, DV_DD1A, t + off_a), r_dd1b = RING(g0, DV_DD1B, t + off_b);
+        const float r_pda = RING(g0, DV_PDA, t + g0.off[DV_PDA]), r_pdb = RING(g0, DV_PDB, t + g0.off[DV_PDB]);
+        const float r_dd2a = RING(g0, DV_DD2A, t + g0.off[DV_DD2A]), r_dd2b = RING(g0, DV_DD2B, t + g0.off[DV_DD2B]);
+        float tl[7], tr[7];
+        const uint32_t t1 = (t + 1) & 0xffffu;
+#pragma unroll
+        for (int i = 0; i < 7; i++) {
+            tl[i] = RING(g0, g0.tap_l[i][0], t1 + g0.tap_l[i][1]);
+            tr[i] = RING(g0, g0.tap_r[i][0], t1 + g0.tap_r[i][1]);
+        }
+        // ---- the network (verb.cpp:272-295) ----
+        float w;
+        RING(g0, DV_PRE, t) = xin;
+        float x = pre_same ? xin : r_pre;
+        x = lowpass(z_pre, pre_filter, x);
+        x = allpass(r_in0, in_diff1, x, w); RING(g0, DV_IN0, t) = w;
+        x = allpass(r_in1, in_diff1, x, w); RING(g0, DV_IN1, t) = w;
+        x = allpass(r_in2, in_diff2, x, w); RING(g0, DV_IN2, t) = w;
+        x = allpass(r_in3, in_diff2, x, w); RING(g0, DV_IN3, t) = w;
+        // half 0 (cross feedback from POSTB), then half 1 (from POSTA, written 3 720 samples ago)
+        float y = __fadd_rn(x, __fmul_rn(r_postb, decay));
+        y = allpass(r_dd1a, -decay_diff1, y, w); RING(g0, DV_DD1A, t) = w;
+        RING(g0, DV_PDA, t) = y; y = r_pda;
+        y = lowpass(z_a, damping, y);
+        y = __fmul_rn(y, decay);
+        y = allpass(r_dd2a, decay_diff2, y, w); RING(g0, DV_DD2A, t) = w;
+        RING(g0, DV_POSTA, t) = y;
+        y = __fadd_rn(x, __fmul_rn(r_posta, decay));
+        y = allpass(r_dd1b, -decay_diff1, y, w); RING(g0, DV_DD1B, t) = w;
+        RING(g0, DV_PDB, t) = y; y = r_pdb;
+        y = lowpass(z_b, damping, y);
+        y = __fmul_rn(y, decay);
+        y = allpass(r_dd2b, decay_diff2, y, w); RING(g0, DV_DD2B, t) = w;
+        RING(g0, DV_POSTB, t) = y;
+        t = t1;
+        // ---- outputs, read after t++ (verb.cpp:302-326) ----
+        float a = __fadd_rn(tl[0], tl[1]); a = __fsub_rn(a, tl[2]); a = __fadd_rn(a, tl[3]);
+        a = __fsub_rn(a, tl[4]); a = __fsub_rn(a, tl[5]); a = __fadd_rn(a, tl[6]);
+        float b = __fadd_rn(tr[0], tr[1]); b = __fsub_rn(b, tr[2]); b = __fadd_rn(b, tr[3]);
+        b = __fsub_rn(b, tr[4]); b = __fsub_rn(b, tr[5]); b = __fadd_rn(b, tr[6]);
+        out_l[(size_t) n * I + inst] = a;
+        out_r[(size_t) n * I + inst] = b;
+    }
+    lp[inst] = z_pre;
+    lp[(size_t) I + inst] = z_a;
+    lp[2 * (size_t) I + inst] = z_b;
+}
+
+}  // namespace olb
+
+using namespace olb;
+
+// ================================================================================================
+// Host side.  Parameter setters mirror DattorroVerb_set* (verb.cpp:136-170); the maths runs here, on the host.
+struct olb_dattorro {
+    int device = 0;
+    uint32_t I = 0;
+    PlateGeom geom{};
+    uint32_t slab_positions = 0;
+    uint32_t t = 0;  // the reference's uint16 sample counter, shared by every instance of the bank
+    std::vector<float> par_host;  // [8][I]
+    bool par_dirty = true;
+    float *d_slab = nullptr, *d_lp = nullptr, *d_par = nullptr;
+};
+
+static void plate_geometry(PlateGeom *g, uint32_t *positions) {
+    uint32_t n = 0;
+    for (int i = 0; i < DV_RINGS; i++) {
+        const uint32_t sz = ring_size(kDelay[i]);
+        g->base[i] = n;
+        g->mask[i] = sz - 1;
+        g->off[i] = sz - kDelay[i];
+        n += sz;
+    }
+    for (int i = 0; i < 7; i++) {
+        g->tap_l[i][0] = kTapL[i][0];
+        g->tap_l[i][1] = g->mask[kTapL[i][0]] + 1 - kTapL[i][1];
+        g->tap_r[i][0] = kTapR[i][0];
+        g->tap_r[i][1] = g->mask[kTapR[i][0]] + 1 - kTapR[i][1];
+    }
+    *positions = n;
+}
+
+// DattorroVerb_setDecay (verb.cpp:162-165): clamp() takes t_sample arguments and returns double.
+static float decay_diffusion2(float decay) {
+    const float x = (float) ((double) decay + 0.15);
+    const float lo = 0.25f, hi = 0.50f;
+    return x < lo ? lo : (x > hi ? hi : x);
+}
+// DattorroVerb_setPreDelay (verb.cpp:137-139): value * MAX_PREDELAY narrowed to uint16, offset = mask + 1 - delay (uint16)
+static float predelay_offset_bits(const PlateGeom &g, float value) {
+    const uint16_t delay = (uint16_t) (value * 4800);
+    const uint16_t off = (uint16_t) (g.mask[DV_PRE] + 1 - delay);
+    const uint32_t u = off;
+    float f;
+    memcpy(&f, &u, 4);
+    return f;
+}
+
+static void plate_defaults(olb_dattorro *h) {  // initialize(), verb.cpp:215-221
+    const uint32_t I = h->I;
+    h->par_host.assign((size_t) 8 * I, 0.f);
+    for (uint32_t i = 0; i < I; i++) {
+        h->par_host[0 * (size_t) I + i] = 0.85;
+        h->par_host[1 * (size_t) I + i] = 0.75;
+        h->par_host[2 * (size_t) I + i] = 0.625;
+        h->par_host[3 * (size_t) I + i] = 0.70;
+        h->par_host[4 * (size_t) I + i] = 0.95;
+        h->par_host[5 * (size_t) I + i] = 0.75;
+        h->par_host[6 * (size_t) I + i] = decay_diffusion2(0.75);
+        h->par_host[7 * (size_t) I + i] = predelay_offset_bits(h->geom, 0.1);
+    }
+    h->par_dirty = true;
+}
+
+OLB_API int olb_dattorro_create(int device, uint32_t instances, olb_dattorro **out) {
+    OLB_ARG(out, "olb_dattorro_create: out is NULL");
+    *out = nullptr;
+    OLB_ARG(instances > 0, "olb_dattorro_create: instances must be > 0");
+    int rc = require_sm100(device);
+    if (rc) return rc;
+    DeviceGuard g(device);
+    olb_dattorro *h = new olb_dattorro();
+    h->device = device;
+    h->I = instances;
+    plate_geometry(&h->geom, &h->slab_positions);
+    plate_defaults(h);
+    const size_t slab_bytes = (size_t) h->slab_positions * instances * sizeof(float);
+    cudaError_t e = cudaMalloc(&h->d_slab, slab_bytes);
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_lp, (size_t) 3 * instances * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_par, (size_t) 8 * instances * sizeof(float));
+    if (e == cudaSuccess) e = cudaMemset(h->d_slab, 0, slab_bytes);
+    if (e == cudaSuccess) e = cudaMemset(h->d_lp, 0, (size_t) 3 * instances * sizeof(float));
+    if (e != cudaSuccess) {
+        cudaFree(h->d_slab); cudaFree(h->d_lp); cudaFree(h->d_par);
+        delete h;
+        return fail_cuda(e, "allocating plate bank", __FILE__, __LINE__);
+    }
+    *out = h;
+    return OLB_OK;
+}
+
+OLB_API int olb_dattorro_destroy(olb_dattorro *h) {
+    if (!h) return OLB_OK;
+    DeviceGuard g(h->device);
+    cudaFree(h->d_slab); cudaFree(h->d_lp); cudaFree(h->d_par);
+    delete h;
+    return OLB_OK;
+}
+
+// DattorroVerb_create()/initialize() again: rings, filters, counter and excursion cleared, parameters back to defaults.
+OLB_API int olb_dattorro_init(olb_dattorro *h) {
+    OLB_ARG(h, "olb_dattorro_init: NULL handle");
+    DeviceGuard g(h->device);
+    OLB_CUDA(cudaMemset(h->d_slab, 0, (size_t) h->slab_positions * h->I * sizeof(float)));
+    OLB_CUDA(cudaMemset(h->d_lp, 0, (size_t) 3 * h->I * sizeof(float)));
+    plate_geometry(&h->geom, &h->slab_positions);
+    h->t = 0;
+    plate_defaults(h);
+    return OLB_OK;
+}
+
+OLB_API int olb_dattorro_set_params(olb_dattorro *h, uint32_t first, uint32_t count, int param, const float *values, uint32_t stride) {
+    OLB_ARG(h && values, "olb_dattorro_set_params: NULL argument");
+    OLB_ARG((uint64_t) first + count <= h->I, "olb_dattorro_set_params: range [%u, %u) exceeds %u instances", first, first + count, h->I);
+    OLB_ARG(param >= OLB_PLATE_PREDELAY && param <= OLB_PLATE_DAMPING, "olb_dattorro_set_params: unknown parameter %d", param);
+    const size_t I = h->I;
+    for (uint32_t i = 0; i < count; i++) {
+        const float v = values[(size_t) i * stride];
+        const size_t c = first + i;
+        switch (param) {
+            case OLB_PLATE_PREDELAY: h->par_host[7 * I + c] = predelay_offset_bits(h->geom, v); break;
+            case OLB_PLATE_PREFILTER: h->par_host[0 * I + c] = v; break;
+            case OLB_PLATE_INPUT_DIFFUSION1: h->par_host[1 * I + c] = v; break;
+            case OLB_PLATE_INPUT_DIFFUSION2: h->par_host[2 * I + c] = v; break;
+            case OLB_PLATE_DECAY: h->par_host[5 * I + c] = v; h->par_host[6 * I + c] = decay_diffusion2(v); break;
+            case OLB_PLATE_DECAY_DIFFUSION: h->par_host[3 * I + c] = v; break;
+            default: h->par_host[4 * I + c] = v; break;
+        }
+    }
+    h->par_dirty = true;
+    return OLB_OK;
+}
+
+OLB_API int olb_dattorro_set_param(olb_dattorro *h, uint32_t first, uint32_t count, int param, float value) {
+    return olb_dattorro_set_params(h, first, count, param, &value, 0);
+}
+
+OLB_API int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *out_l_dev, float *out_r_dev, uint64_t frames, void *stream) {
+    OLB_ARG(h, "olb_dattorro_process: NULL handle");
+    if (frames == 0) return OLB_OK;
+    OLB_ARG(in_dev && out_l_dev && out_r_dev, "olb_dattorro_process: NULL buffer");
+    OLB_ARG(frames < (1ull << 32), "olb_dattorro_process: at most 2^32-1 frames per call");
+    DeviceGuard g(h->device);
+    cudaStream_t st = (cudaStream_t) stream;
+    if (h->par_dirty) {
+        OLB_CUDA(cudaMemcpyAsync(h->d_par, h->par_host.data(), h->par_host.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+        OLB_CUDA(cudaStreamSynchronize(st));  // par_host may change right after we return
+        h->par_dirty = false;
+    }
+    k_dattorro<<<(h->I + 63) / 64, 64, 0, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I, h->d_slab, h->d_lp, h->d_par, h->geom, h->t);
+    OLB_LAUNCHED();
+    // advance the shared counter and the excursion exactly as the kernel did
+    uint32_t t = h->t, oa = h->geom.off[DV_DD1A], ob = h->geom.off[DV_DD1B];
+    for (uint64_t n = 0; n < frames;) {
+        if ((t & 0x07ffu) == 0) {
+            if (t < (1u << 15)) { oa = (oa - 1) & 0xffffu; ob = (ob - 1) & 0xffffu; }
+            else { oa = (oa + 1) & 0xffffu; ob = (ob + 1) & 0xffffu; }
+        }
+        const uint64_t to_next = 0x800u - (t & 0x07ffu);  // frames until the next excursion step
+        const uint64_t step = frames - n < to_next ? frames - n : to_next;
+        n += step;
+        t = (uint32_t) ((t + step) & 0xffffu);
+    }
+    h->t = t;
+    h->geom.off[DV_DD1A] = oa;
+    h->geom.off[DV_DD1B] = ob;
+    return OLB_OK;
+}

@@ -1,0 +1,72 @@
+"""Secondary benchmarks (instance-samples/s for the non-headline rows).  One JSON line per unit.
+    python tools/bench_units.py dattorro [--instances 8192] [--frames 48000] [--steps 3]
+CUDA events on the launch stream; inputs resident in HBM; state (rings) persists across steps like a running plate."""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    return float(json.load(open(p))["hbm_gbs"]) if os.path.exists(p) else 6650.0
+
+
+def timed(fn, steps, warm=2):
+    import torch
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(steps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) * 1e-3 / steps
+
+
+def bench_dattorro(a):
+    import torch
+    from ol_dsp_b200 import DattorroBank, noise_device
+    I, F = a.instances, a.frames
+    b = DattorroBank(I)
+    b.SetDecay((0.5 + 0.4 * (torch.arange(I) % 16) / 16).numpy())
+    x = torch.empty((F, I), dtype=torch.float32, device="cuda")
+    noise_device(x.data_ptr(), 0x01D5B200, 0, I, 0, F, 0.25)
+    l, r = torch.empty_like(x), torch.empty_like(x)
+    st = torch.cuda.current_stream().cuda_stream
+    dt = timed(lambda: b.ProcessDevice(x.data_ptr(), l.data_ptr(), r.data_ptr(), F, st), a.steps)
+    units = I * F
+    line = {"unit": "dattorro", "metric": "instance-samples/s", "value": units / dt, "ms_per_step": dt * 1e3, "instances": I, "frames": F,
+            "roofline": {"bound": "hbm", "algorithmic_bytes_per_unit": 12, "achieved": 12 * units / dt / 1e9, "peak": peaks(), "unit": "GB/s",
+                         "frac": 12 * units / dt / 1e9 / peaks(),
+                         "ring_bytes_per_unit": 4 * (13 + 13 + 14), "ring_traffic_gbs": 160 * units / dt / 1e9},
+            "checksum": float(l.double().sum().item() + r.double().sum().item())}
+    if a.cpu:
+        import time
+
+        import numpy as np
+        from oracle import loader
+        ref = loader.reference() or loader.oracle()
+        xs = np.ascontiguousarray(x[:, 0].cpu().numpy())
+        t0 = time.perf_counter()
+        ref.dattorro(xs, None)
+        line["cpu_baseline"] = {"value": F / (time.perf_counter() - t0), "unit": "instance-samples/s", "cores": 1,
+                                "kind": "reference" if loader.reference() else "port", "sample": f"1 instance x {F} frames, verb.cpp compiled unmodified"}
+    print(json.dumps(line), flush=True)
+    b.close()
+
+
+if __name__ == "__main__":
+    p = argparse.ArgumentParser()
+    p.add_argument("unit", choices=["dattorro"])
+    p.add_argument("--instances", type=int, default=8192)
+    p.add_argument("--frames", type=int, default=48000)
+    p.add_argument("--steps", type=int, default=3)
+    p.add_argument("--cpu", action="store_true")
+    a = p.parse_args()
+    {"dattorro": bench_dattorro}[a.unit](a)
