@@ -117,6 +117,34 @@ int olb_biquad_set_state(olb_biquad *h, const float *state_host);
 const char *olb_biquad_last_kernel(olb_biquad *h);
 int olb_biquad_set_variant(olb_biquad *h, int variant);
 
+/* (a2-a5) fxlib unit banks: FilterFx<1>, DelayFx<1>, ReverbFx<1>, FxRack<1> -----------------------------
+ * One bank = `instances` mono objects of one reference class:
+ *   OLB_FX_FILTER  ol::fx::FilterFx<1>  modules/fxlib/Fx.h:65-165
+ *   OLB_FX_DELAY   ol::fx::DelayFx<1>   modules/fxlib/Fx.h:170-268  (+ its daisysp::DelayLine<float,48000> and wet FilterFx)
+ *   OLB_FX_REVERB  ol::fx::ReverbFx<1>  modules/fxlib/Fx.h:272-393  around the stub ReverbSc (modules/fxlib/Reverb.h:13-41)
+ *   OLB_FX_RACK    ol::fx::FxRack<1>    modules/fxlib/Fx.h:397-493  delay -> reverb -> filter -> master volume
+ * create = construct with the reference's default members + Init(sample_rate).  The CC numbers are
+ * modules/corelib/cc_map.h:7-70; values map through ol::core::scale exactly as in the reference's
+ * UpdateMidiControl / UpdateHardwareControl, on the host.  Audio is [frames][instances] device memory. */
+#define OLB_FX_FILTER 0
+#define OLB_FX_DELAY 1
+#define OLB_FX_REVERB 2
+#define OLB_FX_RACK 3
+
+typedef struct olb_fx olb_fx;
+
+int olb_fx_create(int device, int kind, uint32_t instances, float sample_rate, olb_fx **out);
+int olb_fx_destroy(olb_fx *h);
+/* Init(sample_rate): clears filter state and delay lines, keeps the parameter members (test/fx_test.cpp:32,42). */
+int olb_fx_init(olb_fx *h, float sample_rate);
+/* UpdateMidiControl(control, value 0..127) for instances [first, first+count)  (Fx.h:116-139, 239-266, 313-351, 443-468) */
+int olb_fx_update_midi(olb_fx *h, uint32_t first, uint32_t count, uint8_t control, uint8_t value);
+/* UpdateHardwareControl(control, value 0..1), one value per instance at values_host[i * stride] (stride 0 = one value
+ * for all)  (Fx.h:141-164, 219-237, 353-391, 470-492) */
+int olb_fx_update_hw(olb_fx *h, uint32_t first, uint32_t count, uint8_t control, const float *values_host, uint32_t stride);
+/* Block form of "for each frame: Process(frame_in, frame_out)"; in_dev == out_dev allowed. */
+int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream);
+
 /* (a7) Dattorro plate reverb bank -------------------------------------------------------------------
  * Replaces libs/dattorro-verb/verb.h:5-26 for `instances` plates at once (mono in, stereo wet out):
  *   DattorroVerb_create / initialize (verb.cpp:173-222, 225-232)  -> olb_dattorro_create, olb_dattorro_init

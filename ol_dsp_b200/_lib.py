@@ -64,6 +64,12 @@ def lib():
         "olb_biquad_set_state": ([vp, _F], i32),
         "olb_biquad_last_kernel": ([vp], C.c_char_p),
         "olb_biquad_set_variant": ([vp, i32], i32),
+        "olb_fx_create": ([i32, i32, u32, f32, C.POINTER(vp)], i32),
+        "olb_fx_destroy": ([vp], i32),
+        "olb_fx_init": ([vp, f32], i32),
+        "olb_fx_update_midi": ([vp, u32, u32, C.c_uint8, C.c_uint8], i32),
+        "olb_fx_update_hw": ([vp, u32, u32, C.c_uint8, _F, u32], i32),
+        "olb_fx_process": ([vp, vp, vp, u64, vp], i32),
         "olb_dattorro_create": ([i32, u32, C.POINTER(vp)], i32),
         "olb_dattorro_destroy": ([vp], i32),
         "olb_dattorro_init": ([vp], i32),

@@ -18,6 +18,7 @@
 // of a sample are independent of that sample's arithmetic (every delay is >= 107 samples), so they are issued
 // together at the top of the iteration and the chain of filters then runs out of registers.
 #include <math.h>
+#include <stdlib.h>
 
 #include <vector>
 
@@ -126,6 +127,126 @@ __global__ void __launch_bounds__(64) k_dattorro(const float *__restrict__ in, f
         out_l[(size_t) n * I + inst] = a;
         out_r[(size_t) n * I + inst] = b;
     }
+    lp[inst] = z_pre;
+    lp[(size_t) I + inst] = z_a;
+    lp[2 * (size_t) I + inst] = z_b;
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_dattorro_pf: the same network with a D-sample deep software pipeline.  One instance per thread leaves only
+// ~2 warps per SM, so the simple kernel above pays one full HBM round trip per sample.  Every ring read of sample
+// n + D is independent of samples n .. n + D - 1 as long as every delay exceeds D (they are >= 107; the per-instance
+// pre-delay is checked and falls back to a direct load), so each thread issues its 27 ring reads and its input for
+// sample n + D as 4-byte cp.async (LDGSTS) copies into a private shared-memory slot while it computes sample n.
+__device__ __forceinline__ void cp_async4(float *smem_dst, const float *gmem_src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+constexpr int kPfSlots = 28;  // 13 main taps + 14 output taps + the input sample
+constexpr int kPfThreads = 64;
+
+__device__ __forceinline__ void excursion_step(uint32_t t, uint32_t &off_a, uint32_t &off_b) {  // verb.cpp:262-270
+    if ((t & 0x07ffu) == 0) {
+        if (t < (1u << 15)) { off_a = (off_a - 1) & 0xffffu; off_b = (off_b - 1) & 0xffffu; }
+        else { off_a = (off_a + 1) & 0xffffu; off_b = (off_b + 1) & 0xffffu; }
+    }
+}
+
+template <int D>
+__global__ void __launch_bounds__(kPfThreads) k_dattorro_pf(const float *__restrict__ in, float *__restrict__ out_l, float *__restrict__ out_r,
+                                                            uint32_t frames, uint32_t I, float *slab, float *lp, const float *__restrict__ par,
+                                                            const __grid_constant__ PlateGeom g0, uint32_t t0) {
+    extern __shared__ float pf[];  // [D][kPfSlots][kPfThreads]
+    const uint32_t inst = blockIdx.x * blockDim.x + threadIdx.x;
+    if (inst >= I) return;
+    float *mine = pf + threadIdx.x;
+    auto SLOT = [&](uint32_t d, int k) -> float * { return mine + ((size_t) d * kPfSlots + k) * kPfThreads; };
+    const float pre_filter = par[0 * (size_t) I + inst], in_diff1 = par[1 * (size_t) I + inst], in_diff2 = par[2 * (size_t) I + inst];
+    const float decay_diff1 = par[3 * (size_t) I + inst], damping = par[4 * (size_t) I + inst], decay = par[5 * (size_t) I + inst];
+    const float decay_diff2 = par[6 * (size_t) I + inst];
+    const uint32_t pre_off = __float_as_uint(par[7 * (size_t) I + inst]);
+    float z_pre = lp[inst], z_a = lp[(size_t) I + inst], z_b = lp[2 * (size_t) I + inst];
+    const uint32_t pre_len = (g0.mask[DV_PRE] + 1 - pre_off) & g0.mask[DV_PRE];  // pre-delay in samples
+    const bool pre_same = pre_len == 0, pre_direct = pre_len <= (uint32_t) D;    // too short to fetch D samples ahead
+    uint32_t t = t0, off_a = g0.off[DV_DD1A], off_b = g0.off[DV_DD1B];           // state at the sample being computed
+    uint32_t ta = t0, offa_a = off_a, offb_a = off_b;                            // state at the sample being fetched
+
+    auto fetch = [&](uint32_t n, uint32_t slot) {  // sample index n, counter value ta (before its own excursion step)
+        excursion_step(ta, offa_a, offb_a);
+        cp_async4(SLOT(slot, 27), in + (size_t) n * I + inst);
+        cp_async4(SLOT(slot, 0), &RING(g0, DV_PRE, ta + pre_off));
+        cp_async4(SLOT(slot, 1), &RING(g0, DV_IN0, ta + g0.off[DV_IN0]));
+        cp_async4(SLOT(slot, 2), &RING(g0, DV_IN1, ta + g0.off[DV_IN1]));
+        cp_async4(SLOT(slot, 3), &RING(g0, DV_IN2, ta + g0.off[DV_IN2]));
+        cp_async4(SLOT(slot, 4), &RING(g0, DV_IN3, ta + g0.off[DV_IN3]));
+        cp_async4(SLOT(slot, 5), &RING(g0, DV_POSTB, ta + g0.off[DV_POSTB]));
+        cp_async4(SLOT(slot, 6), &RING(g0, DV_POSTA, ta + g0.off[DV_POSTA]));
+        cp_async4(SLOT(slot, 7), &RING(g0, DV_DD1A, ta + offa_a));
+        cp_async4(SLOT(slot, 8), &RING(g0, DV_DD1B, ta + offb_a));
+        cp_async4(SLOT(slot, 9), &RING(g0, DV_PDA, ta + g0.off[DV_PDA]));
+        cp_async4(SLOT(slot, 10), &RING(g0, DV_PDB, ta + g0.off[DV_PDB]));
+        cp_async4(SLOT(slot, 11), &RING(g0, DV_DD2A, ta + g0.off[DV_DD2A]));
+        cp_async4(SLOT(slot, 12), &RING(g0, DV_DD2B, ta + g0.off[DV_DD2B]));
+        const uint32_t t1 = (ta + 1) & 0xffffu;
+#pragma unroll
+        for (int i = 0; i < 7; i++) {
+            cp_async4(SLOT(slot, 13 + i), &RING(g0, g0.tap_l[i][0], t1 + g0.tap_l[i][1]));
+            cp_async4(SLOT(slot, 20 + i), &RING(g0, g0.tap_r[i][0], t1 + g0.tap_r[i][1]));
+        }
+        ta = t1;
+    };
+
+    for (uint32_t d = 0; d < (uint32_t) D; d++) {
+        if (d < frames) fetch(d, d);
+        cp_async_commit();
+    }
+    for (uint32_t n = 0; n < frames; n++) {
+        const uint32_t slot = n % D;
+        cp_async_wait<D - 1>();
+        excursion_step(t, off_a, off_b);
+        float v[kPfSlots];
+#pragma unroll
+        for (int k = 0; k < kPfSlots; k++) v[k] = *SLOT(slot, k);
+        if (n + D < frames) fetch(n + D, slot);
+        cp_async_commit();
+        const float xin = v[27];
+        float r_pre = v[0];
+        if (pre_direct) r_pre = pre_same ? xin : RING(g0, DV_PRE, t + pre_off);
+        float w;
+        RING(g0, DV_PRE, t) = xin;
+        float x = lowpass(z_pre, pre_filter, r_pre);
+        x = allpass(v[1], in_diff1, x, w); RING(g0, DV_IN0, t) = w;
+        x = allpass(v[2], in_diff1, x, w); RING(g0, DV_IN1, t) = w;
+        x = allpass(v[3], in_diff2, x, w); RING(g0, DV_IN2, t) = w;
+        x = allpass(v[4], in_diff2, x, w); RING(g0, DV_IN3, t) = w;
+        float y = __fadd_rn(x, __fmul_rn(v[5], decay));
+        y = allpass(v[7], -decay_diff1, y, w); RING(g0, DV_DD1A, t) = w;
+        RING(g0, DV_PDA, t) = y; y = v[9];
+        y = lowpass(z_a, damping, y);
+        y = __fmul_rn(y, decay);
+        y = allpass(v[11], decay_diff2, y, w); RING(g0, DV_DD2A, t) = w;
+        RING(g0, DV_POSTA, t) = y;
+        y = __fadd_rn(x, __fmul_rn(v[6], decay));
+        y = allpass(v[8], -decay_diff1, y, w); RING(g0, DV_DD1B, t) = w;
+        RING(g0, DV_PDB, t) = y; y = v[10];
+        y = lowpass(z_b, damping, y);
+        y = __fmul_rn(y, decay);
+        y = allpass(v[12], decay_diff2, y, w); RING(g0, DV_DD2B, t) = w;
+        RING(g0, DV_POSTB, t) = y;
+        t = (t + 1) & 0xffffu;
+        float a = __fadd_rn(v[13], v[14]); a = __fsub_rn(a, v[15]); a = __fadd_rn(a, v[16]);
+        a = __fsub_rn(a, v[17]); a = __fsub_rn(a, v[18]); a = __fadd_rn(a, v[19]);
+        float b = __fadd_rn(v[20], v[21]); b = __fsub_rn(b, v[22]); b = __fadd_rn(b, v[23]);
+        b = __fsub_rn(b, v[24]); b = __fsub_rn(b, v[25]); b = __fadd_rn(b, v[26]);
+        out_l[(size_t) n * I + inst] = a;
+        out_r[(size_t) n * I + inst] = b;
+    }
+    cp_async_wait<0>();
     lp[inst] = z_pre;
     lp[(size_t) I + inst] = z_a;
     lp[2 * (size_t) I + inst] = z_b;
@@ -283,7 +404,23 @@ OLB_API int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *ou
         OLB_CUDA(cudaStreamSynchronize(st));  // par_host may change right after we return
         h->par_dirty = false;
     }
-    k_dattorro<<<(h->I + 63) / 64, 64, 0, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I, h->d_slab, h->d_lp, h->d_par, h->geom, h->t);
+    // OLB_PLATE_KERNEL=simple|pf8|pf16 selects the kernel (tuning aid); default: the 8-deep pipelined one (16 deep measures the same)
+    static const int which = [] {
+        const char *e = getenv("OLB_PLATE_KERNEL");
+        return !e ? 8 : (!strcmp(e, "simple") ? 0 : (!strcmp(e, "pf16") ? 16 : 8));
+    }();
+    const unsigned grid = (h->I + kPfThreads - 1) / kPfThreads;
+    if (which == 0) {
+        k_dattorro<<<(h->I + 63) / 64, 64, 0, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I, h->d_slab, h->d_lp, h->d_par, h->geom, h->t);
+    } else if (which == 8) {
+        constexpr size_t smem = (size_t) 8 * kPfSlots * kPfThreads * sizeof(float);
+        OLB_CUDA(cudaFuncSetAttribute(k_dattorro_pf<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        k_dattorro_pf<8><<<grid, kPfThreads, smem, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I, h->d_slab, h->d_lp, h->d_par, h->geom, h->t);
+    } else {
+        constexpr size_t smem = (size_t) 16 * kPfSlots * kPfThreads * sizeof(float);
+        OLB_CUDA(cudaFuncSetAttribute(k_dattorro_pf<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        k_dattorro_pf<16><<<grid, kPfThreads, smem, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I, h->d_slab, h->d_lp, h->d_par, h->geom, h->t);
+    }
     OLB_LAUNCHED();
     // advance the shared counter and the excursion exactly as the kernel did
     uint32_t t = h->t, oa = h->geom.off[DV_DD1A], ob = h->geom.off[DV_DD1B];

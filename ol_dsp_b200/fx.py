@@ -1,0 +1,50 @@
+"""FxBank: host-side mirror of the reference's fxlib units (modules/fxlib/Fx.h) for a bank of mono instances, over
+the C ABI.  Method names are the reference's: Init, UpdateMidiControl, UpdateHardwareControl, Process (block form).
+All compute happens in libolbank.so on the GPU; the CC -> parameter maths runs on the host inside the library."""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import check
+
+FILTER, DELAY, REVERB, RACK = range(4)
+
+
+class FxBank:
+    def __init__(self, kind, instances, sample_rate=48000.0, device=0):
+        self.L = _lib.lib()
+        self.kind, self.instances, self.device = int(kind), int(instances), int(device)
+        h = C.c_void_p()
+        check(self.L.olb_fx_create(device, kind, instances, sample_rate, C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.olb_fx_destroy(self.h)
+            self.h = None
+
+    __del__ = close
+
+    def Init(self, sample_rate):
+        check(self.L.olb_fx_init(self.h, sample_rate))
+
+    def UpdateMidiControl(self, control, value, first=0, count=None):
+        count = self.instances - first if count is None else count
+        check(self.L.olb_fx_update_midi(self.h, first, count, int(control), int(value)))
+
+    def UpdateHardwareControl(self, control, value, first=0, count=None):
+        """value: scalar for the whole range, or one value per instance."""
+        count = self.instances - first if count is None else count
+        v = np.ascontiguousarray(value, dtype=np.float32).reshape(-1)
+        assert v.size in (1, count)
+        check(self.L.olb_fx_update_hw(self.h, first, count, int(control), v.ctypes.data_as(C.POINTER(C.c_float)), 0 if v.size == 1 else 1))
+
+    def ProcessDevice(self, in_ptr, out_ptr, frames, stream=0):
+        check(self.L.olb_fx_process(self.h, C.c_void_p(in_ptr), C.c_void_p(out_ptr), frames, C.c_void_p(stream)))
+
+
+def FilterFx(instances, **kw): return FxBank(FILTER, instances, **kw)
+def DelayFx(instances, **kw): return FxBank(DELAY, instances, **kw)
+def ReverbFx(instances, **kw): return FxBank(REVERB, instances, **kw)
+def FxRack(instances, **kw): return FxBank(RACK, instances, **kw)

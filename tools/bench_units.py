@@ -61,12 +61,45 @@ def bench_dattorro(a):
     b.close()
 
 
+def bench_fx(a, kind, name, bytes_per_unit):
+    import numpy as np
+    import torch
+    from ol_dsp_b200 import FxBank, noise_device
+    I, F = a.instances, a.frames
+    b = FxBank(kind, I)
+    b.UpdateHardwareControl(35, (0.05 + 0.9 * np.arange(I) / I).astype(np.float32))  # CC_DELAY_TIME sweep
+    x = torch.empty((F, I), dtype=torch.float32, device="cuda")
+    noise_device(x.data_ptr(), 0x01D5B200, 0, I, 0, F, 0.25)
+    y = torch.empty_like(x)
+    st = torch.cuda.current_stream().cuda_stream
+    dt = timed(lambda: b.ProcessDevice(x.data_ptr(), y.data_ptr(), F, st), a.steps)
+    units = I * F
+    line = {"unit": name, "metric": "instance-samples/s", "value": units / dt, "ms_per_step": dt * 1e3, "instances": I, "frames": F,
+            "roofline": {"bound": "hbm", "algorithmic_bytes_per_unit": bytes_per_unit, "achieved": bytes_per_unit * units / dt / 1e9,
+                         "peak": peaks(), "unit": "GB/s", "frac": bytes_per_unit * units / dt / 1e9 / peaks()},
+            "checksum": float(y.double().sum().item())}
+    if a.cpu:
+        import time
+        from oracle import loader
+        ref = loader.reference() or loader.oracle()
+        xs = np.ascontiguousarray(x[:, :1].cpu().numpy())
+        t0 = time.perf_counter()
+        getattr(ref, name)(xs, 48000.0, [])
+        line["cpu_baseline"] = {"value": F / (time.perf_counter() - t0), "unit": "instance-samples/s", "cores": 1,
+                                "kind": "reference" if loader.reference() else "port",
+                                "sample": f"1 instance x {F} frames, the reference's own {name} class over the DaisySP restatement"}
+    print(json.dumps(line), flush=True)
+    b.close()
+
+
 if __name__ == "__main__":
     p = argparse.ArgumentParser()
-    p.add_argument("unit", choices=["dattorro"])
+    p.add_argument("unit", choices=["dattorro", "filterfx", "delayfx", "fxrack"])
     p.add_argument("--instances", type=int, default=8192)
     p.add_argument("--frames", type=int, default=48000)
     p.add_argument("--steps", type=int, default=3)
     p.add_argument("--cpu", action="store_true")
     a = p.parse_args()
-    {"dattorro": bench_dattorro}[a.unit](a)
+    from ol_dsp_b200 import fx as _fx
+    {"dattorro": bench_dattorro, "filterfx": lambda a: bench_fx(a, _fx.FILTER, "filterfx", 8),
+     "delayfx": lambda a: bench_fx(a, _fx.DELAY, "delayfx", 16), "fxrack": lambda a: bench_fx(a, _fx.RACK, "fxrack", 16)}[a.unit](a)
