@@ -145,6 +145,36 @@ int olb_fx_update_hw(olb_fx *h, uint32_t first, uint32_t count, uint8_t control,
 /* Block form of "for each frame: Process(frame_in, frame_out)"; in_dev == out_dev allowed. */
 int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream);
 
+/* (a6) SynthVoice bank and (a8) Polyvoice mixdown -------------------------------------------------------
+ * One bank = `voices` ol::synth::SynthVoice objects with the reference's default parts (PolyBLEP-saw
+ * OscillatorSoundSource, SvfFilter, two DaisyAdsr, DaisyPortamento): modules/synthlib/SynthVoice.h:16-316.
+ *   Init(sr)                         SynthVoice.h:31-39   -> olb_voice_create / olb_voice_init
+ *   UpdateMidiControl / UpdateHardwareControl  :101-229  -> olb_voice_update_midi / olb_voice_update_hw
+ *   UpdateConfig(Voice::Config&)     :55-77; Voice.h:14-31 (16 floats, that order) -> olb_voice_update_config
+ *   NoteOn / NoteOff / GateOn / GateOff / SetFrequency / Playing   :231-267 -> olb_voice_note_on / _note_off / _set_gate /
+ *                                                                    _set_frequency / _playing
+ *   Process(frame_out) per voice     :41-53               -> olb_voice_process with out_dev [frames][voices]
+ *   Polyvoice::Process: *frame_out += every voice, caller zeroes (Polyvoice.h:28-33; stereo duplicate main.cpp:83)
+ *                                                         -> olb_voice_process with bus_dev [frames][bus_channels]:
+ *                                                            bus (+)= bus_gain * sum of voices (accumulate != 0 adds)
+ * Setters take effect at the next process call (the reference applies MIDI between audio blocks).  trace_dev
+ * (optional, tests) receives 4 floats per voice-frame: oscillator output, amp envelope, filter envelope, phase. */
+typedef struct olb_voice olb_voice;
+
+int olb_voice_create(int device, uint32_t voices, float sample_rate, olb_voice **out);
+int olb_voice_destroy(olb_voice *h);
+int olb_voice_init(olb_voice *h, float sample_rate);
+int olb_voice_update_midi(olb_voice *h, uint32_t first, uint32_t count, uint8_t control, uint8_t value);
+int olb_voice_update_hw(olb_voice *h, uint32_t first, uint32_t count, uint8_t control, const float *values_host, uint32_t stride);
+int olb_voice_update_config(olb_voice *h, uint32_t first, uint32_t count, const float *config16_host);
+int olb_voice_note_on(olb_voice *h, uint32_t first, uint32_t count, const uint8_t *notes_host, uint32_t stride, uint8_t velocity);
+int olb_voice_note_off(olb_voice *h, uint32_t first, uint32_t count);
+int olb_voice_set_gate(olb_voice *h, uint32_t first, uint32_t count, int gate);
+int olb_voice_set_frequency(olb_voice *h, uint32_t first, uint32_t count, const float *freqs_host, uint32_t stride);
+int olb_voice_playing(olb_voice *h, uint32_t first, uint32_t count, uint8_t *playing_host);
+int olb_voice_process(olb_voice *h, float *out_dev, float *bus_dev, uint32_t bus_channels, int accumulate, float bus_gain,
+                      float *trace_dev, uint64_t frames, void *stream);
+
 /* (a7) Dattorro plate reverb bank -------------------------------------------------------------------
  * Replaces libs/dattorro-verb/verb.h:5-26 for `instances` plates at once (mono in, stereo wet out):
  *   DattorroVerb_create / initialize (verb.cpp:173-222, 225-232)  -> olb_dattorro_create, olb_dattorro_init

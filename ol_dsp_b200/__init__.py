@@ -3,5 +3,6 @@ from . import _lib  # noqa: F401
 from ._lib import (KIND_BIQUAD, KIND_LPF, KIND_PORT, LAYOUT_FRAMES, LAYOUT_PLANAR, MODE_EXACT, MODE_FAST, MODE_FMA, OlbError)  # noqa: F401
 from .dattorro import DattorroBank  # noqa: F401
 from .fx import FxBank  # noqa: F401
+from .voice import Polyvoice, VoiceBank  # noqa: F401
 from .biquad import BiquadBank, design  # noqa: F401
 from .workloads import c2_coefs, noise_device  # noqa: F401

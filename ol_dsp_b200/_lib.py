@@ -70,6 +70,18 @@ def lib():
         "olb_fx_update_midi": ([vp, u32, u32, C.c_uint8, C.c_uint8], i32),
         "olb_fx_update_hw": ([vp, u32, u32, C.c_uint8, _F, u32], i32),
         "olb_fx_process": ([vp, vp, vp, u64, vp], i32),
+        "olb_voice_create": ([i32, u32, f32, C.POINTER(vp)], i32),
+        "olb_voice_destroy": ([vp], i32),
+        "olb_voice_init": ([vp, f32], i32),
+        "olb_voice_update_midi": ([vp, u32, u32, C.c_uint8, C.c_uint8], i32),
+        "olb_voice_update_hw": ([vp, u32, u32, C.c_uint8, _F, u32], i32),
+        "olb_voice_update_config": ([vp, u32, u32, _F], i32),
+        "olb_voice_note_on": ([vp, u32, u32, C.POINTER(C.c_uint8), u32, C.c_uint8], i32),
+        "olb_voice_note_off": ([vp, u32, u32], i32),
+        "olb_voice_set_gate": ([vp, u32, u32, i32], i32),
+        "olb_voice_set_frequency": ([vp, u32, u32, _F, u32], i32),
+        "olb_voice_playing": ([vp, u32, u32, C.POINTER(C.c_uint8)], i32),
+        "olb_voice_process": ([vp, vp, vp, u32, i32, f32, vp, u64, vp], i32),
         "olb_dattorro_create": ([i32, u32, C.POINTER(vp)], i32),
         "olb_dattorro_destroy": ([vp], i32),
         "olb_dattorro_init": ([vp], i32),

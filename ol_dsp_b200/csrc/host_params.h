@@ -214,5 +214,128 @@ struct RackParams {
     }
 };
 
+// ---- daisysp::Adsr, setter side (upstream Source/Control/adsr.cpp; parity unpinned) -----------------
+struct AdsrParams {
+    int sr = 48000;
+    float sus = 0.7f, a_shape = -1.f, a_target = 0.f, a_time = -1.f, d_time = -1.f, r_time = -1.f;
+    float a_d0 = 0.f, d_d0 = 0.f, r_d0 = 0.f;
+    void SetTime(float t, float *time, float *coeff) {
+        if (t != *time) {
+            *time = t;
+            if (t > 0.f) {
+                const float target = logf(1. / M_E);
+                *coeff = 1.f - expf(target / (t * sr));
+            } else {
+                *coeff = 1.f;
+            }
+        }
+    }
+    void SetAttackTime(float t, float shape) {
+        if (t != a_time || shape != a_shape) {
+            a_time = t;
+            a_shape = shape;
+            if (t > 0.f) {
+                const float target = 9.f * powf(shape, 10.f) + 0.3f * shape + 1.01f;
+                a_target = target;
+                const float lt = logf(1.f - (1.f / target));
+                a_d0 = 1.f - expf(lt / (t * sr));
+            } else {
+                a_d0 = 1.f;
+            }
+        }
+    }
+    void SetDecayTime(float t) { SetTime(t, &d_time, &d_d0); }
+    void SetReleaseTime(float t) { SetTime(t, &r_time, &r_d0); }
+    void SetSustainLevel(float s) { sus = (s <= 0.f) ? -0.01f : (s > 1.f) ? 1.f : s; }
+    void Init(float sample_rate, int block) {
+        *this = AdsrParams();
+        sr = (int) (sample_rate / block);
+        SetAttackTime(0.1f, 0.0f);
+        SetDecayTime(0.1f);
+        SetReleaseTime(0.1f);
+    }
+};
+
+// ---- ol::synth::SynthVoice (modules/synthlib/SynthVoice.h:16-316) with its default parts: OscillatorSoundSource
+// (PolyBLEP saw, OscillatorSoundSource.h:12-38), SvfFilter (Filter.h:65-108), two DaisyAdsr (Adsr.h:35-76) and
+// DaisyPortamento over the in-tree daisysp::Port (Portamento.h:13-42, 57-72).
+struct VoiceParams {
+    // members with the defaults of SynthVoice.h:269-315
+    float filter_cutoff = 0.f, filter_resonance = 0.f, filter_drive = 0.f;
+    float filter_attack = 0.f, filter_attack_shape = 1.f, filter_decay = 0.2f, filter_sustain = 0.f, filter_release = 0.f, filter_env_amount = 1.f;
+    float amp_attack = 0.01f, amp_attack_shape = 1.f, amp_decay = 0.f, amp_sustain = 1.f, amp_release = 0.01f, amp_env_amount = 0.8f;
+    float portamento_htime = 0.f, osc_1_mix = 0.8f;
+    float sample_rate = 48000.f, freq = 0.f;
+    uint8_t playing = 0;
+    int gate = 0;
+    bool retrigger = false;  // NoteOn: both envelopes Retrigger(hard) before the next frame
+    SvfParams svf;
+    AdsrParams filter_env, amp_env;
+    float port_sr = 48000.f, port_coeff = 0.f;
+
+    void SetHtime(float h) { port_coeff = expf(-1.0f / (h * port_sr)); }  // Portamento.h:34-37
+    void Update() {  // SynthVoice.h:79-98 (SetFreq is commented out there)
+        svf.SetRes(filter_resonance);
+        svf.SetDrive(filter_drive);
+        filter_env.SetAttackTime(filter_attack, filter_attack_shape);
+        filter_env.SetDecayTime(filter_decay);
+        filter_env.SetSustainLevel(filter_sustain);
+        filter_env.SetReleaseTime(filter_release);
+        amp_env.SetAttackTime(amp_attack, amp_attack_shape);
+        amp_env.SetDecayTime(amp_decay);
+        amp_env.SetSustainLevel(amp_sustain);
+        amp_env.SetReleaseTime(amp_release);
+        SetHtime(portamento_htime);
+    }
+    void Init(float sr) {  // SynthVoice.h:31-39: Update() is NOT called
+        sample_rate = sr;
+        svf.Init(sr);
+        filter_env.Init(sr, 1);
+        amp_env.Init(sr, 1);
+        port_sr = sr;
+        SetHtime(portamento_htime);
+    }
+    void UpdateConfig(const float *c) {  // Voice::Config field order, modules/synthlib/Voice.h:14-31
+        filter_cutoff = c[0]; filter_resonance = c[1]; filter_drive = c[2]; filter_env_amount = c[3];
+        filter_attack = c[4]; filter_attack_shape = c[5]; filter_decay = c[6]; filter_sustain = c[7]; filter_release = c[8];
+        amp_env_amount = c[9]; amp_attack = c[10]; amp_attack_shape = c[11]; amp_decay = c[12]; amp_sustain = c[13]; amp_release = c[14];
+        portamento_htime = c[15];
+        Update();
+    }
+    bool set(uint8_t cc, float s, float porta, float cutoff, float fdecay) {
+        switch (cc) {
+            case CC_CTL_VOLUME: amp_env_amount = s; break;
+            case CC_CTL_PORTAMENTO: portamento_htime = porta; break;
+            case CC_FILTER_CUTOFF: filter_cutoff = cutoff; break;
+            case CC_FILTER_RESONANCE: filter_resonance = s; break;
+            case CC_FILTER_DRIVE: filter_drive = s; break;
+            case CC_ENV_FILT_AMT: filter_env_amount = s; break;
+            case CC_ENV_FILT_A: filter_attack = s; break;
+            case CC_ENV_FILT_D: filter_decay = fdecay; break;
+            case CC_ENV_FILT_S: filter_sustain = s; break;
+            case CC_ENV_FILT_R: filter_release = s; break;
+            case CC_ENV_AMP_A: amp_attack = s; break;
+            case CC_ENV_AMP_D: amp_decay = s; break;
+            case CC_ENV_AMP_S: amp_sustain = s; break;
+            case CC_ENV_AMP_R: amp_release = s; break;
+            case CC_OSC_1_VOLUME: osc_1_mix = s; break;
+            default: return false;
+        }
+        Update();
+        return true;
+    }
+    bool UpdateHardwareControl(uint8_t cc, float x) {  // SynthVoice.h:101-156
+        return set(cc, x, scale(x, 0, 1, 0, 1, 4), scale(x, 0, 1, 0, 20000, 2.5f), scale(x, 0, 1, 0, 1, 3));
+    }
+    bool UpdateMidiControl(uint8_t cc, uint8_t v) {  // SynthVoice.h:158-229 (the printf in every case is dropped)
+        return set(cc, scale(v, 0, 127, 0, 1, 1), scale(v, 0, 127, 0, 1, 4), scale(v, 0, 127, 0, 20000, 2.5f), scale(v, 0, 127, 0, 1, 3));
+    }
+    static float mtof(float m) { return powf(2.0f, (m - 69.0f) / 12.0f) * 440.0f; }
+    void NoteOn(uint8_t note) {  // SynthVoice.h:245-251
+        gate = 1; playing = note; freq = mtof(note); retrigger = true;
+    }
+    void NoteOff() { gate = 0; playing = 0; }  // SynthVoice.h:253-256
+};
+
 }  // namespace host
 }  // namespace olb

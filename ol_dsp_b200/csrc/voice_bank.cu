@@ -1,0 +1,372 @@
+// voice_bank.cu -- (a6) bank of ol::synth::SynthVoice and (a8) the Polyvoice mixdown.
+//
+// Reference, per output sample (modules/synthlib/SynthVoice.h:41-53):
+//   amp = amp_envelope.Process(gate) * amp_env_amount               DaisyAdsr -> daisysp::Adsr      Adsr.h:48-50
+//   osc.SetFreq(portamento.Process(freq_)); frame = osc.Process()   daisysp::Port Portamento.h:29-32; PolyBLEP saw
+//   fc = filter_cutoff + filter_envelope.Process(gate) * 20000 * filter_env_amount
+//   filter.SetFreq(fc)  (EVERY sample: sinf)                        SvfFilter -> daisysp::Svf       Filter.h:65-108
+//   filter.Process(frame); frame = Low; frame *= amp
+// and the bus (modules/synthlib/Polyvoice.h:28-33): *frame_out += voice frame, in voice order.
+//
+// One voice per thread, all state in registers for the whole block of frames.  Bit-exact pieces (every operation
+// rounded separately, setter maths on the host with the host's libm): envelope stage machine and level recurrence,
+// portamento one-pole, oscillator phase / wrap / PolyBLEP, SVF recurrence.  The one device transcendental is
+// Svf::SetFreq's sinf per sample: CUDA's sinf differs from glibc's by <= 2 ulp, so voice OUTPUT is a tolerance tier
+// (<= 1e-5 of full scale, tests/test_voice_gpu.py) while phase and envelope traces are compared bit for bit.
+//
+// Mixdown: xor-shuffle tree inside the warp (fixed order), one partial per WARP per frame written coalesced 32 frames
+// at a time, then k_bus_reduce sums the warp partials in warp order: deterministic run to run; differs from the
+// reference's sequential voice order by float re-association only (tolerance tier).
+#include <vector>
+
+#include "common.cuh"
+#include "host_params.h"
+
+namespace olb {
+
+enum { VP_FREQ, VP_GATE, VP_RETRIG, VP_PORT_COEFF, VP_SR_RECIP, VP_CUTOFF, VP_F_AMOUNT, VP_A_AMOUNT, VP_SR2, VP_FC_MAX, VP_DAMP_A, VP_DRIVE,
+       VP_A_D0, VP_A_TARGET, VP_A_DD0, VP_A_RD0, VP_A_SUS, VP_F_D0, VP_F_TARGET, VP_F_DD0, VP_F_RD0, VP_F_SUS, VP_COUNT };
+enum { VS_PHASE, VS_PORT_Z, VS_LOW, VS_BAND, VS_A_X, VS_A_MODE, VS_A_GATE, VS_F_X, VS_F_MODE, VS_F_GATE, VS_COUNT };
+
+struct EnvCoef {
+    float a_d0, a_target, d_d0, r_d0, sus;
+};
+
+// daisysp::Adsr::Process (segments idle 0 / attack 1 / decay 2 / release 4)
+__device__ __forceinline__ float env_tick(float &x, int &mode, int &prev_gate, int gate, const EnvCoef &k) {
+    float out = 0.0f;
+    if (gate && !prev_gate) mode = 1;
+    else if (!gate && prev_gate) mode = 4;
+    prev_gate = gate;
+    float d0 = k.a_d0;
+    if (mode == 2) d0 = k.d_d0;
+    else if (mode == 4) d0 = k.r_d0;
+    const float target = mode == 2 ? k.sus : -0.01f;
+    if (mode == 1) {
+        x = __fadd_rn(x, __fmul_rn(d0, __fsub_rn(k.a_target, x)));
+        out = x;
+        if (out > 1.f) { x = out = 1.f; mode = 2; }
+    } else if (mode == 2 || mode == 4) {
+        x = __fadd_rn(x, __fmul_rn(d0, __fsub_rn(target, x)));
+        out = x;
+        if (out < 0.0f) { x = out = 0.f; mode = 0; }
+    }
+    return out;
+}
+
+__device__ __forceinline__ float polyblep(float dt, float t) {
+    if (t < dt) {
+        t = __fdiv_rn(t, dt);
+        return __fsub_rn(__fsub_rn(__fadd_rn(t, t), __fmul_rn(t, t)), 1.0f);
+    }
+    if (t > __fsub_rn(1.0f, dt)) {
+        t = __fdiv_rn(__fsub_rn(t, 1.0f), dt);
+        return __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(t, t), t), t), 1.0f);
+    }
+    return 0.0f;
+}
+
+// trace (optional): 4 floats per voice-frame = oscillator output, amp envelope, filter envelope, phase after the tick
+__global__ void __launch_bounds__(128) k_voice(float *out, float *partial, float *trace, uint32_t frames, uint32_t V,
+                                               const float *__restrict__ par, float *state, uint32_t partial_ld) {
+    const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = v < V;
+    const uint32_t vv = live ? v : V - 1;  // dead lanes shadow a live voice so the warp reductions stay convergent
+    auto P = [&](int p) { return par[(size_t) p * V + vv]; };
+    const float freq = P(VP_FREQ), port_coeff = P(VP_PORT_COEFF), sr_recip = P(VP_SR_RECIP), cutoff = P(VP_CUTOFF);
+    const float f_amount = P(VP_F_AMOUNT), a_amount = P(VP_A_AMOUNT), sr2 = P(VP_SR2), fc_max = P(VP_FC_MAX);
+    const float damp_a = P(VP_DAMP_A), drive = P(VP_DRIVE);
+    const int gate = (int) __float_as_uint(P(VP_GATE));
+    const bool retrig = __float_as_uint(P(VP_RETRIG)) != 0;
+    const EnvCoef ka{P(VP_A_D0), P(VP_A_TARGET), P(VP_A_DD0), P(VP_A_RD0), P(VP_A_SUS)};
+    const EnvCoef kf{P(VP_F_D0), P(VP_F_TARGET), P(VP_F_DD0), P(VP_F_RD0), P(VP_F_SUS)};
+    auto S = [&](int s) -> float & { return state[(size_t) s * V + vv]; };
+    float phase = S(VS_PHASE), port_z = S(VS_PORT_Z), low = S(VS_LOW), band = S(VS_BAND), a_x = S(VS_A_X), f_x = S(VS_F_X);
+    int a_mode = (int) __float_as_uint(S(VS_A_MODE)), a_gate = (int) __float_as_uint(S(VS_A_GATE));
+    int f_mode = (int) __float_as_uint(S(VS_F_MODE)), f_gate = (int) __float_as_uint(S(VS_F_GATE));
+    if (retrig) {  // NoteOn: Retrigger(hard) on both envelopes (SynthVoice.h:249-250)
+        a_mode = 1; a_x = 0.f;
+        f_mode = 1; f_x = 0.f;
+    }
+    const int lane = threadIdx.x & 31;
+    const uint32_t warp_global = v >> 5;
+    float acc = 0.f;  // this lane's frame of the current 32-frame group of warp sums
+
+    for (uint32_t n = 0; n < frames; n++) {
+        const float amp_env = env_tick(a_x, a_mode, a_gate, gate, ka);
+        const float amp = __fmul_rn(amp_env, a_amount);
+        port_z = __fadd_rn(freq, __fmul_rn(port_coeff, __fsub_rn(port_z, freq)));  // Portamento.h:29-32
+        const float inc = __fmul_rn(port_z, sr_recip);
+        // PolyBLEP saw, amp 0.5 (OscillatorSoundSource.h:21-22)
+        float o = __fsub_rn(__fmul_rn(2.0f, phase), 1.0f);
+        o = __fsub_rn(o, polyblep(inc, phase));
+        o = __fmul_rn(o, -1.0f);
+        phase = __fadd_rn(phase, inc);
+        if (phase > 1.0f) phase = __fsub_rn(phase, 1.0f);
+        const float frame = __fmul_rn(o, 0.5f);
+        const float fenv = env_tick(f_x, f_mode, f_gate, gate, kf);
+        const float ff = __fadd_rn(cutoff, __fmul_rn(__fmul_rn(fenv, 20000.f), f_amount));
+        // Svf::SetFreq every sample
+        const float fc = fminf(fmaxf(ff, 1.0e-6f), fc_max);
+        const float sfreq = __fmul_rn(2.0f, sinf(__fmul_rn(3.1415927410125732421875f, fminf(0.25f, __fdiv_rn(fc, sr2)))));
+        const float damp = fminf(damp_a, fminf(2.0f, __fsub_rn(__fdiv_rn(2.0f, sfreq), __fmul_rn(sfreq, 0.5f))));
+        // Svf::Process, two passes, low output
+        float notch = __fsub_rn(frame, __fmul_rn(damp, band));
+        low = __fadd_rn(low, __fmul_rn(sfreq, band));
+        float high = __fsub_rn(notch, low);
+        band = __fsub_rn(__fadd_rn(__fmul_rn(sfreq, high), band), __fmul_rn(__fmul_rn(__fmul_rn(drive, band), band), band));
+        float o_low = __fmul_rn(0.5f, low);
+        notch = __fsub_rn(frame, __fmul_rn(damp, band));
+        low = __fadd_rn(low, __fmul_rn(sfreq, band));
+        high = __fsub_rn(notch, low);
+        band = __fsub_rn(__fadd_rn(__fmul_rn(sfreq, high), band), __fmul_rn(__fmul_rn(__fmul_rn(drive, band), band), band));
+        o_low = __fadd_rn(o_low, __fmul_rn(0.5f, low));
+        const float y = __fmul_rn(o_low, amp);
+        if (out && live) out[(size_t) n * V + v] = y;
+        if (trace && live) {
+            float4 t4 = make_float4(frame, amp_env, fenv, phase);
+            reinterpret_cast<float4 *>(trace)[(size_t) n * V + v] = t4;
+        }
+        if (partial) {
+            float s = live ? y : 0.f;
+#pragma unroll
+            for (int m = 16; m >= 1; m >>= 1) s = __fadd_rn(s, __shfl_xor_sync(0xffffffffu, s, m));
+            if ((int) (n & 31u) == lane) acc = s;
+            if ((n & 31u) == 31u || n + 1 == frames) {
+                const uint32_t n0 = n & ~31u;
+                if (n0 + lane <= n) partial[(size_t) warp_global * partial_ld + n0 + lane] = acc;
+            }
+        }
+    }
+    if (live) {
+        S(VS_PHASE) = phase; S(VS_PORT_Z) = port_z; S(VS_LOW) = low; S(VS_BAND) = band; S(VS_A_X) = a_x; S(VS_F_X) = f_x;
+        S(VS_A_MODE) = __uint_as_float((uint32_t) a_mode); S(VS_A_GATE) = __uint_as_float((uint32_t) a_gate);
+        S(VS_F_MODE) = __uint_as_float((uint32_t) f_mode); S(VS_F_GATE) = __uint_as_float((uint32_t) f_gate);
+    }
+}
+
+// bus[n * bus_stride + c] (+)= gain * sum over warps (in warp order) for every channel c < bus_channels:
+// Polyvoice is mono; the caller duplicates it to stereo (modules/ol_daisy/app/synth/main.cpp:83).
+__global__ void k_bus_reduce(const float *__restrict__ partial, uint32_t warps, uint32_t partial_ld, float *bus, uint32_t frames,
+                             uint32_t bus_channels, int accumulate, float gain) {
+    const uint32_t n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n >= frames) return;
+    float s = 0.f;
+    for (uint32_t w = 0; w < warps; w++) s = __fadd_rn(s, partial[(size_t) w * partial_ld + n]);
+    s = __fmul_rn(s, gain);
+    for (uint32_t c = 0; c < bus_channels; c++) {
+        float *p = bus + (size_t) n * bus_channels + c;
+        *p = accumulate ? __fadd_rn(*p, s) : s;
+    }
+}
+
+}  // namespace olb
+
+using namespace olb;
+
+// ================================================================================================
+// Host side: one host::VoiceParams per voice carries the reference object's members.
+struct olb_voice {
+    int device = 0;
+    uint32_t V = 0;
+    std::vector<host::VoiceParams> voices;
+    bool dirty = true;
+    bool retrig_pending = false;
+    float *d_par = nullptr, *d_state = nullptr, *d_partial = nullptr;
+    uint32_t partial_ld = 0;  // frames capacity of the warp-partial buffer
+    std::vector<float> stage;
+};
+
+static float vbits_f(uint32_t u) {
+    float f;
+    memcpy(&f, &u, 4);
+    return f;
+}
+
+static int voice_upload(olb_voice *h, cudaStream_t st) {
+    const size_t V = h->V;
+    h->stage.resize((size_t) VP_COUNT * V);
+    float *s = h->stage.data();
+    for (size_t i = 0; i < V; i++) {
+        const host::VoiceParams &u = h->voices[i];
+        s[VP_FREQ * V + i] = u.freq;
+        s[VP_GATE * V + i] = vbits_f((uint32_t) u.gate);
+        s[VP_RETRIG * V + i] = vbits_f(u.retrigger ? 1u : 0u);
+        s[VP_PORT_COEFF * V + i] = u.port_coeff;
+        s[VP_SR_RECIP * V + i] = 1.0f / u.sample_rate;  // Oscillator::Init
+        s[VP_CUTOFF * V + i] = u.filter_cutoff;
+        s[VP_F_AMOUNT * V + i] = u.filter_env_amount;
+        s[VP_A_AMOUNT * V + i] = u.amp_env_amount;
+        s[VP_SR2 * V + i] = u.svf.sr * 2.0f;
+        s[VP_FC_MAX * V + i] = u.svf.fc_max;
+        s[VP_DAMP_A * V + i] = 2.0f * (1.0f - powf(u.svf.res, 0.25f));
+        s[VP_DRIVE * V + i] = u.svf.drive;
+        s[VP_A_D0 * V + i] = u.amp_env.a_d0; s[VP_A_TARGET * V + i] = u.amp_env.a_target; s[VP_A_DD0 * V + i] = u.amp_env.d_d0;
+        s[VP_A_RD0 * V + i] = u.amp_env.r_d0; s[VP_A_SUS * V + i] = u.amp_env.sus;
+        s[VP_F_D0 * V + i] = u.filter_env.a_d0; s[VP_F_TARGET * V + i] = u.filter_env.a_target; s[VP_F_DD0 * V + i] = u.filter_env.d_d0;
+        s[VP_F_RD0 * V + i] = u.filter_env.r_d0; s[VP_F_SUS * V + i] = u.filter_env.sus;
+    }
+    OLB_CUDA(cudaMemcpyAsync(h->d_par, s, h->stage.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+    OLB_CUDA(cudaStreamSynchronize(st));
+    h->dirty = false;
+    return OLB_OK;
+}
+
+static int voice_init_all(olb_voice *h, float sr) {
+    for (auto &u : h->voices) {
+        u.Init(sr);
+        u.retrigger = false;
+    }
+    OLB_CUDA(cudaMemset(h->d_state, 0, (size_t) VS_COUNT * h->V * sizeof(float)));
+    h->dirty = true;
+    return OLB_OK;
+}
+
+static void voice_free(olb_voice *h) {
+    cudaFree(h->d_par); cudaFree(h->d_state); cudaFree(h->d_partial);
+    delete h;
+}
+
+OLB_API int olb_voice_create(int device, uint32_t voices, float sample_rate, olb_voice **out) {
+    OLB_ARG(out, "olb_voice_create: out is NULL");
+    *out = nullptr;
+    OLB_ARG(voices > 0, "olb_voice_create: voices must be > 0");
+    int rc = require_sm100(device);
+    if (rc) return rc;
+    DeviceGuard g(device);
+    olb_voice *h = new olb_voice();
+    h->device = device;
+    h->V = voices;
+    h->voices.resize(voices);
+    cudaError_t e = cudaMalloc(&h->d_par, (size_t) VP_COUNT * voices * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_state, (size_t) VS_COUNT * voices * sizeof(float));
+    if (e != cudaSuccess) {
+        voice_free(h);
+        return fail_cuda(e, "allocating voice bank", __FILE__, __LINE__);
+    }
+    rc = voice_init_all(h, sample_rate);
+    if (rc) {
+        voice_free(h);
+        return rc;
+    }
+    *out = h;
+    return OLB_OK;
+}
+
+OLB_API int olb_voice_destroy(olb_voice *h) {
+    if (!h) return OLB_OK;
+    DeviceGuard g(h->device);
+    voice_free(h);
+    return OLB_OK;
+}
+
+OLB_API int olb_voice_init(olb_voice *h, float sample_rate) {
+    OLB_ARG(h, "olb_voice_init: NULL handle");
+    DeviceGuard g(h->device);
+    return voice_init_all(h, sample_rate);
+}
+
+#define OLB_VOICE_RANGE(fn)                                                                                              \
+    OLB_ARG(h, fn ": NULL handle");                                                                                      \
+    OLB_ARG((uint64_t) first + count <= h->V, fn ": range [%u, %u) exceeds %u voices", first, first + count, h->V)
+
+OLB_API int olb_voice_update_midi(olb_voice *h, uint32_t first, uint32_t count, uint8_t control, uint8_t value) {
+    OLB_VOICE_RANGE("olb_voice_update_midi");
+    for (uint32_t i = first; i < first + count; i++) h->voices[i].UpdateMidiControl(control, value);
+    h->dirty = true;
+    return OLB_OK;
+}
+
+OLB_API int olb_voice_update_hw(olb_voice *h, uint32_t first, uint32_t count, uint8_t control, const float *values_host, uint32_t stride) {
+    OLB_VOICE_RANGE("olb_voice_update_hw");
+    OLB_ARG(values_host, "olb_voice_update_hw: values_host is NULL");
+    for (uint32_t i = 0; i < count; i++) h->voices[first + i].UpdateHardwareControl(control, values_host[(size_t) i * stride]);
+    h->dirty = true;
+    return OLB_OK;
+}
+
+OLB_API int olb_voice_update_config(olb_voice *h, uint32_t first, uint32_t count, const float *config16_host) {
+    OLB_VOICE_RANGE("olb_voice_update_config");
+    OLB_ARG(config16_host, "olb_voice_update_config: config is NULL");
+    for (uint32_t i = first; i < first + count; i++) h->voices[i].UpdateConfig(config16_host);
+    h->dirty = true;
+    return OLB_OK;
+}
+
+OLB_API int olb_voice_note_on(olb_voice *h, uint32_t first, uint32_t count, const uint8_t *notes_host, uint32_t stride, uint8_t velocity) {
+    OLB_VOICE_RANGE("olb_voice_note_on");
+    OLB_ARG(notes_host, "olb_voice_note_on: notes_host is NULL");
+    (void) velocity;  // the reference ignores it too (SynthVoice.h:245-251)
+    for (uint32_t i = 0; i < count; i++) h->voices[first + i].NoteOn(notes_host[(size_t) i * stride]);
+    h->dirty = true;
+    h->retrig_pending = true;
+    return OLB_OK;
+}
+
+OLB_API int olb_voice_note_off(olb_voice *h, uint32_t first, uint32_t count) {
+    OLB_VOICE_RANGE("olb_voice_note_off");
+    for (uint32_t i = first; i < first + count; i++) h->voices[i].NoteOff();
+    h->dirty = true;
+    return OLB_OK;
+}
+
+OLB_API int olb_voice_set_gate(olb_voice *h, uint32_t first, uint32_t count, int gate) {
+    OLB_VOICE_RANGE("olb_voice_set_gate");
+    for (uint32_t i = first; i < first + count; i++) h->voices[i].gate = gate ? 1 : 0;
+    h->dirty = true;
+    return OLB_OK;
+}
+
+OLB_API int olb_voice_set_frequency(olb_voice *h, uint32_t first, uint32_t count, const float *freqs_host, uint32_t stride) {
+    OLB_VOICE_RANGE("olb_voice_set_frequency");
+    OLB_ARG(freqs_host, "olb_voice_set_frequency: freqs_host is NULL");
+    for (uint32_t i = 0; i < count; i++) h->voices[first + i].freq = freqs_host[(size_t) i * stride];
+    h->dirty = true;
+    return OLB_OK;
+}
+
+OLB_API int olb_voice_playing(olb_voice *h, uint32_t first, uint32_t count, uint8_t *playing_host) {
+    OLB_VOICE_RANGE("olb_voice_playing");
+    OLB_ARG(playing_host, "olb_voice_playing: playing_host is NULL");
+    for (uint32_t i = 0; i < count; i++) playing_host[i] = h->voices[first + i].playing;
+    return OLB_OK;
+}
+
+OLB_API int olb_voice_process(olb_voice *h, float *out_dev, float *bus_dev, uint32_t bus_channels, int accumulate, float bus_gain,
+                              float *trace_dev, uint64_t frames, void *stream) {
+    OLB_ARG(h, "olb_voice_process: NULL handle");
+    if (frames == 0) return OLB_OK;
+    OLB_ARG(out_dev || bus_dev || trace_dev, "olb_voice_process: no output buffer given");
+    OLB_ARG(!bus_dev || (bus_channels >= 1 && bus_channels <= 8), "olb_voice_process: bus_channels must be 1..8");
+    OLB_ARG(frames < (1ull << 31), "olb_voice_process: at most 2^31-1 frames per call");
+    DeviceGuard g(h->device);
+    cudaStream_t st = (cudaStream_t) stream;
+    if (h->dirty) {
+        int rc = voice_upload(h, st);
+        if (rc) return rc;
+    }
+    const uint32_t warps = (h->V + 31) / 32;
+    if (bus_dev && h->partial_ld < frames) {
+        OLB_CUDA(cudaStreamSynchronize(st));
+        cudaFree(h->d_partial);
+        h->d_partial = nullptr;
+        h->partial_ld = 0;
+        const uint32_t ld = (uint32_t) ((frames + 31) / 32 * 32);
+        OLB_CUDA(cudaMalloc(&h->d_partial, (size_t) warps * ld * sizeof(float)));
+        h->partial_ld = ld;
+    }
+    k_voice<<<(h->V + 127) / 128, 128, 0, st>>>(out_dev, bus_dev ? h->d_partial : nullptr, trace_dev, (uint32_t) frames, h->V, h->d_par,
+                                               h->d_state, h->partial_ld);
+    OLB_LAUNCHED();
+    if (bus_dev) {
+        k_bus_reduce<<<(unsigned) ((frames + 127) / 128), 128, 0, st>>>(h->d_partial, warps, h->partial_ld, bus_dev, (uint32_t) frames,
+                                                                       bus_channels, accumulate, bus_gain);
+        OLB_LAUNCHED();
+    }
+    if (h->retrig_pending) {  // the retrigger was consumed by this launch
+        for (auto &u : h->voices) u.retrigger = false;
+        h->retrig_pending = false;
+        h->dirty = true;
+    }
+    return OLB_OK;
+}

@@ -1,0 +1,152 @@
+"""GPU parity of the SynthVoice bank (row a6) and the Polyvoice mixdown (row a8) through the C ABI.
+Bit-exact: oscillator output and phase, both envelope traces (stage logic + level recurrence), portamento.
+Tolerance (<= 1e-5 of full scale, the bar north_star states): the voice OUTPUT, because Svf::SetFreq's per-sample sinf
+runs in CUDA's libm on the device and in glibc in the reference; and the bus, whose summation order differs."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import loader
+from ol_dsp_b200 import Polyvoice, VoiceBank
+from tests.golden import make_golden as mg
+
+pytestmark = pytest.mark.gpu
+G = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+TOL = 1e-5
+
+
+def bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def apply(bank, e, voice=None):
+    f, k, a, v = e[:4]
+    rng = {} if voice is None else {"first": voice, "count": 1}
+    if k == loader.EV_MIDI_CC:
+        bank.UpdateMidiControl(a, int(v), **rng)
+    elif k == loader.EV_HW_CC:
+        bank.UpdateHardwareControl(a, v, **rng)
+    elif k == loader.EV_NOTE_ON:
+        bank.NoteOn(a, int(v), **rng)
+    elif k == loader.EV_NOTE_OFF:
+        bank.NoteOff(**rng)
+    elif k == loader.EV_INIT:
+        bank.Init(v)
+    elif k == loader.EV_SET_FREQ:
+        bank.SetFrequency(v, **rng)
+    elif k == loader.EV_GATE_ON:
+        bank.GateOn(**rng)
+    elif k == loader.EV_GATE_OFF:
+        bank.GateOff(**rng)
+
+
+def run_voices(V, frames, events_per_voice, config=None, trace=False, sr=48000.0):
+    b = VoiceBank(V, sample_rate=sr)
+    if config is not None:
+        b.UpdateConfig(config)
+    cuts = sorted({0, frames} | {e[0] for ev in events_per_voice for e in ev})
+    out = torch.empty((frames, V), dtype=torch.float32, device="cuda")
+    tr = torch.empty((frames, V, 4), dtype=torch.float32, device="cuda") if trace else None
+    for a, z in zip(cuts[:-1], cuts[1:]):
+        for i, ev in enumerate(events_per_voice):
+            for e in ev:
+                if e[0] == a:
+                    apply(b, e, i)
+        b.ProcessDevice(z - a, out_ptr=out[a:].data_ptr(), trace_ptr=tr[a:].data_ptr() if trace else 0)
+    torch.cuda.synchronize()
+    b.close()
+    return out.cpu().numpy(), (tr.cpu().numpy() if trace else None)
+
+
+def test_voice_matches_reference_golden_and_traces(orc):
+    """tests/golden/synth.npz 'voice': the reference's own SynthVoice run through VOICE_EVENTS (CCs, two notes,
+    portamento change).  Voice 1 of the bank runs the script; voices 0 and 2 are bystanders with other scripts."""
+    g = np.load(os.path.join(G, "synth.npz"))
+    frames = g["voice"].shape[0]
+    other = [(0, loader.EV_NOTE_ON, 40, 100), (100, loader.EV_HW_CC, 41, 0.5), (4000, loader.EV_NOTE_OFF, 40, 0)]
+    y, tr = run_voices(3, frames, [other, mg.VOICE_EVENTS, []], trace=True)
+    assert np.abs(y[:, 1] - g["voice"]).max() <= TOL
+    want, wtr = orc.voice(frames, 48000.0, None, mg.VOICE_EVENTS, trace=True)
+    assert np.array_equal(bits(tr[:, 1, 0]), bits(wtr[:, 0])), "oscillator output"
+    assert np.array_equal(bits(tr[:, 1, 1]), bits(wtr[:, 1])), "amp envelope"
+    assert np.array_equal(bits(tr[:, 1, 2]), bits(wtr[:, 2])), "filter envelope"
+    assert np.array_equal(bits(tr[:, 1, 3]), bits(wtr[:, 3])), "phase"
+    assert np.abs(y[:, 1] - want).max() <= TOL
+    w0, t0 = orc.voice(frames, 48000.0, None, other, trace=True)
+    assert np.array_equal(bits(tr[:, 0, 3]), bits(t0[:, 3])) and np.abs(y[:, 0] - w0).max() <= TOL
+    assert float(np.abs(y[:, 2]).max()) == 0.0  # an idle voice is silent
+
+
+def test_reference_synth_test_voice_default_constructor():
+    """test/synth_test.cpp:102-148 replayed on a one-voice bank: frame == 0 right after NoteOn+NoteOff, != 0 and != 1 on
+    the next gated frame, == 0 with amp_env_amount 0 and != 0 with 1."""
+    b = VoiceBank(1, sample_rate=128.0)
+    f = torch.full((1, 1), 7.0, dtype=torch.float32, device="cuda")
+
+    def frame():
+        b.ProcessDevice(1, out_ptr=f.data_ptr())
+        torch.cuda.synchronize()
+        return float(f[0, 0])
+
+    b.NoteOn(60, 100)
+    b.NoteOff()
+    assert frame() == 0.0
+    b.NoteOn(60, 100)
+    v = frame()
+    assert v != 0.0 and v != 1.0
+    b.UpdateHardwareControl(7, 0.0)  # CC_CTL_VOLUME -> amp_env_amount
+    assert frame() == 0.0
+    b.UpdateHardwareControl(7, 1.0)
+    assert frame() != 0.0
+    b.close()
+
+
+def test_polyvoice_allocation_and_bus(orc):
+    """tests/golden/synth.npz 'poly4': Polyvoice with 4 voices, first-free allocation, accumulate into a zeroed bus."""
+    g = np.load(os.path.join(G, "synth.npz"))
+    want = g["poly4"]
+    frames = want.shape[0]
+    ev = [(0, loader.EV_NOTE_ON, 48, 100), (5, loader.EV_NOTE_ON, 55, 100), (700, loader.EV_NOTE_ON, 64, 100),
+          (1500, loader.EV_NOTE_OFF, 55, 0), (1600, loader.EV_NOTE_ON, 67, 100), (2500, loader.EV_NOTE_OFF, 48, 0)]
+    bank = VoiceBank(4)
+    poly = Polyvoice(bank)
+    bus = torch.zeros((frames, 1), dtype=torch.float32, device="cuda")
+    cuts = sorted({0, frames} | {e[0] for e in ev})
+    for a, z in zip(cuts[:-1], cuts[1:]):
+        for e in ev:
+            if e[0] == a:
+                (poly.NoteOn if e[1] == loader.EV_NOTE_ON else poly.NoteOff)(e[2], e[3])
+        poly.Process(z - a, bus[a:].data_ptr())
+    torch.cuda.synchronize()
+    assert np.abs(bus.cpu().numpy()[:, 0] - want).max() <= 4 * TOL  # 4 voices summed
+    assert list(bank.Playing()) == [0, 67, 64, 0]
+    bank.close()
+
+
+def test_wide_bank_bus_is_deterministic_and_equals_the_sum_of_voices():
+    """C4-shaped (scaled down in time): 65 536 voices, note 36 + (v mod 61), presets through the MIDI maps; the stereo bus
+    equals the float64 sum of the per-voice outputs within re-association error, and is bit-identical run to run."""
+    V, T = 65536, 256
+    notes = (36 + np.arange(V) % 61).astype(np.uint8)
+
+    def run():
+        b = VoiceBank(V)
+        for cc, val in ((41, 70), (42, 30), (73, 64), (75, 60), (108, 10), (111, 40)):
+            b.UpdateMidiControl(cc, val)
+        b.NoteOn(notes)
+        out = torch.empty((T, V), dtype=torch.float32, device="cuda")
+        bus = torch.zeros((T, 2), dtype=torch.float32, device="cuda")
+        b.ProcessDevice(T, out_ptr=out.data_ptr(), bus_ptr=bus.data_ptr(), bus_channels=2, bus_gain=1.0 / V)
+        torch.cuda.synchronize()
+        b.close()
+        return out, bus
+
+    out, bus = run()
+    _, bus2 = run()
+    assert torch.equal(bus, bus2)
+    assert torch.equal(bus[:, 0], bus[:, 1])
+    ref = out.double().sum(dim=1) / V
+    assert float((bus[:, 0].double() - ref).abs().max()) <= 1e-6
+    assert float(out.abs().max()) > 0.01 and torch.isfinite(out).all()
