@@ -159,7 +159,7 @@ def run_olbank(args):
     import torch
     import torch.distributed as dist
 
-    from ol_dsp_b200 import MODE_EXACT, MODE_FAST, MODE_FMA, BiquadBank, _lib, c2_coefs, noise_device
+    from ol_dsp_b200 import MODE_EXACT, MODE_FAST, MODE_FMA, BiquadBank, _lib, c2_coefs, noise_device, shard_range
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -181,7 +181,8 @@ def run_olbank(args):
     x = torch.empty((F, Cn), dtype=torch.float32, device="cuda")
     y = torch.empty_like(x)
     stream = torch.cuda.current_stream()
-    noise_device(x.data_ptr(), SEED, rank * Cn, Cn, 0, F, 1.0, 0, stream.cuda_stream)
+    first, _ = shard_range(world * Cn, rank, world)  # rank r owns channels [r*Cn, (r+1)*Cn) of the job
+    noise_device(x.data_ptr(), SEED, first, Cn, 0, F, 1.0, 0, stream.cuda_stream)
 
     def step():
         bank.ProcessDevice(x.data_ptr(), y.data_ptr(), F, 0, stream.cuda_stream)

@@ -92,14 +92,65 @@ def bench_fx(a, kind, name, bytes_per_unit):
     b.close()
 
 
+def bench_voices(a):
+    """C4: `instances` voices PER GPU (weak), note 36 + (v mod 61), presets through the MIDI maps, NoteOn at t = 0; each rank
+    reduces its voices to a partial stereo bus on chip, then ONE NCCL all-reduce of [frames][2] floats per step."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from ol_dsp_b200 import VoiceBank, reduce_bus
+    rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    V, F = a.instances, a.frames
+    b = VoiceBank(V, device=local)
+    for cc, val in ((41, 70), (42, 30), (73, 64), (75, 60), (108, 10), (111, 40)):
+        b.UpdateMidiControl(cc, val)
+    b.NoteOn((36 + (rank * V + np.arange(V)) % 61).astype(np.uint8))
+    bus = torch.zeros((F, 2), dtype=torch.float32, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+
+    def step():
+        b.ProcessDevice(F, bus_ptr=bus.data_ptr(), bus_channels=2, bus_gain=1.0 / (V * world), stream=st)
+        if world > 1:
+            reduce_bus(bus)
+
+    for _ in range(2):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(a.steps):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    dt = float(ms.item()) * 1e-3 / a.steps
+    if rank == 0:
+        units = V * world * F
+        print(json.dumps({"unit": "voices", "metric": "voice-samples/s", "value": units / dt, "ms_per_step": dt * 1e3, "n_gpus": world,
+                          "voices_per_gpu": V, "frames": F, "scaling": "weak",
+                          "collective": "one NCCL all-reduce of the [frames][2] fp32 bus per step" if world > 1 else "none (1 GPU)",
+                          "bus_bytes_per_step": 8 * F, "bound": "fp32/sfu issue (no input stream; 8 B/frame/GPU out)",
+                          "checksum": float(bus.double().sum().item())}), flush=True)
+    b.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
 if __name__ == "__main__":
     p = argparse.ArgumentParser()
-    p.add_argument("unit", choices=["dattorro", "filterfx", "delayfx", "fxrack"])
+    p.add_argument("unit", choices=["dattorro", "filterfx", "delayfx", "fxrack", "voices"])
     p.add_argument("--instances", type=int, default=8192)
     p.add_argument("--frames", type=int, default=48000)
     p.add_argument("--steps", type=int, default=3)
     p.add_argument("--cpu", action="store_true")
     a = p.parse_args()
     from ol_dsp_b200 import fx as _fx
-    {"dattorro": bench_dattorro, "filterfx": lambda a: bench_fx(a, _fx.FILTER, "filterfx", 8),
+    {"voices": bench_voices, "dattorro": bench_dattorro, "filterfx": lambda a: bench_fx(a, _fx.FILTER, "filterfx", 8),
      "delayfx": lambda a: bench_fx(a, _fx.DELAY, "delayfx", 16), "fxrack": lambda a: bench_fx(a, _fx.RACK, "fxrack", 16)}[a.unit](a)
