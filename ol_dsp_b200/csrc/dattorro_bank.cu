@@ -157,15 +157,20 @@ __device__ __forceinline__ void excursion_step(uint32_t t, uint32_t &off_a, uint
     }
 }
 
-template <int D>
+// L = active lanes per warp: 8 192 instances are only 256 full warps for 592 SM sub-partitions, and each warp is one
+// long dependent chain; with L = 16 or 8 (a tap row is then a 64- or 32-byte segment, still whole sectors) every
+// sub-partition gets several chains to interleave.
+template <int D, int L>
 __global__ void __launch_bounds__(kPfThreads) k_dattorro_pf(const float *__restrict__ in, float *__restrict__ out_l, float *__restrict__ out_r,
                                                             uint32_t frames, uint32_t I, float *slab, float *lp, const float *__restrict__ par,
                                                             const __grid_constant__ PlateGeom g0, uint32_t t0) {
-    extern __shared__ float pf[];  // [D][kPfSlots][kPfThreads]
-    const uint32_t inst = blockIdx.x * blockDim.x + threadIdx.x;
-    if (inst >= I) return;
-    float *mine = pf + threadIdx.x;
-    auto SLOT = [&](uint32_t d, int k) -> float * { return mine + ((size_t) d * kPfSlots + k) * kPfThreads; };
+    extern __shared__ float pf[];  // [D][kPfSlots][kAct]
+    constexpr int kAct = (kPfThreads / 32) * L;  // active threads per CTA
+    const uint32_t wic = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t inst = (blockIdx.x * (kPfThreads / 32) + wic) * L + lane;
+    if (lane >= (uint32_t) L || inst >= I) return;
+    float *mine = pf + wic * L + lane;
+    auto SLOT = [&](uint32_t d, int k) -> float * { return mine + ((size_t) d * kPfSlots + k) * kAct; };
     const float pre_filter = par[0 * (size_t) I + inst], in_diff1 = par[1 * (size_t) I + inst], in_diff2 = par[2 * (size_t) I + inst];
     const float decay_diff1 = par[3 * (size_t) I + inst], damping = par[4 * (size_t) I + inst], decay = par[5 * (size_t) I + inst];
     const float decay_diff2 = par[6 * (size_t) I + inst];
@@ -404,22 +409,25 @@ OLB_API int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *ou
         OLB_CUDA(cudaStreamSynchronize(st));  // par_host may change right after we return
         h->par_dirty = false;
     }
-    // OLB_PLATE_KERNEL=simple|pf8|pf16 selects the kernel (tuning aid); default: the 8-deep pipelined one (16 deep measures the same)
-    static const int which = [] {
-        const char *e = getenv("OLB_PLATE_KERNEL");
-        return !e ? 8 : (!strcmp(e, "simple") ? 0 : (!strcmp(e, "pf16") ? 16 : 8));
-    }();
-    const unsigned grid = (h->I + kPfThreads - 1) / kPfThreads;
-    if (which == 0) {
+    // OLB_PLATE_KERNEL=simple selects the one-frame-at-a-time kernel; OLB_PLATE_LANES=32|16|8 overrides the active lanes per
+    // warp of the pipelined one (default: the widest that leaves >= 2 warps per SM sub-partition, down to 8)
+    const char *ek = getenv("OLB_PLATE_KERNEL"), *el = getenv("OLB_PLATE_LANES");
+    const int forced = el ? atoi(el) : 0;
+    const int lanes = (forced == 32 || forced == 16 || forced == 8) ? forced : (h->I >= 1184u * 32 ? 32 : (h->I >= 1184u * 16 ? 16 : 8));
+    if (ek && !strcmp(ek, "simple")) {
         k_dattorro<<<(h->I + 63) / 64, 64, 0, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I, h->d_slab, h->d_lp, h->d_par, h->geom, h->t);
-    } else if (which == 8) {
-        constexpr size_t smem = (size_t) 8 * kPfSlots * kPfThreads * sizeof(float);
-        OLB_CUDA(cudaFuncSetAttribute(k_dattorro_pf<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        k_dattorro_pf<8><<<grid, kPfThreads, smem, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I, h->d_slab, h->d_lp, h->d_par, h->geom, h->t);
     } else {
-        constexpr size_t smem = (size_t) 16 * kPfSlots * kPfThreads * sizeof(float);
-        OLB_CUDA(cudaFuncSetAttribute(k_dattorro_pf<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        k_dattorro_pf<16><<<grid, kPfThreads, smem, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I, h->d_slab, h->d_lp, h->d_par, h->geom, h->t);
+        constexpr int D = 8;
+        const unsigned warps = (h->I + lanes - 1) / lanes, grid = (warps + kPfThreads / 32 - 1) / (kPfThreads / 32);
+        const size_t smem = (size_t) D * kPfSlots * (kPfThreads / 32) * lanes * sizeof(float);
+#define OLB_PLATE_GO(LN)                                                                                                          \
+    do {                                                                                                                          \
+        OLB_CUDA(cudaFuncSetAttribute(k_dattorro_pf<D, LN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));            \
+        k_dattorro_pf<D, LN><<<grid, kPfThreads, smem, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I, h->d_slab, h->d_lp, \
+                                                             h->d_par, h->geom, h->t);                                            \
+    } while (0)
+        if (lanes == 32) OLB_PLATE_GO(32); else if (lanes == 16) OLB_PLATE_GO(16); else OLB_PLATE_GO(8);
+#undef OLB_PLATE_GO
     }
     OLB_LAUNCHED();
     // advance the shared counter and the excursion exactly as the kernel did

@@ -15,6 +15,8 @@
 //   ring   [instances][48 000] fp32, one contiguous line per instance (delay times differ per instance, so rings are
 //          walked per thread; a 32-byte sector is consumed over 8 consecutive samples out of L1/L2).  The write
 //          pointer is shared by the bank (every instance is Init()ed and ticked together).
+#include <stdlib.h>
+
 #include <vector>
 
 #include "common.cuh"
@@ -90,6 +92,106 @@ __global__ void __launch_bounds__(64) k_fx(const float *in, float *out, uint32_t
         if (KIND == OLB_FX_FILTER || KIND == OLB_FX_RACK) v = svf_tick(v, f_low, f_band, kf);
         if (KIND == OLB_FX_RACK) v = __fmul_rn(v, master);
         out[(size_t) n * I + inst] = v;
+    }
+    svf[inst] = f_low;
+    svf[(size_t) I + inst] = f_band;
+    svf[2 * (size_t) I + inst] = w_low;
+    svf[3 * (size_t) I + inst] = w_band;
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_fx_pf: the same arithmetic with (1) register double buffering -- the inputs (and, for the delay kinds, the ring
+// reads) of frames n+B .. n+2B-1 are in flight while frames n .. n+B-1 run, so the HBM round trip is paid once per B
+// frames instead of once per frame (in and out may alias, so the compiler will not hoist the loads itself) -- and
+// (2) L active lanes per warp: a bank of a few thousand instances is only a few hundred full warps for 592 SM
+// sub-partitions and each warp is one long dependent chain, so narrower warps (L = 16 or 8; a warp row is then a
+// 64- or 32-byte segment, still whole sectors) give every sub-partition several chains to interleave.
+// Ring reads run ahead only when the delay exceeds the look-ahead (2B + 2 samples); shorter delays take the
+// direct path (read after the previous frame's write), lane by lane.
+constexpr int kFxB = 8;
+
+template <int KIND, int L>
+__global__ void __launch_bounds__(64) k_fx_pf(const float *in, float *out, uint32_t frames, uint32_t I,
+                                              const float *__restrict__ par, float *svf, float *ring_all, uint32_t wp0) {
+    constexpr bool kHasRing = (KIND == OLB_FX_DELAY || KIND == OLB_FX_RACK);
+    constexpr int B = kFxB;
+    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    const uint32_t inst = warp * L + lane;
+    if (lane >= (uint32_t) L || inst >= I) return;
+    auto P = [&](int p) { return par[(size_t) p * I + inst]; };
+    const SvfCoef kf{P(P_F_FREQ), P(P_F_DAMP), P(P_F_DRIVE), (int) __float_as_uint(P(P_F_TYPE))};
+    const SvfCoef kw{P(P_W_FREQ), P(P_W_DAMP), P(P_W_DRIVE), (int) __float_as_uint(P(P_W_TYPE))};
+    const float feedback = P(P_D_FEEDBACK), d_balance = P(P_D_BALANCE), frac = P(P_D_FRAC);
+    const uint32_t delay = __float_as_uint(P(P_D_DELAY));
+    const float r_balance = P(P_R_BALANCE), master = P(P_MASTER);
+    float f_low = svf[inst], f_band = svf[(size_t) I + inst], w_low = svf[2 * (size_t) I + inst], w_band = svf[3 * (size_t) I + inst];
+    float *ring = kHasRing ? ring_all + (size_t) inst * kRing : nullptr;
+    const bool far = kHasRing && delay >= (uint32_t) (2 * B + 2);
+    uint32_t wp = wp0;                    // write pointer at the frame being computed
+    uint32_t la = 0;                      // read index (a) of the next frame to be fetched
+    float prev_a = 0.f;                   // a of the previous frame == b of this one (far path)
+    if (kHasRing) {
+        la = wp0 + delay;
+        la = la >= (uint32_t) kRing ? la - kRing : la;
+        if (far) {
+            const uint32_t ib = la + 1 >= (uint32_t) kRing ? la + 1 - kRing : la + 1;
+            prev_a = ring[ib];
+        }
+    }
+    const float *src = in + inst;
+    float *dst = out + inst;
+
+    float x0[B], x1[B], a0[B], a1[B];
+    auto fetch = [&](float (&x)[B], float (&a)[B], uint32_t n0) {
+#pragma unroll
+        for (int j = 0; j < B; j++) {
+            if (n0 + j < frames) {
+                x[j] = src[(size_t) (n0 + j) * I];
+                if (far) {
+                    a[j] = ring[la];
+                    la = la == 0 ? kRing - 1 : la - 1;
+                }
+            }
+        }
+    };
+    auto run = [&](const float (&x)[B], const float (&a)[B], uint32_t n0) {
+#pragma unroll
+        for (int j = 0; j < B; j++) {
+            if (n0 + j >= frames) break;
+            float v = x[j];
+            if (kHasRing) {
+                float ra, rb;
+                if (far) {
+                    ra = a[j];
+                    rb = prev_a;
+                    prev_a = ra;
+                } else {  // DelayLine::Read straight from the ring (Fx.h:198-200)
+                    uint32_t ia = wp + delay;
+                    ia = ia >= (uint32_t) kRing ? ia - kRing : ia;
+                    uint32_t ib = ia + 1;
+                    ib = ib >= (uint32_t) kRing ? ib - kRing : ib;
+                    ra = ring[ia];
+                    rb = ring[ib];
+                }
+                const float rd = __fadd_rn(ra, __fmul_rn(__fsub_rn(rb, ra), frac));
+                ring[wp] = __fadd_rn(v, __fmul_rn(feedback, rd));
+                wp = wp == 0 ? kRing - 1 : wp - 1;
+                const float wet = svf_tick(rd, w_low, w_band, kw);
+                v = dry_wet(wet, v, d_balance);
+            }
+            if (KIND == OLB_FX_REVERB || KIND == OLB_FX_RACK) v = dry_wet(__fmul_rn(v, 0.8f), v, r_balance);
+            if (KIND == OLB_FX_FILTER || KIND == OLB_FX_RACK) v = svf_tick(v, f_low, f_band, kf);
+            if (KIND == OLB_FX_RACK) v = __fmul_rn(v, master);
+            dst[(size_t) (n0 + j) * I] = v;
+        }
+    };
+
+    fetch(x0, a0, 0);
+    for (uint32_t n0 = 0; n0 < frames; n0 += 2 * B) {
+        fetch(x1, a1, n0 + B);
+        run(x0, a0, n0);
+        fetch(x0, a0, n0 + 2 * B);
+        run(x1, a1, n0 + B);
     }
     svf[inst] = f_low;
     svf[(size_t) I + inst] = f_band;
@@ -252,13 +354,37 @@ OLB_API int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev, uint6
         int rc = fx_upload(h, st);
         if (rc) return rc;
     }
-    const unsigned grid = (h->I + 63) / 64;
     const uint32_t F = (uint32_t) frames;
-    switch (h->kind) {
-        case OLB_FX_FILTER: k_fx<OLB_FX_FILTER><<<grid, 64, 0, st>>>(in_dev, out_dev, F, h->I, h->d_par, h->d_svf, h->d_ring, h->wp); break;
-        case OLB_FX_DELAY: k_fx<OLB_FX_DELAY><<<grid, 64, 0, st>>>(in_dev, out_dev, F, h->I, h->d_par, h->d_svf, h->d_ring, h->wp); break;
-        case OLB_FX_REVERB: k_fx<OLB_FX_REVERB><<<grid, 64, 0, st>>>(in_dev, out_dev, F, h->I, h->d_par, h->d_svf, h->d_ring, h->wp); break;
-        default: k_fx<OLB_FX_RACK><<<grid, 64, 0, st>>>(in_dev, out_dev, F, h->I, h->d_par, h->d_svf, h->d_ring, h->wp); break;
+    // OLB_FX_KERNEL=simple selects the one-frame-at-a-time kernel; OLB_FX_LANES=32|16|8 overrides the active lanes per warp
+    // (default: the widest that still leaves >= 2 warps for each of the 592 SM sub-partitions, down to 8)
+    const int forced = [] {
+        const char *e = getenv("OLB_FX_KERNEL");
+        if (e && !strcmp(e, "simple")) return -1;
+        const char *l = getenv("OLB_FX_LANES");
+        return l ? atoi(l) : 0;
+    }();
+    if (forced < 0) {
+        const unsigned grid = (h->I + 63) / 64;
+        switch (h->kind) {
+            case OLB_FX_FILTER: k_fx<OLB_FX_FILTER><<<grid, 64, 0, st>>>(in_dev, out_dev, F, h->I, h->d_par, h->d_svf, h->d_ring, h->wp); break;
+            case OLB_FX_DELAY: k_fx<OLB_FX_DELAY><<<grid, 64, 0, st>>>(in_dev, out_dev, F, h->I, h->d_par, h->d_svf, h->d_ring, h->wp); break;
+            case OLB_FX_REVERB: k_fx<OLB_FX_REVERB><<<grid, 64, 0, st>>>(in_dev, out_dev, F, h->I, h->d_par, h->d_svf, h->d_ring, h->wp); break;
+            default: k_fx<OLB_FX_RACK><<<grid, 64, 0, st>>>(in_dev, out_dev, F, h->I, h->d_par, h->d_svf, h->d_ring, h->wp); break;
+        }
+    } else {
+        const int lanes = (forced == 32 || forced == 16 || forced == 8) ? forced : (h->I >= 1184u * 32 ? 32 : (h->I >= 1184u * 16 ? 16 : 8));
+        const unsigned warps = (h->I + lanes - 1) / lanes, grid = (warps + 1) / 2;
+#define OLB_FX_GO(KIND, LN) k_fx_pf<KIND, LN><<<grid, 64, 0, st>>>(in_dev, out_dev, F, h->I, h->d_par, h->d_svf, h->d_ring, h->wp)
+#define OLB_FX_LN(KIND) \
+    do { if (lanes == 32) OLB_FX_GO(KIND, 32); else if (lanes == 16) OLB_FX_GO(KIND, 16); else OLB_FX_GO(KIND, 8); } while (0)
+        switch (h->kind) {
+            case OLB_FX_FILTER: OLB_FX_LN(OLB_FX_FILTER); break;
+            case OLB_FX_DELAY: OLB_FX_LN(OLB_FX_DELAY); break;
+            case OLB_FX_REVERB: OLB_FX_LN(OLB_FX_REVERB); break;
+            default: OLB_FX_LN(OLB_FX_RACK); break;
+        }
+#undef OLB_FX_LN
+#undef OLB_FX_GO
     }
     OLB_LAUNCHED();
     if (fx_has_ring(h->kind)) h->wp = (uint32_t) ((h->wp + (uint64_t) kRing - frames % kRing) % kRing);

@@ -111,3 +111,17 @@ def test_impulse_response_properties():
     assert float(dl.abs().max()) > 0.0 and float(dr.abs().max()) > 0.0
     assert torch.equal(dl, dl[:, :1].expand(-1, I)) and torch.equal(dr, dr[:, :1].expand(-1, I))
     b.close()
+
+
+@pytest.mark.parametrize("env", [{"OLB_PLATE_KERNEL": "simple"}, {"OLB_PLATE_LANES": "32"}, {"OLB_PLATE_LANES": "16"}, {"OLB_PLATE_LANES": "8"}])
+def test_every_kernel_variant_is_bit_exact(orc, monkeypatch, env):
+    """The one-frame kernel and the pipelined kernel at 32 / 16 / 8 active lanes per warp compute the same bits."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    I, T = 77, 4500
+    x = orc.noise(6, 3, I, 0, T, 0.25)
+    plist = [[(i % 9) / 8.0, NAN, NAN, NAN, 0.5 + 0.4 * (i % 16) / 16, NAN, NAN] for i in range(I)]
+    l, r = run_bank(x, plist, chunks=[2047, 3, T - 2050])
+    for i in (0, 7, 8, 15, 16, 31, 32, 63, 64, 76):
+        wl, wr = orc.dattorro(x[:, i], plist[i])
+        assert np.array_equal(bits(l[:, i]), bits(wl)) and np.array_equal(bits(r[:, i]), bits(wr)), (env, i)
