@@ -144,6 +144,8 @@ int olb_fx_update_midi(olb_fx *h, uint32_t first, uint32_t count, uint8_t contro
 int olb_fx_update_hw(olb_fx *h, uint32_t first, uint32_t count, uint8_t control, const float *values_host, uint32_t stride);
 /* Block form of "for each frame: Process(frame_in, frame_out)"; in_dev == out_dev allowed. */
 int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream);
+/* Diagnostics: which kernel the last process call launched ("k_fx_tma", "k_fx_pf", "k_fx"). */
+const char *olb_fx_last_kernel(olb_fx *h);
 
 /* (a6) SynthVoice bank and (a8) Polyvoice mixdown -------------------------------------------------------
  * One bank = `voices` ol::synth::SynthVoice objects with the reference's default parts (PolyBLEP-saw

@@ -70,6 +70,7 @@ def lib():
         "olb_fx_update_midi": ([vp, u32, u32, C.c_uint8, C.c_uint8], i32),
         "olb_fx_update_hw": ([vp, u32, u32, C.c_uint8, _F, u32], i32),
         "olb_fx_process": ([vp, vp, vp, u64, vp], i32),
+        "olb_fx_last_kernel": ([vp], C.c_char_p),
         "olb_voice_create": ([i32, u32, f32, C.POINTER(vp)], i32),
         "olb_voice_destroy": ([vp], i32),
         "olb_voice_init": ([vp, f32], i32),

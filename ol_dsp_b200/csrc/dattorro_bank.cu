@@ -410,10 +410,10 @@ OLB_API int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *ou
         h->par_dirty = false;
     }
     // OLB_PLATE_KERNEL=simple selects the one-frame-at-a-time kernel; OLB_PLATE_LANES=32|16|8 overrides the active lanes per
-    // warp of the pipelined one (default: the widest that leaves >= 2 warps per SM sub-partition, down to 8)
+    // warp of the pipelined one (default 32: narrower warps measured no faster, profiles/r01_run14_units_lane_sweep.jsonl)
     const char *ek = getenv("OLB_PLATE_KERNEL"), *el = getenv("OLB_PLATE_LANES");
     const int forced = el ? atoi(el) : 0;
-    const int lanes = (forced == 32 || forced == 16 || forced == 8) ? forced : (h->I >= 1184u * 32 ? 32 : (h->I >= 1184u * 16 ? 16 : 8));
+    const int lanes = (forced == 32 || forced == 16 || forced == 8) ? forced : 32;
     if (ek && !strcmp(ek, "simple")) {
         k_dattorro<<<(h->I + 63) / 64, 64, 0, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I, h->d_slab, h->d_lp, h->d_par, h->geom, h->t);
     } else {

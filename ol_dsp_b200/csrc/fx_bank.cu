@@ -21,6 +21,7 @@
 
 #include "common.cuh"
 #include "host_params.h"
+#include "tmap.h"
 
 namespace olb {
 
@@ -33,25 +34,29 @@ struct SvfCoef {
     int type;
 };
 
-// daisysp::Svf::Process, two identical passes; returns the output FilterFx::Process selects (Fx.h:88-108)
+// daisysp::Svf::Process, two identical passes; returns the output FilterFx::Process selects (Fx.h:88-108).
+// Branch-free: the per-lane filter type picks its tap with selects (a switch here puts a divergent region in every
+// frame and keeps ptxas from overlapping consecutive frames); each output is 0.5 * pass1 + 0.5 * pass2 as in Svf.
+__device__ __forceinline__ float svf_pick(int type, float low, float band, float high, float notch) {
+    const float peak = __fsub_rn(low, high);
+    float s = low;
+    s = type == 1 ? band : s;
+    s = type == 2 ? high : s;
+    s = type == 3 ? notch : s;
+    s = type == 4 ? peak : s;
+    return s;
+}
 __device__ __forceinline__ float svf_tick(float in, float &low, float &band, const SvfCoef &k) {
     float notch = __fsub_rn(in, __fmul_rn(k.damp, band));
     low = __fadd_rn(low, __fmul_rn(k.freq, band));
     float high = __fsub_rn(notch, low);
     band = __fsub_rn(__fadd_rn(__fmul_rn(k.freq, high), band), __fmul_rn(__fmul_rn(__fmul_rn(k.drive, band), band), band));
-    float o_low = __fmul_rn(0.5f, low), o_high = __fmul_rn(0.5f, high), o_band = __fmul_rn(0.5f, band);
-    float o_peak = __fmul_rn(0.5f, __fsub_rn(low, high)), o_notch = __fmul_rn(0.5f, notch);
+    const float o1 = __fmul_rn(0.5f, svf_pick(k.type, low, band, high, notch));
     notch = __fsub_rn(in, __fmul_rn(k.damp, band));
     low = __fadd_rn(low, __fmul_rn(k.freq, band));
     high = __fsub_rn(notch, low);
     band = __fsub_rn(__fadd_rn(__fmul_rn(k.freq, high), band), __fmul_rn(__fmul_rn(__fmul_rn(k.drive, band), band), band));
-    switch (k.type) {
-        case 2: return __fadd_rn(o_high, __fmul_rn(0.5f, high));
-        case 1: return __fadd_rn(o_band, __fmul_rn(0.5f, band));
-        case 4: return __fadd_rn(o_peak, __fmul_rn(0.5f, __fsub_rn(low, high)));
-        case 3: return __fadd_rn(o_notch, __fmul_rn(0.5f, notch));
-        default: return __fadd_rn(o_low, __fmul_rn(0.5f, low));
-    }
+    return __fadd_rn(o1, __fmul_rn(0.5f, svf_pick(k.type, low, band, high, notch)));
 }
 
 __device__ __forceinline__ float dry_wet(float wet, float dry, float balance) {  // Fx.h:205-207, 297-299
@@ -100,24 +105,38 @@ __global__ void __launch_bounds__(64) k_fx(const float *in, float *out, uint32_t
 }
 
 // ------------------------------------------------------------------------------------------------
-// k_fx_pf: the same arithmetic with (1) register double buffering -- the inputs (and, for the delay kinds, the ring
-// reads) of frames n+B .. n+2B-1 are in flight while frames n .. n+B-1 run, so the HBM round trip is paid once per B
-// frames instead of once per frame (in and out may alias, so the compiler will not hoist the loads itself) -- and
-// (2) L active lanes per warp: a bank of a few thousand instances is only a few hundred full warps for 592 SM
-// sub-partitions and each warp is one long dependent chain, so narrower warps (L = 16 or 8; a warp row is then a
-// 64- or 32-byte segment, still whole sectors) give every sub-partition several chains to interleave.
-// Ring reads run ahead only when the delay exceeds the look-ahead (2B + 2 samples); shorter delays take the
-// direct path (read after the previous frame's write), lane by lane.
+// One frame of a unit, branch-free (ring kinds: `ra`, `rb` are the two DelayLine taps already read; the value to write
+// back into the ring is returned through `wr`).
+template <int KIND>
+__device__ __forceinline__ float fx_frame(float v, float ra, float rb, float &wr, float frac, float feedback, float d_balance,
+                                          float r_balance, float master, float &w_low, float &w_band, const SvfCoef &kw,
+                                          float &f_low, float &f_band, const SvfCoef &kf) {
+    if (KIND == OLB_FX_DELAY || KIND == OLB_FX_RACK) {
+        const float rd = __fadd_rn(ra, __fmul_rn(__fsub_rn(rb, ra), frac));  // DelayLine::Read (Fx.h:198)
+        wr = __fadd_rn(v, __fmul_rn(feedback, rd));                          // Write(in + feedback * read) (Fx.h:199-200)
+        const float wet = svf_tick(rd, w_low, w_band, kw);
+        v = dry_wet(wet, v, d_balance);
+    }
+    if (KIND == OLB_FX_REVERB || KIND == OLB_FX_RACK) v = dry_wet(__fmul_rn(v, 0.8f), v, r_balance);
+    if (KIND == OLB_FX_FILTER || KIND == OLB_FX_RACK) v = svf_tick(v, f_low, f_band, kf);
+    if (KIND == OLB_FX_RACK) v = __fmul_rn(v, master);
+    return v;
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_fx_pf: register double buffering -- the inputs (and, for the delay kinds, the ring reads) of frames n+B .. n+2B-1
+// are in flight while frames n .. n+B-1 run (in and out may alias, so the compiler will not hoist the loads itself).
+// Fallback of k_fx_tma for banks whose shape or alignment rules out a tensor map.  Ring reads run ahead only when the
+// delay exceeds the look-ahead (2B + 2 samples); shorter delays take the direct path, lane by lane.
 constexpr int kFxB = 8;
 
-template <int KIND, int L>
+template <int KIND>
 __global__ void __launch_bounds__(64) k_fx_pf(const float *in, float *out, uint32_t frames, uint32_t I,
                                               const float *__restrict__ par, float *svf, float *ring_all, uint32_t wp0) {
     constexpr bool kHasRing = (KIND == OLB_FX_DELAY || KIND == OLB_FX_RACK);
     constexpr int B = kFxB;
-    const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-    const uint32_t inst = warp * L + lane;
-    if (lane >= (uint32_t) L || inst >= I) return;
+    const uint32_t inst = blockIdx.x * blockDim.x + threadIdx.x;
+    if (inst >= I) return;
     auto P = [&](int p) { return par[(size_t) p * I + inst]; };
     const SvfCoef kf{P(P_F_FREQ), P(P_F_DAMP), P(P_F_DRIVE), (int) __float_as_uint(P(P_F_TYPE))};
     const SvfCoef kw{P(P_W_FREQ), P(P_W_DAMP), P(P_W_DRIVE), (int) __float_as_uint(P(P_W_TYPE))};
@@ -158,14 +177,13 @@ __global__ void __launch_bounds__(64) k_fx_pf(const float *in, float *out, uint3
 #pragma unroll
         for (int j = 0; j < B; j++) {
             if (n0 + j >= frames) break;
-            float v = x[j];
+            float ra = 0.f, rb = 0.f, wr = 0.f;
             if (kHasRing) {
-                float ra, rb;
                 if (far) {
                     ra = a[j];
                     rb = prev_a;
                     prev_a = ra;
-                } else {  // DelayLine::Read straight from the ring (Fx.h:198-200)
+                } else {  // DelayLine::Read straight from the ring
                     uint32_t ia = wp + delay;
                     ia = ia >= (uint32_t) kRing ? ia - kRing : ia;
                     uint32_t ib = ia + 1;
@@ -173,15 +191,12 @@ __global__ void __launch_bounds__(64) k_fx_pf(const float *in, float *out, uint3
                     ra = ring[ia];
                     rb = ring[ib];
                 }
-                const float rd = __fadd_rn(ra, __fmul_rn(__fsub_rn(rb, ra), frac));
-                ring[wp] = __fadd_rn(v, __fmul_rn(feedback, rd));
-                wp = wp == 0 ? kRing - 1 : wp - 1;
-                const float wet = svf_tick(rd, w_low, w_band, kw);
-                v = dry_wet(wet, v, d_balance);
             }
-            if (KIND == OLB_FX_REVERB || KIND == OLB_FX_RACK) v = dry_wet(__fmul_rn(v, 0.8f), v, r_balance);
-            if (KIND == OLB_FX_FILTER || KIND == OLB_FX_RACK) v = svf_tick(v, f_low, f_band, kf);
-            if (KIND == OLB_FX_RACK) v = __fmul_rn(v, master);
+            const float v = fx_frame<KIND>(x[j], ra, rb, wr, frac, feedback, d_balance, r_balance, master, w_low, w_band, kw, f_low, f_band, kf);
+            if (kHasRing) {
+                ring[wp] = wr;
+                wp = wp == 0 ? kRing - 1 : wp - 1;
+            }
             dst[(size_t) (n0 + j) * I] = v;
         }
     };
@@ -197,6 +212,187 @@ __global__ void __launch_bounds__(64) k_fx_pf(const float *in, float *out, uint3
     svf[(size_t) I + inst] = f_band;
     svf[2 * (size_t) I + inst] = w_low;
     svf[3 * (size_t) I + inst] = w_band;
+}
+
+// ------------------------------------------------------------------------------------------------
+// k_fx_tma: the streaming kernel.  Every instance is one lane running one dependent chain, so a bank's speed is
+// (instances x clock) / (cycles per frame of ONE warp) -- narrower warps buy nothing (measured: 32 / 16 / 8 active lanes
+// tie, profiles/r01_run15_fx_tma_sweep.jsonl); what counts is bytes in flight and a tight, branch-free frame.
+// k_fx_pf keeps only 8-16 frames x 4 B per instance in flight -- 8 192 instances are ~0.3 MB on the wire, and Little's
+// law caps the bank near 0.5 TB/s.  Here ONE warp is one CTA with its own TMA pipeline (the k_bq_tma pattern):
+// [TB frames][32 instances] boxes by cp.async.bulk.tensor.2d into a STAGES-deep shared-memory ring with mbarrier
+// complete_tx, filtered in place (each lane walks its own column), stored by TMA; (STAGES-1) x TB frames per instance
+// are in flight.  The delay kinds fetch the ring reads of the same future tile with 4-byte cp.async (LDGSTS) into a
+// second per-lane column, one commit group per tile.  Ring reads run ahead only when the delay exceeds the look-ahead
+// (STAGES x TB + 2 frames); a warp in which every lane qualifies runs the branch-free loop, any other warp the
+// general loop (direct reads for its short-delay lanes).
+__device__ __forceinline__ void fx_cp_async4(float *smem_dst, const float *gmem_src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
+__device__ __forceinline__ void fx_cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void fx_cp_async_wait() {
+    asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
+constexpr int kFxL = 32;  // instances per warp / CTA
+
+template <int KIND, int TB, int STAGES>
+__global__ void __launch_bounds__(32) k_fx_tma(const __grid_constant__ TensorMap tm_in, const __grid_constant__ TensorMap tm_out,
+                                               uint32_t frames, uint32_t I, const float *__restrict__ par, float *svf, float *ring_all,
+                                               uint32_t wp0) {
+    constexpr bool kHasRing = (KIND == OLB_FX_DELAY || KIND == OLB_FX_RACK);
+    constexpr int L = kFxL;
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const uint32_t lane = threadIdx.x, i0 = blockIdx.x * L, inst = i0 + lane;
+    const bool live = inst < I;
+    float *tiles = reinterpret_cast<float *>(smem_raw);                    // [STAGES][TB][L]
+    float *rtiles = tiles + (size_t) STAGES * TB * L;                      // [STAGES][TB][L], ring kinds only
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + (size_t) (kHasRing ? 2 : 1) * STAGES * TB * L * sizeof(float));
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; s++) mbar_init(&full[s], 1);
+        mbar_fence_init();
+    }
+    __syncwarp();
+    constexpr uint32_t kTileBytes = TB * L * sizeof(float);
+    const uint32_t ntiles = (frames + TB - 1) / TB;
+
+    const uint32_t ci = live ? inst : 0;  // idle lanes read instance 0's parameters and never write
+    auto P = [&](int p) { return par[(size_t) p * I + ci]; };
+    const SvfCoef kf{P(P_F_FREQ), P(P_F_DAMP), P(P_F_DRIVE), (int) __float_as_uint(P(P_F_TYPE))};
+    const SvfCoef kw{P(P_W_FREQ), P(P_W_DAMP), P(P_W_DRIVE), (int) __float_as_uint(P(P_W_TYPE))};
+    const float feedback = P(P_D_FEEDBACK), d_balance = P(P_D_BALANCE), frac = P(P_D_FRAC);
+    const uint32_t delay = __float_as_uint(P(P_D_DELAY));
+    const float r_balance = P(P_R_BALANCE), master = P(P_MASTER);
+    float f_low = svf[ci], f_band = svf[(size_t) I + ci], w_low = svf[2 * (size_t) I + ci], w_band = svf[3 * (size_t) I + ci];
+    float *ring = kHasRing ? ring_all + (size_t) ci * kRing : nullptr;
+    const bool far = kHasRing && live && delay >= (uint32_t) (STAGES * TB + 2);
+    const bool all_far = kHasRing && __all_sync(0xffffffffu, far || !live);
+    uint32_t wp = wp0, la = 0;  // wp is the same in every lane (the bank shares DelayLine::write_ptr_)
+    float prev_a = 0.f;
+    if (kHasRing) {
+        la = wp0 + delay;
+        la = la >= (uint32_t) kRing ? la - kRing : la;
+        if (far) {
+            const uint32_t ib = la + 1 >= (uint32_t) kRing ? la + 1 - kRing : la + 1;
+            prev_a = ring[ib];
+        }
+    }
+    auto fetch_ring = [&](uint32_t tile, uint32_t stage) {  // every lane; one commit group per tile, empty or not
+        if (kHasRing) {
+            if (far && tile < ntiles) {
+                float *dst = rtiles + (size_t) stage * TB * L + lane;
+                const uint32_t rows = min((uint32_t) TB, frames - tile * TB);
+                if (la >= rows) {  // no wrap inside this tile: plain backward walk
+                    const float *srcp = ring + la;
+#pragma unroll 8
+                    for (uint32_t j = 0; j < rows; j++) fx_cp_async4(dst + j * L, srcp - j);
+                    la -= rows;
+                } else {
+                    for (uint32_t j = 0; j < rows; j++) {
+                        fx_cp_async4(dst + j * L, ring + la);
+                        la = la == 0 ? kRing - 1 : la - 1;
+                    }
+                }
+            }
+            fx_cp_async_commit();
+        }
+    };
+
+    for (uint32_t j = 0; j < (uint32_t) (STAGES - 1); j++) {
+        if (lane == 0 && j < ntiles) {
+            mbar_arrive_expect_tx(&full[j], kTileBytes);
+            tma_load_2d(tiles + (size_t) j * TB * L, &tm_in, (int) i0, (int) (j * TB), &full[j]);
+        }
+        fetch_ring(j, j);
+    }
+
+    for (uint32_t i = 0; i < ntiles; i++) {
+        const uint32_t st = i % STAGES, ph = (i / STAGES) & 1;
+        if (kHasRing) fx_cp_async_wait<STAGES - 2>();
+        mbar_wait(&full[st], ph);
+        const uint32_t rows = min((uint32_t) TB, frames - i * TB);
+        float *col = tiles + (size_t) st * TB * L + lane;
+        const float *rcol = rtiles + (size_t) st * TB * L + lane;
+        if (!kHasRing) {
+            if (live) {
+#pragma unroll 4
+                for (uint32_t r = 0; r < rows; r++) {
+                    float wr;
+                    col[r * L] = fx_frame<KIND>(col[r * L], 0.f, 0.f, wr, frac, feedback, d_balance, r_balance, master, w_low, w_band, kw,
+                                                f_low, f_band, kf);
+                }
+            }
+        } else if (all_far) {
+            // the write pointer runs backwards and wraps at most once per tile: one or two straight segments
+            for (uint32_t r0 = 0; r0 < rows;) {
+                const uint32_t seg = min(rows - r0, wp + 1);
+                if (live) {
+                    float *wpp = ring + wp;
+                    float *c = col + r0 * L;
+                    const float *rc = rcol + r0 * L;
+#pragma unroll 4
+                    for (uint32_t r = 0; r < seg; r++) {
+                        const float ra = rc[r * L];
+                        float wr;
+                        c[r * L] = fx_frame<KIND>(c[r * L], ra, prev_a, wr, frac, feedback, d_balance, r_balance, master, w_low, w_band,
+                                                  kw, f_low, f_band, kf);
+                        prev_a = ra;
+                        *(wpp - r) = wr;
+                    }
+                }
+                r0 += seg;
+                wp = seg == wp + 1 ? (uint32_t) kRing - 1 : wp - seg;
+            }
+        } else {
+            if (live) {
+                uint32_t w = wp;
+                for (uint32_t r = 0; r < rows; r++) {
+                    float ra, rb, wr;
+                    if (far) {
+                        ra = rcol[r * L];
+                        rb = prev_a;
+                        prev_a = ra;
+                    } else {  // DelayLine::Read straight from the ring (Fx.h:198-200)
+                        uint32_t ia = w + delay;
+                        ia = ia >= (uint32_t) kRing ? ia - kRing : ia;
+                        uint32_t ib = ia + 1;
+                        ib = ib >= (uint32_t) kRing ? ib - kRing : ib;
+                        ra = ring[ia];
+                        rb = ring[ib];
+                    }
+                    col[r * L] = fx_frame<KIND>(col[r * L], ra, rb, wr, frac, feedback, d_balance, r_balance, master, w_low, w_band, kw,
+                                                f_low, f_band, kf);
+                    ring[w] = wr;
+                    w = w == 0 ? kRing - 1 : w - 1;
+                }
+            }
+            wp = (wp + (uint32_t) kRing - rows % kRing) % kRing;
+        }
+        fence_async_smem();
+        __syncwarp();
+        const uint32_t nxt = i + STAGES - 1;  // goes into the stage tile i-1 was stored from
+        if (lane == 0) {
+            tma_store_2d(&tm_out, (int) i0, (int) (i * TB), tiles + (size_t) st * TB * L);
+            tma_commit();
+            if (nxt < ntiles) {
+                tma_wait_read<1>();
+                const uint32_t ns = nxt % STAGES;
+                mbar_arrive_expect_tx(&full[ns], kTileBytes);
+                tma_load_2d(tiles + (size_t) ns * TB * L, &tm_in, (int) i0, (int) (nxt * TB), &full[ns]);
+            }
+        }
+        fetch_ring(nxt, nxt % STAGES);
+    }
+    if (lane == 0) tma_wait_all<0>();
+    if (kHasRing) fx_cp_async_wait<0>();
+    if (live) {
+        svf[inst] = f_low;
+        svf[(size_t) I + inst] = f_band;
+        svf[2 * (size_t) I + inst] = w_low;
+        svf[3 * (size_t) I + inst] = w_band;
+    }
 }
 
 }  // namespace olb
@@ -215,6 +411,7 @@ struct olb_fx {
     uint32_t wp = 0;  // DelayLine::write_ptr_, shared by the bank
     float *d_par = nullptr, *d_svf = nullptr, *d_ring = nullptr;
     std::vector<float> stage;
+    const char *last_kernel = "none";
 };
 
 static float bits_f(uint32_t u) {
@@ -263,6 +460,34 @@ static int fx_init(olb_fx *h, float sr) {
     h->wp = 0;
     h->dirty = true;
     return OLB_OK;
+}
+
+// k_fx_tma: one warp per CTA, [TB frames][32 instances] boxes, STAGES-deep ring (plus a second ring of the same shape for
+// the delay-line reads).  OLB_FX_TMA_CFG="<TB>x<STAGES>" selects another compiled shape (tuning aid).
+template <int KIND, int TB, int STAGES>
+static int fx_launch_tma_cfg(olb_fx *h, const float *in, float *out, uint32_t frames, cudaStream_t st) {
+    constexpr bool has_ring = (KIND == OLB_FX_DELAY || KIND == OLB_FX_RACK);
+    constexpr size_t smem = (size_t) (has_ring ? 2 : 1) * STAGES * TB * kFxL * sizeof(float) + (size_t) STAGES * sizeof(uint64_t);
+    TensorMap tin, tout;
+    int rc = make_tmap_frames(&tin, in, frames, h->I, kFxL, TB);
+    if (rc) return rc;
+    rc = make_tmap_frames(&tout, out, frames, h->I, kFxL, TB);
+    if (rc) return rc;
+    auto kern = k_fx_tma<KIND, TB, STAGES>;
+    OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    kern<<<(h->I + kFxL - 1) / kFxL, 32, smem, st>>>(tin, tout, frames, h->I, h->d_par, h->d_svf, h->d_ring, h->wp);
+    return OLB_OK;
+}
+
+template <int KIND>
+static int fx_launch_tma(olb_fx *h, const float *in, float *out, uint32_t frames, cudaStream_t st) {
+    int tb = 64, stages = 4;
+    if (const char *e = getenv("OLB_FX_TMA_CFG")) sscanf(e, "%dx%d", &tb, &stages);
+    if (tb == 32 && stages == 4) return fx_launch_tma_cfg<KIND, 32, 4>(h, in, out, frames, st);
+    if (tb == 64 && stages == 4) return fx_launch_tma_cfg<KIND, 64, 4>(h, in, out, frames, st);
+    if (tb == 64 && stages == 8) return fx_launch_tma_cfg<KIND, 64, 8>(h, in, out, frames, st);
+    if (tb == 32 && stages == 8) return fx_launch_tma_cfg<KIND, 32, 8>(h, in, out, frames, st);
+    return fx_launch_tma_cfg<KIND, 64, 4>(h, in, out, frames, st);
 }
 
 OLB_API int olb_fx_create(int device, int kind, uint32_t instances, float sample_rate, olb_fx **out) {
@@ -343,6 +568,8 @@ OLB_API int olb_fx_update_hw(olb_fx *h, uint32_t first, uint32_t count, uint8_t 
     return OLB_OK;
 }
 
+OLB_API const char *olb_fx_last_kernel(olb_fx *h) { return h ? h->last_kernel : "none"; }
+
 OLB_API int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream) {
     OLB_ARG(h, "olb_fx_process: NULL handle");
     if (frames == 0) return OLB_OK;
@@ -355,37 +582,39 @@ OLB_API int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev, uint6
         if (rc) return rc;
     }
     const uint32_t F = (uint32_t) frames;
-    // OLB_FX_KERNEL=simple selects the one-frame-at-a-time kernel; OLB_FX_LANES=32|16|8 overrides the active lanes per warp
-    // (default: the widest that still leaves >= 2 warps for each of the 592 SM sub-partitions, down to 8)
-    const int forced = [] {
-        const char *e = getenv("OLB_FX_KERNEL");
-        if (e && !strcmp(e, "simple")) return -1;
-        const char *l = getenv("OLB_FX_LANES");
-        return l ? atoi(l) : 0;
-    }();
-    if (forced < 0) {
-        const unsigned grid = (h->I + 63) / 64;
-        switch (h->kind) {
-            case OLB_FX_FILTER: k_fx<OLB_FX_FILTER><<<grid, 64, 0, st>>>(in_dev, out_dev, F, h->I, h->d_par, h->d_svf, h->d_ring, h->wp); break;
-            case OLB_FX_DELAY: k_fx<OLB_FX_DELAY><<<grid, 64, 0, st>>>(in_dev, out_dev, F, h->I, h->d_par, h->d_svf, h->d_ring, h->wp); break;
-            case OLB_FX_REVERB: k_fx<OLB_FX_REVERB><<<grid, 64, 0, st>>>(in_dev, out_dev, F, h->I, h->d_par, h->d_svf, h->d_ring, h->wp); break;
-            default: k_fx<OLB_FX_RACK><<<grid, 64, 0, st>>>(in_dev, out_dev, F, h->I, h->d_par, h->d_svf, h->d_ring, h->wp); break;
-        }
-    } else {
-        const int lanes = (forced == 32 || forced == 16 || forced == 8) ? forced : (h->I >= 1184u * 32 ? 32 : (h->I >= 1184u * 16 ? 16 : 8));
-        const unsigned warps = (h->I + lanes - 1) / lanes, grid = (warps + 1) / 2;
-#define OLB_FX_GO(KIND, LN) k_fx_pf<KIND, LN><<<grid, 64, 0, st>>>(in_dev, out_dev, F, h->I, h->d_par, h->d_svf, h->d_ring, h->wp)
-#define OLB_FX_LN(KIND) \
-    do { if (lanes == 32) OLB_FX_GO(KIND, 32); else if (lanes == 16) OLB_FX_GO(KIND, 16); else OLB_FX_GO(KIND, 8); } while (0)
-        switch (h->kind) {
-            case OLB_FX_FILTER: OLB_FX_LN(OLB_FX_FILTER); break;
-            case OLB_FX_DELAY: OLB_FX_LN(OLB_FX_DELAY); break;
-            case OLB_FX_REVERB: OLB_FX_LN(OLB_FX_REVERB); break;
-            default: OLB_FX_LN(OLB_FX_RACK); break;
-        }
-#undef OLB_FX_LN
-#undef OLB_FX_GO
+    // Kernel choice.  Default: k_fx_tma (needs instances % 4 == 0 and 16-byte aligned buffers for the tensor maps), else
+    // k_fx_pf.  Tuning / test aid: OLB_FX_KERNEL=simple|pf|tma.
+    const char *ek = getenv("OLB_FX_KERNEL");
+    const bool tma_ok = (h->I % 4 == 0) && (((uintptr_t) in_dev | (uintptr_t) out_dev) & 15) == 0;
+    const int which = (ek && !strcmp(ek, "simple")) ? 0 : ((ek && !strcmp(ek, "pf")) || !tma_ok ? 1 : 2);
+    const unsigned grid = (h->I + 63) / 64;
+#define OLB_FX_GO(KERNEL, KIND) KERNEL<KIND><<<grid, 64, 0, st>>>(in_dev, out_dev, F, h->I, h->d_par, h->d_svf, h->d_ring, h->wp)
+#define OLB_FX_KINDS(KERNEL)                                          \
+    switch (h->kind) {                                                \
+        case OLB_FX_FILTER: OLB_FX_GO(KERNEL, OLB_FX_FILTER); break;  \
+        case OLB_FX_DELAY: OLB_FX_GO(KERNEL, OLB_FX_DELAY); break;    \
+        case OLB_FX_REVERB: OLB_FX_GO(KERNEL, OLB_FX_REVERB); break;  \
+        default: OLB_FX_GO(KERNEL, OLB_FX_RACK); break;               \
     }
+    if (which == 0) {
+        OLB_FX_KINDS(k_fx);
+        h->last_kernel = "k_fx";
+    } else if (which == 1) {
+        OLB_FX_KINDS(k_fx_pf);
+        h->last_kernel = "k_fx_pf";
+    } else {
+        int rc = OLB_OK;
+        switch (h->kind) {
+            case OLB_FX_FILTER: rc = fx_launch_tma<OLB_FX_FILTER>(h, in_dev, out_dev, F, st); break;
+            case OLB_FX_DELAY: rc = fx_launch_tma<OLB_FX_DELAY>(h, in_dev, out_dev, F, st); break;
+            case OLB_FX_REVERB: rc = fx_launch_tma<OLB_FX_REVERB>(h, in_dev, out_dev, F, st); break;
+            default: rc = fx_launch_tma<OLB_FX_RACK>(h, in_dev, out_dev, F, st); break;
+        }
+        if (rc) return rc;
+        h->last_kernel = "k_fx_tma";
+    }
+#undef OLB_FX_KINDS
+#undef OLB_FX_GO
     OLB_LAUNCHED();
     if (fx_has_ring(h->kind)) h->wp = (uint32_t) ((h->wp + (uint64_t) kRing - frames % kRing) % kRing);
     return OLB_OK;

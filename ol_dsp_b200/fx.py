@@ -43,6 +43,9 @@ class FxBank:
     def ProcessDevice(self, in_ptr, out_ptr, frames, stream=0):
         check(self.L.olb_fx_process(self.h, C.c_void_p(in_ptr), C.c_void_p(out_ptr), frames, C.c_void_p(stream)))
 
+    def LastKernel(self):
+        return self.L.olb_fx_last_kernel(self.h).decode()
+
 
 def FilterFx(instances, **kw): return FxBank(FILTER, instances, **kw)
 def DelayFx(instances, **kw): return FxBank(DELAY, instances, **kw)

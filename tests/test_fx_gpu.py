@@ -122,21 +122,41 @@ def test_reference_fx_test_delay_replayed_on_the_bank(orc):
     b.close()
 
 
-@pytest.mark.parametrize("env", [{"OLB_FX_KERNEL": "simple"}, {"OLB_FX_LANES": "32"}, {"OLB_FX_LANES": "16"}, {"OLB_FX_LANES": "8"}])
+VARIANTS = [{"OLB_FX_KERNEL": "simple"}, {"OLB_FX_KERNEL": "pf"}, {"OLB_FX_KERNEL": "tma"}] + \
+    [{"OLB_FX_KERNEL": "tma", "OLB_FX_TMA_CFG": c} for c in ("32x4", "32x8", "64x8")]
+
+
+@pytest.mark.parametrize("env", VARIANTS, ids=lambda e: "-".join(e.values()))
 @pytest.mark.parametrize("kind", [fx.FILTER, fx.DELAY, fx.RACK])
 def test_every_kernel_variant_is_bit_exact(orc, monkeypatch, env, kind):
-    """The one-frame kernel and the double-buffered kernel at 32 / 16 / 8 active lanes per warp compute the same bits,
-    with delays on both sides of the look-ahead threshold (ring reads run ahead only past 2B + 2 samples), ragged
-    chunk sizes, and in-place processing."""
+    """The one-frame kernel, the register double-buffered kernel and the TMA-pipelined kernel (every compiled tile shape)
+    compute the same bits: delays on both sides of the look-ahead thresholds (ring reads run ahead only past 2B + 2 resp.
+    STAGES x TB + 2 frames; warps 0 and 1 mix short and long delays -> general loop, warp 2 is all long -> branch-free
+    loop), ragged chunk sizes, write-pointer wrap inside a tile, an instance count that is not a multiple of the warp."""
     for k, v in env.items():
         monkeypatch.setenv(k, v)
-    I, T = 77, 5000
+    I, T = 84, 50000  # > 48 000: the shared write pointer wraps
     x = orc.noise(12, 0, I, 0, T, 0.5)
-    times = [0.0, 1.0, 0.0001, 0.0002, 0.0003, 0.0004, 0.0005, 0.001]  # delays of 0 .. 48 samples, and the maximum
+    times = [0.0, 1.0, 0.0001, 0.0002, 0.0003, 0.0004, 0.0005, 0.001, 0.0053, 0.0054, 0.0055, 0.0106, 0.0107, 0.0213, 0.0214]  # 0 .. 1 027 samples, and the maximum
     evs = [[(0, loader.EV_HW_CC, 35, times[i] if i < len(times) else 0.05 + 0.9 * i / I), (0, loader.EV_MIDI_CC, 38, (i * 5) % 128)]
            for i in range(I)]
-    y = run_bank(kind, x, evs, extra_cuts=(1, 8, 17, 2000, 2001, 4097))
+    y = run_bank(kind, x, evs, extra_cuts=(1, 8, 17, 2000, 2001, 4097, 47990))
     name = NAMES[kind]
-    for i in (0, 1, 2, 3, 4, 5, 6, 7, 8, 15, 16, 31, 32, 76):
+    for i in list(range(16)) + [31, 32, 63, 64, 70, 83]:
         want = getattr(orc, name)(np.ascontiguousarray(x[:, i:i + 1]), 48000.0, evs[i])
         assert np.array_equal(bits(y[:, i]), bits(want[:, 0])), (env, name, i)
+
+
+def test_default_kernel_is_the_tma_pipeline():
+    b = FxBank(fx.RACK, 256)
+    x = torch.zeros((64, 256), dtype=torch.float32, device="cuda")
+    b.ProcessDevice(x.data_ptr(), x.data_ptr(), 64)
+    torch.cuda.synchronize()
+    assert b.LastKernel() == "k_fx_tma"
+    b.close()
+    b = FxBank(fx.RACK, 255)  # not a multiple of 4: no tensor map, falls to the register-pipelined kernel
+    x = torch.zeros((64, 255), dtype=torch.float32, device="cuda")
+    b.ProcessDevice(x.data_ptr(), x.data_ptr(), 64)
+    torch.cuda.synchronize()
+    assert b.LastKernel() == "k_fx_pf"
+    b.close()

@@ -45,6 +45,7 @@ def bench_dattorro(a):
             "roofline": {"bound": "hbm", "algorithmic_bytes_per_unit": 12, "achieved": 12 * units / dt / 1e9, "peak": peaks(), "unit": "GB/s",
                          "frac": 12 * units / dt / 1e9 / peaks(),
                          "ring_bytes_per_unit": 4 * (13 + 13 + 14), "ring_traffic_gbs": 160 * units / dt / 1e9},
+            "env": {k: v for k, v in os.environ.items() if k.startswith("OLB_")},
             "checksum": float(l.double().sum().item() + r.double().sum().item())}
     if a.cpu:
         import time
@@ -77,6 +78,7 @@ def bench_fx(a, kind, name, bytes_per_unit):
     line = {"unit": name, "metric": "instance-samples/s", "value": units / dt, "ms_per_step": dt * 1e3, "instances": I, "frames": F,
             "roofline": {"bound": "hbm", "algorithmic_bytes_per_unit": bytes_per_unit, "achieved": bytes_per_unit * units / dt / 1e9,
                          "peak": peaks(), "unit": "GB/s", "frac": bytes_per_unit * units / dt / 1e9 / peaks()},
+            "kernel": b.LastKernel(), "env": {k: v for k, v in os.environ.items() if k.startswith("OLB_")},
             "checksum": float(y.double().sum().item())}
     if a.cpu:
         import time
