@@ -207,6 +207,31 @@ int olb_dattorro_set_params(olb_dattorro *h, uint32_t first, uint32_t count, int
  * [frames][instances] (instance fastest). */
 int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *out_l_dev, float *out_r_dev, uint64_t frames, void *stream);
 
+/* (a9) Chorus bank ------------------------------------------------------------------------------------
+ * The reference has no chorus class; its chorus is the Max/RNBO graph modules/rnbo/patcher/mono-chorus.rnbopat
+ * (LFO-modulated delay~ -> lores~ -> dry/wet).  One bank = `instances` mono choruses with that patch's params
+ * (all 0..1, patch defaults): rate (scale -> 0.01..0.5 Hz), depth (@min 0.08; scale -> 1..12 ms), cutoff
+ * (scale -> 300..15 000 Hz), q, mix, phase (cycle~ phase offset).  Lifecycle and call shape follow the fxlib units:
+ * create = construct + Init(sample_rate); init clears the delay line, filter and LFO phase and keeps the params;
+ * process is the block form of "for each frame: Process(in, out)", in_dev == out_dev allowed.  Arithmetic is
+ * specified by oracle/olb_oracle.cpp (orc_chorus_*): parity unpinned, bit-exact against that restatement. */
+#define OLB_CHORUS_RATE 0
+#define OLB_CHORUS_DEPTH 1
+#define OLB_CHORUS_CUTOFF 2
+#define OLB_CHORUS_Q 3
+#define OLB_CHORUS_MIX 4
+#define OLB_CHORUS_PHASE 5
+
+typedef struct olb_chorus olb_chorus;
+
+int olb_chorus_create(int device, uint32_t instances, float sample_rate, olb_chorus **out);
+int olb_chorus_destroy(olb_chorus *h);
+int olb_chorus_init(olb_chorus *h, float sample_rate);
+int olb_chorus_set_param(olb_chorus *h, uint32_t first, uint32_t count, int param, float value);
+int olb_chorus_set_params(olb_chorus *h, uint32_t first, uint32_t count, int param, const float *values_host, uint32_t stride);
+int olb_chorus_process(olb_chorus *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream);
+const char *olb_chorus_last_kernel(olb_chorus *h);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,376 @@
+// chorus_bank.cu -- (a9) bank of mono choruses.
+//
+// Reference: NO C++ exists.  The only statement of the chorus is the Max/RNBO box graph
+// modules/rnbo/patcher/mono-chorus.rnbopat:  in~ -> delay~ (@maxsize samplerate*2; delay = cycle~(rate') * d + d,
+// "add the depth to keep the delay value > 0") -> lores~ (cutoff', q) -> *~ mix, +~ in~ * (1 - mix) -> out~, with
+// rate' = scale(rate 0..1 -> 0.01..0.5 Hz), d = mstosamps(scale(depth 0.08..1 -> 1..12 ms)),
+// cutoff' = scale(cutoff 0..1 -> 300..15 000 Hz), cycle~ phase offset `phase`; parameter defaults rate .2, depth .5,
+// cutoff .3, q .5, mix .5, phase 1.  Max's object internals are not in the tree: the arithmetic is specified by
+// oracle/olb_oracle.cpp (orc_chorus_*), PARITY UNPINNED, and this kernel is bit-exact against that restatement.
+// The gen~ pitch shifter in front of the delay (pitchshift.gendsp) is not built.
+//
+// Layout
+//   audio   [frames][instances] fp32 in HBM
+//   ring    per CTA (= one warp = 32 instances) a block [R][32] fp32, R = ceil(24 ms * sr) + 4 + 8 spare (1 164 at 48 kHz, 149 KB):
+//           it lives in SHARED MEMORY for the whole launch (bulk-copied in at the start and out at the end), lane-fastest,
+//           so the 32 lanes' reads at 32 different delays never collide on a bank.  All instances tick together and
+//           share the write index.
+//   state   [3][instances]: LFO phase, lores~ y1, y2        par [7][instances]: inc d offset scale a1 a2 mix
+// One warp per CTA with its own TMA tile pipeline for the audio (the k_fx_tma pattern); ~183 KB of shared memory per
+// CTA, one CTA per SM.
+#include <math.h>
+#include <stdlib.h>
+
+#include <vector>
+
+#include "common.cuh"
+#include "tmap.h"
+
+namespace olb {
+
+constexpr int kChL = 32;      // instances per warp / CTA
+constexpr int kChTab = 512;   // cycle~ table points (+1 guard)
+enum { CP_INC, CP_D, CP_OFFSET, CP_SCALE, CP_A1, CP_A2, CP_MIX, CP_COUNT };
+
+__device__ __forceinline__ void bulk_load_1d(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void bulk_store_1d(void *gmem_dst, const void *smem_src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst), "r"(smem_u32(smem_src)), "r"(bytes)
+                 : "memory");
+}
+
+struct ChorusLane {
+    float inc, d, offset, scale, a1, a2, mix;
+    float phase, y1, y2;
+};
+
+constexpr int kChB = 8;  // frames per batch; the ring carries kChB spare slots so a batch may write ahead of its reads
+
+// A batch of up to kChB frames of one instance, in three sweeps so that nothing but the two-op lores~ recurrence is
+// serial: (1) LFO phase -> table lookup -> delay for every frame, (2) all delay~ writes, then all reads (the ring has
+// kChB slots more than the longest delay reaches, so a frame's taps are never overwritten by the writes of the batch's
+// later frames; a tap at delay k < r of frame r reads what frame r-k just wrote, as in the frame-by-frame order),
+// (3) interpolate, filter, mix.  `wp` is the warp-uniform write index of the batch's first frame, wp + n <= R.
+template <int N>
+__device__ __forceinline__ void chorus_batch(float *col, ChorusLane &c, float *ring_col, uint32_t wp, uint32_t R, float dmax, const float *tab,
+                                             uint32_t n) {
+    uint32_t k[N];
+    float fr[N], x[N], a[N], b[N];
+#pragma unroll
+    for (int r = 0; r < N; r++) {
+        if ((uint32_t) r < n) {
+            float p = __fadd_rn(c.phase, c.offset);
+            p = p >= 1.0f ? __fsub_rn(p, 1.0f) : p;
+            const float idx = __fmul_rn(p, 512.0f);
+            int i0 = __float2int_rz(idx);
+            i0 = i0 > kChTab - 1 ? kChTab - 1 : i0;
+            const float f = __fsub_rn(idx, __int2float_rn(i0));
+            const float c0 = tab[i0], c1 = tab[i0 + 1];
+            const float lfo = __fadd_rn(c0, __fmul_rn(__fsub_rn(c1, c0), f));
+            float dt = __fadd_rn(__fmul_rn(lfo, c.d), c.d);
+            dt = dt < 0.0f ? 0.0f : dt;
+            dt = dt > dmax ? dmax : dt;
+            k[r] = (uint32_t) __float2int_rz(dt);
+            fr[r] = __fsub_rn(dt, __uint2float_rn(k[r]));
+            const float ph = __fadd_rn(c.phase, c.inc);
+            c.phase = ph >= 1.0f ? __fsub_rn(ph, 1.0f) : ph;
+            x[r] = col[r * kChL];
+            ring_col[(size_t) (wp + r) * kChL] = x[r];  // delay~ writes, then reads dt samples back
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < N; r++) {
+        if ((uint32_t) r < n) {
+            const uint32_t w = wp + r;
+            const uint32_t ia = w >= k[r] ? w - k[r] : w + R - k[r];
+            const uint32_t ib = ia >= 1 ? ia - 1 : R - 1;
+            a[r] = ring_col[(size_t) ia * kChL];
+            b[r] = ring_col[(size_t) ib * kChL];
+        }
+    }
+#pragma unroll
+    for (int r = 0; r < N; r++) {
+        if ((uint32_t) r < n) {
+            const float wet0 = __fadd_rn(a[r], __fmul_rn(__fsub_rn(b[r], a[r]), fr[r]));
+            float t = __fmul_rn(c.scale, wet0);
+            t = __fsub_rn(t, __fmul_rn(c.a1, c.y1));
+            t = __fsub_rn(t, __fmul_rn(c.a2, c.y2));
+            c.y2 = c.y1;
+            c.y1 = t;
+            col[r * kChL] = __fadd_rn(__fmul_rn(t, c.mix), __fmul_rn(x[r], __fsub_rn(1.0f, c.mix)));
+        }
+    }
+}
+
+template <int TB, int STAGES, bool TMA>
+__global__ void __launch_bounds__(32) k_chorus(const __grid_constant__ TensorMap tm_in, const __grid_constant__ TensorMap tm_out,
+                                               const float *in, float *out, uint32_t frames, uint32_t I, uint32_t R,
+                                               const float *__restrict__ par, float *state, float *ring_all,
+                                               const float *__restrict__ tab_g, uint32_t w0, float dmax) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    constexpr int L = kChL;
+    const uint32_t lane = threadIdx.x, i0 = blockIdx.x * L, inst = i0 + lane;
+    const bool live = inst < I;
+    float *tiles = reinterpret_cast<float *>(smem_raw);          // [STAGES][TB][L]
+    float *ring = tiles + (size_t) STAGES * TB * L;              // [R][L]
+    float *tab = ring + (size_t) R * L;                          // [513] (+3 pad)
+    uint64_t *full = reinterpret_cast<uint64_t *>(tab + kChTab + 4);  // [STAGES] tile barriers, [STAGES] = ring barrier
+    const uint32_t ring_bytes = R * L * (uint32_t) sizeof(float);
+    float *ring_g = ring_all + (size_t) blockIdx.x * R * L;
+    if (lane == 0) {
+#pragma unroll
+        for (int s = 0; s <= STAGES; s++) mbar_init(&full[s], 1);
+        mbar_fence_init();
+    }
+    __syncwarp();
+    constexpr uint32_t kTileBytes = TB * L * sizeof(float);
+    const uint32_t ntiles = (frames + TB - 1) / TB;
+    if (lane == 0) {
+        mbar_arrive_expect_tx(&full[STAGES], ring_bytes);
+        bulk_load_1d(ring, ring_g, ring_bytes, &full[STAGES]);
+        if (TMA) {
+            for (uint32_t j = 0; j < (uint32_t) (STAGES - 1) && j < ntiles; j++) {
+                mbar_arrive_expect_tx(&full[j], kTileBytes);
+                tma_load_2d(tiles + (size_t) j * TB * L, &tm_in, (int) i0, (int) (j * TB), &full[j]);
+            }
+        }
+    }
+    for (uint32_t j = lane; j <= (uint32_t) kChTab; j += 32) tab[j] = tab_g[j];
+    const uint32_t ci = live ? inst : 0;
+    ChorusLane c;
+    c.inc = par[(size_t) CP_INC * I + ci]; c.d = par[(size_t) CP_D * I + ci]; c.offset = par[(size_t) CP_OFFSET * I + ci];
+    c.scale = par[(size_t) CP_SCALE * I + ci]; c.a1 = par[(size_t) CP_A1 * I + ci]; c.a2 = par[(size_t) CP_A2 * I + ci];
+    c.mix = par[(size_t) CP_MIX * I + ci];
+    c.phase = state[ci]; c.y1 = state[(size_t) I + ci]; c.y2 = state[2 * (size_t) I + ci];
+    float *ring_col = ring + lane;
+    uint32_t wp = w0;
+    __syncwarp();
+    mbar_wait(&full[STAGES], 0);
+
+    for (uint32_t i = 0; i < ntiles; i++) {
+        const uint32_t st = TMA ? i % STAGES : 0, ph = (i / STAGES) & 1;
+        const uint32_t rows = min((uint32_t) TB, frames - i * TB);
+        float *col = tiles + (size_t) st * TB * L + lane;
+        if (TMA) {
+            mbar_wait(&full[st], ph);
+        } else if (live) {
+            for (uint32_t r = 0; r < rows; r++) col[r * L] = in[(size_t) (i * TB + r) * I + inst];
+        }
+        // the write index wraps at most once per tile: one or two straight segments
+        for (uint32_t r0 = 0; r0 < rows;) {
+            const uint32_t seg = min(rows - r0, R - wp);
+            if (live) {
+                uint32_t r = 0;
+                for (; r + kChB <= seg; r += kChB) chorus_batch<kChB>(col + (r0 + r) * L, c, ring_col, wp + r, R, dmax, tab, kChB);
+                if (r < seg) chorus_batch<kChB>(col + (r0 + r) * L, c, ring_col, wp + r, R, dmax, tab, seg - r);
+            }
+            r0 += seg;
+            wp = wp + seg == R ? 0 : wp + seg;
+        }
+        if (TMA) {
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+                tma_store_2d(&tm_out, (int) i0, (int) (i * TB), tiles + (size_t) st * TB * L);
+                tma_commit();
+                const uint32_t nxt = i + STAGES - 1;
+                if (nxt < ntiles) {
+                    tma_wait_read<1>();
+                    const uint32_t ns = nxt % STAGES;
+                    mbar_arrive_expect_tx(&full[ns], kTileBytes);
+                    tma_load_2d(tiles + (size_t) ns * TB * L, &tm_in, (int) i0, (int) (nxt * TB), &full[ns]);
+                }
+            }
+        } else if (live) {
+            for (uint32_t r = 0; r < rows; r++) out[(size_t) (i * TB + r) * I + inst] = col[r * L];
+        }
+    }
+    fence_async_smem();
+    __syncwarp();
+    if (lane == 0) {
+        bulk_store_1d(ring_g, ring, ring_bytes);
+        tma_commit();
+        tma_wait_all<0>();
+    }
+    if (live) {
+        state[inst] = c.phase;
+        state[(size_t) I + inst] = c.y1;
+        state[2 * (size_t) I + inst] = c.y2;
+    }
+}
+
+}  // namespace olb
+
+using namespace olb;
+
+// ================================================================================================
+// Host side.  The RNBO params (0..1 domain) are kept per instance; the derived device table is rebuilt when a setter ran
+// (setters take effect at the next process call).
+struct olb_chorus {
+    int device = 0;
+    uint32_t I = 0, R = 0, w = 0, ctas = 0;
+    float sample_rate = 48000.f;
+    std::vector<float> raw;  // [6][I]: rate depth cutoff q mix phase
+    std::vector<float> stage;
+    bool dirty = true;
+    float *d_par = nullptr, *d_state = nullptr, *d_ring = nullptr, *d_tab = nullptr;
+    const char *last_kernel = "none";
+};
+
+constexpr int kChTB = 64, kChStages = 4;
+static size_t chorus_smem(uint32_t R) {
+    return (size_t) kChStages * kChTB * kChL * sizeof(float) + (size_t) R * kChL * sizeof(float) + (kChTab + 4) * sizeof(float) +
+           (kChStages + 1) * sizeof(uint64_t);
+}
+// the specification's ring length (orc_chorus_ring_len: it only enters the arithmetic through the clamp dt <= len - 2) ...
+static uint32_t chorus_spec_len(float sr) { return (uint32_t) ceil(2.0 * 12.0 * (double) sr / 1000.0) + 4u; }
+// ... and the bank's own: kChB spare slots so that a batch may write ahead of its reads
+static uint32_t chorus_ring_len(float sr) { return chorus_spec_len(sr) + (uint32_t) kChB; }
+
+static void chorus_derive(const olb_chorus *h, uint32_t i, float *out /* stride I */) {
+    const size_t I = h->I;
+    const double sr = h->sample_rate;
+    const double rate = h->raw[0 * I + i], depth = h->raw[1 * I + i] < 0.08f ? 0.08 : (double) h->raw[1 * I + i];
+    const double cutoff = h->raw[2 * I + i], q = h->raw[3 * I + i], phase = h->raw[5 * I + i];
+    const double rate_hz = 0.01 + (0.5 - 0.01) * rate;         // [scale 0 1 0.01 0.5]
+    const double depth_ms = 1.0 + (12.0 - 1.0) * depth;        // [scale 0 1 1 12 1]
+    const double fc = 300.0 + (15000.0 - 300.0) * cutoff;      // [scale 0 1 300 15000 1]
+    const double resterm = exp(q * 0.125) * 0.882497, fqterm = cos(fc * 2.0 * 3.14159265358979323846 / sr);
+    const double a1 = -2.0 * resterm * fqterm, a2 = resterm * resterm;
+    out[CP_INC * I + i] = (float) (rate_hz / sr);
+    out[CP_D * I + i] = (float) (depth_ms * sr / 1000.0);      // [mstosamps]
+    out[CP_OFFSET * I + i] = (float) (phase - floor(phase));
+    out[CP_SCALE * I + i] = (float) (1.0 + a1 + a2);
+    out[CP_A1 * I + i] = (float) a1;
+    out[CP_A2 * I + i] = (float) a2;
+    out[CP_MIX * I + i] = h->raw[4 * I + i];
+}
+
+static void chorus_free(olb_chorus *h) {
+    cudaFree(h->d_par); cudaFree(h->d_state); cudaFree(h->d_ring); cudaFree(h->d_tab);
+    delete h;
+}
+
+static int chorus_reset(olb_chorus *h, float sr) {
+    const uint32_t R = chorus_ring_len(sr);
+    OLB_ARG(sr > 0.f && chorus_smem(R) <= 227u * 1024u, "olb_chorus: sample rate %g needs a %u-frame ring that does not fit in shared memory", sr, R);
+    if (R != h->R || !h->d_ring) {
+        cudaFree(h->d_ring);
+        h->d_ring = nullptr;
+        OLB_CUDA(cudaMalloc(&h->d_ring, (size_t) h->ctas * R * kChL * sizeof(float)));
+        h->R = R;
+    }
+    h->sample_rate = sr;
+    OLB_CUDA(cudaMemset(h->d_ring, 0, (size_t) h->ctas * R * kChL * sizeof(float)));
+    OLB_CUDA(cudaMemset(h->d_state, 0, (size_t) 3 * h->I * sizeof(float)));
+    h->w = 0;
+    h->dirty = true;
+    return OLB_OK;
+}
+
+OLB_API int olb_chorus_create(int device, uint32_t instances, float sample_rate, olb_chorus **out) {
+    OLB_ARG(out, "olb_chorus_create: out is NULL");
+    *out = nullptr;
+    OLB_ARG(instances > 0, "olb_chorus_create: instances must be > 0");
+    int rc = require_sm100(device);
+    if (rc) return rc;
+    DeviceGuard g(device);
+    olb_chorus *h = new olb_chorus();
+    h->device = device;
+    h->I = instances;
+    h->ctas = (instances + kChL - 1) / kChL;
+    h->raw.resize((size_t) 6 * instances);
+    const float defaults[6] = {0.2f, 0.5f, 0.3f, 0.5f, 0.5f, 1.0f};  // param defaults of mono-chorus.rnbopat
+    for (int p = 0; p < 6; p++)
+        for (uint32_t i = 0; i < instances; i++) h->raw[(size_t) p * instances + i] = defaults[p];
+    float tab[kChTab + 1];
+    for (int i = 0; i <= kChTab; i++) tab[i] = (float) cos(2.0 * 3.14159265358979323846 * (double) i / (double) kChTab);
+    cudaError_t e = cudaMalloc(&h->d_par, (size_t) CP_COUNT * instances * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_state, (size_t) 3 * instances * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_tab, sizeof(tab));
+    if (e == cudaSuccess) e = cudaMemcpy(h->d_tab, tab, sizeof(tab), cudaMemcpyHostToDevice);
+    if (e != cudaSuccess) {
+        chorus_free(h);
+        return fail_cuda(e, "allocating chorus bank", __FILE__, __LINE__);
+    }
+    rc = chorus_reset(h, sample_rate);
+    if (rc) {
+        chorus_free(h);
+        return rc;
+    }
+    *out = h;
+    return OLB_OK;
+}
+
+OLB_API int olb_chorus_destroy(olb_chorus *h) {
+    if (!h) return OLB_OK;
+    DeviceGuard g(h->device);
+    chorus_free(h);
+    return OLB_OK;
+}
+
+OLB_API int olb_chorus_init(olb_chorus *h, float sample_rate) {
+    OLB_ARG(h, "olb_chorus_init: NULL handle");
+    DeviceGuard g(h->device);
+    return chorus_reset(h, sample_rate);
+}
+
+OLB_API int olb_chorus_set_params(olb_chorus *h, uint32_t first, uint32_t count, int param, const float *values_host, uint32_t stride) {
+    OLB_ARG(h && values_host, "olb_chorus_set_params: NULL argument");
+    OLB_ARG((uint64_t) first + count <= h->I, "olb_chorus_set_params: range [%u, %u) exceeds %u instances", first, first + count, h->I);
+    OLB_ARG(param >= OLB_CHORUS_RATE && param <= OLB_CHORUS_PHASE, "olb_chorus_set_params: unknown parameter %d", param);
+    for (uint32_t i = 0; i < count; i++) {
+        float v = values_host[(size_t) i * stride];
+        v = v < 0.f ? 0.f : (v > 1.f ? 1.f : v);  // RNBO params clip to @min / @max
+        h->raw[(size_t) param * h->I + first + i] = v;
+    }
+    h->dirty = true;
+    return OLB_OK;
+}
+
+OLB_API int olb_chorus_set_param(olb_chorus *h, uint32_t first, uint32_t count, int param, float value) {
+    return olb_chorus_set_params(h, first, count, param, &value, 0);
+}
+
+OLB_API const char *olb_chorus_last_kernel(olb_chorus *h) { return h ? h->last_kernel : "none"; }
+
+OLB_API int olb_chorus_process(olb_chorus *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream) {
+    OLB_ARG(h, "olb_chorus_process: NULL handle");
+    if (frames == 0) return OLB_OK;
+    OLB_ARG(in_dev && out_dev, "olb_chorus_process: NULL buffer");
+    OLB_ARG(frames < (1ull << 32), "olb_chorus_process: at most 2^32-1 frames per call");
+    DeviceGuard g(h->device);
+    cudaStream_t st = (cudaStream_t) stream;
+    if (h->dirty) {
+        h->stage.resize((size_t) CP_COUNT * h->I);
+        for (uint32_t i = 0; i < h->I; i++) chorus_derive(h, i, h->stage.data());
+        OLB_CUDA(cudaMemcpyAsync(h->d_par, h->stage.data(), h->stage.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+        OLB_CUDA(cudaStreamSynchronize(st));
+        h->dirty = false;
+    }
+    const size_t smem = chorus_smem(h->R);
+    const char *ek = getenv("OLB_CHORUS_KERNEL");  // "direct" forces the plain-load variant (test aid)
+    const bool tma = !(ek && !strcmp(ek, "direct")) && (h->I % 4 == 0) && (((uintptr_t) in_dev | (uintptr_t) out_dev) & 15) == 0;
+    TensorMap tin{}, tout{};
+    if (tma) {
+        int rc = make_tmap_frames(&tin, in_dev, frames, h->I, kChL, kChTB);
+        if (rc) return rc;
+        rc = make_tmap_frames(&tout, out_dev, frames, h->I, kChL, kChTB);
+        if (rc) return rc;
+        auto kern = k_chorus<kChTB, kChStages, true>;
+        OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        kern<<<h->ctas, 32, smem, st>>>(tin, tout, in_dev, out_dev, (uint32_t) frames, h->I, h->R, h->d_par, h->d_state, h->d_ring, h->d_tab, h->w, (float) (chorus_spec_len(h->sample_rate) - 2));
+        h->last_kernel = "k_chorus_tma";
+    } else {
+        auto kern = k_chorus<kChTB, kChStages, false>;
+        OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        kern<<<h->ctas, 32, smem, st>>>(tin, tout, in_dev, out_dev, (uint32_t) frames, h->I, h->R, h->d_par, h->d_state, h->d_ring, h->d_tab, h->w, (float) (chorus_spec_len(h->sample_rate) - 2));
+        h->last_kernel = "k_chorus_direct";
+    }
+    OLB_LAUNCHED();
+    h->w = (uint32_t) ((h->w + frames) % h->R);
+    return OLB_OK;
+}

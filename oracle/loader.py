@@ -122,6 +122,30 @@ class Oracle(_Fx):
         lib.orc_dattorro_slab_floats.restype = C.c_uint32
         lib.orc_biquad_bench.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_void_p, _F, C.c_uint64, C.c_uint32, C.c_int, C.POINTER(C.c_double)]
         lib.orc_biquad_bench.restype = C.c_double
+        lib.orc_chorus_params.argtypes = [C.c_float] * 7 + [_F]
+        lib.orc_chorus_params.restype = None
+        lib.orc_chorus_ring_len.argtypes = [C.c_float]
+        lib.orc_chorus_ring_len.restype = C.c_uint32
+        lib.orc_chorus_run.argtypes = [_F, C.c_uint32, _F, _F, C.POINTER(C.c_uint32), _F, _F, C.c_uint64, C.c_uint64]
+        lib.orc_chorus_run.restype = None
+
+    def chorus(self, x, sr=48000.0, rate=0.2, depth=0.5, cutoff=0.3, q=0.5, mix=0.5, phase=1.0, changes=()):
+        """(a9) one chorus instance over x[frames] (defaults = the RNBO patch's param defaults).  changes: list of
+        (frame, dict of params) applied before that frame (state and ring kept)."""
+        x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1)
+        y = np.empty_like(x)
+        cur = dict(rate=rate, depth=depth, cutoff=cutoff, q=q, mix=mix, phase=phase)
+        par = np.zeros(7, np.float32)
+        n = int(self.lib.orc_chorus_ring_len(sr))
+        ring, state, w = np.zeros(n, np.float32), np.zeros(3, np.float32), C.c_uint32(0)
+        cuts = sorted({0, len(x)} | {f for f, _ in changes})
+        for a, z in zip(cuts[:-1], cuts[1:]):
+            for f, d in changes:
+                if f == a:
+                    cur.update(d)
+            self.lib.orc_chorus_params(sr, cur["rate"], cur["depth"], cur["cutoff"], cur["q"], cur["mix"], cur["phase"], _fp(par))
+            self.lib.orc_chorus_run(_fp(par), n, _fp(state), _fp(ring), C.byref(w), _fp(x[a:]), _fp(y[a:]), z - a, 1)
+        return y
 
     def noise(self, seed, first_channel, channels, first_frame, frames, scale=1.0, planar=False):
         """Philox white noise in [-1,1): [frames][channels] (or [channels][frames] when planar)."""

@@ -988,3 +988,82 @@ ORC_API double orc_biquad_bench(int mode, uint32_t channels, uint32_t sections, 
     if (checksum) { double s = 0; for (double v : sums) s += v; *checksum = s; }
     return dt;
 }
+
+// ================================================================================================
+// (a9) Chorus.  The reference holds NO chorus code: the only statement of it is the Max/RNBO box graph
+// modules/rnbo/patcher/mono-chorus.rnbopat (boxes obj-30 rate, obj-5 scale 0 1 0.01 0.5, obj-32 depth @min 0.08,
+// obj-7 scale 0 1 1 12 1, obj-64 mstosamps, obj-6 cycle~, obj-38 *~, obj-36 +~ "add the depth to keep the delay
+// value > 0", obj-24 delay~ @maxsize samplerate*2, obj-33 cutoff, obj-20 scale 0 1 300 15000 1, obj-34 q, obj-21 lores~,
+// obj-13 mix, obj-25/29/28/27 wet*mix + dry*(1-mix)).  The Max objects' internals are not in the tree, so THIS FILE IS THE
+// SPECIFICATION of the arithmetic (PARITY UNPINNED):
+//   cycle~   512-point cosine table (+ guard point), linear interpolation, phase offset added to the running phase
+//   delay~   write, then read `dt` samples back with linear interpolation between the two neighbours
+//   lores~   y = scale*x - a1*y1 - a2*y2 with resterm = exp(q*0.125)*0.882497, fqterm = cos(2*pi*fc/sr),
+//            a1 = -2*resterm*fqterm, a2 = resterm^2, scale = 1 + a1 + a2   (the published lores~ recurrence)
+// Setter-time maths in double, rounded to float once; per-frame maths in float, one rounding per operation.
+struct OrcChorusParams {
+    float inc, d, offset, scale, a1, a2, mix;
+};
+ORC_API void orc_chorus_params(float sr, float rate, float depth, float cutoff, float q, float mix, float phase, float *out7) {
+    const double rate_hz = 0.01 + (0.5 - 0.01) * (double) rate;                        // scale 0 1 0.01 0.5
+    const double dep = depth < 0.08f ? 0.08 : (double) depth;                          // param depth @min 0.08
+    const double depth_ms = 1.0 + (12.0 - 1.0) * dep;                                  // scale 0 1 1 12 1
+    const double fc = 300.0 + (15000.0 - 300.0) * (double) cutoff;                     // scale 0 1 300 15000 1
+    const double resterm = exp((double) q * 0.125) * 0.882497;
+    const double fqterm = cos(fc * 2.0 * 3.14159265358979323846 / (double) sr);
+    const double a1 = -2.0 * resterm * fqterm, a2 = resterm * resterm;
+    out7[0] = (float) (rate_hz / (double) sr);
+    out7[1] = (float) (depth_ms * (double) sr / 1000.0);                               // mstosamps
+    out7[2] = (float) ((double) phase - floor((double) phase));                        // cycle~ phase offset, wrapped to [0,1)
+    out7[3] = (float) (1.0 + a1 + a2);
+    out7[4] = (float) a1;
+    out7[5] = (float) a2;
+    out7[6] = mix;
+}
+ORC_API uint32_t orc_chorus_ring_len(float sr) { return (uint32_t) ceil(2.0 * 12.0 * (double) sr / 1000.0) + 4u; }
+ORC_API void orc_chorus_table(float *tab513) {
+    for (int i = 0; i <= 512; i++) tab513[i] = (float) cos(2.0 * 3.14159265358979323846 * (double) i / 512.0);
+}
+// One instance over `frames` frames.  state: [0] phase, [1] y1, [2] y2; ring: ring_len floats; *w: write index.
+ORC_API void orc_chorus_run(const float *par7, uint32_t ring_len, float *state3, float *ring, uint32_t *w, const float *x, float *y,
+                            uint64_t frames, uint64_t stride) {
+    static float tab[513];
+    static bool have = false;
+    if (!have) { orc_chorus_table(tab); have = true; }
+    const float inc = par7[0], d = par7[1], offset = par7[2], scale = par7[3], a1 = par7[4], a2 = par7[5], mix = par7[6];
+    float phase = state3[0], y1 = state3[1], y2 = state3[2];
+    uint32_t wp = *w;
+    const float dmax = (float) (ring_len - 2);
+    for (uint64_t n = 0; n < frames; n++) {
+        const float xin = x[n * stride];
+        float p = phase + offset;
+        if (p >= 1.0f) p = p - 1.0f;
+        const float idx = p * 512.0f;
+        int i0 = (int) idx;
+        if (i0 > 511) i0 = 511;
+        const float f = idx - (float) i0;
+        const float c0 = tab[i0], c1 = tab[i0 + 1];
+        const float lfo = c0 + (c1 - c0) * f;
+        float dt = lfo * d + d;
+        dt = dt < 0.0f ? 0.0f : dt;
+        dt = dt > dmax ? dmax : dt;
+        ring[wp] = xin;
+        const uint32_t k = (uint32_t) dt;
+        const float fr = dt - (float) k;
+        const uint32_t ia = wp >= k ? wp - k : wp + ring_len - k;
+        const uint32_t ib = ia >= 1 ? ia - 1 : ring_len - 1;
+        const float a = ring[ia], b = ring[ib];
+        const float wet0 = a + (b - a) * fr;
+        float t = scale * wet0;
+        t = t - a1 * y1;
+        t = t - a2 * y2;
+        y2 = y1;
+        y1 = t;
+        y[n * stride] = t * mix + xin * (1.0f - mix);
+        phase = phase + inc;
+        if (phase >= 1.0f) phase = phase - 1.0f;
+        wp = wp + 1 == ring_len ? 0 : wp + 1;
+    }
+    state3[0] = phase; state3[1] = y1; state3[2] = y2;
+    *w = wp;
+}

@@ -1,0 +1,112 @@
+"""GPU parity of the chorus bank through the C ABI.  The reference has no chorus code -- only
+the RNBO graph modules/rnbo/patcher/mono-chorus.rnbopat -- so the oracle (oracle/olb_oracle.cpp orc_chorus_*) is the
+specification of the arithmetic: PARITY UNPINNED.  The bank must match it bit for bit."""
+import numpy as np
+import pytest
+import torch
+
+from ol_dsp_b200 import ChorusBank
+
+pytestmark = pytest.mark.gpu
+NAMES = ("rate", "depth", "cutoff", "q", "mix", "phase")
+
+
+def bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def params_for(i, I):
+    return dict(rate=(i % 11) / 10.0, depth=((i * 7) % 13) / 12.0, cutoff=((i * 3) % 17) / 16.0, q=((i * 5) % 9) / 8.0,
+                mix=((i * 2) % 7) / 6.0, phase=(i % 5) / 4.0)
+
+
+def run_bank(x, plist, sr=48000.0, chunks=None, changes=None):
+    T, I = x.shape
+    b = ChorusBank(I, sample_rate=sr)
+    for i, p in enumerate(plist):
+        for k, v in (p or {}).items():
+            b.Set(k, v, first=i, count=1)
+    dx = torch.from_numpy(np.ascontiguousarray(x)).cuda()
+    dy = torch.empty_like(dx)
+    a = 0
+    for n in (chunks or [T]):
+        for f, d in (changes or []):
+            if f == a:
+                for k, v in d.items():
+                    b.Set(k, v)
+        b.ProcessDevice(dx[a:].data_ptr(), dy[a:].data_ptr(), n)
+        a += n
+    assert a == T
+    torch.cuda.synchronize()
+    kern = b.LastKernel()
+    b.close()
+    return dy.cpu().numpy(), kern
+
+
+@pytest.mark.parametrize("I,env", [(64, None), (84, None), (77, None), (64, "direct")])
+def test_bank_matches_the_restatement(orc, monkeypatch, I, env):
+    """Per-instance parameter sweep over the whole 0..1 range of every param (depth below its 0.08 floor included), ragged
+    chunks whose sizes straddle the ring wrap (1 156 frames at 48 kHz), bank widths that are / are not a multiple of 4."""
+    if env:
+        monkeypatch.setenv("OLB_CHORUS_KERNEL", env)
+    T = 6000
+    x = orc.noise(21, 0, I, 0, T, 0.5)
+    plist = [params_for(i, I) for i in range(I)]
+    plist[1] = None  # patch defaults
+    y, kern = run_bank(x, plist, chunks=[1, 63, 64, 1028, 1, 1155, 1157, T - 3469])
+    assert kern == ("k_chorus_tma" if I % 4 == 0 and not env else "k_chorus_direct")
+    for i in (0, 1, 2, 3, 10, 31, 32, 33, I - 1):
+        want = orc.chorus(x[:, i], **(plist[i] or {}))
+        assert np.array_equal(bits(y[:, i]), bits(want)), (I, i)
+
+
+def test_parameter_change_mid_stream_reinit_and_in_place(orc):
+    I, T = 8, 5000
+    x = orc.noise(22, 0, I, 0, T, 0.5)
+    ch = [(2000, dict(rate=0.9, depth=0.1, mix=1.0)), (3000, dict(cutoff=0.9, q=0.9, phase=0.25))]
+    y, _ = run_bank(x, [None] * I, chunks=[2000, 1000, 2000], changes=ch)
+    want = orc.chorus(x[:, 5], changes=ch)
+    assert np.array_equal(bits(y[:, 5]), bits(want))
+    b = ChorusBank(I, sample_rate=44100.0)
+    dx = torch.from_numpy(x).cuda()
+    b.ProcessDevice(dx.data_ptr(), dx.data_ptr(), 700)  # in place
+    b.Init(48000.0)                                     # re-Init: ring, filter, phase cleared, another ring length
+    dx = torch.from_numpy(x).cuda()
+    b.ProcessDevice(dx.data_ptr(), dx.data_ptr(), T)
+    torch.cuda.synchronize()
+    assert np.array_equal(bits(dx[:, 3].cpu().numpy()), bits(orc.chorus(x[:, 3])))
+    b.close()
+
+
+def test_other_sample_rates_and_the_shared_memory_limit(orc):
+    x = orc.noise(23, 0, 4, 0, 3000, 0.5)
+    for sr in (44100.0, 32000.0):
+        y, _ = run_bank(x, [None] * 4, sr=sr)
+        assert np.array_equal(bits(y[:, 2]), bits(orc.chorus(x[:, 2], sr=sr)))
+    from ol_dsp_b200 import OlbError
+    with pytest.raises(OlbError):
+        ChorusBank(4, sample_rate=96000.0)  # a 2 308-frame ring x 32 lanes does not fit beside the tile pipeline
+
+
+def test_full_width_properties():
+    """8 192 instances (BASELINE configs[4]): silence in -> silence out; mix = 0 returns the input bit for bit; identical
+    instances give identical outputs."""
+    I, T = 8192, 4096
+    b = ChorusBank(I)
+    z = torch.zeros((T, I), dtype=torch.float32, device="cuda")
+    y = torch.empty_like(z)
+    b.ProcessDevice(z.data_ptr(), y.data_ptr(), T)
+    torch.cuda.synchronize()
+    assert float(y.abs().max()) == 0.0
+    b.Init(48000.0)
+    b.Set("mix", 0.0)
+    x = torch.rand((T, 1), device="cuda").expand(T, I).contiguous() - 0.5
+    b.ProcessDevice(x.data_ptr(), y.data_ptr(), T)
+    torch.cuda.synchronize()
+    assert torch.equal(y, x)
+    b.Init(48000.0)
+    b.Set("mix", 0.5)
+    b.ProcessDevice(x.data_ptr(), y.data_ptr(), T)
+    torch.cuda.synchronize()
+    assert torch.isfinite(y).all() and torch.equal(y, y[:, :1].expand(-1, I)) and not torch.equal(y, x)
+    b.close()

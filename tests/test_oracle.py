@@ -165,3 +165,21 @@ def test_biquad_tiers_error_budget(orc):
         y = orc.biquad(x, k, mode=mode)
         assert np.abs(y - truth).max() <= 1.5 * err_e
         assert np.abs(y - e).max() <= 1e-3
+
+
+def test_chorus_restatement_properties(orc):
+    """(a9) The chorus has no reference code (RNBO graph only; parity unpinned).  Properties of the restatement: mix = 0 is
+    the identity; at mix = 1 a constant input settles to the same constant (lores~ has unity DC gain: scale = 1 + a1 + a2);
+    the modulated delay stays inside [0, 2 d]; chunked processing equals one pass."""
+    x = orc.noise(31, 0, 1, 0, 20000, 0.5)[:, 0]
+    assert np.array_equal(orc.chorus(x, mix=0.0).view(np.uint32), x.view(np.uint32))
+    y = orc.chorus(np.full(48000, 0.25, np.float32), mix=1.0, q=0.0, cutoff=0.5)
+    assert abs(float(y[-1]) - 0.25) < 1e-4
+    a = orc.chorus(x, rate=0.7, depth=1.0)
+    b = orc.chorus(x, rate=0.7, depth=1.0, changes=[(1, {}), (1157, {}), (9999, {})])
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    imp = np.zeros(4000, np.float32)
+    imp[0] = 1.0
+    w = orc.chorus(imp, mix=1.0, depth=1.0, rate=0.0, phase=0.0)   # LFO starts at cos(0) = 1 -> delay ~ 2 d = 1 152 samples
+    first = int(np.nonzero(w)[0][0])
+    assert 1140 <= first <= 1153

@@ -94,6 +94,38 @@ def bench_fx(a, kind, name, bytes_per_unit):
     b.close()
 
 
+def bench_chorus(a):
+    """C5: chorus rate / depth swept per instance."""
+    import numpy as np
+    import torch
+    from ol_dsp_b200 import ChorusBank, noise_device
+    I, F = a.instances, a.frames
+    b = ChorusBank(I)
+    b.Set("rate", ((np.arange(I) % 64) / 63.0).astype(np.float32))
+    b.Set("depth", (0.08 + 0.92 * np.arange(I) / I).astype(np.float32))
+    b.Set("phase", ((np.arange(I) % 7) / 7.0).astype(np.float32))
+    x = torch.empty((F, I), dtype=torch.float32, device="cuda")
+    noise_device(x.data_ptr(), 0x01D5B200, 0, I, 0, F, 0.25)
+    y = torch.empty_like(x)
+    st = torch.cuda.current_stream().cuda_stream
+    dt = timed(lambda: b.ProcessDevice(x.data_ptr(), y.data_ptr(), F, st), a.steps)
+    units = I * F
+    line = {"unit": "chorus", "metric": "instance-samples/s", "value": units / dt, "ms_per_step": dt * 1e3, "instances": I, "frames": F,
+            "roofline": {"bound": "hbm", "algorithmic_bytes_per_unit": 8, "achieved": 8 * units / dt / 1e9, "peak": peaks(), "unit": "GB/s",
+                         "frac": 8 * units / dt / 1e9 / peaks()},
+            "kernel": b.LastKernel(), "checksum": float(y.double().sum().item())}
+    if a.cpu:
+        import time
+        from oracle import loader
+        xs = np.ascontiguousarray(x[:, 0].cpu().numpy())
+        t0 = time.perf_counter()
+        loader.oracle().chorus(xs)
+        line["cpu_baseline"] = {"value": F / (time.perf_counter() - t0), "unit": "instance-samples/s", "cores": 1, "kind": "port",
+                                "sample": f"1 instance x {F} frames, the oracle's scalar chorus"}
+    print(json.dumps(line), flush=True)
+    b.close()
+
+
 def bench_voices(a):
     """C4: `instances` voices PER GPU (weak), note 36 + (v mod 61), presets through the MIDI maps, NoteOn at t = 0; each rank
     reduces its voices to a partial stereo bus on chip, then ONE NCCL all-reduce of [frames][2] floats per step."""
@@ -147,12 +179,12 @@ def bench_voices(a):
 
 if __name__ == "__main__":
     p = argparse.ArgumentParser()
-    p.add_argument("unit", choices=["dattorro", "filterfx", "delayfx", "fxrack", "voices"])
+    p.add_argument("unit", choices=["dattorro", "filterfx", "delayfx", "fxrack", "voices", "chorus"])
     p.add_argument("--instances", type=int, default=8192)
     p.add_argument("--frames", type=int, default=48000)
     p.add_argument("--steps", type=int, default=3)
     p.add_argument("--cpu", action="store_true")
     a = p.parse_args()
     from ol_dsp_b200 import fx as _fx
-    {"voices": bench_voices, "dattorro": bench_dattorro, "filterfx": lambda a: bench_fx(a, _fx.FILTER, "filterfx", 8),
+    {"voices": bench_voices, "dattorro": bench_dattorro, "chorus": bench_chorus, "filterfx": lambda a: bench_fx(a, _fx.FILTER, "filterfx", 8),
      "delayfx": lambda a: bench_fx(a, _fx.DELAY, "delayfx", 16), "fxrack": lambda a: bench_fx(a, _fx.RACK, "fxrack", 16)}[a.unit](a)
