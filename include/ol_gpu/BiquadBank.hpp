@@ -21,9 +21,11 @@
 namespace ol {
 namespace gpu {
 
-typedef float t_sample;
-
-enum InitStatus { Ok = 0, Error = 1 };
+#ifndef OL_GPU_T_SAMPLE
+#define OL_GPU_T_SAMPLE
+typedef float t_sample;  // modules/corelib/ol_corelib.h:23
+enum InitStatus { Ok = 0, Error = 1 };  // modules/synthlib/SoundSource.h:9-11
+#endif
 
 class BiquadBank {
 public:

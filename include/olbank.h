@@ -146,6 +146,9 @@ int olb_fx_update_hw(olb_fx *h, uint32_t first, uint32_t count, uint8_t control,
 int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream);
 /* Diagnostics: which kernel the last process call launched ("k_fx_tma", "k_fx_pf", "k_fx"). */
 const char *olb_fx_last_kernel(olb_fx *h);
+/* Same with HOST buffers [frames][instances] (the reference's Process takes host frames: Fx.h:88,194,294,426); chunked
+ * through device staging, returns when out_host is complete.  frames == 1 is the per-frame call. */
+int olb_fx_process_host(olb_fx *h, const float *in_host, float *out_host, uint64_t frames);
 
 /* (a6) SynthVoice bank and (a8) Polyvoice mixdown -------------------------------------------------------
  * One bank = `voices` ol::synth::SynthVoice objects with the reference's default parts (PolyBLEP-saw
@@ -176,6 +179,10 @@ int olb_voice_set_frequency(olb_voice *h, uint32_t first, uint32_t count, const 
 int olb_voice_playing(olb_voice *h, uint32_t first, uint32_t count, uint8_t *playing_host);
 int olb_voice_process(olb_voice *h, float *out_dev, float *bus_dev, uint32_t bus_channels, int accumulate, float bus_gain,
                       float *trace_dev, uint64_t frames, void *stream);
+/* Same with HOST buffers: out_host (optional) [frames][voices]; bus_host (optional) [frames][bus_channels], ADDED to when
+ * accumulate != 0 (Polyvoice::Process adds into *frame_out: Polyvoice.h:28-33). */
+int olb_voice_process_host(olb_voice *h, float *out_host, float *bus_host, uint32_t bus_channels, int accumulate, float bus_gain,
+                           uint64_t frames);
 
 /* (a7) Dattorro plate reverb bank -------------------------------------------------------------------
  * Replaces libs/dattorro-verb/verb.h:5-26 for `instances` plates at once (mono in, stereo wet out):
@@ -206,6 +213,8 @@ int olb_dattorro_set_params(olb_dattorro *h, uint32_t first, uint32_t count, int
 /* For each frame: DattorroVerb_process(in); out_l = getLeft(); out_r = getRight().  Device buffers, all
  * [frames][instances] (instance fastest). */
 int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *out_l_dev, float *out_r_dev, uint64_t frames, void *stream);
+/* Same with HOST buffers (all [frames][instances]); returns when the outputs are complete. */
+int olb_dattorro_process_host(olb_dattorro *h, const float *in_host, float *out_l_host, float *out_r_host, uint64_t frames);
 
 /* (a9) Chorus bank ------------------------------------------------------------------------------------
  * The reference has no chorus class; its chorus is the Max/RNBO graph modules/rnbo/patcher/mono-chorus.rnbopat
@@ -230,6 +239,7 @@ int olb_chorus_init(olb_chorus *h, float sample_rate);
 int olb_chorus_set_param(olb_chorus *h, uint32_t first, uint32_t count, int param, float value);
 int olb_chorus_set_params(olb_chorus *h, uint32_t first, uint32_t count, int param, const float *values_host, uint32_t stride);
 int olb_chorus_process(olb_chorus *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream);
+int olb_chorus_process_host(olb_chorus *h, const float *in_host, float *out_host, uint64_t frames);
 const char *olb_chorus_last_kernel(olb_chorus *h);
 
 #ifdef __cplusplus

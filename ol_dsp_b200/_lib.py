@@ -71,6 +71,10 @@ def lib():
         "olb_fx_update_hw": ([vp, u32, u32, C.c_uint8, _F, u32], i32),
         "olb_fx_process": ([vp, vp, vp, u64, vp], i32),
         "olb_fx_last_kernel": ([vp], C.c_char_p),
+        "olb_fx_process_host": ([vp, vp, vp, u64], i32),
+        "olb_voice_process_host": ([vp, vp, vp, u32, i32, f32, u64], i32),
+        "olb_dattorro_process_host": ([vp, vp, vp, vp, u64], i32),
+        "olb_chorus_process_host": ([vp, vp, vp, u64], i32),
         "olb_voice_create": ([i32, u32, f32, C.POINTER(vp)], i32),
         "olb_voice_destroy": ([vp], i32),
         "olb_voice_init": ([vp, f32], i32),

@@ -218,6 +218,7 @@ struct olb_chorus {
     bool dirty = true;
     float *d_par = nullptr, *d_state = nullptr, *d_ring = nullptr, *d_tab = nullptr;
     const char *last_kernel = "none";
+    HostStage host;
 };
 
 constexpr int kChTB = 64, kChStages = 4;
@@ -251,6 +252,7 @@ static void chorus_derive(const olb_chorus *h, uint32_t i, float *out /* stride 
 
 static void chorus_free(olb_chorus *h) {
     cudaFree(h->d_par); cudaFree(h->d_state); cudaFree(h->d_ring); cudaFree(h->d_tab);
+    h->host.release();
     delete h;
 }
 
@@ -372,5 +374,25 @@ OLB_API int olb_chorus_process(olb_chorus *h, const float *in_dev, float *out_de
     }
     OLB_LAUNCHED();
     h->w = (uint32_t) ((h->w + frames) % h->R);
+    return OLB_OK;
+}
+
+// Host buffers [frames][instances]: chunked in time through device staging; returns when out_host is complete.
+OLB_API int olb_chorus_process_host(olb_chorus *h, const float *in_host, float *out_host, uint64_t frames) {
+    OLB_ARG(h, "olb_chorus_process_host: NULL handle");
+    if (frames == 0) return OLB_OK;
+    OLB_ARG(in_host && out_host, "olb_chorus_process_host: NULL buffer");
+    DeviceGuard g(h->device);
+    const uint64_t I = h->I, chunk = host_chunk_frames(I, frames);
+    int rc = h->host.ensure(0, chunk * I);
+    if (rc) return rc;
+    for (uint64_t t0 = 0; t0 < frames; t0 += chunk) {
+        const uint64_t n = frames - t0 < chunk ? frames - t0 : chunk;
+        OLB_CUDA(cudaMemcpyAsync(h->host.d[0], in_host + t0 * I, n * I * sizeof(float), cudaMemcpyHostToDevice, h->host.st));
+        rc = olb_chorus_process(h, h->host.d[0], h->host.d[0], n, h->host.st);
+        if (rc) return rc;
+        OLB_CUDA(cudaMemcpyAsync(out_host + t0 * I, h->host.d[0], n * I * sizeof(float), cudaMemcpyDeviceToHost, h->host.st));
+    }
+    OLB_CUDA(cudaStreamSynchronize(h->host.st));
     return OLB_OK;
 }

@@ -55,6 +55,37 @@ struct DeviceGuard {
 
 int require_sm100(int device);
 
+// ---- host-buffer convenience path of the small banks (fx, plate, chorus, voices) -----------------
+// Device staging that grows on demand plus one private stream: `process_host` entry points copy a time chunk in, run the
+// bank's own device path on it, copy the result out, and return when the host buffer is complete (the reference's
+// Process() is synchronous).  The biquad bank has its own three-stream overlapped version (biquad_bank.cu).
+struct HostStage {
+    float *d[3] = {nullptr, nullptr, nullptr};
+    size_t cap[3] = {0, 0, 0};
+    cudaStream_t st = nullptr;
+    int ensure(int k, size_t elems) {
+        if (!st) OLB_CUDA(cudaStreamCreateWithFlags(&st, cudaStreamNonBlocking));
+        if (cap[k] < elems) {
+            cudaFree(d[k]);
+            d[k] = nullptr;
+            cap[k] = 0;
+            OLB_CUDA(cudaMalloc(&d[k], elems * sizeof(float)));
+            cap[k] = elems;
+        }
+        return OLB_OK;
+    }
+    void release() {
+        for (int k = 0; k < 3; k++) cudaFree(d[k]);
+        if (st) cudaStreamDestroy(st);
+    }
+};
+// frames per staged chunk: ~32 MiB per buffer, whole frames, a multiple of 64 (the TMA tile height)
+static inline uint64_t host_chunk_frames(uint64_t units, uint64_t frames) {
+    uint64_t c = (32ull << 20) / (units * sizeof(float));
+    c = c < 64 ? 64 : (c / 64) * 64;
+    return c > frames ? frames : c;
+}
+
 // ---- packed fp32x2 arithmetic (sm_100 FFMA2).  One instruction, two IEEE-rounded lanes. ---------
 typedef unsigned long long u64;
 

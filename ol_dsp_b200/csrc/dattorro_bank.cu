@@ -272,6 +272,7 @@ struct olb_dattorro {
     std::vector<float> par_host;  // [8][I]
     bool par_dirty = true;
     float *d_slab = nullptr, *d_lp = nullptr, *d_par = nullptr;
+    HostStage host;
 };
 
 static void plate_geometry(PlateGeom *g, uint32_t *positions) {
@@ -355,6 +356,7 @@ OLB_API int olb_dattorro_destroy(olb_dattorro *h) {
     if (!h) return OLB_OK;
     DeviceGuard g(h->device);
     cudaFree(h->d_slab); cudaFree(h->d_lp); cudaFree(h->d_par);
+    h->host.release();
     delete h;
     return OLB_OK;
 }
@@ -445,5 +447,28 @@ OLB_API int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *ou
     h->t = t;
     h->geom.off[DV_DD1A] = oa;
     h->geom.off[DV_DD1B] = ob;
+    return OLB_OK;
+}
+
+// Host buffers, all [frames][instances]: chunked in time through device staging; returns when the outputs are complete.
+OLB_API int olb_dattorro_process_host(olb_dattorro *h, const float *in_host, float *out_l_host, float *out_r_host, uint64_t frames) {
+    OLB_ARG(h, "olb_dattorro_process_host: NULL handle");
+    if (frames == 0) return OLB_OK;
+    OLB_ARG(in_host && out_l_host && out_r_host, "olb_dattorro_process_host: NULL buffer");
+    DeviceGuard g(h->device);
+    const uint64_t I = h->I, chunk = host_chunk_frames(I, frames);
+    for (int k = 0; k < 3; k++) {
+        int rc = h->host.ensure(k, chunk * I);
+        if (rc) return rc;
+    }
+    for (uint64_t t0 = 0; t0 < frames; t0 += chunk) {
+        const uint64_t n = frames - t0 < chunk ? frames - t0 : chunk;
+        OLB_CUDA(cudaMemcpyAsync(h->host.d[0], in_host + t0 * I, n * I * sizeof(float), cudaMemcpyHostToDevice, h->host.st));
+        int rc = olb_dattorro_process(h, h->host.d[0], h->host.d[1], h->host.d[2], n, h->host.st);
+        if (rc) return rc;
+        OLB_CUDA(cudaMemcpyAsync(out_l_host + t0 * I, h->host.d[1], n * I * sizeof(float), cudaMemcpyDeviceToHost, h->host.st));
+        OLB_CUDA(cudaMemcpyAsync(out_r_host + t0 * I, h->host.d[2], n * I * sizeof(float), cudaMemcpyDeviceToHost, h->host.st));
+    }
+    OLB_CUDA(cudaStreamSynchronize(h->host.st));
     return OLB_OK;
 }

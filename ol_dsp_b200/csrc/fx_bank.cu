@@ -59,6 +59,33 @@ __device__ __forceinline__ float svf_tick(float in, float &low, float &band, con
     return __fadd_rn(o1, __fmul_rn(0.5f, svf_pick(k.type, low, band, high, notch)));
 }
 
+// Two independent SVFs advanced together, statement by statement: the same operations as two svf_tick calls, written
+// interleaved because ptxas keeps close to source order and each filter alone is one 12-deep dependent chain.
+__device__ __forceinline__ void svf_tick_pair(float inA, float &lowA, float &bandA, const SvfCoef &kA, float &outA, float inB, float &lowB,
+                                              float &bandB, const SvfCoef &kB, float &outB) {
+    float dA = __fmul_rn(kA.damp, bandA), dB = __fmul_rn(kB.damp, bandB);
+    float gA = __fmul_rn(kA.freq, bandA), gB = __fmul_rn(kB.freq, bandB);
+    float cA = __fmul_rn(__fmul_rn(__fmul_rn(kA.drive, bandA), bandA), bandA), cB = __fmul_rn(__fmul_rn(__fmul_rn(kB.drive, bandB), bandB), bandB);
+    float notchA = __fsub_rn(inA, dA), notchB = __fsub_rn(inB, dB);
+    lowA = __fadd_rn(lowA, gA); lowB = __fadd_rn(lowB, gB);
+    float highA = __fsub_rn(notchA, lowA), highB = __fsub_rn(notchB, lowB);
+    float tA = __fmul_rn(kA.freq, highA), tB = __fmul_rn(kB.freq, highB);
+    tA = __fadd_rn(tA, bandA); tB = __fadd_rn(tB, bandB);
+    bandA = __fsub_rn(tA, cA); bandB = __fsub_rn(tB, cB);
+    const float o1A = __fmul_rn(0.5f, svf_pick(kA.type, lowA, bandA, highA, notchA)), o1B = __fmul_rn(0.5f, svf_pick(kB.type, lowB, bandB, highB, notchB));
+    dA = __fmul_rn(kA.damp, bandA); dB = __fmul_rn(kB.damp, bandB);
+    gA = __fmul_rn(kA.freq, bandA); gB = __fmul_rn(kB.freq, bandB);
+    cA = __fmul_rn(__fmul_rn(__fmul_rn(kA.drive, bandA), bandA), bandA); cB = __fmul_rn(__fmul_rn(__fmul_rn(kB.drive, bandB), bandB), bandB);
+    notchA = __fsub_rn(inA, dA); notchB = __fsub_rn(inB, dB);
+    lowA = __fadd_rn(lowA, gA); lowB = __fadd_rn(lowB, gB);
+    highA = __fsub_rn(notchA, lowA); highB = __fsub_rn(notchB, lowB);
+    tA = __fmul_rn(kA.freq, highA); tB = __fmul_rn(kB.freq, highB);
+    tA = __fadd_rn(tA, bandA); tB = __fadd_rn(tB, bandB);
+    bandA = __fsub_rn(tA, cA); bandB = __fsub_rn(tB, cB);
+    outA = __fadd_rn(o1A, __fmul_rn(0.5f, svf_pick(kA.type, lowA, bandA, highA, notchA)));
+    outB = __fadd_rn(o1B, __fmul_rn(0.5f, svf_pick(kB.type, lowB, bandB, highB, notchB)));
+}
+
 __device__ __forceinline__ float dry_wet(float wet, float dry, float balance) {  // Fx.h:205-207, 297-299
     return __fadd_rn(__fmul_rn(wet, balance), __fmul_rn(dry, __fsub_rn(1.0f, balance)));
 }
@@ -121,6 +148,71 @@ __device__ __forceinline__ float fx_frame(float v, float ra, float rb, float &wr
     if (KIND == OLB_FX_FILTER || KIND == OLB_FX_RACK) v = svf_tick(v, f_low, f_band, kf);
     if (KIND == OLB_FX_RACK) v = __fmul_rn(v, master);
     return v;
+}
+
+// A batch of N frames of one instance out of shared memory, written stage by stage over register arrays so that ptxas sees
+// the independent streams of one basic block: (A) every input, tap and ring write-back value of the batch, (B) the wet
+// filter's recurrence, (C) the mixes, (D) the main filter's recurrence.  Only B and D are serial (12 dependent FP32 ops
+// per frame each), they are independent of each other (D lags B by one frame), and A / C fill their stall slots; written
+// frame by frame the compiler runs everything in sequence (the next tap load cannot move above the previous frame's
+// shared-memory store) and a delay frame costs 2.3x the recurrence.  Same operations, same order per value: bit-exact.
+// col: this lane's column of the audio tile (stride kFxLanes); tap: its first tap (walks down); wcol: its write-back column.
+constexpr int kFxLanes = 32;
+template <int KIND, int N>
+__device__ __forceinline__ void fx_batch(float *col, const float *tap, float *wcol, int wstride, float &prev_a, float frac, float feedback,
+                                         float d_balance, float r_balance, float master, float &w_low, float &w_band, const SvfCoef &kw,
+                                         float &f_low, float &f_band, const SvfCoef &kf) {
+    constexpr bool kHasRing = (KIND == OLB_FX_DELAY || KIND == OLB_FX_RACK);
+    float x[N], rd[N], v[N];
+#pragma unroll
+    for (int r = 0; r < N; r++) x[r] = col[r * kFxLanes];
+    if (kHasRing) {
+        float ra[N];
+#pragma unroll
+        for (int r = 0; r < N; r++) ra[r] = *(tap - r);
+#pragma unroll
+        for (int r = 0; r < N; r++) {
+            const float rb = r == 0 ? prev_a : ra[r - 1];
+            rd[r] = __fadd_rn(ra[r], __fmul_rn(__fsub_rn(rb, ra[r]), frac));     // DelayLine::Read (Fx.h:198)
+            wcol[r * wstride] = __fadd_rn(x[r], __fmul_rn(feedback, rd[r]));    // Write(in + feedback * read) (Fx.h:199-200)
+        }
+        prev_a = ra[N - 1];
+        if (KIND == OLB_FX_RACK) {
+            // the two recurrences side by side, the main filter one frame behind the wet filter: in source order frame r of
+            // chain B sits next to frame r-1 of chain D, which is where ptxas's in-order schedule needs them to overlap
+            float u = 0.f;  // main filter input of frame r-1
+#pragma unroll
+            for (int r = 0; r <= N; r++) {
+                float wet = 0.f, y = 0.f;
+                if (r > 0 && r < N) svf_tick_pair(rd[r], w_low, w_band, kw, wet, u, f_low, f_band, kf, y);
+                else if (r < N) wet = svf_tick(rd[r], w_low, w_band, kw);
+                else y = svf_tick(u, f_low, f_band, kf);
+                if (r > 0) v[r - 1] = y;
+                if (r < N) {
+                    u = dry_wet(wet, x[r], d_balance);
+                    u = dry_wet(__fmul_rn(u, 0.8f), u, r_balance);
+                }
+            }
+        } else {
+#pragma unroll
+            for (int r = 0; r < N; r++) v[r] = svf_tick(rd[r], w_low, w_band, kw);
+#pragma unroll
+            for (int r = 0; r < N; r++) v[r] = dry_wet(v[r], x[r], d_balance);
+        }
+    } else {
+#pragma unroll
+        for (int r = 0; r < N; r++) v[r] = x[r];
+    }
+    if (KIND == OLB_FX_REVERB) {
+#pragma unroll
+        for (int r = 0; r < N; r++) v[r] = dry_wet(__fmul_rn(v[r], 0.8f), v[r], r_balance);
+    }
+    if (KIND == OLB_FX_FILTER) {
+#pragma unroll
+        for (int r = 0; r < N; r++) v[r] = svf_tick(v[r], f_low, f_band, kf);
+    }
+#pragma unroll
+    for (int r = 0; r < N; r++) col[r * kFxLanes] = KIND == OLB_FX_RACK ? __fmul_rn(v[r], master) : v[r];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -222,10 +314,12 @@ __global__ void __launch_bounds__(64) k_fx_pf(const float *in, float *out, uint3
 // law caps the bank near 0.5 TB/s.  Here ONE warp is one CTA with its own TMA pipeline (the k_bq_tma pattern):
 // [TB frames][32 instances] boxes by cp.async.bulk.tensor.2d into a STAGES-deep shared-memory ring with mbarrier
 // complete_tx, filtered in place (each lane walks its own column), stored by TMA; (STAGES-1) x TB frames per instance
-// are in flight.  The delay kinds fetch the ring reads of the same future tile with 4-byte cp.async (LDGSTS) into a
-// second per-lane column, one commit group per tile.  Ring reads run ahead only when the delay exceeds the look-ahead
-// (STAGES x TB + 2 frames); a warp in which every lane qualifies runs the branch-free loop, any other warp the
-// general loop (direct reads for its short-delay lanes).
+// are in flight.  The delay kinds also stream their rings ([instances][48 000], one contiguous line per instance because
+// delay times differ per instance) COALESCED: the taps of a future tile are one contiguous run per instance, copied by
+// its lane as 16-byte cp.async chunks into a per-instance row of a tap tile; the tile's new samples are staged in shared
+// memory and written back as float4s.  (4-byte accesses cost one instruction and 32 L1 wavefronts per frame each way and
+// held the delay kinds at 1.0e11 instance-samples/s at every bank size.)  This needs every live lane's delay to exceed the look-ahead (STAGES x TB + 2 frames); any other
+// warp runs the general loop, direct per-lane reads and writes.
 __device__ __forceinline__ void fx_cp_async4(float *smem_dst, const float *gmem_src) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
 }
@@ -235,7 +329,18 @@ __device__ __forceinline__ void fx_cp_async_wait() {
     asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
 }
 
-constexpr int kFxL = 32;  // instances per warp / CTA
+__device__ __forceinline__ void fx_cp_async16(float *smem_dst, const float *gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_u32(smem_dst)), "l"(gmem_src) : "memory");
+}
+
+constexpr int kFxL = kFxLanes;  // instances per warp / CTA
+constexpr int kFxBatch = 8;    // frames per fx_batch
+
+// floats of shared memory in front of the mbarriers: audio tiles, and for the ring kinds the tap tiles + the write-back tile
+template <int TB, int STAGES>
+__host__ __device__ constexpr size_t fx_tma_smem_floats(bool has_ring) {
+    return ((size_t) STAGES * TB * kFxL + (has_ring ? (size_t) STAGES * kFxL * (TB + 4) + (size_t) TB * kFxL : 0) + 1) & ~(size_t) 1;
+}
 
 template <int KIND, int TB, int STAGES>
 __global__ void __launch_bounds__(32) k_fx_tma(const __grid_constant__ TensorMap tm_in, const __grid_constant__ TensorMap tm_out,
@@ -246,9 +351,12 @@ __global__ void __launch_bounds__(32) k_fx_tma(const __grid_constant__ TensorMap
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const uint32_t lane = threadIdx.x, i0 = blockIdx.x * L, inst = i0 + lane;
     const bool live = inst < I;
+    constexpr int RS = TB + 4;   // floats per instance row of a ring tile: TB taps + alignment slack, 16-byte multiple
+    constexpr int WS = L;        // row of the write-staging tile (each lane owns a column)
     float *tiles = reinterpret_cast<float *>(smem_raw);                    // [STAGES][TB][L]
-    float *rtiles = tiles + (size_t) STAGES * TB * L;                      // [STAGES][TB][L], ring kinds only
-    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + (size_t) (kHasRing ? 2 : 1) * STAGES * TB * L * sizeof(float));
+    float *rtiles = tiles + (size_t) STAGES * TB * L;                      // [STAGES][L][RS]  ring kinds only: delay-line taps
+    float *wtile = rtiles + (size_t) STAGES * L * RS;                      // [TB][WS]         ring kinds only: values to write back
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + fx_tma_smem_floats<TB, STAGES>(kHasRing) * sizeof(float));
     if (lane == 0) {
 #pragma unroll
         for (int s = 0; s < STAGES; s++) mbar_init(&full[s], 1);
@@ -268,33 +376,39 @@ __global__ void __launch_bounds__(32) k_fx_tma(const __grid_constant__ TensorMap
     float f_low = svf[ci], f_band = svf[(size_t) I + ci], w_low = svf[2 * (size_t) I + ci], w_band = svf[3 * (size_t) I + ci];
     float *ring = kHasRing ? ring_all + (size_t) ci * kRing : nullptr;
     const bool far = kHasRing && live && delay >= (uint32_t) (STAGES * TB + 2);
+    // Ring traffic is coalesced only when the whole warp can run ahead (every live lane's delay exceeds the look-ahead);
+    // any other warp takes the general loop: per-lane direct reads and writes, no look-ahead.
     const bool all_far = kHasRing && __all_sync(0xffffffffu, far || !live);
-    uint32_t wp = wp0, la = 0;  // wp is the same in every lane (the bank shares DelayLine::write_ptr_)
-    float prev_a = 0.f;
+    uint32_t wp = wp0, la = 0, lc = 0;  // wp is the same in every lane (the bank shares DelayLine::write_ptr_)
+    float prev_a = 0.f;                 // la / lc: tap index of the next frame to be fetched / computed
     if (kHasRing) {
         la = wp0 + delay;
         la = la >= (uint32_t) kRing ? la - kRing : la;
-        if (far) {
+        lc = la;
+        if (all_far && live) {
             const uint32_t ib = la + 1 >= (uint32_t) kRing ? la + 1 - kRing : la + 1;
             prev_a = ring[ib];
         }
     }
+    // Taps of a future tile.  This lane's TB taps are one contiguous run of its ring, la - TB + 1 .. la (the read index
+    // walks backwards): copied as 16-byte chunks (cp.async.cg 16 -> LDGSTS.128) into this lane's row of the tap tile, 17
+    // instructions per tile instead of 64 4-byte ones.  Rings are 48 000 floats (a multiple of 4) and 16-byte aligned,
+    // so a chunk never straddles the wrap.
     auto fetch_ring = [&](uint32_t tile, uint32_t stage) {  // every lane; one commit group per tile, empty or not
         if (kHasRing) {
-            if (far && tile < ntiles) {
-                float *dst = rtiles + (size_t) stage * TB * L + lane;
+            if (all_far && live && tile < ntiles) {
                 const uint32_t rows = min((uint32_t) TB, frames - tile * TB);
-                if (la >= rows) {  // no wrap inside this tile: plain backward walk
-                    const float *srcp = ring + la;
-#pragma unroll 8
-                    for (uint32_t j = 0; j < rows; j++) fx_cp_async4(dst + j * L, srcp - j);
-                    la -= rows;
-                } else {
-                    for (uint32_t j = 0; j < rows; j++) {
-                        fx_cp_async4(dst + j * L, ring + la);
-                        la = la == 0 ? kRing - 1 : la - 1;
+                float *dst = rtiles + (size_t) stage * L * RS + lane * RS;
+                const int base4 = ((int) la - (TB - 1)) & ~3;  // floor to a multiple of 4, also below zero
+#pragma unroll
+                for (int c = 0; c < RS / 4; c++) {
+                    int idx = base4 + 4 * c;
+                    if (idx <= (int) la) {
+                        idx = idx < 0 ? idx + kRing : idx;
+                        fx_cp_async16(dst + 4 * c, ring + idx);
                     }
                 }
+                la = la >= rows ? la - rows : la + kRing - rows;
             }
             fx_cp_async_commit();
         }
@@ -310,11 +424,12 @@ __global__ void __launch_bounds__(32) k_fx_tma(const __grid_constant__ TensorMap
 
     for (uint32_t i = 0; i < ntiles; i++) {
         const uint32_t st = i % STAGES, ph = (i / STAGES) & 1;
-        if (kHasRing) fx_cp_async_wait<STAGES - 2>();
+        if (kHasRing) {
+            fx_cp_async_wait<STAGES - 2>();  // each lane reads only the row it copied itself
+        }
         mbar_wait(&full[st], ph);
         const uint32_t rows = min((uint32_t) TB, frames - i * TB);
         float *col = tiles + (size_t) st * TB * L + lane;
-        const float *rcol = rtiles + (size_t) st * TB * L + lane;
         if (!kHasRing) {
             if (live) {
 #pragma unroll 4
@@ -325,50 +440,52 @@ __global__ void __launch_bounds__(32) k_fx_tma(const __grid_constant__ TensorMap
                 }
             }
         } else if (all_far) {
-            // the write pointer runs backwards and wraps at most once per tile: one or two straight segments
-            for (uint32_t r0 = 0; r0 < rows;) {
-                const uint32_t seg = min(rows - r0, wp + 1);
-                if (live) {
-                    float *wpp = ring + wp;
-                    float *c = col + r0 * L;
-                    const float *rc = rcol + r0 * L;
-#pragma unroll 4
-                    for (uint32_t r = 0; r < seg; r++) {
-                        const float ra = rc[r * L];
-                        float wr;
-                        c[r * L] = fx_frame<KIND>(c[r * L], ra, prev_a, wr, frac, feedback, d_balance, r_balance, master, w_low, w_band,
-                                                  kw, f_low, f_band, kf);
-                        prev_a = ra;
-                        *(wpp - r) = wr;
-                    }
-                }
-                r0 += seg;
-                wp = seg == wp + 1 ? (uint32_t) kRing - 1 : wp - seg;
+            if (live) {
+                // frame r's tap a sits at virtual ring index lc - r, i.e. at row offset (lc - base4) - r of this lane's row
+                const int base4 = ((int) lc - (TB - 1)) & ~3;
+                const float *tap = rtiles + (size_t) st * L * RS + lane * RS + ((int) lc - base4);
+                float *wcol = wtile + lane;
+                uint32_t r = 0;
+                for (; r + kFxBatch <= rows; r += kFxBatch)
+                    fx_batch<KIND, kFxBatch>(col + r * L, tap - r, wcol + r * WS, WS, prev_a, frac, feedback, d_balance, r_balance, master, w_low,
+                                             w_band, kw, f_low, f_band, kf);
+                for (; r < rows; r++)
+                    fx_batch<KIND, 1>(col + r * L, tap - r, wcol + r * WS, WS, prev_a, frac, feedback, d_balance, r_balance, master, w_low,
+                                      w_band, kw, f_low, f_band, kf);
+                lc = lc >= rows ? lc - rows : lc + kRing - rows;
             }
+            // write-back: this lane's `rows` new samples are the contiguous run wp - rows + 1 .. wp of its ring (the write
+            // pointer walks backwards): scalar stores up to a 16-byte boundary, then whole float4s, then the scalar rest.
+            // wp is warp-uniform, so the three loops do not diverge.
+            if (live) {
+                const float *wcol = wtile + lane;
+                uint32_t r = 0;
+                auto at = [&](uint32_t rr) { return wp >= rr ? wp - rr : wp + kRing - rr; };
+                for (; r < rows && (at(r) & 3u) != 3u; r++) ring[at(r)] = wcol[r * WS];
+                for (; r + 4 <= rows; r += 4) {
+                    const float4 q = make_float4(wcol[(r + 3) * WS], wcol[(r + 2) * WS], wcol[(r + 1) * WS], wcol[r * WS]);
+                    *reinterpret_cast<float4 *>(ring + at(r) - 3) = q;
+                }
+                for (; r < rows; r++) ring[at(r)] = wcol[r * WS];
+            }
+            wp = wp >= rows ? wp - rows : wp + kRing - rows;
         } else {
             if (live) {
                 uint32_t w = wp;
-                for (uint32_t r = 0; r < rows; r++) {
-                    float ra, rb, wr;
-                    if (far) {
-                        ra = rcol[r * L];
-                        rb = prev_a;
-                        prev_a = ra;
-                    } else {  // DelayLine::Read straight from the ring (Fx.h:198-200)
-                        uint32_t ia = w + delay;
-                        ia = ia >= (uint32_t) kRing ? ia - kRing : ia;
-                        uint32_t ib = ia + 1;
-                        ib = ib >= (uint32_t) kRing ? ib - kRing : ib;
-                        ra = ring[ia];
-                        rb = ring[ib];
-                    }
+                for (uint32_t r = 0; r < rows; r++) {  // DelayLine::Read straight from the ring (Fx.h:198-200)
+                    uint32_t ia = w + delay;
+                    ia = ia >= (uint32_t) kRing ? ia - kRing : ia;
+                    uint32_t ib = ia + 1;
+                    ib = ib >= (uint32_t) kRing ? ib - kRing : ib;
+                    const float ra = ring[ia], rb = ring[ib];
+                    float wr;
                     col[r * L] = fx_frame<KIND>(col[r * L], ra, rb, wr, frac, feedback, d_balance, r_balance, master, w_low, w_band, kw,
                                                 f_low, f_band, kf);
                     ring[w] = wr;
                     w = w == 0 ? kRing - 1 : w - 1;
                 }
             }
-            wp = (wp + (uint32_t) kRing - rows % kRing) % kRing;
+            wp = wp >= rows ? wp - rows : wp + kRing - rows;
         }
         fence_async_smem();
         __syncwarp();
@@ -412,6 +529,7 @@ struct olb_fx {
     float *d_par = nullptr, *d_svf = nullptr, *d_ring = nullptr;
     std::vector<float> stage;
     const char *last_kernel = "none";
+    HostStage host;
 };
 
 static float bits_f(uint32_t u) {
@@ -467,7 +585,7 @@ static int fx_init(olb_fx *h, float sr) {
 template <int KIND, int TB, int STAGES>
 static int fx_launch_tma_cfg(olb_fx *h, const float *in, float *out, uint32_t frames, cudaStream_t st) {
     constexpr bool has_ring = (KIND == OLB_FX_DELAY || KIND == OLB_FX_RACK);
-    constexpr size_t smem = (size_t) (has_ring ? 2 : 1) * STAGES * TB * kFxL * sizeof(float) + (size_t) STAGES * sizeof(uint64_t);
+    constexpr size_t smem = fx_tma_smem_floats<TB, STAGES>(has_ring) * sizeof(float) + (size_t) STAGES * sizeof(uint64_t);
     TensorMap tin, tout;
     int rc = make_tmap_frames(&tin, in, frames, h->I, kFxL, TB);
     if (rc) return rc;
@@ -525,6 +643,7 @@ OLB_API int olb_fx_destroy(olb_fx *h) {
     if (!h) return OLB_OK;
     DeviceGuard g(h->device);
     cudaFree(h->d_par); cudaFree(h->d_svf); cudaFree(h->d_ring);
+    h->host.release();
     delete h;
     return OLB_OK;
 }
@@ -617,5 +736,25 @@ OLB_API int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev, uint6
 #undef OLB_FX_GO
     OLB_LAUNCHED();
     if (fx_has_ring(h->kind)) h->wp = (uint32_t) ((h->wp + (uint64_t) kRing - frames % kRing) % kRing);
+    return OLB_OK;
+}
+
+// Host buffers [frames][instances]: chunked in time through device staging; returns when out_host is complete.
+OLB_API int olb_fx_process_host(olb_fx *h, const float *in_host, float *out_host, uint64_t frames) {
+    OLB_ARG(h, "olb_fx_process_host: NULL handle");
+    if (frames == 0) return OLB_OK;
+    OLB_ARG(in_host && out_host, "olb_fx_process_host: NULL buffer");
+    DeviceGuard g(h->device);
+    const uint64_t I = h->I, chunk = host_chunk_frames(I, frames);
+    int rc = h->host.ensure(0, chunk * I);
+    if (rc) return rc;
+    for (uint64_t t0 = 0; t0 < frames; t0 += chunk) {
+        const uint64_t n = frames - t0 < chunk ? frames - t0 : chunk;
+        OLB_CUDA(cudaMemcpyAsync(h->host.d[0], in_host + t0 * I, n * I * sizeof(float), cudaMemcpyHostToDevice, h->host.st));
+        rc = olb_fx_process(h, h->host.d[0], h->host.d[0], n, h->host.st);
+        if (rc) return rc;
+        OLB_CUDA(cudaMemcpyAsync(out_host + t0 * I, h->host.d[0], n * I * sizeof(float), cudaMemcpyDeviceToHost, h->host.st));
+    }
+    OLB_CUDA(cudaStreamSynchronize(h->host.st));
     return OLB_OK;
 }

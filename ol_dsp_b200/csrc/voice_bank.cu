@@ -175,6 +175,7 @@ struct olb_voice {
     float *d_par = nullptr, *d_state = nullptr, *d_partial = nullptr;
     uint32_t partial_ld = 0;  // frames capacity of the warp-partial buffer
     std::vector<float> stage;
+    HostStage host;
 };
 
 static float vbits_f(uint32_t u) {
@@ -224,6 +225,7 @@ static int voice_init_all(olb_voice *h, float sr) {
 
 static void voice_free(olb_voice *h) {
     cudaFree(h->d_par); cudaFree(h->d_state); cudaFree(h->d_partial);
+    h->host.release();
     delete h;
 }
 
@@ -368,5 +370,35 @@ OLB_API int olb_voice_process(olb_voice *h, float *out_dev, float *bus_dev, uint
         h->retrig_pending = false;
         h->dirty = true;
     }
+    return OLB_OK;
+}
+
+// Host buffers.  out_host (optional) [frames][voices] = SynthVoice::Process of every voice; bus_host (optional)
+// [frames][bus_channels] = Polyvoice::Process: with accumulate != 0 the mix is ADDED to what bus_host holds (the reference
+// adds into *frame_out and the caller zeroes it: Polyvoice.h:28-33, main.cpp:79).  Chunked in time; synchronous.
+OLB_API int olb_voice_process_host(olb_voice *h, float *out_host, float *bus_host, uint32_t bus_channels, int accumulate, float bus_gain,
+                                   uint64_t frames) {
+    OLB_ARG(h, "olb_voice_process_host: NULL handle");
+    if (frames == 0) return OLB_OK;
+    OLB_ARG(out_host || bus_host, "olb_voice_process_host: no output buffer given");
+    OLB_ARG(!bus_host || (bus_channels >= 1 && bus_channels <= 8), "olb_voice_process_host: bus_channels must be 1..8");
+    DeviceGuard g(h->device);
+    const uint64_t V = h->V, chunk = host_chunk_frames(V, frames);
+    int rc = OLB_OK;
+    if (out_host && (rc = h->host.ensure(0, chunk * V))) return rc;
+    if (bus_host && (rc = h->host.ensure(1, chunk * bus_channels))) return rc;
+    if (!h->host.st && (rc = h->host.ensure(2, 1))) return rc;
+    for (uint64_t t0 = 0; t0 < frames; t0 += chunk) {
+        const uint64_t n = frames - t0 < chunk ? frames - t0 : chunk;
+        if (bus_host && accumulate)
+            OLB_CUDA(cudaMemcpyAsync(h->host.d[1], bus_host + t0 * bus_channels, n * bus_channels * sizeof(float), cudaMemcpyHostToDevice, h->host.st));
+        rc = olb_voice_process(h, out_host ? h->host.d[0] : nullptr, bus_host ? h->host.d[1] : nullptr, bus_channels, accumulate, bus_gain,
+                               nullptr, n, h->host.st);
+        if (rc) return rc;
+        if (out_host) OLB_CUDA(cudaMemcpyAsync(out_host + t0 * V, h->host.d[0], n * V * sizeof(float), cudaMemcpyDeviceToHost, h->host.st));
+        if (bus_host)
+            OLB_CUDA(cudaMemcpyAsync(bus_host + t0 * bus_channels, h->host.d[1], n * bus_channels * sizeof(float), cudaMemcpyDeviceToHost, h->host.st));
+    }
+    OLB_CUDA(cudaStreamSynchronize(h->host.st));
     return OLB_OK;
 }
