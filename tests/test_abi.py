@@ -71,6 +71,14 @@ def test_cpp_host_mirror_builds_and_fails_loudly_without_gpu(tmp_path):
     r = subprocess.run([exe, "8", "4", str(tmp_path / "in.f32"), str(tmp_path / "k.f32"), str(tmp_path / "out.f32"), "0"],
                        capture_output=True, text=True)
     assert r.returncode == 4 and "no CPU fallback" in r.stderr
+    # the fx / plate / chorus / voice mirrors (include/ol_gpu/{FxBank,DattorroBank,ChorusBank,VoiceBank}.hpp)
+    exe = os.path.join(g.ROOT, "tests", "cpp", "units_host")
+    assert os.path.exists(exe)
+    x.tofile(tmp_path / "in.f32")
+    for unit in ("rack", "plate", "chorus", "poly"):
+        r = subprocess.run([exe, unit, "8", "4", str(tmp_path / "in.f32"), str(tmp_path / "out.f32"), str(tmp_path / "out2.f32")],
+                           capture_output=True, text=True)
+        assert r.returncode == 4 and "no CPU fallback" in r.stderr, (unit, r.returncode, r.stderr)
 
 
 def test_product_never_touches_the_oracle():

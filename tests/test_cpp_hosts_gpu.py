@@ -1,0 +1,68 @@
+"""C++ callers written against include/ol_gpu/*.hpp (the reference-style host mirrors: Init -> setters -> Process per frame
+-> ProcessBlock, host buffers) run on the GPU box and compared with the oracle."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+from oracle import loader
+
+pytestmark = pytest.mark.gpu
+NAN = float("nan")
+
+
+def bits(a):
+    return np.ascontiguousarray(a, dtype=np.float32).view(np.uint32)
+
+
+def run(unit, I, T, x, tmp_path, two=False):
+    import __graft_entry__ as g
+    g.build_cpp_hosts()
+    exe = os.path.join(g.ROOT, "tests", "cpp", "units_host")
+    if x is not None:
+        x.tofile(tmp_path / "in.f32")
+    args = [exe, unit, str(I), str(T), str(tmp_path / "in.f32"), str(tmp_path / "out.f32")] + ([str(tmp_path / "out2.f32")] if two else [])
+    r = subprocess.run(args, capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    return r.stdout
+
+
+@pytest.mark.parametrize("unit,name", [("filter", "filterfx"), ("delay", "delayfx"), ("reverb", "reverbfx"), ("rack", "fxrack")])
+def test_fx_mirrors(orc, tmp_path, unit, name):
+    I, T = 40, 700
+    x = orc.noise(51, 0, I, 0, T, 0.5)
+    run(unit, I, T, x, tmp_path)
+    y = np.fromfile(tmp_path / "out.f32", dtype=np.float32).reshape(T, I)
+    ev = [(0, loader.EV_HW_CC, 35, 0.3), (0, loader.EV_MIDI_CC, 41, 90)]
+    for i in (0, 7, 39):
+        want = getattr(orc, name)(np.ascontiguousarray(x[:, i:i + 1]), 48000.0, ev)
+        assert np.array_equal(bits(y[:, i]), bits(want[:, 0])), (unit, i)
+
+
+def test_plate_mirror(orc, tmp_path):
+    I, T = 12, 900
+    x = orc.noise(52, 0, I, 0, T, 0.3)
+    run("plate", I, T, x, tmp_path, two=True)
+    l = np.fromfile(tmp_path / "out.f32", dtype=np.float32).reshape(T, I)
+    r = np.fromfile(tmp_path / "out2.f32", dtype=np.float32).reshape(T, I)
+    wl, wr = orc.dattorro(x[:, 5], [0.05, NAN, NAN, NAN, 0.8, NAN, NAN])
+    assert np.array_equal(bits(l[:, 5]), bits(wl)) and np.array_equal(bits(r[:, 5]), bits(wr))
+
+
+def test_chorus_mirror(orc, tmp_path):
+    I, T = 16, 2000
+    x = orc.noise(53, 0, I, 0, T, 0.5)
+    run("chorus", I, T, x, tmp_path)
+    y = np.fromfile(tmp_path / "out.f32", dtype=np.float32).reshape(T, I)
+    assert np.array_equal(bits(y[:, 9]), bits(orc.chorus(x[:, 9], rate=0.7, depth=0.9)))
+
+
+def test_polyvoice_mirror(orc, tmp_path):
+    V, T = 4, 3000
+    out = run("poly", V, T, None, tmp_path)
+    y = np.fromfile(tmp_path / "out.f32", dtype=np.float32)
+    ev = [(0, loader.EV_NOTE_ON, 48, 100), (0, loader.EV_NOTE_ON, 55, 100), (T // 2, loader.EV_NOTE_OFF, 48, 0), (T // 2, loader.EV_NOTE_ON, 64, 100)]
+    want = orc.polyvoice(V, T, ev=ev)
+    assert np.abs(y - np.asarray(want).reshape(-1)).max() <= 4e-5
+    assert out.split()[:4] == ["64", "55", "0", "0"]  # NoteOff(48) frees voice 0, NoteOn(64) takes the first free voice
