@@ -14,9 +14,10 @@
 // Svf::SetFreq's sinf per sample: CUDA's sinf differs from glibc's by <= 2 ulp, so voice OUTPUT is a tolerance tier
 // (<= 1e-5 of full scale, tests/test_voice_gpu.py) while phase and envelope traces are compared bit for bit.
 //
-// Mixdown: xor-shuffle tree inside the warp (fixed order), one partial per WARP per frame written coalesced 32 frames
-// at a time, then k_bus_reduce sums the warp partials in warp order: deterministic run to run; differs from the
-// reference's sequential voice order by float re-association only (tolerance tier).
+// Mixdown: each warp parks 32 frames of its 32 voices in shared memory and adds them in voice order, one partial per
+// WARP per frame written coalesced 32 frames at a time; k_bus_reduce then sums the warp partials in warp order:
+// deterministic run to run; differs from the reference's one sequential sum over all voices only by where the
+// partial sums are cut (float re-association, tolerance tier).
 #include <vector>
 
 #include "common.cuh"
@@ -32,26 +33,21 @@ struct EnvCoef {
     float a_d0, a_target, d_d0, r_d0, sus;
 };
 
-// daisysp::Adsr::Process (segments idle 0 / attack 1 / decay 2 / release 4)
+// daisysp::Adsr::Process (segments idle 0 / attack 1 / decay 2 / release 4), branch-free: the segment picks (d0, target)
+// with selects, the one-pole step x += d0 * (target - x) is the same expression in every active segment, and the two
+// segment exits (attack overshoots 1 -> decay at 1; decay / release undershoot 0 -> idle at 0) are selects as well.
+// 32 voices of a warp are rarely in the same segment, so a branchy version runs every path anyway.
 __device__ __forceinline__ float env_tick(float &x, int &mode, int &prev_gate, int gate, const EnvCoef &k) {
-    float out = 0.0f;
-    if (gate && !prev_gate) mode = 1;
-    else if (!gate && prev_gate) mode = 4;
+    mode = (gate && !prev_gate) ? 1 : ((!gate && prev_gate) ? 4 : mode);
     prev_gate = gate;
-    float d0 = k.a_d0;
-    if (mode == 2) d0 = k.d_d0;
-    else if (mode == 4) d0 = k.r_d0;
-    const float target = mode == 2 ? k.sus : -0.01f;
-    if (mode == 1) {
-        x = __fadd_rn(x, __fmul_rn(d0, __fsub_rn(k.a_target, x)));
-        out = x;
-        if (out > 1.f) { x = out = 1.f; mode = 2; }
-    } else if (mode == 2 || mode == 4) {
-        x = __fadd_rn(x, __fmul_rn(d0, __fsub_rn(target, x)));
-        out = x;
-        if (out < 0.0f) { x = out = 0.f; mode = 0; }
-    }
-    return out;
+    const float d0 = mode == 2 ? k.d_d0 : (mode == 4 ? k.r_d0 : k.a_d0);
+    const float target = mode == 1 ? k.a_target : (mode == 2 ? k.sus : -0.01f);
+    const float step = __fadd_rn(x, __fmul_rn(d0, __fsub_rn(target, x)));
+    const bool active = mode != 0, attack = mode == 1;
+    const bool over = attack && step > 1.f, under = active && !attack && step < 0.0f;
+    x = active ? (over ? 1.f : (under ? 0.f : step)) : x;
+    mode = over ? 2 : (under ? 0 : mode);
+    return active ? x : 0.0f;
 }
 
 __device__ __forceinline__ float polyblep(float dt, float t) {
@@ -64,6 +60,17 @@ __device__ __forceinline__ float polyblep(float dt, float t) {
         return __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(t, t), t), t), 1.0f);
     }
     return 0.0f;
+}
+
+// sin(x) for 0 <= x <= pi/4, the only range Svf::SetFreq can ask for (its argument is pi * min(0.25, fc / (2 sr))):
+// odd Taylor polynomial to x^9 in Horner form with FMAs; truncation error x^11 / 11! <= 1.8e-9, i.e. below half an ulp of
+// the result, so it is as close to glibc's sinf (the oracle's) as CUDA's own sinf is, at 6 instructions instead of ~25.
+__device__ __forceinline__ float sin_quarter(float x) {
+    const float x2 = __fmul_rn(x, x);
+    float p = __fmaf_rn(x2, 2.75573192e-6f, -1.98412698e-4f);
+    p = __fmaf_rn(x2, p, 8.33333333e-3f);
+    p = __fmaf_rn(x2, p, -1.66666667e-1f);
+    return __fmaf_rn(__fmul_rn(x, x2), p, x);
 }
 
 // trace (optional): 4 floats per voice-frame = oscillator output, amp envelope, filter envelope, phase after the tick
@@ -88,9 +95,12 @@ __global__ void __launch_bounds__(128) k_voice(float *out, float *partial, float
         a_mode = 1; a_x = 0.f;
         f_mode = 1; f_x = 0.f;
     }
-    const int lane = threadIdx.x & 31;
+    __shared__ float ytile[4][32][33];
+    // Svf::SetFreq runs every sample and its result is a tolerance tier already (device sine): its two divisions are a
+    // multiplication by 1 / (2 sr) and a fast division (<= 2 ulp each)
+    const float inv_sr2 = __frcp_rn(sr2);
+    const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
     const uint32_t warp_global = v >> 5;
-    float acc = 0.f;  // this lane's frame of the current 32-frame group of warp sums
 
     for (uint32_t n = 0; n < frames; n++) {
         const float amp_env = env_tick(a_x, a_mode, a_gate, gate, ka);
@@ -108,8 +118,8 @@ __global__ void __launch_bounds__(128) k_voice(float *out, float *partial, float
         const float ff = __fadd_rn(cutoff, __fmul_rn(__fmul_rn(fenv, 20000.f), f_amount));
         // Svf::SetFreq every sample
         const float fc = fminf(fmaxf(ff, 1.0e-6f), fc_max);
-        const float sfreq = __fmul_rn(2.0f, sinf(__fmul_rn(3.1415927410125732421875f, fminf(0.25f, __fdiv_rn(fc, sr2)))));
-        const float damp = fminf(damp_a, fminf(2.0f, __fsub_rn(__fdiv_rn(2.0f, sfreq), __fmul_rn(sfreq, 0.5f))));
+        const float sfreq = __fmul_rn(2.0f, sin_quarter(__fmul_rn(3.1415927410125732421875f, fminf(0.25f, __fmul_rn(fc, inv_sr2)))));
+        const float damp = fminf(damp_a, fminf(2.0f, __fsub_rn(__fdividef(2.0f, sfreq), __fmul_rn(sfreq, 0.5f))));
         // Svf::Process, two passes, low output
         float notch = __fsub_rn(frame, __fmul_rn(damp, band));
         low = __fadd_rn(low, __fmul_rn(sfreq, band));
@@ -128,13 +138,19 @@ __global__ void __launch_bounds__(128) k_voice(float *out, float *partial, float
             reinterpret_cast<float4 *>(trace)[(size_t) n * V + v] = t4;
         }
         if (partial) {
-            float s = live ? y : 0.f;
-#pragma unroll
-            for (int m = 16; m >= 1; m >>= 1) s = __fadd_rn(s, __shfl_xor_sync(0xffffffffu, s, m));
-            if ((int) (n & 31u) == lane) acc = s;
+            // warp mixdown without a per-frame shuffle chain: 32 frames of the warp's 32 voices are parked in shared memory,
+            // then lane f adds frame f's voices in voice order (rows are padded to 33 floats: both sweeps are conflict-free)
+            ytile[wic][n & 31u][lane] = live ? y : 0.f;
             if ((n & 31u) == 31u || n + 1 == frames) {
+                __syncwarp();
                 const uint32_t n0 = n & ~31u;
-                if (n0 + lane <= n) partial[(size_t) warp_global * partial_ld + n0 + lane] = acc;
+                if (n0 + lane <= n) {
+                    float s = 0.f;
+#pragma unroll
+                    for (int j = 0; j < 32; j++) s = __fadd_rn(s, ytile[wic][lane][j]);
+                    partial[(size_t) warp_global * partial_ld + n0 + lane] = s;
+                }
+                __syncwarp();
             }
         }
     }
