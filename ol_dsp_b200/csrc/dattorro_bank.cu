@@ -257,6 +257,165 @@ __global__ void __launch_bounds__(kPfThreads) k_dattorro_pf(const float *__restr
     lp[2 * (size_t) I + inst] = z_b;
 }
 
+// ------------------------------------------------------------------------------------------------
+// k_dattorro_rp: k_dattorro_pf with the ring addressing taken out of the frame loop.  ncu on k_dattorro_pf: 531 warp
+// instructions per frame, 72 % of them index and address arithmetic (LEA / IADD / IMAD / LOP / constant loads) for 41 ring
+// accesses that each recompute (t + offset) & mask, + base, * instances, + lane.  Every index but the per-instance
+// pre-delay tap is warp-uniform and advances by one per frame, so time is cut into BLOCKS inside which no ring index
+// wraps and no excursion step falls (<= 64 frames; the smallest ring has 128 slots): per block one pointer per access
+// is set up, per frame an access is one IMAD.WIDE (frame-in-block x row stride + pointer) and the memory instruction.
+// Same reads, same arithmetic, same writes as k_dattorro_pf: bit-exact.
+struct PlateTap {
+    int ring;
+    int kind;  // 0: main tap, offset g.off[ring]; 1 / 2: main tap with the excursion offset a / b; 3: output tap (reads at t + 1)
+    int off;   // kind 3: index into tap_l (0..6) / tap_r (7..13)
+};
+
+template <int D>
+__global__ void __launch_bounds__(kPfThreads) k_dattorro_rp(const float *__restrict__ in, float *__restrict__ out_l, float *__restrict__ out_r,
+                                                            uint32_t frames, uint32_t I, float *slab, float *lp, const float *__restrict__ par,
+                                                            const __grid_constant__ PlateGeom g0, uint32_t t0) {
+    extern __shared__ float pf[];  // [D][kPfSlots][kPfThreads]
+    const uint32_t inst = blockIdx.x * blockDim.x + threadIdx.x;
+    if (inst >= I) return;
+    float *mine = pf + threadIdx.x;
+    auto SLOT = [&](uint32_t d, int k) -> float * { return mine + ((size_t) d * kPfSlots + k) * kPfThreads; };
+    const float pre_filter = par[0 * (size_t) I + inst], in_diff1 = par[1 * (size_t) I + inst], in_diff2 = par[2 * (size_t) I + inst];
+    const float decay_diff1 = par[3 * (size_t) I + inst], damping = par[4 * (size_t) I + inst], decay = par[5 * (size_t) I + inst];
+    const float decay_diff2 = par[6 * (size_t) I + inst];
+    const uint32_t pre_off = __float_as_uint(par[7 * (size_t) I + inst]);
+    float z_pre = lp[inst], z_a = lp[(size_t) I + inst], z_b = lp[2 * (size_t) I + inst];
+    const uint32_t pre_len = (g0.mask[DV_PRE] + 1 - pre_off) & g0.mask[DV_PRE];  // pre-delay in samples
+    const bool pre_same = pre_len == 0, pre_direct = pre_len <= (uint32_t) D;    // too short to fetch D samples ahead
+    const uint32_t stride = I * (uint32_t) sizeof(float);                        // bytes from one ring position / frame to the next
+    char *lane_slab = reinterpret_cast<char *>(slab + inst);
+    const char *lane_in = reinterpret_cast<const char *>(in + inst);
+    char *lane_l = reinterpret_cast<char *>(out_l + inst), *lane_r = reinterpret_cast<char *>(out_r + inst);
+    auto at = [&](uint32_t ring, uint32_t idx) -> char * { return lane_slab + (uint64_t) (g0.base[ring] + idx) * stride; };
+    auto row = [&](char *p, uint32_t r) -> float * { return reinterpret_cast<float *>(p + (uint64_t) r * stride); };
+
+    // the 12 warp-uniform main taps in slot order 1..12, then the 14 output taps in slot order 13..26 (slot 0 = pre-delay
+    // tap, per lane; slot 27 = the input sample)
+    constexpr int kMain[12][2] = {{DV_IN0, 0}, {DV_IN1, 0}, {DV_IN2, 0}, {DV_IN3, 0}, {DV_POSTB, 0}, {DV_POSTA, 0}, {DV_DD1A, 1}, {DV_DD1B, 2},
+                                  {DV_PDA, 0}, {DV_PDB, 0}, {DV_DD2A, 0}, {DV_DD2B, 0}};
+    uint32_t t = t0, ta = t0, off_a = g0.off[DV_DD1A], off_b = g0.off[DV_DD1B];  // ta / off_*: state of the FETCH stream
+
+    // prologue: the first D frames are fetched with plain per-frame index arithmetic
+    for (uint32_t d = 0; d < (uint32_t) D; d++) {
+        if (d < frames) {
+            excursion_step(ta, off_a, off_b);
+            cp_async4(SLOT(d, 27), in + (size_t) d * I + inst);
+            cp_async4(SLOT(d, 0), row(at(DV_PRE, (ta + pre_off) & g0.mask[DV_PRE]), 0));
+#pragma unroll
+            for (int k = 0; k < 12; k++) {
+                const uint32_t off = kMain[k][1] == 1 ? off_a : (kMain[k][1] == 2 ? off_b : g0.off[kMain[k][0]]);
+                cp_async4(SLOT(d, 1 + k), row(at(kMain[k][0], (ta + off) & g0.mask[kMain[k][0]]), 0));
+            }
+            const uint32_t t1 = (ta + 1) & 0xffffu;
+#pragma unroll
+            for (int i = 0; i < 7; i++) {
+                cp_async4(SLOT(d, 13 + i), row(at(g0.tap_l[i][0], (t1 + g0.tap_l[i][1]) & g0.mask[g0.tap_l[i][0]]), 0));
+                cp_async4(SLOT(d, 20 + i), row(at(g0.tap_r[i][0], (t1 + g0.tap_r[i][1]) & g0.mask[g0.tap_r[i][0]]), 0));
+            }
+            ta = t1;
+        }
+        cp_async_commit();
+    }
+
+    constexpr int kTapRingL[7] = {DV_PDB, DV_PDB, DV_DD2B, DV_POSTB, DV_PDA, DV_DD2A, DV_POSTA};  // = kTapL[i][0]
+    constexpr int kTapRingR[7] = {DV_PDA, DV_PDA, DV_DD2A, DV_POSTA, DV_PDB, DV_DD2B, DV_POSTB};  // = kTapR[i][0]
+    uint32_t slot = 0;
+    for (uint32_t n = 0; n < frames;) {
+        // ---- block set-up, all warp-uniform: B frames during which no ring index wraps and no excursion step falls.
+        // ta is the counter of frame n + D (the one fetched while frame n is computed).
+        uint32_t B = min(frames - n, 64u);
+        {
+            const uint32_t e = ta & 0x7ffu;
+            B = min(B, e ? 0x800u - e : 0x800u);
+        }
+        excursion_step(ta, off_a, off_b);  // acts only when (ta & 0x7ff) == 0, which can only be a block's first frame
+        char *wp[DV_RINGS], *rp[12], *opl[7], *opr[7];
+#pragma unroll
+        for (int ring = 0; ring < DV_RINGS; ring++) {
+            const uint32_t idx = t & g0.mask[ring];
+            B = min(B, g0.mask[ring] + 1 - idx);
+            wp[ring] = at(ring, idx);
+        }
+#pragma unroll
+        for (int k = 0; k < 12; k++) {
+            const int ring = kMain[k][0];
+            const uint32_t off = kMain[k][1] == 1 ? off_a : (kMain[k][1] == 2 ? off_b : g0.off[ring]);
+            const uint32_t idx = (ta + off) & g0.mask[ring];
+            B = min(B, g0.mask[ring] + 1 - idx);
+            rp[k] = at(ring, idx);
+        }
+#pragma unroll
+        for (int i = 0; i < 7; i++) {
+            const uint32_t il = (ta + 1 + g0.tap_l[i][1]) & g0.mask[kTapRingL[i]], ir = (ta + 1 + g0.tap_r[i][1]) & g0.mask[kTapRingR[i]];
+            B = min(B, min(g0.mask[kTapRingL[i]] + 1 - il, g0.mask[kTapRingR[i]] + 1 - ir));
+            opl[i] = at(kTapRingL[i], il);
+            opr[i] = at(kTapRingR[i], ir);
+        }
+        // ---- the frames of the block ----
+        for (uint32_t r = 0; r < B; r++) {
+            cp_async_wait<D - 1>();
+            float v[kPfSlots];
+#pragma unroll
+            for (int k = 0; k < kPfSlots; k++) v[k] = *SLOT(slot, k);
+            if (n + r + D < frames) {
+                cp_async4(SLOT(slot, 27), reinterpret_cast<const float *>(lane_in + (uint64_t) (n + r + D) * stride));
+                cp_async4(SLOT(slot, 0), row(at(DV_PRE, (ta + r + pre_off) & g0.mask[DV_PRE]), 0));
+#pragma unroll
+                for (int k = 0; k < 12; k++) cp_async4(SLOT(slot, 1 + k), row(rp[k], r));
+#pragma unroll
+                for (int i = 0; i < 7; i++) {
+                    cp_async4(SLOT(slot, 13 + i), row(opl[i], r));
+                    cp_async4(SLOT(slot, 20 + i), row(opr[i], r));
+                }
+            }
+            cp_async_commit();
+            const float xin = v[27];
+            float r_pre = v[0];
+            if (pre_direct) r_pre = pre_same ? xin : *row(at(DV_PRE, (t + r + pre_off) & g0.mask[DV_PRE]), 0);
+            float w;
+            *row(wp[DV_PRE], r) = xin;
+            float x = lowpass(z_pre, pre_filter, r_pre);
+            x = allpass(v[1], in_diff1, x, w); *row(wp[DV_IN0], r) = w;
+            x = allpass(v[2], in_diff1, x, w); *row(wp[DV_IN1], r) = w;
+            x = allpass(v[3], in_diff2, x, w); *row(wp[DV_IN2], r) = w;
+            x = allpass(v[4], in_diff2, x, w); *row(wp[DV_IN3], r) = w;
+            float y = __fadd_rn(x, __fmul_rn(v[5], decay));
+            y = allpass(v[7], -decay_diff1, y, w); *row(wp[DV_DD1A], r) = w;
+            *row(wp[DV_PDA], r) = y; y = v[9];
+            y = lowpass(z_a, damping, y);
+            y = __fmul_rn(y, decay);
+            y = allpass(v[11], decay_diff2, y, w); *row(wp[DV_DD2A], r) = w;
+            *row(wp[DV_POSTA], r) = y;
+            y = __fadd_rn(x, __fmul_rn(v[6], decay));
+            y = allpass(v[8], -decay_diff1, y, w); *row(wp[DV_DD1B], r) = w;
+            *row(wp[DV_PDB], r) = y; y = v[10];
+            y = lowpass(z_b, damping, y);
+            y = __fmul_rn(y, decay);
+            y = allpass(v[12], decay_diff2, y, w); *row(wp[DV_DD2B], r) = w;
+            *row(wp[DV_POSTB], r) = y;
+            float a = __fadd_rn(v[13], v[14]); a = __fsub_rn(a, v[15]); a = __fadd_rn(a, v[16]);
+            a = __fsub_rn(a, v[17]); a = __fsub_rn(a, v[18]); a = __fadd_rn(a, v[19]);
+            float b = __fadd_rn(v[20], v[21]); b = __fsub_rn(b, v[22]); b = __fadd_rn(b, v[23]);
+            b = __fsub_rn(b, v[24]); b = __fsub_rn(b, v[25]); b = __fadd_rn(b, v[26]);
+            *row(lane_l, n + r) = a;
+            *row(lane_r, n + r) = b;
+            slot = slot + 1 == (uint32_t) D ? 0 : slot + 1;
+        }
+        n += B;
+        t = (t + B) & 0xffffu;
+        ta = (ta + B) & 0xffffu;
+    }
+    cp_async_wait<0>();
+    lp[inst] = z_pre;
+    lp[(size_t) I + inst] = z_a;
+    lp[2 * (size_t) I + inst] = z_b;
+}
+
 }  // namespace olb
 
 using namespace olb;
@@ -411,14 +570,14 @@ OLB_API int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *ou
         OLB_CUDA(cudaStreamSynchronize(st));  // par_host may change right after we return
         h->par_dirty = false;
     }
-    // OLB_PLATE_KERNEL=simple selects the one-frame-at-a-time kernel; OLB_PLATE_LANES=32|16|8 overrides the active lanes per
-    // warp of the pipelined one (default 32: narrower warps measured no faster, profiles/r01_run14_units_lane_sweep.jsonl)
+    // OLB_PLATE_KERNEL=simple|pf selects the one-frame-at-a-time / the index-arithmetic pipelined kernel (default: k_dattorro_rp);
+    // OLB_PLATE_LANES=32|16|8 overrides the active lanes per warp of the pf one (default 32: narrower warps measured no faster, profiles/r01_run14_units_lane_sweep.jsonl)
     const char *ek = getenv("OLB_PLATE_KERNEL"), *el = getenv("OLB_PLATE_LANES");
     const int forced = el ? atoi(el) : 0;
     const int lanes = (forced == 32 || forced == 16 || forced == 8) ? forced : 32;
     if (ek && !strcmp(ek, "simple")) {
         k_dattorro<<<(h->I + 63) / 64, 64, 0, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I, h->d_slab, h->d_lp, h->d_par, h->geom, h->t);
-    } else {
+    } else if (ek && !strcmp(ek, "pf")) {
         constexpr int D = 8;
         const unsigned warps = (h->I + lanes - 1) / lanes, grid = (warps + kPfThreads / 32 - 1) / (kPfThreads / 32);
         const size_t smem = (size_t) D * kPfSlots * (kPfThreads / 32) * lanes * sizeof(float);
@@ -430,6 +589,13 @@ OLB_API int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *ou
     } while (0)
         if (lanes == 32) OLB_PLATE_GO(32); else if (lanes == 16) OLB_PLATE_GO(16); else OLB_PLATE_GO(8);
 #undef OLB_PLATE_GO
+    } else {  // default: block-wise ring pointers; row offsets are 32-bit (frame x instances x 4 bytes)
+        constexpr int D = 8;
+        OLB_ARG((uint64_t) frames * h->I * sizeof(float) < (1ull << 62), "olb_dattorro_process: block too large");
+        constexpr size_t smem = (size_t) D * kPfSlots * kPfThreads * sizeof(float);
+        OLB_CUDA(cudaFuncSetAttribute(k_dattorro_rp<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        k_dattorro_rp<D><<<(h->I + kPfThreads - 1) / kPfThreads, kPfThreads, smem, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I,
+                                                                                       h->d_slab, h->d_lp, h->d_par, h->geom, h->t);
     }
     OLB_LAUNCHED();
     // advance the shared counter and the excursion exactly as the kernel did

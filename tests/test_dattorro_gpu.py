@@ -113,15 +113,20 @@ def test_impulse_response_properties():
     b.close()
 
 
-@pytest.mark.parametrize("env", [{"OLB_PLATE_KERNEL": "simple"}, {"OLB_PLATE_LANES": "32"}, {"OLB_PLATE_LANES": "16"}, {"OLB_PLATE_LANES": "8"}])
+@pytest.mark.parametrize("env", [{}, {"OLB_PLATE_KERNEL": "simple"}] + [{"OLB_PLATE_KERNEL": "pf", "OLB_PLATE_LANES": l} for l in ("32", "16", "8")],
+                         ids=lambda e: "-".join(e.values()) or "default")
 def test_every_kernel_variant_is_bit_exact(orc, monkeypatch, env):
-    """The one-frame kernel and the pipelined kernel at 32 / 16 / 8 active lanes per warp compute the same bits."""
+    """The default kernel (block-wise ring pointers), the one-frame kernel and the index-arithmetic pipelined kernel at
+    32 / 16 / 8 active lanes per warp compute the same bits; chunks straddle the 2 048-frame excursion steps and the
+    16-bit counter wrap is crossed (a first chunk of 63 000 silent frames)."""
     for k, v in env.items():
         monkeypatch.setenv(k, v)
-    I, T = 77, 4500
+    I, T = 77, 69000
     x = orc.noise(6, 3, I, 0, T, 0.25)
+    x[:63000] = 0.0
+    x[100:140] = orc.noise(7, 3, I, 0, 40, 0.25)
     plist = [[(i % 9) / 8.0, NAN, NAN, NAN, 0.5 + 0.4 * (i % 16) / 16, NAN, NAN] for i in range(I)]
-    l, r = run_bank(x, plist, chunks=[2047, 3, T - 2050])
+    l, r = run_bank(x, plist, chunks=[2047, 3, 60950, 2500, T - 65500])
     for i in (0, 7, 8, 15, 16, 31, 32, 63, 64, 76):
         wl, wr = orc.dattorro(x[:, i], plist[i])
         assert np.array_equal(bits(l[:, i]), bits(wl)) and np.array_equal(bits(r[:, i]), bits(wr)), (env, i)
