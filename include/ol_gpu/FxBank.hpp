@@ -88,6 +88,8 @@ typedef FxBank<OLB_FX_FILTER> FilterFxBank;  // bank of ol::fx::FilterFx<1>   (F
 typedef FxBank<OLB_FX_DELAY> DelayFxBank;    // bank of ol::fx::DelayFx<1>    (Fx.h:170-268)
 typedef FxBank<OLB_FX_REVERB> ReverbFxBank;  // bank of ol::fx::ReverbFx<1>   (Fx.h:272-393)
 typedef FxBank<OLB_FX_RACK> FxRackBank;      // bank of ol::fx::FxRack<1>     (Fx.h:397-493)
+// FxRack<1> with the Dattorro plate in the reverb slot (the wiring sketched in modules/fxlib/ReverbFx.cpp:11-37)
+typedef FxBank<OLB_FX_RACK_PLATE> FxRackPlateBank;
 
 }  // namespace gpu
 }  // namespace ol

@@ -130,6 +130,12 @@ int olb_biquad_set_variant(olb_biquad *h, int variant);
 #define OLB_FX_DELAY 1
 #define OLB_FX_REVERB 2
 #define OLB_FX_RACK 3
+/* FxRack<1> with the Dattorro plate of libs/dattorro-verb in the reverb slot instead of the stub ReverbSc -- the wiring the
+ * reference sketches in modules/fxlib/ReverbFx.cpp:11-37 (commented out there): mono in -> DattorroVerb_process ->
+ * getLeft as the wet signal of ReverbFx's dry/wet; PreFilter <- pre_cutoff, InputDiffusion1/2, Decay <- decay_time,
+ * DecayDiffusion from the ReverbFx members.  One deviation: Damping <- cutoff / 20 000 (the sketch passes the cutoff in
+ * Hz, which is outside the plate's 0..1 coefficient range). */
+#define OLB_FX_RACK_PLATE 4
 
 typedef struct olb_fx olb_fx;
 

@@ -512,6 +512,40 @@ __global__ void __launch_bounds__(32) k_fx_tma(const __grid_constant__ TensorMap
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// k_plate_tail: the back half of the plate rack (OLB_FX_RACK_PLATE): ReverbFx's dry/wet around the Dattorro plate's left
+// output (Fx.h:294-300 with the plate of libs/dattorro-verb substituted for the stub ReverbSc, the mapping the reference
+// sketches in modules/fxlib/ReverbFx.cpp:11-37), then FxRack's filter and master volume (Fx.h:426-434).  One instance
+// per thread, 8 frames of loads in flight.
+__global__ void __launch_bounds__(64) k_plate_tail(const float *wet, const float *dry, float *out, uint32_t frames, uint32_t I,
+                                                   const float *__restrict__ par, float *svf) {
+    constexpr int B = kFxB;
+    const uint32_t inst = blockIdx.x * blockDim.x + threadIdx.x;
+    if (inst >= I) return;
+    auto P = [&](int p) { return par[(size_t) p * I + inst]; };
+    const SvfCoef kf{P(P_F_FREQ), P(P_F_DAMP), P(P_F_DRIVE), (int) __float_as_uint(P(P_F_TYPE))};
+    const float r_balance = P(P_R_BALANCE), master = P(P_MASTER);
+    float f_low = svf[inst], f_band = svf[(size_t) I + inst];
+    for (uint32_t n0 = 0; n0 < frames; n0 += B) {
+        float w[B], d[B];
+#pragma unroll
+        for (int j = 0; j < B; j++)
+            if (n0 + j < frames) {
+                w[j] = wet[(size_t) (n0 + j) * I + inst];
+                d[j] = dry[(size_t) (n0 + j) * I + inst];
+            }
+#pragma unroll
+        for (int j = 0; j < B; j++)
+            if (n0 + j < frames) {
+                float v = dry_wet(w[j], d[j], r_balance);
+                v = svf_tick(v, f_low, f_band, kf);
+                out[(size_t) (n0 + j) * I + inst] = __fmul_rn(v, master);
+            }
+    }
+    svf[inst] = f_low;
+    svf[(size_t) I + inst] = f_band;
+}
+
 }  // namespace olb
 
 using namespace olb;
@@ -530,6 +564,11 @@ struct olb_fx {
     std::vector<float> stage;
     const char *last_kernel = "none";
     HostStage host;
+    // OLB_FX_RACK_PLATE: the Dattorro bank in the reverb slot and the buffers between the three stages
+    olb_dattorro *plate = nullptr;
+    bool plate_dirty = true;
+    float *d_mid[3] = {nullptr, nullptr, nullptr};  // delay output (dry), plate left, plate right
+    size_t mid_elems = 0;
 };
 
 static float bits_f(uint32_t u) {
@@ -560,7 +599,7 @@ static int fx_upload(olb_fx *h, cudaStream_t st) {
     return OLB_OK;
 }
 
-static bool fx_has_ring(int kind) { return kind == OLB_FX_DELAY || kind == OLB_FX_RACK; }
+static bool fx_has_ring(int kind) { return kind == OLB_FX_DELAY || kind == OLB_FX_RACK || kind == OLB_FX_RACK_PLATE; }
 
 // Init(sample_rate) of every instance (Fx.h:83-86, 183-192, 287-290, 416-424): state cleared, members kept.
 static int fx_init(olb_fx *h, float sr) {
@@ -577,6 +616,11 @@ static int fx_init(olb_fx *h, float sr) {
     if (h->d_ring) OLB_CUDA(cudaMemset(h->d_ring, 0, (size_t) h->I * kRing * sizeof(float)));
     h->wp = 0;
     h->dirty = true;
+    if (h->plate) {  // the plate has no sample-rate dependence (verb.cpp sizes its rings in samples); re-create = clear
+        int rc = olb_dattorro_init(h->plate);
+        if (rc) return rc;
+        h->plate_dirty = true;
+    }
     return OLB_OK;
 }
 
@@ -611,7 +655,7 @@ static int fx_launch_tma(olb_fx *h, const float *in, float *out, uint32_t frames
 OLB_API int olb_fx_create(int device, int kind, uint32_t instances, float sample_rate, olb_fx **out) {
     OLB_ARG(out, "olb_fx_create: out is NULL");
     *out = nullptr;
-    OLB_ARG(kind >= OLB_FX_FILTER && kind <= OLB_FX_RACK, "olb_fx_create: unknown kind %d", kind);
+    OLB_ARG(kind >= OLB_FX_FILTER && kind <= OLB_FX_RACK_PLATE, "olb_fx_create: unknown kind %d", kind);
     OLB_ARG(instances > 0, "olb_fx_create: instances must be > 0");
     int rc = require_sm100(device);
     if (rc) return rc;
@@ -629,10 +673,10 @@ OLB_API int olb_fx_create(int device, int kind, uint32_t instances, float sample
         delete h;
         return fail_cuda(e, "allocating fx bank", __FILE__, __LINE__);
     }
-    rc = fx_init(h, sample_rate);
+    rc = kind == OLB_FX_RACK_PLATE ? olb_dattorro_create(device, instances, &h->plate) : OLB_OK;
+    if (!rc) rc = fx_init(h, sample_rate);
     if (rc) {
-        cudaFree(h->d_par); cudaFree(h->d_svf); cudaFree(h->d_ring);
-        delete h;
+        olb_fx_destroy(h);
         return rc;
     }
     *out = h;
@@ -643,6 +687,8 @@ OLB_API int olb_fx_destroy(olb_fx *h) {
     if (!h) return OLB_OK;
     DeviceGuard g(h->device);
     cudaFree(h->d_par); cudaFree(h->d_svf); cudaFree(h->d_ring);
+    for (float *p : h->d_mid) cudaFree(p);
+    olb_dattorro_destroy(h->plate);
     h->host.release();
     delete h;
     return OLB_OK;
@@ -689,18 +735,58 @@ OLB_API int olb_fx_update_hw(olb_fx *h, uint32_t first, uint32_t count, uint8_t 
 
 OLB_API const char *olb_fx_last_kernel(olb_fx *h) { return h ? h->last_kernel : "none"; }
 
-OLB_API int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream) {
+// The plate rack's stages 2 and 3 (stage 1, the DelayFx kernel, has just written h->d_mid[0]).
+static int fx_plate_stages(olb_fx *h, float *out_dev, uint32_t frames, cudaStream_t st) {
+    if (h->plate_dirty) {  // ReverbFx members -> DattorroVerb setters (modules/fxlib/ReverbFx.cpp:29-37)
+        const uint32_t I = h->I;
+        std::vector<float> v(I);
+        auto push = [&](int param, float (*get)(const host::ReverbParams &)) {
+            for (uint32_t i = 0; i < I; i++) v[i] = get(h->units[i].reverb);
+            return olb_dattorro_set_params(h->plate, 0, I, param, v.data(), 1);
+        };
+        int rc = push(OLB_PLATE_PREFILTER, [](const host::ReverbParams &r) { return r.pre_cutoff; });
+        if (!rc) rc = push(OLB_PLATE_INPUT_DIFFUSION1, [](const host::ReverbParams &r) { return r.input_diffusion1; });
+        if (!rc) rc = push(OLB_PLATE_INPUT_DIFFUSION2, [](const host::ReverbParams &r) { return r.input_diffusion2; });
+        if (!rc) rc = push(OLB_PLATE_DECAY, [](const host::ReverbParams &r) { return r.decay_time; });
+        if (!rc) rc = push(OLB_PLATE_DAMPING, [](const host::ReverbParams &r) { return host::scale(r.cutoff, 0, 20000, 0, 1, 1); });
+        if (!rc) rc = push(OLB_PLATE_DECAY_DIFFUSION, [](const host::ReverbParams &r) { return r.decay_diffusion; });
+        if (rc) return rc;
+        h->plate_dirty = false;
+    }
+    int rc = olb_dattorro_process(h->plate, h->d_mid[0], h->d_mid[1], h->d_mid[2], frames, st);
+    if (rc) return rc;
+    k_plate_tail<<<(h->I + 63) / 64, 64, 0, st>>>(h->d_mid[1], h->d_mid[0], out_dev, frames, h->I, h->d_par, h->d_svf);
+    OLB_LAUNCHED();
+    return OLB_OK;
+}
+
+OLB_API int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev_arg, uint64_t frames, void *stream) {
     OLB_ARG(h, "olb_fx_process: NULL handle");
     if (frames == 0) return OLB_OK;
-    OLB_ARG(in_dev && out_dev, "olb_fx_process: NULL buffer");
+    OLB_ARG(in_dev && out_dev_arg, "olb_fx_process: NULL buffer");
     OLB_ARG(frames < (1ull << 32), "olb_fx_process: at most 2^32-1 frames per call");
     DeviceGuard g(h->device);
     cudaStream_t st = (cudaStream_t) stream;
     if (h->dirty) {
+        h->plate_dirty = true;
         int rc = fx_upload(h, st);
         if (rc) return rc;
     }
     const uint32_t F = (uint32_t) frames;
+    // the plate rack runs DelayFx -> Dattorro bank -> k_plate_tail through intermediate buffers that grow on demand
+    const bool plate = h->kind == OLB_FX_RACK_PLATE;
+    const int kind = plate ? OLB_FX_DELAY : h->kind;
+    if (plate && h->mid_elems < frames * h->I) {
+        OLB_CUDA(cudaStreamSynchronize(st));
+        for (float *&p : h->d_mid) {
+            cudaFree(p);
+            p = nullptr;
+        }
+        h->mid_elems = 0;
+        for (float *&p : h->d_mid) OLB_CUDA(cudaMalloc(&p, frames * h->I * sizeof(float)));
+        h->mid_elems = frames * h->I;
+    }
+    float *out_dev = plate ? h->d_mid[0] : out_dev_arg;
     // Kernel choice.  Default: k_fx_tma (needs instances % 4 == 0 and 16-byte aligned buffers for the tensor maps), else
     // k_fx_pf.  Tuning / test aid: OLB_FX_KERNEL=simple|pf|tma.
     const char *ek = getenv("OLB_FX_KERNEL");
@@ -709,7 +795,7 @@ OLB_API int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev, uint6
     const unsigned grid = (h->I + 63) / 64;
 #define OLB_FX_GO(KERNEL, KIND) KERNEL<KIND><<<grid, 64, 0, st>>>(in_dev, out_dev, F, h->I, h->d_par, h->d_svf, h->d_ring, h->wp)
 #define OLB_FX_KINDS(KERNEL)                                          \
-    switch (h->kind) {                                                \
+    switch (kind) {                                                   \
         case OLB_FX_FILTER: OLB_FX_GO(KERNEL, OLB_FX_FILTER); break;  \
         case OLB_FX_DELAY: OLB_FX_GO(KERNEL, OLB_FX_DELAY); break;    \
         case OLB_FX_REVERB: OLB_FX_GO(KERNEL, OLB_FX_REVERB); break;  \
@@ -723,7 +809,7 @@ OLB_API int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev, uint6
         h->last_kernel = "k_fx_pf";
     } else {
         int rc = OLB_OK;
-        switch (h->kind) {
+        switch (kind) {
             case OLB_FX_FILTER: rc = fx_launch_tma<OLB_FX_FILTER>(h, in_dev, out_dev, F, st); break;
             case OLB_FX_DELAY: rc = fx_launch_tma<OLB_FX_DELAY>(h, in_dev, out_dev, F, st); break;
             case OLB_FX_REVERB: rc = fx_launch_tma<OLB_FX_REVERB>(h, in_dev, out_dev, F, st); break;
@@ -736,6 +822,7 @@ OLB_API int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev, uint6
 #undef OLB_FX_GO
     OLB_LAUNCHED();
     if (fx_has_ring(h->kind)) h->wp = (uint32_t) ((h->wp + (uint64_t) kRing - frames % kRing) % kRing);
+    if (plate) return fx_plate_stages(h, out_dev_arg, F, st);
     return OLB_OK;
 }
 

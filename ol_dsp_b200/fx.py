@@ -8,7 +8,7 @@ import numpy as np
 from . import _lib
 from ._lib import check
 
-FILTER, DELAY, REVERB, RACK = range(4)
+FILTER, DELAY, REVERB, RACK, RACK_PLATE = range(5)
 
 
 class FxBank:
@@ -51,3 +51,4 @@ def FilterFx(instances, **kw): return FxBank(FILTER, instances, **kw)
 def DelayFx(instances, **kw): return FxBank(DELAY, instances, **kw)
 def ReverbFx(instances, **kw): return FxBank(REVERB, instances, **kw)
 def FxRack(instances, **kw): return FxBank(RACK, instances, **kw)
+def FxRackPlate(instances, **kw): return FxBank(RACK_PLATE, instances, **kw)

@@ -160,3 +160,45 @@ def test_default_kernel_is_the_tma_pipeline():
     torch.cuda.synchronize()
     assert b.LastKernel() == "k_fx_pf"
     b.close()
+
+
+def test_plate_rack_bank_with_reverb_controls(orc):
+    """OLB_FX_RACK_PLATE: FxRack<1> with the Dattorro plate in the reverb slot, the wiring
+    sketched in modules/fxlib/ReverbFx.cpp:11-37.  Per-instance reverb controls through the rack's hardware-control map
+    (Fx.h:353-391), ragged chunks, and a re-Init; checked against the composition DelayFx -> plate (left) in ReverbFx's
+    dry/wet -> FilterFx -> master volume of pieces that are each pinned on their own."""
+    NAN = float("nan")
+    I, T = 36, 2600
+    x = orc.noise(14, 0, I, 0, T, 0.5)
+    b = FxBank(fx.RACK_PLATE, I)
+    dec = (0.2 + 0.6 * np.arange(I) / I).astype(np.float32)
+    bal = (0.05 + 0.9 * np.arange(I) / I).astype(np.float32)
+    cut = (0.1 + 0.8 * ((np.arange(I) * 7) % I) / I).astype(np.float32)
+    b.UpdateHardwareControl(32, dec)   # CC_REVERB_TIME -> decay_time -> DattorroVerb_setDecay
+    b.UpdateHardwareControl(34, bal)   # CC_REVERB_BALANCE
+    b.UpdateHardwareControl(33, cut)   # CC_REVERB_CUTOFF -> cutoff (Hz) -> damping = cutoff / 20 000
+    b.UpdateHardwareControl(53, 0.7)   # CC_REVERB_PREFILTER
+    b.UpdateHardwareControl(7, 0.6)    # CC_CTL_VOLUME
+    dx = torch.from_numpy(x).cuda()
+    dy = torch.empty_like(dx)
+
+    def run():
+        a = 0
+        for n in (1, 999, 1600):
+            b.ProcessDevice(dx[a:].data_ptr(), dy[a:].data_ptr(), n)
+            a += n
+        torch.cuda.synchronize()
+        return dy.cpu().numpy()
+
+    y = run()
+    b.Init(48000.0)  # clears delay line, filters and plate; keeps every control
+    y2 = run()
+    assert np.array_equal(bits(y), bits(y2))
+    for i in (0, 1, 17, 35):
+        d = orc.delayfx(np.ascontiguousarray(x[:, i:i + 1]), 48000.0, [])[:, 0]
+        damping = orc.scale(orc.scale(float(cut[i]), 0.0, 1.0, 0.0, 20000.0, 1.0), 0.0, 20000.0, 0.0, 1.0, 1.0)
+        wl, _ = orc.dattorro(d, [NAN, 0.7, 0.5, 0.5, float(dec[i]), 0.5, damping])
+        mix = wl * bal[i] + d * (np.float32(1.0) - bal[i])
+        want = orc.filterfx(np.ascontiguousarray(mix.reshape(-1, 1)), 48000.0, [])[:, 0] * np.float32(0.6)
+        assert np.array_equal(bits(y[:, i]), bits(want)), i
+    b.close()
