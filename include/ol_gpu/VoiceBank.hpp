@@ -78,6 +78,13 @@ public:
         note(olb_voice_process(h_, out_dev, bus_dev, bus_channels, accumulate ? 1 : 0, bus_gain, nullptr, frames, stream));
     }
 
+    // Sample-accurate control: events (sorted by frame) are applied before the frame they name; voice < 0 routes notes
+    // through Polyvoice's allocation (olb_voice_process_events).  Device buffers.
+    void ProcessEvents(const olb_voice_event *events, uint32_t n_events, t_sample *out_dev, t_sample *bus_dev, uint32_t bus_channels,
+                       bool accumulate, t_sample bus_gain, uint64_t frames, void *stream = nullptr) {
+        note(olb_voice_process_events(h_, events, n_events, out_dev, bus_dev, bus_channels, accumulate ? 1 : 0, bus_gain, frames, stream));
+    }
+
     uint32_t Voices() const { return voices_; }
     int status() const { return status_; }
     std::string error() const { return olb_last_error(); }

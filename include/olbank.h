@@ -185,6 +185,22 @@ int olb_voice_set_frequency(olb_voice *h, uint32_t first, uint32_t count, const 
 int olb_voice_playing(olb_voice *h, uint32_t first, uint32_t count, uint8_t *playing_host);
 int olb_voice_process(olb_voice *h, float *out_dev, float *bus_dev, uint32_t bus_channels, int accumulate, float bus_gain,
                       float *trace_dev, uint64_t frames, void *stream);
+/* Sample-accurate control.  Events sorted by frame are applied BEFORE the frame they name; the
+ * block is cut there.  voice < 0: Polyvoice's allocation (NoteOn -> first voice not playing, NoteOff -> first voice playing
+ * that note: Polyvoice.h:35-51; CCs fan out to every voice: Polyvoice.h:53-63); voice >= 0: that voice (Voice.h:33-57). */
+#define OLB_EV_MIDI_CC 0  /* UpdateMidiControl(cc = a, value = (uint8) v) */
+#define OLB_EV_HW_CC 1    /* UpdateHardwareControl(cc = a, value = v) */
+#define OLB_EV_NOTE_ON 2  /* NoteOn(note = a, velocity = (uint8) v) */
+#define OLB_EV_NOTE_OFF 3 /* NoteOff(note = a, velocity = (uint8) v) */
+typedef struct olb_voice_event {
+    uint32_t frame;
+    uint32_t kind;
+    uint32_t a;
+    float v;
+    int32_t voice;
+} olb_voice_event;
+int olb_voice_process_events(olb_voice *h, const olb_voice_event *events, uint32_t n_events, float *out_dev, float *bus_dev,
+                             uint32_t bus_channels, int accumulate, float bus_gain, uint64_t frames, void *stream);
 /* Same with HOST buffers: out_host (optional) [frames][voices]; bus_host (optional) [frames][bus_channels], ADDED to when
  * accumulate != 0 (Polyvoice::Process adds into *frame_out: Polyvoice.h:28-33). */
 int olb_voice_process_host(olb_voice *h, float *out_host, float *bus_host, uint32_t bus_channels, int accumulate, float bus_gain,

@@ -73,6 +73,7 @@ def lib():
         "olb_fx_last_kernel": ([vp], C.c_char_p),
         "olb_fx_process_host": ([vp, vp, vp, u64], i32),
         "olb_voice_process_host": ([vp, vp, vp, u32, i32, f32, u64], i32),
+        "olb_voice_process_events": ([vp, vp, u32, vp, vp, u32, i32, f32, u64, vp], i32),
         "olb_dattorro_process_host": ([vp, vp, vp, vp, u64], i32),
         "olb_chorus_process_host": ([vp, vp, vp, u64], i32),
         "olb_voice_create": ([i32, u32, f32, C.POINTER(vp)], i32),

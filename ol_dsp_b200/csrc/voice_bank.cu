@@ -418,3 +418,64 @@ OLB_API int olb_voice_process_host(olb_voice *h, float *out_host, float *bus_hos
     OLB_CUDA(cudaStreamSynchronize(h->host.st));
     return OLB_OK;
 }
+
+// Sample-accurate control: `events` (sorted by frame) are applied BEFORE the frame they name, the block is cut there, and
+// the pieces run back to back on the stream -- what a host does by hand when it applies MIDI between audio blocks
+// (modules/juce/plugin/workout/src/PluginProcessor.cpp:24-38), at frame instead of block granularity.  Events with
+// voice < 0 go through Polyvoice's allocation (first voice that is not playing / first voice playing the note:
+// Polyvoice.h:35-51), events with voice >= 0 address that voice (the Voice interface, Voice.h:33-57).
+OLB_API int olb_voice_process_events(olb_voice *h, const olb_voice_event *events, uint32_t n_events, float *out_dev, float *bus_dev,
+                                     uint32_t bus_channels, int accumulate, float bus_gain, uint64_t frames, void *stream) {
+    OLB_ARG(h, "olb_voice_process_events: NULL handle");
+    OLB_ARG(n_events == 0 || events, "olb_voice_process_events: events is NULL");
+    for (uint32_t e = 0; e < n_events; e++) {
+        OLB_ARG(events[e].frame <= frames && (e == 0 || events[e].frame >= events[e - 1].frame),
+                "olb_voice_process_events: event %u is out of order or past the block", e);
+        OLB_ARG(events[e].voice < 0 || (uint32_t) events[e].voice < h->V, "olb_voice_process_events: event %u addresses voice %d of %u", e,
+                events[e].voice, h->V);
+    }
+    uint64_t pos = 0;
+    uint32_t e = 0;
+    while (pos < frames || e < n_events) {
+        for (; e < n_events && events[e].frame == pos; e++) {
+            const olb_voice_event &ev = events[e];
+            const uint8_t note = (uint8_t) ev.a;
+            int rc = OLB_OK;
+            int32_t voice = ev.voice;
+            switch (ev.kind) {
+                case OLB_EV_NOTE_ON:
+                    if (voice < 0)
+                        for (uint32_t v = 0; v < h->V && voice < 0; v++)
+                            if (!h->voices[v].playing) voice = (int32_t) v;
+                    if (voice >= 0) rc = olb_voice_note_on(h, (uint32_t) voice, 1, &note, 0, (uint8_t) ev.v);
+                    break;  // every voice busy: dropped, as in the reference
+                case OLB_EV_NOTE_OFF:
+                    if (voice < 0)
+                        for (uint32_t v = 0; v < h->V && voice < 0; v++)
+                            if (h->voices[v].playing == note) voice = (int32_t) v;
+                    if (voice >= 0) rc = olb_voice_note_off(h, (uint32_t) voice, 1);
+                    break;
+                case OLB_EV_MIDI_CC:
+                    rc = voice < 0 ? olb_voice_update_midi(h, 0, h->V, (uint8_t) ev.a, (uint8_t) ev.v)
+                                   : olb_voice_update_midi(h, (uint32_t) voice, 1, (uint8_t) ev.a, (uint8_t) ev.v);
+                    break;
+                case OLB_EV_HW_CC:
+                    rc = voice < 0 ? olb_voice_update_hw(h, 0, h->V, (uint8_t) ev.a, &ev.v, 0)
+                                   : olb_voice_update_hw(h, (uint32_t) voice, 1, (uint8_t) ev.a, &ev.v, 0);
+                    break;
+                default:
+                    set_error("olb_voice_process_events: unknown event kind %u", ev.kind);
+                    return OLB_E_ARG;
+            }
+            if (rc) return rc;
+        }
+        if (pos >= frames) break;
+        const uint64_t next = e < n_events ? events[e].frame : frames;
+        const uint64_t n = next - pos;
+        int rc = olb_voice_process(h, out_dev ? out_dev + pos * h->V : nullptr, bus_dev ? bus_dev + pos * bus_channels : nullptr, bus_channels,
+                                   accumulate, bus_gain, nullptr, n, stream);
+        if (rc) return rc;
+        pos = next;
+    }
+    return OLB_OK;
+}

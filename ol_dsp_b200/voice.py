@@ -85,6 +85,26 @@ class VoiceBank:
                                        float(bus_gain), C.c_void_p(trace_ptr), frames, C.c_void_p(stream)))
 
 
+class VoiceEvent(C.Structure):
+    """olb_voice_event (include/olbank.h)."""
+    _fields_ = [("frame", C.c_uint32), ("kind", C.c_uint32), ("a", C.c_uint32), ("v", C.c_float), ("voice", C.c_int32)]
+
+
+EV_MIDI_CC, EV_HW_CC, EV_NOTE_ON, EV_NOTE_OFF = range(4)
+
+
+def process_events(bank, events, frames, out_ptr=0, bus_ptr=0, bus_channels=1, accumulate=False, bus_gain=1.0, stream=0):
+    """Sample-accurate control: events = [(frame, kind, a, v[, voice])], applied before the frame they name (voice < 0 or
+    omitted: Polyvoice allocation)."""
+    ev = sorted(events, key=lambda e: e[0])
+    arr = (VoiceEvent * max(1, len(ev)))()
+    for i, e in enumerate(ev):
+        arr[i].frame, arr[i].kind, arr[i].a, arr[i].v = int(e[0]), int(e[1]), int(e[2]), float(e[3])
+        arr[i].voice = int(e[4]) if len(e) > 4 else -1
+    check(bank.L.olb_voice_process_events(bank.h, C.cast(arr, C.c_void_p), len(ev), C.c_void_p(out_ptr), C.c_void_p(bus_ptr), bus_channels,
+                                          int(bool(accumulate)), float(bus_gain), frames, C.c_void_p(stream)))
+
+
 class Polyvoice:
     """ol::synth::Polyvoice (Polyvoice.h:12-86) over a VoiceBank: NoteOn takes the first voice that is not playing,
     NoteOff releases the first voice playing that note, setters fan out to every voice, Process accumulates the voices

@@ -150,3 +150,24 @@ def test_wide_bank_bus_is_deterministic_and_equals_the_sum_of_voices():
     ref = out.double().sum(dim=1) / V
     assert float((bus[:, 0].double() - ref).abs().max()) <= 1e-6
     assert float(out.abs().max()) > 0.01 and torch.isfinite(out).all()
+
+
+def test_sample_accurate_event_list(orc):
+    """olb_voice_process_events: one call, the event list cuts the block at frame granularity
+    and routes notes through Polyvoice's first-free allocation; same golden as the hand-cut test above."""
+    from ol_dsp_b200.voice import process_events
+    g = np.load(os.path.join(G, "synth.npz"))
+    want = g["poly4"]
+    frames = want.shape[0]
+    ev = [(0, loader.EV_NOTE_ON, 48, 100), (5, loader.EV_NOTE_ON, 55, 100), (700, loader.EV_NOTE_ON, 64, 100),
+          (1500, loader.EV_NOTE_OFF, 55, 0), (1600, loader.EV_NOTE_ON, 67, 100), (2500, loader.EV_NOTE_OFF, 48, 0)]
+    assert (loader.EV_MIDI_CC, loader.EV_HW_CC, loader.EV_NOTE_ON, loader.EV_NOTE_OFF) == (0, 1, 2, 3)  # same codes as olbank.h
+    bank = VoiceBank(4)
+    bus = torch.zeros((frames, 1), dtype=torch.float32, device="cuda")
+    process_events(bank, ev, frames, bus_ptr=bus.data_ptr(), bus_channels=1, accumulate=True)
+    torch.cuda.synchronize()
+    assert np.abs(bus.cpu().numpy()[:, 0] - want).max() <= 4 * TOL
+    assert list(bank.Playing()) == [0, 67, 64, 0]
+    with pytest.raises(Exception):
+        process_events(bank, [(10, 2, 60, 100), (5, 2, 62, 100)][::-1] + [(frames + 1, 2, 60, 100)], frames, bus_ptr=bus.data_ptr())
+    bank.close()
