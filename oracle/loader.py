@@ -255,6 +255,16 @@ class Reference(_Fx):
         assert rc == 0
         return out
 
+    def control_wire(self, which, controller, value):
+        """The reference's own ol::ctl::Control + SimpleSerializer::SerializeControl: which 0 MIDI / 1 float / 2 ADC.
+        Returns (controller, adc, midi, float bits, wire bytes)."""
+        out = (C.c_uint32 * 4)()
+        wire = (C.c_uint8 * 64)()
+        self.lib.ref_control_wire.argtypes = [C.c_int, C.c_uint32, C.c_double, C.POINTER(C.c_uint32), C.POINTER(C.c_uint8)]
+        self.lib.ref_control_wire.restype = C.c_int
+        n = self.lib.ref_control_wire(which, controller, float(value), out, wire)
+        return out[0], out[1], out[2], out[3], bytes(wire[:n])
+
     def test_fx_delay(self):
         out = np.empty(48000, dtype=np.float32)
         return self.lib.ref_test_fx_delay(_fp(out)), out

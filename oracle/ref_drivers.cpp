@@ -25,6 +25,8 @@
 #include "daisysp.h"
 #include "fxlib/Fx.h"
 #include "synthlib/ol_synthlib.h"
+#include "ctllib/Control.h"
+#include "iolib/Serializer.h"
 #undef printf
 
 #include "oracle_abi.h"
@@ -339,6 +341,33 @@ int ref_test_synth_voice(float *frames4) {
     v->NoteOff(midi_note, velocity);
     delete v;
     return fail;
+}
+
+// ---- control wire format: the reference's own SimpleSerializer::SerializeControl
+// (modules/iolib/Serializer.h:113-133) and ol::ctl::Control conversions (modules/ctllib/Control.h:16-115) -------------
+struct RefNullSerial : public ol::io::Serial {
+    int Write(const char *, int size) override { return size; }
+    int Write(const uint8_t *, int size) override { return size; }
+    int Write(std::vector<uint8_t>, int size) override { return size; }
+};
+// which: 0 = Control(controller, MIDI value), 1 = Control(controller, float value), 2 = Control(controller, ADC value).
+// out4 = controller, adc, midi, float bits; wire (>= 64 bytes) receives SerializeControl's bytes; returns their count.
+int ref_control_wire(int which, uint32_t controller, double value, uint32_t *out4, uint8_t *wire) {
+    ol::ctl::Control c;
+    if (which == 0) c = ol::ctl::Control((ol::ctl::Control::CONTROLLER_TYPE) controller, (ol::ctl::Control::MIDI_TYPE) value);
+    else if (which == 1) c = ol::ctl::Control((ol::ctl::Control::CONTROLLER_TYPE) controller, (ol::ctl::Control::FLOAT_TYPE) value);
+    else c = ol::ctl::Control((ol::ctl::Control::CONTROLLER_TYPE) controller, (ol::ctl::Control::ADC_TYPE) value);
+    out4[0] = c.GetController();
+    out4[1] = c.GetAdcValue();
+    out4[2] = c.GetMidiValue();
+    const float f = c.GetFloatValue();
+    memcpy(&out4[3], &f, 4);
+    RefNullSerial serial;
+    ol::io::SimpleSerializer ser(serial);
+    std::vector<uint8_t> buf;
+    ser.SerializeControl(c, buf);
+    memcpy(wire, buf.data(), buf.size());
+    return (int) buf.size();
 }
 
 }  // extern "C"
