@@ -16,8 +16,8 @@
 //           so the 32 lanes' reads at 32 different delays never collide on a bank.  All instances tick together and
 //           share the write index.
 //   state   [3][instances]: LFO phase, lores~ y1, y2        par [7][instances]: inc d offset scale a1 a2 mix
-// One warp per CTA with its own TMA tile pipeline for the audio (the k_fx_tma pattern); ~183 KB of shared memory per
-// CTA, one CTA per SM.
+// One CTA = 32 instances = two warps: an audio warp with its own TMA tile pipeline (the k_fx_tma pattern) and an LFO warp
+// one tile ahead of it; ~216 KB of shared memory per CTA, one CTA per SM.
 #include <math.h>
 #include <stdlib.h>
 
@@ -49,16 +49,12 @@ struct ChorusLane {
 
 constexpr int kChB = 8;  // frames per batch; the ring carries kChB spare slots so a batch may write ahead of its reads
 
-// A batch of up to kChB frames of one instance, in three sweeps so that nothing but the two-op lores~ recurrence is
-// serial: (1) LFO phase -> table lookup -> delay for every frame, (2) all delay~ writes, then all reads (the ring has
-// kChB slots more than the longest delay reaches, so a frame's taps are never overwritten by the writes of the batch's
-// later frames; a tap at delay k < r of frame r reads what frame r-k just wrote, as in the frame-by-frame order),
-// (3) interpolate, filter, mix.  `wp` is the warp-uniform write index of the batch's first frame, wp + n <= R.
+// The chorus frame has two halves that share nothing but the delay they agree on: the LFO (phase -> table lookup -> delay
+// in samples: a pure function of the phase state, independent of the audio) and the audio path (delay~ write and
+// interpolated read, lores~, mix).  Each half is one long per-frame chain, so they run on TWO WARPS of the CTA, the LFO
+// warp one tile ahead, handing (whole samples k, fraction fr) over through shared memory.
 template <int N>
-__device__ __forceinline__ void chorus_batch(float *col, ChorusLane &c, float *ring_col, uint32_t wp, uint32_t R, float dmax, const float *tab,
-                                             uint32_t n) {
-    uint32_t k[N];
-    float fr[N], x[N], a[N], b[N];
+__device__ __forceinline__ void chorus_lfo_batch(ChorusLane &c, uint32_t *kq, float *frq, float dmax, const float *tab, uint32_t n) {
 #pragma unroll
     for (int r = 0; r < N; r++) {
         if ((uint32_t) r < n) {
@@ -73,10 +69,30 @@ __device__ __forceinline__ void chorus_batch(float *col, ChorusLane &c, float *r
             float dt = __fadd_rn(__fmul_rn(lfo, c.d), c.d);
             dt = dt < 0.0f ? 0.0f : dt;
             dt = dt > dmax ? dmax : dt;
-            k[r] = (uint32_t) __float2int_rz(dt);
-            fr[r] = __fsub_rn(dt, __uint2float_rn(k[r]));
+            const uint32_t k = (uint32_t) __float2int_rz(dt);
+            kq[r * kChL] = k;
+            frq[r * kChL] = __fsub_rn(dt, __uint2float_rn(k));
             const float ph = __fadd_rn(c.phase, c.inc);
             c.phase = ph >= 1.0f ? __fsub_rn(ph, 1.0f) : ph;
+        }
+    }
+}
+
+// A batch of up to kChB frames of the audio path, in three sweeps so that nothing but the two-op lores~ recurrence is
+// serial: (1) all delay~ writes, (2) all reads (the ring has kChB slots more than the longest delay reaches, so a frame's
+// taps are never overwritten by the writes of the batch's later frames; a tap at delay k < r of frame r reads what frame
+// r-k just wrote, as in the frame-by-frame order), (3) interpolate, filter, mix.  `wp` is the warp-uniform write index
+// of the batch's first frame, wp + n <= R.
+template <int N>
+__device__ __forceinline__ void chorus_audio_batch(float *col, ChorusLane &c, float *ring_col, uint32_t wp, uint32_t R, const uint32_t *kq,
+                                                   const float *frq, uint32_t n) {
+    uint32_t k[N];
+    float fr[N], x[N], a[N], b[N];
+#pragma unroll
+    for (int r = 0; r < N; r++) {
+        if ((uint32_t) r < n) {
+            k[r] = kq[r * kChL];
+            fr[r] = frq[r * kChL];
             x[r] = col[r * kChL];
             ring_col[(size_t) (wp + r) * kChL] = x[r];  // delay~ writes, then reads dt samples back
         }
@@ -105,29 +121,67 @@ __device__ __forceinline__ void chorus_batch(float *col, ChorusLane &c, float *r
     }
 }
 
+__device__ __forceinline__ void mbar_arrive_all(uint64_t *bar) { mbar_arrive(bar); }
+
 template <int TB, int STAGES, bool TMA>
-__global__ void __launch_bounds__(32) k_chorus(const __grid_constant__ TensorMap tm_in, const __grid_constant__ TensorMap tm_out,
+__global__ void __launch_bounds__(64) k_chorus(const __grid_constant__ TensorMap tm_in, const __grid_constant__ TensorMap tm_out,
                                                const float *in, float *out, uint32_t frames, uint32_t I, uint32_t R,
                                                const float *__restrict__ par, float *state, float *ring_all,
                                                const float *__restrict__ tab_g, uint32_t w0, float dmax) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     constexpr int L = kChL;
-    const uint32_t lane = threadIdx.x, i0 = blockIdx.x * L, inst = i0 + lane;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, i0 = blockIdx.x * L, inst = i0 + lane;
     const bool live = inst < I;
-    float *tiles = reinterpret_cast<float *>(smem_raw);          // [STAGES][TB][L]
-    float *ring = tiles + (size_t) STAGES * TB * L;              // [R][L]
+    float *tiles = reinterpret_cast<float *>(smem_raw);          // [STAGES][TB][L]   audio tiles (TMA)
+    uint32_t *kq = reinterpret_cast<uint32_t *>(tiles + (size_t) STAGES * TB * L);  // [2][TB][L]  whole samples of delay
+    float *frq = reinterpret_cast<float *>(kq + (size_t) 2 * TB * L);               // [2][TB][L]  fraction of delay
+    float *ring = frq + (size_t) 2 * TB * L;                     // [R][L]
     float *tab = ring + (size_t) R * L;                          // [513] (+3 pad)
     uint64_t *full = reinterpret_cast<uint64_t *>(tab + kChTab + 4);  // [STAGES] tile barriers, [STAGES] = ring barrier
+    uint64_t *lfo_full = full + STAGES + 1, *lfo_empty = lfo_full + 2;  // [2] each, 32 arrivals per phase
     const uint32_t ring_bytes = R * L * (uint32_t) sizeof(float);
     float *ring_g = ring_all + (size_t) blockIdx.x * R * L;
-    if (lane == 0) {
+    if (threadIdx.x == 0) {
 #pragma unroll
         for (int s = 0; s <= STAGES; s++) mbar_init(&full[s], 1);
+        for (int s = 0; s < 2; s++) {
+            mbar_init(&lfo_full[s], 32);
+            mbar_init(&lfo_empty[s], 32);
+        }
         mbar_fence_init();
     }
-    __syncwarp();
+    __syncthreads();
     constexpr uint32_t kTileBytes = TB * L * sizeof(float);
     const uint32_t ntiles = (frames + TB - 1) / TB;
+    const uint32_t ci = live ? inst : 0;
+    ChorusLane c;
+    c.inc = par[(size_t) CP_INC * I + ci]; c.d = par[(size_t) CP_D * I + ci]; c.offset = par[(size_t) CP_OFFSET * I + ci];
+    c.scale = par[(size_t) CP_SCALE * I + ci]; c.a1 = par[(size_t) CP_A1 * I + ci]; c.a2 = par[(size_t) CP_A2 * I + ci];
+    c.mix = par[(size_t) CP_MIX * I + ci];
+    c.phase = state[ci]; c.y1 = state[(size_t) I + ci]; c.y2 = state[2 * (size_t) I + ci];
+
+    if (warp == 1) {
+        // ---- LFO warp: one tile ahead of the audio warp (two hand-over buffers) ----
+        for (uint32_t j = lane; j <= (uint32_t) kChTab; j += 32) tab[j] = tab_g[j];
+        __syncwarp();
+        for (uint32_t i = 0; i < ntiles; i++) {
+            const uint32_t s = i & 1;
+            if (i >= 2) mbar_wait(&lfo_empty[s], ((i >> 1) - 1) & 1);
+            const uint32_t rows = min((uint32_t) TB, frames - i * TB);
+            uint32_t *kcol = kq + (size_t) s * TB * L + lane;
+            float *fcol = frq + (size_t) s * TB * L + lane;
+            if (live) {
+                uint32_t r = 0;
+                for (; r + kChB <= rows; r += kChB) chorus_lfo_batch<kChB>(c, kcol + r * L, fcol + r * L, dmax, tab, kChB);
+                if (r < rows) chorus_lfo_batch<kChB>(c, kcol + r * L, fcol + r * L, dmax, tab, rows - r);
+            }
+            mbar_arrive_all(&lfo_full[s]);
+        }
+        if (live) state[inst] = c.phase;
+        return;
+    }
+
+    // ---- audio warp ----
     if (lane == 0) {
         mbar_arrive_expect_tx(&full[STAGES], ring_bytes);
         bulk_load_1d(ring, ring_g, ring_bytes, &full[STAGES]);
@@ -138,38 +192,36 @@ __global__ void __launch_bounds__(32) k_chorus(const __grid_constant__ TensorMap
             }
         }
     }
-    for (uint32_t j = lane; j <= (uint32_t) kChTab; j += 32) tab[j] = tab_g[j];
-    const uint32_t ci = live ? inst : 0;
-    ChorusLane c;
-    c.inc = par[(size_t) CP_INC * I + ci]; c.d = par[(size_t) CP_D * I + ci]; c.offset = par[(size_t) CP_OFFSET * I + ci];
-    c.scale = par[(size_t) CP_SCALE * I + ci]; c.a1 = par[(size_t) CP_A1 * I + ci]; c.a2 = par[(size_t) CP_A2 * I + ci];
-    c.mix = par[(size_t) CP_MIX * I + ci];
-    c.phase = state[ci]; c.y1 = state[(size_t) I + ci]; c.y2 = state[2 * (size_t) I + ci];
     float *ring_col = ring + lane;
     uint32_t wp = w0;
     __syncwarp();
     mbar_wait(&full[STAGES], 0);
 
     for (uint32_t i = 0; i < ntiles; i++) {
-        const uint32_t st = TMA ? i % STAGES : 0, ph = (i / STAGES) & 1;
+        const uint32_t st = TMA ? i % STAGES : 0, ph = (i / STAGES) & 1, ls = i & 1;
         const uint32_t rows = min((uint32_t) TB, frames - i * TB);
         float *col = tiles + (size_t) st * TB * L + lane;
+        const uint32_t *kcol = kq + (size_t) ls * TB * L + lane;
+        const float *fcol = frq + (size_t) ls * TB * L + lane;
         if (TMA) {
             mbar_wait(&full[st], ph);
         } else if (live) {
             for (uint32_t r = 0; r < rows; r++) col[r * L] = in[(size_t) (i * TB + r) * I + inst];
         }
+        mbar_wait(&lfo_full[ls], (i >> 1) & 1);
         // the write index wraps at most once per tile: one or two straight segments
         for (uint32_t r0 = 0; r0 < rows;) {
             const uint32_t seg = min(rows - r0, R - wp);
             if (live) {
                 uint32_t r = 0;
-                for (; r + kChB <= seg; r += kChB) chorus_batch<kChB>(col + (r0 + r) * L, c, ring_col, wp + r, R, dmax, tab, kChB);
-                if (r < seg) chorus_batch<kChB>(col + (r0 + r) * L, c, ring_col, wp + r, R, dmax, tab, seg - r);
+                for (; r + kChB <= seg; r += kChB)
+                    chorus_audio_batch<kChB>(col + (r0 + r) * L, c, ring_col, wp + r, R, kcol + (r0 + r) * L, fcol + (r0 + r) * L, kChB);
+                if (r < seg) chorus_audio_batch<kChB>(col + (r0 + r) * L, c, ring_col, wp + r, R, kcol + (r0 + r) * L, fcol + (r0 + r) * L, seg - r);
             }
             r0 += seg;
             wp = wp + seg == R ? 0 : wp + seg;
         }
+        mbar_arrive_all(&lfo_empty[ls]);
         if (TMA) {
             fence_async_smem();
             __syncwarp();
@@ -196,7 +248,6 @@ __global__ void __launch_bounds__(32) k_chorus(const __grid_constant__ TensorMap
         tma_wait_all<0>();
     }
     if (live) {
-        state[inst] = c.phase;
         state[(size_t) I + inst] = c.y1;
         state[2 * (size_t) I + inst] = c.y2;
     }
@@ -223,8 +274,8 @@ struct olb_chorus {
 
 constexpr int kChTB = 64, kChStages = 4;
 static size_t chorus_smem(uint32_t R) {
-    return (size_t) kChStages * kChTB * kChL * sizeof(float) + (size_t) R * kChL * sizeof(float) + (kChTab + 4) * sizeof(float) +
-           (kChStages + 1) * sizeof(uint64_t);
+    return (size_t) kChStages * kChTB * kChL * sizeof(float) + (size_t) 4 * kChTB * kChL * sizeof(float) + (size_t) R * kChL * sizeof(float) +
+           (kChTab + 4) * sizeof(float) + (kChStages + 1 + 4) * sizeof(uint64_t);
 }
 // the specification's ring length (orc_chorus_ring_len: it only enters the arithmetic through the clamp dt <= len - 2) ...
 static uint32_t chorus_spec_len(float sr) { return (uint32_t) ceil(2.0 * 12.0 * (double) sr / 1000.0) + 4u; }
@@ -364,12 +415,12 @@ OLB_API int olb_chorus_process(olb_chorus *h, const float *in_dev, float *out_de
         if (rc) return rc;
         auto kern = k_chorus<kChTB, kChStages, true>;
         OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        kern<<<h->ctas, 32, smem, st>>>(tin, tout, in_dev, out_dev, (uint32_t) frames, h->I, h->R, h->d_par, h->d_state, h->d_ring, h->d_tab, h->w, (float) (chorus_spec_len(h->sample_rate) - 2));
+        kern<<<h->ctas, 64, smem, st>>>(tin, tout, in_dev, out_dev, (uint32_t) frames, h->I, h->R, h->d_par, h->d_state, h->d_ring, h->d_tab, h->w, (float) (chorus_spec_len(h->sample_rate) - 2));
         h->last_kernel = "k_chorus_tma";
     } else {
         auto kern = k_chorus<kChTB, kChStages, false>;
         OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        kern<<<h->ctas, 32, smem, st>>>(tin, tout, in_dev, out_dev, (uint32_t) frames, h->I, h->R, h->d_par, h->d_state, h->d_ring, h->d_tab, h->w, (float) (chorus_spec_len(h->sample_rate) - 2));
+        kern<<<h->ctas, 64, smem, st>>>(tin, tout, in_dev, out_dev, (uint32_t) frames, h->I, h->R, h->d_par, h->d_state, h->d_ring, h->d_tab, h->w, (float) (chorus_spec_len(h->sample_rate) - 2));
         h->last_kernel = "k_chorus_direct";
     }
     OLB_LAUNCHED();
