@@ -150,7 +150,7 @@ int olb_fx_update_midi(olb_fx *h, uint32_t first, uint32_t count, uint8_t contro
 int olb_fx_update_hw(olb_fx *h, uint32_t first, uint32_t count, uint8_t control, const float *values_host, uint32_t stride);
 /* Block form of "for each frame: Process(frame_in, frame_out)"; in_dev == out_dev allowed. */
 int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream);
-/* Diagnostics: which kernel the last process call launched ("k_fx_tma", "k_fx_pf", "k_fx"). */
+/* Diagnostics: which kernel the last process call launched ("k_fx_split", "k_fx_tma", "k_fx_pf", "k_fx"). */
 const char *olb_fx_last_kernel(olb_fx *h);
 /* Same with HOST buffers [frames][instances] (the reference's Process takes host frames: Fx.h:88,194,294,426); chunked
  * through device staging, returns when out_host is complete.  frames == 1 is the per-frame call. */

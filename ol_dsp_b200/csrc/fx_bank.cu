@@ -215,6 +215,59 @@ __device__ __forceinline__ void fx_batch(float *col, const float *tap, float *wc
     for (int r = 0; r < N; r++) col[r * kFxLanes] = KIND == OLB_FX_RACK ? __fmul_rn(v[r], master) : v[r];
 }
 
+// The ring kinds cut into pipeline stages for k_fx_split, one warp each (same operations, same order per value):
+//   io_batch    DelayLine::Read + Write: taps -> interpolated read `rd` (to the rd tile) and the value written back
+//   wet_batch   the wet filter, the delay's dry/wet mix and (rack) the reverb slot's mix, in place in the audio tile
+//   tail_batch  (rack) the main filter and the master volume, in place
+template <int N>
+__device__ __forceinline__ void io_batch(const float *col, const float *tap, float *wcol, int wstride, float *rdcol, float &prev_a, float frac,
+                                         float feedback) {
+    float x[N], ra[N];
+#pragma unroll
+    for (int r = 0; r < N; r++) x[r] = col[r * kFxLanes];
+#pragma unroll
+    for (int r = 0; r < N; r++) ra[r] = *(tap - r);
+#pragma unroll
+    for (int r = 0; r < N; r++) {
+        const float rb = r == 0 ? prev_a : ra[r - 1];
+        const float rd = __fadd_rn(ra[r], __fmul_rn(__fsub_rn(rb, ra[r]), frac));  // DelayLine::Read (Fx.h:198)
+        rdcol[r * kFxLanes] = rd;
+        wcol[r * wstride] = __fadd_rn(x[r], __fmul_rn(feedback, rd));              // Write(in + feedback * read) (Fx.h:199-200)
+    }
+    prev_a = ra[N - 1];
+}
+
+template <int N, bool RACK>
+__device__ __forceinline__ void wet_batch(float *col, const float *rdcol, float d_balance, float r_balance, float &w_low, float &w_band,
+                                          const SvfCoef &kw) {
+    float x[N], v[N];
+#pragma unroll
+    for (int r = 0; r < N; r++) x[r] = col[r * kFxLanes];
+#pragma unroll
+    for (int r = 0; r < N; r++) v[r] = rdcol[r * kFxLanes];
+#pragma unroll
+    for (int r = 0; r < N; r++) v[r] = svf_tick(v[r], w_low, w_band, kw);
+#pragma unroll
+    for (int r = 0; r < N; r++) v[r] = dry_wet(v[r], x[r], d_balance);                              // Fx.h:205-207
+    if (RACK) {
+#pragma unroll
+        for (int r = 0; r < N; r++) v[r] = dry_wet(__fmul_rn(v[r], 0.8f), v[r], r_balance);         // Fx.h:294-300, stub reverb
+    }
+#pragma unroll
+    for (int r = 0; r < N; r++) col[r * kFxLanes] = v[r];
+}
+
+template <int N>
+__device__ __forceinline__ void tail_batch(float *col, float master, float &f_low, float &f_band, const SvfCoef &kf) {
+    float v[N];
+#pragma unroll
+    for (int r = 0; r < N; r++) v[r] = col[r * kFxLanes];
+#pragma unroll
+    for (int r = 0; r < N; r++) v[r] = svf_tick(v[r], f_low, f_band, kf);                           // Fx.h:426-434
+#pragma unroll
+    for (int r = 0; r < N; r++) col[r * kFxLanes] = __fmul_rn(v[r], master);
+}
+
 // ------------------------------------------------------------------------------------------------
 // k_fx_pf: register double buffering -- the inputs (and, for the delay kinds, the ring reads) of frames n+B .. n+2B-1
 // are in flight while frames n .. n+B-1 run (in and out may alias, so the compiler will not hoist the loads itself).
@@ -513,6 +566,243 @@ __global__ void __launch_bounds__(32) k_fx_tma(const __grid_constant__ TensorMap
 }
 
 // ------------------------------------------------------------------------------------------------
+// k_fx_split: the ring kinds (DelayFx, FxRack) as a pipeline of warps inside one CTA of 32 instances.  In k_fx_tma one warp
+// issues everything a frame needs back to back: the ring traffic of the tile, the wet filter's 12-deep recurrence, the mixes
+// and (rack) the main filter's recurrence -- 132 (delay) and 196 (rack) cycles per frame against the 78 of one recurrence.
+// Nothing but the two filters is recurrent, and the second filter only consumes the first one's output, so the frame is
+// cut at those points and each piece gets its own warp, i.e. its own scheduler slot:
+//   warp 0  I/O     TMA tile of inputs + cp.async tap runs -> DelayLine::Read (to the rd tile), ring write-back
+//   warp 1  wet     wet filter, dry/wet mixes, in place in the audio tile          [delay: stores the tile]
+//   warp 2  tail    main filter, master volume, in place (rack only)               [rack: stores the tile]
+// Tiles move down the pipeline through shared memory with one 32-arrival mbarrier per stage and hand-over (`tapd`: I/O -> wet,
+// `mid`: wet -> tail); the last warp stores the tile by TMA and refills its stage, which is the only back-pressure needed
+// (a stage's `full` barrier cannot complete before the tile that used it STAGES tiles ago was stored).  Shared memory per
+// CTA at 64 x 4: audio 32 KB + taps 34 KB + write-back 8 KB + rd 32 KB = 106 KB, two CTAs per SM.
+template <int TB, int STAGES>
+__host__ __device__ constexpr size_t fx_split_smem_floats() {
+    return fx_tma_smem_floats<TB, STAGES>(true) + (size_t) STAGES * TB * kFxL;
+}
+
+//
+// G pipelines (32 instances each) share a CTA so that the kernel, not the block scheduler, decides which scheduler (SM
+// sub-partition = warp index mod 4) each warp lands on: two co-resident 3-warp CTAs double up on sub-partitions 0-2 and
+// ran 117 cycles per frame where one alone runs 82 (profiles/r01_run25_fx_split.jsonl).  G = 2: the two wet warps and
+// the two tail warps get a sub-partition each, the light I/O warps share with the tails (warps 4, 5 exit at once);
+// G = 4: pipeline p is warps p, p + 4, p + 8 -- all three of its stages on sub-partition p, 99 issue slots per frame each.
+constexpr int kFxIo = 0, kFxWet = 1, kFxTail = 2, kFxIdle = 3;
+template <int KIND, int G>
+__host__ __device__ constexpr int fx_split_warps() {
+    return G == 1 ? (KIND == OLB_FX_RACK ? 3 : 2) : G == 2 ? (KIND == OLB_FX_RACK ? 8 : 4) : (KIND == OLB_FX_RACK ? 12 : 8);
+}
+template <int TB, int STAGES>
+__host__ __device__ constexpr size_t fx_split_pipe_bytes() {  // one pipeline's tiles + barriers, rounded for TMA alignment
+    return (fx_split_smem_floats<TB, STAGES>() * sizeof(float) + (size_t) 3 * STAGES * sizeof(uint64_t) + 1023) & ~(size_t) 1023;
+}
+
+template <int KIND, int TB, int STAGES, int G>
+__global__ void __launch_bounds__(32 * fx_split_warps<KIND, G>()) k_fx_split(const __grid_constant__ TensorMap tm_in,
+                                                                              const __grid_constant__ TensorMap tm_out, uint32_t frames,
+                                                                              uint32_t I, const float *__restrict__ par, float *svf,
+                                                                              float *ring_all, uint32_t wp0) {
+    static_assert(KIND == OLB_FX_DELAY || KIND == OLB_FX_RACK, "ring kinds only");
+    static_assert(G == 1 || G == 2 || G == 4, "1, 2 or 4 pipelines per CTA");
+    constexpr bool kRack = KIND == OLB_FX_RACK;
+    constexpr int L = kFxL, RS = TB + 4, WS = L;
+    extern __shared__ __align__(1024) unsigned char smem_all[];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t pipe, role;
+    if (G == 1) {
+        pipe = 0;
+        role = warp;  // io, wet, tail
+    } else if (G == 2) {
+        pipe = warp & 1;
+        role = kRack ? (warp < 2 ? kFxWet : warp < 4 ? kFxTail : warp < 6 ? kFxIdle : kFxIo) : (warp < 2 ? kFxWet : kFxIo);
+    } else {
+        pipe = warp & 3;
+        role = warp >> 2;
+    }
+    unsigned char *smem_raw = smem_all + (size_t) pipe * fx_split_pipe_bytes<TB, STAGES>();
+    const uint32_t i0 = (blockIdx.x * G + pipe) * L, inst = i0 + lane;
+    const bool live = inst < I;
+    float *tiles = reinterpret_cast<float *>(smem_raw);                    // [STAGES][TB][L]  audio, in place
+    float *rtiles = tiles + (size_t) STAGES * TB * L;                      // [STAGES][L][RS]  delay-line taps
+    float *wtile = rtiles + (size_t) STAGES * L * RS;                      // [TB][WS]         values to write back
+    float *rdtiles = reinterpret_cast<float *>(smem_raw) + fx_tma_smem_floats<TB, STAGES>(true);  // [STAGES][TB][L] DelayLine::Read
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw + fx_split_smem_floats<TB, STAGES>() * sizeof(float));
+    uint64_t *tapd = full + STAGES, *mid = tapd + STAGES;
+    if (role == kFxIo && lane == 0) {
+#pragma unroll
+        for (int s = 0; s < STAGES; s++) {
+            mbar_init(&full[s], 1);
+            mbar_init(&tapd[s], 32);
+            mbar_init(&mid[s], 32);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (role == kFxIdle || i0 >= I) return;  // padding warps, and the pipelines past the end of the bank
+    constexpr uint32_t kTileBytes = TB * L * sizeof(float);
+    const uint32_t ntiles = (frames + TB - 1) / TB;
+    const uint32_t ci = live ? inst : 0;  // idle lanes read instance 0's parameters and never write
+    auto P = [&](int p) { return par[(size_t) p * I + ci]; };
+    // the last warp of the pipeline: store tile i, then refill the stage tile i-1 was stored from
+    auto store_and_refill = [&](uint32_t i, uint32_t st) {
+        fence_async_smem();
+        __syncwarp();
+        const uint32_t nxt = i + STAGES - 1;
+        if (lane == 0) {
+            tma_store_2d(&tm_out, (int) i0, (int) (i * TB), tiles + (size_t) st * TB * L);
+            tma_commit();
+            if (nxt < ntiles) {
+                tma_wait_read<1>();
+                const uint32_t ns = nxt % STAGES;
+                mbar_arrive_expect_tx(&full[ns], kTileBytes);
+                tma_load_2d(tiles + (size_t) ns * TB * L, &tm_in, (int) i0, (int) (nxt * TB), &full[ns]);
+            }
+        }
+    };
+
+    if (role == kFxTail) {  // ---- tail (rack): main filter + master volume
+        const SvfCoef kf{P(P_F_FREQ), P(P_F_DAMP), P(P_F_DRIVE), (int) __float_as_uint(P(P_F_TYPE))};
+        const float master = P(P_MASTER);
+        float f_low = svf[ci], f_band = svf[(size_t) I + ci];
+        for (uint32_t i = 0; i < ntiles; i++) {
+            const uint32_t st = i % STAGES, ph = (i / STAGES) & 1;
+            mbar_wait(&mid[st], ph);
+            const uint32_t rows = min((uint32_t) TB, frames - i * TB);
+            float *col = tiles + (size_t) st * TB * L + lane;
+            if (live) {
+                uint32_t r = 0;
+                for (; r + kFxBatch <= rows; r += kFxBatch) tail_batch<kFxBatch>(col + r * L, master, f_low, f_band, kf);
+                for (; r < rows; r++) tail_batch<1>(col + r * L, master, f_low, f_band, kf);
+            }
+            store_and_refill(i, st);
+        }
+        if (lane == 0) tma_wait_all<0>();
+        if (live) {
+            svf[inst] = f_low;
+            svf[(size_t) I + inst] = f_band;
+        }
+        return;
+    }
+    if (role == kFxWet) {  // ---- wet filter + mixes
+        const SvfCoef kw{P(P_W_FREQ), P(P_W_DAMP), P(P_W_DRIVE), (int) __float_as_uint(P(P_W_TYPE))};
+        const float d_balance = P(P_D_BALANCE), r_balance = P(P_R_BALANCE);
+        float w_low = svf[2 * (size_t) I + ci], w_band = svf[3 * (size_t) I + ci];
+        for (uint32_t i = 0; i < ntiles; i++) {
+            const uint32_t st = i % STAGES, ph = (i / STAGES) & 1;
+            mbar_wait(&full[st], ph);  // the inputs (async proxy) ...
+            mbar_wait(&tapd[st], ph);  // ... and warp 0's reads of the delay line
+            const uint32_t rows = min((uint32_t) TB, frames - i * TB);
+            float *col = tiles + (size_t) st * TB * L + lane;
+            const float *rdcol = rdtiles + (size_t) st * TB * L + lane;
+            if (live) {
+                uint32_t r = 0;
+                for (; r + kFxBatch <= rows; r += kFxBatch) wet_batch<kFxBatch, kRack>(col + r * L, rdcol + r * L, d_balance, r_balance, w_low, w_band, kw);
+                for (; r < rows; r++) wet_batch<1, kRack>(col + r * L, rdcol + r * L, d_balance, r_balance, w_low, w_band, kw);
+            }
+            if (kRack) mbar_arrive(&mid[st]);
+            else store_and_refill(i, st);
+        }
+        if (!kRack && lane == 0) tma_wait_all<0>();
+        if (live) {
+            svf[2 * (size_t) I + inst] = w_low;
+            svf[3 * (size_t) I + inst] = w_band;
+        }
+        return;
+    }
+
+    // ---- I/O
+    const float feedback = P(P_D_FEEDBACK), frac = P(P_D_FRAC);
+    const uint32_t delay = __float_as_uint(P(P_D_DELAY));
+    float *ring = ring_all + (size_t) ci * kRing;
+    const bool far = live && delay >= (uint32_t) (STAGES * TB + 2);
+    const bool all_far = __all_sync(0xffffffffu, far || !live);  // see k_fx_tma: coalesced ring traffic needs the whole warp ahead
+    uint32_t wp = wp0, la = wp0 + delay, lc;
+    la = la >= (uint32_t) kRing ? la - kRing : la;
+    lc = la;
+    float prev_a = 0.f;
+    if (all_far && live) {
+        const uint32_t ib = la + 1 >= (uint32_t) kRing ? la + 1 - kRing : la + 1;
+        prev_a = ring[ib];
+    }
+    auto fetch_ring = [&](uint32_t tile, uint32_t stage) {  // as in k_fx_tma: 16-byte runs into this lane's tap row
+        if (all_far && live && tile < ntiles) {
+            const uint32_t rows = min((uint32_t) TB, frames - tile * TB);
+            float *dst = rtiles + (size_t) stage * L * RS + lane * RS;
+            const int base4 = ((int) la - (TB - 1)) & ~3;
+#pragma unroll
+            for (int c = 0; c < RS / 4; c++) {
+                int idx = base4 + 4 * c;
+                if (idx <= (int) la) {
+                    idx = idx < 0 ? idx + kRing : idx;
+                    fx_cp_async16(dst + 4 * c, ring + idx);
+                }
+            }
+            la = la >= rows ? la - rows : la + kRing - rows;
+        }
+        fx_cp_async_commit();
+    };
+    for (uint32_t j = 0; j < (uint32_t) (STAGES - 1); j++) {
+        if (lane == 0 && j < ntiles) {
+            mbar_arrive_expect_tx(&full[j], kTileBytes);
+            tma_load_2d(tiles + (size_t) j * TB * L, &tm_in, (int) i0, (int) (j * TB), &full[j]);
+        }
+        fetch_ring(j, j);
+    }
+    for (uint32_t i = 0; i < ntiles; i++) {
+        const uint32_t st = i % STAGES, ph = (i / STAGES) & 1;
+        fx_cp_async_wait<STAGES - 2>();  // each lane reads only the row it copied itself
+        mbar_wait(&full[st], ph);
+        const uint32_t rows = min((uint32_t) TB, frames - i * TB);
+        const float *col = tiles + (size_t) st * TB * L + lane;
+        float *rdcol = rdtiles + (size_t) st * TB * L + lane;
+        if (all_far) {
+            if (live) {
+                const int base4 = ((int) lc - (TB - 1)) & ~3;
+                const float *tap = rtiles + (size_t) st * L * RS + lane * RS + ((int) lc - base4);
+                float *wcol = wtile + lane;
+                uint32_t r = 0;
+                for (; r + kFxBatch <= rows; r += kFxBatch) io_batch<kFxBatch>(col + r * L, tap - r, wcol + r * WS, WS, rdcol + r * L, prev_a, frac, feedback);
+                for (; r < rows; r++) io_batch<1>(col + r * L, tap - r, wcol + r * WS, WS, rdcol + r * L, prev_a, frac, feedback);
+                lc = lc >= rows ? lc - rows : lc + kRing - rows;
+            }
+            mbar_arrive(&tapd[st]);  // the wet warp can start while the ring is written back
+            if (live) {  // write-back as in k_fx_tma: scalars to a 16-byte boundary, float4s, scalar rest
+                const float *wcol = wtile + lane;
+                uint32_t r = 0;
+                auto at = [&](uint32_t rr) { return wp >= rr ? wp - rr : wp + kRing - rr; };
+                for (; r < rows && (at(r) & 3u) != 3u; r++) ring[at(r)] = wcol[r * WS];
+                for (; r + 4 <= rows; r += 4) {
+                    const float4 q = make_float4(wcol[(r + 3) * WS], wcol[(r + 2) * WS], wcol[(r + 1) * WS], wcol[r * WS]);
+                    *reinterpret_cast<float4 *>(ring + at(r) - 3) = q;
+                }
+                for (; r < rows; r++) ring[at(r)] = wcol[r * WS];
+            }
+        } else {
+            if (live) {
+                uint32_t w = wp;
+                for (uint32_t r = 0; r < rows; r++) {  // DelayLine::Read straight from the ring (Fx.h:198-200)
+                    uint32_t ia = w + delay;
+                    ia = ia >= (uint32_t) kRing ? ia - kRing : ia;
+                    uint32_t ib = ia + 1;
+                    ib = ib >= (uint32_t) kRing ? ib - kRing : ib;
+                    const float ra = ring[ia], rb = ring[ib];
+                    const float rd = __fadd_rn(ra, __fmul_rn(__fsub_rn(rb, ra), frac));
+                    rdcol[r * L] = rd;
+                    ring[w] = __fadd_rn(col[r * L], __fmul_rn(feedback, rd));
+                    w = w == 0 ? kRing - 1 : w - 1;
+                }
+            }
+            mbar_arrive(&tapd[st]);
+        }
+        wp = wp >= rows ? wp - rows : wp + kRing - rows;
+        fetch_ring(i + STAGES - 1, (i + STAGES - 1) % STAGES);
+    }
+    fx_cp_async_wait<0>();
+}
+
+// ------------------------------------------------------------------------------------------------
 // k_plate_tail: the back half of the plate rack (OLB_FX_RACK_PLATE): ReverbFx's dry/wet around the Dattorro plate's left
 // output (Fx.h:294-300 with the plate of libs/dattorro-verb substituted for the stub ReverbSc, the mapping the reference
 // sketches in modules/fxlib/ReverbFx.cpp:11-37), then FxRack's filter and master volume (Fx.h:426-434).  One instance
@@ -641,10 +931,48 @@ static int fx_launch_tma_cfg(olb_fx *h, const float *in, float *out, uint32_t fr
     return OLB_OK;
 }
 
+// k_fx_split: the ring kinds as a pipeline of two (delay) or three (rack) warps per CTA.
+template <int KIND, int TB, int STAGES, int G>
+static int fx_launch_split_cfg(olb_fx *h, const float *in, float *out, uint32_t frames, cudaStream_t st) {
+    constexpr size_t smem = (size_t) G * fx_split_pipe_bytes<TB, STAGES>();
+    static_assert(smem <= 227 * 1024, "pipelines do not fit one SM");
+    TensorMap tin, tout;
+    int rc = make_tmap_frames(&tin, in, frames, h->I, kFxL, TB);
+    if (rc) return rc;
+    rc = make_tmap_frames(&tout, out, frames, h->I, kFxL, TB);
+    if (rc) return rc;
+    auto kern = k_fx_split<KIND, TB, STAGES, G>;
+    OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    const uint32_t pipes = (h->I + kFxL - 1) / kFxL;
+    kern<<<(pipes + G - 1) / G, 32 * fx_split_warps<KIND, G>(), smem, st>>>(tin, tout, frames, h->I, h->d_par, h->d_svf, h->d_ring, h->wp);
+    return OLB_OK;
+}
+
+// The ring kinds run k_fx_split unless OLB_FX_SPLIT=0 asks for the one-warp k_fx_tma (test / tuning aid).
+static bool fx_use_split(int kind) {
+    if (kind != OLB_FX_DELAY && kind != OLB_FX_RACK) return false;
+    const char *e = getenv("OLB_FX_SPLIT");
+    return !e || atoi(e) != 0;
+}
+
 template <int KIND>
 static int fx_launch_tma(olb_fx *h, const float *in, float *out, uint32_t frames, cudaStream_t st) {
     int tb = 64, stages = 4;
     if (const char *e = getenv("OLB_FX_TMA_CFG")) sscanf(e, "%dx%d", &tb, &stages);
+    if (fx_use_split(KIND)) {
+        constexpr int SK = (KIND == OLB_FX_DELAY || KIND == OLB_FX_RACK) ? KIND : OLB_FX_DELAY;
+        // pipelines per CTA: as many as it takes to keep the bank on one CTA per SM (up to 4), so that the kernel places
+        // every warp on a scheduler itself; OLB_FX_SPLIT_G / OLB_FX_TMA_CFG override (test / tuning aids)
+        const uint32_t pipes = (h->I + kFxL - 1) / kFxL;
+        int sms = 148;
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device);
+        int g = pipes <= (uint32_t) sms ? 1 : pipes <= 2u * sms ? 2 : 4;
+        if (const char *e = getenv("OLB_FX_SPLIT_G")) g = atoi(e);
+        const bool tb32 = getenv("OLB_FX_TMA_CFG") ? tb == 32 : g == 4;
+        if (g == 4) return fx_launch_split_cfg<SK, 32, 4, 4>(h, in, out, frames, st);  // 4 x 53 KB
+        if (g == 2) return tb32 ? fx_launch_split_cfg<SK, 32, 4, 2>(h, in, out, frames, st) : fx_launch_split_cfg<SK, 64, 4, 2>(h, in, out, frames, st);
+        return tb32 ? fx_launch_split_cfg<SK, 32, 4, 1>(h, in, out, frames, st) : fx_launch_split_cfg<SK, 64, 4, 1>(h, in, out, frames, st);
+    }
     if (tb == 32 && stages == 4) return fx_launch_tma_cfg<KIND, 32, 4>(h, in, out, frames, st);
     if (tb == 64 && stages == 4) return fx_launch_tma_cfg<KIND, 64, 4>(h, in, out, frames, st);
     if (tb == 64 && stages == 8) return fx_launch_tma_cfg<KIND, 64, 8>(h, in, out, frames, st);
@@ -816,7 +1144,7 @@ OLB_API int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev_arg, u
             default: rc = fx_launch_tma<OLB_FX_RACK>(h, in_dev, out_dev, F, st); break;
         }
         if (rc) return rc;
-        h->last_kernel = "k_fx_tma";
+        h->last_kernel = fx_use_split(kind) ? "k_fx_split" : "k_fx_tma";
     }
 #undef OLB_FX_KINDS
 #undef OLB_FX_GO

@@ -123,7 +123,10 @@ def test_reference_fx_test_delay_replayed_on_the_bank(orc):
 
 
 VARIANTS = [{"OLB_FX_KERNEL": "simple"}, {"OLB_FX_KERNEL": "pf"}, {"OLB_FX_KERNEL": "tma"}] + \
-    [{"OLB_FX_KERNEL": "tma", "OLB_FX_TMA_CFG": c} for c in ("32x4", "32x8", "64x8")]
+    [{"OLB_FX_KERNEL": "tma", "OLB_FX_SPLIT": "0", "OLB_FX_TMA_CFG": c} for c in ("32x4", "32x8", "64x8")] + \
+    [{"OLB_FX_KERNEL": "tma", "OLB_FX_SPLIT_G": g, "OLB_FX_TMA_CFG": c} for g, c in (("1", "32x4"), ("2", "64x4"), ("2", "32x4"), ("4", "32x4"))]
+# FilterFx: "tma" is k_fx_tma in the shape OLB_FX_TMA_CFG names.  Ring kinds: "tma" is the warp pipeline k_fx_split with
+# OLB_FX_SPLIT_G pipelines per CTA, unless OLB_FX_SPLIT=0 asks for the one-warp k_fx_tma.
 
 
 @pytest.mark.parametrize("env", VARIANTS, ids=lambda e: "-".join(e.values()))
@@ -147,9 +150,39 @@ def test_every_kernel_variant_is_bit_exact(orc, monkeypatch, env, kind):
         assert np.array_equal(bits(y[:, i]), bits(want[:, 0])), (env, name, i)
 
 
+@pytest.mark.parametrize("kind", [fx.DELAY, fx.RACK])
+@pytest.mark.parametrize("instances", [6000, 9604])
+def test_large_bank_dispatch_is_bit_exact(orc, kind, instances):
+    """Banks past one pipeline per SM run 2 (here 188 pipelines) or 4 (301 pipelines, the last CTA three-quarters empty and
+    its last pipeline ragged) pipelines per CTA: sampled instances against the oracle, the block cut once mid-tile."""
+    T = 1500
+    x = orc.noise(21, 0, instances, 0, T, 0.5)
+    b = FxBank(kind, instances)
+    times = np.linspace(0.02, 1.0, instances, dtype=np.float32)
+    b.UpdateHardwareControl(35, times, first=0, count=instances)
+    b.UpdateMidiControl(38, 90)
+    dx = torch.from_numpy(np.ascontiguousarray(x)).cuda()
+    dy = torch.empty_like(dx)
+    b.ProcessDevice(dx.data_ptr(), dy.data_ptr(), 1001)
+    b.ProcessDevice(dx[1001:].data_ptr(), dy[1001:].data_ptr(), T - 1001)
+    torch.cuda.synchronize()
+    assert b.LastKernel() == "k_fx_split"
+    b.close()
+    y = dy.cpu().numpy()
+    for i in [0, 31, 32, 63, 64, 95, 96, 127, 128, 2999, 5999, instances - 5, instances - 1]:
+        ev = [(0, loader.EV_HW_CC, 35, float(times[i])), (0, loader.EV_MIDI_CC, 38, 90)]
+        want = getattr(orc, NAMES[kind])(np.ascontiguousarray(x[:, i:i + 1]), 48000.0, ev)
+        assert np.array_equal(bits(y[:, i]), bits(want[:, 0])), (NAMES[kind], instances, i)
+
+
 def test_default_kernel_is_the_tma_pipeline():
     b = FxBank(fx.RACK, 256)
     x = torch.zeros((64, 256), dtype=torch.float32, device="cuda")
+    b.ProcessDevice(x.data_ptr(), x.data_ptr(), 64)
+    torch.cuda.synchronize()
+    assert b.LastKernel() == "k_fx_split"  # the ring kinds: one warp per pipeline stage
+    b.close()
+    b = FxBank(fx.FILTER, 256)
     b.ProcessDevice(x.data_ptr(), x.data_ptr(), 64)
     torch.cuda.synchronize()
     assert b.LastKernel() == "k_fx_tma"

@@ -1,4 +1,17 @@
 #!/bin/bash
 set -u
 O=gpurun_out; mkdir -p $O
-timeout 900 python -m pytest tests/test_wav_rack.py tests/test_fx_gpu.py tests/test_abi.py -x -q > $O/pytest_wav.log 2>&1; echo "pytest rc=$?"; tail -15 $O/pytest_wav.log
+timeout 900 python -m pytest tests/test_fx_gpu.py tests/test_full_duration_gpu.py -m gpu -x -q > $O/pytest_fx.log 2>&1; echo "pytest rc=$?"; tail -15 $O/pytest_fx.log
+: > $O/units11.jsonl
+for inst in 8192 65536; do
+  OLB_FX_SPLIT=0 timeout 300 python tools/bench_units.py fxrack --instances $inst 2>/dev/null | grep '^{' | sed 's/^{/{"cfg": "one-warp", /' >> $O/units11.jsonl
+  for cfg in 64x4 64x6 32x8; do
+    OLB_FX_TMA_CFG=$cfg timeout 300 python tools/bench_units.py fxrack --instances $inst 2>/dev/null | grep '^{' | sed "s/^{/{\"cfg\": \"split-$cfg\", /" >> $O/units11.jsonl
+  done
+done
+python - <<'PY'
+import json
+for l in open('gpurun_out/units11.jsonl'):
+    d=json.loads(l); print(d['cfg'], d['unit'], d.get('kernel'), d['instances'], '%.3e'%d['value'])
+PY
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_fx_tma -s 1 -c 1 -f -o $O/k_rack_split_full python tools/bench_units.py fxrack --frames 4800 --steps 1 > $O/ncu_rack.log 2>&1
