@@ -47,7 +47,7 @@ struct ChorusLane {
     float phase, y1, y2;
 };
 
-constexpr int kChB = 8;  // frames per batch; the ring carries kChB spare slots so a batch may write ahead of its reads
+constexpr int kChB = 16;  // frames per batch; the ring carries kChB spare slots so a batch may write ahead of its reads
 
 // The chorus frame has two halves that share nothing but the delay they agree on: the LFO (phase -> table lookup -> delay
 // in samples: a pure function of the phase state, independent of the audio) and the audio path (delay~ write and
@@ -75,6 +75,15 @@ __device__ __forceinline__ void chorus_lfo_batch(ChorusLane &c, uint32_t *kq, fl
             const float ph = __fadd_rn(c.phase, c.inc);
             c.phase = ph >= 1.0f ? __fsub_rn(ph, 1.0f) : ph;
         }
+    }
+}
+
+// The phase recurrence alone over n frames: what an LFO warp runs across the tiles the other LFO warp expands.
+__device__ __forceinline__ void chorus_phase_skip(ChorusLane &c, uint32_t n) {
+#pragma unroll 8
+    for (uint32_t r = 0; r < n; r++) {
+        const float ph = __fadd_rn(c.phase, c.inc);
+        c.phase = ph >= 1.0f ? __fsub_rn(ph, 1.0f) : ph;
     }
 }
 
@@ -124,7 +133,7 @@ __device__ __forceinline__ void chorus_audio_batch(float *col, ChorusLane &c, fl
 __device__ __forceinline__ void mbar_arrive_all(uint64_t *bar) { mbar_arrive(bar); }
 
 template <int TB, int STAGES, bool TMA>
-__global__ void __launch_bounds__(64) k_chorus(const __grid_constant__ TensorMap tm_in, const __grid_constant__ TensorMap tm_out,
+__global__ void __launch_bounds__(96) k_chorus(const __grid_constant__ TensorMap tm_in, const __grid_constant__ TensorMap tm_out,
                                                const float *in, float *out, uint32_t frames, uint32_t I, uint32_t R,
                                                const float *__restrict__ par, float *state, float *ring_all,
                                                const float *__restrict__ tab_g, uint32_t w0, float dmax) {
@@ -150,6 +159,7 @@ __global__ void __launch_bounds__(64) k_chorus(const __grid_constant__ TensorMap
         }
         mbar_fence_init();
     }
+    for (uint32_t j = threadIdx.x; j <= (uint32_t) kChTab; j += blockDim.x) tab[j] = tab_g[j];
     __syncthreads();
     constexpr uint32_t kTileBytes = TB * L * sizeof(float);
     const uint32_t ntiles = (frames + TB - 1) / TB;
@@ -160,14 +170,18 @@ __global__ void __launch_bounds__(64) k_chorus(const __grid_constant__ TensorMap
     c.mix = par[(size_t) CP_MIX * I + ci];
     c.phase = state[ci]; c.y1 = state[(size_t) I + ci]; c.y2 = state[2 * (size_t) I + ci];
 
-    if (warp == 1) {
-        // ---- LFO warp: one tile ahead of the audio warp (two hand-over buffers) ----
-        for (uint32_t j = lane; j <= (uint32_t) kChTab; j += 32) tab[j] = tab_g[j];
-        __syncwarp();
+    if (warp >= 1) {
+        // ---- LFO warps 1 and 2: warp 1 expands the even tiles into hand-over buffer 0, warp 2 the odd tiles into buffer 1
+        // (table lookups and float <-> int conversions, ~30 instructions per frame); across the other warp's tiles each
+        // runs only the 3-operation phase recurrence, so both carry the same phase sequence as the one-warp version. ----
+        const uint32_t s = warp - 1;
         for (uint32_t i = 0; i < ntiles; i++) {
-            const uint32_t s = i & 1;
-            if (i >= 2) mbar_wait(&lfo_empty[s], ((i >> 1) - 1) & 1);
             const uint32_t rows = min((uint32_t) TB, frames - i * TB);
+            if ((i & 1) != s) {
+                if (live) chorus_phase_skip(c, rows);
+                continue;
+            }
+            if (i >= 2) mbar_wait(&lfo_empty[s], ((i >> 1) - 1) & 1);
             uint32_t *kcol = kq + (size_t) s * TB * L + lane;
             float *fcol = frq + (size_t) s * TB * L + lane;
             if (live) {
@@ -177,7 +191,7 @@ __global__ void __launch_bounds__(64) k_chorus(const __grid_constant__ TensorMap
             }
             mbar_arrive_all(&lfo_full[s]);
         }
-        if (live) state[inst] = c.phase;
+        if (live && warp == 1) state[inst] = c.phase;
         return;
     }
 
@@ -415,12 +429,12 @@ OLB_API int olb_chorus_process(olb_chorus *h, const float *in_dev, float *out_de
         if (rc) return rc;
         auto kern = k_chorus<kChTB, kChStages, true>;
         OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        kern<<<h->ctas, 64, smem, st>>>(tin, tout, in_dev, out_dev, (uint32_t) frames, h->I, h->R, h->d_par, h->d_state, h->d_ring, h->d_tab, h->w, (float) (chorus_spec_len(h->sample_rate) - 2));
+        kern<<<h->ctas, 96, smem, st>>>(tin, tout, in_dev, out_dev, (uint32_t) frames, h->I, h->R, h->d_par, h->d_state, h->d_ring, h->d_tab, h->w, (float) (chorus_spec_len(h->sample_rate) - 2));
         h->last_kernel = "k_chorus_tma";
     } else {
         auto kern = k_chorus<kChTB, kChStages, false>;
         OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        kern<<<h->ctas, 64, smem, st>>>(tin, tout, in_dev, out_dev, (uint32_t) frames, h->I, h->R, h->d_par, h->d_state, h->d_ring, h->d_tab, h->w, (float) (chorus_spec_len(h->sample_rate) - 2));
+        kern<<<h->ctas, 96, smem, st>>>(tin, tout, in_dev, out_dev, (uint32_t) frames, h->I, h->R, h->d_par, h->d_state, h->d_ring, h->d_tab, h->w, (float) (chorus_spec_len(h->sample_rate) - 2));
         h->last_kernel = "k_chorus_direct";
     }
     OLB_LAUNCHED();
