@@ -5,6 +5,8 @@
 //   PolyvoiceBank   ol::synth::Polyvoice over a VoiceBank (modules/synthlib/Polyvoice.h:12-86): NoteOn takes the first voice
 //                   that is not playing, NoteOff releases the first voice playing that note, Process ADDS every voice
 //                   into the caller's frame (the caller zeroes it: main.cpp:79)
+//   VoiceMapBank    ol::synth::VoiceMap over a VoiceBank (modules/synthlib/VoiceMap.h:14-90): note -> voice and channel -> voice
+//                   tables
 // Call order as in the reference (modules/ol_daisy/app/synth/main.cpp:74-90, 114-128, 161-168):
 //     ol::gpu::VoiceBank bank(65536);  bank.Init(48000);
 //     ol::gpu::PolyvoiceBank poly(bank);
@@ -136,6 +138,48 @@ public:
 private:
     VoiceBank &bank_;
     std::vector<uint8_t> playing_;
+};
+
+// ol::synth::VoiceMap (modules/synthlib/VoiceMap.h:14-90) over a VoiceBank: a note -> voice table (a pad kit: every mapped
+// note triggers ITS voice) and a channel -> voice table for MIDI CCs (the voice last set on that channel).  Unmapped notes
+// and channels are ignored as in the reference; Process adds the bank into the caller's frame (voices that were never
+// triggered are silent).  One deviation: the reference walks its note table in Process, so a voice set under two notes
+// would be advanced twice per frame there -- SetVoice refuses that (returns false).
+class VoiceMapBank {
+public:
+    explicit VoiceMapBank(VoiceBank &bank) : bank_(bank) {
+        for (int &v : note2voice_) v = -1;
+        for (int &v : channel2voice_) v = -1;
+    }
+    bool SetVoice(uint8_t channel, uint8_t note, uint32_t voice) {  // VoiceMap.h:45-59
+        if (note >= 128 || channel >= 16) return true;               // silently ignored, as upstream
+        if (voice >= bank_.Voices()) return false;
+        for (int n = 0; n < 128; n++)
+            if (n != note && note2voice_[n] == (int) voice) return false;
+        note2voice_[note] = (int) voice;
+        channel2voice_[channel] = (int) voice;
+        return true;
+    }
+    InitStatus Init(t_sample sample_rate) { return bank_.Init(sample_rate); }  // VoiceMap.h:61-63
+    void NoteOn(uint8_t note, uint8_t velocity) {                              // VoiceMap.h:27-34
+        if (note < 128 && note2voice_[note] >= 0) bank_.NoteOn((uint32_t) note2voice_[note], note, velocity);
+    }
+    void NoteOff(uint8_t note, uint8_t /*velocity*/) {  // VoiceMap.h:36-43
+        if (note < 128 && note2voice_[note] >= 0) bank_.NoteOff((uint32_t) note2voice_[note]);
+    }
+    void UpdateMidiControl(uint8_t channel, uint8_t control, uint8_t value) {  // VoiceMap.h:80-87
+        if (channel < 16 && channel2voice_[channel] >= 0) bank_.UpdateMidiControl(control, value, (uint32_t) channel2voice_[channel], 1);
+    }
+    // VoiceMap::Process: frame_out[0] += every mapped voice (VoiceMap.h:65-78)
+    void Process(t_sample *frame_out) { bank_.ProcessBlock(nullptr, frame_out, 1, true, 1.0f, 1); }
+    void ProcessBlock(t_sample *bus_host, uint64_t frames, uint32_t bus_channels = 1, t_sample gain = 1.0f) {
+        bank_.ProcessBlock(nullptr, bus_host, bus_channels, true, gain, frames);
+    }
+    int status() const { return bank_.status(); }
+
+private:
+    VoiceBank &bank_;
+    int note2voice_[128], channel2voice_[16];
 };
 
 }  // namespace gpu

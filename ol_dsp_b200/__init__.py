@@ -4,7 +4,7 @@ from ._lib import (KIND_BIQUAD, KIND_LPF, KIND_PORT, LAYOUT_FRAMES, LAYOUT_PLANA
 from .chorus import ChorusBank  # noqa: F401
 from .dattorro import DattorroBank  # noqa: F401
 from .fx import FxBank  # noqa: F401
-from .voice import Polyvoice, VoiceBank  # noqa: F401
+from .voice import Polyvoice, VoiceBank, VoiceMap  # noqa: F401
 from .sharding import reduce_bus, shard_range  # noqa: F401
 from .biquad import BiquadBank, design  # noqa: F401
 from .workloads import c2_coefs, noise_device  # noqa: F401

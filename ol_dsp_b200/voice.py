@@ -131,3 +131,48 @@ class Polyvoice:
 
     def Process(self, frames, bus_ptr, bus_channels=1, stream=0):
         self.bank.ProcessDevice(frames, bus_ptr=bus_ptr, bus_channels=bus_channels, accumulate=True, stream=stream)
+
+
+class VoiceMap:
+    """ol::synth::VoiceMap (modules/synthlib/VoiceMap.h:14-90) over a VoiceBank: a note -> voice table (a pad kit: every
+    mapped note triggers ITS voice) and a channel -> voice table for MIDI CCs (the voice last set on that channel).
+    Notes and channels that are not mapped are ignored, as in the reference.  Process accumulates the bank into the
+    caller's (zeroed) bus; voices that were never triggered are silent.  One deviation: the reference walks its note
+    table in Process, so a voice set under two notes would be advanced twice per frame there -- SetVoice refuses that."""
+
+    MAP_SIZE, CHANNELS = 128, 16
+
+    def __init__(self, bank):
+        self.bank = bank
+        self.note2voice, self.channel2voice = {}, {}
+
+    def SetVoice(self, channel, note, voice):
+        if not (0 <= note < self.MAP_SIZE and 0 <= channel < self.CHANNELS):
+            return  # VoiceMap.h:46-47: silently ignored
+        if not 0 <= voice < self.bank.voices:
+            raise ValueError("voice %d is not in the bank" % voice)
+        if any(v == voice and n != note for n, v in self.note2voice.items()):
+            raise ValueError("voice %d is already mapped under another note" % voice)
+        self.note2voice[note] = voice
+        self.channel2voice[channel] = voice
+
+    def Init(self, sample_rate):
+        self.bank.Init(sample_rate)
+
+    def NoteOn(self, note, velocity=100):
+        v = self.note2voice.get(note)
+        if v is not None:
+            self.bank.NoteOn(note, velocity, first=v, count=1)
+
+    def NoteOff(self, note, velocity=0):
+        v = self.note2voice.get(note)
+        if v is not None:
+            self.bank.NoteOff(first=v, count=1)
+
+    def UpdateMidiControl(self, channel, control, value):
+        v = self.channel2voice.get(channel)
+        if v is not None:
+            self.bank.UpdateMidiControl(control, value, first=v, count=1)
+
+    def Process(self, frames, bus_ptr, bus_channels=1, stream=0):
+        self.bank.ProcessDevice(frames, bus_ptr=bus_ptr, bus_channels=bus_channels, accumulate=True, stream=stream)

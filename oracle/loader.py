@@ -255,6 +255,20 @@ class Reference(_Fx):
         assert rc == 0
         return out
 
+    def voicemap(self, n, frames, mapping, sr=48000.0, config=None, ev=None):
+        """The reference's own ol::synth::VoiceMap<1> over n SynthVoices.  mapping = [(channel, note, voice)], fed to
+        SetVoice in order; events as everywhere, a MIDI CC's 5th field is the MIDI channel."""
+        out = np.empty(frames, dtype=np.float32)
+        cfg = np.ascontiguousarray(config, dtype=np.float32) if config is not None else None
+        arr, n_ev = events(ev or [])
+        m = np.ascontiguousarray(mapping, dtype=np.int32).reshape(-1, 3)
+        fn = self.lib.ref_voicemap_run
+        fn.argtypes = [C.c_int, C.c_float, _F, C.POINTER(C.c_int32), C.c_size_t, _EVP, C.c_size_t, _F, C.c_size_t]
+        fn.restype = C.c_int
+        rc = fn(n, sr, _fp(cfg) if cfg is not None else None, m.ctypes.data_as(C.POINTER(C.c_int32)), m.shape[0], arr, n_ev, _fp(out), frames)
+        assert rc == 0
+        return out
+
     def control_wire(self, which, controller, value):
         """The reference's own ol::ctl::Control + SimpleSerializer::SerializeControl: which 0 MIDI / 1 float / 2 ADC.
         Returns (controller, adc, midi, float bits, wire bytes)."""

@@ -264,6 +264,44 @@ int ref_polyvoice_run(int n_voices, float sr, const float *config16, const olb_e
     return 0;
 }
 
+// VoiceMap over n SynthVoices (VoiceMap.h:14-90): map3 = n_map x (channel, note, voice index) fed to SetVoice in order.
+// Note events go to the voice mapped to that NOTE (VoiceMap.h:27-43), MIDI CCs to the voice last set on the CHANNEL
+// carried in ev.voice (VoiceMap.h:80-87).  out[t] = the mapped voices in note order, accumulated into a zeroed frame.
+int ref_voicemap_run(int n_voices, float sr, const float *config16, const int32_t *map3, size_t n_map, const olb_event *ev,
+                     size_t n_ev, float *out, size_t frames) {
+    std::vector<ol::synth::SynthVoice *> voices;
+    for (int i = 0; i < n_voices; i++) voices.push_back(new_voice());
+    ol::synth::VoiceMap<1> map;
+    for (size_t m = 0; m < n_map; m++) {
+        const int32_t v = map3[3 * m + 2];
+        if (v < 0 || v >= n_voices) return 1;
+        map.SetVoice((uint8_t) map3[3 * m], (uint8_t) map3[3 * m + 1], voices[v]);
+    }
+    map.Init(sr);
+    if (config16) {
+        ol::synth::Voice::Config c;
+        memcpy(&c, config16, sizeof(c));
+        for (auto v : voices) v->UpdateConfig(c);
+    }
+    size_t next = 0;
+    for (size_t t = 0; t < frames; t++) {
+        while (next < n_ev && ev[next].frame <= t) {
+            const olb_event &e = ev[next++];
+            switch (e.kind) {
+                case OLB_EV_NOTE_ON: map.NoteOn((uint8_t) e.a, (uint8_t) e.v); break;
+                case OLB_EV_NOTE_OFF: map.NoteOff((uint8_t) e.a, (uint8_t) e.v); break;
+                case OLB_EV_MIDI_CC: map.UpdateMidiControl((uint8_t) e.voice, (uint8_t) e.a, (uint8_t) e.v); break;
+                default: break;
+            }
+        }
+        float frame = 0.f;
+        map.Process(&frame);
+        out[t] = frame;
+    }
+    for (auto v : voices) delete v;
+    return 0;
+}
+
 // Replays test/fx_test.cpp:25-55 (TEST(FX, Delay)); returns the number of NaN outputs (reference expects 0).
 int ref_test_fx_delay(float *out_48000) {
     RefDelayLine *dl = new RefDelayLine();

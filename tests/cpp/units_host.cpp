@@ -1,7 +1,7 @@
 // C++ callers written the way a reference user writes them (Init -> setters -> Process per frame, then per block), against
 // include/ol_gpu/{FxBank,DattorroBank,ChorusBank,VoiceBank}.hpp.  Built by tests/test_abi.py (link check, CPU) and run by
 // tests/test_cpp_hosts_gpu.py on the GPU box, where the outputs are compared with the oracle.
-//   usage: units_host <filter|delay|reverb|rack|plate|chorus|poly> <instances> <frames> <in.f32> <out.f32> [out2.f32]
+//   usage: units_host <filter|delay|reverb|rack|plate|chorus|poly|voicemap> <instances> <frames> <in.f32> <out.f32> [out2.f32]
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -54,7 +54,7 @@ int main(int argc, char **argv) {
     const char *unit = argv[1];
     const uint32_t I = (uint32_t) atoi(argv[2]), T = (uint32_t) atoi(argv[3]);
     std::vector<float> in((size_t) I * T), out((size_t) I * T), out2;
-    if (strcmp(unit, "poly") && !slurp(argv[4], in)) return 3;
+    if (strcmp(unit, "poly") && strcmp(unit, "voicemap") && !slurp(argv[4], in)) return 3;
     int rc = 0;
     if (!strcmp(unit, "filter")) rc = run_fx<ol::gpu::FilterFxBank>(I, T, in, out);
     else if (!strcmp(unit, "delay")) rc = run_fx<ol::gpu::DelayFxBank>(I, T, in, out);
@@ -111,6 +111,39 @@ int main(int argc, char **argv) {
         bank.Playing(playing, 0, I < 8 ? I : 8);
         for (uint32_t v = 0; v < (I < 8 ? I : 8); v++) printf("%u ", playing[v]);
         printf("\n");
+    } else if (!strcmp(unit, "voicemap")) {
+        // the scenario of tests/golden/make_golden.py VOICEMAP_*: pads on notes 36 / 38 / 42 / 60 / 62, channel 3 set twice
+        ol::gpu::VoiceBank bank(I);
+        ol::gpu::VoiceMapBank map(bank);
+        if (map.Init(48000.f) != ol::gpu::Ok) {
+            fprintf(stderr, "Init failed: %s\n", bank.error().c_str());
+            return 4;
+        }
+        const int mapping[5][3] = {{0, 36, 0}, {1, 38, 1}, {2, 42, 2}, {3, 60, 3}, {3, 62, 4}};
+        for (auto &m : mapping)
+            if (!map.SetVoice((uint8_t) m[0], (uint8_t) m[1], (uint32_t) m[2])) return 6;
+        if (map.SetVoice(5, 70, 0)) return 7;  // voice 0 already sits under note 36: refused
+        struct Ev { uint32_t frame; int kind, a, v, ch; };  // kind 0 CC, 2 note on, 3 note off
+        const Ev evs[] = {{0, 0, 41, 40, 1}, {0, 0, 42, 90, 3}, {0, 2, 36, 100, 0}, {3, 2, 38, 90, 0}, {400, 2, 62, 127, 0}, {401, 2, 61, 100, 0},
+                          {900, 3, 36, 0, 0}, {1000, 2, 60, 80, 0}, {1200, 2, 200, 100, 0}, {1500, 0, 41, 100, 0}, {1700, 2, 36, 110, 0},
+                          {2000, 3, 38, 0, 0}, {2400, 2, 42, 64, 0}, {2600, 0, 41, 20, 7}};
+        out.assign(T, 0.f);
+        uint32_t t = 0;
+        size_t e = 0;
+        const size_t n_ev = sizeof(evs) / sizeof(evs[0]);
+        while (t < T) {
+            for (; e < n_ev && evs[e].frame <= t; e++) {
+                if (evs[e].kind == 0) map.UpdateMidiControl((uint8_t) evs[e].ch, (uint8_t) evs[e].a, (uint8_t) evs[e].v);
+                else if (evs[e].kind == 2) map.NoteOn((uint8_t) evs[e].a, (uint8_t) evs[e].v);
+                else map.NoteOff((uint8_t) evs[e].a, (uint8_t) evs[e].v);
+            }
+            const uint32_t stop = e < n_ev && evs[e].frame < T ? evs[e].frame : T;
+            if (stop - t == 1) map.Process(&out[t]);
+            else map.ProcessBlock(&out[t], stop - t);
+            t = stop;
+        }
+        rc = bank.status() == OLB_OK ? 0 : 5;
+        if (rc) fprintf(stderr, "process failed: %s\n", bank.error().c_str());
     } else {
         fprintf(stderr, "unknown unit %s\n", unit);
         return 2;

@@ -44,6 +44,16 @@ VOICE_EVENTS = [
 ]
 
 
+# VoiceMap scenario (modules/synthlib/VoiceMap.h): a pad-style kit.  Channel 3 is set twice, so its CCs reach voice 4 only;
+# voice 5 is never mapped; note 61 and note 200 are not mapped and must be ignored.
+VOICEMAP_MAPPING = [(0, 36, 0), (1, 38, 1), (2, 42, 2), (3, 60, 3), (3, 62, 4)]
+VOICEMAP_EVENTS = [(0, loader.EV_MIDI_CC, 41, 40, 1), (0, loader.EV_MIDI_CC, 42, 90, 3), (0, loader.EV_NOTE_ON, 36, 100),
+                   (3, loader.EV_NOTE_ON, 38, 90), (400, loader.EV_NOTE_ON, 62, 127), (401, loader.EV_NOTE_ON, 61, 100),
+                   (900, loader.EV_NOTE_OFF, 36, 0), (1000, loader.EV_NOTE_ON, 60, 80), (1200, loader.EV_NOTE_ON, 200, 100),
+                   (1500, loader.EV_MIDI_CC, 41, 100, 0), (1700, loader.EV_NOTE_ON, 36, 110), (2000, loader.EV_NOTE_OFF, 38, 0),
+                   (2400, loader.EV_NOTE_ON, 42, 64), (2600, loader.EV_MIDI_CC, 41, 20, 7)]
+
+
 def sha(a):
     return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
 
@@ -90,6 +100,7 @@ def main():
                       [(0, loader.EV_NOTE_ON, 48, 100), (5, loader.EV_NOTE_ON, 55, 100), (700, loader.EV_NOTE_ON, 64, 100),
                        (1500, loader.EV_NOTE_OFF, 55, 0), (1600, loader.EV_NOTE_ON, 67, 100), (2500, loader.EV_NOTE_OFF, 48, 0)])
     v["poly4"] = p
+    v["voicemap"] = ref.voicemap(6, 3000, VOICEMAP_MAPPING, 48000.0, None, VOICEMAP_EVENTS)
     rc, fr = ref.test_synth_voice()
     v["test_synth_voice_failed_mask"] = np.array([rc])
     v["test_synth_voice_frames"] = fr

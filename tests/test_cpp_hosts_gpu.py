@@ -66,3 +66,11 @@ def test_polyvoice_mirror(orc, tmp_path):
     want = orc.polyvoice(V, T, ev=ev)
     assert np.abs(y - np.asarray(want).reshape(-1)).max() <= 4e-5
     assert out.split()[:4] == ["64", "55", "0", "0"]  # NoteOff(48) frees voice 0, NoteOn(64) takes the first free voice
+
+
+def test_voicemap_mirror(tmp_path):
+    """ol::gpu::VoiceMapBank driven like the reference's VoiceMap, against the reference's own output (golden)."""
+    want = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "synth.npz"))["voicemap"]
+    run("voicemap", 6, want.shape[0], None, tmp_path)
+    y = np.fromfile(tmp_path / "out.f32", dtype=np.float32)
+    assert np.abs(y - want).max() <= 5e-5

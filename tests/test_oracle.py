@@ -66,6 +66,31 @@ def test_voice_and_polyvoice_match_reference_golden(orc):
     assert np.array_equal(bits(p), bits(g["poly4"]))
 
 
+def voicemap_as_voice_events():
+    """VoiceMap semantics (VoiceMap.h:27-43, 80-87) spelt out as per-voice events: a note goes to the voice mapped under it,
+    a CC to the voice last set on its channel, anything unmapped is dropped."""
+    note2voice, channel2voice = {}, {}
+    for ch, note, v in mg.VOICEMAP_MAPPING:
+        note2voice[note], channel2voice[ch] = v, v
+    out = []
+    for (f, k, a, v, *ch) in mg.VOICEMAP_EVENTS:
+        tgt = channel2voice.get(ch[0]) if k == loader.EV_MIDI_CC else note2voice.get(a)
+        if tgt is not None:
+            out.append((f, k, a, v, tgt))
+    return out
+
+
+def test_voicemap_matches_reference_golden(orc):
+    """tests/golden/synth.npz 'voicemap' is the reference's own VoiceMap<1> over six SynthVoices; the oracle's voices driven
+    with the routed events give the same frames (the kit's note order is its voice order, so even the sum order agrees)."""
+    g = np.load(os.path.join(G, "synth.npz"))
+    ev = voicemap_as_voice_events()
+    assert len(ev) == len(mg.VOICEMAP_EVENTS) - 3  # note 61, note 200 and the CC on channel 7 are not mapped
+    p = orc.polyvoice(6, 3000, 48000.0, None, ev)
+    assert np.array_equal(p, g["voicemap"])
+    assert np.abs(g["voicemap"]).max() > 0.1
+
+
 def test_scale_matches_reference_golden(orc):
     g = np.load(os.path.join(G, "synth.npz"))
     got = np.array([orc.scale(*a) for a in g["scale_args"]], dtype=np.float32)

@@ -9,7 +9,7 @@ import pytest
 import torch
 
 from oracle import loader
-from ol_dsp_b200 import Polyvoice, VoiceBank
+from ol_dsp_b200 import Polyvoice, VoiceBank, VoiceMap
 from tests.golden import make_golden as mg
 
 pytestmark = pytest.mark.gpu
@@ -170,4 +170,37 @@ def test_sample_accurate_event_list(orc):
     assert list(bank.Playing()) == [0, 67, 64, 0]
     with pytest.raises(Exception):
         process_events(bank, [(10, 2, 60, 100), (5, 2, 62, 100)][::-1] + [(frames + 1, 2, 60, 100)], frames, bus_ptr=bus.data_ptr())
+    bank.close()
+
+
+def test_voicemap_against_the_reference_golden():
+    """ol::synth::VoiceMap over a bank (SURVEY.md section 8f item 2): tests/golden/synth.npz 'voicemap' is the reference's own
+    VoiceMap<1> over six SynthVoices (pads on five notes, channel 3 set twice, unmapped notes / channels ignored)."""
+    want = np.load(os.path.join(G, "synth.npz"))["voicemap"]
+    frames = want.shape[0]
+    bank = VoiceBank(6)
+    vm = VoiceMap(bank)
+    for ch, note, v in mg.VOICEMAP_MAPPING:
+        vm.SetVoice(ch, note, v)
+    with pytest.raises(ValueError):
+        vm.SetVoice(5, 70, 0)  # voice 0 already sits under note 36
+    vm.SetVoice(20, 70, 5)  # channel out of range: ignored like upstream
+    assert 70 not in vm.note2voice
+    bus = torch.zeros((frames, 1), dtype=torch.float32, device="cuda")
+    ev = mg.VOICEMAP_EVENTS
+    cuts = sorted({0, frames} | {e[0] for e in ev})
+    for a, z in zip(cuts[:-1], cuts[1:]):
+        for (f, k, x, v, *ch) in ev:
+            if f != a:
+                continue
+            if k == loader.EV_MIDI_CC:
+                vm.UpdateMidiControl(ch[0], x, v)
+            elif k == loader.EV_NOTE_ON:
+                vm.NoteOn(x, v)
+            else:
+                vm.NoteOff(x, v)
+        vm.Process(z - a, bus[a:].data_ptr())
+    torch.cuda.synchronize()
+    assert np.abs(bus.cpu().numpy()[:, 0] - want).max() <= 5 * TOL  # five sounding voices summed
+    assert list(bank.Playing()) == [36, 0, 42, 60, 62, 0]
     bank.close()
