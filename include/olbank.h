@@ -264,6 +264,40 @@ int olb_chorus_process(olb_chorus *h, const float *in_dev, float *out_dev, uint6
 int olb_chorus_process_host(olb_chorus *h, const float *in_host, float *out_host, uint64_t frames);
 const char *olb_chorus_last_kernel(olb_chorus *h);
 
+/* ================================================================================================
+ * Sample playback bank: `instances` x ol::synth::Sample behind SampleSoundSource
+ * (modules/synthlib/Sample.h:16-52, Sample.cpp:9-61, SampleSoundSource.h:14-41) over a DEVICE-RESIDENT sample pool, which
+ * replaces the per-frame SampleDataSource::Read (SampleDataSource.h:11-25; the reference's only implementation decodes a
+ * file through miniaudio one frame at a time, workouts/workout_buddy.h:18-42).  Every instance is one Sample object: play
+ * state, OneShot / Loop, loop points, position.  As in the reference, Process leaves a frame UNTOUCHED when the instance
+ * is not playing or is past the end of its sample: `out` is played INTO.  Bit-exact (the path copies samples).
+ * All samples of a bank have the bank's channel count (1 or 2, interleaved); out is [frames][instances * channels]. */
+typedef struct olb_sampler olb_sampler;
+#define OLB_SAMPLE_ONESHOT 0 /* ol::synth::SamplePlayMode (Sample.h:11-14) */
+#define OLB_SAMPLE_LOOP 1
+int olb_sampler_create(int device, uint32_t instances, uint32_t channels, olb_sampler **out);
+int olb_sampler_destroy(olb_sampler *h);
+/* Copy one sample ([frames][channels] floats, host) into the pool; *sample_id names it. */
+int olb_sampler_load_sample(olb_sampler *h, const float *frames_host, uint64_t frames, uint32_t *sample_id);
+/* Bind instances to samples (the Sample constructor's data source): the instance becomes a fresh Sample object
+ * (not playing, OneShot, loop points 0, position 0).  ids_host: one id, or one per instance when per_instance != 0. */
+int olb_sampler_set_sample(olb_sampler *h, uint32_t first, uint32_t count, const uint32_t *ids_host, int per_instance);
+int olb_sampler_init(olb_sampler *h, float sample_rate);                                             /* Sample::Init */
+int olb_sampler_seek(olb_sampler *h, uint32_t first, uint32_t count, uint64_t frame_index);          /* Sample::Seek */
+int olb_sampler_set_loop_start(olb_sampler *h, uint32_t first, uint32_t count, uint64_t frame_index);
+int olb_sampler_set_loop_end(olb_sampler *h, uint32_t first, uint32_t count, uint64_t frame_index);
+int olb_sampler_set_play_mode(olb_sampler *h, uint32_t first, uint32_t count, int mode);
+int olb_sampler_play(olb_sampler *h, uint32_t first, uint32_t count);                                /* Sample::Play */
+int olb_sampler_pause(olb_sampler *h, uint32_t first, uint32_t count);                               /* Sample::Pause */
+int olb_sampler_toggle_play(olb_sampler *h, uint32_t first, uint32_t count);                         /* Sample::TogglePlay */
+/* SampleSoundSource::GateOn (Seek(0) + Play) / GateOff (Pause), SampleSoundSource.h:21-26 */
+int olb_sampler_gate(olb_sampler *h, uint32_t first, uint32_t count, int on);
+/* Position (next frame to be read) and play flag of a range, after all work queued so far. */
+int olb_sampler_position(olb_sampler *h, uint32_t first, uint32_t count, uint64_t *frame_index_host, uint8_t *playing_host);
+int olb_sampler_process(olb_sampler *h, float *out_dev, uint64_t frames, void *stream);
+/* Host buffer, played INTO: copied to the device, processed, copied back. */
+int olb_sampler_process_host(olb_sampler *h, float *out_host, uint64_t frames);
+
 #ifdef __cplusplus
 }
 #endif

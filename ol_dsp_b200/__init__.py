@@ -2,6 +2,7 @@
 from . import _lib  # noqa: F401
 from ._lib import (KIND_BIQUAD, KIND_LPF, KIND_PORT, LAYOUT_FRAMES, LAYOUT_PLANAR, MODE_EXACT, MODE_FAST, MODE_FMA, OlbError)  # noqa: F401
 from .chorus import ChorusBank  # noqa: F401
+from .sampler import SamplerBank  # noqa: F401
 from .dattorro import DattorroBank  # noqa: F401
 from .fx import FxBank  # noqa: F401
 from .voice import Polyvoice, VoiceBank, VoiceMap  # noqa: F401

@@ -101,6 +101,22 @@ def lib():
         "olb_chorus_set_params": ([vp, u32, u32, i32, _F, u32], i32),
         "olb_chorus_process": ([vp, vp, vp, u64, vp], i32),
         "olb_chorus_last_kernel": ([vp], C.c_char_p),
+        "olb_sampler_create": ([i32, u32, u32, C.POINTER(vp)], i32),
+        "olb_sampler_destroy": ([vp], i32),
+        "olb_sampler_load_sample": ([vp, _F, u64, C.POINTER(u32)], i32),
+        "olb_sampler_set_sample": ([vp, u32, u32, C.POINTER(u32), i32], i32),
+        "olb_sampler_init": ([vp, f32], i32),
+        "olb_sampler_seek": ([vp, u32, u32, u64], i32),
+        "olb_sampler_set_loop_start": ([vp, u32, u32, u64], i32),
+        "olb_sampler_set_loop_end": ([vp, u32, u32, u64], i32),
+        "olb_sampler_set_play_mode": ([vp, u32, u32, i32], i32),
+        "olb_sampler_play": ([vp, u32, u32], i32),
+        "olb_sampler_pause": ([vp, u32, u32], i32),
+        "olb_sampler_toggle_play": ([vp, u32, u32], i32),
+        "olb_sampler_gate": ([vp, u32, u32, i32], i32),
+        "olb_sampler_position": ([vp, u32, u32, C.POINTER(u64), C.POINTER(C.c_uint8)], i32),
+        "olb_sampler_process": ([vp, vp, u64, vp], i32),
+        "olb_sampler_process_host": ([vp, vp, u64], i32),
     }
     for name, (args, res) in sig.items():
         f = getattr(L, name)

@@ -16,6 +16,7 @@ import numpy as np
 HERE = os.path.dirname(os.path.abspath(__file__))
 
 EV_MIDI_CC, EV_HW_CC, EV_NOTE_ON, EV_NOTE_OFF, EV_INIT, EV_SET_FREQ, EV_GATE_ON, EV_GATE_OFF = range(8)
+EV_SAMPLE_SEEK, EV_SAMPLE_LOOP_START, EV_SAMPLE_LOOP_END, EV_SAMPLE_MODE, EV_SAMPLE_TOGGLE, EV_SAMPLE_PLAY, EV_SAMPLE_PAUSE = range(8, 15)
 KIND_BIQUAD, KIND_PORT, KIND_LPF = 0, 1, 2
 MODE_EXACT, MODE_FMA, MODE_FAST = 0, 1, 2
 LAYOUT_FRAMES, LAYOUT_PLANAR = 0, 1
@@ -147,6 +148,19 @@ class Oracle(_Fx):
             self.lib.orc_chorus_run(_fp(par), n, _fp(state), _fp(ring), C.byref(w), _fp(x[a:]), _fp(y[a:]), z - a, 1)
         return y
 
+    def sampler(self, data, ev, out, state=None):
+        """One sample player (oracle restatement of Sample + SampleSoundSource).  data [sample_frames][channels], out
+        [frames][channels] is played INTO (frames not played stay as they are).  Returns the state after the block."""
+        data = np.ascontiguousarray(data, dtype=np.float32).reshape(len(data), out.shape[1])
+        assert out.dtype == np.float32 and out.flags.c_contiguous
+        st = np.zeros(5, dtype=np.uint64) if state is None else np.ascontiguousarray(state, dtype=np.uint64)
+        arr, n_ev = events(ev or [])
+        fn = self.lib.orc_sampler_run
+        fn.argtypes = [C.c_int, _F, C.c_uint64, C.POINTER(C.c_uint64), _EVP, C.c_size_t, _F, C.c_size_t]
+        fn.restype = None
+        fn(data.shape[1], _fp(data), data.shape[0], st.ctypes.data_as(C.POINTER(C.c_uint64)), arr, n_ev, _fp(out), out.shape[0])
+        return st
+
     def noise(self, seed, first_channel, channels, first_frame, frames, scale=1.0, planar=False):
         """Philox white noise in [-1,1): [frames][channels] (or [channels][frames] when planar)."""
         if planar:
@@ -268,6 +282,16 @@ class Reference(_Fx):
         rc = fn(n, sr, _fp(cfg) if cfg is not None else None, m.ctypes.data_as(C.POINTER(C.c_int32)), m.shape[0], arr, n_ev, _fp(out), frames)
         assert rc == 0
         return out
+
+    def sampler(self, data, ev, out):
+        """The reference's own ol::synth::Sample + SampleSoundSource over an in-memory data source."""
+        data = np.ascontiguousarray(data, dtype=np.float32).reshape(len(data), out.shape[1])
+        assert out.dtype == np.float32 and out.flags.c_contiguous
+        arr, n_ev = events(ev or [])
+        fn = self.lib.ref_sampler_run
+        fn.argtypes = [C.c_int, _F, C.c_uint64, _EVP, C.c_size_t, _F, C.c_size_t]
+        fn.restype = C.c_int
+        assert fn(data.shape[1], _fp(data), data.shape[0], arr, n_ev, _fp(out), out.shape[0]) == 0
 
     def control_wire(self, which, controller, value):
         """The reference's own ol::ctl::Control + SimpleSerializer::SerializeControl: which 0 MIDI / 1 float / 2 ADC.

@@ -1067,3 +1067,42 @@ ORC_API void orc_chorus_run(const float *par7, uint32_t ring_len, float *state3,
     state3[0] = phase; state3[1] = y1; state3[2] = y2;
     *w = wp;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Sample playback: ol::synth::Sample behind SampleSoundSource (modules/synthlib/Sample.cpp:9-61, SampleSoundSource.h:16-30)
+// over an in-memory sample, one player.  Restated as one loop over frames:
+//   playing:  read frame `cur` if it exists (SampleDataSource::Read returns 0 past the end) and advance; in Loop mode seek
+//             to loop_start when nothing was read, or when loop_end is set and the new position is past it (Sample.cpp:10-22)
+//   a frame that is not played is left as the caller filled it
+// state5 = {playing, mode, loop_start, loop_end, cur} carries over between calls.  Events: oracle_abi.h.
+ORC_API void orc_sampler_run(int channels, const float *data, uint64_t sample_frames, uint64_t *state5, const olb_event *ev, size_t n_ev,
+                             float *out, size_t frames) {
+    uint64_t playing = state5[0], mode = state5[1], loop_start = state5[2], loop_end = state5[3], cur = state5[4];
+    size_t next = 0;
+    for (size_t t = 0; t < frames; t++) {
+        while (next < n_ev && ev[next].frame <= t) {
+            const olb_event &e = ev[next++];
+            switch (e.kind) {
+                case OLB_EV_GATE_ON: cur = 0; playing = 1; break;      // Seek(0); Play()
+                case OLB_EV_GATE_OFF: playing = 0; break;              // Pause()
+                case OLB_EV_SAMPLE_SEEK: cur = e.a; break;
+                case OLB_EV_SAMPLE_LOOP_START: loop_start = e.a; break;
+                case OLB_EV_SAMPLE_LOOP_END: loop_end = e.a; break;
+                case OLB_EV_SAMPLE_MODE: mode = e.a ? 1 : 0; break;
+                case OLB_EV_SAMPLE_TOGGLE: playing = !playing; break;
+                case OLB_EV_SAMPLE_PLAY: playing = 1; break;
+                case OLB_EV_SAMPLE_PAUSE: playing = 0; break;
+                default: break;
+            }
+        }
+        if (!playing) continue;
+        uint64_t read = 0;
+        if (cur < sample_frames) {
+            for (int c = 0; c < channels; c++) out[t * channels + c] = data[cur * channels + c];
+            read = 1;
+        }
+        cur += read;
+        if (mode == 1 && (!read || (loop_end && cur > loop_end))) cur = loop_start;
+    }
+    state5[0] = playing; state5[1] = mode; state5[2] = loop_start; state5[3] = loop_end; state5[4] = cur;
+}

@@ -20,6 +20,14 @@ enum {
     OLB_EV_SET_FREQ = 5,  // SetFrequency(v)
     OLB_EV_GATE_ON = 6,
     OLB_EV_GATE_OFF = 7,
+    // sample playback (Sample.h:20-38; gates go through SampleSoundSource::GateOn / GateOff, SampleSoundSource.h:21-26)
+    OLB_EV_SAMPLE_SEEK = 8,        // Seek(a)
+    OLB_EV_SAMPLE_LOOP_START = 9,  // SetLoopStart(a)
+    OLB_EV_SAMPLE_LOOP_END = 10,   // SetLoopEnd(a)
+    OLB_EV_SAMPLE_MODE = 11,       // SetPlayMode(a): 0 OneShot, 1 Loop
+    OLB_EV_SAMPLE_TOGGLE = 12,     // TogglePlay()
+    OLB_EV_SAMPLE_PLAY = 13,       // Play()
+    OLB_EV_SAMPLE_PAUSE = 14,      // Pause()
 };
 
 typedef struct olb_event {

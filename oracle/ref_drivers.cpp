@@ -302,6 +302,65 @@ int ref_voicemap_run(int n_voices, float sr, const float *config16, const int32_
     return 0;
 }
 
+// ol::synth::Sample + SampleSoundSource<CH> (Sample.cpp, SampleSoundSource.h) over an in-memory SampleDataSource (the
+// reference's only implementation decodes files through miniaudio, workouts/workout_buddy.h:18-42; the interface is
+// SampleDataSource.h:11-25: Read one frame, return frames read, Seek to a frame).  `out` [frames][channels] arrives
+// pre-filled by the caller: Sample::Process leaves a frame untouched when it is not playing or nothing was read.
+}  // extern "C"
+namespace {
+class MemDataSource : public ol::synth::SampleDataSource {
+public:
+    MemDataSource(const float *data, uint64_t frames, uint64_t channels) : data_(data), frames_(frames), channels_(channels) {}
+    uint64_t GetChannelCount() override { return channels_; }
+    ol::synth::InitStatus Init(t_sample, const char *) override { return ol::synth::Ok; }
+    void Seek(uint64_t frame_index) override { pos_ = frame_index; }
+    uint64_t Read(t_sample *out) override {
+        if (pos_ >= frames_) return 0;
+        for (uint64_t c = 0; c < channels_; c++) out[c] = data_[pos_ * channels_ + c];
+        pos_++;
+        return 1;
+    }
+
+private:
+    const float *data_;
+    uint64_t frames_, channels_, pos_ = 0;
+};
+
+template <int CH>
+void run_sampler(const float *data, uint64_t sample_frames, const olb_event *ev, size_t n_ev, float *out, size_t frames) {
+    MemDataSource src(data, sample_frames, CH);
+    ol::synth::Sample sample(src);
+    ol::synth::SampleSoundSource<CH> source(&sample);
+    source.Init(48000.f);
+    size_t next = 0;
+    for (size_t t = 0; t < frames; t++) {
+        while (next < n_ev && ev[next].frame <= t) {
+            const olb_event &e = ev[next++];
+            switch (e.kind) {
+                case OLB_EV_GATE_ON: source.GateOn(); break;
+                case OLB_EV_GATE_OFF: source.GateOff(); break;
+                case OLB_EV_SAMPLE_SEEK: sample.Seek(e.a); break;
+                case OLB_EV_SAMPLE_LOOP_START: sample.SetLoopStart(e.a); break;
+                case OLB_EV_SAMPLE_LOOP_END: sample.SetLoopEnd(e.a); break;
+                case OLB_EV_SAMPLE_MODE: sample.SetPlayMode(e.a ? ol::synth::Loop : ol::synth::OneShot); break;
+                case OLB_EV_SAMPLE_TOGGLE: sample.TogglePlay(); break;
+                case OLB_EV_SAMPLE_PLAY: sample.Play(); break;
+                case OLB_EV_SAMPLE_PAUSE: sample.Pause(); break;
+                default: break;
+            }
+        }
+        source.Process(out + t * CH);
+    }
+}
+}  // namespace
+extern "C" {
+int ref_sampler_run(int channels, const float *data, uint64_t sample_frames, const olb_event *ev, size_t n_ev, float *out, size_t frames) {
+    if (channels == 1) run_sampler<1>(data, sample_frames, ev, n_ev, out, frames);
+    else if (channels == 2) run_sampler<2>(data, sample_frames, ev, n_ev, out, frames);
+    else return 1;
+    return 0;
+}
+
 // Replays test/fx_test.cpp:25-55 (TEST(FX, Delay)); returns the number of NaN outputs (reference expects 0).
 int ref_test_fx_delay(float *out_48000) {
     RefDelayLine *dl = new RefDelayLine();

@@ -1,7 +1,7 @@
 // C++ callers written the way a reference user writes them (Init -> setters -> Process per frame, then per block), against
 // include/ol_gpu/{FxBank,DattorroBank,ChorusBank,VoiceBank}.hpp.  Built by tests/test_abi.py (link check, CPU) and run by
 // tests/test_cpp_hosts_gpu.py on the GPU box, where the outputs are compared with the oracle.
-//   usage: units_host <filter|delay|reverb|rack|plate|chorus|poly|voicemap> <instances> <frames> <in.f32> <out.f32> [out2.f32]
+//   usage: units_host <filter|delay|reverb|rack|plate|chorus|poly|voicemap|sampler> <instances> <frames> <in.f32> <out.f32> [out2.f32]
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -10,6 +10,7 @@
 #include "ol_gpu/ChorusBank.hpp"
 #include "ol_gpu/DattorroBank.hpp"
 #include "ol_gpu/FxBank.hpp"
+#include "ol_gpu/SamplerBank.hpp"
 #include "ol_gpu/VoiceBank.hpp"
 
 static bool slurp(const char *path, std::vector<float> &v) {
@@ -54,6 +55,13 @@ int main(int argc, char **argv) {
     const char *unit = argv[1];
     const uint32_t I = (uint32_t) atoi(argv[2]), T = (uint32_t) atoi(argv[3]);
     std::vector<float> in((size_t) I * T), out((size_t) I * T), out2;
+    if (!strcmp(unit, "sampler")) {  // in.f32 is one sample of any length
+        FILE *f = fopen(argv[4], "rb");
+        if (!f) return 3;
+        fseek(f, 0, SEEK_END);
+        in.assign((size_t) ftell(f) / sizeof(float), 0.f);
+        fclose(f);
+    }
     if (strcmp(unit, "poly") && strcmp(unit, "voicemap") && !slurp(argv[4], in)) return 3;
     int rc = 0;
     if (!strcmp(unit, "filter")) rc = run_fx<ol::gpu::FilterFxBank>(I, T, in, out);
@@ -144,6 +152,30 @@ int main(int argc, char **argv) {
         }
         rc = bank.status() == OLB_OK ? 0 : 5;
         if (rc) fprintf(stderr, "process failed: %s\n", bank.error().c_str());
+    } else if (!strcmp(unit, "sampler")) {
+        // in.f32 is ONE mono sample of T0 = (file size) frames; every instance plays it: instance i loops [i, i + 40] from a
+        // gate at frame 0, except instance 0 (one-shot from a seek to T0 - 10) -- out [T][I] pre-filled with 9
+        ol::gpu::SamplerBank kit(I, 1);
+        if (kit.Init(48000.f) != ol::gpu::Ok) {
+            fprintf(stderr, "create failed: %s\n", kit.error().c_str());
+            return 4;
+        }
+        const uint32_t id = kit.LoadSample(in.data(), in.size());
+        kit.SetSample(id);
+        for (uint32_t i = 1; i < I; i++) {
+            kit.SetPlayMode(OLB_SAMPLE_LOOP, i, 1);
+            kit.SetLoopStart(i, i, 1);
+            kit.SetLoopEnd(i + 40, i, 1);
+        }
+        kit.GateOn();
+        kit.Seek(in.size() - 10, 0, 1);
+        out.assign((size_t) T * I, 9.f);
+        uint32_t t = 0;
+        for (; t < 2 && t < T; t++) kit.Process(&out[(size_t) t * I]);
+        if (t < T) kit.ProcessBlock(&out[(size_t) t * I], T - t);
+        rc = kit.status() == OLB_OK ? 0 : 5;
+        if (rc) fprintf(stderr, "process failed: %s\n", kit.error().c_str());
+        printf("%llu\n", (unsigned long long) kit.Position(0));
     } else {
         fprintf(stderr, "unknown unit %s\n", unit);
         return 2;

@@ -54,6 +54,26 @@ VOICEMAP_EVENTS = [(0, loader.EV_MIDI_CC, 41, 40, 1), (0, loader.EV_MIDI_CC, 42,
                    (2400, loader.EV_NOTE_ON, 42, 64), (2600, loader.EV_MIDI_CC, 41, 20, 7)]
 
 
+# Sample playback scenarios (modules/synthlib/Sample.cpp, SampleSoundSource.h): seed -> a random sample and a random script
+# of gates / seeks / loop points (some past the end of the sample) / mode changes / play toggles.
+def sampler_scenario(seed, channels, sample_frames=200, frames=1500, n_events=40):
+    L = loader
+    r = np.random.default_rng(seed)
+    data = r.standard_normal((sample_frames, channels)).astype(np.float32)
+    kinds = [L.EV_GATE_ON, L.EV_GATE_OFF, L.EV_SAMPLE_SEEK, L.EV_SAMPLE_LOOP_START, L.EV_SAMPLE_LOOP_END, L.EV_SAMPLE_MODE,
+             L.EV_SAMPLE_TOGGLE, L.EV_SAMPLE_PLAY, L.EV_SAMPLE_PAUSE]
+    ev = []
+    for f in sorted(r.integers(0, frames, n_events)):
+        k = kinds[r.integers(0, len(kinds))]
+        a = int(r.integers(0, sample_frames + 30)) if k in (L.EV_SAMPLE_SEEK, L.EV_SAMPLE_LOOP_START, L.EV_SAMPLE_LOOP_END) else int(r.integers(0, 2))
+        ev.append((int(f), k, a, 0.0))
+    return data, ev, frames
+
+
+SAMPLER_CASES = [(seed, 1 + seed % 2) for seed in range(24)]
+SAMPLER_FILL = 7.0  # what the output holds before the player runs: frames it does not play must keep it
+
+
 def sha(a):
     return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
 
@@ -109,6 +129,13 @@ def main():
     v["scale_args"] = np.array(sc, dtype=np.float32)
     v["scale_out"] = np.array([ref.scale(*a) for a in sc], dtype=np.float32)
     np.savez_compressed(os.path.join(HERE, "synth.npz"), **v)
+    sp = {}
+    for seed, ch in SAMPLER_CASES:
+        data, ev, frames = sampler_scenario(seed, ch)
+        o = np.full((frames, ch), SAMPLER_FILL, dtype=np.float32)
+        ref.sampler(data, ev, o)
+        sp[f"out_{seed}"] = o
+    np.savez_compressed(os.path.join(HERE, "sampler.npz"), **sp)
     print("wrote", [f for f in os.listdir(HERE) if f.endswith(".npz")])
 
 

@@ -74,3 +74,20 @@ def test_voicemap_mirror(tmp_path):
     run("voicemap", 6, want.shape[0], None, tmp_path)
     y = np.fromfile(tmp_path / "out.f32", dtype=np.float32)
     assert np.abs(y - want).max() <= 5e-5
+
+
+def test_sampler_mirror(orc, tmp_path):
+    """ol::gpu::SamplerBank driven like the reference's Sample / SampleSoundSource, against the oracle restatement."""
+    I, T, n = 40, 500, 300
+    data = orc.noise(54, 0, 1, 0, n, 0.5)[:, 0].copy()
+    out = run("sampler", I, T, data, tmp_path)
+    y = np.fromfile(tmp_path / "out.f32", dtype=np.float32).reshape(T, I)
+    L = loader
+    for i in (0, 1, 7, 39):
+        ev = [(0, L.EV_GATE_ON, 0, 0.0), (0, L.EV_SAMPLE_SEEK, n - 10, 0.0)] if i == 0 else \
+             [(0, L.EV_SAMPLE_MODE, 1, 0.0), (0, L.EV_SAMPLE_LOOP_START, i, 0.0), (0, L.EV_SAMPLE_LOOP_END, i + 40, 0.0), (0, L.EV_GATE_ON, 0, 0.0)]
+        want = np.full((T, 1), 9.0, dtype=np.float32)
+        st = orc.sampler(data, ev, want)
+        assert np.array_equal(bits(y[:, i]), bits(want[:, 0])), i
+        if i == 0:
+            assert int(out.split()[0]) == int(st[4]) == n

@@ -91,6 +91,24 @@ def test_voicemap_matches_reference_golden(orc):
     assert np.abs(g["voicemap"]).max() > 0.1
 
 
+def test_sampler_matches_reference_golden(orc):
+    """tests/golden/sampler.npz: the reference's own Sample + SampleSoundSource (Sample.cpp compiled from where it lies) on 24
+    random samples and scripts; the restatement gives the same bits, in one call or cut anywhere with its state carried."""
+    g = np.load(os.path.join(G, "sampler.npz"))
+    for seed, ch in mg.SAMPLER_CASES:
+        data, ev, frames = mg.sampler_scenario(seed, ch)
+        want = g[f"out_{seed}"]
+        got = np.full((frames, ch), mg.SAMPLER_FILL, dtype=np.float32)
+        orc.sampler(data, ev, got)
+        assert np.array_equal(bits(got), bits(want)), seed
+        assert (want != mg.SAMPLER_FILL).any() and (want == mg.SAMPLER_FILL).any()  # played and untouched frames both occur
+        cut = 1 + 61 * seed
+        two = np.full((frames, ch), mg.SAMPLER_FILL, dtype=np.float32)
+        st = orc.sampler(data, [e for e in ev if e[0] < cut], two[:cut])
+        orc.sampler(data, [(e[0] - cut,) + tuple(e[1:]) for e in ev if e[0] >= cut], two[cut:], state=st)
+        assert np.array_equal(bits(two), bits(want)), (seed, cut)
+
+
 def test_scale_matches_reference_golden(orc):
     g = np.load(os.path.join(G, "synth.npz"))
     got = np.array([orc.scale(*a) for a in g["scale_args"]], dtype=np.float32)

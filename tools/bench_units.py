@@ -177,14 +177,50 @@ def bench_voices(a):
         dist.destroy_process_group()
 
 
+def bench_sampler(a):
+    """Sample playback bank: a kit of 128 one-second samples, every instance looping one of them
+    from its own start offset (the pool is 24.6 MB: it lives in L2, the output stream goes to HBM)."""
+    import numpy as np
+    import torch
+    from ol_dsp_b200 import SamplerBank, sampler
+    I, F = a.instances, a.frames
+    b = SamplerBank(I, 1)
+    r = np.random.default_rng(7)
+    ids = [b.LoadSample(r.standard_normal(48000).astype(np.float32)) for _ in range(128)]
+    b.SetSample(np.array([ids[i % 128] for i in range(I)], dtype=np.uint32))
+    b.SetPlayMode(sampler.LOOP)
+    b.Play()
+    for k in range(64):  # 64 start offsets across the bank
+        b.Seek(741 * k, first=k * (I // 64), count=I // 64)
+    y = torch.zeros((F, I), dtype=torch.float32, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+    dt = timed(lambda: b.ProcessDevice(y.data_ptr(), F, st), a.steps)
+    units = I * F
+    line = {"unit": "sampler", "metric": "instance-samples/s", "value": units / dt, "ms_per_step": dt * 1e3, "instances": I, "frames": F,
+            "roofline": {"bound": "hbm", "algorithmic_bytes_per_unit": 8, "achieved": 8 * units / dt / 1e9, "peak": peaks(), "unit": "GB/s",
+                         "frac": 8 * units / dt / 1e9 / peaks()},
+            "kernel": "k_sampler", "checksum": float(y.double().sum().item())}
+    if a.cpu:
+        import time
+        from oracle import loader
+        data = r.standard_normal(48000).astype(np.float32)
+        out = np.zeros((F, 1), dtype=np.float32)
+        t0 = time.perf_counter()
+        loader.oracle().sampler(data, [(0, loader.EV_SAMPLE_MODE, 1, 0.0), (0, loader.EV_GATE_ON, 0, 0.0)], out)
+        line["cpu_baseline"] = {"value": F / (time.perf_counter() - t0), "unit": "instance-samples/s", "cores": 1, "kind": "port",
+                                "sample": f"1 instance x {F} frames, the oracle's Sample restatement"}
+    print(json.dumps(line), flush=True)
+    b.close()
+
+
 if __name__ == "__main__":
     p = argparse.ArgumentParser()
-    p.add_argument("unit", choices=["dattorro", "filterfx", "delayfx", "fxrack", "voices", "chorus"])
+    p.add_argument("unit", choices=["dattorro", "filterfx", "delayfx", "fxrack", "voices", "chorus", "sampler"])
     p.add_argument("--instances", type=int, default=8192)
     p.add_argument("--frames", type=int, default=48000)
     p.add_argument("--steps", type=int, default=3)
     p.add_argument("--cpu", action="store_true")
     a = p.parse_args()
     from ol_dsp_b200 import fx as _fx
-    {"voices": bench_voices, "dattorro": bench_dattorro, "chorus": bench_chorus, "filterfx": lambda a: bench_fx(a, _fx.FILTER, "filterfx", 8),
+    {"voices": bench_voices, "dattorro": bench_dattorro, "chorus": bench_chorus, "sampler": bench_sampler, "filterfx": lambda a: bench_fx(a, _fx.FILTER, "filterfx", 8),
      "delayfx": lambda a: bench_fx(a, _fx.DELAY, "delayfx", 16), "fxrack": lambda a: bench_fx(a, _fx.RACK, "fxrack", 16)}[a.unit](a)
