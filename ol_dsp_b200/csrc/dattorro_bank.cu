@@ -416,6 +416,266 @@ __global__ void __launch_bounds__(kPfThreads) k_dattorro_rp(const float *__restr
     lp[2 * (size_t) I + inst] = z_b;
 }
 
+// ------------------------------------------------------------------------------------------------
+// k_dattorro_split: the network cut over the four warps of a CTA (32 instances).  One warp running the whole plate
+// spends ~710 cycles per frame on one dependent chain (pre-filter -> four input diffusers -> tank half A -> tank half B ->
+// output sums) while 8 192 instances are only 256 warps for 592 schedulers.  The pieces are coupled loosely:
+//   warp 0  input    pre-delay, pre-filter, the four input diffusers            -> x, handed on through shared memory
+//   warp 1  tank A   x + decay * (POSTB tap), diffuser 1A, delay, damping, diffuser 2A, delay     (verb.cpp:281-287)
+//   warp 2  tank B   the same with A <-> B                                                        (verb.cpp:288-294)
+//   warp 3  output   the 14 output taps and the two sums                                          (verb.cpp:302-326)
+// x is the only same-frame dependency; the two halves see each other only through taps >= 3 163 frames back and the output
+// taps are >= 120 frames back, so it suffices that no warp runs more than kXs tiles (of 32 frames) ahead of another and
+// that the output warp starts a tile after both tank warps finished it.  Hand-over per tile with mbarriers, one arrival
+// per warp (lane 0 after __syncwarp): x_full (input -> tanks), done (tanks -> output), x_empty (tanks + output -> input).
+// Ring addressing is k_dattorro_rp's (blocks inside which no ring index wraps), every warp fetching only ITS taps D frames
+// ahead.  Same reads, same arithmetic, same writes: bit-exact.
+constexpr int kSplitSlots = 14;  // most taps any one warp fetches (the output warp)
+constexpr int kXs = 4;           // x tiles in flight
+constexpr int kXt = 32;          // frames per tile
+
+template <int D>
+__global__ void __launch_bounds__(128) k_dattorro_split(const float *in, float *out_l, float *out_r, uint32_t frames, uint32_t I, float *slab,
+                                                        float *lp, const float *__restrict__ par, const __grid_constant__ PlateGeom g0,
+                                                        uint32_t t0) {
+    extern __shared__ __align__(16) float sm[];  // [D][kSplitSlots][128] prefetch slots, [kXs][kXt][32] x tiles, barriers
+    float *xs = sm + (size_t) D * kSplitSlots * 128;
+    uint64_t *x_full = reinterpret_cast<uint64_t *>(xs + (size_t) kXs * kXt * 32), *x_empty = x_full + kXs, *done = x_empty + kXs;
+    const uint32_t lane = threadIdx.x & 31, role = threadIdx.x >> 5, inst = blockIdx.x * 32 + lane;
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < kXs; s++) {
+            mbar_init(&x_full[s], 1);
+            mbar_init(&x_empty[s], 3);
+            mbar_init(&done[s], 2);
+        }
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (inst >= I) return;  // lane 0 of every warp is live; arrivals are lane 0's
+    float *mine = sm + threadIdx.x;
+    auto SLOT = [&](uint32_t d, int k) -> float * { return mine + ((size_t) d * kSplitSlots + k) * 128; };
+    const uint32_t stride = I * (uint32_t) sizeof(float);
+    char *lane_slab = reinterpret_cast<char *>(slab + inst);
+    auto at = [&](uint32_t ring, uint32_t idx) -> char * { return lane_slab + (uint64_t) (g0.base[ring] + idx) * stride; };
+    auto row = [&](char *p, uint32_t r) -> float * { return reinterpret_cast<float *>(p + (uint64_t) r * stride); };
+    constexpr int kTapRingL[7] = {DV_PDB, DV_PDB, DV_DD2B, DV_POSTB, DV_PDA, DV_DD2A, DV_POSTA};
+    constexpr int kTapRingR[7] = {DV_PDA, DV_PDA, DV_DD2A, DV_POSTA, DV_PDB, DV_DD2B, DV_POSTB};
+    constexpr int kMainRings[12] = {DV_IN0, DV_IN1, DV_IN2, DV_IN3, DV_POSTB, DV_POSTA, DV_DD1A, DV_DD1B, DV_PDA, DV_PDB, DV_DD2A, DV_DD2B};
+
+    uint32_t t = t0, ta = t0, off_a = g0.off[DV_DD1A], off_b = g0.off[DV_DD1B];  // ta / off_*: state of the FETCH stream
+    // frames from n on that share one set of ring pointers: no ring index of any warp wraps, no excursion step, no tile edge
+    auto block_len = [&](uint32_t n) -> uint32_t {
+        uint32_t B = min(frames - n, (uint32_t) kXt - (n & (kXt - 1)));
+        const uint32_t e = ta & 0x7ffu;
+        B = min(B, e ? 0x800u - e : 0x800u);
+#pragma unroll
+        for (int ring = 0; ring < DV_RINGS; ring++) B = min(B, g0.mask[ring] + 1 - (t & g0.mask[ring]));
+#pragma unroll
+        for (int k = 0; k < 12; k++) {
+            const int ring = kMainRings[k];
+            const uint32_t off = ring == DV_DD1A ? off_a : (ring == DV_DD1B ? off_b : g0.off[ring]);
+            B = min(B, g0.mask[ring] + 1 - ((ta + off) & g0.mask[ring]));
+        }
+#pragma unroll
+        for (int i = 0; i < 7; i++) {
+            B = min(B, g0.mask[kTapRingL[i]] + 1 - ((ta + 1 + g0.tap_l[i][1]) & g0.mask[kTapRingL[i]]));
+            B = min(B, g0.mask[kTapRingR[i]] + 1 - ((ta + 1 + g0.tap_r[i][1]) & g0.mask[kTapRingR[i]]));
+        }
+        return B;
+    };
+    auto tile_wait = [&](uint64_t *bar, uint32_t tile, bool previous_phase) {
+        const uint32_t turn = tile / kXs;
+        mbar_wait(&bar[tile % kXs], (previous_phase ? turn - 1 : turn) & 1);
+    };
+    auto tile_arrive = [&](uint64_t *bar, uint32_t tile) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar[tile % kXs]);
+    };
+    uint32_t slot = 0;
+
+    if (role == 0) {  // ---------------- input section
+        const float pre_filter = par[0 * (size_t) I + inst], in_diff1 = par[1 * (size_t) I + inst], in_diff2 = par[2 * (size_t) I + inst];
+        const uint32_t pre_off = __float_as_uint(par[7 * (size_t) I + inst]);
+        float z_pre = lp[inst];
+        const uint32_t pre_len = (g0.mask[DV_PRE] + 1 - pre_off) & g0.mask[DV_PRE];
+        const bool pre_same = pre_len == 0, pre_direct = pre_len <= (uint32_t) D;
+        const char *lane_in = reinterpret_cast<const char *>(in + inst);
+        constexpr int kRings[4] = {DV_IN0, DV_IN1, DV_IN2, DV_IN3};
+        for (uint32_t d = 0; d < (uint32_t) D; d++) {
+            if (d < frames) {
+                excursion_step(ta, off_a, off_b);
+                cp_async4(SLOT(d, 0), in + (size_t) d * I + inst);
+                cp_async4(SLOT(d, 1), row(at(DV_PRE, (ta + pre_off) & g0.mask[DV_PRE]), 0));
+#pragma unroll
+                for (int k = 0; k < 4; k++) cp_async4(SLOT(d, 2 + k), row(at(kRings[k], (ta + g0.off[kRings[k]]) & g0.mask[kRings[k]]), 0));
+                ta = (ta + 1) & 0xffffu;
+            }
+            cp_async_commit();
+        }
+        for (uint32_t n = 0; n < frames;) {
+            excursion_step(ta, off_a, off_b);  // acts only when (ta & 0x7ff) == 0, which can only be a block's first frame
+            const uint32_t B = block_len(n), tile = n / kXt;
+            if ((n & (kXt - 1)) == 0 && tile >= (uint32_t) kXs) tile_wait(x_empty, tile, true);
+            char *wp[5], *rp[4];
+            wp[0] = at(DV_PRE, t & g0.mask[DV_PRE]);
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                wp[1 + k] = at(kRings[k], t & g0.mask[kRings[k]]);
+                rp[k] = at(kRings[k], (ta + g0.off[kRings[k]]) & g0.mask[kRings[k]]);
+            }
+            float *xrow = xs + ((size_t) (tile % kXs) * kXt + (n & (kXt - 1))) * 32 + lane;
+            for (uint32_t r = 0; r < B; r++) {
+                cp_async_wait<D - 1>();
+                float v[6];
+#pragma unroll
+                for (int k = 0; k < 6; k++) v[k] = *SLOT(slot, k);
+                if (n + r + D < frames) {
+                    cp_async4(SLOT(slot, 0), reinterpret_cast<const float *>(lane_in + (uint64_t) (n + r + D) * stride));
+                    cp_async4(SLOT(slot, 1), row(at(DV_PRE, (ta + r + pre_off) & g0.mask[DV_PRE]), 0));
+#pragma unroll
+                    for (int k = 0; k < 4; k++) cp_async4(SLOT(slot, 2 + k), row(rp[k], r));
+                }
+                cp_async_commit();
+                const float xin = v[0];
+                float r_pre = v[1];
+                if (pre_direct) r_pre = pre_same ? xin : *row(at(DV_PRE, (t + r + pre_off) & g0.mask[DV_PRE]), 0);
+                float w;
+                *row(wp[0], r) = xin;
+                float x = lowpass(z_pre, pre_filter, r_pre);
+                x = allpass(v[2], in_diff1, x, w); *row(wp[1], r) = w;
+                x = allpass(v[3], in_diff1, x, w); *row(wp[2], r) = w;
+                x = allpass(v[4], in_diff2, x, w); *row(wp[3], r) = w;
+                x = allpass(v[5], in_diff2, x, w); *row(wp[4], r) = w;
+                xrow[(size_t) r * 32] = x;
+                slot = slot + 1 == (uint32_t) D ? 0 : slot + 1;
+            }
+            n += B;
+            t = (t + B) & 0xffffu;
+            ta = (ta + B) & 0xffffu;
+            if ((n & (kXt - 1)) == 0 || n == frames) tile_arrive(x_full, tile);
+        }
+        cp_async_wait<0>();
+        lp[inst] = z_pre;
+    } else if (role <= 2) {  // ---------------- tank half A (role 1) / B (role 2)
+        const bool A = role == 1;
+        const float decay_diff1 = par[3 * (size_t) I + inst], damping = par[4 * (size_t) I + inst], decay = par[5 * (size_t) I + inst];
+        const float decay_diff2 = par[6 * (size_t) I + inst];
+        float z = lp[(size_t) (A ? 1 : 2) * I + inst];
+        const int r_cross = A ? DV_POSTB : DV_POSTA, r_dd1 = A ? DV_DD1A : DV_DD1B, r_pd = A ? DV_PDA : DV_PDB, r_dd2 = A ? DV_DD2A : DV_DD2B,
+                  r_post = A ? DV_POSTA : DV_POSTB;
+        auto fetch_idx = [&](int k) -> uint32_t {  // ring index of tap k of the frame whose counter is ta
+            const int ring = k == 0 ? r_cross : k == 1 ? r_dd1 : k == 2 ? r_pd : r_dd2;
+            const uint32_t off = k == 1 ? (A ? off_a : off_b) : g0.off[ring];
+            return (ta + off) & g0.mask[ring];
+        };
+        auto tap_ring = [&](int k) -> int { return k == 0 ? r_cross : k == 1 ? r_dd1 : k == 2 ? r_pd : r_dd2; };
+        for (uint32_t d = 0; d < (uint32_t) D; d++) {
+            if (d < frames) {
+                excursion_step(ta, off_a, off_b);
+#pragma unroll
+                for (int k = 0; k < 4; k++) cp_async4(SLOT(d, k), row(at(tap_ring(k), fetch_idx(k)), 0));
+                ta = (ta + 1) & 0xffffu;
+            }
+            cp_async_commit();
+        }
+        for (uint32_t n = 0; n < frames;) {
+            excursion_step(ta, off_a, off_b);  // acts only when (ta & 0x7ff) == 0, which can only be a block's first frame
+            const uint32_t B = block_len(n), tile = n / kXt;
+            if ((n & (kXt - 1)) == 0) tile_wait(x_full, tile, false);
+            char *wp[4], *rp[4];
+            wp[0] = at(r_dd1, t & g0.mask[r_dd1]);
+            wp[1] = at(r_pd, t & g0.mask[r_pd]);
+            wp[2] = at(r_dd2, t & g0.mask[r_dd2]);
+            wp[3] = at(r_post, t & g0.mask[r_post]);
+#pragma unroll
+            for (int k = 0; k < 4; k++) rp[k] = at(tap_ring(k), fetch_idx(k));
+            const float *xrow = xs + ((size_t) (tile % kXs) * kXt + (n & (kXt - 1))) * 32 + lane;
+            for (uint32_t r = 0; r < B; r++) {
+                cp_async_wait<D - 1>();
+                float v[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++) v[k] = *SLOT(slot, k);
+                if (n + r + D < frames) {
+#pragma unroll
+                    for (int k = 0; k < 4; k++) cp_async4(SLOT(slot, k), row(rp[k], r));
+                }
+                cp_async_commit();
+                const float x = xrow[(size_t) r * 32];
+                float w;
+                float y = __fadd_rn(x, __fmul_rn(v[0], decay));
+                y = allpass(v[1], -decay_diff1, y, w); *row(wp[0], r) = w;
+                *row(wp[1], r) = y; y = v[2];
+                y = lowpass(z, damping, y);
+                y = __fmul_rn(y, decay);
+                y = allpass(v[3], decay_diff2, y, w); *row(wp[2], r) = w;
+                *row(wp[3], r) = y;
+                slot = slot + 1 == (uint32_t) D ? 0 : slot + 1;
+            }
+            n += B;
+            t = (t + B) & 0xffffu;
+            ta = (ta + B) & 0xffffu;
+            if ((n & (kXt - 1)) == 0 || n == frames) {
+                tile_arrive(done, tile);
+                if (lane == 0) mbar_arrive(&x_empty[tile % kXs]);
+            }
+        }
+        cp_async_wait<0>();
+        lp[(size_t) (A ? 1 : 2) * I + inst] = z;
+    } else {  // ---------------- output taps
+        char *lane_l = reinterpret_cast<char *>(out_l + inst), *lane_r = reinterpret_cast<char *>(out_r + inst);
+        for (uint32_t d = 0; d < (uint32_t) D; d++) {
+            if (d < frames) {
+                excursion_step(ta, off_a, off_b);
+                const uint32_t t1 = (ta + 1) & 0xffffu;
+#pragma unroll
+                for (int i = 0; i < 7; i++) {
+                    cp_async4(SLOT(d, i), row(at(kTapRingL[i], (t1 + g0.tap_l[i][1]) & g0.mask[kTapRingL[i]]), 0));
+                    cp_async4(SLOT(d, 7 + i), row(at(kTapRingR[i], (t1 + g0.tap_r[i][1]) & g0.mask[kTapRingR[i]]), 0));
+                }
+                ta = t1;
+            }
+            cp_async_commit();
+        }
+        for (uint32_t n = 0; n < frames;) {
+            excursion_step(ta, off_a, off_b);  // acts only when (ta & 0x7ff) == 0, which can only be a block's first frame
+            const uint32_t B = block_len(n), tile = n / kXt;
+            if ((n & (kXt - 1)) == 0) tile_wait(done, tile, false);
+            char *opl[7], *opr[7];
+#pragma unroll
+            for (int i = 0; i < 7; i++) {
+                opl[i] = at(kTapRingL[i], (ta + 1 + g0.tap_l[i][1]) & g0.mask[kTapRingL[i]]);
+                opr[i] = at(kTapRingR[i], (ta + 1 + g0.tap_r[i][1]) & g0.mask[kTapRingR[i]]);
+            }
+            for (uint32_t r = 0; r < B; r++) {
+                cp_async_wait<D - 1>();
+                float v[14];
+#pragma unroll
+                for (int k = 0; k < 14; k++) v[k] = *SLOT(slot, k);
+                if (n + r + D < frames) {
+#pragma unroll
+                    for (int i = 0; i < 7; i++) {
+                        cp_async4(SLOT(slot, i), row(opl[i], r));
+                        cp_async4(SLOT(slot, 7 + i), row(opr[i], r));
+                    }
+                }
+                cp_async_commit();
+                float a = __fadd_rn(v[0], v[1]); a = __fsub_rn(a, v[2]); a = __fadd_rn(a, v[3]);
+                a = __fsub_rn(a, v[4]); a = __fsub_rn(a, v[5]); a = __fadd_rn(a, v[6]);
+                float b = __fadd_rn(v[7], v[8]); b = __fsub_rn(b, v[9]); b = __fadd_rn(b, v[10]);
+                b = __fsub_rn(b, v[11]); b = __fsub_rn(b, v[12]); b = __fadd_rn(b, v[13]);
+                *row(lane_l, n + r) = a;
+                *row(lane_r, n + r) = b;
+                slot = slot + 1 == (uint32_t) D ? 0 : slot + 1;
+            }
+            n += B;
+            t = (t + B) & 0xffffu;
+            ta = (ta + B) & 0xffffu;
+            if ((n & (kXt - 1)) == 0 || n == frames) tile_arrive(x_empty, tile);
+        }
+        cp_async_wait<0>();
+    }
+}
+
 }  // namespace olb
 
 using namespace olb;
@@ -570,7 +830,8 @@ OLB_API int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *ou
         OLB_CUDA(cudaStreamSynchronize(st));  // par_host may change right after we return
         h->par_dirty = false;
     }
-    // OLB_PLATE_KERNEL=simple|pf selects the one-frame-at-a-time / the index-arithmetic pipelined kernel (default: k_dattorro_rp);
+    // OLB_PLATE_KERNEL=simple|pf|rp selects the one-frame-at-a-time / the index-arithmetic pipelined / the one-warp ring-pointer
+    // kernel (default: k_dattorro_split);
     // OLB_PLATE_LANES=32|16|8 overrides the active lanes per warp of the pf one (default 32: narrower warps measured no faster, profiles/r01_run14_units_lane_sweep.jsonl)
     const char *ek = getenv("OLB_PLATE_KERNEL"), *el = getenv("OLB_PLATE_LANES");
     const int forced = el ? atoi(el) : 0;
@@ -589,7 +850,14 @@ OLB_API int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *ou
     } while (0)
         if (lanes == 32) OLB_PLATE_GO(32); else if (lanes == 16) OLB_PLATE_GO(16); else OLB_PLATE_GO(8);
 #undef OLB_PLATE_GO
-    } else {  // default: block-wise ring pointers; row offsets are 32-bit (frame x instances x 4 bytes)
+    } else if (!ek || strcmp(ek, "rp")) {  // default: the network cut over the four warps of a CTA
+        constexpr int D = 8;
+        OLB_ARG((uint64_t) frames * h->I * sizeof(float) < (1ull << 62), "olb_dattorro_process: block too large");
+        constexpr size_t smem = ((size_t) D * kSplitSlots * 128 + (size_t) kXs * kXt * 32) * sizeof(float) + 3 * kXs * sizeof(uint64_t);
+        OLB_CUDA(cudaFuncSetAttribute(k_dattorro_split<D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+        k_dattorro_split<D><<<(h->I + 31) / 32, 128, smem, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I, h->d_slab, h->d_lp,
+                                                               h->d_par, h->geom, h->t);
+    } else {  // OLB_PLATE_KERNEL=rp: one warp per 32 instances, block-wise ring pointers
         constexpr int D = 8;
         OLB_ARG((uint64_t) frames * h->I * sizeof(float) < (1ull << 62), "olb_dattorro_process: block too large");
         constexpr size_t smem = (size_t) D * kPfSlots * kPfThreads * sizeof(float);

@@ -113,11 +113,11 @@ def test_impulse_response_properties():
     b.close()
 
 
-@pytest.mark.parametrize("env", [{}, {"OLB_PLATE_KERNEL": "simple"}] + [{"OLB_PLATE_KERNEL": "pf", "OLB_PLATE_LANES": l} for l in ("32", "16", "8")],
+@pytest.mark.parametrize("env", [{}, {"OLB_PLATE_KERNEL": "rp"}, {"OLB_PLATE_KERNEL": "simple"}] + [{"OLB_PLATE_KERNEL": "pf", "OLB_PLATE_LANES": l} for l in ("32", "16", "8")],
                          ids=lambda e: "-".join(e.values()) or "default")
 def test_every_kernel_variant_is_bit_exact(orc, monkeypatch, env):
-    """The default kernel (block-wise ring pointers), the one-frame kernel and the index-arithmetic pipelined kernel at
-    32 / 16 / 8 active lanes per warp compute the same bits; chunks straddle the 2 048-frame excursion steps and the
+    """The default kernel (the network cut over four warps), the one-warp ring-pointer kernel, the one-frame kernel and the
+    index-arithmetic pipelined kernel at 32 / 16 / 8 active lanes per warp compute the same bits; chunks straddle the 2 048-frame excursion steps and the
     16-bit counter wrap is crossed (a first chunk of 63 000 silent frames)."""
     for k, v in env.items():
         monkeypatch.setenv(k, v)
