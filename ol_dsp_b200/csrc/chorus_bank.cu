@@ -132,7 +132,7 @@ __device__ __forceinline__ void chorus_audio_batch(float *col, ChorusLane &c, fl
 
 __device__ __forceinline__ void mbar_arrive_all(uint64_t *bar) { mbar_arrive(bar); }
 
-template <int TB, int STAGES, bool TMA>
+template <int TB, int STAGES, bool TMA, bool ring_in_smem>
 __global__ void __launch_bounds__(96) k_chorus(const __grid_constant__ TensorMap tm_in, const __grid_constant__ TensorMap tm_out,
                                                const float *in, float *out, uint32_t frames, uint32_t I, uint32_t R,
                                                const float *__restrict__ par, float *state, float *ring_all,
@@ -144,8 +144,11 @@ __global__ void __launch_bounds__(96) k_chorus(const __grid_constant__ TensorMap
     float *tiles = reinterpret_cast<float *>(smem_raw);          // [STAGES][TB][L]   audio tiles (TMA)
     uint32_t *kq = reinterpret_cast<uint32_t *>(tiles + (size_t) STAGES * TB * L);  // [2][TB][L]  whole samples of delay
     float *frq = reinterpret_cast<float *>(kq + (size_t) 2 * TB * L);               // [2][TB][L]  fraction of delay
-    float *ring = frq + (size_t) 2 * TB * L;                     // [R][L]
-    float *tab = ring + (size_t) R * L;                          // [513] (+3 pad)
+    // [R][L] ring: shared-memory resident for the launch when it fits (sample rates up to ~53 kHz), else used in place in HBM
+    // (same code through generic pointers: the ring is lane-fastest, so its rows stay coalesced there)
+    float *ring_s = frq + (size_t) 2 * TB * L;
+    float *tab = ring_s + (size_t) (ring_in_smem ? R : 0) * L;   // [513] (+3 pad)
+    float *ring = ring_in_smem ? ring_s : ring_all + (size_t) blockIdx.x * R * L;
     uint64_t *full = reinterpret_cast<uint64_t *>(tab + kChTab + 4);  // [STAGES] tile barriers, [STAGES] = ring barrier
     uint64_t *lfo_full = full + STAGES + 1, *lfo_empty = lfo_full + 2;  // [2] each, 32 arrivals per phase
     const uint32_t ring_bytes = R * L * (uint32_t) sizeof(float);
@@ -197,8 +200,10 @@ __global__ void __launch_bounds__(96) k_chorus(const __grid_constant__ TensorMap
 
     // ---- audio warp ----
     if (lane == 0) {
-        mbar_arrive_expect_tx(&full[STAGES], ring_bytes);
-        bulk_load_1d(ring, ring_g, ring_bytes, &full[STAGES]);
+        if (ring_in_smem) {
+            mbar_arrive_expect_tx(&full[STAGES], ring_bytes);
+            bulk_load_1d(ring, ring_g, ring_bytes, &full[STAGES]);
+        }
         if (TMA) {
             for (uint32_t j = 0; j < (uint32_t) (STAGES - 1) && j < ntiles; j++) {
                 mbar_arrive_expect_tx(&full[j], kTileBytes);
@@ -209,7 +214,7 @@ __global__ void __launch_bounds__(96) k_chorus(const __grid_constant__ TensorMap
     float *ring_col = ring + lane;
     uint32_t wp = w0;
     __syncwarp();
-    mbar_wait(&full[STAGES], 0);
+    if (ring_in_smem) mbar_wait(&full[STAGES], 0);
 
     for (uint32_t i = 0; i < ntiles; i++) {
         const uint32_t st = TMA ? i % STAGES : 0, ph = (i / STAGES) & 1, ls = i & 1;
@@ -257,8 +262,10 @@ __global__ void __launch_bounds__(96) k_chorus(const __grid_constant__ TensorMap
     fence_async_smem();
     __syncwarp();
     if (lane == 0) {
-        bulk_store_1d(ring_g, ring, ring_bytes);
-        tma_commit();
+        if (ring_in_smem) {
+            bulk_store_1d(ring_g, ring, ring_bytes);
+            tma_commit();
+        }
         tma_wait_all<0>();
     }
     if (live) {
@@ -287,10 +294,11 @@ struct olb_chorus {
 };
 
 constexpr int kChTB = 64, kChStages = 4;
-static size_t chorus_smem(uint32_t R) {
+static size_t chorus_smem(uint32_t R) {  // with the ring resident; R = 0: ring left in HBM
     return (size_t) kChStages * kChTB * kChL * sizeof(float) + (size_t) 4 * kChTB * kChL * sizeof(float) + (size_t) R * kChL * sizeof(float) +
            (kChTab + 4) * sizeof(float) + (kChStages + 1 + 4) * sizeof(uint64_t);
 }
+static bool chorus_ring_fits(uint32_t R) { return chorus_smem(R) <= 227u * 1024u; }
 // the specification's ring length (orc_chorus_ring_len: it only enters the arithmetic through the clamp dt <= len - 2) ...
 static uint32_t chorus_spec_len(float sr) { return (uint32_t) ceil(2.0 * 12.0 * (double) sr / 1000.0) + 4u; }
 // ... and the bank's own: kChB spare slots so that a batch may write ahead of its reads
@@ -323,7 +331,7 @@ static void chorus_free(olb_chorus *h) {
 
 static int chorus_reset(olb_chorus *h, float sr) {
     const uint32_t R = chorus_ring_len(sr);
-    OLB_ARG(sr > 0.f && chorus_smem(R) <= 227u * 1024u, "olb_chorus: sample rate %g needs a %u-frame ring that does not fit in shared memory", sr, R);
+    OLB_ARG(sr > 0.f && sr <= 768000.f, "olb_chorus: sample rate %g out of range", sr);
     if (R != h->R || !h->d_ring) {
         cudaFree(h->d_ring);
         h->d_ring = nullptr;
@@ -418,7 +426,8 @@ OLB_API int olb_chorus_process(olb_chorus *h, const float *in_dev, float *out_de
         OLB_CUDA(cudaStreamSynchronize(st));
         h->dirty = false;
     }
-    const size_t smem = chorus_smem(h->R);
+    const uint32_t in_smem = chorus_ring_fits(h->R) ? 1u : 0u;
+    const size_t smem = chorus_smem(in_smem ? h->R : 0);
     const char *ek = getenv("OLB_CHORUS_KERNEL");  // "direct" forces the plain-load variant (test aid)
     const bool tma = !(ek && !strcmp(ek, "direct")) && (h->I % 4 == 0) && (((uintptr_t) in_dev | (uintptr_t) out_dev) & 15) == 0;
     TensorMap tin{}, tout{};
@@ -427,12 +436,12 @@ OLB_API int olb_chorus_process(olb_chorus *h, const float *in_dev, float *out_de
         if (rc) return rc;
         rc = make_tmap_frames(&tout, out_dev, frames, h->I, kChL, kChTB);
         if (rc) return rc;
-        auto kern = k_chorus<kChTB, kChStages, true>;
+        auto kern = in_smem ? k_chorus<kChTB, kChStages, true, true> : k_chorus<kChTB, kChStages, true, false>;
         OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
         kern<<<h->ctas, 96, smem, st>>>(tin, tout, in_dev, out_dev, (uint32_t) frames, h->I, h->R, h->d_par, h->d_state, h->d_ring, h->d_tab, h->w, (float) (chorus_spec_len(h->sample_rate) - 2));
         h->last_kernel = "k_chorus_tma";
     } else {
-        auto kern = k_chorus<kChTB, kChStages, false>;
+        auto kern = in_smem ? k_chorus<kChTB, kChStages, false, true> : k_chorus<kChTB, kChStages, false, false>;
         OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
         kern<<<h->ctas, 96, smem, st>>>(tin, tout, in_dev, out_dev, (uint32_t) frames, h->I, h->R, h->d_par, h->d_state, h->d_ring, h->d_tab, h->w, (float) (chorus_spec_len(h->sample_rate) - 2));
         h->last_kernel = "k_chorus_direct";

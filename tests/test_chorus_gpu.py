@@ -78,14 +78,17 @@ def test_parameter_change_mid_stream_reinit_and_in_place(orc):
     b.close()
 
 
-def test_other_sample_rates_and_the_shared_memory_limit(orc):
-    x = orc.noise(23, 0, 4, 0, 3000, 0.5)
-    for sr in (44100.0, 32000.0):
-        y, _ = run_bank(x, [None] * 4, sr=sr)
-        assert np.array_equal(bits(y[:, 2]), bits(orc.chorus(x[:, 2], sr=sr)))
+def test_other_sample_rates_on_both_sides_of_the_shared_memory_limit(orc):
+    """Up to ~53 kHz the ring is shared-memory resident for the launch; above (96 / 192 kHz: 2 324 / 4 628 frames x 32 lanes)
+    the same kernel uses it in place in HBM.  Chunked, so the ring is carried from launch to launch in both forms."""
+    x = orc.noise(23, 0, 40, 0, 6000, 0.5)
+    for sr in (44100.0, 32000.0, 96000.0, 192000.0):
+        y, _ = run_bank(x, [None] * 40, sr=sr, chunks=[1, 2047, 1500, 2452])
+        for i in (2, 31, 32, 39):
+            assert np.array_equal(bits(y[:, i]), bits(orc.chorus(x[:, i], sr=sr))), (sr, i)
     from ol_dsp_b200 import OlbError
     with pytest.raises(OlbError):
-        ChorusBank(4, sample_rate=96000.0)  # a 2 308-frame ring x 32 lanes does not fit beside the tile pipeline
+        ChorusBank(4, sample_rate=0.0)
 
 
 def test_full_width_properties():
