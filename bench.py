@@ -28,7 +28,7 @@ SEED = 0x01D5B200
 def parse():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
-    p.add_argument("--steps", type=int, default=200)
+    p.add_argument("--steps", type=int, default=100)
     p.add_argument("--warmup", type=int, default=5)
     p.add_argument("--impl", default="olbank", choices=["olbank", "reference"])
     p.add_argument("--channels", type=int, default=65536)
