@@ -41,6 +41,7 @@ def parse():
     p.add_argument("--e2e-steps", type=int, default=10)
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
+    p.add_argument("--no-small", action="store_true", help="skip the 4096-channel configuration reported beside the headline")
     return p.parse_args()
 
 
@@ -236,6 +237,34 @@ def run_olbank(args):
                "frames_per_step": EF, "api": "olb_biquad_process_host (pinned host buffers, chunked H2D/kernel/D2H overlap)",
                "checksum": float(hout.double().sum().item())}
 
+    # ---- BASELINE configs[1] beside the headline (N = 1 only): the 4 096-channel cascade, 10 s of audio as 192 000-frame blocks
+    small = None
+    if world == 1 and not args.no_small and Cn != 4096:
+        C2, F2, K2 = 4096, 192000, 10
+        if e2e:
+            del hin, hout
+        b2 = BiquadBank(C2, S, 48000.0, device=local)
+        b2.SetMode({"fast": MODE_FAST, "fma": MODE_FMA, "exact": MODE_EXACT}[args.mode])
+        b2.SetCoeffs(c2_coefs(C2)[:, :S])
+        x2 = torch.empty((F2, C2), dtype=torch.float32, device="cuda")
+        y2 = torch.empty_like(x2)
+        noise_device(x2.data_ptr(), SEED, 0, C2, 0, F2, 1.0, 0, stream.cuda_stream)
+        for _ in range(3):
+            b2.ProcessDevice(x2.data_ptr(), y2.data_ptr(), F2, 0, stream.cuda_stream)
+        torch.cuda.synchronize()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s0.record(stream)
+        for _ in range(K2):
+            b2.ProcessDevice(x2.data_ptr(), y2.data_ptr(), F2, 0, stream.cuda_stream)
+        s1.record(stream)
+        torch.cuda.synchronize()
+        ms2 = s0.elapsed_time(s1) / K2
+        small = {"workload": "BASELINE configs[1]: 4096-channel x %d-section cascade, 48 kHz, streamed in 192000-frame blocks (4 s)" % S,
+                 "value": C2 * F2 / (ms2 * 1e-3), "unit": "channel-samples/s", "ms_per_step": ms2, "steps": K2, "kernel": b2.LastKernel(),
+                 "gbs": BYTES_PER_CHANNEL_SAMPLE * C2 * F2 / (ms2 * 1e-3) / 1e9}
+        b2.close()
+        del x2, y2
+
     if rank == 0:
         peak, peak_src = measured_peaks()
         per_launch_s = total_ms * 1e-3 / args.steps
@@ -259,6 +288,9 @@ def run_olbank(args):
         }
         if e2e:
             line["e2e"] = e2e
+        if small:
+            small["roofline_frac"] = small["gbs"] / peak
+            line["configs1"] = small
         if world == 1 and not args.no_cpu_baseline:
             orc, k, channels, frames, threads, mode = cpu_arm(args, target_seconds=8.0)
             dt, _ = orc.biquad_bench(k, None, frames, SEED, threads, mode)
