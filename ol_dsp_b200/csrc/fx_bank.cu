@@ -59,6 +59,27 @@ __device__ __forceinline__ float svf_tick(float in, float &low, float &band, con
     return __fadd_rn(o1, __fmul_rn(0.5f, svf_pick(k.type, low, band, high, notch)));
 }
 
+// The same filter with the output tap fixed at compile time (T = 0..4; T < 0: per-lane selects as above).  A bank whose
+// instances all use one filter type -- the usual case -- saves the 8 selects and the 2 peak subtractions of a frame.
+template <int T>
+__device__ __forceinline__ float svf_pick_t(int type, float low, float band, float high, float notch) {
+    if (T < 0) return svf_pick(type, low, band, high, notch);
+    return T == 1 ? band : T == 2 ? high : T == 3 ? notch : T == 4 ? __fsub_rn(low, high) : low;
+}
+template <int T>
+__device__ __forceinline__ float svf_tick_t(float in, float &low, float &band, const SvfCoef &k) {
+    float notch = __fsub_rn(in, __fmul_rn(k.damp, band));
+    low = __fadd_rn(low, __fmul_rn(k.freq, band));
+    float high = __fsub_rn(notch, low);
+    band = __fsub_rn(__fadd_rn(__fmul_rn(k.freq, high), band), __fmul_rn(__fmul_rn(__fmul_rn(k.drive, band), band), band));
+    const float o1 = __fmul_rn(0.5f, svf_pick_t<T>(k.type, low, band, high, notch));
+    notch = __fsub_rn(in, __fmul_rn(k.damp, band));
+    low = __fadd_rn(low, __fmul_rn(k.freq, band));
+    high = __fsub_rn(notch, low);
+    band = __fsub_rn(__fadd_rn(__fmul_rn(k.freq, high), band), __fmul_rn(__fmul_rn(__fmul_rn(k.drive, band), band), band));
+    return __fadd_rn(o1, __fmul_rn(0.5f, svf_pick_t<T>(k.type, low, band, high, notch)));
+}
+
 // Two independent SVFs advanced together, statement by statement: the same operations as two svf_tick calls, written
 // interleaved because ptxas keeps close to source order and each filter alone is one 12-deep dependent chain.
 __device__ __forceinline__ void svf_tick_pair(float inA, float &lowA, float &bandA, const SvfCoef &kA, float &outA, float inB, float &lowB,
@@ -428,6 +449,9 @@ __global__ void __launch_bounds__(32) k_fx_tma(const __grid_constant__ TensorMap
     const float r_balance = P(P_R_BALANCE), master = P(P_MASTER);
     float f_low = svf[ci], f_band = svf[(size_t) I + ci], w_low = svf[2 * (size_t) I + ci], w_band = svf[3 * (size_t) I + ci];
     float *ring = kHasRing ? ring_all + (size_t) ci * kRing : nullptr;
+    // one filter type for the whole warp (idle lanes carry instance 0's)?  then the tap is picked at compile time
+    const int type0 = __shfl_sync(0xffffffffu, kf.type, 0);
+    const int uniform_type = (__all_sync(0xffffffffu, kf.type == type0 || !live) && type0 >= 0 && type0 <= 4) ? type0 : -1;
     const bool far = kHasRing && live && delay >= (uint32_t) (STAGES * TB + 2);
     // Ring traffic is coalesced only when the whole warp can run ahead (every live lane's delay exceeds the look-ahead);
     // any other warp takes the general loop: per-lane direct reads and writes, no look-ahead.
@@ -484,7 +508,22 @@ __global__ void __launch_bounds__(32) k_fx_tma(const __grid_constant__ TensorMap
         const uint32_t rows = min((uint32_t) TB, frames - i * TB);
         float *col = tiles + (size_t) st * TB * L + lane;
         if (!kHasRing) {
-            if (live) {
+            if (KIND == OLB_FX_FILTER && uniform_type >= 0) {  // FilterFx::Process is the filter alone (Fx.h:88-108)
+                if (live) {
+                    switch (uniform_type) {
+#define OLB_FX_TYPE_CASE(T_)                                                                             \
+    case T_:                                                                                             \
+        _Pragma("unroll 4") for (uint32_t r = 0; r < rows; r++) col[r * L] = svf_tick_t<T_>(col[r * L], f_low, f_band, kf); \
+        break;
+                        OLB_FX_TYPE_CASE(0)
+                        OLB_FX_TYPE_CASE(1)
+                        OLB_FX_TYPE_CASE(2)
+                        OLB_FX_TYPE_CASE(3)
+                        OLB_FX_TYPE_CASE(4)
+#undef OLB_FX_TYPE_CASE
+                    }
+                }
+            } else if (live) {
 #pragma unroll 4
                 for (uint32_t r = 0; r < rows; r++) {
                     float wr;
