@@ -24,11 +24,14 @@
 #include <math.h>
 #include <stdlib.h>
 
+#include <algorithm>
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
 #include "tmap.h"
 #include "biquad_sys.cuh"
+#include "biquad_skew.cuh"
 
 namespace olb {
 
@@ -351,19 +354,35 @@ using namespace olb;
 
 // ================================================================================================
 // Host side
+//
+// Threading and ordering contract (include/olbank.h): one thread at a time runs process on a handle; setters, init and
+// the state calls may come from another (control) thread.  Every entry point takes the handle's mutex.  Setters touch
+// HOST tables only and mark what they changed; the device tables are brought up to date at the top of the next process
+// call, on that call's stream (async copies ordered before the kernel), so a parameter change is atomic at a block
+// boundary and can never reach a kernel that is already queued.  Init and set_state are queued the same way.
 struct olb_biquad {
+    std::mutex mu;
+    StreamOrder order;
     int device = 0;
     uint32_t C = 0, S = 0;
     float sample_rate = 0.f;
     int mode = OLB_MODE_EXACT;      // as set by the caller
-    int eff_mode = OLB_MODE_EXACT;  // arithmetic of the device table (FAST may drop to FMA, see upload_all)
-    int variant = 0;  // 0 auto, 1 direct, 2 tma (whole cascade per thread), 3 systolic (sections split over warps)
+    int eff_mode = OLB_MODE_EXACT;  // arithmetic of the device table: FAST drops to FMA while some channel cannot be normalised
+    int variant = 0;  // 0 auto, 1 direct, 2 tma (whole cascade per thread), 3 systolic (sections split over warps), 4 skewed section pairs
     Kinds kinds{};
     bool all_biquad = true;
-    std::vector<float> coefs_host;  // [C][S][5] as the caller set them
-    float *d_coef = nullptr;        // [S][5][C] effective
-    float *d_hist = nullptr;        // [S+1][2][C]
-    bool coef_dirty = true;
+    std::vector<float> coefs_host;   // [C][S][5] as the caller set them
+    std::vector<uint8_t> unnormal;   // [C] 1 = this channel cannot run the FAST arithmetic (b0 == 0, scale out of range)
+    uint32_t n_unnormal = 0;
+    bool unnormal_valid = false;
+    std::vector<double> node_scale;  // [C][S+1] node scaling of the device table: prod_{j >= n} b0_j in FAST, 1 otherwise, 0 = no table yet
+    bool hist_is_zero = true;        // the device history is all zeros (fresh / after Init): it carries any scaling
+    float *d_coef = nullptr;         // [S][5][C] effective
+    float *d_hist = nullptr;         // [S+1][2][C]
+    float *d_ratio = nullptr;        // [S+1][C] scratch of the history rescale
+    uint32_t dirty_lo = 0, dirty_hi = 0;  // channels whose device rows are stale: [lo, hi)
+    bool pending_init = false;            // Init() queued: history to zero at the next process
+    std::vector<float> pending_hist;      // set_state() queued: [S+1][2][C] to upload at the next process (empty = none)
     const char *last_kernel = "none";
     // host-buffer path
     float *d_stage[2][2] = {{nullptr, nullptr}, {nullptr, nullptr}};  // [slot][in/out]
@@ -371,6 +390,16 @@ struct olb_biquad {
     cudaStream_t s_h2d = nullptr, s_run = nullptr, s_d2h = nullptr;
     cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_run[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
 };
+
+static void mark_dirty(olb_biquad *h, uint32_t lo, uint32_t hi) {
+    if (h->dirty_lo == h->dirty_hi) {
+        h->dirty_lo = lo;
+        h->dirty_hi = hi;
+    } else {
+        h->dirty_lo = lo < h->dirty_lo ? lo : h->dirty_lo;
+        h->dirty_hi = hi > h->dirty_hi ? hi : h->dirty_hi;
+    }
+}
 
 // One-pole kinds as biquads (the FMA and FAST tiers run the biquad recurrence everywhere).
 static void as_biquad(int kind, const float *in5, float *k) {
@@ -383,10 +412,12 @@ static void as_biquad(int kind, const float *in5, float *k) {
     }
 }
 
-// FAST-tier table of one channel: out[s] = {G (s == 0 only), r1, r2, -a1, -a2}.  False when the channel cannot be
-// normalised (b0 == 0 / non-finite, or a node scale outside [1e-30, 1e30]).
-static bool fast_coefs(const olb_biquad *h, const float *chan, float *out) {
+// FAST-tier table of one channel: out[s] = {G (s == 0 only), r1, r2, -a1, -a2}; scale[n] = prod_{j >= n} b0_j (the scaling of
+// node n; scale[S] = 1).  False when the channel cannot be normalised (b0 == 0 / non-finite, or a node scale outside
+// [1e-30, 1e30]).  out / scale may be NULL (test only).
+static bool fast_coefs(const olb_biquad *h, const float *chan, float *out, double *scale) {
     double g = 1.0;
+    if (scale) scale[h->S] = 1.0;
     for (uint32_t s = h->S; s-- > 0;) {
         float k[5];
         as_biquad(h->kinds.k[s], chan + 5 * s, k);
@@ -394,13 +425,16 @@ static bool fast_coefs(const olb_biquad *h, const float *chan, float *out) {
         if (!(b0 != 0.0) || !std::isfinite(b0)) return false;
         g *= b0;
         if (!(fabs(g) >= 1e-30 && fabs(g) <= 1e30)) return false;
-        out[5 * s + 0] = 0.f;
-        out[5 * s + 1] = (float) ((double) k[1] / b0);
-        out[5 * s + 2] = (float) ((double) k[2] / b0);
-        out[5 * s + 3] = -k[3];
-        out[5 * s + 4] = -k[4];
+        if (scale) scale[s] = g;
+        if (out) {
+            out[5 * s + 0] = 0.f;
+            out[5 * s + 1] = (float) ((double) k[1] / b0);
+            out[5 * s + 2] = (float) ((double) k[2] / b0);
+            out[5 * s + 3] = -k[3];
+            out[5 * s + 4] = -k[4];
+        }
     }
-    out[0] = (float) g;
+    if (out) out[0] = (float) g;
     return true;
 }
 
@@ -411,36 +445,88 @@ static void effective_coefs(const olb_biquad *h, const float *in5, int s, float 
     out5[0] = k[0]; out5[1] = k[1]; out5[2] = k[2]; out5[3] = -k[3]; out5[4] = -k[4];  // negation is exact
 }
 
-// Rebuild the device table for channels [first, first+count) from the host copy, in the arithmetic of h->eff_mode.
-// Returns OLB_E_STATE (without uploading) when eff_mode is FAST and one of the channels cannot be normalised.
-static int upload_coefs(olb_biquad *h, uint32_t first, uint32_t count) {
-    const uint32_t S = h->S;
-    std::vector<float> stage((size_t) S * 5 * count), e((size_t) S * 5);
+// hist[n][i][first + c] *= ratio[n][c]: brings the history of `count` channels from the node scaling it was written in to
+// the scaling of the new coefficient table (one rounded product per element; the oracle does the same: orc_biquad_rescale_state).
+__global__ void k_bq_rescale(float *hist, const float *ratio, uint32_t first, uint32_t count, uint32_t C, uint32_t nodes) {
+    const uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= count) return;
+    for (uint32_t n = 0; n < nodes; n++) {
+        const float r = ratio[(size_t) n * count + c];
+        if (r == 1.0f) continue;
+        float *p = hist + (size_t) (n * 2) * C + first + c;
+        p[0] = __fmul_rn(p[0], r);
+        p[C] = __fmul_rn(p[C], r);
+    }
+}
+
+// Brings the device tables up to date on `st` (called at the top of process, under the handle's mutex).
+static int apply_pending(olb_biquad *h, cudaStream_t st) {
+    const uint32_t C = h->C, S = h->S;
+    const size_t hist_bytes = (size_t) (S + 1) * 2 * C * sizeof(float);
+    if (h->pending_init) {
+        OLB_CUDA(cudaMemsetAsync(h->d_hist, 0, hist_bytes, st));
+        h->hist_is_zero = true;
+        h->pending_init = false;
+    }
+    if (!h->pending_hist.empty()) {  // set_state: the caller speaks the scaling of the CURRENT device table (see get_state)
+        OLB_CUDA(cudaMemcpyAsync(h->d_hist, h->pending_hist.data(), hist_bytes, cudaMemcpyHostToDevice, st));
+        OLB_CUDA(cudaStreamSynchronize(st));  // pageable source: keep it alive until the copy has read it
+        h->pending_hist.clear();
+        h->pending_hist.shrink_to_fit();
+        h->hist_is_zero = false;
+    }
+    if (h->dirty_lo == h->dirty_hi) return OLB_OK;
+    // which arithmetic: FAST needs every channel of the bank normalisable
+    if (h->mode == OLB_MODE_FAST) {
+        const uint32_t lo = h->unnormal_valid ? h->dirty_lo : 0, hi = h->unnormal_valid ? h->dirty_hi : C;
+        for (uint32_t c = lo; c < hi; c++) {
+            const uint8_t bad = fast_coefs(h, &h->coefs_host[(size_t) c * S * 5], nullptr, nullptr) ? 0 : 1;
+            h->n_unnormal += bad - h->unnormal[c];
+            h->unnormal[c] = bad;
+        }
+        h->unnormal_valid = true;
+    }
+    const int eff = (h->mode == OLB_MODE_FAST && h->n_unnormal) ? OLB_MODE_FMA : h->mode;
+    if (eff != h->eff_mode) {  // the whole table changes arithmetic
+        h->eff_mode = eff;
+        h->dirty_lo = 0;
+        h->dirty_hi = C;
+    }
+    const uint32_t first = h->dirty_lo, count = h->dirty_hi - h->dirty_lo;
+    std::vector<float> stage((size_t) S * 5 * count), e((size_t) S * 5), ratio;
+    std::vector<double> sc(S + 1);
+    bool need_rescale = false;
     for (uint32_t i = 0; i < count; i++) {
         const float *chan = &h->coefs_host[(size_t) (first + i) * S * 5];
         if (h->eff_mode == OLB_MODE_FAST) {
-            if (!fast_coefs(h, chan, e.data())) return OLB_E_STATE;
+            fast_coefs(h, chan, e.data(), sc.data());
         } else {
             for (uint32_t s = 0; s < S; s++) effective_coefs(h, chan + 5 * s, (int) s, &e[5 * s]);
+            std::fill(sc.begin(), sc.end(), 1.0);
         }
         for (uint32_t s = 0; s < S; s++)
             for (int j = 0; j < 5; j++) stage[(size_t) (s * 5 + j) * count + i] = e[5 * s + j];
+        double *old = &h->node_scale[(size_t) (first + i) * (S + 1)];
+        for (uint32_t n = 0; n <= S; n++) {
+            if (!h->hist_is_zero && old[n] != 0.0 && old[n] != sc[n]) {
+                if (ratio.empty()) ratio.assign((size_t) (S + 1) * count, 1.0f);
+                ratio[(size_t) n * count + i] = (float) (sc[n] / old[n]);
+                need_rescale = true;
+            }
+            old[n] = sc[n];
+        }
     }
-    OLB_CUDA(cudaMemcpy2D(h->d_coef + first, (size_t) h->C * sizeof(float), stage.data(), (size_t) count * sizeof(float),
-                          (size_t) count * sizeof(float), (size_t) S * 5, cudaMemcpyHostToDevice));
+    if (need_rescale) {
+        if (!h->d_ratio) OLB_CUDA(cudaMalloc(&h->d_ratio, (size_t) (S + 1) * C * sizeof(float)));
+        OLB_CUDA(cudaMemcpyAsync(h->d_ratio, ratio.data(), ratio.size() * sizeof(float), cudaMemcpyHostToDevice, st));
+        k_bq_rescale<<<(count + 127) / 128, 128, 0, st>>>(h->d_hist, h->d_ratio, first, count, C, S + 1);
+        OLB_LAUNCHED();
+    }
+    OLB_CUDA(cudaMemcpy2DAsync(h->d_coef + first, (size_t) C * sizeof(float), stage.data(), (size_t) count * sizeof(float),
+                               (size_t) count * sizeof(float), (size_t) S * 5, cudaMemcpyHostToDevice, st));
+    OLB_CUDA(cudaStreamSynchronize(st));  // pageable sources (stage, ratio) die with this frame
+    h->dirty_lo = h->dirty_hi = 0;
     return OLB_OK;
-}
-
-// Full rebuild; a FAST bank with a channel that cannot be normalised drops to the FMA arithmetic.
-static int upload_all(olb_biquad *h) {
-    h->eff_mode = h->mode;
-    int rc = upload_coefs(h, 0, h->C);
-    if (rc == OLB_E_STATE && h->mode == OLB_MODE_FAST) {
-        h->eff_mode = OLB_MODE_FMA;
-        rc = upload_coefs(h, 0, h->C);
-    }
-    if (rc == OLB_OK) h->coef_dirty = false;
-    return rc;
 }
 
 OLB_API int olb_biquad_create(int device, uint32_t channels, uint32_t sections, float sample_rate, olb_biquad **out) {
@@ -458,6 +544,10 @@ OLB_API int olb_biquad_create(int device, uint32_t channels, uint32_t sections, 
     h->sample_rate = sample_rate;
     h->coefs_host.assign((size_t) channels * sections * 5, 0.f);
     for (size_t i = 0; i < (size_t) channels * sections; i++) h->coefs_host[i * 5] = 1.0f;
+    h->unnormal.assign(channels, 0);
+    h->node_scale.assign((size_t) channels * (sections + 1), 0.0);
+    h->dirty_lo = 0;
+    h->dirty_hi = channels;
     cudaError_t e = cudaMalloc(&h->d_coef, (size_t) sections * 5 * channels * sizeof(float));
     if (e == cudaSuccess) e = cudaMalloc(&h->d_hist, (size_t) (sections + 1) * 2 * channels * sizeof(float));
     if (e == cudaSuccess) e = cudaMemset(h->d_hist, 0, (size_t) (sections + 1) * 2 * channels * sizeof(float));
@@ -474,8 +564,10 @@ OLB_API int olb_biquad_create(int device, uint32_t channels, uint32_t sections, 
 OLB_API int olb_biquad_destroy(olb_biquad *h) {
     if (!h) return OLB_OK;
     DeviceGuard g(h->device);
+    h->order.quiesce();
     cudaFree(h->d_coef);
     cudaFree(h->d_hist);
+    cudaFree(h->d_ratio);
     for (int i = 0; i < 2; i++) {
         cudaFree(h->d_stage[i][0]);
         cudaFree(h->d_stage[i][1]);
@@ -486,43 +578,53 @@ OLB_API int olb_biquad_destroy(olb_biquad *h) {
     if (h->s_h2d) cudaStreamDestroy(h->s_h2d);
     if (h->s_run) cudaStreamDestroy(h->s_run);
     if (h->s_d2h) cudaStreamDestroy(h->s_d2h);
+    h->order.release();
     delete h;
     return OLB_OK;
 }
 
 OLB_API int olb_biquad_init(olb_biquad *h, float sample_rate) {
     OLB_ARG(h, "olb_biquad_init: NULL handle");
-    DeviceGuard g(h->device);
+    std::lock_guard<std::mutex> lk(h->mu);
     h->sample_rate = sample_rate;
-    OLB_CUDA(cudaMemset(h->d_hist, 0, (size_t) (h->S + 1) * 2 * h->C * sizeof(float)));
+    h->pending_init = true;
+    h->pending_hist.clear();
     return OLB_OK;
 }
 
 OLB_API int olb_biquad_set_kinds(olb_biquad *h, const uint8_t *kinds, uint32_t sections) {
     OLB_ARG(h && kinds, "olb_biquad_set_kinds: NULL argument");
     OLB_ARG(sections == h->S, "olb_biquad_set_kinds: bank has %u sections, got %u", h->S, sections);
+    for (uint32_t s = 0; s < sections; s++)
+        OLB_ARG(kinds[s] <= OLB_KIND_LPF, "olb_biquad_set_kinds: unknown kind %u at section %u", kinds[s], s);
+    std::lock_guard<std::mutex> lk(h->mu);
     bool all = true;
     for (uint32_t s = 0; s < sections; s++) {
-        OLB_ARG(kinds[s] <= OLB_KIND_LPF, "olb_biquad_set_kinds: unknown kind %u at section %u", kinds[s], s);
         h->kinds.k[s] = kinds[s];
         all = all && kinds[s] == OLB_KIND_BIQUAD;
     }
     h->all_biquad = all;
-    h->coef_dirty = true;
+    h->unnormal_valid = false;
+    mark_dirty(h, 0, h->C);
     return OLB_OK;
 }
 
 OLB_API int olb_biquad_set_mode(olb_biquad *h, int mode) {
     OLB_ARG(h, "olb_biquad_set_mode: NULL handle");
     OLB_ARG(mode == OLB_MODE_EXACT || mode == OLB_MODE_FMA || mode == OLB_MODE_FAST, "olb_biquad_set_mode: unknown mode %d", mode);
-    if (mode != h->mode) h->coef_dirty = true;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (mode != h->mode) {
+        h->unnormal_valid = false;
+        mark_dirty(h, 0, h->C);
+    }
     h->mode = mode;
     return OLB_OK;
 }
 
 OLB_API int olb_biquad_set_variant(olb_biquad *h, int variant) {
     OLB_ARG(h, "olb_biquad_set_variant: NULL handle");
-    OLB_ARG(variant >= 0 && variant <= 3, "olb_biquad_set_variant: unknown variant %d", variant);
+    OLB_ARG(variant >= 0 && variant <= 4, "olb_biquad_set_variant: unknown variant %d", variant);
+    std::lock_guard<std::mutex> lk(h->mu);
     h->variant = variant;
     return OLB_OK;
 }
@@ -533,13 +635,9 @@ OLB_API int olb_biquad_set_coeffs(olb_biquad *h, uint32_t first, uint32_t count,
     OLB_ARG(h && coefs_host, "olb_biquad_set_coeffs: NULL argument");
     OLB_ARG((uint64_t) first + count <= h->C, "olb_biquad_set_coeffs: range [%u, %u) exceeds %u channels", first, first + count, h->C);
     if (count == 0) return OLB_OK;
+    std::lock_guard<std::mutex> lk(h->mu);
     memcpy(&h->coefs_host[(size_t) first * h->S * 5], coefs_host, (size_t) count * h->S * 5 * sizeof(float));
-    if (!h->coef_dirty) {
-        DeviceGuard g(h->device);
-        const int rc = upload_coefs(h, first, count);
-        if (rc != OLB_E_STATE) return rc;
-        h->coef_dirty = true;  // a FAST bank met a channel it cannot normalise: rebuild everything at the next process
-    }
+    mark_dirty(h, first, first + count);
     return OLB_OK;
 }
 
@@ -569,13 +667,19 @@ OLB_API int olb_biquad_design(int type, double fs, double f0, double q, double g
 
 // ---- state in the oracle's layout [C][S][4] = x1 x2 y1 y2 ---------------------------------------
 // Sections that never touch a slot (one-pole kinds in EXACT mode keep only y1) report 0 there, as a
-// freshly Init()ed oracle would.
+// freshly Init()ed oracle would.  In FAST the values carry the node scaling of the table the last process call ran with.
 OLB_API int olb_biquad_get_state(olb_biquad *h, float *state_host) {
     OLB_ARG(h && state_host, "olb_biquad_get_state: NULL argument");
+    std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
     const uint32_t C = h->C, S = h->S;
-    std::vector<float> hist((size_t) (S + 1) * 2 * C);
-    OLB_CUDA(cudaMemcpy(hist.data(), h->d_hist, hist.size() * sizeof(float), cudaMemcpyDeviceToHost));
+    std::vector<float> hist((size_t) (S + 1) * 2 * C, 0.f);
+    if (!h->pending_hist.empty()) {
+        hist = h->pending_hist;
+    } else if (!h->pending_init) {
+        OLB_CUDA(h->order.sync());  // everything queued so far has written its history
+        OLB_CUDA(cudaMemcpy(hist.data(), h->d_hist, hist.size() * sizeof(float), cudaMemcpyDeviceToHost));
+    }
     for (uint32_t c = 0; c < C; c++)
         for (uint32_t s = 0; s < S; s++) {
             const bool full = h->eff_mode != OLB_MODE_EXACT || h->kinds.k[s] == OLB_KIND_BIQUAD;
@@ -590,7 +694,7 @@ OLB_API int olb_biquad_get_state(olb_biquad *h, float *state_host) {
 
 OLB_API int olb_biquad_set_state(olb_biquad *h, const float *state_host) {
     OLB_ARG(h && state_host, "olb_biquad_set_state: NULL argument");
-    DeviceGuard g(h->device);
+    std::lock_guard<std::mutex> lk(h->mu);
     const uint32_t C = h->C, S = h->S;
     std::vector<float> hist((size_t) (S + 1) * 2 * C, 0.f);
     auto full = [&](uint32_t s) { return h->eff_mode != OLB_MODE_EXACT || h->kinds.k[s] == OLB_KIND_BIQUAD; };
@@ -607,7 +711,8 @@ OLB_API int olb_biquad_set_state(olb_biquad *h, const float *state_host) {
             hist[(size_t) ((s + 1) * 2 + 1) * C + c] = h2;
         }
     }
-    OLB_CUDA(cudaMemcpy(h->d_hist, hist.data(), hist.size() * sizeof(float), cudaMemcpyHostToDevice));
+    h->pending_hist.swap(hist);
+    h->pending_init = false;
     return OLB_OK;
 }
 
@@ -670,15 +775,9 @@ static int launch_tma(olb_biquad *h, const float *in, float *out, uint32_t frame
 // ---- k_bq_sys shapes ----------------------------------------------------------------------------
 // OLB_BQ_SYS_CFG="<SPW>x<TB>x<NST>x<PACK>" picks one of the compiled shapes (tuning aid).
 static bool sys_cfg_env(SysCfg *c) {
-    static int have = -1;
-    static SysCfg cfg{};
-    if (have < 0) {
-        have = 0;
-        if (const char *e = getenv("OLB_BQ_SYS_CFG"))
-            if (sscanf(e, "%dx%dx%dx%d", &cfg.spw, &cfg.tb, &cfg.nst, &cfg.pack) == 4) have = 1;
-    }
-    *c = cfg;
-    return have == 1;
+    if (const char *e = getenv("OLB_BQ_SYS_CFG"))  // read per call: a tuning aid
+        if (sscanf(e, "%dx%dx%dx%d", &c->spw, &c->tb, &c->nst, &c->pack) == 4) return true;
+    return false;
 }
 
 // Automatic shape: packed lanes when that still gives every SM a CTA, scalar lanes below that.
@@ -733,6 +832,54 @@ static int launch_sys(olb_biquad *h, const float *in, float *out, uint32_t frame
     return OLB_E_ARG;
 }
 
+// ---- k_bq_skew shapes ---------------------------------------------------------------------------
+// Tile height x ring depth.  A CTA is 32 channels; what changes with the bank size is how many CTAs share an SM, and a
+// lone CTA must keep ~100 KiB of loads in flight to cover the HBM latency by itself (profiles/r01_run7_small_banks.txt).
+// OLB_BQ_SKEW_CFG="<TB>x<NST>" picks one of the compiled shapes (tuning aid).
+struct SkewCfg {
+    int tb, nst, lag;
+};
+static SkewCfg skew_cfg_auto(uint32_t C) {
+    SkewCfg env{};
+    if (const char *e = getenv("OLB_BQ_SKEW_CFG"))  // read per call: a tuning aid, cheap next to a launch
+        if (sscanf(e, "%dx%dx%d", &env.tb, &env.nst, &env.lag) == 3) return env;
+    const uint32_t ctas = (C + 31) / 32, per_sm = (ctas + 147) / 148;
+    if (per_sm <= 1) return SkewCfg{48, 32, 4};  // 192 KiB: the SM to itself
+    if (per_sm <= 2) return SkewCfg{48, 16, 4};  // 96 KiB
+    if (per_sm <= 4) return SkewCfg{48, 8, 4};   // 48 KiB
+    if (per_sm <= 8) return SkewCfg{24, 8, 4};   // 24 KiB
+    return SkewCfg{24, 4, 4};                    // 12 KiB: up to 18 CTAs per SM
+}
+
+#define OLB_SKEW_TRY(S_, TB_, NST_, D_, LAG_)                                  \
+    if (S == S_ && c.tb == TB_ && c.nst == NST_ && c.lag == LAG_)              \
+        return launch_skew_cfg<S_, MODE, TB_, NST_, D_, LAG_>(h->C, h->d_coef, h->d_hist, in, out, frames, st);
+
+template <int MODE>
+static int launch_skew(olb_biquad *h, const float *in, float *out, uint32_t frames, cudaStream_t st) {
+    const uint32_t S = h->S;
+    SkewCfg c = skew_cfg_auto(h->C);
+    if (S != 8) c = SkewCfg{24, 8, 4};
+    OLB_SKEW_TRY(8, 48, 32, 4, 4)
+    OLB_SKEW_TRY(8, 48, 16, 4, 4)
+    OLB_SKEW_TRY(8, 48, 8, 4, 4)
+    OLB_SKEW_TRY(8, 24, 8, 4, 4)
+    OLB_SKEW_TRY(8, 24, 4, 4, 4)
+    OLB_SKEW_TRY(8, 24, 6, 4, 4)
+    OLB_SKEW_TRY(8, 96, 16, 4, 4)
+    OLB_SKEW_TRY(8, 96, 8, 4, 4)
+    OLB_SKEW_TRY(8, 96, 4, 4, 4)
+    OLB_SKEW_TRY(8, 96, 2, 4, 4)
+    OLB_SKEW_TRY(8, 48, 32, 4, 6)
+    OLB_SKEW_TRY(8, 48, 16, 4, 6)
+    OLB_SKEW_TRY(8, 96, 16, 4, 6)
+    OLB_SKEW_TRY(6, 24, 8, 4, 4)
+    OLB_SKEW_TRY(4, 24, 8, 4, 4)
+    OLB_SKEW_TRY(2, 24, 8, 4, 4)
+    set_error("olb_biquad_process: no compiled skewed shape for S=%u tb=%d nst=%d lag=%d", S, c.tb, c.nst, c.lag);
+    return OLB_E_ARG;
+}
+
 template <int S, int MODE, bool GENERIC>
 static int launch_direct(olb_biquad *h, const float *in, float *out, uint64_t frames, int layout, cudaStream_t st) {
     if (layout == OLB_LAYOUT_FRAMES) {
@@ -759,10 +906,9 @@ static int dispatch_s(olb_biquad *h, const float *in, float *out, uint64_t frame
 }
 
 static int process_dev(olb_biquad *h, const float *in, float *out, uint64_t frames, int layout, cudaStream_t st) {
-    if (h->coef_dirty) {
-        int rc = upload_all(h);
-        if (rc) return rc;
-    }
+    int rc0 = apply_pending(h, st);
+    if (rc0) return rc0;
+    h->hist_is_zero = false;  // whatever runs next writes a history in the table's scaling
     const uint32_t S = h->S;
     if (S > 8) {
         h->last_kernel = "k_bq_runtime";
@@ -781,14 +927,32 @@ static int process_dev(olb_biquad *h, const float *in, float *out, uint64_t fram
         set_error("olb_biquad_process: the TMA variants need FRAMES layout, channels %% 4 == 0, 16-byte aligned buffers and biquad-only kinds in EXACT mode");
         return OLB_E_ARG;
     }
-    if (h->variant == 3 && !sys_supported(S)) {
-        set_error("olb_biquad_process: the systolic variant is compiled for 2, 4, 6 and 8 sections");
+    if (h->variant >= 3 && !sys_supported(S)) {
+        set_error("olb_biquad_process: the systolic and skewed variants are compiled for 2, 4, 6 and 8 sections");
         return OLB_E_ARG;
     }
-    // automatic choice (profiles/r01_run4_sys_sweep.txt): banks with a warp-group of 64 channels for every SM run the
-    // whole cascade per thread (k_bq_tma); smaller banks split the sections over the warps of a CTA (k_bq_sys, 8x the
-    // parallelism); tiny or unaligned ones run one channel per thread without TMA
-    bool tma = tma_ok && (h->variant == 2 || (h->variant == 0 && h->C >= 64u * 148u));
+    if (h->variant == 4) {
+        h->last_kernel = "k_bq_skew";
+        const int m = h->eff_mode;
+        return m == OLB_MODE_FAST  ? launch_skew<OLB_MODE_FAST>(h, in, out, (uint32_t) frames, st)
+               : m == OLB_MODE_FMA ? launch_skew<OLB_MODE_FMA>(h, in, out, (uint32_t) frames, st)
+                                   : launch_skew<OLB_MODE_EXACT>(h, in, out, (uint32_t) frames, st);
+    }
+    // automatic choice (profiles/r01_run4_sys_sweep.txt, profiles/r02_run2_sweep.txt): what limits every one of these
+    // kernels is the register-operand bandwidth of an SM sub-partition, so the question is only how evenly a bank can be
+    // spread over the 592 of them.  >= 32 768 channels: the whole cascade per thread (k_bq_tma: fewest instructions per
+    // channel-frame); 4 737 .. 32 767 channels of an 8-section bank: skewed section pairs (k_bq_skew: units of 32
+    // channels x 2 sections, 2-7 per sub-partition where k_bq_tma would leave most of them idle); smaller banks: one
+    // section per warp (k_bq_sys); tiny or unaligned ones run one channel per thread without TMA
+    bool tma = tma_ok && (h->variant == 2 || (h->variant == 0 && h->C >= 32768u) || (h->variant == 0 && S != 8 && h->C >= 64u * 148u));
+    const bool skew = !tma && tma_ok && S == 8 && h->variant == 0 && h->C > 32u * 148u;
+    if (skew) {
+        h->last_kernel = "k_bq_skew";
+        const int m = h->eff_mode;
+        return m == OLB_MODE_FAST  ? launch_skew<OLB_MODE_FAST>(h, in, out, (uint32_t) frames, st)
+               : m == OLB_MODE_FMA ? launch_skew<OLB_MODE_FMA>(h, in, out, (uint32_t) frames, st)
+                                   : launch_skew<OLB_MODE_EXACT>(h, in, out, (uint32_t) frames, st);
+    }
     bool sys = !tma && tma_ok && sys_supported(S) && (h->variant == 3 || (h->variant == 0 && h->C >= 32u * 16u));
     if (sys) {
         h->last_kernel = "k_bq_sys";
@@ -815,7 +979,9 @@ OLB_API int olb_biquad_process(olb_biquad *h, const float *in_dev, float *out_de
     OLB_ARG(layout == OLB_LAYOUT_FRAMES || layout == OLB_LAYOUT_PLANAR, "olb_biquad_process: bad layout %d", layout);
     if (frames == 0) return OLB_OK;
     OLB_ARG(in_dev && out_dev, "olb_biquad_process: NULL buffer");
+    std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
+    OLB_CUDA(h->order.enter((cudaStream_t) stream));
     return process_dev(h, in_dev, out_dev, frames, layout, (cudaStream_t) stream);
 }
 
@@ -827,6 +993,7 @@ OLB_API int olb_biquad_process_host(olb_biquad *h, const float *in_host, float *
     OLB_ARG(layout == OLB_LAYOUT_FRAMES || layout == OLB_LAYOUT_PLANAR, "olb_biquad_process_host: bad layout %d", layout);
     if (frames == 0) return OLB_OK;
     OLB_ARG(in_host && out_host, "olb_biquad_process_host: NULL buffer");
+    std::lock_guard<std::mutex> lk(h->mu);
     DeviceGuard g(h->device);
     const uint64_t C = h->C;
     // ~64 MiB per staging buffer, whole frames, multiple of the TMA tile height
@@ -852,6 +1019,7 @@ OLB_API int olb_biquad_process_host(olb_biquad *h, const float *in_host, float *
             }
         h->stage_elems = chunk * C;
     }
+    OLB_CUDA(h->order.enter(h->s_run));
     uint64_t k = 0;
     for (uint64_t t0 = 0; t0 < frames; t0 += chunk, k++) {
         const uint64_t n = frames - t0 < chunk ? frames - t0 : chunk;

@@ -1,0 +1,275 @@
+// biquad_skew.cuh -- k_bq_skew: the skewed section-pair cascade kernel.
+//
+// Why: what limits the section-pipelined kernel (k_bq_sys) is not HBM but (a) the shared-memory round trip of every
+// section hop (8 hops x 2 x 4 B per channel-frame = 128 B/clk/SM of shared-memory bandwidth is the wall)
+// and (b) the dependent FMA chain of a warp that has its sub-partition to itself.  Here one WARP runs TWO consecutive
+// sections of its 32 channels in the two halves of ONE packed fp32x2 instruction stream:
+//     low half  = section 2w   at stream position m
+//     high half = section 2w+1 at stream position m - 2      (its input is the low half's output of two steps ago)
+// so a hop through shared memory happens once per section PAIR, a warp-frame costs 4 FFMA2 (FAST) for 2 sections x 32
+// channels, the FFMA2 recurrence of one step overlaps the next one (the two-step lag keeps the low -> high hand-over off
+// the critical path), and the unit of scheduling is 32 channels x 2 sections = 12 pipe-cycles: 4 096 channels put one
+// warp on each of 512 SM sub-partitions, 65 536 channels are 8 192 such units (13.8 per sub-partition).
+// Per-section operation order is untouched, so results are bit-identical to every other kernel of the bank (and to
+// the oracle) in all three modes.
+//
+// Stream positions.  Each warp delays its stream by kLag = 2 positions, so with W = S/2 warps the tile that arrives as
+// frames [i*TB, (i+1)*TB) leaves as frames [i*TB - 2W, (i+1)*TB - 2W): the TMA store is issued at that (possibly
+// negative) row coordinate -- rows outside [0, frames) are clipped by the hardware -- and the stream is 2W positions
+// longer than the block (the tail loads are out of bounds and read as zeros).  Warp w's low half carries real frames at
+// positions [2w, 2w + F), its high half at [2w + 2, 2w + 2 + F); outside these a half is FROZEN (state restored after the
+// step) so that at the end of the launch every node of the cascade has seen exactly frames [0, F) and the history table
+// is in the bank's ordinary node format.  Only the first and last tiles take the freezing path.
+#pragma once
+#include "biquad_sys.cuh"
+
+namespace olb {
+
+
+template <int MODE>
+__device__ __forceinline__ u64 skew_section(u64 v, u64 x1, u64 x2, u64 y1, u64 y2, const u64 (&k)[5], u64 one, u64 negzero) {
+    return Lane<2>::template section<MODE>(v, x1, x2, y1, y2, k, one, negzero);
+}
+
+// Shared-memory accesses the compiler must keep in program order relative to one another (it otherwise sinks the
+// prefetches down to their uses and the warp waits out the full load latency every frame).
+__device__ __forceinline__ float lds_ordered(const float *p) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(smem_u32(p)) : "memory");
+    return v;
+}
+__device__ __forceinline__ void sts_ordered(float *p, float v) {
+    asm volatile("st.shared.f32 [%0], %1;" ::"r"(smem_u32(p)), "f"(v) : "memory");
+}
+
+__device__ __forceinline__ u64 sel_halves(bool lo_new, bool hi_new, u64 fresh, u64 old) {
+    float fl, fh, ol, oh;
+    unpack2(fresh, fl, fh);
+    unpack2(old, ol, oh);
+    return pack2(lo_new ? fl : ol, hi_new ? fh : oh);
+}
+
+// One tile in which both halves carry real frames throughout, fully unrolled into one basic block.  The input of step
+// j + D is fetched from shared memory during step j (one load between the arithmetic of every step: back-to-back memory
+// instructions of one warp issue four cycles apart, interleaved ones do not wait), so a warp that has its scheduler to
+// itself still keeps the FMA pipe fed.
+template <int MODE, int TB, int D, int kSkewLag, bool GAIN>
+__device__ __forceinline__ void skew_tile(float *col, const u64 (&k)[5], u64 gain2, u64 &x1, u64 &x2, u64 &y1, u64 &y2,
+                                          float (&p)[kSkewLag], u64 one, u64 negzero) {
+    constexpr int CH = 32;
+    float x[TB];
+#pragma unroll
+    for (int j = 0; j < D && j < TB; j++) x[j] = lds_ordered(col + j * CH);
+#pragma unroll
+    for (int j = 0; j < TB; j++) {
+        if (j + D < TB) x[j + D] = lds_ordered(col + (j + D) * CH);
+        // warp 0 of a FAST bank applies G = prod(b0) to its input: (x, p) * (G, 1) as one packed product (p * 1 is exact)
+        u64 v = pack2(x[j], p[kSkewLag - 1]);
+        if (GAIN) v = fmul2(v, gain2);
+        const u64 y = skew_section<MODE>(v, x1, x2, y1, y2, k, one, negzero);
+        x2 = x1; x1 = v; y2 = y1; y1 = y;
+        float ylo, yhi;
+        unpack2(y, ylo, yhi);
+#pragma unroll
+        for (int q = kSkewLag - 1; q > 0; q--) p[q] = p[q - 1];
+        p[0] = ylo;
+        sts_ordered(col + j * CH, yhi);
+    }
+}
+
+// FAST tier, hand software-pipelined: the four fused operations of a step are issued for four DIFFERENT stream
+// positions (A for m + 3, B for m + 2, C for m + 1, Y for m), so that every operand was produced at least three
+// instructions earlier and a lone warp issues back to back; the pipeline fills at the top of a tile and drains at its end.
+// Same operations on the same operands as skew_tile<OLB_MODE_FAST>: bit-identical results.
+//     A = fma(r1, V[m-1], V[m])   B = fma(r2, V[m-2], A)   C = fma(-a2, Y[m-2], B)   Y = fma(-a1, Y[m-1], C)
+template <int TB, int D, int kSkewLag, bool GAIN>
+__device__ __forceinline__ void skew_tile_fast(float *col, const u64 (&k)[5], float gain, u64 &x1, u64 &x2, u64 &y1, u64 &y2,
+                                               float (&p)[kSkewLag], u64, u64) {
+    constexpr int CH = 32, P = 3;  // pipeline depth in stream positions
+    static_assert(kSkewLag >= P + 1, "the low half's output must be complete before the high half consumes it");
+    float x[TB];
+    u64 V[TB + 2], Y[TB + 2], A[TB], B[TB], C[TB];  // V[j + 2], Y[j + 2] = position j of this tile; [0], [1] = history
+    V[1] = x1; V[0] = x2; Y[1] = y1; Y[0] = y2;
+#pragma unroll
+    for (int j = 0; j < D + P && j < TB; j++) {
+        x[j] = lds_ordered(col + j * CH);
+        if (GAIN) x[j] = __fmul_rn(gain, x[j]);
+    }
+#pragma unroll
+    for (int t = -P; t < TB; t++) {
+        if (t + P + D < TB && t + P + D >= D + P) {
+            x[t + P + D] = lds_ordered(col + (t + P + D) * CH);
+            if (GAIN) x[t + P + D] = __fmul_rn(gain, x[t + P + D]);
+        }
+        if (t + 3 < TB) {
+            const int j = t + 3;  // the high half's input: the low half's output kSkewLag positions back
+            float ylo, yhi;
+            if (j - kSkewLag >= 0) unpack2(Y[j - kSkewLag + 2], ylo, yhi);
+            else ylo = p[kSkewLag - 1 - j];
+            V[j + 2] = pack2(x[j], ylo);
+            A[j] = ffma2(k[1], V[j + 1], V[j + 2]);
+        }
+        if (t + 2 >= 0 && t + 2 < TB) B[t + 2] = ffma2(k[2], V[t + 2], A[t + 2]);
+        if (t + 1 >= 0 && t + 1 < TB) C[t + 1] = ffma2(k[4], Y[t + 1], B[t + 1]);
+        if (t >= 0) {
+            Y[t + 2] = ffma2(k[3], Y[t + 1], C[t]);
+            float ylo, yhi;
+            unpack2(Y[t + 2], ylo, yhi);
+            sts_ordered(col + t * CH, yhi);
+        }
+    }
+    x1 = V[TB + 1]; x2 = V[TB]; y1 = Y[TB + 1]; y2 = Y[TB];
+#pragma unroll
+    for (int q = 0; q < kSkewLag; q++) {
+        float ylo, yhi;
+        unpack2(Y[TB + 1 - q], ylo, yhi);
+        p[q] = ylo;
+    }
+}
+
+template <int S, int MODE, int TB, int NST, int D, int kSkewLag>
+__global__ void __launch_bounds__((S / 2) * 32) k_bq_skew(const __grid_constant__ TensorMap tm_in, const __grid_constant__ TensorMap tm_out,
+                                                          const __grid_constant__ TensorMap tm_out_head, uint32_t frames, uint32_t C, const float *__restrict__ coef, float *hist,
+                                                          u64 one, u64 negzero) {
+    constexpr int W = S / 2, CH = 32, DELAY = kSkewLag * W;  // stream positions between a frame's arrival and its departure
+    static_assert(S % 2 == 0 && TB > DELAY, "bad shape");
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    float *tiles = reinterpret_cast<float *>(smem_raw);
+    uint64_t *bar = reinterpret_cast<uint64_t *>(smem_raw + (size_t) NST * TB * CH * sizeof(float));  // [NST][W]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t ch0 = blockIdx.x * CH;
+    constexpr uint32_t kTileBytes = TB * CH * sizeof(float);
+    const uint32_t total = frames + DELAY;  // stream length
+    const uint32_t ntiles = (total + TB - 1) / TB;
+
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < NST * W; i++) mbar_init(&bar[i], 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (warp == W - 1 && lane == 0) {
+        for (uint32_t j = 0; j < (uint32_t) NST && j < ntiles; j++) {
+            mbar_arrive_expect_tx(&bar[j * W], kTileBytes);
+            tma_load_2d(tiles + (size_t) j * TB * CH, &tm_in, (int) ch0, (int) (j * TB), &bar[j * W]);
+        }
+    }
+
+    // sections s0 (low half) and s0 + 1 (high half); history nodes s0, s0 + 1, s0 + 2
+    const int s0 = warp * 2;
+    const uint32_t c = ch0 + lane;
+    const bool live = c < C;
+    u64 k[5];
+#pragma unroll
+    for (int j = 0; j < 5; j++)
+        k[j] = live ? pack2(coef[(size_t) (s0 * 5 + j) * C + c], coef[(size_t) ((s0 + 1) * 5 + j) * C + c]) : 0ull;
+    const bool with_gain = MODE == OLB_MODE_FAST && warp == 0;
+    const float gain = (with_gain && live) ? coef[c] : 1.0f;  // G = prod(b0) sits in section 0's b0 slot
+    auto node = [&](int n, int i) { return live ? hist[(size_t) (n * 2 + i) * C + c] : 0.f; };
+    u64 x1 = pack2(node(s0, 0), node(s0 + 1, 0)), x2 = pack2(node(s0, 1), node(s0 + 1, 1));
+    u64 y1 = pack2(node(s0 + 1, 0), node(s0 + 2, 0)), y2 = pack2(node(s0 + 1, 1), node(s0 + 2, 1));
+    float p[kSkewLag];  // low-half outputs of the last kSkewLag steps, on their way to the high half
+#pragma unroll
+    for (int q = 0; q < kSkewLag; q++) p[q] = 0.f;
+    __syncthreads();  // every warp has read its nodes before any warp can finish and write one back
+
+    const uint32_t lo0 = kSkewLag * warp, hi0 = lo0 + kSkewLag;  // first real position of each half
+
+    for (uint32_t i = 0; i < ntiles; i++) {
+        const uint32_t st = i % NST, par = (i / NST) & 1;
+        mbar_wait(&bar[st * W + warp], par);
+        float *col = tiles + (size_t) st * TB * CH + lane;
+        const uint32_t m0 = i * TB;
+        if (m0 >= hi0 && m0 + TB <= lo0 + frames) {  // both halves carry real frames throughout the tile
+            if (MODE == OLB_MODE_FAST) {
+                if (with_gain) skew_tile_fast<TB, D, kSkewLag, true>(col, k, gain, x1, x2, y1, y2, p, one, negzero);
+                else skew_tile_fast<TB, D, kSkewLag, false>(col, k, gain, x1, x2, y1, y2, p, one, negzero);
+            } else {
+                skew_tile<MODE, TB, D, kSkewLag, false>(col, k, 0ull, x1, x2, y1, y2, p, one, negzero);
+            }
+        } else {
+            const uint32_t rows = min((uint32_t) TB, total - m0);
+            for (uint32_t r = 0; r < rows; r++) {
+                const uint32_t m = m0 + r;
+                const bool lo_on = m >= lo0 && m < lo0 + frames, hi_on = m >= hi0 && m < hi0 + frames;
+                float xin = col[r * CH];
+                if (with_gain) xin = __fmul_rn(gain, xin);
+                const u64 v = pack2(xin, p[kSkewLag - 1]);
+                const u64 y = skew_section<MODE>(v, x1, x2, y1, y2, k, one, negzero);
+                const u64 nx2 = sel_halves(lo_on, hi_on, x1, x2), nx1 = sel_halves(lo_on, hi_on, v, x1);
+                const u64 ny2 = sel_halves(lo_on, hi_on, y1, y2), ny1 = sel_halves(lo_on, hi_on, y, y1);
+                x2 = nx2; x1 = nx1; y2 = ny2; y1 = ny1;
+                float ylo, yhi;
+                unpack2(y, ylo, yhi);
+#pragma unroll
+                for (int q = kSkewLag - 1; q > 0; q--) p[q] = p[q - 1];
+                p[0] = ylo;
+                col[r * CH] = yhi;
+            }
+        }
+        if (warp < W - 1) {
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bar[st * W + warp + 1]);
+        } else {
+            fence_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+                // tile i leaves as frames [i*TB - DELAY, (i+1)*TB - DELAY); the first tile's leading DELAY rows are not frames
+                // (its box is TB - DELAY rows high: tm_out_head), rows >= frames are clipped by the hardware
+                if (i == 0) tma_store_2d(&tm_out_head, (int) ch0, 0, tiles + (size_t) DELAY * CH);
+                else tma_store_2d(&tm_out, (int) ch0, (int) (i * TB) - DELAY, tiles + (size_t) st * TB * CH);
+                tma_commit();
+                // the stage tile i-1 was stored from is free once that store has read it: refill it with tile i-1+NST
+                if (i >= 1 && i - 1 + NST < ntiles) {
+                    tma_wait_read<1>();
+                    const uint32_t nxt = i - 1 + NST, ns = nxt % NST;
+                    mbar_arrive_expect_tx(&bar[ns * W], kTileBytes);
+                    tma_load_2d(tiles + (size_t) ns * TB * CH, &tm_in, (int) ch0, (int) (nxt * TB), &bar[ns * W]);
+                }
+            }
+        }
+    }
+    if (warp == W - 1 && lane == 0) tma_wait_all<0>();
+    if (live) {
+        // every half has now seen frames [0, F): x1.hi == y1.lo again and the table is back in node format.
+        // Node s0 is the previous warp's output node (it writes it) except for warp 0, which owns the input node.
+        float a, b;
+        if (warp == 0) {
+            unpack2(x1, a, b);
+            hist[(size_t) (s0 * 2 + 0) * C + c] = a;
+            unpack2(x2, a, b);
+            hist[(size_t) (s0 * 2 + 1) * C + c] = a;
+        }
+        unpack2(y1, a, b);
+        hist[(size_t) ((s0 + 1) * 2 + 0) * C + c] = a;
+        hist[(size_t) ((s0 + 2) * 2 + 0) * C + c] = b;
+        unpack2(y2, a, b);
+        hist[(size_t) ((s0 + 1) * 2 + 1) * C + c] = a;
+        hist[(size_t) ((s0 + 2) * 2 + 1) * C + c] = b;
+    }
+}
+
+template <int S, int MODE, int TB, int NST, int D, int kSkewLag>
+static int launch_skew_cfg(uint32_t C, const float *d_coef, float *d_hist, const float *in, float *out, uint32_t frames, cudaStream_t st) {
+    constexpr int W = S / 2, CH = 32;
+    constexpr size_t smem = (size_t) NST * TB * CH * sizeof(float) + (size_t) NST * W * sizeof(uint64_t);
+    TensorMap tin, tout, thead;
+    int rc = make_tmap_frames(&tin, in, frames, C, CH, TB);
+    if (rc) return rc;
+    rc = make_tmap_frames(&tout, out, frames, C, CH, TB);
+    if (rc) return rc;
+    rc = make_tmap_frames(&thead, out, frames, C, CH, TB - kSkewLag * W);
+    if (rc) return rc;
+    auto kern = k_bq_skew<S, MODE, TB, NST, D, kSkewLag>;
+    OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+    OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    const float onef = 1.0f, nzf = -0.0f;
+    uint32_t ob, nb;
+    memcpy(&ob, &onef, 4);
+    memcpy(&nb, &nzf, 4);
+    const u64 one = ((u64) ob << 32) | ob, negzero = ((u64) nb << 32) | nb;
+    kern<<<(C + CH - 1) / CH, W * 32, smem, st>>>(tin, tout, thead, frames, C, d_coef, d_hist, one, negzero);
+    OLB_LAUNCHED();
+    return OLB_OK;
+}
+
+}  // namespace olb

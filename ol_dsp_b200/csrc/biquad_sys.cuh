@@ -131,6 +131,7 @@ __global__ void __launch_bounds__((S / SPW) * 32) k_bq_sys(const __grid_constant
         h[n][0] = live ? *reinterpret_cast<const T *>(hist + (size_t) ((s0 + n) * 2 + 0) * C + c) : T(0);
         h[n][1] = live ? *reinterpret_cast<const T *>(hist + (size_t) ((s0 + n) * 2 + 1) * C + c) : T(0);
     }
+    __syncthreads();  // every warp has read its nodes before any warp can finish and write a shared one back
 
     for (uint32_t i = 0; i < ntiles; i++) {
         const uint32_t st = i % NST, par = (i / NST) & 1;

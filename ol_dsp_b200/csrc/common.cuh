@@ -55,6 +55,36 @@ struct DeviceGuard {
 
 int require_sm100(int device);
 
+// ---- stream ordering of a handle's device work ------------------------------------------------------
+// A bank's state lives on the device between process calls, and callers may hand every call a different stream (and
+// non-blocking streams are not ordered against the legacy default stream).  enter(st) makes `st` wait for whatever the
+// handle queued on the previous stream; sync() waits for everything queued so far (state read-back, destroy).
+struct StreamOrder {
+    cudaStream_t last = nullptr;
+    bool any = false;
+    cudaEvent_t ev = nullptr;
+    cudaError_t enter(cudaStream_t st) {
+        cudaError_t e = cudaSuccess;
+        if (any && st != last) {
+            if (!ev) e = cudaEventCreateWithFlags(&ev, cudaEventDisableTiming);
+            if (e == cudaSuccess) e = cudaEventRecord(ev, last);
+            if (e == cudaSuccess) e = cudaStreamWaitEvent(st, ev, 0);
+        }
+        last = st;
+        any = true;
+        return e;
+    }
+    cudaStream_t stream() const { return last; }
+    cudaError_t sync() const { return any ? cudaStreamSynchronize(last) : cudaSuccess; }
+    void quiesce() const {
+        if (any) cudaStreamSynchronize(last);
+    }
+    void release() {
+        if (ev) cudaEventDestroy(ev);
+        ev = nullptr;
+    }
+};
+
 // ---- host-buffer convenience path of the small banks (fx, plate, chorus, voices) -----------------
 // Device staging that grows on demand plus one private stream: `process_host` entry points copy a time chunk in, run the
 // bank's own device path on it, copy the result out, and return when the host buffer is complete (the reference's

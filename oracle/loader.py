@@ -115,6 +115,8 @@ class Oracle(_Fx):
         lib.orc_biquad_run_f64.argtypes = [C.c_uint32, C.c_uint32, C.c_void_p, _F, _F, C.POINTER(C.c_double), C.c_uint64]
         lib.orc_biquad_run_f64.restype = C.c_int
         lib.orc_biquad_fma_coefs.argtypes = [C.c_int, _F, _F]
+        lib.orc_biquad_rescale_state.argtypes = [C.c_uint32, C.c_uint32, C.c_void_p, _F, C.c_int, C.c_void_p, _F, C.c_int, _F]
+        lib.orc_biquad_rescale_state.restype = C.c_int
         lib.orc_rbj.argtypes = [C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, _F]
         lib.orc_rbj.restype = None
         lib.orc_voice_run.argtypes = [C.c_float, _F, _EVP, C.c_size_t, _F, _F, C.c_size_t]
@@ -196,6 +198,17 @@ class Oracle(_Fx):
                                      LAYOUT_PLANAR if planar else LAYOUT_FRAMES)
         assert rc == 0
         return out
+
+    def biquad_rescale(self, state, coefs_old, mode_old, coefs_new, mode_new, kinds_old=None, kinds_new=None):
+        """Re-expresses a FAST history ([C][S][4], in place) in the node scaling of a new coefficient table / mode."""
+        co = np.ascontiguousarray(coefs_old, dtype=np.float32)
+        cn = np.ascontiguousarray(coefs_new, dtype=np.float32)
+        ko = np.ascontiguousarray(kinds_old, dtype=np.uint8) if kinds_old is not None else None
+        kn = np.ascontiguousarray(kinds_new, dtype=np.uint8) if kinds_new is not None else ko
+        assert state.dtype == np.float32 and state.flags.c_contiguous and state.shape == (co.shape[0], co.shape[1], 4)
+        rc = self.lib.orc_biquad_rescale_state(co.shape[0], co.shape[1], ko.ctypes.data if ko is not None else None, _fp(co), mode_old,
+                                               kn.ctypes.data if kn is not None else None, _fp(cn), mode_new, _fp(state))
+        assert rc == 0
 
     def biquad_f64(self, x, coefs, kinds=None):
         x = np.ascontiguousarray(x, dtype=np.float32)

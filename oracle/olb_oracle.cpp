@@ -233,16 +233,14 @@ static void biquad_channel(int mode, uint32_t sections, const uint8_t *kinds, co
     }
 }
 
+static int biquad_bank_mode(int mode, uint32_t channels, uint32_t sections, const uint8_t *kinds, const float *coefs);
+
 // state may be NULL (zero initial state, final state discarded).  sections <= 64.
 ORC_API int orc_biquad_run(int mode, uint32_t channels, uint32_t sections, const uint8_t *kinds, const float *coefs,
                            float *state, const float *in, float *out, uint64_t frames, int layout) {
     if (sections > 64) return -1;
     std::vector<float> tmp(4 * (size_t) sections);
-    if (mode == ORC_MODE_FAST) {  // the decision is per BANK: one channel that cannot be normalised sends all to FMA
-        float k4[64 * 4], g;
-        for (uint32_t c = 0; c < channels && mode == ORC_MODE_FAST; c++)
-            if (!orc_biquad_fast_coefs(sections, kinds, coefs + (size_t) c * sections * 5, k4, &g)) mode = ORC_MODE_FMA;
-    }
+    mode = biquad_bank_mode(mode, channels, sections, kinds, coefs);  // per BANK: one channel that cannot be normalised sends all to FMA
     for (uint32_t c = 0; c < channels; c++) {
         float *st = state ? state + (size_t) c * sections * 4 : tmp.data();
         if (!state) memset(st, 0, sizeof(float) * 4 * sections);
@@ -251,6 +249,56 @@ ORC_API int orc_biquad_run(int mode, uint32_t channels, uint32_t sections, const
             biquad_channel(mode, sections, kinds, k, st, in + c, out + c, frames, channels);
         else
             biquad_channel(mode, sections, kinds, k, st, in + (size_t) c * frames, out + (size_t) c * frames, frames, 1);
+    }
+    return 0;
+}
+
+// The arithmetic a whole bank runs in: FAST only when EVERY channel can be normalised, else FMA.
+static int biquad_bank_mode(int mode, uint32_t channels, uint32_t sections, const uint8_t *kinds, const float *coefs) {
+    if (mode != ORC_MODE_FAST) return mode;
+    float k4[64 * 4], g;
+    for (uint32_t c = 0; c < channels; c++)
+        if (!orc_biquad_fast_coefs(sections, kinds, coefs + (size_t) c * sections * 5, k4, &g)) return ORC_MODE_FMA;
+    return ORC_MODE_FAST;
+}
+
+// Node scaling of one channel: scale[n] = prod_{j >= n} b0_j in FAST (double products from the output side), 1 otherwise.
+static void biquad_node_scales(int bank_mode, uint32_t sections, const uint8_t *kinds, const float *coefs, double *scale) {
+    double g = 1.0;
+    scale[sections] = 1.0;
+    for (uint32_t s = sections; s-- > 0;) {
+        float k[5];
+        orc_biquad_fma_coefs(kinds ? kinds[s] : 0, coefs + 5 * s, k);
+        if (bank_mode == ORC_MODE_FAST) g *= (double) k[0];
+        scale[s] = bank_mode == ORC_MODE_FAST ? g : 1.0;
+    }
+}
+
+// A bank keeps its FAST history in the node scaling of its coefficient table, so a coefficient (or mode) change between
+// two blocks re-expresses the history in the new scaling: every history value of node n is multiplied ONCE by
+// (float) (scale_new[n] / scale_old[n]) (double division, rounded to float; values whose ratio is 1 are left alone).
+// state: [channels][sections][4] = x1 x2 y1 y2 (x of section s is node s, y is node s + 1), rescaled in place.
+// The GPU bank does the same at the top of the first process call after the change (ol_dsp_b200/csrc/biquad_bank.cu).
+ORC_API int orc_biquad_rescale_state(uint32_t channels, uint32_t sections, const uint8_t *kinds_old, const float *coefs_old, int mode_old,
+                                     const uint8_t *kinds_new, const float *coefs_new, int mode_new, float *state) {
+    if (sections > 64) return -1;
+    const int bm_old = biquad_bank_mode(mode_old, channels, sections, kinds_old, coefs_old);
+    const int bm_new = biquad_bank_mode(mode_new, channels, sections, kinds_new, coefs_new);
+    double so[65], sn[65];
+    for (uint32_t c = 0; c < channels; c++) {
+        biquad_node_scales(bm_old, sections, kinds_old, coefs_old + (size_t) c * sections * 5, so);
+        biquad_node_scales(bm_new, sections, kinds_new, coefs_new + (size_t) c * sections * 5, sn);
+        float *st = state + (size_t) c * sections * 4;
+        for (uint32_t s = 0; s < sections; s++) {
+            if (so[s] != sn[s]) {
+                const float r = (float) (sn[s] / so[s]);
+                if (r != 1.0f) { st[4 * s + 0] = st[4 * s + 0] * r; st[4 * s + 1] = st[4 * s + 1] * r; }
+            }
+            if (so[s + 1] != sn[s + 1]) {
+                const float r = (float) (sn[s + 1] / so[s + 1]);
+                if (r != 1.0f) { st[4 * s + 2] = st[4 * s + 2] * r; st[4 * s + 3] = st[4 * s + 3] * r; }
+            }
+        }
     }
     return 0;
 }
@@ -962,30 +1010,39 @@ ORC_API int orc_polyvoice_run(int n_voices, float sr, const float *config16, con
 // ---------------------------------------------------------------------------------------------------
 // CPU baseline driver (bench.py cpu_baseline / --impl reference): one channel per std::thread at a
 // time, threads = n_threads, each thread pulls channels from a shared counter and runs the scalar
-// cascade over `frames` frames of replayable Philox noise.  Returns seconds of wall time.
+// cascade (not vectorised across channels) over `frames` frames of replayable Philox noise held in
+// planar host buffers.  Returns the seconds of wall time the cascades took; noise generation and
+// the checksum pass are outside the timed region.
 ORC_API double orc_biquad_bench(int mode, uint32_t channels, uint32_t sections, const uint8_t *kinds, const float *coefs,
                                 uint64_t frames, uint32_t seed, int n_threads, double *checksum) {
+    // inputs first, OUTSIDE the timed region (the GPU arm's noise is resident before its clock starts too)
+    std::vector<float> x((size_t) channels * frames), y((size_t) channels * frames);
+    {
+        std::atomic<uint32_t> nx(0);
+        std::vector<std::thread> gen;
+        for (int w = 0; w < n_threads; w++)
+            gen.emplace_back([&]() {
+                for (uint32_t c; (c = nx.fetch_add(1)) < channels;) orc_noise_fill(seed, c, 1, 0, frames, 1.0f, &x[(size_t) c * frames], 1, 0);
+            });
+        for (auto &th : gen) th.join();
+    }
+    const int bank_mode = biquad_bank_mode(mode, channels, sections, kinds, coefs);
     std::atomic<uint32_t> next(0);
-    std::vector<double> sums((size_t) n_threads, 0.0);
     auto t0 = std::chrono::steady_clock::now();
     std::vector<std::thread> pool;
     for (int w = 0; w < n_threads; w++) {
-        pool.emplace_back([&, w]() {
-            std::vector<float> x(frames), y(frames), st(4 * (size_t) sections);
-            for (;;) {
-                uint32_t c = next.fetch_add(1);
-                if (c >= channels) break;
-                orc_noise_fill(seed, c, 1, 0, frames, 1.0f, x.data(), 1, 0);
+        pool.emplace_back([&]() {
+            std::vector<float> st(4 * (size_t) sections);
+            for (uint32_t c; (c = next.fetch_add(1)) < channels;) {
                 std::fill(st.begin(), st.end(), 0.f);
-                biquad_channel(mode, sections, kinds, coefs + (size_t) c * sections * 5, st.data(), x.data(), y.data(), frames, 1);
-                double s = 0; for (uint64_t t = 0; t < frames; t++) s += y[t];
-                sums[w] += s;
+                biquad_channel(bank_mode, sections, kinds, coefs + (size_t) c * sections * 5, st.data(), &x[(size_t) c * frames],
+                               &y[(size_t) c * frames], frames, 1);
             }
         });
     }
     for (auto &th : pool) th.join();
     double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-    if (checksum) { double s = 0; for (double v : sums) s += v; *checksum = s; }
+    if (checksum) { double s = 0; for (float v : y) s += v; *checksum = s; }
     return dt;
 }
 

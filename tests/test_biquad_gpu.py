@@ -11,8 +11,8 @@ from ol_dsp_b200 import (KIND_LPF, KIND_PORT, LAYOUT_FRAMES, LAYOUT_PLANAR, MODE
 
 pytestmark = pytest.mark.gpu
 
-V_AUTO, V_DIRECT, V_TMA, V_SYS = 0, 1, 2, 3
-KNAME = {V_DIRECT: "k_bq_direct", V_TMA: "k_bq_tma", V_SYS: "k_bq_sys"}
+V_AUTO, V_DIRECT, V_TMA, V_SYS, V_SKEW = 0, 1, 2, 3, 4
+KNAME = {V_DIRECT: "k_bq_direct", V_TMA: "k_bq_tma", V_SYS: "k_bq_sys", V_SKEW: "k_bq_skew"}
 
 
 def bits(a):
@@ -90,7 +90,7 @@ def test_one_pole_kinds_reproduce_port_and_verb_lpf(orc, mode):
     assert np.array_equal(bits(st), bits(ost))
 
 
-@pytest.mark.parametrize("variant", [V_DIRECT, V_TMA, V_SYS])
+@pytest.mark.parametrize("variant", [V_DIRECT, V_TMA, V_SYS, V_SKEW])
 def test_state_carries_across_calls_and_per_frame_process(orc, variant):
     C, T = 64, 300
     x = orc.noise(4, 0, C, 0, T)
@@ -196,8 +196,45 @@ def test_systolic_shapes_bit_exact(orc, S, mode, C):
     assert np.array_equal(bits(st), bits(ost))
 
 
+@pytest.mark.parametrize("S", [2, 4, 6, 8])
+@pytest.mark.parametrize("mode", [MODE_EXACT, MODE_FMA, MODE_FAST])
+@pytest.mark.parametrize("C,chunks", [(132, [500, 277]), (4096, [777]), (9600, [1, 7, 23, 24, 25, 697]), (36, [3, 774])])
+def test_skewed_pairs_bit_exact(orc, S, mode, C, chunks):
+    """k_bq_skew: two sections per warp in the halves of a packed FFMA2 stream, the second trailing the first; ragged
+    frame counts (shorter than the lag, than a tile, straddling tiles) exercise the freezing path at both ends and the
+    history hand-over between calls."""
+    T = sum(chunks)
+    x = orc.noise(22, 0, C, 0, T)
+    k = np.ascontiguousarray(c2_coefs(C)[:, :S])
+    y, name, st = run_bank(x, k, mode, V_SKEW, chunks=chunks)
+    assert name == "k_bq_skew"
+    ost = np.zeros((C, S, 4), dtype=np.float32)
+    want = orc.biquad(x, k, mode=mode, state=ost)
+    assert np.array_equal(bits(y), bits(want))
+    assert np.array_equal(bits(st), bits(ost))
+
+
+def test_skewed_pairs_in_place(orc):
+    C, T = 4096, 3000
+    dev = torch.empty((T, C), dtype=torch.float32, device="cuda")
+    noise_device(dev.data_ptr(), 23, 0, C, 0, T)
+    x = dev.cpu().numpy()
+    k = c2_coefs(C)
+    b = BiquadBank(C, 8)
+    b.SetMode(MODE_FAST)
+    b.SetVariant(V_SKEW)
+    b.SetCoeffs(k)
+    b.ProcessDevice(dev.data_ptr(), dev.data_ptr(), T)
+    torch.cuda.synchronize()
+    assert b.LastKernel() == "k_bq_skew"
+    pick = np.r_[0:40, 2000:2040, 4060:4096]
+    want = orc.biquad(np.ascontiguousarray(x[:, pick]), np.ascontiguousarray(k[pick]), mode=loader.MODE_FAST)
+    assert np.array_equal(bits(dev.cpu().numpy()[:, pick]), bits(want))
+    b.close()
+
+
 @pytest.mark.parametrize("variant,C,S", [(V_DIRECT, 77, 8), (V_TMA, 260, 8), (V_SYS, 132, 8), (V_SYS, 9600, 8), (V_TMA, 64, 3),
-                                         (V_DIRECT, 64, 12), (V_SYS, 64, 4)])
+                                         (V_DIRECT, 64, 12), (V_SYS, 64, 4), (V_SKEW, 132, 8), (V_SKEW, 64, 4)])
 def test_fast_mode_bit_exact_to_oracle_fast_and_close_to_exact(orc, variant, C, S):
     """OLB_MODE_FAST (normalised 4-op sections): same operations as the oracle's FAST mode -> bit-exact to it;
     against EXACT it is a tolerance tier (bound measured in DESIGN.md; both are compared with the float64 cascade)."""
@@ -224,6 +261,93 @@ def test_fast_mode_falls_back_to_fma_when_a_section_has_zero_b0(orc):
     k[5, 3] = (0.0, 1.0, 0.0, 0.0, 0.0)  # a pure one-sample delay: b0 == 0 cannot be normalised
     y, _, _ = run_bank(x, k, MODE_FAST)
     assert np.array_equal(bits(y), bits(orc.biquad(x, k, mode=MODE_FMA)))
+
+
+@pytest.mark.parametrize("variant,C", [(V_AUTO, 128), (V_TMA, 256), (V_SYS, 128), (V_SKEW, 128)])
+def test_fast_history_follows_a_mid_stream_coefficient_change(orc, variant, C):
+    """FAST keeps its history in the node scaling of the coefficient table; set_coeffs between two blocks (a filter sweep,
+    an EQ gain change) re-expresses it at the next process call, as the oracle does (orc_biquad_rescale_state): bit-exact
+    to the oracle across the change, and still a tolerance tier against EXACT (no jump)."""
+    T = 600
+    x = orc.noise(34, 0, C, 0, 2 * T)
+    k = c2_coefs(C)
+    k2 = k.copy()
+    k2[32:96, 4] = k[::-1][32:96, 4]
+    k2[32:96, 0, :3] *= 0.5
+    b = BiquadBank(C, 8)
+    b.SetMode(MODE_FAST)
+    b.SetVariant(variant)
+    b.SetCoeffs(k)
+    ya = b.ProcessBlock(x[:T])
+    b.SetCoeffs(k2[32:96], first=32)
+    yb = b.ProcessBlock(x[T:])
+    st = b.GetState()
+    b.close()
+    ost = np.zeros((C, 8, 4), dtype=np.float32)
+    wa = orc.biquad(x[:T], k, mode=loader.MODE_FAST, state=ost)
+    orc.biquad_rescale(ost, k, loader.MODE_FAST, k2, loader.MODE_FAST)
+    wb = orc.biquad(x[T:], k2, mode=loader.MODE_FAST, state=ost)
+    assert np.array_equal(bits(ya), bits(wa)) and np.array_equal(bits(yb), bits(wb))
+    assert np.array_equal(bits(st), bits(ost))
+    est = np.zeros((C, 8, 4), dtype=np.float32)
+    orc.biquad(x[:T], k, mode=MODE_EXACT, state=est)
+    assert np.abs(yb - orc.biquad(x[T:], k2, mode=MODE_EXACT, state=est)).max() <= 1e-3
+
+
+def test_fast_fallback_is_not_sticky_and_mode_switches_rescale(orc):
+    """A channel with b0 == 0 sends the bank to the FMA arithmetic; repairing it brings FAST back (history re-expressed in
+    the table's scaling); switching the mode mid-stream goes through plain values again.  The oracle re-decides per call."""
+    C, T = 64, 500
+    x = orc.noise(35, 0, C, 0, 3 * T)
+    k = c2_coefs(C)
+    kbad = k.copy()
+    kbad[5, 3] = (0.0, 1.0, 0.0, 0.0, 0.0)
+    b = BiquadBank(C, 8)
+    b.SetMode(MODE_FAST)
+    b.SetCoeffs(kbad)
+    ost = np.zeros((C, 8, 4), dtype=np.float32)
+    y1 = b.ProcessBlock(x[:T])
+    w1 = orc.biquad(x[:T], kbad, mode=loader.MODE_FAST, state=ost)          # runs FMA: channel 5 cannot be normalised
+    b.SetCoeffs(k[5:6], first=5)
+    y2 = b.ProcessBlock(x[T:2 * T])
+    orc.biquad_rescale(ost, kbad, loader.MODE_FAST, k, loader.MODE_FAST)
+    w2 = orc.biquad(x[T:2 * T], k, mode=loader.MODE_FAST, state=ost)
+    b.SetMode(MODE_EXACT)
+    y3 = b.ProcessBlock(x[2 * T:])
+    orc.biquad_rescale(ost, k, loader.MODE_FAST, k, loader.MODE_EXACT)
+    w3 = orc.biquad(x[2 * T:], k, mode=MODE_EXACT, state=ost)
+    b.close()
+    assert np.array_equal(bits(y1), bits(w1)) and np.array_equal(bits(y1), bits(orc.biquad(x[:T], kbad, mode=MODE_FMA)))
+    assert np.array_equal(bits(y2), bits(w2))
+    assert np.array_equal(bits(y3), bits(w3))
+
+
+def test_control_calls_are_ordered_on_a_non_blocking_stream(orc):
+    """process on a non-default (non-blocking) stream, Init, process again: Init takes effect between the two blocks and
+    cannot be overtaken by the first block's final history write; a coefficient change reaches only the second block."""
+    C, T = 9600, 4000
+    s = torch.cuda.Stream()
+    dev = torch.empty((T, C), dtype=torch.float32, device="cuda")
+    out1, out2, out3 = torch.empty_like(dev), torch.empty_like(dev), torch.empty_like(dev)
+    noise_device(dev.data_ptr(), 36, 0, C, 0, T)
+    torch.cuda.synchronize()
+    k = c2_coefs(C)
+    b = BiquadBank(C, 8)
+    b.SetMode(MODE_FMA)
+    b.SetCoeffs(k)
+    b.ProcessDevice(dev.data_ptr(), out1.data_ptr(), T, LAYOUT_FRAMES, s.cuda_stream)
+    b.Init(48000.0)
+    b.ProcessDevice(dev.data_ptr(), out2.data_ptr(), T, LAYOUT_FRAMES, s.cuda_stream)
+    b.SetCoeffs(k[::-1].copy())
+    b.ProcessDevice(dev.data_ptr(), out3.data_ptr(), T, LAYOUT_FRAMES, torch.cuda.current_stream().cuda_stream)  # another stream
+    torch.cuda.synchronize()
+    assert torch.equal(out1, out2)
+    x = dev[:, :64].cpu().numpy()
+    st = np.zeros((64, 8, 4), dtype=np.float32)
+    orc.biquad(x, k[:64], mode=MODE_FMA, state=st)
+    want3 = orc.biquad(x, k[::-1][:64], mode=MODE_FMA, state=st)
+    assert np.array_equal(bits(out3[:, :64].cpu().numpy()), bits(want3))
+    b.close()
 
 
 def test_fast_mode_one_pole_kinds(orc):

@@ -7,7 +7,7 @@ import pytest
 import torch
 
 from oracle import loader
-from ol_dsp_b200 import MODE_EXACT, MODE_FAST, BiquadBank, ChorusBank, DattorroBank, FxBank, VoiceBank, c2_coefs, fx
+from ol_dsp_b200 import MODE_EXACT, MODE_FAST, BiquadBank, ChorusBank, DattorroBank, FxBank, VoiceBank, c2_coefs, fx, noise_device
 
 pytestmark = pytest.mark.gpu
 T, BLOCK = 480000, 24000
@@ -43,6 +43,45 @@ def test_biquad_cascade_10s(orc, mode):
     assert np.array_equal(bits(y), bits(want))
     if mode == MODE_FAST:  # the throughput tier against the bit-exact tier over the whole 10 s
         assert np.abs(y - orc.biquad(x, k, mode=MODE_EXACT)).max() <= 1e-3
+
+
+def _streamed_bank_vs_oracle(orc, C, mode, kernel, blocks, block_frames, pick, seed=0x01D5B200):
+    """A full-width bank fed device-generated Philox noise block by block (state resident between blocks); the channels in
+    `pick` are checked against the oracle replaying the same noise.  Returns (max |y|, kernel name)."""
+    k = c2_coefs(C)
+    b = BiquadBank(C, 8)
+    b.SetMode(mode)
+    b.SetCoeffs(k)
+    dev = torch.empty((block_frames, C), dtype=torch.float32, device="cuda")
+    out = torch.empty_like(dev)
+    idx = torch.as_tensor(pick, device="cuda")
+    st = np.zeros((len(pick), 8, 4), dtype=np.float32)
+    kp = np.ascontiguousarray(k[pick])
+    for blk in range(blocks):
+        noise_device(dev.data_ptr(), seed, 0, C, blk * block_frames, block_frames)
+        b.ProcessDevice(dev.data_ptr(), out.data_ptr(), block_frames)
+        got = out[:, idx].cpu().numpy()
+        x = np.stack([orc.noise(seed, c, 1, blk * block_frames, block_frames)[:, 0] for c in pick], axis=1)
+        want = orc.biquad(x, kp, mode=mode, state=st)
+        assert b.LastKernel() == kernel
+        assert np.array_equal(bits(got), bits(want)), (blk, b.LastKernel())
+    b.close()
+
+
+@pytest.mark.parametrize("mode", [MODE_FAST, MODE_EXACT])
+def test_headline_shape_one_block(orc, mode):
+    """The shape bench.py times -- 65 536 channels x 24 000 frames through k_bq_tma -- with 256 channels spread over the
+    bank (first, middle and last warps of the grid) checked bit for bit against the oracle."""
+    pick = sorted(set(list(range(0, 64)) + list(range(20000, 20064)) + list(range(32768 + 31, 65536, 1021))[:64] + list(range(65472, 65536))))
+    _streamed_bank_vs_oracle(orc, 65536, mode, "k_bq_tma", 1, 24000, pick)
+
+
+@pytest.mark.parametrize("C,kernel", [(32768, "k_bq_tma"), (8192, "k_bq_skew"), (4096, "k_bq_sys")])
+def test_wide_banks_10s_fast(orc, C, kernel):
+    """The throughput tier over the full 10 s (20 blocks of 24 000 frames) at bank widths that reach each of the three
+    TMA kernels through the automatic choice; 64 channels spread over the bank against the oracle, bit-exact."""
+    pick = sorted(set(list(range(0, 16)) + list(range(C // 2 - 8, C // 2 + 8)) + list(range(7, C, C // 16))[:16] + list(range(C - 16, C))))
+    _streamed_bank_vs_oracle(orc, C, MODE_FAST, kernel, T // BLOCK, BLOCK, pick)
 
 
 @pytest.mark.parametrize("kind,name", [(fx.DELAY, "delayfx"), (fx.RACK, "fxrack")])

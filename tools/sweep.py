@@ -45,6 +45,20 @@ if __name__ == "__main__":
         for C, F in ((8192, 96000), (4096, 192000)):
             for mode in ("fast", "fma"):
                 run(f"C{C} {mode} auto", {}, ["--mode", mode, "--steps", "10", "--channels", str(C), "--block-frames", str(F)])
+    if which == "skew":
+        shapes = {4096: (192000, ["48x32x4", "48x32x6", "96x16x4", "96x16x6", "48x16x4"]),
+                  8192: (96000, ["48x16x4", "48x16x6", "48x32x4", "96x16x4", "48x8x4"]),
+                  16384: (48000, ["48x8x4", "48x16x4", "24x8x4"]),
+                  32768: (48000, ["24x8x4", "48x8x4", "24x6x4"]),
+                  65536: (24000, ["24x4x4", "24x6x4", "24x8x4"])}
+        for C, (F, cfgs) in shapes.items():
+            for mode in ("fast", "fma", "exact"):
+                for cfg in (cfgs if mode == "fast" else cfgs[:1]):
+                    run(f"C{C} {mode} skew {cfg}", {"OLB_BQ_SKEW_CFG": cfg},
+                        ["--variant", "4", "--mode", mode, "--steps", "10", "--channels", str(C), "--block-frames", str(F), "--no-small"])
+            for mode in ("fast", "exact"):
+                run(f"C{C} {mode} auto", {}, ["--mode", mode, "--steps", "10", "--channels", str(C), "--block-frames", str(F), "--no-small"])
+                run(f"C{C} {mode} tma", {}, ["--variant", "2", "--mode", mode, "--steps", "10", "--channels", str(C), "--block-frames", str(F), "--no-small"])
     if which == "small":
         for C, F in ((4096, 192000), (8192, 96000)):
             for cfg in ("1x32x24x1", "1x64x24x1", "1x32x48x1", "2x64x24x1", "1x32x24x2", "1x32x12x2", "2x32x24x2"):
