@@ -103,9 +103,38 @@ private:
     int status_ = OLB_OK;
 };
 
+// The cross-GPU voice bus of a SHARDED bank (one process per GPU, rank r owns a contiguous range of the voices): rank 0
+// makes the id (VoiceBusComm::UniqueId), the host's launcher hands it to the other ranks, every rank constructs its
+// VoiceBusComm (collective), and PolyvoiceBank::SetComm makes ProcessBlock return the mix of ALL ranks' voices
+// (Polyvoice.h:28-33 summed over the shards: one in-place NCCL all-reduce of the partial bus over NVLink).
+class VoiceBusComm {
+public:
+    static bool UniqueId(unsigned char (&id)[OLB_COMM_ID_BYTES]) { return olb_comm_unique_id(id) == OLB_OK; }
+    VoiceBusComm(int device, int rank, int world, const unsigned char (&id)[OLB_COMM_ID_BYTES]) { status_ = olb_comm_init(device, rank, world, id, &c_); }
+    ~VoiceBusComm() { olb_comm_destroy(c_); }
+    VoiceBusComm(const VoiceBusComm &) = delete;
+    VoiceBusComm &operator=(const VoiceBusComm &) = delete;
+    // device buffers: in place on `stream`, or overlapped on the communicator's own stream (see olbank.h)
+    int AllReduceBus(t_sample *bus_dev, uint64_t frames, uint32_t channels, void *stream = nullptr) {
+        return status_ = olb_voice_bus_allreduce(c_, bus_dev, frames, channels, stream);
+    }
+    int AllReduceBusAsync(t_sample *bus_dev, uint64_t frames, uint32_t channels, void *producer_stream, int slot) {
+        return status_ = olb_voice_bus_allreduce_async(c_, bus_dev, frames, channels, producer_stream, slot);
+    }
+    int Wait(int slot, void *stream = nullptr) { return status_ = olb_comm_wait(c_, slot, stream); }
+    int status() const { return status_; }
+    olb_comm *handle() { return c_; }
+
+private:
+    olb_comm *c_ = nullptr;
+    int status_ = OLB_OK;
+};
+
 class PolyvoiceBank {
 public:
     explicit PolyvoiceBank(VoiceBank &bank) : bank_(bank), playing_(bank.Voices()) {}
+    // this bank holds ONE SHARD of the voices: Process / ProcessBlock mix the voices of every rank of `comm`
+    void SetComm(VoiceBusComm *comm) { comm_ = comm; }
     InitStatus Init(t_sample sample_rate) { return bank_.Init(sample_rate); }  // Polyvoice.h:22-26
     // Polyvoice::NoteOn: the first voice that is not playing; silently dropped when all are busy (Polyvoice.h:35-43)
     void NoteOn(uint8_t midi_note, uint8_t velocity) {
@@ -129,14 +158,17 @@ public:
     void UpdateHardwareControl(uint8_t control, t_sample value) { bank_.UpdateHardwareControl(control, value); }  // Polyvoice.h:59-63
     void UpdateConfig(const t_sample *config16) { bank_.UpdateConfig(config16); }
     // Polyvoice::Process: *frame_out += every voice (Polyvoice.h:28-33); the caller zeroes the frame (main.cpp:79)
-    void Process(t_sample *frame_out) { bank_.ProcessBlock(nullptr, frame_out, 1, true, 1.0f, 1); }
+    void Process(t_sample *frame_out) { ProcessBlock(frame_out, 1, 1, 1.0f); }
     void ProcessBlock(t_sample *bus_host, uint64_t frames, uint32_t bus_channels = 1, t_sample gain = 1.0f) {
-        bank_.ProcessBlock(nullptr, bus_host, bus_channels, true, gain, frames);
+        if (comm_) status_ = olb_voice_process_host_comm(bank_.handle(), comm_->handle(), bus_host, bus_channels, 1, gain, frames);
+        else bank_.ProcessBlock(nullptr, bus_host, bus_channels, true, gain, frames);
     }
-    int status() const { return bank_.status(); }
+    int status() const { return status_ != OLB_OK ? status_ : bank_.status(); }
 
 private:
     VoiceBank &bank_;
+    VoiceBusComm *comm_ = nullptr;
+    int status_ = OLB_OK;
     std::vector<uint8_t> playing_;
 };
 

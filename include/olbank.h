@@ -30,7 +30,7 @@ extern "C" {
 #define OLB_OK 0
 #define OLB_E_ARG (-1)   /* bad argument (NULL handle, size 0, unsupported layout ...) */
 #define OLB_E_CUDA (-2)  /* a CUDA runtime/driver call failed; see olb_last_error() */
-#define OLB_E_NCCL (-3)  /* reserved for the voice-bus reduce */
+#define OLB_E_NCCL (-3)  /* an NCCL call failed (the cross-GPU voice-bus reduce); see olb_last_error() */
 #define OLB_E_STATE (-4) /* call not valid in the handle's current state */
 
 /* Audio layouts.  A reference frame is N consecutive floats (Fx.h:38); a bank frame is one float per
@@ -205,6 +205,34 @@ int olb_voice_process_events(olb_voice *h, const olb_voice_event *events, uint32
  * accumulate != 0 (Polyvoice::Process adds into *frame_out: Polyvoice.h:28-33). */
 int olb_voice_process_host(olb_voice *h, float *out_host, float *bus_host, uint32_t bus_channels, int accumulate, float bus_gain,
                            uint64_t frames);
+
+/* (e2) Cross-GPU voice bus ------------------------------------------------------------------------------
+ * Polyvoice::Process adds every voice into one frame (modules/synthlib/Polyvoice.h:28-33; the caller duplicates it to
+ * stereo, modules/ol_daisy/app/synth/main.cpp:83).  With the voices sharded over the GPUs of a box -- one process per GPU,
+ * no other inter-GPU traffic on the hot path -- each rank's olb_voice_process leaves a PARTIAL bus in bus_dev, and one
+ * in-place sum all-reduce (NCCL over NVLink / NVSwitch) makes it the global mixdown on every rank.  The partial bus is the
+ * send buffer.  Lifecycle: rank 0 calls olb_comm_unique_id and hands the OLB_COMM_ID_BYTES to the other ranks by whatever
+ * means the host has; every rank then calls olb_comm_init (collective).  Failures return OLB_E_NCCL.
+ *   olb_voice_bus_allreduce        on the caller's stream, after what produced the bus there
+ *   olb_voice_bus_allreduce_async  on the communicator's own stream once `producer_stream` has finished what is queued on it
+ *                                  now: the reduce of block k overlaps the voices of block k + 1 (written to another bus
+ *                                  buffer); `slot` (0..3) names the buffer
+ *   olb_comm_wait                  `stream` waits for the last reduce queued for `slot` (before reading the reduced bus, and
+ *                                  before the bank writes that buffer again)
+ *   olb_voice_process_host_comm    olb_voice_process_host with the bus reduced over the ranks before it is copied back:
+ *                                  the block form of Polyvoice::Process for a sharded bank (collective: every rank calls it) */
+#define OLB_COMM_ID_BYTES 128
+typedef struct olb_comm olb_comm;
+int olb_comm_unique_id(void *id_out);
+int olb_comm_init(int device, int rank, int world, const void *id_bytes, olb_comm **out);
+int olb_comm_destroy(olb_comm *c);
+int olb_comm_info(olb_comm *c, int *rank, int *world);
+int olb_voice_bus_allreduce(olb_comm *c, float *bus_dev, uint64_t frames, uint32_t channels, void *stream);
+int olb_voice_bus_allreduce_async(olb_comm *c, float *bus_dev, uint64_t frames, uint32_t channels, void *producer_stream, int slot);
+int olb_comm_wait(olb_comm *c, int slot, void *stream);
+int olb_comm_sync(olb_comm *c);
+int olb_voice_process_host_comm(olb_voice *h, olb_comm *c, float *bus_host, uint32_t bus_channels, int accumulate, float bus_gain,
+                                uint64_t frames);
 
 /* (a7) Dattorro plate reverb bank -------------------------------------------------------------------
  * Replaces libs/dattorro-verb/verb.h:5-26 for `instances` plates at once (mono in, stereo wet out):

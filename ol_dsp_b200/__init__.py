@@ -6,6 +6,6 @@ from .sampler import SamplerBank  # noqa: F401
 from .dattorro import DattorroBank  # noqa: F401
 from .fx import FxBank  # noqa: F401
 from .voice import Polyvoice, VoiceBank, VoiceMap  # noqa: F401
-from .sharding import reduce_bus, shard_range  # noqa: F401
+from .sharding import Comm, shard_range  # noqa: F401
 from .biquad import BiquadBank, design  # noqa: F401
 from .workloads import c2_coefs, noise_device  # noqa: F401

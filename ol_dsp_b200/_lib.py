@@ -88,6 +88,15 @@ def lib():
         "olb_voice_set_frequency": ([vp, u32, u32, _F, u32], i32),
         "olb_voice_playing": ([vp, u32, u32, C.POINTER(C.c_uint8)], i32),
         "olb_voice_process": ([vp, vp, vp, u32, i32, f32, vp, u64, vp], i32),
+        "olb_comm_unique_id": ([vp], i32),
+        "olb_comm_init": ([i32, i32, i32, vp, C.POINTER(vp)], i32),
+        "olb_comm_destroy": ([vp], i32),
+        "olb_comm_info": ([vp, C.POINTER(i32), C.POINTER(i32)], i32),
+        "olb_voice_bus_allreduce": ([vp, vp, u64, u32, vp], i32),
+        "olb_voice_bus_allreduce_async": ([vp, vp, u64, u32, vp, i32], i32),
+        "olb_comm_wait": ([vp, i32, vp], i32),
+        "olb_comm_sync": ([vp], i32),
+        "olb_voice_process_host_comm": ([vp, vp, vp, u32, i32, f32, u64], i32),
         "olb_dattorro_create": ([i32, u32, C.POINTER(vp)], i32),
         "olb_dattorro_destroy": ([vp], i32),
         "olb_dattorro_init": ([vp], i32),

@@ -419,6 +419,34 @@ OLB_API int olb_voice_process_host(olb_voice *h, float *out_host, float *bus_hos
     return OLB_OK;
 }
 
+// Polyvoice::Process of a bank whose voices are sharded over the ranks of `c`: every rank runs its voices into its partial
+// bus, the partial buses are summed in place over NVLink (olb_voice_bus_allreduce), and every rank gets the global mixdown
+// in bus_host.  With accumulate != 0 the mix is added to what bus_host holds ON RANK 0's terms: each rank adds its own
+// bus_host contents, so callers that accumulate pass the running frame on one rank and zeros on the others.
+OLB_API int olb_voice_process_host_comm(olb_voice *h, olb_comm *c, float *bus_host, uint32_t bus_channels, int accumulate, float bus_gain,
+                                        uint64_t frames) {
+    OLB_ARG(h && c, "olb_voice_process_host_comm: NULL handle");
+    if (frames == 0) return OLB_OK;
+    OLB_ARG(bus_host, "olb_voice_process_host_comm: bus_host is NULL");
+    OLB_ARG(bus_channels >= 1 && bus_channels <= 8, "olb_voice_process_host_comm: bus_channels must be 1..8");
+    DeviceGuard g(h->device);
+    const uint64_t V = h->V, chunk = host_chunk_frames(V, frames);
+    int rc = h->host.ensure(1, chunk * bus_channels);
+    if (rc) return rc;
+    for (uint64_t t0 = 0; t0 < frames; t0 += chunk) {
+        const uint64_t n = frames - t0 < chunk ? frames - t0 : chunk;
+        if (accumulate)
+            OLB_CUDA(cudaMemcpyAsync(h->host.d[1], bus_host + t0 * bus_channels, n * bus_channels * sizeof(float), cudaMemcpyHostToDevice, h->host.st));
+        rc = olb_voice_process(h, nullptr, h->host.d[1], bus_channels, accumulate, bus_gain, nullptr, n, h->host.st);
+        if (rc) return rc;
+        rc = olb_voice_bus_allreduce(c, h->host.d[1], n, bus_channels, h->host.st);
+        if (rc) return rc;
+        OLB_CUDA(cudaMemcpyAsync(bus_host + t0 * bus_channels, h->host.d[1], n * bus_channels * sizeof(float), cudaMemcpyDeviceToHost, h->host.st));
+    }
+    OLB_CUDA(cudaStreamSynchronize(h->host.st));
+    return OLB_OK;
+}
+
 // Sample-accurate control: `events` (sorted by frame) are applied BEFORE the frame they name, the block is cut there, and
 // the pieces run back to back on the stream -- what a host does by hand when it applies MIDI between audio blocks
 // (modules/juce/plugin/workout/src/PluginProcessor.cpp:24-38), at frame instead of block granularity.  Events with

@@ -1,6 +1,8 @@
-"""The N > 1 path on CPU (gloo, world_size 2): contiguous sharding of the units and the one exchange step of the hot
-path, the voice-bus sum.  Each rank computes the partial bus of ITS voices with the oracle
-(the CUDA bank needs a GPU), all-reduces it, and rank 0 compares with the oracle's single-process Polyvoice."""
+"""The N > 1 host logic on CPU (gloo, world_size 2): contiguous sharding of the units, the 128-byte communicator id
+carried from rank 0 to the others over the host's process group, and the arithmetic of the one exchange step of the hot
+path, the voice-bus sum.  Each rank computes the partial bus of ITS voices with the oracle (the
+CUDA bank and its NCCL reduce need GPUs: tests/test_voice_gpu.py), the partial buses are summed, and rank 0 compares
+with the oracle's single-process Polyvoice."""
 import os
 import socket
 
@@ -9,7 +11,7 @@ import torch
 import torch.distributed as dist
 import torch.multiprocessing as mp
 
-from ol_dsp_b200.sharding import reduce_bus, shard_range
+from ol_dsp_b200.sharding import ID_BYTES, shard_range
 
 
 def test_shard_range_covers_everything_once():
@@ -39,8 +41,12 @@ def _worker(rank, world, port, voices, frames, q):
     bus = np.zeros(frames, dtype=np.float32)
     for v in range(first, first + count):  # every voice of the shard plays its own note from frame 0
         bus += orc.voice(frames, 48000.0, None, [(0, loader.EV_NOTE_ON, 36 + v % 61, 100)])
+    # the id broadcast of Comm.from_torch_distributed (the bytes only: olb_comm_init itself needs a GPU)
+    ident = torch.arange(ID_BYTES, dtype=torch.uint8) if rank == 0 else torch.zeros(ID_BYTES, dtype=torch.uint8)
+    dist.broadcast(ident, 0)
+    assert ident.tolist() == list(range(ID_BYTES))
     t = torch.from_numpy(bus)
-    reduce_bus(t)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)  # what olb_voice_bus_allreduce computes on the GPUs (fp32 sum over ranks)
     if rank == 0:
         q.put(t.numpy().copy())
     dist.barrier()
