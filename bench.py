@@ -9,10 +9,24 @@ bank at 48 kHz fed replayable white noise, streamed in blocks of --block-frames 
 recurrence state resident on the device between blocks (a "step" = one block of every channel).
 Channels are independent, so N GPUs hold N disjoint 65,536-channel shards (weak scaling, no collective).
 `--channels 4096` gives BASELINE.json configs[1] (C2).  Prints ONE JSON line on rank 0.
+
+Beside the headline (`value`, device-resident, FAST tier) the line carries, all measured in the same run:
+  tiers         the same launch in the three arithmetic tiers (EXACT is the bit-exact one)
+  parity_check  one more step of the headline launch, checked bit for bit against the oracle for 256 channels
+  sustained     >= 2 s of back-to-back headline launches with the NVML clock / reason sample
+  strong        the SAME 65,536-channel bank cut into N shards (BASELINE configs[2] as written): 65,536 / N channels per GPU
+  voices        BASELINE configs[3]: 65,536 voices per GPU, the stereo bus reduced across the GPUs by the library's NCCL
+                all-reduce on its own stream, under the next block's voices
+  configs1      BASELINE configs[1] (4,096 channels), N = 1
+  e2e           the metric through olb_biquad_process_host (pinned HOST buffers near the GPU's NUMA node, H2D and D2H inside
+                the timed region), with the box's concurrent copy ceiling measured in the same run (pcie_frac)
+  cpu_baseline  the oracle's scalar cascade on the host cores, N = 1
 """
 import argparse
+import ctypes
 import json
 import os
+import subprocess
 import sys
 import threading
 import time
@@ -23,6 +37,7 @@ if ROOT not in sys.path:
 
 BYTES_PER_CHANNEL_SAMPLE = 8  # 4 B read + 4 B written per channel-sample
 SEED = 0x01D5B200
+LANE_OPS = {"fast": lambda s: 4 * s + 1, "fma": lambda s: 5 * s, "exact": lambda s: 9 * s}
 
 
 def parse():
@@ -38,10 +53,19 @@ def parse():
                    help="fast: normalised 4-op sections (throughput tier); fma: fused 5-op; exact: separately rounded (bit-exact tier)")
     p.add_argument("--variant", type=int, default=0)
     p.add_argument("--e2e-frames", type=int, default=4800)
-    p.add_argument("--e2e-steps", type=int, default=10)
+    p.add_argument("--e2e-seconds", type=float, default=2.0)
+    p.add_argument("--sustain-seconds", type=float, default=2.0)
+    p.add_argument("--voices", type=int, default=65536, help="voices per GPU of the `voices` record")
+    p.add_argument("--voice-frames", type=int, default=4800)
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-small", action="store_true", help="skip the 4096-channel configuration reported beside the headline")
+    p.add_argument("--no-tiers", action="store_true")
+    p.add_argument("--no-parity", action="store_true")
+    p.add_argument("--no-sustained", action="store_true")
+    p.add_argument("--no-strong", action="store_true")
+    p.add_argument("--no-voices", action="store_true")
+    p.add_argument("--only-headline", action="store_true", help="tuning aid: value + roofline only")
     return p.parse_args()
 
 
@@ -58,7 +82,7 @@ class ClockSampler(threading.Thread):
 
     def __init__(self, index):
         super().__init__(daemon=True)
-        self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz = index, [], set(), False, None
+        self.index, self.samples, self.reasons, self.stop_flag, self.max_mhz, self.power = index, [], set(), False, None, []
         try:
             import pynvml
             pynvml.nvmlInit()
@@ -82,6 +106,7 @@ class ClockSampler(threading.Thread):
         while not self.stop_flag:
             try:
                 self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                self.power.append(nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
                 r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
                 for bit, name in names.items():
                     if r & bit:
@@ -90,37 +115,75 @@ class ClockSampler(threading.Thread):
                 pass
             time.sleep(0.005)
 
+    def finish(self):
+        self.stop_flag = True
+        self.join()
+        return self.result()
+
     def result(self):
         s = sorted(self.samples)
         return {"sm_mhz": s[len(s) // 2] if s else None, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons),
-                "samples": len(s)}
+                "samples": len(s), "power_w_max": max(self.power) if self.power else None}
+
+
+def git_head():
+    try:
+        return subprocess.run(["git", "-C", ROOT, "rev-parse", "--short", "HEAD"], capture_output=True, text=True, timeout=5).stdout.strip() or None
+    except Exception:
+        return None
+
+
+# ---- the C2 / C3 coefficient workload, from the ORACLE's designer (reference arm and cpu_baseline: nothing of libolbank) ----
+def c2_coefs_oracle(orc, channels, sample_rate=48000.0):
+    """Same table as ol_dsp_b200.workloads.c2_coefs (tests/test_abi.py holds the two designers bit-equal)."""
+    import numpy as np
+    base = np.empty((64, 8, 5), dtype=np.float32)
+
+    def rbj(typ, f0, q, gain_db=0.0):
+        out = np.empty(5, dtype=np.float32)
+        orc.lib.orc_rbj(typ, sample_rate, f0, q, gain_db, out.ctypes.data_as(ctypes.POINTER(ctypes.c_float)))
+        return out
+
+    for m in range(64):
+        fc = 200.0 * (12000.0 / 200.0) ** (m / 63.0)
+        for s in range(4):
+            base[m, s] = rbj(0, fc, 0.707)
+        base[m, 4] = rbj(2, min(fc * 1.5, 0.45 * sample_rate), 2.0, 3.0)
+        base[m, 5] = rbj(2, max(fc * 0.5, 40.0), 2.0, -3.0)
+        base[m, 6] = rbj(1, 30.0, 0.707)
+        base[m, 7] = rbj(3, min(fc * 2.0, 0.45 * sample_rate), 1.0)
+    return np.ascontiguousarray(base[np.arange(channels) % 64])
 
 
 def cpu_arm(args, target_seconds):
-    """Times the oracle's scalar cascade on the host cores: one channel per std::thread at a time,
-    all hardware threads, on a bounded sample of the same workload (same coefficients, same noise)."""
+    """The oracle's scalar cascade on the host cores: one channel per std::thread at a time, all hardware threads, on a
+    bounded sample of the same workload (same coefficients, same noise).  -> (orc, coefs, channels, frames, threads, mode)"""
     from oracle import loader
-    from ol_dsp_b200 import c2_coefs
     orc = loader.oracle()
     threads = os.cpu_count() or 1
     mode = {"fast": loader.MODE_FAST, "fma": loader.MODE_FMA, "exact": loader.MODE_EXACT}[args.mode]
     frames = 48000
     probe_ch = threads
-    k = c2_coefs(max(probe_ch, 64))[:, :args.sections]
+    k = c2_coefs_oracle(orc, max(probe_ch, 64))[:, :args.sections]
     dt, _ = orc.biquad_bench(k[:probe_ch], None, frames, SEED, threads, mode)
     rate = probe_ch * frames / max(dt, 1e-6)
     channels = int(max(threads, min(args.channels, (rate * target_seconds / frames) // threads * threads)))
-    k = c2_coefs(channels)[:, :args.sections]
+    k = c2_coefs_oracle(orc, channels)[:, :args.sections]
     return orc, k, channels, frames, threads, mode
+
+
+CPU_NOTE = ("scalar oracle cascade (the reference has no biquad class, SURVEY.md 0.2), one channel per std::thread at a time, not "
+            "vectorised across channels; noise generation and the checksum pass are outside the timed region")
 
 
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    orc, k, channels, frames, threads, mode = cpu_arm(args, target_seconds=3.0)
-    steps = max(1, min(args.steps, 5))
-    warm = max(0, min(args.warmup, 1))
+    # each step is a bounded sample of the workload sized so that --steps of them end within a few minutes
+    per_step = max(0.5, min(3.0, 150.0 / max(1, args.steps + args.warmup)))
+    orc, k, channels, frames, threads, mode = cpu_arm(args, target_seconds=per_step)
+    steps, warm = max(1, args.steps), max(0, args.warmup)
     for _ in range(warm):
         orc.biquad_bench(k, None, frames, SEED, threads, mode)
     total = 0.0
@@ -128,17 +191,15 @@ def run_reference(args):
         dt, _ = orc.biquad_bench(k, None, frames, SEED, threads, mode)
         total += dt
     value = channels * frames * steps / total
-    sample = f"{channels} channels x {frames} frames per step ({steps} timed steps), same coefficients and Philox noise"
+    sample = f"{channels} channels x {frames} frames per step ({steps} timed steps, {warm} warm-up), same coefficients and Philox noise"
     line = {
         "impl": "reference", "metric": "channel-samples/s, 8-biquad cascade bank", "value": value, "unit": "channel-samples/s",
         "n_gpus": args.gpus, "steps": steps, "warmup": warm, "ms_per_step": 1e3 * total / steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(args, args.gpus),
-        "cpu_baseline": {"value": value, "unit": "channel-samples/s", "cores": threads, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "channel-samples/s", "cores": threads, "kind": "port", "sample": sample, "note": CPU_NOTE},
         "e2e": {"value": value, "unit": "channel-samples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
-        "note": "the reference has no biquad class (SURVEY.md 0.2): this arm is the scalar oracle cascade, one channel per "
-                "std::thread at a time, all host threads; noise generation is inside the timed region",
     }
     print(json.dumps(line), flush=True)
 
@@ -155,150 +216,326 @@ def workload_config(args, n):
 
 
 def run_olbank(args):
-    import ctypes as C
-
+    import numpy as np
     import torch
     import torch.distributed as dist
 
-    from ol_dsp_b200 import MODE_EXACT, MODE_FAST, MODE_FMA, BiquadBank, _lib, c2_coefs, noise_device, shard_range
+    from ol_dsp_b200 import MODE_EXACT, MODE_FAST, MODE_FMA, BiquadBank, Comm, VoiceBank, _lib, c2_coefs, noise_device, shard_range
 
+    MODES = {"fast": MODE_FAST, "fma": MODE_FMA, "exact": MODE_EXACT}
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     assert torch.cuda.is_available(), "bench.py needs a GPU: libolbank has no CPU fallback"
     torch.cuda.set_device(local)
+    L = _lib.lib()
+    numa = ctypes.c_int(-1)
+    _lib.check(L.olb_bind_thread_near(local, ctypes.byref(numa)))  # this rank's host thread next to its GPU, before anything is allocated
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    peak, peak_src = measured_peaks()
+    if args.only_headline:
+        args.no_tiers = args.no_parity = args.no_sustained = args.no_strong = args.no_voices = args.no_small = args.no_e2e = args.no_cpu_baseline = True
 
     def barrier():
         if world > 1:
             dist.barrier()
 
+    def max_over_ranks(v):
+        t = torch.tensor([v], dtype=torch.float64, device="cuda")
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    stream = torch.cuda.current_stream()
+    sid = stream.cuda_stream
+
+    def timed(fn, steps, warm=3, clocks=False):
+        """-> (ms per step, max over ranks; clock sample or None).  CUDA events on the launch stream, barrier on both sides."""
+        for _ in range(warm):
+            fn()
+        torch.cuda.synchronize()
+        barrier()
+        sampler = ClockSampler(local) if clocks else None
+        if sampler:
+            sampler.start()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(steps):
+            fn()
+        e1.record(stream)
+        torch.cuda.synchronize()
+        ck = sampler.finish() if sampler else None
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1)) / steps, ck
+
     Cn, S, F = args.channels, args.sections, args.block_frames
+    coefs = c2_coefs(Cn)[:, :S]
     bank = BiquadBank(Cn, S, 48000.0, device=local)
-    bank.SetMode({"fast": MODE_FAST, "fma": MODE_FMA, "exact": MODE_EXACT}[args.mode])
+    bank.SetMode(MODES[args.mode])
     bank.SetVariant(args.variant)
-    bank.SetCoeffs(c2_coefs(Cn)[:, :S])
+    bank.SetCoeffs(coefs)
     x = torch.empty((F, Cn), dtype=torch.float32, device="cuda")
     y = torch.empty_like(x)
-    stream = torch.cuda.current_stream()
     first, _ = shard_range(world * Cn, rank, world)  # rank r owns channels [r*Cn, (r+1)*Cn) of the job
-    noise_device(x.data_ptr(), SEED, first, Cn, 0, F, 1.0, 0, stream.cuda_stream)
+    noise_device(x.data_ptr(), SEED, first, Cn, 0, F, 1.0, 0, sid)
 
     def step():
-        bank.ProcessDevice(x.data_ptr(), y.data_ptr(), F, 0, stream.cuda_stream)
+        bank.ProcessDevice(x.data_ptr(), y.data_ptr(), F, 0, sid)
 
-    for _ in range(max(args.warmup, 3)):
-        step()
-    torch.cuda.synchronize()
-    barrier()
-    sampler = ClockSampler(local)
-    sampler.start()
+    def frac_of(cs_per_s):
+        return BYTES_PER_CHANNEL_SAMPLE * cs_per_s / 1e9 / peak
+
+    # ---- headline ------------------------------------------------------------------------------------------------
+    warm = max(args.warmup, 3)
     l0 = _lib.launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize()
-    e0.record(stream)
-    for _ in range(args.steps):
-        step()
-    e1.record(stream)
-    torch.cuda.synchronize()
-    launches = _lib.launch_count() - l0
-    sampler.stop_flag = True
-    sampler.join()
-    barrier()
-    ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
-    if world > 1:
-        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    total_ms = float(ms.item())
+    ms, clocks = timed(step, args.steps, warm, clocks=True)
+    launches = (_lib.launch_count() - l0) * args.steps // (args.steps + warm)
     kernel = bank.LastKernel()
-    value = world * Cn * F * args.steps / (total_ms * 1e-3)
+    value = world * Cn * F / (ms * 1e-3)
 
-    # ---- e2e: host buffers through olb_biquad_process_host (pinned memory, copies inside the timed region)
-    e2e = None
-    if not args.no_e2e:
-        EF = args.e2e_frames
-        hin = torch.empty((EF, Cn), dtype=torch.float32).pin_memory()
-        hout = torch.empty((EF, Cn), dtype=torch.float32).pin_memory()
-        hin.copy_(x[:EF].cpu())
-        bank.ProcessHostPtr(hin.data_ptr(), hout.data_ptr(), EF)  # warm-up (allocates staging)
-        bank.ProcessHostPtr(hin.data_ptr(), hout.data_ptr(), EF)
+    # ---- parity_check: one more step of the same launch, from the bank's read-back state, against the oracle ---------
+    parity = None
+    if not args.no_parity and rank == 0:
+        from oracle import loader
+        orc = loader.oracle()
+        omode = {"fast": loader.MODE_FAST, "fma": loader.MODE_FMA, "exact": loader.MODE_EXACT}[args.mode]
+        pick = np.unique(np.r_[0:64, Cn // 3:Cn // 3 + 64, Cn // 2:Cn // 2 + 32, np.linspace(0, Cn - 1, 64).astype(np.int64), Cn - 64:Cn] % Cn)
+        st = bank.GetState()[pick]
+        step()
+        torch.cuda.synchronize()
+        idx = torch.as_tensor(pick, device="cuda")
+        got, xin = y[:, idx].cpu().numpy(), x[:, idx].cpu().numpy()
+        want = orc.biquad(xin, np.ascontiguousarray(coefs[pick]), mode=omode, state=np.ascontiguousarray(st))
+        ok = bool(np.array_equal(got.view(np.uint32), want.view(np.uint32)))
+        parity = {"channels": int(len(pick)), "frames": F, "mode": args.mode, "kernel": bank.LastKernel(), "bit_exact": ok,
+                  "how": "one more step of the timed launch (same buffers, state read back from the bank before it); oracle fed the same "
+                         "input block and state; channels from the first, middle and last warps of the grid"}
+    if world > 1:
+        barrier()
+
+    # ---- sustained: >= sustain_seconds of back-to-back headline launches -----------------------------------------
+    sustained = None
+    if not args.no_sustained:
+        n = max(args.steps, int(args.sustain_seconds / (ms * 1e-3)) + 1)
+        ms_s, ck_s = timed(step, n, 1, clocks=True)
+        v = world * Cn * F / (ms_s * 1e-3)
+        sustained = {"seconds": n * ms_s * 1e-3, "steps": n, "value": v, "ms_per_step": ms_s, "roofline_frac": frac_of(v / world), "clocks": ck_s}
+
+    # ---- tiers: the same launch in the three arithmetic tiers ------------------------------------------------------
+    tiers = None
+    if not args.no_tiers:
+        tiers = {}
+        for name in ("exact", "fma", "fast"):
+            bank.SetMode(MODES[name])
+            bank.Init(48000.0)
+            ms_t, _ = timed(step, max(10, args.steps // 5), 3)
+            v = world * Cn * F / (ms_t * 1e-3)
+            tiers[name] = {"value": v, "ms_per_step": ms_t, "roofline_frac": frac_of(v / world), "kernel": bank.LastKernel(),
+                           "fp32_lane_ops_per_channel_sample": LANE_OPS[name](S),
+                           "parity": "bit-exact vs the oracle's separately rounded cascade" if name == "exact" else
+                                     "bit-exact vs the oracle's restatement of the same fused operations; tolerance tier vs EXACT (BASELINE.md)"}
+        bank.SetMode(MODES[args.mode])
+        bank.Init(48000.0)
+
+    # ---- strong: the SAME bank cut into `world` shards (BASELINE configs[2] as written) ---------------------------
+    strong = None
+    if not args.no_strong:
+        if world == 1:
+            strong = {"channels_total": Cn, "channels_per_gpu": Cn, "value": value, "ms_per_step": ms, "kernel": kernel,
+                      "roofline_frac": frac_of(value), "note": "N = 1: the headline launch"}
+        else:
+            Cs = Cn // world
+            Fs = F * world  # the same bytes per GPU and step as the headline
+            f0, _ = shard_range(Cn, rank, world)
+            bs = BiquadBank(Cs, S, 48000.0, device=local)
+            bs.SetMode(MODES[args.mode])
+            bs.SetCoeffs(np.ascontiguousarray(c2_coefs(Cn)[f0:f0 + Cs, :S]))
+            xs, ys = x.view(-1)[:Fs * Cs].view(Fs, Cs), y.view(-1)[:Fs * Cs].view(Fs, Cs)
+            noise_device(xs.data_ptr(), SEED, f0, Cs, 0, Fs, 1.0, 0, sid)
+            ms_g, _ = timed(lambda: bs.ProcessDevice(xs.data_ptr(), ys.data_ptr(), Fs, 0, sid), max(10, args.steps // 5), 3)
+            v = Cn * Fs / (ms_g * 1e-3)
+            strong = {"channels_total": Cn, "channels_per_gpu": Cs, "block_frames": Fs, "value": v, "ms_per_step": ms_g,
+                      "kernel": bs.LastKernel(), "roofline_frac": frac_of(v / world),
+                      "note": "total channel-samples/s of ONE 65,536-channel bank sharded by channel range; divide by the N = 1 line's value for the strong-scaling factor"}
+            bs.close()
+            noise_device(x.data_ptr(), SEED, first, Cn, 0, F, 1.0, 0, sid)
+
+    # ---- voices: BASELINE configs[3] -------------------------------------------------------------------------------
+    voices = None
+    if not args.no_voices:
+        V, VF = args.voices, args.voice_frames
+        vb = VoiceBank(V, device=local)
+        for cc, val in ((41, 70), (42, 30), (73, 64), (75, 60), (108, 10), (111, 40)):  # presets through the MIDI maps (main.cpp:114-128)
+            vb.UpdateMidiControl(cc, val)
+        vb.NoteOn((36 + (rank * V + np.arange(V)) % 61).astype(np.uint8))
+        comm = Comm.from_torch_distributed(local) if world > 1 else None
+        buses = [torch.zeros((VF, 2), dtype=torch.float32, device="cuda") for _ in range(2)]
+        k = [0]
+
+        def vstep():
+            slot = k[0] % 2  # block k -> bus k % 2; its reduce runs on the communicator's stream under block k + 1's voices
+            if comm:
+                comm.Wait(slot, sid)
+            vb.ProcessDevice(VF, bus_ptr=buses[slot].data_ptr(), bus_channels=2, bus_gain=1.0 / (V * world), stream=sid)
+            if comm:
+                comm.AllReduceBusAsync(buses[slot].data_ptr(), VF, 2, sid, slot)
+            k[0] += 1
+
+        def vsteps_done():
+            if comm:
+                comm.Wait(0, sid)
+                comm.Wait(1, sid)
+
+        for _ in range(3):
+            vstep()
+        vsteps_done()
         torch.cuda.synchronize()
         barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.e2e_steps):
-            bank.ProcessHostPtr(hin.data_ptr(), hout.data_ptr(), EF)
+        nv = 20
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(stream)
+        for _ in range(nv):
+            vstep()
+        vsteps_done()
+        e1.record(stream)
         torch.cuda.synchronize()
-        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
         barrier()
-        if world > 1:
-            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        e2e = {"value": world * Cn * EF * args.e2e_steps / float(dt.item()), "unit": "channel-samples/s",
-               "h2d_bytes_per_step": 4 * Cn * EF, "d2h_bytes_per_step": 4 * Cn * EF, "steps": args.e2e_steps,
-               "frames_per_step": EF, "api": "olb_biquad_process_host (pinned host buffers, chunked H2D/kernel/D2H overlap)",
-               "checksum": float(hout.double().sum().item())}
+        ms_v = max_over_ranks(e0.elapsed_time(e1)) / nv
+        voices = {"workload": f"BASELINE configs[3]: {V} SynthVoice per GPU (PolyBLEP saw + 2 ADSR + portamento + SVF), note 36 + (v mod 61), stereo bus",
+                  "voices_per_gpu": V, "frames_per_step": VF, "steps": nv, "value": world * V * VF / (ms_v * 1e-3), "unit": "voice-samples/s",
+                  "ms_per_step": ms_v, "kernel": "k_voice + k_bus_reduce",
+                  "collective": ("olb_voice_bus_allreduce_async (libolbank.so: one NCCL fp32 sum all-reduce of the [frames][2] bus per step, on the "
+                                 "communicator's stream under the next step's voices)") if comm else "none (1 GPU)",
+                  "bus_bytes_per_step": 8 * VF, "bus_checksum": float(buses[(k[0] - 1) % 2].double().sum().item())}
+        if comm:
+            comm.close()
+        vb.close()
 
     # ---- BASELINE configs[1] beside the headline (N = 1 only): the 4 096-channel cascade, 10 s of audio as 192 000-frame blocks
     small = None
     if world == 1 and not args.no_small and Cn != 4096:
-        C2, F2, K2 = 4096, 192000, 10
-        if e2e:
-            del hin, hout
+        C2, F2 = 4096, 192000
         b2 = BiquadBank(C2, S, 48000.0, device=local)
-        b2.SetMode({"fast": MODE_FAST, "fma": MODE_FMA, "exact": MODE_EXACT}[args.mode])
+        b2.SetMode(MODES[args.mode])
         b2.SetCoeffs(c2_coefs(C2)[:, :S])
-        x2 = torch.empty((F2, C2), dtype=torch.float32, device="cuda")
-        y2 = torch.empty_like(x2)
-        noise_device(x2.data_ptr(), SEED, 0, C2, 0, F2, 1.0, 0, stream.cuda_stream)
-        for _ in range(3):
-            b2.ProcessDevice(x2.data_ptr(), y2.data_ptr(), F2, 0, stream.cuda_stream)
-        torch.cuda.synchronize()
-        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        s0.record(stream)
-        for _ in range(K2):
-            b2.ProcessDevice(x2.data_ptr(), y2.data_ptr(), F2, 0, stream.cuda_stream)
-        s1.record(stream)
-        torch.cuda.synchronize()
-        ms2 = s0.elapsed_time(s1) / K2
+        x2, y2 = x.view(-1)[:F2 * C2].view(F2, C2), y.view(-1)[:F2 * C2].view(F2, C2)
+        noise_device(x2.data_ptr(), SEED, 0, C2, 0, F2, 1.0, 0, sid)
+        ms2, _ = timed(lambda: b2.ProcessDevice(x2.data_ptr(), y2.data_ptr(), F2, 0, sid), 10, 3)
         small = {"workload": "BASELINE configs[1]: 4096-channel x %d-section cascade, 48 kHz, streamed in 192000-frame blocks (4 s)" % S,
-                 "value": C2 * F2 / (ms2 * 1e-3), "unit": "channel-samples/s", "ms_per_step": ms2, "steps": K2, "kernel": b2.LastKernel(),
+                 "value": C2 * F2 / (ms2 * 1e-3), "unit": "channel-samples/s", "ms_per_step": ms2, "steps": 10, "kernel": b2.LastKernel(),
                  "gbs": BYTES_PER_CHANNEL_SAMPLE * C2 * F2 / (ms2 * 1e-3) / 1e9}
+        small["roofline_frac"] = small["gbs"] / peak
         b2.close()
-        del x2, y2
+        noise_device(x.data_ptr(), SEED, first, Cn, 0, F, 1.0, 0, sid)
+
+    # ---- e2e: host buffers through olb_biquad_process_host (pinned, near the GPU's NUMA node; copies inside the timed region)
+    e2e = None
+    if not args.no_e2e:
+        EF = args.e2e_frames
+        nbytes = 4 * Cn * EF
+        hp_in, hp_out = ctypes.c_void_p(), ctypes.c_void_p()
+        _lib.check(L.olb_host_alloc_near(local, ctypes.byref(hp_in), nbytes, None))
+        _lib.check(L.olb_host_alloc_near(local, ctypes.byref(hp_out), nbytes, None))
+        hin = np.ctypeslib.as_array(ctypes.cast(hp_in, ctypes.POINTER(ctypes.c_float)), shape=(EF, Cn))
+        hout = np.ctypeslib.as_array(ctypes.cast(hp_out, ctypes.POINTER(ctypes.c_float)), shape=(EF, Cn))
+        hin[:] = x[:EF].cpu().numpy()
+        hout[:] = 0
+
+        # (1) what the box gives N ranks copying both ways at once: plain cudaMemcpyAsync of the same buffers, 64 MiB chunks
+        s_up, s_dn = torch.cuda.Stream(), torch.cuda.Stream()
+        hin_t, hout_t = torch.from_numpy(hin), torch.from_numpy(hout)  # cudaHostAlloc memory: torch sees it as pinned
+        assert hin_t.is_pinned() and hout_t.is_pinned()
+        rows = max(1, (64 << 20) // (4 * Cn))
+
+        def raw_copies():
+            with torch.cuda.stream(s_up):
+                for r in range(0, EF, rows):
+                    x[r:r + rows].copy_(hin_t[r:r + rows], non_blocking=True)    # H2D
+            with torch.cuda.stream(s_dn):
+                for r in range(0, EF, rows):
+                    hout_t[r:r + rows].copy_(y[r:r + rows], non_blocking=True)   # D2H
+
+        def wall(fn, reps):
+            torch.cuda.synchronize()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                fn()
+            torch.cuda.synchronize()
+            dt = max_over_ranks(time.perf_counter() - t0)
+            barrier()
+            return dt
+
+        raw_copies()
+        t1 = wall(raw_copies, 2) / 2
+        raw_reps = max(3, int(1.0 / max(t1, 1e-4)))
+        t_raw = wall(raw_copies, raw_reps) / raw_reps
+        ceiling = nbytes / t_raw / 1e9  # GB/s per GPU, each direction, all ranks copying at once
+        noise_device(x.data_ptr(), SEED, first, Cn, 0, F, 1.0, 0, sid)
+        torch.cuda.synchronize()
+
+        # (2) the product path
+        def host_step():
+            bank.ProcessHostPtr(hp_in.value, hp_out.value, EF)
+
+        host_step()
+        host_step()
+        t1 = wall(host_step, 2) / 2
+        reps = max(5, int(args.e2e_seconds / max(t1, 1e-4)) + 1)
+        dt = wall(host_step, reps)
+        e2e_gbs = nbytes * reps / dt / 1e9
+        e2e = {"value": world * Cn * EF * reps / dt, "unit": "channel-samples/s",
+               "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": nbytes, "steps": reps, "seconds": dt,
+               "frames_per_step": EF, "api": "olb_biquad_process_host (pinned host buffers from olb_host_alloc_near, chunked H2D / kernel / D2H overlap)",
+               "gbs_each_way_per_gpu": e2e_gbs, "pcie_ceiling_gbs_each_way_per_gpu": ceiling, "pcie_frac": e2e_gbs / ceiling,
+               "pcie_ceiling_how": f"{world} rank(s) at once: plain async H2D + D2H copies of the same pinned buffers in 64 MiB chunks on two streams, "
+                                   f"{raw_reps} repetitions, max over ranks",
+               "numa_node": int(numa.value), "checksum": float(hout.astype(np.float64).sum())}
+        del hin, hout, hin_t, hout_t
+        L.olb_host_free(hp_in)
+        L.olb_host_free(hp_out)
 
     if rank == 0:
-        peak, peak_src = measured_peaks()
-        per_launch_s = total_ms * 1e-3 / args.steps
+        per_launch_s = ms * 1e-3
         achieved = BYTES_PER_CHANNEL_SAMPLE * Cn * F / per_launch_s / 1e9
-        traffic = None
+        traffic, traffic_commit = None, None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp):
             try:
-                traffic = json.load(open(tp)).get(kernel, {}).get(f"{Cn}x{F}")
+                tj = json.load(open(tp))
+                traffic = tj.get(kernel, {}).get(f"{Cn}x{F}")
+                traffic_commit = tj.get("commit")
             except Exception:
                 traffic = None
         line = {
             "metric": "channel-samples/s, 8-biquad cascade bank", "value": value, "unit": "channel-samples/s", "n_gpus": world,
-            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+            "steps": args.steps, "warmup": warm, "ms_per_step": ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": workload_config(args, world),
-            "kernel": kernel, "gpu_launches": int(launches), "clocks": sampler.result(),
+            "kernel": kernel, "gpu_launches": int(launches), "clocks": clocks, "head": git_head(),
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": traffic, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": BYTES_PER_CHANNEL_SAMPLE * Cn * F,
-                         "fp32_lane_ops_per_channel_sample": {"fast": 4 * S + 1, "fma": 5 * S, "exact": 9 * S}[args.mode]},
+                         "traffic": traffic, "traffic_commit": traffic_commit,
+                         "traffic_how": "ncu --set full dram__bytes_read.sum + dram__bytes_write.sum of one launch of this kernel at this shape, captured at traffic_commit (profiles/traffic.json)",
+                         "peak_source": peak_src, "algorithmic_bytes_per_launch": BYTES_PER_CHANNEL_SAMPLE * Cn * F,
+                         "fp32_lane_ops_per_channel_sample": LANE_OPS[args.mode](S)},
         }
-        if e2e:
-            line["e2e"] = e2e
-        if small:
-            small["roofline_frac"] = small["gbs"] / peak
-            line["configs1"] = small
+        for key, val in (("parity_check", parity), ("sustained", sustained), ("tiers", tiers), ("strong", strong), ("voices", voices),
+                         ("e2e", e2e), ("configs1", small)):
+            if val is not None:
+                line[key] = val
         if world == 1 and not args.no_cpu_baseline:
             orc, k, channels, frames, threads, mode = cpu_arm(args, target_seconds=8.0)
             dt, _ = orc.biquad_bench(k, None, frames, SEED, threads, mode)
             line["cpu_baseline"] = {"value": channels * frames / dt, "unit": "channel-samples/s", "cores": threads, "kind": "port",
-                                    "sample": f"{channels} channels x {frames} frames, scalar oracle cascade, one channel per std::thread at a time"}
+                                    "sample": f"{channels} channels x {frames} frames", "note": CPU_NOTE}
         print(json.dumps(line), flush=True)
+        if parity is not None and not parity["bit_exact"]:
+            print("bench.py: parity_check FAILED: the timed launch does not match the oracle", file=sys.stderr)
+            bank.close()
+            sys.exit(3)
     bank.close()
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 

@@ -46,6 +46,12 @@ int olb_device_count(int *count);
 /* Pinned host memory for the *_host entry points (cudaHostAlloc / cudaFreeHost). */
 int olb_host_alloc(void **ptr, size_t bytes);
 int olb_host_free(void *ptr);
+/* Host placement for the *_host entry points on a multi-socket box (one process per GPU): olb_bind_thread_near pins the
+ * CALLING thread to the cores of the NUMA node the GPU hangs off (/sys/bus/pci/devices/<bdf>/numa_node; a no-op when the
+ * platform reports none), olb_host_alloc_near does that and then allocates pinned memory from there.  *numa_node_out
+ * (optional) receives the node, -1 = unknown. */
+int olb_bind_thread_near(int device, int *numa_node_out);
+int olb_host_alloc_near(int device, void **ptr, size_t bytes, int *numa_node_out);
 /* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
 uint64_t olb_launch_count(void);
 

@@ -49,6 +49,8 @@ def lib():
         "olb_device_count": ([C.POINTER(i32)], i32),
         "olb_host_alloc": ([C.POINTER(vp), C.c_size_t], i32),
         "olb_host_free": ([vp], i32),
+        "olb_bind_thread_near": ([i32, C.POINTER(i32)], i32),
+        "olb_host_alloc_near": ([i32, C.POINTER(vp), C.c_size_t, C.POINTER(i32)], i32),
         "olb_launch_count": ([], u64),
         "olb_noise_fill": ([vp, u32, u32, u32, u64, u64, f32, i32, vp], i32),
         "olb_biquad_create": ([i32, u32, u32, f32, C.POINTER(vp)], i32),

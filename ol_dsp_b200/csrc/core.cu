@@ -1,6 +1,7 @@
 // core.cu -- library plumbing of libolbank.so: errors, device checks, pinned memory, replayable noise,
 // TMA descriptor encoding.  No DSP here.
 #include <cuda.h>
+#include <sched.h>
 #include <stdarg.h>
 
 #include "common.cuh"
@@ -135,6 +136,70 @@ OLB_API int olb_device_count(int *count) {
         n = 0;
     }
     *count = n;
+    return OLB_OK;
+}
+
+// ---- host placement: the NUMA node a GPU hangs off (sysfs), the calling thread bound to that node's cores ----------
+// Host-buffer entry points move every block over PCIe in both directions; with one process per GPU on a two-socket box the
+// copies of a rank whose buffers live on the other socket cross the inter-socket link and all ranks queue on one
+// memory controller.  olb_bind_thread_near pins the CALLING thread to the cores of the GPU's node (so that the pages it
+// allocates and touches afterwards land there); olb_host_alloc_near = bind + pinned allocation.
+static int gpu_numa_node(int device, int *node) {
+    char bdf[32] = "";
+    OLB_CUDA(cudaDeviceGetPCIBusId(bdf, sizeof(bdf), device));
+    for (char *p = bdf; *p; p++)
+        if (*p >= 'A' && *p <= 'F') *p = (char) (*p - 'A' + 'a');
+    char path[128];
+    snprintf(path, sizeof(path), "/sys/bus/pci/devices/%s/numa_node", bdf);
+    *node = -1;
+    if (FILE *f = fopen(path, "r")) {
+        if (fscanf(f, "%d", node) != 1) *node = -1;
+        fclose(f);
+    }
+    return OLB_OK;
+}
+
+OLB_API int olb_bind_thread_near(int device, int *numa_node_out) {
+    int node = -1;
+    int rc = gpu_numa_node(device, &node);
+    if (rc) return rc;
+    if (numa_node_out) *numa_node_out = node;
+    if (node < 0) return OLB_OK;  // the platform reports no locality: leave the thread where it is
+    char path[128];
+    snprintf(path, sizeof(path), "/sys/devices/system/node/node%d/cpulist", node);
+    FILE *f = fopen(path, "r");
+    if (!f) return OLB_OK;
+    cpu_set_t set;
+    CPU_ZERO(&set);
+    int a = 0, b = 0, n = 0;
+    char sep = 0;
+    while (fscanf(f, "%d", &a) == 1) {  // "0-31,64-95"
+        b = a;
+        if (fscanf(f, "%c", &sep) == 1 && sep == '-') {
+            if (fscanf(f, "%d", &b) != 1) b = a;
+            if (fscanf(f, "%c", &sep) != 1) sep = 0;
+        }
+        for (int c = a; c <= b && c < CPU_SETSIZE; c++, n++) CPU_SET(c, &set);
+        if (sep != ',') break;
+    }
+    fclose(f);
+    if (n) {
+        cpu_set_t allowed;  // stay inside what the container / launcher allows
+        if (sched_getaffinity(0, sizeof(allowed), &allowed) == 0) {
+            cpu_set_t both;
+            CPU_AND(&both, &set, &allowed);
+            if (CPU_COUNT(&both) > 0) sched_setaffinity(0, sizeof(both), &both);
+        }
+    }
+    return OLB_OK;
+}
+
+OLB_API int olb_host_alloc_near(int device, void **ptr, size_t bytes, int *numa_node_out) {
+    OLB_ARG(ptr && bytes, "olb_host_alloc_near: bad argument");
+    int rc = olb_bind_thread_near(device, numa_node_out);
+    if (rc) return rc;
+    DeviceGuard g(device);
+    OLB_CUDA(cudaHostAlloc(ptr, bytes, cudaHostAllocDefault));
     return OLB_OK;
 }
 
