@@ -10,6 +10,11 @@
 // NCCL is the transport (ncclAllReduce, fp32 sum); this file is the only place that names it.  The id is created on
 // rank 0 and carried to the other ranks by whatever the host has (bench.py: torch.distributed; a C++ host: its own
 // launcher) -- the library never opens a socket of its own.
+//
+// libnccl.so.2 is bound at the FIRST olb_comm_* call (dlopen), not at load time: a process has room for one NCCL, and a
+// host application that brings its own (PyTorch ships a newer one than the system's) must get to load it first, whatever
+// the order in which it and libolbank.so were loaded.
+#include <dlfcn.h>
 #include <nccl.h>
 
 #include <mutex>
@@ -18,8 +23,40 @@
 
 namespace olb {
 
+struct NcclApi {
+    ncclResult_t (*GetUniqueId)(ncclUniqueId *) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t *, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+    bool ok = false;
+};
+
+static const NcclApi &nccl() {
+    static NcclApi api = [] {
+        NcclApi a;
+        void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) return a;
+        a.GetUniqueId = (decltype(a.GetUniqueId)) dlsym(h, "ncclGetUniqueId");
+        a.CommInitRank = (decltype(a.CommInitRank)) dlsym(h, "ncclCommInitRank");
+        a.CommDestroy = (decltype(a.CommDestroy)) dlsym(h, "ncclCommDestroy");
+        a.AllReduce = (decltype(a.AllReduce)) dlsym(h, "ncclAllReduce");
+        a.GetErrorString = (decltype(a.GetErrorString)) dlsym(h, "ncclGetErrorString");
+        a.ok = a.GetUniqueId && a.CommInitRank && a.CommDestroy && a.AllReduce && a.GetErrorString;
+        return a;
+    }();
+    return api;
+}
+
+static int need_nccl() {
+    if (nccl().ok) return OLB_OK;
+    set_error("libnccl.so.2 could not be loaded (%s): the cross-GPU voice bus needs NCCL", dlerror() ? dlerror() : "symbols missing");
+    return OLB_E_NCCL;
+}
+
 static int fail_nccl(ncclResult_t r, const char *what, const char *file, int line) {
-    set_error("NCCL error %d (%s) in %s at %s:%d", (int) r, ncclGetErrorString(r), what, file, line);
+    set_error("NCCL error %d (%s) in %s at %s:%d", (int) r, nccl().GetErrorString(r), what, file, line);
     return OLB_E_NCCL;
 }
 #define OLB_NCCL(call)                                                          \
@@ -48,8 +85,10 @@ static_assert(OLB_COMM_ID_BYTES >= sizeof(ncclUniqueId), "OLB_COMM_ID_BYTES must
 
 OLB_API int olb_comm_unique_id(void *id_out) {
     OLB_ARG(id_out, "olb_comm_unique_id: id_out is NULL");
+    int rc = need_nccl();
+    if (rc) return rc;
     ncclUniqueId id;
-    OLB_NCCL(ncclGetUniqueId(&id));
+    OLB_NCCL(nccl().GetUniqueId(&id));
     memset(id_out, 0, OLB_COMM_ID_BYTES);
     memcpy(id_out, &id, sizeof(id));
     return OLB_OK;
@@ -60,7 +99,9 @@ OLB_API int olb_comm_init(int device, int rank, int world, const void *id_bytes,
     *out = nullptr;
     OLB_ARG(id_bytes, "olb_comm_init: id is NULL");
     OLB_ARG(world >= 1 && rank >= 0 && rank < world, "olb_comm_init: rank %d of %d", rank, world);
-    int rc = require_sm100(device);
+    int rc = need_nccl();
+    if (rc) return rc;
+    rc = require_sm100(device);
     if (rc) return rc;
     DeviceGuard g(device);
     olb_comm *c = new olb_comm();
@@ -69,7 +110,7 @@ OLB_API int olb_comm_init(int device, int rank, int world, const void *id_bytes,
     c->world = world;
     ncclUniqueId id;
     memcpy(&id, id_bytes, sizeof(id));
-    ncclResult_t r = ncclCommInitRank(&c->comm, world, id, rank);
+    ncclResult_t r = nccl().CommInitRank(&c->comm, world, id, rank);
     if (r != ncclSuccess) {
         delete c;
         return fail_nccl(r, "ncclCommInitRank", __FILE__, __LINE__);
@@ -89,7 +130,7 @@ OLB_API int olb_comm_destroy(olb_comm *c) {
     if (!c) return OLB_OK;
     DeviceGuard g(c->device);
     if (c->st) cudaStreamSynchronize(c->st);
-    if (c->comm) ncclCommDestroy(c->comm);
+    if (c->comm) nccl().CommDestroy(c->comm);
     if (c->produced) cudaEventDestroy(c->produced);
     for (cudaEvent_t e : c->done)
         if (e) cudaEventDestroy(e);
@@ -112,7 +153,7 @@ OLB_API int olb_voice_bus_allreduce(olb_comm *c, float *bus_dev, uint64_t frames
     if (frames == 0) return OLB_OK;
     std::lock_guard<std::mutex> lk(c->mu);
     DeviceGuard g(c->device);
-    OLB_NCCL(ncclAllReduce(bus_dev, bus_dev, (size_t) frames * channels, ncclFloat, ncclSum, c->comm, (cudaStream_t) stream));
+    OLB_NCCL(nccl().AllReduce(bus_dev, bus_dev, (size_t) frames * channels, ncclFloat, ncclSum, c->comm, (cudaStream_t) stream));
     return OLB_OK;
 }
 
@@ -127,7 +168,7 @@ OLB_API int olb_voice_bus_allreduce_async(olb_comm *c, float *bus_dev, uint64_t 
     DeviceGuard g(c->device);
     OLB_CUDA(cudaEventRecord(c->produced, (cudaStream_t) producer_stream));
     OLB_CUDA(cudaStreamWaitEvent(c->st, c->produced, 0));
-    if (frames) OLB_NCCL(ncclAllReduce(bus_dev, bus_dev, (size_t) frames * channels, ncclFloat, ncclSum, c->comm, c->st));
+    if (frames) OLB_NCCL(nccl().AllReduce(bus_dev, bus_dev, (size_t) frames * channels, ncclFloat, ncclSum, c->comm, c->st));
     OLB_CUDA(cudaEventRecord(c->done[slot], c->st));
     c->used[slot] = true;
     return OLB_OK;

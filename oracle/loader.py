@@ -126,6 +126,9 @@ class Oracle(_Fx):
         lib.orc_dattorro_slab_floats.restype = C.c_uint32
         lib.orc_biquad_bench.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_void_p, _F, C.c_uint64, C.c_uint32, C.c_int, C.POINTER(C.c_double)]
         lib.orc_biquad_bench.restype = C.c_double
+        lib.orc_biquad_bench_steps.argtypes = [C.c_int, C.c_uint32, C.c_uint32, C.c_void_p, _F, C.c_uint64, C.c_uint32, C.c_int, C.c_int, C.c_int,
+                                               C.POINTER(C.c_double)]
+        lib.orc_biquad_bench_steps.restype = C.c_double
         lib.orc_chorus_params.argtypes = [C.c_float] * 7 + [_F]
         lib.orc_chorus_params.restype = None
         lib.orc_chorus_ring_len.argtypes = [C.c_float]
@@ -244,12 +247,13 @@ class Oracle(_Fx):
         assert rc == 0
         return out
 
-    def biquad_bench(self, coefs, kinds, frames, seed, threads, mode=MODE_EXACT):
+    def biquad_bench(self, coefs, kinds, frames, seed, threads, mode=MODE_EXACT, steps=1, warmup=0):
+        """-> (seconds of the `steps` timed passes together, checksum of the last pass's output)"""
         coefs = np.ascontiguousarray(coefs, dtype=np.float32)
         k = np.ascontiguousarray(kinds, dtype=np.uint8) if kinds is not None else None
         chk = C.c_double(0)
-        dt = self.lib.orc_biquad_bench(mode, coefs.shape[0], coefs.shape[1], k.ctypes.data if k is not None else None,
-                                       _fp(coefs), frames, seed, threads, C.byref(chk))
+        dt = self.lib.orc_biquad_bench_steps(mode, coefs.shape[0], coefs.shape[1], k.ctypes.data if k is not None else None,
+                                             _fp(coefs), frames, seed, threads, warmup, steps, C.byref(chk))
         return dt, chk.value
 
 

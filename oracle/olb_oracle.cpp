@@ -1013,8 +1013,8 @@ ORC_API int orc_polyvoice_run(int n_voices, float sr, const float *config16, con
 // cascade (not vectorised across channels) over `frames` frames of replayable Philox noise held in
 // planar host buffers.  Returns the seconds of wall time the cascades took; noise generation and
 // the checksum pass are outside the timed region.
-ORC_API double orc_biquad_bench(int mode, uint32_t channels, uint32_t sections, const uint8_t *kinds, const float *coefs,
-                                uint64_t frames, uint32_t seed, int n_threads, double *checksum) {
+static double biquad_bench_steps(int mode, uint32_t channels, uint32_t sections, const uint8_t *kinds, const float *coefs, uint64_t frames,
+                                 uint32_t seed, int n_threads, int warmup, int steps, double *checksum) {
     // inputs first, OUTSIDE the timed region (the GPU arm's noise is resident before its clock starts too)
     std::vector<float> x((size_t) channels * frames), y((size_t) channels * frames);
     {
@@ -1027,23 +1027,37 @@ ORC_API double orc_biquad_bench(int mode, uint32_t channels, uint32_t sections, 
         for (auto &th : gen) th.join();
     }
     const int bank_mode = biquad_bank_mode(mode, channels, sections, kinds, coefs);
-    std::atomic<uint32_t> next(0);
-    auto t0 = std::chrono::steady_clock::now();
-    std::vector<std::thread> pool;
-    for (int w = 0; w < n_threads; w++) {
-        pool.emplace_back([&]() {
-            std::vector<float> st(4 * (size_t) sections);
-            for (uint32_t c; (c = next.fetch_add(1)) < channels;) {
-                std::fill(st.begin(), st.end(), 0.f);
-                biquad_channel(bank_mode, sections, kinds, coefs + (size_t) c * sections * 5, st.data(), &x[(size_t) c * frames],
-                               &y[(size_t) c * frames], frames, 1);
-            }
-        });
+    double total = 0.0;
+    for (int it = 0; it < warmup + steps; it++) {
+        std::atomic<uint32_t> next(0);
+        auto t0 = std::chrono::steady_clock::now();
+        std::vector<std::thread> pool;
+        for (int w = 0; w < n_threads; w++) {
+            pool.emplace_back([&]() {
+                std::vector<float> st(4 * (size_t) sections);
+                for (uint32_t c; (c = next.fetch_add(1)) < channels;) {
+                    std::fill(st.begin(), st.end(), 0.f);
+                    biquad_channel(bank_mode, sections, kinds, coefs + (size_t) c * sections * 5, st.data(), &x[(size_t) c * frames],
+                                   &y[(size_t) c * frames], frames, 1);
+                }
+            });
+        }
+        for (auto &th : pool) th.join();
+        if (it >= warmup) total += std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     }
-    for (auto &th : pool) th.join();
-    double dt = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     if (checksum) { double s = 0; for (float v : y) s += v; *checksum = s; }
-    return dt;
+    return total;
+}
+
+ORC_API double orc_biquad_bench(int mode, uint32_t channels, uint32_t sections, const uint8_t *kinds, const float *coefs,
+                                uint64_t frames, uint32_t seed, int n_threads, double *checksum) {
+    return biquad_bench_steps(mode, channels, sections, kinds, coefs, frames, seed, n_threads, 0, 1, checksum);
+}
+
+// `warmup` untimed + `steps` timed passes over ONE set of inputs; returns the seconds of the timed passes together.
+ORC_API double orc_biquad_bench_steps(int mode, uint32_t channels, uint32_t sections, const uint8_t *kinds, const float *coefs,
+                                      uint64_t frames, uint32_t seed, int n_threads, int warmup, int steps, double *checksum) {
+    return biquad_bench_steps(mode, channels, sections, kinds, coefs, frames, seed, n_threads, warmup, steps, checksum);
 }
 
 // ================================================================================================
