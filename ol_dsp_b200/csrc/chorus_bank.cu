@@ -282,6 +282,8 @@ using namespace olb;
 // Host side.  The RNBO params (0..1 domain) are kept per instance; the derived device table is rebuilt when a setter ran
 // (setters take effect at the next process call).
 struct olb_chorus {
+    std::recursive_mutex mu;
+    StreamOrder order;
     int device = 0;
     uint32_t I = 0, R = 0, w = 0, ctas = 0;
     float sample_rate = 48000.f;
@@ -339,8 +341,8 @@ static int chorus_reset(olb_chorus *h, float sr) {
         h->R = R;
     }
     h->sample_rate = sr;
-    OLB_CUDA(cudaMemset(h->d_ring, 0, (size_t) h->ctas * R * kChL * sizeof(float)));
-    OLB_CUDA(cudaMemset(h->d_state, 0, (size_t) 3 * h->I * sizeof(float)));
+    OLB_CUDA(h->order.memset0(h->d_ring, (size_t) h->ctas * R * kChL * sizeof(float)));
+    OLB_CUDA(h->order.memset0(h->d_state, (size_t) 3 * h->I * sizeof(float)));
     h->w = 0;
     h->dirty = true;
     return OLB_OK;
@@ -389,12 +391,14 @@ OLB_API int olb_chorus_destroy(olb_chorus *h) {
 
 OLB_API int olb_chorus_init(olb_chorus *h, float sample_rate) {
     OLB_ARG(h, "olb_chorus_init: NULL handle");
+    OLB_LOCK(h);
     DeviceGuard g(h->device);
     return chorus_reset(h, sample_rate);
 }
 
 OLB_API int olb_chorus_set_params(olb_chorus *h, uint32_t first, uint32_t count, int param, const float *values_host, uint32_t stride) {
     OLB_ARG(h && values_host, "olb_chorus_set_params: NULL argument");
+    OLB_LOCK(h);
     OLB_ARG((uint64_t) first + count <= h->I, "olb_chorus_set_params: range [%u, %u) exceeds %u instances", first, first + count, h->I);
     OLB_ARG(param >= OLB_CHORUS_RATE && param <= OLB_CHORUS_PHASE, "olb_chorus_set_params: unknown parameter %d", param);
     for (uint32_t i = 0; i < count; i++) {
@@ -407,6 +411,8 @@ OLB_API int olb_chorus_set_params(olb_chorus *h, uint32_t first, uint32_t count,
 }
 
 OLB_API int olb_chorus_set_param(olb_chorus *h, uint32_t first, uint32_t count, int param, float value) {
+    if (!h) { olb::set_error("NULL handle"); return OLB_E_ARG; }
+    OLB_LOCK(h);
     return olb_chorus_set_params(h, first, count, param, &value, 0);
 }
 
@@ -414,11 +420,13 @@ OLB_API const char *olb_chorus_last_kernel(olb_chorus *h) { return h ? h->last_k
 
 OLB_API int olb_chorus_process(olb_chorus *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream) {
     OLB_ARG(h, "olb_chorus_process: NULL handle");
+    OLB_LOCK(h);
     if (frames == 0) return OLB_OK;
     OLB_ARG(in_dev && out_dev, "olb_chorus_process: NULL buffer");
     OLB_ARG(frames < (1ull << 32), "olb_chorus_process: at most 2^32-1 frames per call");
     DeviceGuard g(h->device);
     cudaStream_t st = (cudaStream_t) stream;
+    OLB_CUDA(h->order.enter(st));
     if (h->dirty) {
         h->stage.resize((size_t) CP_COUNT * h->I);
         for (uint32_t i = 0; i < h->I; i++) chorus_derive(h, i, h->stage.data());
@@ -454,6 +462,7 @@ OLB_API int olb_chorus_process(olb_chorus *h, const float *in_dev, float *out_de
 // Host buffers [frames][instances]: chunked in time through device staging; returns when out_host is complete.
 OLB_API int olb_chorus_process_host(olb_chorus *h, const float *in_host, float *out_host, uint64_t frames) {
     OLB_ARG(h, "olb_chorus_process_host: NULL handle");
+    OLB_LOCK(h);
     if (frames == 0) return OLB_OK;
     OLB_ARG(in_host && out_host, "olb_chorus_process_host: NULL buffer");
     DeviceGuard g(h->device);

@@ -6,6 +6,7 @@
 #include <string.h>
 
 #include <atomic>
+#include <mutex>
 
 #include "../../include/olbank.h"
 
@@ -55,6 +56,11 @@ struct DeviceGuard {
 
 int require_sm100(int device);
 
+// Every entry point of a handle takes its mutex: setters and Init may come from a control thread while the audio thread
+// is inside process (the reference's hosts do exactly that, unsynchronised: workouts/workout_buddy.cpp:35-72 vs :76-100).
+// Recursive, because the composite calls (process_host, process_events, the plate rack) go through the public ones.
+#define OLB_LOCK(h) std::lock_guard<std::recursive_mutex> olb_lock_((h)->mu)
+
 // ---- stream ordering of a handle's device work ------------------------------------------------------
 // A bank's state lives on the device between process calls, and callers may hand every call a different stream (and
 // non-blocking streams are not ordered against the legacy default stream).  enter(st) makes `st` wait for whatever the
@@ -75,6 +81,8 @@ struct StreamOrder {
         return e;
     }
     cudaStream_t stream() const { return last; }
+    // control-path clear (Init): queued behind the work of the last process call, or at once when nothing was ever queued
+    cudaError_t memset0(void *p, size_t bytes) const { return any ? cudaMemsetAsync(p, 0, bytes, last) : cudaMemset(p, 0, bytes); }
     cudaError_t sync() const { return any ? cudaStreamSynchronize(last) : cudaSuccess; }
     void quiesce() const {
         if (any) cudaStreamSynchronize(last);

@@ -683,6 +683,8 @@ using namespace olb;
 // ================================================================================================
 // Host side.  Parameter setters mirror DattorroVerb_set* (verb.cpp:136-170); the maths runs here, on the host.
 struct olb_dattorro {
+    std::recursive_mutex mu;
+    StreamOrder order;
     int device = 0;
     uint32_t I = 0;
     PlateGeom geom{};
@@ -783,9 +785,10 @@ OLB_API int olb_dattorro_destroy(olb_dattorro *h) {
 // DattorroVerb_create()/initialize() again: rings, filters, counter and excursion cleared, parameters back to defaults.
 OLB_API int olb_dattorro_init(olb_dattorro *h) {
     OLB_ARG(h, "olb_dattorro_init: NULL handle");
+    OLB_LOCK(h);
     DeviceGuard g(h->device);
-    OLB_CUDA(cudaMemset(h->d_slab, 0, (size_t) h->slab_positions * h->I * sizeof(float)));
-    OLB_CUDA(cudaMemset(h->d_lp, 0, (size_t) 3 * h->I * sizeof(float)));
+    OLB_CUDA(h->order.memset0(h->d_slab, (size_t) h->slab_positions * h->I * sizeof(float)));
+    OLB_CUDA(h->order.memset0(h->d_lp, (size_t) 3 * h->I * sizeof(float)));
     plate_geometry(&h->geom, &h->slab_positions);
     h->t = 0;
     plate_defaults(h);
@@ -794,6 +797,7 @@ OLB_API int olb_dattorro_init(olb_dattorro *h) {
 
 OLB_API int olb_dattorro_set_params(olb_dattorro *h, uint32_t first, uint32_t count, int param, const float *values, uint32_t stride) {
     OLB_ARG(h && values, "olb_dattorro_set_params: NULL argument");
+    OLB_LOCK(h);
     OLB_ARG((uint64_t) first + count <= h->I, "olb_dattorro_set_params: range [%u, %u) exceeds %u instances", first, first + count, h->I);
     OLB_ARG(param >= OLB_PLATE_PREDELAY && param <= OLB_PLATE_DAMPING, "olb_dattorro_set_params: unknown parameter %d", param);
     const size_t I = h->I;
@@ -815,16 +819,20 @@ OLB_API int olb_dattorro_set_params(olb_dattorro *h, uint32_t first, uint32_t co
 }
 
 OLB_API int olb_dattorro_set_param(olb_dattorro *h, uint32_t first, uint32_t count, int param, float value) {
+    if (!h) { olb::set_error("NULL handle"); return OLB_E_ARG; }
+    OLB_LOCK(h);
     return olb_dattorro_set_params(h, first, count, param, &value, 0);
 }
 
 OLB_API int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *out_l_dev, float *out_r_dev, uint64_t frames, void *stream) {
     OLB_ARG(h, "olb_dattorro_process: NULL handle");
+    OLB_LOCK(h);
     if (frames == 0) return OLB_OK;
     OLB_ARG(in_dev && out_l_dev && out_r_dev, "olb_dattorro_process: NULL buffer");
     OLB_ARG(frames < (1ull << 32), "olb_dattorro_process: at most 2^32-1 frames per call");
     DeviceGuard g(h->device);
     cudaStream_t st = (cudaStream_t) stream;
+    OLB_CUDA(h->order.enter(st));
     if (h->par_dirty) {
         OLB_CUDA(cudaMemcpyAsync(h->d_par, h->par_host.data(), h->par_host.size() * sizeof(float), cudaMemcpyHostToDevice, st));
         OLB_CUDA(cudaStreamSynchronize(st));  // par_host may change right after we return
@@ -887,6 +895,7 @@ OLB_API int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *ou
 // Host buffers, all [frames][instances]: chunked in time through device staging; returns when the outputs are complete.
 OLB_API int olb_dattorro_process_host(olb_dattorro *h, const float *in_host, float *out_l_host, float *out_r_host, uint64_t frames) {
     OLB_ARG(h, "olb_dattorro_process_host: NULL handle");
+    OLB_LOCK(h);
     if (frames == 0) return OLB_OK;
     OLB_ARG(in_host && out_l_host && out_r_host, "olb_dattorro_process_host: NULL buffer");
     DeviceGuard g(h->device);

@@ -883,6 +883,8 @@ using namespace olb;
 // Host side: one host::RackParams per instance carries the reference objects' members; the device table is rebuilt
 // from it when a setter ran (setters take effect at the next Process, as Update() does in the reference).
 struct olb_fx {
+    std::recursive_mutex mu;
+    StreamOrder order;
     int device = 0, kind = 0;
     uint32_t I = 0;
     float sample_rate = 48000.f;
@@ -941,8 +943,8 @@ static int fx_init(olb_fx *h, float sr) {
             default: u.Init(sr); break;
         }
     }
-    OLB_CUDA(cudaMemset(h->d_svf, 0, (size_t) 4 * h->I * sizeof(float)));
-    if (h->d_ring) OLB_CUDA(cudaMemset(h->d_ring, 0, (size_t) h->I * kRing * sizeof(float)));
+    OLB_CUDA(h->order.memset0(h->d_svf, (size_t) 4 * h->I * sizeof(float)));
+    if (h->d_ring) OLB_CUDA(h->order.memset0(h->d_ring, (size_t) h->I * kRing * sizeof(float)));
     h->wp = 0;
     h->dirty = true;
     if (h->plate) {  // the plate has no sample-rate dependence (verb.cpp sizes its rings in samples); re-create = clear
@@ -1063,12 +1065,14 @@ OLB_API int olb_fx_destroy(olb_fx *h) {
 
 OLB_API int olb_fx_init(olb_fx *h, float sample_rate) {
     OLB_ARG(h, "olb_fx_init: NULL handle");
+    OLB_LOCK(h);
     DeviceGuard g(h->device);
     return fx_init(h, sample_rate);
 }
 
 OLB_API int olb_fx_update_midi(olb_fx *h, uint32_t first, uint32_t count, uint8_t control, uint8_t value) {
     OLB_ARG(h, "olb_fx_update_midi: NULL handle");
+    OLB_LOCK(h);
     OLB_ARG((uint64_t) first + count <= h->I, "olb_fx_update_midi: range [%u, %u) exceeds %u instances", first, first + count, h->I);
     for (uint32_t i = first; i < first + count; i++) {
         host::RackParams &u = h->units[i];
@@ -1085,6 +1089,7 @@ OLB_API int olb_fx_update_midi(olb_fx *h, uint32_t first, uint32_t count, uint8_
 
 OLB_API int olb_fx_update_hw(olb_fx *h, uint32_t first, uint32_t count, uint8_t control, const float *values_host, uint32_t stride) {
     OLB_ARG(h && values_host, "olb_fx_update_hw: NULL argument");
+    OLB_LOCK(h);
     OLB_ARG((uint64_t) first + count <= h->I, "olb_fx_update_hw: range [%u, %u) exceeds %u instances", first, first + count, h->I);
     for (uint32_t i = 0; i < count; i++) {
         host::RackParams &u = h->units[first + i];
@@ -1129,11 +1134,13 @@ static int fx_plate_stages(olb_fx *h, float *out_dev, uint32_t frames, cudaStrea
 
 OLB_API int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev_arg, uint64_t frames, void *stream) {
     OLB_ARG(h, "olb_fx_process: NULL handle");
+    OLB_LOCK(h);
     if (frames == 0) return OLB_OK;
     OLB_ARG(in_dev && out_dev_arg, "olb_fx_process: NULL buffer");
     OLB_ARG(frames < (1ull << 32), "olb_fx_process: at most 2^32-1 frames per call");
     DeviceGuard g(h->device);
     cudaStream_t st = (cudaStream_t) stream;
+    OLB_CUDA(h->order.enter(st));
     if (h->dirty) {
         h->plate_dirty = true;
         int rc = fx_upload(h, st);
@@ -1196,6 +1203,7 @@ OLB_API int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev_arg, u
 // Host buffers [frames][instances]: chunked in time through device staging; returns when out_host is complete.
 OLB_API int olb_fx_process_host(olb_fx *h, const float *in_host, float *out_host, uint64_t frames) {
     OLB_ARG(h, "olb_fx_process_host: NULL handle");
+    OLB_LOCK(h);
     if (frames == 0) return OLB_OK;
     OLB_ARG(in_host && out_host, "olb_fx_process_host: NULL buffer");
     DeviceGuard g(h->device);

@@ -153,6 +153,8 @@ __global__ void __launch_bounds__(128) k_sampler_play(float *out, uint32_t frame
 using namespace olb;
 
 struct olb_sampler {
+    std::recursive_mutex mu;
+    StreamOrder order;
     int device = 0;
     uint32_t I = 0, channels = 1;
     float sample_rate = 0.f;
@@ -234,6 +236,7 @@ OLB_API int olb_sampler_destroy(olb_sampler *h) {
 
 OLB_API int olb_sampler_load_sample(olb_sampler *h, const float *frames_host, uint64_t frames, uint32_t *sample_id) {
     OLB_ARG(h && sample_id, "olb_sampler_load_sample: NULL argument");
+    OLB_LOCK(h);
     OLB_ARG(frames_host || frames == 0, "olb_sampler_load_sample: NULL data");
     OLB_ARG(frames < 0xffffff00ull, "olb_sampler_load_sample: %llu frames exceed the 32-bit positions of the bank", (unsigned long long) frames);
     DeviceGuard g(h->device);
@@ -252,6 +255,8 @@ OLB_API int olb_sampler_load_sample(olb_sampler *h, const float *frames_host, ui
 }
 
 OLB_API int olb_sampler_set_sample(olb_sampler *h, uint32_t first, uint32_t count, const uint32_t *ids_host, int per_instance) {
+    if (!h) { olb::set_error("NULL handle"); return OLB_E_ARG; }
+    OLB_LOCK(h);
     int rc = sampler_range(h, first, count, "olb_sampler_set_sample");
     if (rc) return rc;
     OLB_ARG(ids_host, "olb_sampler_set_sample: NULL ids");
@@ -274,6 +279,7 @@ OLB_API int olb_sampler_set_sample(olb_sampler *h, uint32_t first, uint32_t coun
 
 OLB_API int olb_sampler_init(olb_sampler *h, float sample_rate) {
     OLB_ARG(h, "olb_sampler_init: NULL handle");
+    OLB_LOCK(h);
     h->sample_rate = sample_rate;  // Sample::Init stores the rate and nothing else (Sample.cpp:30-33)
     return OLB_OK;
 }
@@ -286,28 +292,44 @@ OLB_API int olb_sampler_init(olb_sampler *h, float sample_rate) {
     return OLB_OK;
 
 OLB_API int olb_sampler_seek(olb_sampler *h, uint32_t first, uint32_t count, uint64_t frame_index) {
+    if (!h) { olb::set_error("NULL handle"); return OLB_E_ARG; }
+    OLB_LOCK(h);
     OLB_SAMPLER_EACH("olb_sampler_seek", h->seek[k] = sampler_clamp(frame_index); h->flags[k] |= kSpSeek)
 }
 OLB_API int olb_sampler_set_loop_start(olb_sampler *h, uint32_t first, uint32_t count, uint64_t frame_index) {
+    if (!h) { olb::set_error("NULL handle"); return OLB_E_ARG; }
+    OLB_LOCK(h);
     OLB_SAMPLER_EACH("olb_sampler_set_loop_start", h->ls[k] = sampler_clamp(frame_index))
 }
 OLB_API int olb_sampler_set_loop_end(olb_sampler *h, uint32_t first, uint32_t count, uint64_t frame_index) {
+    if (!h) { olb::set_error("NULL handle"); return OLB_E_ARG; }
+    OLB_LOCK(h);
     OLB_SAMPLER_EACH("olb_sampler_set_loop_end", h->le[k] = sampler_clamp(frame_index))
 }
 OLB_API int olb_sampler_set_play_mode(olb_sampler *h, uint32_t first, uint32_t count, int mode) {
+    if (!h) { olb::set_error("NULL handle"); return OLB_E_ARG; }
+    OLB_LOCK(h);
     OLB_ARG(mode == OLB_SAMPLE_ONESHOT || mode == OLB_SAMPLE_LOOP, "olb_sampler_set_play_mode: unknown mode %d", mode);
     OLB_SAMPLER_EACH("olb_sampler_set_play_mode", h->flags[k] = mode == OLB_SAMPLE_LOOP ? h->flags[k] | kSpLoop : h->flags[k] & ~kSpLoop)
 }
 OLB_API int olb_sampler_play(olb_sampler *h, uint32_t first, uint32_t count) {
+    if (!h) { olb::set_error("NULL handle"); return OLB_E_ARG; }
+    OLB_LOCK(h);
     OLB_SAMPLER_EACH("olb_sampler_play", h->flags[k] |= kSpPlaying)
 }
 OLB_API int olb_sampler_pause(olb_sampler *h, uint32_t first, uint32_t count) {
+    if (!h) { olb::set_error("NULL handle"); return OLB_E_ARG; }
+    OLB_LOCK(h);
     OLB_SAMPLER_EACH("olb_sampler_pause", h->flags[k] &= ~kSpPlaying)
 }
 OLB_API int olb_sampler_toggle_play(olb_sampler *h, uint32_t first, uint32_t count) {
+    if (!h) { olb::set_error("NULL handle"); return OLB_E_ARG; }
+    OLB_LOCK(h);
     OLB_SAMPLER_EACH("olb_sampler_toggle_play", h->flags[k] ^= kSpPlaying)
 }
 OLB_API int olb_sampler_gate(olb_sampler *h, uint32_t first, uint32_t count, int on) {
+    if (!h) { olb::set_error("NULL handle"); return OLB_E_ARG; }
+    OLB_LOCK(h);
     if (on) {  // SampleSoundSource::GateOn: Seek(0); Play()
         OLB_SAMPLER_EACH("olb_sampler_gate", h->seek[k] = 0; h->flags[k] |= kSpSeek | kSpPlaying)
     }
@@ -315,12 +337,14 @@ OLB_API int olb_sampler_gate(olb_sampler *h, uint32_t first, uint32_t count, int
 }
 
 OLB_API int olb_sampler_position(olb_sampler *h, uint32_t first, uint32_t count, uint64_t *frame_index_host, uint8_t *playing_host) {
+    if (!h) { olb::set_error("NULL handle"); return OLB_E_ARG; }
+    OLB_LOCK(h);
     int rc = sampler_range(h, first, count, "olb_sampler_position");
     if (rc) return rc;
     DeviceGuard g(h->device);
     if (frame_index_host) {
         std::vector<uint32_t> cur(count);
-        OLB_CUDA(cudaDeviceSynchronize());
+        OLB_CUDA(h->order.sync());  // everything queued on the bank so far has advanced the positions
         OLB_CUDA(cudaMemcpy(cur.data(), h->dev(5) + first, (size_t) count * 4, cudaMemcpyDeviceToHost));
         for (uint32_t i = 0; i < count; i++) frame_index_host[i] = (h->flags[first + i] & kSpSeek) ? h->seek[first + i] : cur[i];
     }
@@ -331,6 +355,7 @@ OLB_API int olb_sampler_position(olb_sampler *h, uint32_t first, uint32_t count,
 
 OLB_API int olb_sampler_process(olb_sampler *h, float *out_dev, uint64_t frames, void *stream) {
     OLB_ARG(h, "olb_sampler_process: NULL handle");
+    OLB_LOCK(h);
     if (frames == 0) return OLB_OK;
     OLB_ARG(out_dev, "olb_sampler_process: NULL buffer");
     OLB_ARG(frames <= 0x7fffffffull, "olb_sampler_process: at most 2^31 - 1 frames per call");
@@ -338,6 +363,7 @@ OLB_API int olb_sampler_process(olb_sampler *h, float *out_dev, uint64_t frames,
             h->channels * sizeof(float));
     DeviceGuard g(h->device);
     cudaStream_t st = (cudaStream_t) stream;
+    OLB_CUDA(h->order.enter(st));
     int rc = sampler_upload(h, st);
     if (rc) return rc;
     const uint32_t I = h->I, blocks = (I + 127) / 128;
@@ -368,6 +394,7 @@ OLB_API int olb_sampler_process(olb_sampler *h, float *out_dev, uint64_t frames,
 
 OLB_API int olb_sampler_process_host(olb_sampler *h, float *out_host, uint64_t frames) {
     OLB_ARG(h, "olb_sampler_process_host: NULL handle");
+    OLB_LOCK(h);
     if (frames == 0) return OLB_OK;
     OLB_ARG(out_host, "olb_sampler_process_host: NULL buffer");
     DeviceGuard g(h->device);

@@ -183,6 +183,8 @@ using namespace olb;
 // ================================================================================================
 // Host side: one host::VoiceParams per voice carries the reference object's members.
 struct olb_voice {
+    std::recursive_mutex mu;
+    StreamOrder order;
     int device = 0;
     uint32_t V = 0;
     std::vector<host::VoiceParams> voices;
@@ -234,7 +236,7 @@ static int voice_init_all(olb_voice *h, float sr) {
         u.Init(sr);
         u.retrigger = false;
     }
-    OLB_CUDA(cudaMemset(h->d_state, 0, (size_t) VS_COUNT * h->V * sizeof(float)));
+    OLB_CUDA(h->order.memset0(h->d_state, (size_t) VS_COUNT * h->V * sizeof(float)));
     h->dirty = true;
     return OLB_OK;
 }
@@ -280,6 +282,7 @@ OLB_API int olb_voice_destroy(olb_voice *h) {
 
 OLB_API int olb_voice_init(olb_voice *h, float sample_rate) {
     OLB_ARG(h, "olb_voice_init: NULL handle");
+    OLB_LOCK(h);
     DeviceGuard g(h->device);
     return voice_init_all(h, sample_rate);
 }
@@ -290,6 +293,7 @@ OLB_API int olb_voice_init(olb_voice *h, float sample_rate) {
 
 OLB_API int olb_voice_update_midi(olb_voice *h, uint32_t first, uint32_t count, uint8_t control, uint8_t value) {
     OLB_VOICE_RANGE("olb_voice_update_midi");
+    OLB_LOCK(h);
     for (uint32_t i = first; i < first + count; i++) h->voices[i].UpdateMidiControl(control, value);
     h->dirty = true;
     return OLB_OK;
@@ -297,6 +301,7 @@ OLB_API int olb_voice_update_midi(olb_voice *h, uint32_t first, uint32_t count, 
 
 OLB_API int olb_voice_update_hw(olb_voice *h, uint32_t first, uint32_t count, uint8_t control, const float *values_host, uint32_t stride) {
     OLB_VOICE_RANGE("olb_voice_update_hw");
+    OLB_LOCK(h);
     OLB_ARG(values_host, "olb_voice_update_hw: values_host is NULL");
     for (uint32_t i = 0; i < count; i++) h->voices[first + i].UpdateHardwareControl(control, values_host[(size_t) i * stride]);
     h->dirty = true;
@@ -305,6 +310,7 @@ OLB_API int olb_voice_update_hw(olb_voice *h, uint32_t first, uint32_t count, ui
 
 OLB_API int olb_voice_update_config(olb_voice *h, uint32_t first, uint32_t count, const float *config16_host) {
     OLB_VOICE_RANGE("olb_voice_update_config");
+    OLB_LOCK(h);
     OLB_ARG(config16_host, "olb_voice_update_config: config is NULL");
     for (uint32_t i = first; i < first + count; i++) h->voices[i].UpdateConfig(config16_host);
     h->dirty = true;
@@ -313,6 +319,7 @@ OLB_API int olb_voice_update_config(olb_voice *h, uint32_t first, uint32_t count
 
 OLB_API int olb_voice_note_on(olb_voice *h, uint32_t first, uint32_t count, const uint8_t *notes_host, uint32_t stride, uint8_t velocity) {
     OLB_VOICE_RANGE("olb_voice_note_on");
+    OLB_LOCK(h);
     OLB_ARG(notes_host, "olb_voice_note_on: notes_host is NULL");
     (void) velocity;  // the reference ignores it too (SynthVoice.h:245-251)
     for (uint32_t i = 0; i < count; i++) h->voices[first + i].NoteOn(notes_host[(size_t) i * stride]);
@@ -323,6 +330,7 @@ OLB_API int olb_voice_note_on(olb_voice *h, uint32_t first, uint32_t count, cons
 
 OLB_API int olb_voice_note_off(olb_voice *h, uint32_t first, uint32_t count) {
     OLB_VOICE_RANGE("olb_voice_note_off");
+    OLB_LOCK(h);
     for (uint32_t i = first; i < first + count; i++) h->voices[i].NoteOff();
     h->dirty = true;
     return OLB_OK;
@@ -330,6 +338,7 @@ OLB_API int olb_voice_note_off(olb_voice *h, uint32_t first, uint32_t count) {
 
 OLB_API int olb_voice_set_gate(olb_voice *h, uint32_t first, uint32_t count, int gate) {
     OLB_VOICE_RANGE("olb_voice_set_gate");
+    OLB_LOCK(h);
     for (uint32_t i = first; i < first + count; i++) h->voices[i].gate = gate ? 1 : 0;
     h->dirty = true;
     return OLB_OK;
@@ -337,6 +346,7 @@ OLB_API int olb_voice_set_gate(olb_voice *h, uint32_t first, uint32_t count, int
 
 OLB_API int olb_voice_set_frequency(olb_voice *h, uint32_t first, uint32_t count, const float *freqs_host, uint32_t stride) {
     OLB_VOICE_RANGE("olb_voice_set_frequency");
+    OLB_LOCK(h);
     OLB_ARG(freqs_host, "olb_voice_set_frequency: freqs_host is NULL");
     for (uint32_t i = 0; i < count; i++) h->voices[first + i].freq = freqs_host[(size_t) i * stride];
     h->dirty = true;
@@ -345,6 +355,7 @@ OLB_API int olb_voice_set_frequency(olb_voice *h, uint32_t first, uint32_t count
 
 OLB_API int olb_voice_playing(olb_voice *h, uint32_t first, uint32_t count, uint8_t *playing_host) {
     OLB_VOICE_RANGE("olb_voice_playing");
+    OLB_LOCK(h);
     OLB_ARG(playing_host, "olb_voice_playing: playing_host is NULL");
     for (uint32_t i = 0; i < count; i++) playing_host[i] = h->voices[first + i].playing;
     return OLB_OK;
@@ -353,12 +364,14 @@ OLB_API int olb_voice_playing(olb_voice *h, uint32_t first, uint32_t count, uint
 OLB_API int olb_voice_process(olb_voice *h, float *out_dev, float *bus_dev, uint32_t bus_channels, int accumulate, float bus_gain,
                               float *trace_dev, uint64_t frames, void *stream) {
     OLB_ARG(h, "olb_voice_process: NULL handle");
+    OLB_LOCK(h);
     if (frames == 0) return OLB_OK;
     OLB_ARG(out_dev || bus_dev || trace_dev, "olb_voice_process: no output buffer given");
     OLB_ARG(!bus_dev || (bus_channels >= 1 && bus_channels <= 8), "olb_voice_process: bus_channels must be 1..8");
     OLB_ARG(frames < (1ull << 31), "olb_voice_process: at most 2^31-1 frames per call");
     DeviceGuard g(h->device);
     cudaStream_t st = (cudaStream_t) stream;
+    OLB_CUDA(h->order.enter(st));
     if (h->dirty) {
         int rc = voice_upload(h, st);
         if (rc) return rc;
@@ -395,6 +408,7 @@ OLB_API int olb_voice_process(olb_voice *h, float *out_dev, float *bus_dev, uint
 OLB_API int olb_voice_process_host(olb_voice *h, float *out_host, float *bus_host, uint32_t bus_channels, int accumulate, float bus_gain,
                                    uint64_t frames) {
     OLB_ARG(h, "olb_voice_process_host: NULL handle");
+    OLB_LOCK(h);
     if (frames == 0) return OLB_OK;
     OLB_ARG(out_host || bus_host, "olb_voice_process_host: no output buffer given");
     OLB_ARG(!bus_host || (bus_channels >= 1 && bus_channels <= 8), "olb_voice_process_host: bus_channels must be 1..8");
@@ -426,6 +440,7 @@ OLB_API int olb_voice_process_host(olb_voice *h, float *out_host, float *bus_hos
 OLB_API int olb_voice_process_host_comm(olb_voice *h, olb_comm *c, float *bus_host, uint32_t bus_channels, int accumulate, float bus_gain,
                                         uint64_t frames) {
     OLB_ARG(h && c, "olb_voice_process_host_comm: NULL handle");
+    OLB_LOCK(h);
     if (frames == 0) return OLB_OK;
     OLB_ARG(bus_host, "olb_voice_process_host_comm: bus_host is NULL");
     OLB_ARG(bus_channels >= 1 && bus_channels <= 8, "olb_voice_process_host_comm: bus_channels must be 1..8");
@@ -455,6 +470,7 @@ OLB_API int olb_voice_process_host_comm(olb_voice *h, olb_comm *c, float *bus_ho
 OLB_API int olb_voice_process_events(olb_voice *h, const olb_voice_event *events, uint32_t n_events, float *out_dev, float *bus_dev,
                                      uint32_t bus_channels, int accumulate, float bus_gain, uint64_t frames, void *stream) {
     OLB_ARG(h, "olb_voice_process_events: NULL handle");
+    OLB_LOCK(h);
     OLB_ARG(n_events == 0 || events, "olb_voice_process_events: events is NULL");
     for (uint32_t e = 0; e < n_events; e++) {
         OLB_ARG(events[e].frame <= frames && (e == 0 || events[e].frame >= events[e - 1].frame),

@@ -91,3 +91,13 @@ def test_sampler_mirror(orc, tmp_path):
         assert np.array_equal(bits(y[:, i]), bits(want[:, 0])), i
         if i == 0:
             assert int(out.split()[0]) == int(st[4]) == n
+
+
+def test_setters_from_a_control_thread_never_tear_a_block():
+    """tests/cpp/setter_race.cpp: a control thread flips the coefficient table of every channel (and an fx bank's cutoff)
+    as fast as it can while the audio thread streams blocks; every block must be computed with ONE coherent table."""
+    import __graft_entry__ as g
+    g.build_cpp_hosts()
+    r = subprocess.run([os.path.join(g.ROOT, "tests", "cpp", "setter_race"), "4096", "300", "64"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "torn 0" in r.stdout
