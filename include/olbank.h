@@ -269,6 +269,9 @@ int olb_dattorro_set_params(olb_dattorro *h, uint32_t first, uint32_t count, int
 /* For each frame: DattorroVerb_process(in); out_l = getLeft(); out_r = getRight().  Device buffers, all
  * [frames][instances] (instance fastest). */
 int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *out_l_dev, float *out_r_dev, uint64_t frames, void *stream);
+/* Diagnostics: which kernel the last process call launched ("k_dattorro_smem": rings resident in shared memory, blocks of
+ * >= 8 192 frames; "k_dattorro_split": rings in HBM, any block length). */
+const char *olb_dattorro_last_kernel(olb_dattorro *h);
 /* Same with HOST buffers (all [frames][instances]); returns when the outputs are complete. */
 int olb_dattorro_process_host(olb_dattorro *h, const float *in_host, float *out_l_host, float *out_r_host, uint64_t frames);
 

@@ -105,6 +105,7 @@ def lib():
         "olb_dattorro_set_param": ([vp, u32, u32, i32, f32], i32),
         "olb_dattorro_set_params": ([vp, u32, u32, i32, _F, u32], i32),
         "olb_dattorro_process": ([vp, vp, vp, vp, u64, vp], i32),
+        "olb_dattorro_last_kernel": ([vp], C.c_char_p),
         "olb_chorus_create": ([i32, u32, f32, C.POINTER(vp)], i32),
         "olb_chorus_destroy": ([vp], i32),
         "olb_chorus_init": ([vp, f32], i32),

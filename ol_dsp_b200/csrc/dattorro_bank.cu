@@ -678,6 +678,8 @@ __global__ void __launch_bounds__(128) k_dattorro_split(const float *in, float *
 
 }  // namespace olb
 
+#include "dattorro_smem.cuh"
+
 using namespace olb;
 
 // ================================================================================================
@@ -693,8 +695,14 @@ struct olb_dattorro {
     std::vector<float> par_host;  // [8][I]
     bool par_dirty = true;
     float *d_slab = nullptr, *d_lp = nullptr, *d_par = nullptr;
+    const char *last_kernel = "none";
     HostStage host;
 };
+
+// banks up to this size take k_dattorro_smem for long blocks.  Measured (profiles/r02_run10_dattorro.txt, 48 000-frame blocks):
+// the resident kernel runs 1.5e10 instance-samples/s from 296 instances up (two plates per SM, bounded by the one-pole
+// recurrences), the HBM-ring kernel 1.8e9 at 296, 6.2e9 at 1 024, 2.4e10 from 4 736 up: they cross near 2 600 instances.
+constexpr uint32_t kSmemAutoMaxInstances = 2560;
 
 static void plate_geometry(PlateGeom *g, uint32_t *positions) {
     uint32_t n = 0;
@@ -818,6 +826,8 @@ OLB_API int olb_dattorro_set_params(olb_dattorro *h, uint32_t first, uint32_t co
     return OLB_OK;
 }
 
+OLB_API const char *olb_dattorro_last_kernel(olb_dattorro *h) { return h ? h->last_kernel : "none"; }
+
 OLB_API int olb_dattorro_set_param(olb_dattorro *h, uint32_t first, uint32_t count, int param, float value) {
     if (!h) { olb::set_error("NULL handle"); return OLB_E_ARG; }
     OLB_LOCK(h);
@@ -844,9 +854,21 @@ OLB_API int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *ou
     const char *ek = getenv("OLB_PLATE_KERNEL"), *el = getenv("OLB_PLATE_LANES");
     const int forced = el ? atoi(el) : 0;
     const int lanes = (forced == 32 || forced == 16 || forced == 8) ? forced : 32;
-    if (ek && !strcmp(ek, "simple")) {
+    // k_dattorro_smem (rings resident in shared memory, time-vectorised): long blocks only -- a launch gathers and scatters
+    // 107 KiB of rings per plate, which a block of >= 8 192 frames amortises to < 2.3 B per instance-sample each way.
+    // OLB_PLATE_KERNEL=smem forces it, any other value of the variable keeps it off.
+    const bool smem_kernel = ek ? !strcmp(ek, "smem") : (frames >= 8192 && h->I <= kSmemAutoMaxInstances);
+    if (smem_kernel) {
+        OLB_CUDA(cudaFuncSetAttribute(k_dattorro_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kSmBytes));
+        OLB_CUDA(cudaFuncSetAttribute(k_dattorro_smem, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        k_dattorro_smem<<<h->I, 96, kSmBytes, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I, h->d_slab, h->d_lp, h->d_par, h->geom,
+                                                   h->t);
+        h->last_kernel = "k_dattorro_smem";
+    } else if (ek && !strcmp(ek, "simple")) {
+        h->last_kernel = "k_dattorro";
         k_dattorro<<<(h->I + 63) / 64, 64, 0, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I, h->d_slab, h->d_lp, h->d_par, h->geom, h->t);
     } else if (ek && !strcmp(ek, "pf")) {
+        h->last_kernel = "k_dattorro_pf";
         constexpr int D = 8;
         const unsigned warps = (h->I + lanes - 1) / lanes, grid = (warps + kPfThreads / 32 - 1) / (kPfThreads / 32);
         const size_t smem = (size_t) D * kPfSlots * (kPfThreads / 32) * lanes * sizeof(float);
@@ -859,6 +881,7 @@ OLB_API int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *ou
         if (lanes == 32) OLB_PLATE_GO(32); else if (lanes == 16) OLB_PLATE_GO(16); else OLB_PLATE_GO(8);
 #undef OLB_PLATE_GO
     } else if (!ek || strcmp(ek, "rp")) {  // default: the network cut over the four warps of a CTA
+        h->last_kernel = "k_dattorro_split";
         constexpr int D = 8;
         OLB_ARG((uint64_t) frames * h->I * sizeof(float) < (1ull << 62), "olb_dattorro_process: block too large");
         constexpr size_t smem = ((size_t) D * kSplitSlots * 128 + (size_t) kXs * kXt * 32) * sizeof(float) + 3 * kXs * sizeof(uint64_t);
@@ -866,6 +889,7 @@ OLB_API int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *ou
         k_dattorro_split<D><<<(h->I + 31) / 32, 128, smem, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I, h->d_slab, h->d_lp,
                                                                h->d_par, h->geom, h->t);
     } else {  // OLB_PLATE_KERNEL=rp: one warp per 32 instances, block-wise ring pointers
+        h->last_kernel = "k_dattorro_rp";
         constexpr int D = 8;
         OLB_ARG((uint64_t) frames * h->I * sizeof(float) < (1ull << 62), "olb_dattorro_process: block too large");
         constexpr size_t smem = (size_t) D * kPfSlots * kPfThreads * sizeof(float);

@@ -50,3 +50,6 @@ class DattorroBank:
     def ProcessDevice(self, in_ptr, out_l_ptr, out_r_ptr, frames, stream=0):
         check(self.L.olb_dattorro_process(self.h, C.c_void_p(in_ptr), C.c_void_p(out_l_ptr), C.c_void_p(out_r_ptr), frames,
                                           C.c_void_p(stream)))
+
+    def LastKernel(self):
+        return self.L.olb_dattorro_last_kernel(self.h).decode()

@@ -113,10 +113,11 @@ def test_impulse_response_properties():
     b.close()
 
 
-@pytest.mark.parametrize("env", [{}, {"OLB_PLATE_KERNEL": "rp"}, {"OLB_PLATE_KERNEL": "simple"}] + [{"OLB_PLATE_KERNEL": "pf", "OLB_PLATE_LANES": l} for l in ("32", "16", "8")],
+@pytest.mark.parametrize("env", [{}, {"OLB_PLATE_KERNEL": "smem"}, {"OLB_PLATE_KERNEL": "split"}, {"OLB_PLATE_KERNEL": "rp"}, {"OLB_PLATE_KERNEL": "simple"}] + [{"OLB_PLATE_KERNEL": "pf", "OLB_PLATE_LANES": l} for l in ("32", "16", "8")],
                          ids=lambda e: "-".join(e.values()) or "default")
 def test_every_kernel_variant_is_bit_exact(orc, monkeypatch, env):
-    """The default kernel (the network cut over four warps), the one-warp ring-pointer kernel, the one-frame kernel and the
+    """The shared-memory-resident time-vectorised kernel (k_dattorro_smem, also what long blocks take by default), the
+    kernel with the network cut over four warps, the one-warp ring-pointer kernel, the one-frame kernel and the
     index-arithmetic pipelined kernel at 32 / 16 / 8 active lanes per warp compute the same bits; chunks straddle the 2 048-frame excursion steps and the
     16-bit counter wrap is crossed (a first chunk of 63 000 silent frames)."""
     for k, v in env.items():
@@ -130,3 +131,31 @@ def test_every_kernel_variant_is_bit_exact(orc, monkeypatch, env):
     for i in (0, 7, 8, 15, 16, 31, 32, 63, 64, 76):
         wl, wr = orc.dattorro(x[:, i], plist[i])
         assert np.array_equal(bits(l[:, i]), bits(wl)) and np.array_equal(bits(r[:, i]), bits(wr)), (env, i)
+
+
+def test_smem_kernel_takes_long_blocks_and_hands_state_to_the_hbm_kernels(orc, monkeypatch):
+    """Blocks of >= 8 192 frames run with the rings resident in shared memory (k_dattorro_smem), shorter ones with the rings
+    in HBM (k_dattorro_split); both speak the same state format, so a stream that alternates between them is bit-exact."""
+    monkeypatch.delenv("OLB_PLATE_KERNEL", raising=False)
+    I, T = 37, 30000
+    x = orc.noise(8, 3, I, 0, T, 0.25)
+    plist = [[(i % 5) / 4.0, NAN, NAN, NAN, 0.5 + 0.4 * (i % 16) / 16, NAN, 0.3 + 0.02 * i] for i in range(I)]
+    b = DattorroBank(I)
+    for i, p in enumerate(plist):
+        for which, v in zip(SETTERS, p):
+            if not np.isnan(v):
+                b.Set(which, float(v), first=i, count=1)
+    dx = torch.from_numpy(x).cuda()
+    dl, dr = torch.empty_like(dx), torch.empty_like(dx)
+    a, used = 0, []
+    for n in (9000, 1000, 8192, 11808):
+        b.ProcessDevice(dx[a:].data_ptr(), dl[a:].data_ptr(), dr[a:].data_ptr(), n)
+        used.append(b.LastKernel())
+        a += n
+    torch.cuda.synchronize()
+    assert used == ["k_dattorro_smem", "k_dattorro_split", "k_dattorro_smem", "k_dattorro_smem"]
+    l, r = dl.cpu().numpy(), dr.cpu().numpy()
+    for i in (0, 1, 17, 36):
+        wl, wr = orc.dattorro(x[:, i], plist[i])
+        assert np.array_equal(bits(l[:, i]), bits(wl)) and np.array_equal(bits(r[:, i]), bits(wr)), i
+    b.close()
