@@ -91,5 +91,55 @@ typedef FxBank<OLB_FX_RACK> FxRackBank;      // bank of ol::fx::FxRack<1>     (F
 // FxRack<1> with the Dattorro plate in the reverb slot (the wiring sketched in modules/fxlib/ReverbFx.cpp:11-37)
 typedef FxBank<OLB_FX_RACK_PLATE> FxRackPlateBank;
 
+// ---- stereo instances: banks of the reference's <2> templates (olb_fx2_*, include/olbank.h) ----------------------------
+// Frames are the reference's t_sample[2] per instance, side by side: [instances][2] per bank frame.  Second-channel
+// behaviour is the reference's own (FilterFx<2> leaves frame_out[1] alone, DelayFx<2> filters channel 0 only, FxRack<2>'s
+// channel 1 is 0 * master_volume): modules/fxlib/Fx.h:88-108, 194-208, 294-300, 426-434; caller main.cpp:83-85.
+template <int KIND>
+class FxBank2 {
+public:
+    explicit FxBank2(uint32_t instances, int device = 0) : instances_(instances), device_(device) {}
+    ~FxBank2() { olb_fx2_destroy(h_); }
+    FxBank2(const FxBank2 &) = delete;
+    FxBank2 &operator=(const FxBank2 &) = delete;
+    InitStatus Init(t_sample sample_rate) {
+        if (!h_) return note(olb_fx2_create(device_, KIND, instances_, sample_rate, &h_));
+        return note(olb_fx2_init(h_, sample_rate));
+    }
+    void Update() {}
+    void UpdateMidiControl(uint8_t control, uint8_t value) { note(olb_fx2_update_midi(h_, 0, instances_, control, value)); }
+    void UpdateMidiControl(uint8_t control, uint8_t value, uint32_t first, uint32_t count) {
+        note(olb_fx2_update_midi(h_, first, count, control, value));
+    }
+    void UpdateHardwareControl(uint8_t control, t_sample value) { note(olb_fx2_update_hw(h_, 0, instances_, control, &value, 0)); }
+    void UpdateHardwareControl(uint8_t control, const t_sample *values, uint32_t first, uint32_t count) {
+        note(olb_fx2_update_hw(h_, first, count, control, values, 1));
+    }
+    // one stereo frame of every instance: HOST arrays of 2 * instances floats (in place allowed)
+    void Process(const t_sample *frame_in, t_sample *frame_out) { note(olb_fx2_process_host(h_, frame_in, frame_out, 1)); }
+    void ProcessBlock(const t_sample *in_host, t_sample *out_host, uint64_t frames) { note(olb_fx2_process_host(h_, in_host, out_host, frames)); }
+    void ProcessDevice(const t_sample *in_dev, t_sample *out_dev, uint64_t frames, void *stream = nullptr) {
+        note(olb_fx2_process(h_, in_dev, out_dev, frames, stream));
+    }
+    uint32_t Instances() const { return instances_; }
+    int status() const { return status_; }
+    std::string error() const { return olb_last_error(); }
+    const char *LastKernel() { return olb_fx2_last_kernel(h_); }
+
+private:
+    InitStatus note(int rc) {
+        status_ = rc;
+        return rc == OLB_OK ? Ok : Error;
+    }
+    olb_fx2 *h_ = nullptr;
+    uint32_t instances_;
+    int device_;
+    int status_ = OLB_OK;
+};
+typedef FxBank2<OLB_FX_FILTER> FilterFx2Bank;  // bank of ol::fx::FilterFx<2>
+typedef FxBank2<OLB_FX_DELAY> DelayFx2Bank;    // bank of ol::fx::DelayFx<2>
+typedef FxBank2<OLB_FX_REVERB> ReverbFx2Bank;  // bank of ol::fx::ReverbFx<2>
+typedef FxBank2<OLB_FX_RACK> FxRack2Bank;      // bank of ol::fx::FxRack<2>
+
 }  // namespace gpu
 }  // namespace ol

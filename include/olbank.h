@@ -162,6 +162,28 @@ const char *olb_fx_last_kernel(olb_fx *h);
  * through device staging, returns when out_host is complete.  frames == 1 is the per-frame call. */
 int olb_fx_process_host(olb_fx *h, const float *in_host, float *out_host, uint64_t frames);
 
+/* (a2-a5, CHANNEL_COUNT = 2) stereo fxlib unit banks: FilterFx<2>, DelayFx<2>, ReverbFx<2>, FxRack<2> -- the shapes the
+ * reference's own caller runs (modules/ol_daisy/app/synth/main.cpp:83-85: reverb.Process / filter.Process on a stereo
+ * frame).  Audio is [frames][instances][2]: an instance's frame is the reference's t_sample[2].  The second channel gets
+ * exactly what the reference's templates give it:
+ *   OLB_FX_FILTER  Fx.h:88-108   filters frame_in[0] into frame_out[0]; frame_out[1] is not written (out_dev keeps it)
+ *   OLB_FX_DELAY   Fx.h:194-208  one delay line per channel; the wet filter runs on channel 0 only
+ *   OLB_FX_REVERB  Fx.h:294-300  both channels through the stub ReverbSc and the dry/wet
+ *   OLB_FX_RACK    Fx.h:426-434  channel 0 = FxRack<1> of channel 0; channel 1 = 0 * master_volume (buf_c[1] is never written)
+ * Setters are per INSTANCE (one object, two channels), same CC maps as the mono banks.  OLB_FX_RACK_PLATE has no stereo
+ * form.  in_dev == out_dev allowed; 8-byte aligned. */
+typedef struct olb_fx2 olb_fx2;
+int olb_fx2_create(int device, int kind, uint32_t instances, float sample_rate, olb_fx2 **out);
+int olb_fx2_destroy(olb_fx2 *h);
+int olb_fx2_init(olb_fx2 *h, float sample_rate);
+int olb_fx2_update_midi(olb_fx2 *h, uint32_t first, uint32_t count, uint8_t control, uint8_t value);
+int olb_fx2_update_hw(olb_fx2 *h, uint32_t first, uint32_t count, uint8_t control, const float *values_host, uint32_t stride);
+int olb_fx2_process(olb_fx2 *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream);
+/* "k_fx2_put" (merge; DelayFx<2>'s channel 1 time-parallel) or "k_fx2_delay1" (channel 1 walking time: delays shorter than a cut) */
+const char *olb_fx2_last_kernel(olb_fx2 *h);
+/* HOST buffers [frames][instances][2]; for OLB_FX_FILTER out_host's channel 1 is read and kept. */
+int olb_fx2_process_host(olb_fx2 *h, const float *in_host, float *out_host, uint64_t frames);
+
 /* (a6) SynthVoice bank and (a8) Polyvoice mixdown -------------------------------------------------------
  * One bank = `voices` ol::synth::SynthVoice objects with the reference's default parts (PolyBLEP-saw
  * OscillatorSoundSource, SvfFilter, two DaisyAdsr, DaisyPortamento): modules/synthlib/SynthVoice.h:16-316.

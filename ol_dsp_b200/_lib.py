@@ -74,6 +74,14 @@ def lib():
         "olb_fx_process": ([vp, vp, vp, u64, vp], i32),
         "olb_fx_last_kernel": ([vp], C.c_char_p),
         "olb_fx_process_host": ([vp, vp, vp, u64], i32),
+        "olb_fx2_create": ([i32, i32, u32, f32, C.POINTER(vp)], i32),
+        "olb_fx2_destroy": ([vp], i32),
+        "olb_fx2_init": ([vp, f32], i32),
+        "olb_fx2_update_midi": ([vp, u32, u32, C.c_uint8, C.c_uint8], i32),
+        "olb_fx2_update_hw": ([vp, u32, u32, C.c_uint8, _F, u32], i32),
+        "olb_fx2_process": ([vp, vp, vp, u64, vp], i32),
+        "olb_fx2_last_kernel": ([vp], C.c_char_p),
+        "olb_fx2_process_host": ([vp, vp, vp, u64], i32),
         "olb_voice_process_host": ([vp, vp, vp, u32, i32, f32, u64], i32),
         "olb_voice_process_events": ([vp, vp, u32, vp, vp, u32, i32, f32, u64, vp], i32),
         "olb_dattorro_process_host": ([vp, vp, vp, vp, u64], i32),

@@ -867,6 +867,9 @@ static int launch_skew(olb_biquad *h, const float *in, float *out, uint32_t fram
     OLB_SKEW_TRY(8, 24, 4, 4, 4)
     OLB_SKEW_TRY(8, 24, 6, 4, 4)
     OLB_SKEW_TRY(8, 96, 16, 4, 4)
+    OLB_SKEW_TRY(8, 192, 8, 4, 4)
+    OLB_SKEW_TRY(8, 192, 4, 4, 4)
+    OLB_SKEW_TRY(8, 192, 2, 4, 4)
     OLB_SKEW_TRY(8, 96, 8, 4, 4)
     OLB_SKEW_TRY(8, 96, 4, 4, 4)
     OLB_SKEW_TRY(8, 96, 2, 4, 4)

@@ -83,7 +83,7 @@ __device__ __forceinline__ void skew_tile(float *col, const u64 (&k)[5], u64 gai
 // Same operations on the same operands as skew_tile<OLB_MODE_FAST>: bit-identical results.
 //     A = fma(r1, V[m-1], V[m])   B = fma(r2, V[m-2], A)   C = fma(-a2, Y[m-2], B)   Y = fma(-a1, Y[m-1], C)
 template <int TB, int D, int kSkewLag, bool GAIN>
-__device__ __forceinline__ void skew_tile_fast(float *col, const u64 (&k)[5], float gain, u64 &x1, u64 &x2, u64 &y1, u64 &y2,
+__device__ __forceinline__ void skew_tile_fast_unrolled(float *col, const u64 (&k)[5], float gain, u64 &x1, u64 &x2, u64 &y1, u64 &y2,
                                                float (&p)[kSkewLag], u64, u64) {
     constexpr int CH = 32, P = 3;  // pipeline depth in stream positions
     static_assert(kSkewLag >= P + 1, "the low half's output must be complete before the high half consumes it");
@@ -91,22 +91,25 @@ __device__ __forceinline__ void skew_tile_fast(float *col, const u64 (&k)[5], fl
     u64 V[TB + 2], Y[TB + 2], A[TB], B[TB], C[TB];  // V[j + 2], Y[j + 2] = position j of this tile; [0], [1] = history
     V[1] = x1; V[0] = x2; Y[1] = y1; Y[0] = y2;
 #pragma unroll
-    for (int j = 0; j < D + P && j < TB; j++) {
-        x[j] = lds_ordered(col + j * CH);
-        if (GAIN) x[j] = __fmul_rn(gain, x[j]);
-    }
+    for (int j = 0; j < D + P && j < TB; j++) x[j] = lds_ordered(col + j * CH);
+    // warp 0 of a FAST bank scales its input by G = prod(b0): two consecutive inputs per packed product, (x[j], x[j+1]) *
+    // (G, G), taken one step before the first of them is used.  A scalar product at the load -- the obvious place -- is
+    // scheduled by ptxas right behind its load (one register rotates through all loads), which put the load's latency into
+    // every step of warp 0, the slowest stage of the pipeline (ncu: 28 cycles a step against 15.5 for the other warps).
+    const u64 gain2 = pack2(gain, gain);
+    float xg[TB + 1];
+    static_assert(TB % 2 == 0 && D >= 2, "inputs are scaled in pairs");
+    if (GAIN) unpack2(fmul2(pack2(x[0], x[1]), gain2), xg[0], xg[1]);
 #pragma unroll
     for (int t = -P; t < TB; t++) {
-        if (t + P + D < TB && t + P + D >= D + P) {
-            x[t + P + D] = lds_ordered(col + (t + P + D) * CH);
-            if (GAIN) x[t + P + D] = __fmul_rn(gain, x[t + P + D]);
-        }
+        if (t + P + D < TB && t + P + D >= D + P) x[t + P + D] = lds_ordered(col + (t + P + D) * CH);
         if (t + 3 < TB) {
             const int j = t + 3;  // the high half's input: the low half's output kSkewLag positions back
             float ylo, yhi;
             if (j - kSkewLag >= 0) unpack2(Y[j - kSkewLag + 2], ylo, yhi);
             else ylo = p[kSkewLag - 1 - j];
-            V[j + 2] = pack2(x[j], ylo);
+            if (GAIN && j % 2 == 1 && j + 1 < TB) unpack2(fmul2(pack2(x[j + 1], x[j + 2]), gain2), xg[j + 1], xg[j + 2]);
+            V[j + 2] = pack2(GAIN ? xg[j] : x[j], ylo);
             A[j] = ffma2(k[1], V[j + 1], V[j + 2]);
         }
         if (t + 2 >= 0 && t + 2 < TB) B[t + 2] = ffma2(k[2], V[t + 2], A[t + 2]);
@@ -124,6 +127,100 @@ __device__ __forceinline__ void skew_tile_fast(float *col, const u64 (&k)[5], fl
         float ylo, yhi;
         unpack2(Y[TB + 1 - q], ylo, yhi);
         p[q] = ylo;
+    }
+}
+
+// FAST tier, rolled and modulo-scheduled (the default; kSkewLag == 4).  ptxas orders a fully unrolled tile for register
+// pressure: it un-pipelines the hand-written schedule above back into one dependent A -> B -> C -> Y chain per step (four
+// 4-5 cycle stalls a step, 19-20 cycles by its own stall counts whatever TB and D are: tools/sass_model.py) and sinks the
+// prefetches down to their uses -- right for a scheduler with warps to switch to, wrong for a warp that has its scheduler
+// to itself.  What ptxas cannot do is move work across a loop's back edge.  So the tile is a ROLLED loop of 8 positions per
+// trip in which every instruction's operands were produced in an EARLIER position (the four fused operations of position t
+// belong to four different frames, as above), the registers are named modulo the trip (V[8], two of everything else: no
+// rotation copies), and the input of frame j is fetched 8 positions before its use into the slot frame j - 8 has just
+// vacated.  Static count: 84 instructions and ~104 issue cycles per 8 positions (32 FFMA2) for either kind of warp.
+// Same operations on the same operands as skew_tile<OLB_MODE_FAST>: bit-identical results.
+//
+// One position t (t == K mod 8):  Y_t, C_{t+1}, B_{t+2}, A_{t+3} (with V_{t+3} = (x_{t+3}, lo Y_{t-1})), store hi Y_t.
+template <bool DOA, bool DOB, bool DOC, bool DOY, int K>
+__device__ __forceinline__ void skew_pos(float *colt, const u64 (&k)[5], u64 (&V)[8], u64 (&Y)[2], u64 (&A)[2], u64 (&B)[2], u64 (&C)[2],
+                                         float xin, float ylo_in) {
+    constexpr int t = K + 8;  // keeps the modular arithmetic below positive
+    if (DOY) Y[t & 1] = ffma2(k[3], Y[(t - 1) & 1], C[t & 1]);
+    if (DOC) C[(t + 1) & 1] = ffma2(k[4], Y[(t - 1) & 1], B[(t + 1) & 1]);
+    if (DOB) B[(t + 2) & 1] = ffma2(k[2], V[t & 7], A[(t + 2) & 1]);
+    if (DOA) {
+        V[(t + 3) & 7] = pack2(xin, ylo_in);
+        A[(t + 3) & 1] = ffma2(k[1], V[(t + 2) & 7], V[(t + 3) & 7]);
+    }
+    if (DOY) {
+        float ylo, yhi;
+        unpack2(Y[t & 1], ylo, yhi);
+        colt[0] = yhi;
+    }
+}
+
+// Eight positions t .. t+7 (t == 0 mod 8).  FETCH = number of positions that still fetch an input 8 frames on (8 in the
+// steady state, 5 in the last trip but one: frames beyond the tile are not read), DRAIN: the tile's last eight positions
+// (the pipeline runs empty: no A after frame TB-1, and the low outputs of the last four frames go to p).
+template <bool GAIN, int FETCH, bool DRAIN, int kSkewLag>
+__device__ __forceinline__ void skew_block8(float *colt, const u64 (&k)[5], float gain, u64 (&V)[8], u64 (&Y)[2], u64 (&A)[2], u64 (&B)[2],
+                                            u64 (&C)[2], float (&xr)[8], float (&p)[kSkewLag]) {
+#define OLB_SKEW_POS(Q, DOA_, DOB_, DOC_)                                                                          \
+    {                                                                                                              \
+        float ylo, yhi;                                                                                            \
+        unpack2(Y[((Q) + 1) & 1], ylo, yhi);                                                                       \
+        if (DRAIN && (Q) >= 5) p[8 - (Q)] = ylo;                                                                   \
+        float xin = xr[((Q) + 3) & 7];                                                                             \
+        if (GAIN && (DOA_)) xin = __fmul_rn(gain, xin); /* warp 0 of a FAST bank applies G = prod(b0) to its input */ \
+        skew_pos<DOA_, DOB_, DOC_, true, Q>(colt + (Q) * 32, k, V, Y, A, B, C, xin, ylo);                           \
+        if ((Q) < FETCH) xr[((Q) + 3) & 7] = colt[((Q) + 11) * 32];                                                \
+    }
+    OLB_SKEW_POS(0, true, true, true)
+    OLB_SKEW_POS(1, true, true, true)
+    OLB_SKEW_POS(2, true, true, true)
+    OLB_SKEW_POS(3, true, true, true)
+    OLB_SKEW_POS(4, true, true, true)
+    OLB_SKEW_POS(5, !DRAIN, true, true)
+    OLB_SKEW_POS(6, !DRAIN, !DRAIN, true)
+    OLB_SKEW_POS(7, !DRAIN, !DRAIN, !DRAIN)
+#undef OLB_SKEW_POS
+}
+
+template <int TB, int D, int kSkewLag, bool GAIN>
+__device__ __forceinline__ void skew_tile_fast(float *col, const u64 (&k)[5], float gain, u64 &x1, u64 &x2, u64 &y1, u64 &y2,
+                                               float (&p)[kSkewLag], u64 one, u64 negzero) {
+    if constexpr (kSkewLag != 4 || TB % 8 != 0 || TB < 24) {
+        skew_tile_fast_unrolled<TB, D, kSkewLag, GAIN>(col, k, gain, x1, x2, y1, y2, p, one, negzero);
+    } else {
+        u64 V[8], Y[2], A[2], B[2], C[2];
+        V[7] = x1; V[6] = x2; Y[1] = y1; Y[0] = y2;  // V_{-1}, V_{-2}, Y_{-1}, Y_{-2}
+        A[0] = A[1] = B[0] = B[1] = C[0] = C[1] = 0ull;
+        float xr[8];  // xr[j & 7] = input of frame j
+#pragma unroll
+        for (int q = 0; q < 8; q++) xr[q] = col[q * 32];
+        // fill, positions -3, -2, -1:  A_0;  A_1 B_0;  A_2 B_1 C_0.  V_0 .. V_2 take the previous tile's low outputs from p.
+        skew_pos<true, false, false, false, 5>(col, k, V, Y, A, B, C, GAIN ? __fmul_rn(gain, xr[0]) : xr[0], p[3]);
+        skew_pos<true, true, false, false, 6>(col, k, V, Y, A, B, C, GAIN ? __fmul_rn(gain, xr[1]) : xr[1], p[2]);
+        skew_pos<true, true, true, false, 7>(col, k, V, Y, A, B, C, GAIN ? __fmul_rn(gain, xr[2]) : xr[2], p[1]);
+#pragma unroll
+        for (int q = 0; q < 3; q++) xr[q] = col[(8 + q) * 32];  // frames 0 .. 2 are consumed: their slots take frames 8 .. 10
+        float *colt = col;
+        constexpr int NS = TB / 8 - 2;  // steady-state blocks, two per trip (halves the copies that restore the loop's register names)
+#pragma unroll 1
+        for (int i = 0; i < NS / 2; i++, colt += 16 * 32) {
+            skew_block8<GAIN, 8, false, kSkewLag>(colt, k, gain, V, Y, A, B, C, xr, p);
+            skew_block8<GAIN, 8, false, kSkewLag>(colt + 8 * 32, k, gain, V, Y, A, B, C, xr, p);
+        }
+        if (NS % 2) {
+            skew_block8<GAIN, 8, false, kSkewLag>(colt, k, gain, V, Y, A, B, C, xr, p);
+            colt += 8 * 32;
+        }
+        skew_block8<GAIN, 5, false, kSkewLag>(colt, k, gain, V, Y, A, B, C, xr, p);
+        skew_block8<GAIN, 0, true, kSkewLag>(colt + 8 * 32, k, gain, V, Y, A, B, C, xr, p);
+        float yhi;
+        unpack2(Y[1], p[0], yhi);  // lo Y_{TB-1}
+        x1 = V[7]; x2 = V[6]; y1 = Y[1]; y2 = Y[0];
     }
 }
 

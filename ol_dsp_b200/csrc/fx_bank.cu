@@ -1220,3 +1220,267 @@ OLB_API int olb_fx_process_host(olb_fx *h, const float *in_host, float *out_host
     OLB_CUDA(cudaStreamSynchronize(h->host.st));
     return OLB_OK;
 }
+
+// ================================================================================================
+// Stereo instances (CHANNEL_COUNT = 2): banks of FilterFx<2> / DelayFx<2> / ReverbFx<2> / FxRack<2>, the shapes the
+// reference's production caller runs (modules/ol_daisy/app/synth/main.cpp:83-85).  What the reference's templates do with
+// the second channel is reproduced as it is, not as one might wish it were:
+//   FilterFx<2>::Process  filters frame_in[0] into frame_out[0]; frame_out[1] is NOT WRITTEN               (Fx.h:88-108)
+//   DelayFx<2>::Process   a delay line per channel, the wet filter on channel 0 only: channel 1's wet signal is the raw
+//                         DelayLine::Read                                                                   (Fx.h:194-208)
+//   ReverbFx<2>::Process  the stub ReverbSc and the dry/wet on both channels                               (Fx.h:294-300)
+//   FxRack<2>::Process    delay -> reverb -> filter1(buf_b, buf_c): buf_c[1] is never written and stays 0, so
+//                         frame_out[1] = 0 * master_volume; channel 0 is what FxRack<1> makes of channel 0  (Fx.h:426-434)
+// Channel 0 of every kind therefore IS the mono unit: it runs through the mono bank above (its TMA / warp-pipeline kernels)
+// on a de-interleaved copy that is cut in time so that it stays in L2, and a merge kernel writes the stereo frames.
+// Audio is [frames][instances][2] (an instance's frame is the reference's t_sample[2]).  DelayFx<2>'s channel-1 rings are
+// [48 000 positions][instances] (the write pointer is shared by the bank, so a write is one coalesced row).
+struct olb_fx2 {
+    std::recursive_mutex mu;
+    olb_fx *mono = nullptr;  // channel 0
+    int device = 0, kind = 0;
+    uint32_t I = 0;
+    float *d_ring1 = nullptr;  // DelayFx<2>: delay_lines_[1]
+    uint32_t wp1 = 0;
+    float *d_tmp = nullptr;
+    size_t tmp_elems = 0;
+    uint32_t min_delay = 0, max_delay = 0;
+    const char *last_kernel = "none";
+    HostStage host;
+};
+
+namespace olb {
+
+__global__ void __launch_bounds__(256) k_fx2_take0(const float2 *__restrict__ in, float *__restrict__ tmp, size_t n) {
+    const size_t i = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) tmp[i] = in[i].x;
+}
+
+// One thread per (frame, instance) of a time cut: merges channel 0 (already processed, `tmp`) with channel 1.
+// KIND == OLB_FX_DELAY here is the time-parallel form of channel 1's delay line, valid while no frame of the cut reads a
+// ring position another frame of the cut writes (cut <= delay and delay + 1 <= 48 000 - cut for every instance; the host
+// checks).  in may alias out (each thread reads its frame before writing it).
+template <int KIND>
+__global__ void __launch_bounds__(256) k_fx2_put(const float2 *in, const float *__restrict__ tmp, float2 *out, uint32_t frames, uint32_t I,
+                                                 const float *__restrict__ par, float *ring1, uint32_t wp0) {
+    const size_t idx = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (size_t) frames * I) return;
+    const uint32_t n = (uint32_t) (idx / I), inst = (uint32_t) (idx - (size_t) n * I);
+    auto P = [&](int p) { return par[(size_t) p * I + inst]; };
+    if (KIND == OLB_FX_FILTER) {
+        reinterpret_cast<float *>(out)[2 * idx] = tmp[idx];  // frame_out[1] stays what the caller had there
+    } else if (KIND == OLB_FX_RACK) {
+        out[idx] = make_float2(tmp[idx], __fmul_rn(0.0f, P(P_MASTER)));  // buf_c[1] * master_volume, buf_c[1] == 0 for ever
+    } else if (KIND == OLB_FX_REVERB) {
+        const float2 v = in[idx];
+        const float b = P(P_R_BALANCE);
+        out[idx] = make_float2(dry_wet(__fmul_rn(v.x, 0.8f), v.x, b), dry_wet(__fmul_rn(v.y, 0.8f), v.y, b));
+    } else {
+        const float x1 = in[idx].y;
+        const uint32_t delay = __float_as_uint(P(P_D_DELAY));
+        const uint32_t wp = (wp0 + (uint32_t) kRing - n % (uint32_t) kRing) % (uint32_t) kRing;
+        uint32_t ia = wp + delay;
+        ia = ia >= (uint32_t) kRing ? ia - kRing : ia;
+        uint32_t ib = ia + 1;
+        ib = ib >= (uint32_t) kRing ? ib - kRing : ib;
+        const float a = ring1[(size_t) ia * I + inst], b = ring1[(size_t) ib * I + inst];
+        const float rd = __fadd_rn(a, __fmul_rn(__fsub_rn(b, a), P(P_D_FRAC)));           // DelayLine::Read
+        ring1[(size_t) wp * I + inst] = __fadd_rn(x1, __fmul_rn(P(P_D_FEEDBACK), rd));   // Write(in + feedback * read)
+        out[idx] = make_float2(tmp[idx], dry_wet(rd, x1, P(P_D_BALANCE)));                // filter_.Process(buf, buf) left buf[1] alone
+    }
+}
+
+// DelayFx<2> channel 1, one instance per thread walking time: any delay (a cut may read what it wrote).
+__global__ void __launch_bounds__(64) k_fx2_delay1(const float2 *in, const float *__restrict__ tmp, float2 *out, uint32_t frames, uint32_t I,
+                                                   const float *__restrict__ par, float *ring1, uint32_t wp0) {
+    const uint32_t inst = blockIdx.x * blockDim.x + threadIdx.x;
+    if (inst >= I) return;
+    auto P = [&](int p) { return par[(size_t) p * I + inst]; };
+    const float feedback = P(P_D_FEEDBACK), balance = P(P_D_BALANCE), frac = P(P_D_FRAC);
+    const uint32_t delay = __float_as_uint(P(P_D_DELAY));
+    uint32_t wp = wp0;
+    for (uint32_t n = 0; n < frames; n++) {
+        const size_t idx = (size_t) n * I + inst;
+        const float x1 = in[idx].y;
+        uint32_t ia = wp + delay;
+        ia = ia >= (uint32_t) kRing ? ia - kRing : ia;
+        uint32_t ib = ia + 1;
+        ib = ib >= (uint32_t) kRing ? ib - kRing : ib;
+        const float a = ring1[(size_t) ia * I + inst], b = ring1[(size_t) ib * I + inst];
+        const float rd = __fadd_rn(a, __fmul_rn(__fsub_rn(b, a), frac));
+        ring1[(size_t) wp * I + inst] = __fadd_rn(x1, __fmul_rn(feedback, rd));
+        wp = wp == 0 ? kRing - 1 : wp - 1;
+        out[idx] = make_float2(tmp[idx], dry_wet(rd, x1, balance));
+    }
+}
+
+}  // namespace olb
+
+static bool fx2_kind_ok(int kind) { return kind >= OLB_FX_FILTER && kind <= OLB_FX_RACK; }
+
+static int fx2_init(olb_fx2 *h, float sr) {
+    int rc = olb_fx_init(h->mono, sr);
+    if (rc) return rc;
+    if (h->d_ring1) OLB_CUDA(h->mono->order.memset0(h->d_ring1, (size_t) h->I * kRing * sizeof(float)));
+    h->wp1 = 0;
+    return OLB_OK;
+}
+
+OLB_API int olb_fx2_create(int device, int kind, uint32_t instances, float sample_rate, olb_fx2 **out) {
+    OLB_ARG(out, "olb_fx2_create: out is NULL");
+    *out = nullptr;
+    OLB_ARG(fx2_kind_ok(kind), "olb_fx2_create: kind %d has no stereo form in the reference", kind);
+    olb_fx *mono = nullptr;
+    int rc = olb_fx_create(device, kind, instances, sample_rate, &mono);
+    if (rc) return rc;
+    DeviceGuard g(device);
+    olb_fx2 *h = new olb_fx2();
+    h->mono = mono;
+    h->device = device;
+    h->kind = kind;
+    h->I = instances;
+    if (kind == OLB_FX_DELAY) {
+        cudaError_t e = cudaMalloc(&h->d_ring1, (size_t) instances * kRing * sizeof(float));
+        if (e == cudaSuccess) e = cudaMemset(h->d_ring1, 0, (size_t) instances * kRing * sizeof(float));
+        if (e != cudaSuccess) {
+            olb_fx_destroy(mono);
+            delete h;
+            return fail_cuda(e, "allocating the channel-1 delay lines", __FILE__, __LINE__);
+        }
+    }
+    *out = h;
+    return OLB_OK;
+}
+
+OLB_API int olb_fx2_destroy(olb_fx2 *h) {
+    if (!h) return OLB_OK;
+    DeviceGuard g(h->device);
+    h->mono->order.quiesce();
+    cudaFree(h->d_ring1);
+    cudaFree(h->d_tmp);
+    h->host.release();
+    olb_fx_destroy(h->mono);
+    delete h;
+    return OLB_OK;
+}
+
+OLB_API int olb_fx2_init(olb_fx2 *h, float sample_rate) {
+    OLB_ARG(h, "olb_fx2_init: NULL handle");
+    OLB_LOCK(h);
+    DeviceGuard g(h->device);
+    return fx2_init(h, sample_rate);
+}
+
+OLB_API int olb_fx2_update_midi(olb_fx2 *h, uint32_t first, uint32_t count, uint8_t control, uint8_t value) {
+    OLB_ARG(h, "olb_fx2_update_midi: NULL handle");
+    OLB_LOCK(h);
+    return olb_fx_update_midi(h->mono, first, count, control, value);
+}
+
+OLB_API int olb_fx2_update_hw(olb_fx2 *h, uint32_t first, uint32_t count, uint8_t control, const float *values_host, uint32_t stride) {
+    OLB_ARG(h, "olb_fx2_update_hw: NULL handle");
+    OLB_LOCK(h);
+    return olb_fx_update_hw(h->mono, first, count, control, values_host, stride);
+}
+
+OLB_API const char *olb_fx2_last_kernel(olb_fx2 *h) { return h ? h->last_kernel : "none"; }
+
+OLB_API int olb_fx2_process(olb_fx2 *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream) {
+    OLB_ARG(h, "olb_fx2_process: NULL handle");
+    OLB_LOCK(h);
+    if (frames == 0) return OLB_OK;
+    OLB_ARG(in_dev && out_dev, "olb_fx2_process: NULL buffer");
+    OLB_ARG((((uintptr_t) in_dev | (uintptr_t) out_dev) & 7) == 0, "olb_fx2_process: stereo frames must be 8-byte aligned");
+    OLB_ARG(frames < (1ull << 32), "olb_fx2_process: at most 2^32-1 frames per call");
+    DeviceGuard g(h->device);
+    cudaStream_t st = (cudaStream_t) stream;
+    std::lock_guard<std::recursive_mutex> mono_lock(h->mono->mu);  // setters wait for the end of this block: one parameter set per call
+    const uint64_t I = h->I;
+    if (h->kind == OLB_FX_DELAY && h->mono->dirty) {
+        uint32_t lo = ~0u, hi = 0;
+        for (const auto &u : h->mono->units) {
+            lo = u.delay.delay < lo ? u.delay.delay : lo;
+            hi = u.delay.delay > hi ? u.delay.delay : hi;
+        }
+        h->min_delay = lo;
+        h->max_delay = hi;
+    }
+    // time cuts: the de-interleaved channel stays in L2 between its three kernels (<= 16 MiB), whole TMA tiles
+    uint64_t cut = (16ull << 20) / (I * sizeof(float));
+    cut = cut < 64 ? 64 : (cut / 64) * 64;
+    if (h->kind == OLB_FX_REVERB) cut = frames;  // stateless, no intermediate
+    bool par_delay = false;
+    if (h->kind == OLB_FX_DELAY) {
+        uint64_t c = cut;
+        if (h->min_delay >= 64 && c > h->min_delay) c = (h->min_delay / 64) * 64;
+        par_delay = c >= 64 && c <= h->min_delay && (uint64_t) h->max_delay + 1 + c <= (uint64_t) kRing;
+        if (par_delay) cut = c;
+    }
+    if (cut > frames) cut = frames;
+    if (h->kind != OLB_FX_REVERB && h->tmp_elems < cut * I) {
+        OLB_CUDA(h->mono->order.sync());
+        cudaFree(h->d_tmp);
+        h->d_tmp = nullptr;
+        h->tmp_elems = 0;
+        OLB_CUDA(cudaMalloc(&h->d_tmp, cut * I * sizeof(float)));
+        h->tmp_elems = cut * I;
+    }
+    const float2 *in2 = reinterpret_cast<const float2 *>(in_dev);
+    float2 *out2 = reinterpret_cast<float2 *>(out_dev);
+    OLB_CUDA(h->mono->order.enter(st));  // the intermediate and the channel-1 rings follow the mono bank's stream order
+    for (uint64_t t0 = 0; t0 < frames; t0 += cut) {
+        const uint32_t n = (uint32_t) (frames - t0 < cut ? frames - t0 : cut);
+        const size_t elems = (size_t) n * I;
+        const unsigned grid = (unsigned) ((elems + 255) / 256);
+        const float2 *in_c = in2 + t0 * I;
+        float2 *out_c = out2 + t0 * I;
+        if (h->kind == OLB_FX_REVERB) {
+            if (h->mono->dirty) {
+                int rc = fx_upload(h->mono, st);
+                if (rc) return rc;
+            }
+            k_fx2_put<OLB_FX_REVERB><<<grid, 256, 0, st>>>(in_c, nullptr, out_c, n, h->I, h->mono->d_par, nullptr, 0);
+            OLB_LAUNCHED();
+            h->last_kernel = "k_fx2_put";
+            continue;
+        }
+        k_fx2_take0<<<grid, 256, 0, st>>>(in_c, h->d_tmp, elems);
+        OLB_LAUNCHED();
+        int rc = olb_fx_process(h->mono, h->d_tmp, h->d_tmp, n, st);
+        if (rc) return rc;
+        if (h->kind == OLB_FX_FILTER) k_fx2_put<OLB_FX_FILTER><<<grid, 256, 0, st>>>(in_c, h->d_tmp, out_c, n, h->I, h->mono->d_par, nullptr, 0);
+        else if (h->kind == OLB_FX_RACK) k_fx2_put<OLB_FX_RACK><<<grid, 256, 0, st>>>(in_c, h->d_tmp, out_c, n, h->I, h->mono->d_par, nullptr, 0);
+        else if (par_delay) k_fx2_put<OLB_FX_DELAY><<<grid, 256, 0, st>>>(in_c, h->d_tmp, out_c, n, h->I, h->mono->d_par, h->d_ring1, h->wp1);
+        else k_fx2_delay1<<<(h->I + 63) / 64, 64, 0, st>>>(in_c, h->d_tmp, out_c, n, h->I, h->mono->d_par, h->d_ring1, h->wp1);
+        OLB_LAUNCHED();
+        if (h->kind == OLB_FX_DELAY) h->wp1 = (uint32_t) ((h->wp1 + (uint64_t) kRing - n % kRing) % kRing);
+        h->last_kernel = h->kind == OLB_FX_DELAY && !par_delay ? "k_fx2_delay1" : "k_fx2_put";
+    }
+    return OLB_OK;
+}
+
+// Host buffers [frames][instances][2], chunked through device staging; returns when out_host is complete.
+OLB_API int olb_fx2_process_host(olb_fx2 *h, const float *in_host, float *out_host, uint64_t frames) {
+    OLB_ARG(h, "olb_fx2_process_host: NULL handle");
+    OLB_LOCK(h);
+    if (frames == 0) return OLB_OK;
+    OLB_ARG(in_host && out_host, "olb_fx2_process_host: NULL buffer");
+    DeviceGuard g(h->device);
+    const uint64_t W = 2ull * h->I, chunk = host_chunk_frames(W, frames);
+    int rc = h->host.ensure(0, chunk * W);
+    if (rc) return rc;
+    // FilterFx<2> leaves frame_out[1] as the caller had it: the staging buffer starts from the caller's out frames
+    const bool keep_out = h->kind == OLB_FX_FILTER && in_host != out_host;
+    if (keep_out && (rc = h->host.ensure(1, chunk * W))) return rc;
+    for (uint64_t t0 = 0; t0 < frames; t0 += chunk) {
+        const uint64_t n = frames - t0 < chunk ? frames - t0 : chunk;
+        float *d_in = h->host.d[0], *d_out = keep_out ? h->host.d[1] : h->host.d[0];
+        OLB_CUDA(cudaMemcpyAsync(d_in, in_host + t0 * W, n * W * sizeof(float), cudaMemcpyHostToDevice, h->host.st));
+        if (keep_out) OLB_CUDA(cudaMemcpyAsync(d_out, out_host + t0 * W, n * W * sizeof(float), cudaMemcpyHostToDevice, h->host.st));
+        rc = olb_fx2_process(h, d_in, d_out, n, h->host.st);
+        if (rc) return rc;
+        OLB_CUDA(cudaMemcpyAsync(out_host + t0 * W, d_out, n * W * sizeof(float), cudaMemcpyDeviceToHost, h->host.st));
+    }
+    OLB_CUDA(cudaStreamSynchronize(h->host.st));
+    return OLB_OK;
+}

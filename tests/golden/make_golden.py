@@ -36,6 +36,15 @@ FX_EVENTS = [
     (12000, loader.EV_MIDI_CC, 7, 100),  # CC_VOLUME
 ]
 
+# stereo runs are 4 000 frames: a delay short enough for the wet path (and the feedback) to be heard several times over
+FX2_SHORT_EVENTS = [
+    (0, loader.EV_HW_CC, 35, 0.0113),   # CC_DELAY_TIME -> 542.4 samples (fractional read)
+    (0, loader.EV_MIDI_CC, 36, 100),    # CC_DELAY_FEEDBACK
+    (0, loader.EV_MIDI_CC, 39, 90),     # CC_DELAY_BALANCE
+    (1500, loader.EV_MIDI_CC, 37, 30),  # CC_DELAY_CUTOFF
+    (2500, loader.EV_HW_CC, 35, 0.004),  # a shorter delay mid-stream
+]
+
 VOICE_EVENTS = [
     (0, loader.EV_MIDI_CC, 41, 70), (0, loader.EV_MIDI_CC, 42, 30), (0, loader.EV_MIDI_CC, 73, 64),
     (0, loader.EV_MIDI_CC, 75, 60), (0, loader.EV_MIDI_CC, 108, 10), (0, loader.EV_MIDI_CC, 111, 40),
@@ -107,6 +116,14 @@ def main():
     x2 = orc.noise(22, 0, 2, 0, 4000, 0.5)
     fx["stereo_meta"] = np.array([22, 4000, 0.5], dtype=np.float64)
     fx["fxrack2"] = ref.fxrack(x2, 44100.0, FX_EVENTS[:2])
+    # the other <2> templates (channel 1: FilterFx<2> leaves frame_out[1] alone -> the 0.25 prefill survives; DelayFx<2>
+    # filters channel 0 only; ReverbFx<2> both): Fx.h:88-108, 194-208, 294-300
+    fx["filterfx2"] = ref.filterfx(x2, 48000.0, FX_EVENTS, prefill=0.25)
+    fx["delayfx2"] = ref.delayfx(x2, 48000.0, FX_EVENTS)
+    fx["reverbfx2"] = ref.reverbfx(x2, 48000.0, FX_EVENTS)
+    fx["fxrack2_full"] = ref.fxrack(x2, 48000.0, FX_EVENTS)
+    fx["delayfx2_short"] = ref.delayfx(x2, 48000.0, FX2_SHORT_EVENTS)
+    fx["fxrack2_short"] = ref.fxrack(x2, 48000.0, FX2_SHORT_EVENTS)
     rc, d = ref.test_fx_delay()
     fx["test_fx_delay_nans"] = np.array([rc])
     fx["test_fx_delay_sha"] = np.array([sha(d)])

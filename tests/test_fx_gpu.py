@@ -235,3 +235,109 @@ def test_plate_rack_bank_with_reverb_controls(orc):
         want = orc.filterfx(np.ascontiguousarray(mix.reshape(-1, 1)), 48000.0, [])[:, 0] * np.float32(0.6)
         assert np.array_equal(bits(y[:, i]), bits(want)), i
     b.close()
+
+
+# ---- stereo instances: the reference's <2> templates (olb_fx2_*) ----------------------------------------------------------
+def run_bank2(kind, x, events_per_instance, sr=48000.0, extra_cuts=(), prefill=0.0, host=False, in_place=False):
+    """x: [frames][instances][2].  Same control-script convention as run_bank."""
+    T, I, _ = x.shape
+    b = FxBank(kind, I, sample_rate=sr, channels=2)
+    cuts = sorted(c for c in ({0, T} | {e[0] for ev in events_per_instance for e in ev} | set(extra_cuts)) if c <= T)  # later events never fire
+    dx = torch.from_numpy(np.ascontiguousarray(x)).cuda()
+    dy = dx if in_place else torch.full_like(dx, prefill)
+    hy = np.full_like(x, prefill)
+    kernels = set()
+    for a, z in zip(cuts[:-1], cuts[1:]):
+        for i, ev in enumerate(events_per_instance):
+            for (f, k, cc, v) in ev:
+                if f != a:
+                    continue
+                if k == loader.EV_MIDI_CC:
+                    b.UpdateMidiControl(cc, int(v), first=i, count=1)
+                elif k == loader.EV_HW_CC:
+                    b.UpdateHardwareControl(cc, v, first=i, count=1)
+                elif k == loader.EV_INIT:
+                    b.Init(v)
+        if host:
+            b.ProcessHost(x[a:z], out=hy[a:z])
+        else:
+            b.ProcessDevice(dx[a:].data_ptr(), dy[a:].data_ptr(), z - a)
+        kernels.add(b.LastKernel())
+    torch.cuda.synchronize()
+    b.close()
+    return (hy if host else dy.cpu().numpy()), kernels
+
+
+@pytest.mark.parametrize("kind", [fx.FILTER, fx.DELAY, fx.REVERB, fx.RACK])
+@pytest.mark.parametrize("host", [False, True])
+def test_stereo_unit_matches_reference_golden(orc, kind, host):
+    """tests/golden/fx.npz stereo entries: the reference's own <2> class over 4 000 stereo frames with the FX_EVENTS script;
+    bystander instances with other settings against the oracle."""
+    g = np.load(os.path.join(G, "fx.npz"))
+    seed, frames, scale = g["stereo_meta"]
+    frames = int(frames)
+    x2 = orc.noise(int(seed), 0, 2, 0, frames, float(scale))
+    other = orc.noise(6, 2, 6, 0, frames, 0.4)
+    x = np.concatenate([x2, other], axis=1).reshape(frames, 4, 2)
+    evs = [mg.FX_EVENTS, mg.FX2_SHORT_EVENTS, [(0, loader.EV_HW_CC, 35, 0.0013), (100, loader.EV_MIDI_CC, 43, 60)], [(0, loader.EV_HW_CC, 35, 0.9999)]]
+    prefill = 0.25 if kind == fx.FILTER else 0.0
+    y, _ = run_bank2(kind, x, evs, extra_cuts=(1, 777), prefill=prefill, host=host)
+    name = NAMES[kind]
+    want = g["fxrack2_full" if kind == fx.RACK else f"{name}2"]
+    assert np.array_equal(bits(y[:, 0, :]), bits(want))
+    if kind in (fx.DELAY, fx.RACK):  # the reference's own short-delay golden (the wet path and the feedback are heard)
+        xs = np.ascontiguousarray(x[:, [0, 0, 2, 3], :])
+        ys, _ = run_bank2(kind, xs, [evs[1], evs[1], evs[2], evs[3]], prefill=prefill, host=host)
+        assert np.array_equal(bits(ys[:, 0, :]), bits(g[f"{name}2_short"]))
+    for i in (1, 2, 3):
+        kw = {"prefill": prefill} if kind == fx.FILTER else {}
+        w = getattr(orc, name)(np.ascontiguousarray(x[:, i, :]), 48000.0, evs[i], **kw)
+        assert np.array_equal(bits(y[:, i, :]), bits(w)), (name, i)
+
+
+def test_stereo_delay_both_channel1_kernels_and_in_place(orc):
+    """DelayFx<2>'s channel 1: a bank whose delays are all long takes the time-parallel kernel, one short delay sends the
+    bank to the kernel that walks time; both bit-equal to the oracle, also in place and across a mid-stream re-Init."""
+    I, T = 36, 9000
+    x = orc.noise(12, 0, 2 * I, 0, T, 0.5).reshape(T, I, 2)
+    for short in (False, True):
+        evs = []
+        for i in range(I):
+            t = 0.2 + 0.6 * i / I
+            if short and i == 7:
+                t = 0.0004
+            evs.append([(0, loader.EV_HW_CC, 35, t), (0, loader.EV_MIDI_CC, 36, 40 + i), (0, loader.EV_MIDI_CC, 39, 30 + 2 * i),
+                        (5000, loader.EV_INIT, 0, 44100.0)])
+        y, kernels = run_bank2(fx.DELAY, x.copy(), evs, in_place=True)
+        assert kernels == ({"k_fx2_delay1"} if short else {"k_fx2_put"}), kernels
+        for i in (0, 7, 20, 35):
+            w = orc.delayfx(np.ascontiguousarray(x[:, i, :]), 48000.0, evs[i])
+            assert np.array_equal(bits(y[:, i, :]), bits(w)), (short, i)
+
+
+def test_stereo_rack_wide_bank_channel0_is_the_mono_rack(orc):
+    """2 052 stereo racks (the mono bank inside takes its TMA warp pipeline): channel 0 equals the mono bank on channel 0,
+    channel 1 is zero, sampled instances equal the oracle's FxRack<2>."""
+    I, T = 2052, 3000
+    x = orc.noise(13, 0, 2 * I, 0, T, 0.5).reshape(T, I, 2)
+    times = (0.05 + 0.9 * np.arange(I) / I).astype(np.float32)
+    b2 = FxBank(fx.RACK, I, channels=2)
+    b1 = FxBank(fx.RACK, I)
+    for b in (b1, b2):
+        b.UpdateHardwareControl(35, times)
+    dx = torch.from_numpy(x).cuda()
+    dy = torch.empty_like(dx)
+    b2.ProcessDevice(dx.data_ptr(), dy.data_ptr(), T)
+    m = dx[:, :, 0].contiguous()
+    my = torch.empty_like(m)
+    b1.ProcessDevice(m.data_ptr(), my.data_ptr(), T)
+    torch.cuda.synchronize()
+    assert b1.LastKernel() == "k_fx_split"
+    y = dy.cpu().numpy()
+    assert np.array_equal(bits(y[:, :, 0]), bits(my.cpu().numpy()))
+    assert not y[:, :, 1].any()
+    for i in (0, 1000, 2051):
+        w = orc.fxrack(np.ascontiguousarray(x[:, i, :]), 48000.0, [(0, loader.EV_HW_CC, 35, float(times[i]))])
+        assert np.array_equal(bits(y[:, i, :]), bits(w)), i
+    b1.close()
+    b2.close()

@@ -56,6 +56,29 @@ def test_fxrack_stereo_matches_reference_golden(orc):
     assert not y[:, 1].any()  # FilterFx writes channel 0 only (Fx.h:88-108): channel 1 of the rack stays 0
 
 
+@pytest.mark.parametrize("name", ["filterfx", "delayfx", "reverbfx", "fxrack"])
+def test_fx_stereo_templates_match_reference_golden(orc, name):
+    """The <2> templates as the reference runs them (main.cpp:83-85): FilterFx<2> never writes channel 1 (the caller's
+    0.25 prefill survives), DelayFx<2> filters channel 0 only, ReverbFx<2> treats both alike, FxRack<2>'s channel 1 is 0."""
+    g = np.load(os.path.join(G, "fx.npz"))
+    seed, frames, scale = g["stereo_meta"]
+    x2 = orc.noise(int(seed), 0, 2, 0, int(frames), float(scale))
+    kw = {"prefill": 0.25} if name == "filterfx" else {}
+    y = getattr(orc, name)(x2, 48000.0, mg.FX_EVENTS, **kw)
+    want = g["fxrack2_full" if name == "fxrack" else f"{name}2"]
+    assert np.array_equal(bits(y), bits(want))
+    if name == "filterfx":
+        assert (y[:, 1] == 0.25).all()
+    if name == "fxrack":
+        assert not y[:, 1].any()
+    if name in ("delayfx", "fxrack"):  # a delay short enough to be heard within the 4 000 frames
+        ys = getattr(orc, name)(x2, 48000.0, mg.FX2_SHORT_EVENTS)
+        assert np.array_equal(bits(ys), bits(g[f"{name}2_short"]))
+    if name == "delayfx":  # channel 1 is not channel 0's signal path: the wet filter is missing
+        y1 = orc.delayfx(np.ascontiguousarray(x2[:, 1:2]), 48000.0, mg.FX2_SHORT_EVENTS)
+        assert not np.array_equal(bits(ys[:, 1]), bits(y1[:, 0]))
+
+
 def test_voice_and_polyvoice_match_reference_golden(orc):
     g = np.load(os.path.join(G, "synth.npz"))
     y = orc.voice(6000, 48000.0, None, mg.VOICE_EVENTS)
