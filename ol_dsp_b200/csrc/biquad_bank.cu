@@ -833,53 +833,66 @@ static int launch_sys(olb_biquad *h, const float *in, float *out, uint32_t frame
 }
 
 // ---- k_bq_skew shapes ---------------------------------------------------------------------------
-// Tile height x ring depth.  A CTA is 32 channels; what changes with the bank size is how many CTAs share an SM, and a
-// lone CTA must keep ~100 KiB of loads in flight to cover the HBM latency by itself (profiles/r01_run7_small_banks.txt).
-// OLB_BQ_SKEW_CFG="<TB>x<NST>" picks one of the compiled shapes (tuning aid).
+// Tile height x ring depth x lag [r = rolled FAST tile].  A CTA is 32 channels; what changes with the bank size is how many
+// CTAs share an SM.  A lone CTA must keep ~100 KiB of loads in flight to cover the HBM latency by itself
+// (profiles/r01_run7_small_banks.txt), and with one or two warps per scheduler the per-tile bookkeeping (barrier wait,
+// pipeline fill and drain: ~650 cycles) wants TALL tiles (profiles/r02_run13_skew_sweep.txt: 4 096 channels 31.8 / 24.9 /
+// 21.6 cycles per frame at 48 / 96 / 192 frames).  OLB_BQ_SKEW_CFG="<TB>x<NST>x<LAG>[r]" picks a compiled shape (tuning aid).
 struct SkewCfg {
     int tb, nst, lag;
+    bool roll;
 };
-static SkewCfg skew_cfg_auto(uint32_t C) {
+static SkewCfg skew_cfg_auto(uint32_t C, uint32_t frames) {
     SkewCfg env{};
-    if (const char *e = getenv("OLB_BQ_SKEW_CFG"))  // read per call: a tuning aid, cheap next to a launch
-        if (sscanf(e, "%dx%dx%d", &env.tb, &env.nst, &env.lag) == 3) return env;
+    if (const char *e = getenv("OLB_BQ_SKEW_CFG")) {  // read per call: a tuning aid, cheap next to a launch
+        char r = 0;
+        const int n = sscanf(e, "%dx%dx%d%c", &env.tb, &env.nst, &env.lag, &r);
+        if (n >= 3) {
+            env.roll = n == 4 && r == 'r';
+            return env;
+        }
+    }
     const uint32_t ctas = (C + 31) / 32, per_sm = (ctas + 147) / 148;
-    if (per_sm <= 1) return SkewCfg{48, 32, 4};  // 192 KiB: the SM to itself
-    if (per_sm <= 2) return SkewCfg{48, 16, 4};  // 96 KiB
-    if (per_sm <= 4) return SkewCfg{48, 8, 4};   // 48 KiB
-    if (per_sm <= 8) return SkewCfg{24, 8, 4};   // 24 KiB
-    return SkewCfg{24, 4, 4};                    // 12 KiB: up to 18 CTAs per SM
+    // the first and the last tile of a launch run the frame-by-frame path: short blocks keep the short tiles
+    if (per_sm <= 1) return frames >= 3072 ? SkewCfg{192, 8, 4, true} : SkewCfg{48, 32, 4, true};  // the SM to itself: 192 KiB
+    if (per_sm <= 2) return frames >= 1536 ? SkewCfg{96, 8, 4, true} : SkewCfg{48, 16, 4, true};   // 96 KiB
+    if (per_sm <= 4) return SkewCfg{48, 8, 4, false};  // 48 KiB
+    if (per_sm <= 8) return SkewCfg{24, 8, 4, false};  // 24 KiB
+    return SkewCfg{24, 4, 4, false};                   // 12 KiB: up to 18 CTAs per SM
 }
 
-#define OLB_SKEW_TRY(S_, TB_, NST_, D_, LAG_)                                  \
-    if (S == S_ && c.tb == TB_ && c.nst == NST_ && c.lag == LAG_)              \
-        return launch_skew_cfg<S_, MODE, TB_, NST_, D_, LAG_>(h->C, h->d_coef, h->d_hist, in, out, frames, st);
+#define OLB_SKEW_TRY(S_, TB_, NST_, D_, LAG_, ROLL_)                                       \
+    if (S == S_ && c.tb == TB_ && c.nst == NST_ && c.lag == LAG_ && c.roll == ROLL_)       \
+        return launch_skew_cfg<S_, MODE, TB_, NST_, D_, LAG_, ROLL_>(h->C, h->d_coef, h->d_hist, in, out, frames, st);
 
 template <int MODE>
 static int launch_skew(olb_biquad *h, const float *in, float *out, uint32_t frames, cudaStream_t st) {
     const uint32_t S = h->S;
-    SkewCfg c = skew_cfg_auto(h->C);
-    if (S != 8) c = SkewCfg{24, 8, 4};
-    OLB_SKEW_TRY(8, 48, 32, 4, 4)
-    OLB_SKEW_TRY(8, 48, 16, 4, 4)
-    OLB_SKEW_TRY(8, 48, 8, 4, 4)
-    OLB_SKEW_TRY(8, 24, 8, 4, 4)
-    OLB_SKEW_TRY(8, 24, 4, 4, 4)
-    OLB_SKEW_TRY(8, 24, 6, 4, 4)
-    OLB_SKEW_TRY(8, 96, 16, 4, 4)
-    OLB_SKEW_TRY(8, 192, 8, 4, 4)
-    OLB_SKEW_TRY(8, 192, 4, 4, 4)
-    OLB_SKEW_TRY(8, 192, 2, 4, 4)
-    OLB_SKEW_TRY(8, 96, 8, 4, 4)
-    OLB_SKEW_TRY(8, 96, 4, 4, 4)
-    OLB_SKEW_TRY(8, 96, 2, 4, 4)
-    OLB_SKEW_TRY(8, 48, 32, 4, 6)
-    OLB_SKEW_TRY(8, 48, 16, 4, 6)
-    OLB_SKEW_TRY(8, 96, 16, 4, 6)
-    OLB_SKEW_TRY(6, 24, 8, 4, 4)
-    OLB_SKEW_TRY(4, 24, 8, 4, 4)
-    OLB_SKEW_TRY(2, 24, 8, 4, 4)
-    set_error("olb_biquad_process: no compiled skewed shape for S=%u tb=%d nst=%d lag=%d", S, c.tb, c.nst, c.lag);
+    SkewCfg c = skew_cfg_auto(h->C, frames);
+    if (MODE != OLB_MODE_FAST) c.roll = false;  // the rolled tile is the FAST tier's
+    if (S != 8) c = SkewCfg{24, 8, 4, false};
+    OLB_SKEW_TRY(8, 192, 8, 4, 4, true)
+    OLB_SKEW_TRY(8, 96, 8, 4, 4, true)
+    OLB_SKEW_TRY(8, 96, 16, 4, 4, true)
+    OLB_SKEW_TRY(8, 48, 32, 4, 4, true)
+    OLB_SKEW_TRY(8, 48, 16, 4, 4, true)
+    OLB_SKEW_TRY(8, 48, 8, 4, 4, true)
+    OLB_SKEW_TRY(8, 24, 8, 4, 4, true)
+    OLB_SKEW_TRY(8, 192, 8, 4, 4, false)
+    OLB_SKEW_TRY(8, 96, 8, 4, 4, false)
+    OLB_SKEW_TRY(8, 96, 16, 4, 4, false)
+    OLB_SKEW_TRY(8, 48, 32, 4, 4, false)
+    OLB_SKEW_TRY(8, 48, 16, 4, 4, false)
+    OLB_SKEW_TRY(8, 48, 8, 4, 4, false)
+    OLB_SKEW_TRY(8, 24, 8, 4, 4, false)
+    OLB_SKEW_TRY(8, 24, 4, 4, 4, false)
+    OLB_SKEW_TRY(8, 24, 6, 4, 4, false)
+    OLB_SKEW_TRY(8, 48, 32, 4, 6, false)
+    OLB_SKEW_TRY(8, 48, 16, 4, 6, false)
+    OLB_SKEW_TRY(6, 24, 8, 4, 4, false)
+    OLB_SKEW_TRY(4, 24, 8, 4, 4, false)
+    OLB_SKEW_TRY(2, 24, 8, 4, 4, false)
+    set_error("olb_biquad_process: no compiled skewed shape for S=%u tb=%d nst=%d lag=%d roll=%d", S, c.tb, c.nst, c.lag, (int) c.roll);
     return OLB_E_ARG;
 }
 
@@ -944,11 +957,12 @@ static int process_dev(olb_biquad *h, const float *in, float *out, uint64_t fram
     // automatic choice (profiles/r01_run4_sys_sweep.txt, profiles/r02_run2_sweep.txt): what limits every one of these
     // kernels is the register-operand bandwidth of an SM sub-partition, so the question is only how evenly a bank can be
     // spread over the 592 of them.  >= 32 768 channels: the whole cascade per thread (k_bq_tma: fewest instructions per
-    // channel-frame); 4 737 .. 32 767 channels of an 8-section bank: skewed section pairs (k_bq_skew: units of 32
-    // channels x 2 sections, 2-7 per sub-partition where k_bq_tma would leave most of them idle); smaller banks: one
-    // section per warp (k_bq_sys); tiny or unaligned ones run one channel per thread without TMA
+    // channel-frame); 512 .. 32 767 channels of an 8-section bank: skewed section pairs (k_bq_skew: units of 32 channels
+    // x 2 sections, 1-7 per sub-partition where k_bq_tma would leave most of them idle; below 4 737 channels only for
+    // blocks of 3 072 frames or more, whose tall tiles pay); other small banks: one section per warp (k_bq_sys); tiny or
+    // unaligned ones run one channel per thread without TMA
     bool tma = tma_ok && (h->variant == 2 || (h->variant == 0 && h->C >= 32768u) || (h->variant == 0 && S != 8 && h->C >= 64u * 148u));
-    const bool skew = !tma && tma_ok && S == 8 && h->variant == 0 && h->C > 32u * 148u;
+    const bool skew = !tma && tma_ok && S == 8 && h->variant == 0 && (h->C > 32u * 148u || (h->C >= 32u * 16u && frames >= 3072));
     if (skew) {
         h->last_kernel = "k_bq_skew";
         const int m = h->eff_mode;

@@ -187,10 +187,10 @@ __device__ __forceinline__ void skew_block8(float *colt, const u64 (&k)[5], floa
 #undef OLB_SKEW_POS
 }
 
-template <int TB, int D, int kSkewLag, bool GAIN>
+template <int TB, int D, int kSkewLag, bool GAIN, bool ROLL>
 __device__ __forceinline__ void skew_tile_fast(float *col, const u64 (&k)[5], float gain, u64 &x1, u64 &x2, u64 &y1, u64 &y2,
                                                float (&p)[kSkewLag], u64 one, u64 negzero) {
-    if constexpr (kSkewLag != 4 || TB % 8 != 0 || TB < 24) {
+    if constexpr (!ROLL || kSkewLag != 4 || TB % 8 != 0 || TB < 24) {
         skew_tile_fast_unrolled<TB, D, kSkewLag, GAIN>(col, k, gain, x1, x2, y1, y2, p, one, negzero);
     } else {
         u64 V[8], Y[2], A[2], B[2], C[2];
@@ -224,7 +224,10 @@ __device__ __forceinline__ void skew_tile_fast(float *col, const u64 (&k)[5], fl
     }
 }
 
-template <int S, int MODE, int TB, int NST, int D, int kSkewLag>
+// ROLL: the FAST tier's rolled tile (banks of at most two CTAs per SM, where a warp has its scheduler to itself or shares
+// it with one other: 21.6 against 31.2 cycles per frame at 4 096 channels); with more warps per scheduler the unrolled
+// tile's 7.3 instructions per step beat the rolled tile's 9.6 (16 384 channels: 72.7 against 79.1).
+template <int S, int MODE, int TB, int NST, int D, int kSkewLag, bool ROLL>
 __global__ void __launch_bounds__((S / 2) * 32) k_bq_skew(const __grid_constant__ TensorMap tm_in, const __grid_constant__ TensorMap tm_out,
                                                           const __grid_constant__ TensorMap tm_out_head, uint32_t frames, uint32_t C, const float *__restrict__ coef, float *hist,
                                                           u64 one, u64 negzero) {
@@ -278,8 +281,8 @@ __global__ void __launch_bounds__((S / 2) * 32) k_bq_skew(const __grid_constant_
         const uint32_t m0 = i * TB;
         if (m0 >= hi0 && m0 + TB <= lo0 + frames) {  // both halves carry real frames throughout the tile
             if (MODE == OLB_MODE_FAST) {
-                if (with_gain) skew_tile_fast<TB, D, kSkewLag, true>(col, k, gain, x1, x2, y1, y2, p, one, negzero);
-                else skew_tile_fast<TB, D, kSkewLag, false>(col, k, gain, x1, x2, y1, y2, p, one, negzero);
+                if (with_gain) skew_tile_fast<TB, D, kSkewLag, true, ROLL>(col, k, gain, x1, x2, y1, y2, p, one, negzero);
+                else skew_tile_fast<TB, D, kSkewLag, false, ROLL>(col, k, gain, x1, x2, y1, y2, p, one, negzero);
             } else {
                 skew_tile<MODE, TB, D, kSkewLag, false>(col, k, 0ull, x1, x2, y1, y2, p, one, negzero);
             }
@@ -345,7 +348,7 @@ __global__ void __launch_bounds__((S / 2) * 32) k_bq_skew(const __grid_constant_
     }
 }
 
-template <int S, int MODE, int TB, int NST, int D, int kSkewLag>
+template <int S, int MODE, int TB, int NST, int D, int kSkewLag, bool ROLL>
 static int launch_skew_cfg(uint32_t C, const float *d_coef, float *d_hist, const float *in, float *out, uint32_t frames, cudaStream_t st) {
     constexpr int W = S / 2, CH = 32;
     constexpr size_t smem = (size_t) NST * TB * CH * sizeof(float) + (size_t) NST * W * sizeof(uint64_t);
@@ -356,7 +359,7 @@ static int launch_skew_cfg(uint32_t C, const float *d_coef, float *d_hist, const
     if (rc) return rc;
     rc = make_tmap_frames(&thead, out, frames, C, CH, TB - kSkewLag * W);
     if (rc) return rc;
-    auto kern = k_bq_skew<S, MODE, TB, NST, D, kSkewLag>;
+    auto kern = k_bq_skew<S, MODE, TB, NST, D, kSkewLag, ROLL && MODE == OLB_MODE_FAST>;
     OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     const float onef = 1.0f, nzf = -0.0f;

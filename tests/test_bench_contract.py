@@ -42,4 +42,4 @@ def test_olbank_arm_prints_one_json_line():
     assert d["e2e"]["h2d_bytes_per_step"] == d["e2e"]["d2h_bytes_per_step"] > 0 and 0 < d["e2e"]["value"] < d["value"]
     assert d["cpu_baseline"]["kind"] == "port" and d["cpu_baseline"]["value"] > 0
     assert {"sm_mhz", "sm_max_mhz", "reasons"} <= set(d["clocks"])
-    assert d["configs1"]["kernel"] == "k_bq_sys" and d["configs1"]["value"] > 0
+    assert d["configs1"]["kernel"] == "k_bq_skew" and d["configs1"]["value"] > 0

@@ -214,6 +214,39 @@ def test_skewed_pairs_bit_exact(orc, S, mode, C, chunks):
     assert np.array_equal(bits(st), bits(ost))
 
 
+@pytest.mark.parametrize("C,chunks,cfg", [(4096, [3500, 3100, 3072], None), (8192, [1600, 2000, 1536], None), (1024, [3333], None),
+                                          (4096, [700], "24x8x4r"), (4096, [1000], "48x8x4r"), (4096, [2000], "96x16x4r")])
+def test_skewed_pairs_rolled_tile(orc, C, chunks, cfg, monkeypatch):
+    """The FAST tier's rolled tile in every compiled height: 192 frames (<= 4 736 channels, blocks of 3 072 frames or more),
+    96 (<= 9 472 channels, 1 536 or more), 48 and 24; several calls so that the pipeline's fill from and drain into the
+    bank's history format is exercised at tile boundaries that move from call to call."""
+    if cfg:
+        monkeypatch.setenv("OLB_BQ_SKEW_CFG", cfg)
+    T = sum(chunks)
+    dev = torch.empty((T, C), dtype=torch.float32, device="cuda")
+    noise_device(dev.data_ptr(), 24, 0, C, 0, T)
+    out = torch.empty_like(dev)
+    k = c2_coefs(C)
+    b = BiquadBank(C, 8)
+    b.SetMode(MODE_FAST)
+    if cfg:
+        b.SetVariant(V_SKEW)
+    b.SetCoeffs(k)
+    t0 = 0
+    for n in chunks:
+        b.ProcessDevice(dev[t0:].data_ptr(), out[t0:].data_ptr(), n)
+        assert b.LastKernel() == "k_bq_skew"
+        t0 += n
+    torch.cuda.synchronize()
+    pick = np.r_[0:34, C // 2 - 3:C // 2 + 30, C - 33:C]
+    x = dev[:, torch.as_tensor(pick, device="cuda")].cpu().numpy()
+    ost = np.zeros((len(pick), 8, 4), dtype=np.float32)
+    want = orc.biquad(x, np.ascontiguousarray(k[pick]), mode=loader.MODE_FAST, state=ost)
+    assert np.array_equal(bits(out.cpu().numpy()[:, pick]), bits(want))
+    assert np.array_equal(bits(b.GetState()[pick]), bits(ost))
+    b.close()
+
+
 def test_skewed_pairs_in_place(orc):
     C, T = 4096, 3000
     dev = torch.empty((T, C), dtype=torch.float32, device="cuda")
