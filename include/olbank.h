@@ -183,6 +183,17 @@ int olb_fx2_process(olb_fx2 *h, const float *in_dev, float *out_dev, uint64_t fr
 const char *olb_fx2_last_kernel(olb_fx2 *h);
 /* HOST buffers [frames][instances][2]; for OLB_FX_FILTER out_host's channel 1 is read and kept. */
 int olb_fx2_process_host(olb_fx2 *h, const float *in_host, float *out_host, uint64_t frames);
+/* olb_fx2_process without any device allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same arguments, same results (bit-identical) as olb_fx2_process; the stereo path's only scratch -- the
+ * de-interleaved channel-0 cut -- lives in a static device array of OLB_FX2_STATIC_SCRATCH_BYTES that every GPU which loads
+ * the library holds until exit.  Limits: banks of at most OLB_FX2_STATIC_MAX_INSTANCES instances (one 64-frame cut must
+ * fit; OLB_E_ARG beyond); any number of frames.  The array is shared by ALL handles and calls on a device and keeps the
+ * last call's contents (every cut overwrites what it reads, nothing needs clearing): calls that overlap on the GPU --
+ * different streams with no ordering between them -- race; serialise them.  Calls no cudaMalloc / cudaFree. */
+#define OLB_FX2_STATIC_SCRATCH_BYTES (8u << 20)
+#define OLB_FX2_STATIC_MAX_INSTANCES 32768u
+int olb_fx2_process_static(olb_fx2 *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream);
 
 /* (a6) SynthVoice bank and (a8) Polyvoice mixdown -------------------------------------------------------
  * One bank = `voices` ol::synth::SynthVoice objects with the reference's default parts (PolyBLEP-saw

@@ -82,6 +82,7 @@ def lib():
         "olb_fx2_process": ([vp, vp, vp, u64, vp], i32),
         "olb_fx2_last_kernel": ([vp], C.c_char_p),
         "olb_fx2_process_host": ([vp, vp, vp, u64], i32),
+        "olb_fx2_process_static": ([vp, vp, vp, u64, vp], i32),
         "olb_voice_process_host": ([vp, vp, vp, u32, i32, f32, u64], i32),
         "olb_voice_process_events": ([vp, vp, u32, vp, vp, u32, i32, f32, u64, vp], i32),
         "olb_dattorro_process_host": ([vp, vp, vp, vp, u64], i32),

@@ -1484,3 +1484,99 @@ OLB_API int olb_fx2_process_host(olb_fx2 *h, const float *in_host, float *out_ho
     OLB_CUDA(cudaStreamSynchronize(h->host.st));
     return OLB_OK;
 }
+
+// ================================================================================================
+// olb_fx2_process_static: olb_fx2_process WITHOUT any device allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving
+// loops, harnesses that forbid it).  The only scratch of the stereo path -- the de-interleaved channel-0 cut that
+// k_fx2_take0 writes, the mono bank's kernel filters in place and k_fx2_put / k_fx2_delay1 merge back -- lives in a
+// file-scope device array of OLB_FX2_STATIC_SCRATCH_BYTES (8 MiB) that every GPU which loads the library holds until exit.
+// A cut is whole 64-frame tiles, so banks of up to OLB_FX2_STATIC_MAX_INSTANCES (32 768) instances fit; larger ones are
+// rejected.  Every cut overwrites the part of the array it reads (nothing has to start at zero); ALL handles and calls on
+// a device share the array, so two calls that overlap on the GPU (different streams, no ordering between them) race.
+static __device__ __align__(256) float g_fx2_static_scratch[OLB_FX2_STATIC_SCRATCH_BYTES / sizeof(float)];
+
+// In host code `g_fx2_static_scratch` is a host-side stand-in, not a device address: the address a kernel may use comes
+// from cudaGetSymbolAddress, asked once per device with that device current.
+static std::mutex g_fx2_static_mu;
+static float *g_fx2_static_ptr[64] = {nullptr};
+
+static int fx2_static_scratch(int device, float **out) {
+    OLB_ARG(device >= 0 && device < 64, "olb_fx2_process_static: device index %d out of range", device);
+    std::lock_guard<std::mutex> lk(g_fx2_static_mu);
+    if (!g_fx2_static_ptr[device]) {  // the caller's DeviceGuard has made `device` current
+        void *p = nullptr;
+        OLB_CUDA(cudaGetSymbolAddress(&p, g_fx2_static_scratch));
+        g_fx2_static_ptr[device] = static_cast<float *>(p);
+    }
+    *out = g_fx2_static_ptr[device];
+    return OLB_OK;
+}
+
+OLB_API int olb_fx2_process_static(olb_fx2 *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream) {
+    OLB_ARG(h, "olb_fx2_process_static: NULL handle");
+    OLB_LOCK(h);
+    if (frames == 0) return OLB_OK;
+    OLB_ARG(in_dev && out_dev, "olb_fx2_process_static: NULL buffer");
+    OLB_ARG((((uintptr_t) in_dev | (uintptr_t) out_dev) & 7) == 0, "olb_fx2_process_static: stereo frames must be 8-byte aligned");
+    OLB_ARG(frames < (1ull << 32), "olb_fx2_process_static: at most 2^32-1 frames per call");
+    OLB_ARG(h->I <= OLB_FX2_STATIC_MAX_INSTANCES,
+            "olb_fx2_process_static: %u instances exceed the static scratch (%u instances = one 64-frame cut in %u bytes); use olb_fx2_process",
+            h->I, (unsigned) OLB_FX2_STATIC_MAX_INSTANCES, (unsigned) OLB_FX2_STATIC_SCRATCH_BYTES);
+    DeviceGuard g(h->device);
+    float *tmp = nullptr;
+    int rc = fx2_static_scratch(h->device, &tmp);
+    if (rc) return rc;
+    cudaStream_t st = (cudaStream_t) stream;
+    std::lock_guard<std::recursive_mutex> mono_lock(h->mono->mu);
+    const uint64_t I = h->I;
+    if (h->kind == OLB_FX_DELAY && h->mono->dirty) {
+        uint32_t lo = ~0u, hi = 0;
+        for (const auto &u : h->mono->units) {
+            lo = u.delay.delay < lo ? u.delay.delay : lo;
+            hi = u.delay.delay > hi ? u.delay.delay : hi;
+        }
+        h->min_delay = lo;
+        h->max_delay = hi;
+    }
+    uint64_t cut = (uint64_t) OLB_FX2_STATIC_SCRATCH_BYTES / (I * sizeof(float));  // >= 64 by the instance limit
+    cut = (cut / 64) * 64;
+    if (h->kind == OLB_FX_REVERB) cut = frames;  // stateless, no intermediate
+    bool par_delay = false;
+    if (h->kind == OLB_FX_DELAY) {
+        uint64_t c = cut;
+        if (h->min_delay >= 64 && c > h->min_delay) c = (h->min_delay / 64) * 64;
+        par_delay = c >= 64 && c <= h->min_delay && (uint64_t) h->max_delay + 1 + c <= (uint64_t) kRing;
+        if (par_delay) cut = c;
+    }
+    if (cut > frames) cut = frames;
+    const float2 *in2 = reinterpret_cast<const float2 *>(in_dev);
+    float2 *out2 = reinterpret_cast<float2 *>(out_dev);
+    OLB_CUDA(h->mono->order.enter(st));
+    for (uint64_t t0 = 0; t0 < frames; t0 += cut) {
+        const uint32_t n = (uint32_t) (frames - t0 < cut ? frames - t0 : cut);
+        const size_t elems = (size_t) n * I;
+        const unsigned grid = (unsigned) ((elems + 255) / 256);
+        const float2 *in_c = in2 + t0 * I;
+        float2 *out_c = out2 + t0 * I;
+        if (h->kind == OLB_FX_REVERB) {
+            if (h->mono->dirty && (rc = fx_upload(h->mono, st))) return rc;
+            k_fx2_put<OLB_FX_REVERB><<<grid, 256, 0, st>>>(in_c, nullptr, out_c, n, h->I, h->mono->d_par, nullptr, 0);
+            OLB_LAUNCHED();
+            h->last_kernel = "k_fx2_put";
+            continue;
+        }
+        k_fx2_take0<<<grid, 256, 0, st>>>(in_c, tmp, elems);
+        OLB_LAUNCHED();
+        rc = olb_fx_process(h->mono, tmp, tmp, n, st);  // OLB_FX_FILTER / _DELAY / _RACK: launches only, no allocation
+        if (rc) return rc;
+        if (h->kind == OLB_FX_FILTER) k_fx2_put<OLB_FX_FILTER><<<grid, 256, 0, st>>>(in_c, tmp, out_c, n, h->I, h->mono->d_par, nullptr, 0);
+        else if (h->kind == OLB_FX_RACK) k_fx2_put<OLB_FX_RACK><<<grid, 256, 0, st>>>(in_c, tmp, out_c, n, h->I, h->mono->d_par, nullptr, 0);
+        else if (par_delay) k_fx2_put<OLB_FX_DELAY><<<grid, 256, 0, st>>>(in_c, tmp, out_c, n, h->I, h->mono->d_par, h->d_ring1, h->wp1);
+        else k_fx2_delay1<<<(h->I + 63) / 64, 64, 0, st>>>(in_c, tmp, out_c, n, h->I, h->mono->d_par, h->d_ring1, h->wp1);
+        OLB_LAUNCHED();
+        if (h->kind == OLB_FX_DELAY) h->wp1 = (uint32_t) ((h->wp1 + (uint64_t) kRing - n % kRing) % kRing);
+        h->last_kernel = h->kind == OLB_FX_DELAY && !par_delay ? "k_fx2_delay1" : "k_fx2_put";
+    }
+    return OLB_OK;
+}

@@ -51,6 +51,12 @@ class FxBank:
     def ProcessDevice(self, in_ptr, out_ptr, frames, stream=0):
         check(self._f("process")(self.h, C.c_void_p(in_ptr), C.c_void_p(out_ptr), frames, C.c_void_p(stream)))
 
+    def ProcessDeviceStatic(self, in_ptr, out_ptr, frames, stream=0):
+        """Stereo banks only: ProcessDevice without any device allocation (olb_fx2_process_static: scratch in a static
+        device array shared by every call on the device; at most 32 768 instances)."""
+        assert self.channels == 2
+        check(self.L.olb_fx2_process_static(self.h, C.c_void_p(in_ptr), C.c_void_p(out_ptr), frames, C.c_void_p(stream)))
+
     def ProcessHost(self, x, out=None):
         """x: host array [frames][instances] (or [frames][instances][2]); returns the processed block (out, if given, is
         filled in place: FilterFx<2> keeps its channel 1)."""
