@@ -310,9 +310,11 @@ int olb_dattorro_process_host(olb_dattorro *h, const float *in_host, float *out_
 
 /* (a9) Chorus bank ------------------------------------------------------------------------------------
  * The reference has no chorus class; its chorus is the Max/RNBO graph modules/rnbo/patcher/mono-chorus.rnbopat
- * (LFO-modulated delay~ -> lores~ -> dry/wet).  One bank = `instances` mono choruses with that patch's params
+ * (gen~ pitchshift -> LFO-modulated delay~ -> lores~ -> dry/wet).  One bank = `instances` mono choruses with that patch's params
  * (all 0..1, patch defaults): rate (scale -> 0.01..0.5 Hz), depth (@min 0.08; scale -> 1..12 ms), cutoff
- * (scale -> 300..15 000 Hz), q, mix, phase (cycle~ phase offset).  Lifecycle and call shape follow the fxlib units:
+ * (scale -> 300..15 000 Hz), q, mix, phase (cycle~ phase offset), pitch.  stereo-chorus.rnbopat = two of these per stereo
+ * instance, phase 1 on the left and 0 on the right, all other params shared: a bank of 2 x instances units over audio
+ * [frames][instances][2] (ol::gpu::StereoChorusBank / ol_dsp_b200.StereoChorusBank set it up).  Lifecycle and call shape follow the fxlib units:
  * create = construct + Init(sample_rate); init clears the delay line, filter and LFO phase and keeps the params;
  * process is the block form of "for each frame: Process(in, out)", in_dev == out_dev allowed.  Arithmetic is
  * specified by oracle/olb_oracle.cpp (orc_chorus_*): parity unpinned, bit-exact against that restatement. */
@@ -322,6 +324,9 @@ int olb_dattorro_process_host(olb_dattorro *h, const float *in_host, float *out_
 #define OLB_CHORUS_Q 3
 #define OLB_CHORUS_MIX 4
 #define OLB_CHORUS_PHASE 5
+/* param pitch @min 0 @max 3 (mono-chorus.rnbopat obj-8): the frequency in Hz of the phasor of the gen~ pitch shifter in front
+ * of delay~ (modules/rnbo/patcher/pitchshift.gendsp: two cosine-windowed taps of a 10 ms window).  Not a 0..1 param: 0..3. */
+#define OLB_CHORUS_PITCH 6
 
 typedef struct olb_chorus olb_chorus;
 

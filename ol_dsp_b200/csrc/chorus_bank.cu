@@ -7,7 +7,9 @@
 // cutoff' = scale(cutoff 0..1 -> 300..15 000 Hz), cycle~ phase offset `phase`; parameter defaults rate .2, depth .5,
 // cutoff .3, q .5, mix .5, phase 1.  Max's object internals are not in the tree: the arithmetic is specified by
 // oracle/olb_oracle.cpp (orc_chorus_*), PARITY UNPINNED, and this kernel is bit-exact against that restatement.
-// The gen~ pitch shifter in front of the delay (pitchshift.gendsp) is not built.
+// In front of delay~ sits the gen~ pitch shifter modules/rnbo/patcher/pitchshift.gendsp (param pitch 0..3: a phasor driving two
+// cosine-windowed taps of a 10 ms window): k_pitch_* below.  stereo-chorus.rnbopat is two of these with phase 1 (left) and 0
+// (right) sharing every other param: a bank of 2 x instances units, set up by the host mirrors (no kernel of its own).
 //
 // Layout
 //   audio   [frames][instances] fp32 in HBM
@@ -30,7 +32,7 @@ namespace olb {
 
 constexpr int kChL = 32;      // instances per warp / CTA
 constexpr int kChTab = 512;   // cycle~ table points (+1 guard)
-enum { CP_INC, CP_D, CP_OFFSET, CP_SCALE, CP_A1, CP_A2, CP_MIX, CP_COUNT };
+enum { CP_INC, CP_D, CP_OFFSET, CP_SCALE, CP_A1, CP_A2, CP_MIX, CP_PINC, CP_COUNT };  // CP_PINC: the pitch shifter's phasor increment
 
 __device__ __forceinline__ void bulk_load_1d(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar) {
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
@@ -93,8 +95,8 @@ __device__ __forceinline__ void chorus_phase_skip(ChorusLane &c, uint32_t n) {
 // r-k just wrote, as in the frame-by-frame order), (3) interpolate, filter, mix.  `wp` is the warp-uniform write index
 // of the batch's first frame, wp + n <= R.
 template <int N>
-__device__ __forceinline__ void chorus_audio_batch(float *col, ChorusLane &c, float *ring_col, uint32_t wp, uint32_t R, const uint32_t *kq,
-                                                   const float *frq, uint32_t n) {
+__device__ __forceinline__ void chorus_audio_batch(float *col, const float *pcol, ChorusLane &c, float *ring_col, uint32_t wp, uint32_t R,
+                                                   const uint32_t *kq, const float *frq, uint32_t n) {
     uint32_t k[N];
     float fr[N], x[N], a[N], b[N];
 #pragma unroll
@@ -103,7 +105,7 @@ __device__ __forceinline__ void chorus_audio_batch(float *col, ChorusLane &c, fl
             k[r] = kq[r * kChL];
             fr[r] = frq[r * kChL];
             x[r] = col[r * kChL];
-            ring_col[(size_t) (wp + r) * kChL] = x[r];  // delay~ writes, then reads dt samples back
+            ring_col[(size_t) (wp + r) * kChL] = pcol[r * kChL];  // delay~ writes (the pitch shifter's output), then reads dt samples back
         }
     }
 #pragma unroll
@@ -132,17 +134,111 @@ __device__ __forceinline__ void chorus_audio_batch(float *col, ChorusLane &c, fl
 
 __device__ __forceinline__ void mbar_arrive_all(uint64_t *bar) { mbar_arrive(bar); }
 
+// ------------------------------------------------------------------------------------------------
+// The gen~ pitch shifter in front of delay~ (modules/rnbo/patcher/pitchshift.gendsp; restated in oracle/olb_oracle.cpp:
+// orc_pitch_run).  It is feed-forward -- two cosine-windowed taps of the INPUT at phasor-driven delays of at most one
+// window (10 ms) -- so only the phasor is a recurrence, and that one is two operations a frame:
+//   k_pitch_phase  one thread per instance walks the phase over the block and leaves it at the start of every 64-frame chunk
+//   k_pitch_taps   (instances x chunks) grid: a thread re-walks its chunk's 64 phases (the same operations on the same
+//                  values: identical) and reads its taps straight from the input block in HBM / L2, or from the bank's
+//                  history of the previous block's last H frames for taps that reach behind the block
+//   k_pitch_hist   the last H input frames of this block -> the other history buffer (before the chorus kernel may
+//                  overwrite an in-place block)
+// The shifted signal goes to a scratch block that k_chorus streams beside the input (delay~ is fed the shifted signal, the
+// dry path the input).
+constexpr int kPitchChunk = 64;
+
+__device__ __forceinline__ float pitch_cos_poly(float t) {  // orc_cos_poly: cos t on [-pi/2, pi/2]
+    const float u = __fmul_rn(t, t);
+    float c = 2.0876756987868099e-9f;
+    c = __fadd_rn(__fmul_rn(c, u), -2.7557319223985888e-7f);
+    c = __fadd_rn(__fmul_rn(c, u), 2.4801587301587302e-5f);
+    c = __fadd_rn(__fmul_rn(c, u), -1.3888888888888889e-3f);
+    c = __fadd_rn(__fmul_rn(c, u), 4.1666666666666664e-2f);
+    c = __fadd_rn(__fmul_rn(c, u), -0.5f);
+    c = __fadd_rn(__fmul_rn(c, u), 1.0f);
+    return c;
+}
+
+__global__ void __launch_bounds__(128) k_pitch_phase(uint32_t frames, uint32_t I, const float *__restrict__ pinc, float *pstate,
+                                                     float *__restrict__ chunk_phase) {
+    const uint32_t inst = blockIdx.x * blockDim.x + threadIdx.x;
+    if (inst >= I) return;
+    const float inc = pinc[inst];
+    float ph = pstate[inst];
+    const uint32_t nchunks = (frames + kPitchChunk - 1) / kPitchChunk;
+    if (inc == 0.0f) {  // pitch 0, the patch's default: the phase rests (ph + 0 wraps only from exactly 1, which it never holds)
+        for (uint32_t c = 0; c < nchunks; c++) chunk_phase[(size_t) c * I + inst] = ph;
+        return;
+    }
+    for (uint32_t c = 0; c < nchunks; c++) {
+        chunk_phase[(size_t) c * I + inst] = ph;
+        const uint32_t rows = min((uint32_t) kPitchChunk, frames - c * kPitchChunk);
+#pragma unroll 8
+        for (uint32_t r = 0; r < rows; r++) {
+            ph = __fadd_rn(ph, inc);
+            ph = ph >= 1.0f ? __fsub_rn(ph, 1.0f) : ph;
+        }
+    }
+    pstate[inst] = ph;
+}
+
+// x[m] for block-relative frame m in [-H, frames): the block itself, or the history rows (row j = frame j - H)
+__device__ __forceinline__ float pitch_x(const float *__restrict__ in, const float *__restrict__ hist, uint32_t H, uint32_t I, uint32_t inst, int m) {
+    return m >= 0 ? in[(size_t) m * I + inst] : hist[(size_t) (H + m) * I + inst];
+}
+__device__ __forceinline__ float pitch_tap(const float *__restrict__ in, const float *__restrict__ hist, uint32_t H, uint32_t I, uint32_t inst, int n, float d) {
+    d = d < 1.0f ? 1.0f : d;
+    d = d > 44100.0f ? 44100.0f : d;
+    const uint32_t k = (uint32_t) __float2int_rz(d);
+    const float f = __fsub_rn(d, __uint2float_rn(k));
+    const float a = pitch_x(in, hist, H, I, inst, n - (int) k), b = pitch_x(in, hist, H, I, inst, n - (int) k - 1);
+    return __fadd_rn(a, __fmul_rn(__fsub_rn(b, a), f));
+}
+
+__global__ void __launch_bounds__(128) k_pitch_taps(const float *__restrict__ in, float *__restrict__ shifted, uint32_t frames, uint32_t I, uint32_t H,
+                                                    const float *__restrict__ pinc, float win, const float *__restrict__ chunk_phase,
+                                                    const float *__restrict__ hist) {
+    const uint32_t inst = blockIdx.x * 32 + (threadIdx.x & 31), c = blockIdx.y * 4 + (threadIdx.x >> 5);
+    if (inst >= I || c * kPitchChunk >= frames) return;
+    const float inc = pinc[inst];
+    float ph = chunk_phase[(size_t) c * I + inst];
+    const uint32_t rows = min((uint32_t) kPitchChunk, frames - c * kPitchChunk);
+#pragma unroll 4
+    for (uint32_t r = 0; r < rows; r++) {
+        const int n = (int) (c * kPitchChunk + r);
+        ph = __fadd_rn(ph, inc);
+        ph = ph >= 1.0f ? __fsub_rn(ph, 1.0f) : ph;
+        float p2 = __fadd_rn(ph, 0.5f);
+        p2 = p2 >= 1.0f ? __fsub_rn(p2, 1.0f) : p2;
+        const float w1 = pitch_cos_poly(__fmul_rn(__fsub_rn(ph, 0.5f), 3.14159274f)), w2 = pitch_cos_poly(__fmul_rn(__fsub_rn(p2, 0.5f), 3.14159274f));
+        const float t1 = pitch_tap(in, hist, H, I, inst, n, __fmul_rn(ph, win)), t2 = pitch_tap(in, hist, H, I, inst, n, __fmul_rn(p2, win));
+        shifted[(size_t) n * I + inst] = __fadd_rn(__fmul_rn(t1, w1), __fmul_rn(t2, w2));
+    }
+}
+
+__global__ void __launch_bounds__(256) k_pitch_hist(const float *__restrict__ in, uint32_t frames, uint32_t I, uint32_t H,
+                                                    const float *__restrict__ hist_old, float *__restrict__ hist_new) {
+    const size_t idx = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= (size_t) H * I) return;
+    const uint32_t j = (uint32_t) (idx / I), inst = (uint32_t) (idx - (size_t) j * I);
+    const long long m = (long long) frames - (long long) H + (long long) j;  // block-relative frame of new row j
+    hist_new[idx] = m >= 0 ? in[(size_t) m * I + inst] : hist_old[(size_t) (m + (long long) H) * I + inst];
+}
+
 template <int TB, int STAGES, bool TMA, bool ring_in_smem>
 __global__ void __launch_bounds__(96) k_chorus(const __grid_constant__ TensorMap tm_in, const __grid_constant__ TensorMap tm_out,
-                                               const float *in, float *out, uint32_t frames, uint32_t I, uint32_t R,
+                                               const __grid_constant__ TensorMap tm_p, const float *in, const float *pin, float *out,
+                                               uint32_t frames, uint32_t I, uint32_t R,
                                                const float *__restrict__ par, float *state, float *ring_all,
                                                const float *__restrict__ tab_g, uint32_t w0, float dmax) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     constexpr int L = kChL;
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5, i0 = blockIdx.x * L, inst = i0 + lane;
     const bool live = inst < I;
-    float *tiles = reinterpret_cast<float *>(smem_raw);          // [STAGES][TB][L]   audio tiles (TMA)
-    uint32_t *kq = reinterpret_cast<uint32_t *>(tiles + (size_t) STAGES * TB * L);  // [2][TB][L]  whole samples of delay
+    float *tiles = reinterpret_cast<float *>(smem_raw);          // [STAGES][TB][L]   audio tiles (TMA): input, output in place
+    float *ptiles = tiles + (size_t) STAGES * TB * L;            // [2][TB][L]        pitch-shifted input tiles (read only)
+    uint32_t *kq = reinterpret_cast<uint32_t *>(ptiles + (size_t) 2 * TB * L);      // [2][TB][L]  whole samples of delay
     float *frq = reinterpret_cast<float *>(kq + (size_t) 2 * TB * L);               // [2][TB][L]  fraction of delay
     // [R][L] ring: shared-memory resident for the launch when it fits (sample rates up to ~53 kHz), else used in place in HBM
     // (same code through generic pointers: the ring is lane-fastest, so its rows stay coalesced there)
@@ -151,6 +247,7 @@ __global__ void __launch_bounds__(96) k_chorus(const __grid_constant__ TensorMap
     float *ring = ring_in_smem ? ring_s : ring_all + (size_t) blockIdx.x * R * L;
     uint64_t *full = reinterpret_cast<uint64_t *>(tab + kChTab + 4);  // [STAGES] tile barriers, [STAGES] = ring barrier
     uint64_t *lfo_full = full + STAGES + 1, *lfo_empty = lfo_full + 2;  // [2] each, 32 arrivals per phase
+    uint64_t *pfull = lfo_empty + 2;                                    // [2] shifted-tile barriers
     const uint32_t ring_bytes = R * L * (uint32_t) sizeof(float);
     float *ring_g = ring_all + (size_t) blockIdx.x * R * L;
     if (threadIdx.x == 0) {
@@ -159,6 +256,7 @@ __global__ void __launch_bounds__(96) k_chorus(const __grid_constant__ TensorMap
         for (int s = 0; s < 2; s++) {
             mbar_init(&lfo_full[s], 32);
             mbar_init(&lfo_empty[s], 32);
+            mbar_init(&pfull[s], 1);
         }
         mbar_fence_init();
     }
@@ -209,6 +307,10 @@ __global__ void __launch_bounds__(96) k_chorus(const __grid_constant__ TensorMap
                 mbar_arrive_expect_tx(&full[j], kTileBytes);
                 tma_load_2d(tiles + (size_t) j * TB * L, &tm_in, (int) i0, (int) (j * TB), &full[j]);
             }
+            for (uint32_t j = 0; j < 2 && j < ntiles; j++) {
+                mbar_arrive_expect_tx(&pfull[j], kTileBytes);
+                tma_load_2d(ptiles + (size_t) j * TB * L, &tm_p, (int) i0, (int) (j * TB), &pfull[j]);
+            }
         }
     }
     float *ring_col = ring + lane;
@@ -220,12 +322,17 @@ __global__ void __launch_bounds__(96) k_chorus(const __grid_constant__ TensorMap
         const uint32_t st = TMA ? i % STAGES : 0, ph = (i / STAGES) & 1, ls = i & 1;
         const uint32_t rows = min((uint32_t) TB, frames - i * TB);
         float *col = tiles + (size_t) st * TB * L + lane;
+        float *pcol = ptiles + (size_t) (TMA ? ls : 0) * TB * L + lane;
         const uint32_t *kcol = kq + (size_t) ls * TB * L + lane;
         const float *fcol = frq + (size_t) ls * TB * L + lane;
         if (TMA) {
             mbar_wait(&full[st], ph);
+            mbar_wait(&pfull[ls], (i >> 1) & 1);
         } else if (live) {
-            for (uint32_t r = 0; r < rows; r++) col[r * L] = in[(size_t) (i * TB + r) * I + inst];
+            for (uint32_t r = 0; r < rows; r++) {
+                col[r * L] = in[(size_t) (i * TB + r) * I + inst];
+                pcol[r * L] = pin[(size_t) (i * TB + r) * I + inst];
+            }
         }
         mbar_wait(&lfo_full[ls], (i >> 1) & 1);
         // the write index wraps at most once per tile: one or two straight segments
@@ -234,8 +341,9 @@ __global__ void __launch_bounds__(96) k_chorus(const __grid_constant__ TensorMap
             if (live) {
                 uint32_t r = 0;
                 for (; r + kChB <= seg; r += kChB)
-                    chorus_audio_batch<kChB>(col + (r0 + r) * L, c, ring_col, wp + r, R, kcol + (r0 + r) * L, fcol + (r0 + r) * L, kChB);
-                if (r < seg) chorus_audio_batch<kChB>(col + (r0 + r) * L, c, ring_col, wp + r, R, kcol + (r0 + r) * L, fcol + (r0 + r) * L, seg - r);
+                    chorus_audio_batch<kChB>(col + (r0 + r) * L, pcol + (r0 + r) * L, c, ring_col, wp + r, R, kcol + (r0 + r) * L, fcol + (r0 + r) * L, kChB);
+                if (r < seg)
+                    chorus_audio_batch<kChB>(col + (r0 + r) * L, pcol + (r0 + r) * L, c, ring_col, wp + r, R, kcol + (r0 + r) * L, fcol + (r0 + r) * L, seg - r);
             }
             r0 += seg;
             wp = wp + seg == R ? 0 : wp + seg;
@@ -245,6 +353,10 @@ __global__ void __launch_bounds__(96) k_chorus(const __grid_constant__ TensorMap
             fence_async_smem();
             __syncwarp();
             if (lane == 0) {
+                if (i + 2 < ntiles) {  // this tile's shifted input has been read by every lane (__syncwarp above): refill its stage
+                    mbar_arrive_expect_tx(&pfull[ls], kTileBytes);
+                    tma_load_2d(ptiles + (size_t) ls * TB * L, &tm_p, (int) i0, (int) ((i + 2) * TB), &pfull[ls]);
+                }
                 tma_store_2d(&tm_out, (int) i0, (int) (i * TB), tiles + (size_t) st * TB * L);
                 tma_commit();
                 const uint32_t nxt = i + STAGES - 1;
@@ -287,18 +399,26 @@ struct olb_chorus {
     int device = 0;
     uint32_t I = 0, R = 0, w = 0, ctas = 0;
     float sample_rate = 48000.f;
-    std::vector<float> raw;  // [6][I]: rate depth cutoff q mix phase
+    std::vector<float> raw;  // [7][I]: rate depth cutoff q mix phase pitch
     std::vector<float> stage;
     bool dirty = true;
     float *d_par = nullptr, *d_state = nullptr, *d_ring = nullptr, *d_tab = nullptr;
+    // the gen~ pitch shifter: phasor phase [I], the last H input frames [2][H][I] (ping-pong), and per-call scratch that grows
+    // on demand: the shifted block [cut frames][I] and the phase at every 64-frame chunk start [chunks][I]
+    float *d_pstate = nullptr, *d_phist[2] = {nullptr, nullptr}, *d_shift = nullptr, *d_cphase = nullptr;
+    uint32_t H = 0, hist_cur = 0;
+    size_t shift_cap = 0, cphase_cap = 0;
+    float win = 480.f;
     const char *last_kernel = "none";
     HostStage host;
 };
 
-constexpr int kChTB = 64, kChStages = 4;
+// 3 stages of input / output tiles (a tile is 64 frames = ~5 700 cycles of the audio warp: two tiles ahead is plenty) + 2 of
+// shifted-input tiles + 2 x 2 hand-over buffers + the ring
+constexpr int kChTB = 64, kChStages = 3;
 static size_t chorus_smem(uint32_t R) {  // with the ring resident; R = 0: ring left in HBM
-    return (size_t) kChStages * kChTB * kChL * sizeof(float) + (size_t) 4 * kChTB * kChL * sizeof(float) + (size_t) R * kChL * sizeof(float) +
-           (kChTab + 4) * sizeof(float) + (kChStages + 1 + 4) * sizeof(uint64_t);
+    return (size_t) (kChStages + 2) * kChTB * kChL * sizeof(float) + (size_t) 4 * kChTB * kChL * sizeof(float) + (size_t) R * kChL * sizeof(float) +
+           (kChTab + 4) * sizeof(float) + (kChStages + 1 + 6) * sizeof(uint64_t);
 }
 static bool chorus_ring_fits(uint32_t R) { return chorus_smem(R) <= 227u * 1024u; }
 // the specification's ring length (orc_chorus_ring_len: it only enters the arithmetic through the clamp dt <= len - 2) ...
@@ -323,10 +443,16 @@ static void chorus_derive(const olb_chorus *h, uint32_t i, float *out /* stride 
     out[CP_A1 * I + i] = (float) a1;
     out[CP_A2 * I + i] = (float) a2;
     out[CP_MIX * I + i] = h->raw[4 * I + i];
+    out[CP_PINC * I + i] = (float) ((double) h->raw[6 * I + i] / sr);  // phasor(shift): shift Hz -> phase per frame
+}
+static uint32_t pitch_hist_len(float sr) {  // orc_pitch_hist_len
+    const double win = 10.0 * (double) sr / 1000.0;
+    return (uint32_t) (win < 44100.0 ? win : 44100.0) + 2u;
 }
 
 static void chorus_free(olb_chorus *h) {
     cudaFree(h->d_par); cudaFree(h->d_state); cudaFree(h->d_ring); cudaFree(h->d_tab);
+    cudaFree(h->d_pstate); cudaFree(h->d_phist[0]); cudaFree(h->d_phist[1]); cudaFree(h->d_shift); cudaFree(h->d_cphase);
     h->host.release();
     delete h;
 }
@@ -340,9 +466,23 @@ static int chorus_reset(olb_chorus *h, float sr) {
         OLB_CUDA(cudaMalloc(&h->d_ring, (size_t) h->ctas * R * kChL * sizeof(float)));
         h->R = R;
     }
+    const uint32_t H = pitch_hist_len(sr);
+    if (H != h->H || !h->d_phist[0]) {
+        OLB_CUDA(h->order.sync());
+        for (float *&q : h->d_phist) {
+            cudaFree(q);
+            q = nullptr;
+            OLB_CUDA(cudaMalloc(&q, (size_t) H * h->I * sizeof(float)));
+        }
+        h->H = H;
+    }
     h->sample_rate = sr;
+    h->win = (float) (10.0 * (double) sr / 1000.0);  // mstosamps(param window 10)
     OLB_CUDA(h->order.memset0(h->d_ring, (size_t) h->ctas * R * kChL * sizeof(float)));
     OLB_CUDA(h->order.memset0(h->d_state, (size_t) 3 * h->I * sizeof(float)));
+    OLB_CUDA(h->order.memset0(h->d_pstate, (size_t) h->I * sizeof(float)));
+    for (float *q : h->d_phist) OLB_CUDA(h->order.memset0(q, (size_t) H * h->I * sizeof(float)));
+    h->hist_cur = 0;
     h->w = 0;
     h->dirty = true;
     return OLB_OK;
@@ -359,14 +499,15 @@ OLB_API int olb_chorus_create(int device, uint32_t instances, float sample_rate,
     h->device = device;
     h->I = instances;
     h->ctas = (instances + kChL - 1) / kChL;
-    h->raw.resize((size_t) 6 * instances);
-    const float defaults[6] = {0.2f, 0.5f, 0.3f, 0.5f, 0.5f, 1.0f};  // param defaults of mono-chorus.rnbopat
-    for (int p = 0; p < 6; p++)
+    h->raw.resize((size_t) 7 * instances);
+    const float defaults[7] = {0.2f, 0.5f, 0.3f, 0.5f, 0.5f, 1.0f, 0.0f};  // param defaults of mono-chorus.rnbopat (pitch: none given = 0)
+    for (int p = 0; p < 7; p++)
         for (uint32_t i = 0; i < instances; i++) h->raw[(size_t) p * instances + i] = defaults[p];
     float tab[kChTab + 1];
     for (int i = 0; i <= kChTab; i++) tab[i] = (float) cos(2.0 * 3.14159265358979323846 * (double) i / (double) kChTab);
     cudaError_t e = cudaMalloc(&h->d_par, (size_t) CP_COUNT * instances * sizeof(float));
     if (e == cudaSuccess) e = cudaMalloc(&h->d_state, (size_t) 3 * instances * sizeof(float));
+    if (e == cudaSuccess) e = cudaMalloc(&h->d_pstate, (size_t) instances * sizeof(float));
     if (e == cudaSuccess) e = cudaMalloc(&h->d_tab, sizeof(tab));
     if (e == cudaSuccess) e = cudaMemcpy(h->d_tab, tab, sizeof(tab), cudaMemcpyHostToDevice);
     if (e != cudaSuccess) {
@@ -400,10 +541,11 @@ OLB_API int olb_chorus_set_params(olb_chorus *h, uint32_t first, uint32_t count,
     OLB_ARG(h && values_host, "olb_chorus_set_params: NULL argument");
     OLB_LOCK(h);
     OLB_ARG((uint64_t) first + count <= h->I, "olb_chorus_set_params: range [%u, %u) exceeds %u instances", first, first + count, h->I);
-    OLB_ARG(param >= OLB_CHORUS_RATE && param <= OLB_CHORUS_PHASE, "olb_chorus_set_params: unknown parameter %d", param);
+    OLB_ARG(param >= OLB_CHORUS_RATE && param <= OLB_CHORUS_PITCH, "olb_chorus_set_params: unknown parameter %d", param);
+    const float vmax = param == OLB_CHORUS_PITCH ? 3.f : 1.f;  // param pitch @min 0 @max 3 (Hz of the shifter's phasor)
     for (uint32_t i = 0; i < count; i++) {
         float v = values_host[(size_t) i * stride];
-        v = v < 0.f ? 0.f : (v > 1.f ? 1.f : v);  // RNBO params clip to @min / @max
+        v = v < 0.f ? 0.f : (v > vmax ? vmax : v);  // RNBO params clip to @min / @max
         h->raw[(size_t) param * h->I + first + i] = v;
     }
     h->dirty = true;
@@ -438,24 +580,59 @@ OLB_API int olb_chorus_process(olb_chorus *h, const float *in_dev, float *out_de
     const size_t smem = chorus_smem(in_smem ? h->R : 0);
     const char *ek = getenv("OLB_CHORUS_KERNEL");  // "direct" forces the plain-load variant (test aid)
     const bool tma = !(ek && !strcmp(ek, "direct")) && (h->I % 4 == 0) && (((uintptr_t) in_dev | (uintptr_t) out_dev) & 15) == 0;
-    TensorMap tin{}, tout{};
-    if (tma) {
-        int rc = make_tmap_frames(&tin, in_dev, frames, h->I, kChL, kChTB);
-        if (rc) return rc;
-        rc = make_tmap_frames(&tout, out_dev, frames, h->I, kChL, kChTB);
-        if (rc) return rc;
-        auto kern = in_smem ? k_chorus<kChTB, kChStages, true, true> : k_chorus<kChTB, kChStages, true, false>;
-        OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        kern<<<h->ctas, 96, smem, st>>>(tin, tout, in_dev, out_dev, (uint32_t) frames, h->I, h->R, h->d_par, h->d_state, h->d_ring, h->d_tab, h->w, (float) (chorus_spec_len(h->sample_rate) - 2));
-        h->last_kernel = "k_chorus_tma";
-    } else {
-        auto kern = in_smem ? k_chorus<kChTB, kChStages, false, true> : k_chorus<kChTB, kChStages, false, false>;
-        OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
-        kern<<<h->ctas, 96, smem, st>>>(tin, tout, in_dev, out_dev, (uint32_t) frames, h->I, h->R, h->d_par, h->d_state, h->d_ring, h->d_tab, h->w, (float) (chorus_spec_len(h->sample_rate) - 2));
-        h->last_kernel = "k_chorus_direct";
+    // Time cuts: the pitch shifter's output is an intermediate block of its own; cut so that it stays in L2 between the
+    // kernel that writes it and the chorus kernel that streams it (~48 MiB, whole 64-frame tiles).
+    const uint64_t I = h->I;
+    uint64_t cut = (48ull << 20) / (I * sizeof(float));
+    cut = cut < 64 ? 64 : (cut / 64) * 64;
+    if (const char *ec = getenv("OLB_CHORUS_CUT")) cut = (uint64_t) atoll(ec) < 1 ? 1 : (uint64_t) atoll(ec);  // test aid: any cut length
+    if (cut > frames) cut = frames;
+    const uint64_t chunks = (cut + kPitchChunk - 1) / kPitchChunk;
+    if (h->shift_cap < cut * I || h->cphase_cap < chunks * I) {
+        OLB_CUDA(h->order.sync());
+        cudaFree(h->d_shift);
+        cudaFree(h->d_cphase);
+        h->d_shift = h->d_cphase = nullptr;
+        h->shift_cap = h->cphase_cap = 0;
+        OLB_CUDA(cudaMalloc(&h->d_shift, cut * I * sizeof(float)));
+        OLB_CUDA(cudaMalloc(&h->d_cphase, chunks * I * sizeof(float)));
+        h->shift_cap = cut * I;
+        h->cphase_cap = chunks * I;
     }
-    OLB_LAUNCHED();
-    h->w = (uint32_t) ((h->w + frames) % h->R);
+    const float dmax = (float) (chorus_spec_len(h->sample_rate) - 2);
+    const float *pinc = h->d_par + (size_t) CP_PINC * I;
+    for (uint64_t t0 = 0; t0 < frames; t0 += cut) {
+        const uint32_t n = (uint32_t) (frames - t0 < cut ? frames - t0 : cut);
+        const float *in_c = in_dev + t0 * I;
+        float *out_c = out_dev + t0 * I;
+        // the pitch shifter: phases, taps, then the input history for the next cut (before an in-place block is overwritten)
+        const uint32_t nch = (n + kPitchChunk - 1) / kPitchChunk;
+        k_pitch_phase<<<(h->I + 127) / 128, 128, 0, st>>>(n, h->I, pinc, h->d_pstate, h->d_cphase);
+        OLB_LAUNCHED();
+        k_pitch_taps<<<dim3(h->ctas, (nch + 3) / 4), 128, 0, st>>>(in_c, h->d_shift, n, h->I, h->H, pinc, h->win, h->d_cphase, h->d_phist[h->hist_cur]);
+        OLB_LAUNCHED();
+        k_pitch_hist<<<(unsigned) (((size_t) h->H * I + 255) / 256), 256, 0, st>>>(in_c, n, h->I, h->H, h->d_phist[h->hist_cur], h->d_phist[h->hist_cur ^ 1]);
+        OLB_LAUNCHED();
+        h->hist_cur ^= 1;
+        TensorMap tin{}, tout{}, tp{};
+        if (tma) {
+            int rc = make_tmap_frames(&tin, in_c, n, h->I, kChL, kChTB);
+            if (!rc) rc = make_tmap_frames(&tout, out_c, n, h->I, kChL, kChTB);
+            if (!rc) rc = make_tmap_frames(&tp, h->d_shift, n, h->I, kChL, kChTB);
+            if (rc) return rc;
+            auto kern = in_smem ? k_chorus<kChTB, kChStages, true, true> : k_chorus<kChTB, kChStages, true, false>;
+            OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+            kern<<<h->ctas, 96, smem, st>>>(tin, tout, tp, in_c, h->d_shift, out_c, n, h->I, h->R, h->d_par, h->d_state, h->d_ring, h->d_tab, h->w, dmax);
+            h->last_kernel = "k_chorus_tma";
+        } else {
+            auto kern = in_smem ? k_chorus<kChTB, kChStages, false, true> : k_chorus<kChTB, kChStages, false, false>;
+            OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+            kern<<<h->ctas, 96, smem, st>>>(tin, tout, tp, in_c, h->d_shift, out_c, n, h->I, h->R, h->d_par, h->d_state, h->d_ring, h->d_tab, h->w, dmax);
+            h->last_kernel = "k_chorus_direct";
+        }
+        OLB_LAUNCHED();
+        h->w = (uint32_t) ((h->w + n) % h->R);
+    }
     return OLB_OK;
 }
 

@@ -133,25 +133,48 @@ class Oracle(_Fx):
         lib.orc_chorus_params.restype = None
         lib.orc_chorus_ring_len.argtypes = [C.c_float]
         lib.orc_chorus_ring_len.restype = C.c_uint32
-        lib.orc_chorus_run.argtypes = [_F, C.c_uint32, _F, _F, C.POINTER(C.c_uint32), _F, _F, C.c_uint64, C.c_uint64]
+        lib.orc_chorus_run.argtypes = [_F, C.c_uint32, _F, _F, C.POINTER(C.c_uint32), _F, _F, _F, C.c_uint64, C.c_uint64]
         lib.orc_chorus_run.restype = None
+        lib.orc_pitch_hist_len.argtypes = [C.c_float]
+        lib.orc_pitch_hist_len.restype = C.c_uint32
+        lib.orc_pitch_params.argtypes = [C.c_float, C.c_float, _F]
+        lib.orc_pitch_params.restype = None
+        lib.orc_pitch_run.argtypes = [_F, C.c_uint32, _F, _F, _F, _F, C.c_uint64, C.c_uint64]
+        lib.orc_pitch_run.restype = None
 
-    def chorus(self, x, sr=48000.0, rate=0.2, depth=0.5, cutoff=0.3, q=0.5, mix=0.5, phase=1.0, changes=()):
-        """(a9) one chorus instance over x[frames] (defaults = the RNBO patch's param defaults).  changes: list of
-        (frame, dict of params) applied before that frame (state and ring kept)."""
+    def pitchshift(self, x, sr=48000.0, pitch=0.0):
+        """The gen~ stage alone (pitchshift.gendsp) over x[frames], from rest."""
         x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1)
         y = np.empty_like(x)
-        cur = dict(rate=rate, depth=depth, cutoff=cutoff, q=q, mix=mix, phase=phase)
-        par = np.zeros(7, np.float32)
-        n = int(self.lib.orc_chorus_ring_len(sr))
+        hl = int(self.lib.orc_pitch_hist_len(sr))
+        par, ph, hist = np.zeros(2, np.float32), np.zeros(1, np.float32), np.zeros(hl, np.float32)
+        self.lib.orc_pitch_params(sr, pitch, _fp(par))
+        self.lib.orc_pitch_run(_fp(par), hl, _fp(ph), _fp(hist), _fp(x), _fp(y), len(x), 1)
+        return y
+
+    def chorus(self, x, sr=48000.0, rate=0.2, depth=0.5, cutoff=0.3, q=0.5, mix=0.5, phase=1.0, pitch=0.0, changes=(), pitch_stage=True):
+        """(a9) one chorus instance over x[frames] (defaults = the RNBO patch's param defaults): in~ -> gen~ pitchshift ->
+        delay~ -> lores~ -> dry / wet.  changes: list of (frame, dict of params) applied before that frame (state and rings
+        kept).  pitch_stage=False leaves the gen~ stage out (delay~ fed by the input itself)."""
+        x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1)
+        y = np.empty_like(x)
+        xp = np.empty_like(x)
+        cur = dict(rate=rate, depth=depth, cutoff=cutoff, q=q, mix=mix, phase=phase, pitch=pitch)
+        par, ppar = np.zeros(7, np.float32), np.zeros(2, np.float32)
+        n, hl = int(self.lib.orc_chorus_ring_len(sr)), int(self.lib.orc_pitch_hist_len(sr))
         ring, state, w = np.zeros(n, np.float32), np.zeros(3, np.float32), C.c_uint32(0)
+        pph, hist = np.zeros(1, np.float32), np.zeros(hl, np.float32)
         cuts = sorted({0, len(x)} | {f for f, _ in changes})
         for a, z in zip(cuts[:-1], cuts[1:]):
             for f, d in changes:
                 if f == a:
                     cur.update(d)
             self.lib.orc_chorus_params(sr, cur["rate"], cur["depth"], cur["cutoff"], cur["q"], cur["mix"], cur["phase"], _fp(par))
-            self.lib.orc_chorus_run(_fp(par), n, _fp(state), _fp(ring), C.byref(w), _fp(x[a:]), _fp(y[a:]), z - a, 1)
+            self.lib.orc_pitch_params(sr, cur["pitch"], _fp(ppar))
+            if pitch_stage:
+                self.lib.orc_pitch_run(_fp(ppar), hl, _fp(pph), _fp(hist), _fp(x[a:]), _fp(xp[a:]), z - a, 1)
+            self.lib.orc_chorus_run(_fp(par), n, _fp(state), _fp(ring), C.byref(w), _fp(x[a:]), _fp(xp[a:]) if pitch_stage else None,
+                                    _fp(y[a:]), z - a, 1)
         return y
 
     def sampler(self, data, ev, out, state=None):

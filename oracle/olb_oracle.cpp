@@ -16,7 +16,7 @@
 //                                  algorithm; only the reference's zero / non-zero / not-NaN tests pin it
 //   * biquad / one-pole cascade -> no reference implementation exists; this file IS the
 //                                  specification; parity unpinned by construction
-//   * chorus                    -> spec-level restatement of modules/rnbo/patcher/mono-chorus.rnbopat; unpinned
+//   * chorus                    -> spec-level restatement of modules/rnbo/patcher/mono-chorus.rnbopat + pitchshift.gendsp; unpinned
 #include <math.h>
 #include <stdint.h>
 #include <stdlib.h>
@@ -1095,9 +1095,69 @@ ORC_API uint32_t orc_chorus_ring_len(float sr) { return (uint32_t) ceil(2.0 * 12
 ORC_API void orc_chorus_table(float *tab513) {
     for (int i = 0; i <= 512; i++) tab513[i] = (float) cos(2.0 * 3.14159265358979323846 * (double) i / 512.0);
 }
+// The gen~ pitch shifter in front of delay~ (modules/rnbo/patcher/pitchshift.gendsp; mono-chorus.rnbopat obj-8 `param pitch
+// @min 0 @max 3` -> obj-3 `gen~ @file pitchshift` inlet 2 -> obj-24 delay~).  Box graph: obj-2 phasor(shift) -> (+0, +0.5) ->
+// `% 1` -> two tap times `* mstosamps(param window 10)` into obj-17 `delay 44100 2`, each tap weighted by
+// cos((phase - 0.5) * pi), summed.  gen~'s operator internals are not in the tree; restated here (PARITY UNPINNED) as
+//   phasor   phase = wrap(phase + shift / sr); the NEW phase is the output (genlib's Phasor increments, then returns)
+//   % 1      x - 1 when x >= 1 (both operands are in [0, 1.5))
+//   cos      even polynomial of degree 12 in float (|argument| <= pi/2, error ~1e-7), one rounding per operation
+//   delay    read before write, tap time clamped to [1, 44100], linear interpolation a + (b - a) * frac between x[n-k], x[n-k-1]
+// With pitch = 0 (the default) the phase rests at 0: tap 1 = x[n-1] * cos(-pi/2) ~ -4e-8 x[n-1], tap 2 = x delayed by half
+// the window (240 samples at 48 kHz) at weight 1.
+// pitch2 = {phase increment shift / sr, window in samples}; state: phase; hist: the last `hist_len` inputs, hist[hist_len-1] newest.
+ORC_API uint32_t orc_pitch_hist_len(float sr) {
+    const double win = 10.0 * (double) sr / 1000.0;
+    const double m = win < 44100.0 ? win : 44100.0;
+    return (uint32_t) m + 2u;
+}
+ORC_API void orc_pitch_params(float sr, float pitch, float *out2) {
+    const double p = pitch < 0.f ? 0.0 : (pitch > 3.f ? 3.0 : (double) pitch);  // param pitch @min 0 @max 3
+    out2[0] = (float) (p / (double) sr);
+    out2[1] = (float) (10.0 * (double) sr / 1000.0);                           // mstosamps(param window 10)
+}
+static inline float orc_cos_poly(float t) {  // cos t on [-pi/2, pi/2]
+    const float u = t * t;
+    float c = 2.0876756987868099e-9f;      // 1/12!
+    c = c * u + -2.7557319223985888e-7f;   // -1/10!
+    c = c * u + 2.4801587301587302e-5f;    // 1/8!
+    c = c * u + -1.3888888888888889e-3f;   // -1/6!
+    c = c * u + 4.1666666666666664e-2f;    // 1/4!
+    c = c * u + -0.5f;
+    c = c * u + 1.0f;
+    return c;
+}
+static inline float orc_pitch_tap(const float *hist, uint32_t hist_len, float d) {
+    d = d < 1.0f ? 1.0f : d;
+    d = d > 44100.0f ? 44100.0f : d;
+    const uint32_t k = (uint32_t) d;
+    const float f = d - (float) k;
+    const float a = hist[hist_len - k], b = hist[hist_len - k - 1];  // x[n-k], x[n-k-1]
+    return a + (b - a) * f;
+}
+ORC_API void orc_pitch_run(const float *pitch2, uint32_t hist_len, float *phase_state, float *hist, const float *x, float *y, uint64_t frames,
+                           uint64_t stride) {
+    const float inc = pitch2[0], win = pitch2[1];
+    float ph = *phase_state;
+    for (uint64_t n = 0; n < frames; n++) {
+        ph = ph + inc;
+        if (ph >= 1.0f) ph = ph - 1.0f;
+        float p2 = ph + 0.5f;
+        if (p2 >= 1.0f) p2 = p2 - 1.0f;
+        const float w1 = orc_cos_poly((ph - 0.5f) * 3.14159274f), w2 = orc_cos_poly((p2 - 0.5f) * 3.14159274f);
+        const float t1 = orc_pitch_tap(hist, hist_len, ph * win), t2 = orc_pitch_tap(hist, hist_len, p2 * win);
+        const float xin = x[n * stride];
+        y[n * stride] = t1 * w1 + t2 * w2;
+        memmove(hist, hist + 1, (hist_len - 1) * sizeof(float));
+        hist[hist_len - 1] = xin;
+    }
+    *phase_state = ph;
+}
+
 // One instance over `frames` frames.  state: [0] phase, [1] y1, [2] y2; ring: ring_len floats; *w: write index.
-ORC_API void orc_chorus_run(const float *par7, uint32_t ring_len, float *state3, float *ring, uint32_t *w, const float *x, float *y,
-                            uint64_t frames, uint64_t stride) {
+// xd: what delay~ is fed (the pitch shifter's output; NULL = x itself, the patch without its gen~ stage); x stays the dry signal.
+ORC_API void orc_chorus_run(const float *par7, uint32_t ring_len, float *state3, float *ring, uint32_t *w, const float *x, const float *xd,
+                            float *y, uint64_t frames, uint64_t stride) {
     static float tab[513];
     static bool have = false;
     if (!have) { orc_chorus_table(tab); have = true; }
@@ -1118,7 +1178,7 @@ ORC_API void orc_chorus_run(const float *par7, uint32_t ring_len, float *state3,
         float dt = lfo * d + d;
         dt = dt < 0.0f ? 0.0f : dt;
         dt = dt > dmax ? dmax : dt;
-        ring[wp] = xin;
+        ring[wp] = xd ? xd[n * stride] : xin;
         const uint32_t k = (uint32_t) dt;
         const float fr = dt - (float) k;
         const uint32_t ia = wp >= k ? wp - k : wp + ring_len - k;

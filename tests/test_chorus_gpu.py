@@ -1,14 +1,15 @@
 """GPU parity of the chorus bank through the C ABI.  The reference has no chorus code -- only
 the RNBO graph modules/rnbo/patcher/mono-chorus.rnbopat -- so the oracle (oracle/olb_oracle.cpp orc_chorus_*) is the
-specification of the arithmetic: PARITY UNPINNED.  The bank must match it bit for bit."""
+specification of the arithmetic: PARITY UNPINNED.  The bank must match it bit for bit.  The graph includes the gen~ pitch
+shifter in front of the delay (pitchshift.gendsp, param pitch) and, for stereo-chorus.rnbopat, two mono choruses per instance."""
 import numpy as np
 import pytest
 import torch
 
-from ol_dsp_b200 import ChorusBank
+from ol_dsp_b200 import ChorusBank, StereoChorusBank
 
 pytestmark = pytest.mark.gpu
-NAMES = ("rate", "depth", "cutoff", "q", "mix", "phase")
+NAMES = ("rate", "depth", "cutoff", "q", "mix", "phase", "pitch")
 
 
 def bits(a):
@@ -17,7 +18,7 @@ def bits(a):
 
 def params_for(i, I):
     return dict(rate=(i % 11) / 10.0, depth=((i * 7) % 13) / 12.0, cutoff=((i * 3) % 17) / 16.0, q=((i * 5) % 9) / 8.0,
-                mix=((i * 2) % 7) / 6.0, phase=(i % 5) / 4.0)
+                mix=((i * 2) % 7) / 6.0, phase=(i % 5) / 4.0, pitch=[0.0, 3.0, 0.37, 1.0, 2.5, 0.01][i % 6])
 
 
 def run_bank(x, plist, sr=48000.0, chunks=None, changes=None):
@@ -113,3 +114,59 @@ def test_full_width_properties():
     torch.cuda.synchronize()
     assert torch.isfinite(y).all() and torch.equal(y, y[:, :1].expand(-1, I)) and not torch.equal(y, x)
     b.close()
+
+
+@pytest.mark.parametrize("cut", [None, "100", "37", "640"])
+def test_pitch_shifter_taps_reach_back_across_cuts_and_calls(orc, monkeypatch, cut):
+    """The gen~ stage's taps reach up to one window (480 frames at 48 kHz) back: through the bank's input history when the
+    block or the library's internal time cut is shorter than that.  Cuts of 37 and 100 frames, calls of 1 .. 2 000 frames,
+    every instance with its own shifter frequency; in place."""
+    if cut:
+        monkeypatch.setenv("OLB_CHORUS_CUT", cut)
+    I, T = 40, 5200
+    x = orc.noise(25, 0, I, 0, T, 0.5)
+    pitches = np.linspace(0.0, 3.0, I).astype(np.float32)
+    b = ChorusBank(I)
+    b.Set("pitch", pitches)
+    b.Set("mix", 0.8)
+    dx = torch.from_numpy(x.copy()).cuda()
+    a = 0
+    for n in (1, 2, 61, 300, 500, 2000, 479, 481, T - 3824):
+        b.ProcessDevice(dx[a:].data_ptr(), dx[a:].data_ptr(), n)
+        a += n
+    assert a == T
+    torch.cuda.synchronize()
+    y = dx.cpu().numpy()
+    b.close()
+    for i in (0, 1, 13, 20, 39):
+        want = orc.chorus(x[:, i], mix=0.8, pitch=float(pitches[i]))
+        assert np.array_equal(bits(y[:, i]), bits(want)), (cut, i)
+    # the stage is really in the path: at pitch 0 the wet signal is the input 240 frames late (+ the LFO delay)
+    assert not np.array_equal(bits(y[:, 0]), bits(orc.chorus(x[:, 0], mix=0.8, pitch_stage=False)))
+
+
+@pytest.mark.parametrize("sr", [44100.0, 96000.0])
+def test_pitch_shifter_other_sample_rates(orc, sr):
+    I, T = 8, 4000
+    x = orc.noise(26, 0, I, 0, T, 0.5)
+    y, _ = run_bank(x, [dict(pitch=1.5, rate=0.7)] * I, sr=sr, chunks=[1500, 2500])
+    assert np.array_equal(bits(y[:, 6]), bits(orc.chorus(x[:, 6], sr=sr, pitch=1.5, rate=0.7)))
+
+
+def test_stereo_chorus_is_two_mono_choruses_phase_1_and_0(orc):
+    """stereo-chorus.rnbopat: in~ 1 -> mono-chorus (phase 1) -> out~ 1, in~ 2 -> mono-chorus (phase 0) -> out~ 2, the other
+    params shared per stereo instance."""
+    I, T = 18, 4000
+    x = orc.noise(27, 0, 2 * I, 0, T, 0.5).reshape(T, I, 2)
+    b = StereoChorusBank(I)
+    rates = np.linspace(0.0, 1.0, I).astype(np.float32)
+    b.Set("rate", rates)
+    b.Set("depth", 0.9)
+    b.Set("pitch", 0.5, first=3, count=2)
+    y = b.ProcessHost(x)
+    b.close()
+    for i in (0, 3, 4, 17):
+        pitch = 0.5 if i in (3, 4) else 0.0
+        left = orc.chorus(x[:, i, 0], rate=float(rates[i]), depth=0.9, phase=1.0, pitch=pitch)
+        right = orc.chorus(x[:, i, 1], rate=float(rates[i]), depth=0.9, phase=0.0, pitch=pitch)
+        assert np.array_equal(bits(y[:, i, 0]), bits(left)) and np.array_equal(bits(y[:, i, 1]), bits(right)), i

@@ -79,6 +79,25 @@ def test_fx_stereo_templates_match_reference_golden(orc, name):
         assert not np.array_equal(bits(ys[:, 1]), bits(y1[:, 0]))
 
 
+def test_pitch_shifter_restatement_properties(orc):
+    """pitchshift.gendsp restated (no reference code, no golden: PARITY UNPINNED): at pitch 0 the phasor rests, tap 2 is the
+    input half a window late at weight cos(0) = 1 and tap 1 carries weight cos(-pi/2) ~ -4e-8; the stage is linear in its
+    input; a running phasor sweeps the taps without ever reading outside the window; the polynomial cosine is within 2e-7."""
+    x = orc.noise(40, 0, 1, 0, 6000, 0.5)[:, 0]
+    for sr, half in ((48000.0, 240), (44100.0, 220)):
+        y = orc.pitchshift(x, sr, 0.0)
+        if sr == 48000.0:
+            assert np.array_equal(y[half:], x[:-half]) and not y[:half].any()
+        else:  # 220.5 samples: the mean of two neighbours
+            assert np.abs(y[half + 1:] - 0.5 * (x[1:-half] + x[:-half - 1])).max() < 1e-6
+    y1, y2 = orc.pitchshift(x, 48000.0, 2.0), orc.pitchshift(2.0 * x, 48000.0, 2.0)
+    assert np.array_equal(y2, 2.0 * y1)  # scaling by 2 is exact in floating point
+    assert np.isfinite(y1).all() and 0.5 < y1.std() / x.std() < 1.0  # two windowed taps of white noise: cos^2 + sin^2 power
+    ones = orc.pitchshift(np.ones(48000, np.float32), 48000.0, 3.0)
+    w = ones[600:]  # a constant input shows the two window weights: sin(pi p) + cos(pi p) over the phase, in [1, sqrt 2]
+    assert w.min() > 1.0 - 2e-6 and w.max() < np.sqrt(2.0) + 2e-6
+
+
 def test_voice_and_polyvoice_match_reference_golden(orc):
     g = np.load(os.path.join(G, "synth.npz"))
     y = orc.voice(6000, 48000.0, None, mg.VOICE_EVENTS)
