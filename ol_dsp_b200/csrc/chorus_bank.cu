@@ -187,33 +187,89 @@ __global__ void __launch_bounds__(128) k_pitch_phase(uint32_t frames, uint32_t I
 __device__ __forceinline__ float pitch_x(const float *__restrict__ in, const float *__restrict__ hist, uint32_t H, uint32_t I, uint32_t inst, int m) {
     return m >= 0 ? in[(size_t) m * I + inst] : hist[(size_t) (H + m) * I + inst];
 }
-__device__ __forceinline__ float pitch_tap(const float *__restrict__ in, const float *__restrict__ hist, uint32_t H, uint32_t I, uint32_t inst, int n, float d) {
-    d = d < 1.0f ? 1.0f : d;
-    d = d > 44100.0f ? 44100.0f : d;
-    const uint32_t k = (uint32_t) __float2int_rz(d);
-    const float f = __fsub_rn(d, __uint2float_rn(k));
-    const float a = pitch_x(in, hist, H, I, inst, n - (int) k), b = pitch_x(in, hist, H, I, inst, n - (int) k - 1);
-    return __fadd_rn(a, __fmul_rn(__fsub_rn(b, a), f));
-}
-
 __global__ void __launch_bounds__(128) k_pitch_taps(const float *__restrict__ in, float *__restrict__ shifted, uint32_t frames, uint32_t I, uint32_t H,
                                                     const float *__restrict__ pinc, float win, const float *__restrict__ chunk_phase,
                                                     const float *__restrict__ hist) {
     const uint32_t inst = blockIdx.x * 32 + (threadIdx.x & 31), c = blockIdx.y * 4 + (threadIdx.x >> 5);
-    if (inst >= I || c * kPitchChunk >= frames) return;
-    const float inc = pinc[inst];
-    float ph = chunk_phase[(size_t) c * I + inst];
+    if (c * kPitchChunk >= frames) return;  // warp-uniform
+    const bool live = inst < I;
+    const float inc = live ? pinc[inst] : 0.0f;
+    float ph = live ? chunk_phase[(size_t) c * I + inst] : 0.0f;
     const uint32_t rows = min((uint32_t) kPitchChunk, frames - c * kPitchChunk);
-#pragma unroll 4
-    for (uint32_t r = 0; r < rows; r++) {
-        const int n = (int) (c * kPitchChunk + r);
-        ph = __fadd_rn(ph, inc);
-        ph = ph >= 1.0f ? __fsub_rn(ph, 1.0f) : ph;
-        float p2 = __fadd_rn(ph, 0.5f);
-        p2 = p2 >= 1.0f ? __fsub_rn(p2, 1.0f) : p2;
-        const float w1 = pitch_cos_poly(__fmul_rn(__fsub_rn(ph, 0.5f), 3.14159274f)), w2 = pitch_cos_poly(__fmul_rn(__fsub_rn(p2, 0.5f), 3.14159274f));
-        const float t1 = pitch_tap(in, hist, H, I, inst, n, __fmul_rn(ph, win)), t2 = pitch_tap(in, hist, H, I, inst, n, __fmul_rn(p2, win));
-        shifted[(size_t) n * I + inst] = __fadd_rn(__fmul_rn(t1, w1), __fmul_rn(t2, w2));
+    // A warp whose 32 phasors all rest (pitch 0: the patch's default) has the same phase, tap times and window weights in
+    // every frame: they are computed once -- by the same operations, so the results are the general path's bit for bit --
+    // and a frame is four loads, two interpolations and the weighted sum.
+    if (__all_sync(0xffffffffu, inc == 0.0f)) {
+        if (!live) return;
+        float q = __fadd_rn(ph, 0.5f);
+        q = q >= 1.0f ? __fsub_rn(q, 1.0f) : q;
+        float d1 = __fmul_rn(ph, win), d2 = __fmul_rn(q, win);
+        d1 = d1 < 1.0f ? 1.0f : d1; d1 = d1 > 44100.0f ? 44100.0f : d1;
+        d2 = d2 < 1.0f ? 1.0f : d2; d2 = d2 > 44100.0f ? 44100.0f : d2;
+        const uint32_t k1 = (uint32_t) __float2int_rz(d1), k2 = (uint32_t) __float2int_rz(d2);
+        const float f1 = __fsub_rn(d1, __uint2float_rn(k1)), f2 = __fsub_rn(d2, __uint2float_rn(k2));
+        const float w1 = pitch_cos_poly(__fmul_rn(__fsub_rn(ph, 0.5f), 3.14159274f)), w2 = pitch_cos_poly(__fmul_rn(__fsub_rn(q, 0.5f), 3.14159274f));
+        const int n0 = (int) (c * kPitchChunk);
+        constexpr int B = 8;
+        for (uint32_t r0 = 0; r0 < rows; r0 += B) {
+            float a1[B], b1[B], a2[B], b2[B];
+#pragma unroll
+            for (int j = 0; j < B; j++) {
+                if (r0 + j < rows) {
+                    const int n = n0 + (int) r0 + j;
+                    a1[j] = pitch_x(in, hist, H, I, inst, n - (int) k1); b1[j] = pitch_x(in, hist, H, I, inst, n - (int) k1 - 1);
+                    a2[j] = pitch_x(in, hist, H, I, inst, n - (int) k2); b2[j] = pitch_x(in, hist, H, I, inst, n - (int) k2 - 1);
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < B; j++) {
+                if (r0 + j < rows) {
+                    const float t1 = __fadd_rn(a1[j], __fmul_rn(__fsub_rn(b1[j], a1[j]), f1)), t2 = __fadd_rn(a2[j], __fmul_rn(__fsub_rn(b2[j], a2[j]), f2));
+                    shifted[(size_t) (n0 + r0 + j) * I + inst] = __fadd_rn(__fmul_rn(t1, w1), __fmul_rn(t2, w2));
+                }
+            }
+        }
+        return;
+    }
+    if (!live) return;
+    // batches of 8 frames in three sweeps so that the 32 tap loads of a batch are in flight together: (1) the phase recurrence
+    // and the tap times, (2) the loads, (3) interpolation, windows, sum
+    constexpr int B = 8;
+    for (uint32_t r0 = 0; r0 < rows; r0 += B) {
+        float p1[B], p2[B], f1[B], f2[B], a1[B], b1[B], a2[B], b2[B];
+        int m1[B], m2[B];
+#pragma unroll
+        for (int j = 0; j < B; j++) {
+            ph = __fadd_rn(ph, inc);
+            ph = ph >= 1.0f ? __fsub_rn(ph, 1.0f) : ph;
+            p1[j] = ph;
+            float q = __fadd_rn(ph, 0.5f);
+            p2[j] = q >= 1.0f ? __fsub_rn(q, 1.0f) : q;
+            float d1 = __fmul_rn(p1[j], win), d2 = __fmul_rn(p2[j], win);
+            d1 = d1 < 1.0f ? 1.0f : d1; d1 = d1 > 44100.0f ? 44100.0f : d1;
+            d2 = d2 < 1.0f ? 1.0f : d2; d2 = d2 > 44100.0f ? 44100.0f : d2;
+            const uint32_t k1 = (uint32_t) __float2int_rz(d1), k2 = (uint32_t) __float2int_rz(d2);
+            f1[j] = __fsub_rn(d1, __uint2float_rn(k1));
+            f2[j] = __fsub_rn(d2, __uint2float_rn(k2));
+            const int n = (int) (c * kPitchChunk + r0) + j;
+            m1[j] = n - (int) k1;
+            m2[j] = n - (int) k2;
+        }
+#pragma unroll
+        for (int j = 0; j < B; j++) {
+            if (r0 + j < rows) {
+                a1[j] = pitch_x(in, hist, H, I, inst, m1[j]); b1[j] = pitch_x(in, hist, H, I, inst, m1[j] - 1);
+                a2[j] = pitch_x(in, hist, H, I, inst, m2[j]); b2[j] = pitch_x(in, hist, H, I, inst, m2[j] - 1);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < B; j++) {
+            if (r0 + j < rows) {
+                const float w1 = pitch_cos_poly(__fmul_rn(__fsub_rn(p1[j], 0.5f), 3.14159274f)), w2 = pitch_cos_poly(__fmul_rn(__fsub_rn(p2[j], 0.5f), 3.14159274f));
+                const float t1 = __fadd_rn(a1[j], __fmul_rn(__fsub_rn(b1[j], a1[j]), f1[j])), t2 = __fadd_rn(a2[j], __fmul_rn(__fsub_rn(b2[j], a2[j]), f2[j]));
+                shifted[(size_t) (c * kPitchChunk + r0 + j) * I + inst] = __fadd_rn(__fmul_rn(t1, w1), __fmul_rn(t2, w2));
+            }
+        }
     }
 }
 
@@ -580,10 +636,12 @@ OLB_API int olb_chorus_process(olb_chorus *h, const float *in_dev, float *out_de
     const size_t smem = chorus_smem(in_smem ? h->R : 0);
     const char *ek = getenv("OLB_CHORUS_KERNEL");  // "direct" forces the plain-load variant (test aid)
     const bool tma = !(ek && !strcmp(ek, "direct")) && (h->I % 4 == 0) && (((uintptr_t) in_dev | (uintptr_t) out_dev) & 15) == 0;
-    // Time cuts: the pitch shifter's output is an intermediate block of its own; cut so that it stays in L2 between the
-    // kernel that writes it and the chorus kernel that streams it (~48 MiB, whole 64-frame tiles).
+    // Time cuts: the pitch shifter's output is an intermediate block of its own;
+    // scratch bounded (256 MiB, whole 64-frame tiles).  Long cuts matter more than L2 residency: every cut is a launch of
+    // k_chorus with its ring load / store and pipeline fill (profiles/r02_run19_chorus_cuts.txt: 8 192 instances x 48 000 frames
+    // 12.3 / 8.3 / 6.9 / 6.4 / 6.2 ms at cuts of 512 / 1 536 / 4 096 / 12 288 / 48 000 frames).
     const uint64_t I = h->I;
-    uint64_t cut = (48ull << 20) / (I * sizeof(float));
+    uint64_t cut = (256ull << 20) / (I * sizeof(float));
     cut = cut < 64 ? 64 : (cut / 64) * 64;
     if (const char *ec = getenv("OLB_CHORUS_CUT")) cut = (uint64_t) atoll(ec) < 1 ? 1 : (uint64_t) atoll(ec);  // test aid: any cut length
     if (cut > frames) cut = frames;

@@ -153,6 +153,26 @@ def test_pitch_shifter_other_sample_rates(orc, sr):
     assert np.array_equal(bits(y[:, 6]), bits(orc.chorus(x[:, 6], sr=sr, pitch=1.5, rate=0.7)))
 
 
+def test_pitch_shifter_resting_and_running_warps_in_one_bank(orc):
+    """Warps whose 32 phasors all rest take the hoisted path of k_pitch_taps, the others the general one; a resting phasor
+    that was running before (pitch set back to 0 mid-stream) rests at a phase other than 0."""
+    I, T = 96, 3000
+    x = orc.noise(28, 0, I, 0, T, 0.5)
+    b = ChorusBank(I)
+    b.Set("pitch", 2.0, first=32, count=33)  # warp 1 entirely, and lane 0 of warp 2
+    dx = torch.from_numpy(x).cuda()
+    dy = torch.empty_like(dx)
+    b.ProcessDevice(dx.data_ptr(), dy.data_ptr(), 1700)
+    b.Set("pitch", 0.0)                      # every phasor rests from here on, warp 1's at whatever phase it reached
+    b.ProcessDevice(dx[1700:].data_ptr(), dy[1700:].data_ptr(), T - 1700)
+    torch.cuda.synchronize()
+    y = dy.cpu().numpy()
+    b.close()
+    for i, p in ((0, 0.0), (31, 0.0), (32, 2.0), (50, 2.0), (64, 2.0), (65, 0.0), (95, 0.0)):
+        want = orc.chorus(x[:, i], pitch=p, changes=[(1700, dict(pitch=0.0))])
+        assert np.array_equal(bits(y[:, i]), bits(want)), i
+
+
 def test_stereo_chorus_is_two_mono_choruses_phase_1_and_0(orc):
     """stereo-chorus.rnbopat: in~ 1 -> mono-chorus (phase 1) -> out~ 1, in~ 2 -> mono-chorus (phase 0) -> out~ 2, the other
     params shared per stereo instance."""
