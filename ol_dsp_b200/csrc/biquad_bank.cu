@@ -837,7 +837,7 @@ static int launch_sys(olb_biquad *h, const float *in, float *out, uint32_t frame
 // CTAs share an SM.  A lone CTA must keep ~100 KiB of loads in flight to cover the HBM latency by itself
 // (profiles/r01_run7_small_banks.txt), and with one or two warps per scheduler the per-tile bookkeeping (barrier wait,
 // pipeline fill and drain: ~650 cycles) wants TALL tiles (profiles/r02_run13_skew_sweep.txt: 4 096 channels 31.8 / 24.9 /
-// 21.6 cycles per frame at 48 / 96 / 192 frames).  OLB_BQ_SKEW_CFG="<TB>x<NST>x<LAG>[r]" picks a compiled shape (tuning aid).
+// 21.6 / 20.9 cycles per frame at 48 / 96 / 192 / 256 frames).  OLB_BQ_SKEW_CFG="<TB>x<NST>x<LAG>[r]" picks a compiled shape (tuning aid).
 struct SkewCfg {
     int tb, nst, lag;
     bool roll;
@@ -854,7 +854,8 @@ static SkewCfg skew_cfg_auto(uint32_t C, uint32_t frames) {
     }
     const uint32_t ctas = (C + 31) / 32, per_sm = (ctas + 147) / 148;
     // the first and the last tile of a launch run the frame-by-frame path: short blocks keep the short tiles
-    if (per_sm <= 1) return frames >= 3072 ? SkewCfg{192, 8, 4, true} : SkewCfg{48, 32, 4, true};  // the SM to itself: 192 KiB
+    if (per_sm <= 1)  // the SM to itself: 192 KiB (256 rows is the tallest TMA box)
+        return frames >= 4096 ? SkewCfg{256, 6, 4, true} : frames >= 3072 ? SkewCfg{192, 8, 4, true} : SkewCfg{48, 32, 4, true};
     if (per_sm <= 2) return frames >= 1536 ? SkewCfg{96, 8, 4, true} : SkewCfg{48, 16, 4, true};   // 96 KiB
     if (per_sm <= 4) return SkewCfg{48, 8, 4, false};  // 48 KiB
     if (per_sm <= 8) return SkewCfg{24, 8, 4, false};  // 24 KiB
@@ -871,6 +872,7 @@ static int launch_skew(olb_biquad *h, const float *in, float *out, uint32_t fram
     SkewCfg c = skew_cfg_auto(h->C, frames);
     if (MODE != OLB_MODE_FAST) c.roll = false;  // the rolled tile is the FAST tier's
     if (S != 8) c = SkewCfg{24, 8, 4, false};
+    OLB_SKEW_TRY(8, 256, 6, 4, 4, true)
     OLB_SKEW_TRY(8, 192, 8, 4, 4, true)
     OLB_SKEW_TRY(8, 96, 8, 4, 4, true)
     OLB_SKEW_TRY(8, 96, 16, 4, 4, true)

@@ -1,7 +1,8 @@
 """Parity over the FULL duration of the BASELINE configs (48 kHz x 10 s = 480 000 frames per unit), streamed in the block
-sizes the benches use, for a handful of units of every bank against the oracle: bit-exact for the sequential-order
-kernels, <= 1e-5 of full scale for the voice output (north_star's tolerance, the only device transcendental path).  The
-unit counts are small so that the scalar oracle finishes in seconds; bank-width properties live in the per-unit files."""
+sizes the benches use, against the oracle: bit-exact for the sequential-order kernels, <= 1e-5 of full scale for the voice
+output (north_star's tolerance, the only device transcendental path).  First with a handful of units (every unit checked),
+then with every bank at its BASELINE width (C3's 65 536 channels, C4's 65 536 voices, C5's 8 192 instances) on device-generated
+noise, sampled units checked -- the scalar oracle runs only the sampled units, so the file still takes about a minute."""
 import numpy as np
 import pytest
 import torch
@@ -149,3 +150,101 @@ def test_voices_10s(orc):
         want = orc.voice(T, ev=ev)
         assert np.abs(y[:, i] - want).max() <= 1e-5, (note, float(np.abs(y[:, i] - want).max()))
         assert np.abs(want[:T // 2]).max() > 0.01  # the voice sounded
+
+
+# ---- banks at their BASELINE width over long runs: device-generated noise block by block, sampled units against the oracle ----
+def _wide_stream(process, units, frames, block, pick, scale=0.25, seed=0x01D5B200, outs=1):
+    """Streams `frames` frames of Philox noise through a bank of `units` units, `block` frames at a time, keeping only the
+    columns in `pick`.  Returns (x[frames][len(pick)], [y ...]) on the host."""
+    dev = torch.empty((block, units), dtype=torch.float32, device="cuda")
+    dout = [torch.empty_like(dev) for _ in range(outs)]
+    idx = torch.as_tensor(pick, device="cuda")
+    xs, ys = [], [[] for _ in range(outs)]
+    for a in range(0, frames, block):
+        n = min(block, frames - a)
+        noise_device(dev.data_ptr(), seed, 0, units, a, n, scale)
+        process(dev.data_ptr(), [d.data_ptr() for d in dout], n)
+        xs.append(dev[:n, idx].cpu().numpy())
+        for k in range(outs):
+            ys[k].append(dout[k][:n, idx].cpu().numpy())
+    return np.concatenate(xs), [np.concatenate(y) for y in ys]
+
+
+@pytest.mark.parametrize("kind,name,I,frames,kernel", [(fx.RACK, "fxrack", 8192, T, "k_fx_split"), (fx.DELAY, "delayfx", 8192, T, "k_fx_split"),
+                                                       (fx.RACK, "fxrack", 16384, T, "k_fx_split"), (fx.FILTER, "filterfx", 65536, T, "k_fx_tma")])
+def test_fx_banks_at_baseline_width_long(orc, kind, name, I, frames, kernel):
+    """C5's 8 192 instances (FxRack, DelayFx), 16 384 racks (four pipelines per CTA) and 65 536 filters over the full 10 s:
+    the write pointer of the 48 000-sample delay lines wraps 10 times under the warp pipelines with 2 and 4 pipelines per CTA.
+    C5's delay-time sweep across the bank; sampled instances bit-exact against the oracle."""
+    b = FxBank(kind, I)
+    times = (0.05 + 0.9 * np.arange(I) / I).astype(np.float32)
+    b.UpdateHardwareControl(35, times)  # CC_DELAY_TIME
+    pick = sorted({0, 1, 31, 32, I // 2 - 1, I // 2, I - 33, I - 1})
+    x, (y,) = _wide_stream(lambda i, o, n: b.ProcessDevice(i, o[0], n), I, frames, BLOCK, pick)
+    assert b.LastKernel() == kernel
+    b.close()
+    for j, i in enumerate(pick):
+        want = getattr(orc, name)(np.ascontiguousarray(x[:, j:j + 1]), 48000.0, [(0, loader.EV_HW_CC, 35, float(times[i]))])
+        assert np.array_equal(bits(y[:, j]), bits(want[:, 0])), (name, I, i)
+
+
+def test_dattorro_at_baseline_width_across_the_counter_wrap(orc):
+    """C5's 8 192 plates (two waves of the four-warp kernel with its rings in HBM) over the full 10 s: the 16-bit sample counter
+    all ring indices derive from wraps 7 times.  C5's decay sweep; sampled instances bit-exact against verb.cpp's restatement."""
+    I, frames = 8192, T
+    b = DattorroBank(I)
+    decay = (0.5 + 0.4 * (np.arange(I) % 16) / 16).astype(np.float32)
+    b.SetDecay(decay)
+    pick = sorted({0, 31, 32, 4735, 4736, I - 1})
+    x, (l, r) = _wide_stream(lambda i, o, n: b.ProcessDevice(i, o[0], o[1], n), I, frames, BLOCK, pick, outs=2)
+    assert b.LastKernel() == "k_dattorro_split"
+    b.close()
+    for j, i in enumerate(pick):
+        wl, wr = orc.dattorro(x[:, j], [NAN, NAN, NAN, NAN, float(decay[i]), NAN, NAN])
+        assert np.array_equal(bits(l[:, j]), bits(wl)) and np.array_equal(bits(r[:, j]), bits(wr)), i
+
+
+def test_chorus_at_baseline_width_long(orc):
+    """C5's 8 192 choruses over the full 10 s, rate and depth swept across the bank, every 7th instance with a running pitch shifter."""
+    I, frames = 8192, T
+    b = ChorusBank(I)
+    rate = (np.arange(I) % 101 / 100.0).astype(np.float32)
+    depth = (0.08 + 0.92 * (np.arange(I) % 53) / 52.0).astype(np.float32)
+    pitch = np.where(np.arange(I) % 7 == 0, 0.25 + (np.arange(I) % 11) / 4.0, 0.0).astype(np.float32)
+    b.Set("rate", rate)
+    b.Set("depth", depth)
+    b.Set("pitch", pitch)
+    pick = sorted({0, 7, 31, 32, 4095, 4102, I - 2, I - 1})
+    x, (y,) = _wide_stream(lambda i, o, n: b.ProcessDevice(i, o[0], n), I, frames, BLOCK, pick)
+    b.close()
+    for j, i in enumerate(pick):
+        want = orc.chorus(x[:, j], rate=float(rate[i]), depth=float(depth[i]), pitch=float(pitch[i]))
+        assert np.array_equal(bits(y[:, j]), bits(want)), i
+
+
+def test_voices_at_baseline_width(orc):
+    """C4's 65 536 voices (note 36 + v mod 61) over the full 10 s in 4 800-frame blocks, NoteOff at 5 s; sampled voices (first,
+    last, both sides of the note wrap and of the bank's middle) within 1e-5 of the oracle."""
+    V, frames, block = 65536, T, 4800
+    notes = (36 + np.arange(V) % 61).astype(np.uint8)
+    ccs = [(41, 70), (42, 30), (73, 64), (75, 60), (108, 10), (111, 40)]
+    b = VoiceBank(V)
+    for cc, val in ccs:
+        b.UpdateMidiControl(cc, val)
+    b.NoteOn(notes)
+    pick = sorted({0, 1, 60, 61, 32767, 32768, V - 2, V - 1})
+    idx = torch.as_tensor(pick, device="cuda")
+    out = torch.empty((block, V), dtype=torch.float32, device="cuda")
+    ys = []
+    for a in range(0, frames, block):
+        if a == frames // 2:
+            b.NoteOff()
+        b.ProcessDevice(block, out_ptr=out.data_ptr())
+        ys.append(out[:, idx].cpu().numpy())
+    b.close()
+    y = np.concatenate(ys)
+    for j, v in enumerate(pick):
+        note = int(notes[v])
+        ev = [(0, loader.EV_MIDI_CC, cc, val) for cc, val in ccs] + [(0, loader.EV_NOTE_ON, note, 100), (frames // 2, loader.EV_NOTE_OFF, note, 0)]
+        want = orc.voice(frames, ev=ev)
+        assert np.abs(y[:, j] - want).max() <= 1e-5, (v, note, float(np.abs(y[:, j] - want).max()))
