@@ -91,25 +91,25 @@ __device__ __forceinline__ void skew_tile_fast_unrolled(float *col, const u64 (&
     u64 V[TB + 2], Y[TB + 2], A[TB], B[TB], C[TB];  // V[j + 2], Y[j + 2] = position j of this tile; [0], [1] = history
     V[1] = x1; V[0] = x2; Y[1] = y1; Y[0] = y2;
 #pragma unroll
-    for (int j = 0; j < D + P && j < TB; j++) x[j] = lds_ordered(col + j * CH);
-    // warp 0 of a FAST bank scales its input by G = prod(b0): two consecutive inputs per packed product, (x[j], x[j+1]) *
-    // (G, G), taken one step before the first of them is used.  A scalar product at the load -- the obvious place -- is
-    // scheduled by ptxas right behind its load (one register rotates through all loads), which put the load's latency into
-    // every step of warp 0, the slowest stage of the pipeline (ncu: 28 cycles a step against 15.5 for the other warps).
-    const u64 gain2 = pack2(gain, gain);
-    float xg[TB + 1];
-    static_assert(TB % 2 == 0 && D >= 2, "inputs are scaled in pairs");
-    if (GAIN) unpack2(fmul2(pack2(x[0], x[1]), gain2), xg[0], xg[1]);
+    for (int j = 0; j < D + P && j < TB; j++) {
+        x[j] = lds_ordered(col + j * CH);
+        if (GAIN) x[j] = __fmul_rn(gain, x[j]);  // warp 0 of a FAST bank applies G = prod(b0) to its input
+    }
+    // (Scaling the inputs in pairs with one packed product, away from the loads, was tried for this tile: 571 instructions
+    // against 399, and with three or more warps on a scheduler -- the only banks this tile serves -- issue slots are what
+    // counts: 16 384 channels 4.00e11 against 4.43e11.)
 #pragma unroll
     for (int t = -P; t < TB; t++) {
-        if (t + P + D < TB && t + P + D >= D + P) x[t + P + D] = lds_ordered(col + (t + P + D) * CH);
+        if (t + P + D < TB && t + P + D >= D + P) {
+            x[t + P + D] = lds_ordered(col + (t + P + D) * CH);
+            if (GAIN) x[t + P + D] = __fmul_rn(gain, x[t + P + D]);
+        }
         if (t + 3 < TB) {
             const int j = t + 3;  // the high half's input: the low half's output kSkewLag positions back
             float ylo, yhi;
             if (j - kSkewLag >= 0) unpack2(Y[j - kSkewLag + 2], ylo, yhi);
             else ylo = p[kSkewLag - 1 - j];
-            if (GAIN && j % 2 == 1 && j + 1 < TB) unpack2(fmul2(pack2(x[j + 1], x[j + 2]), gain2), xg[j + 1], xg[j + 2]);
-            V[j + 2] = pack2(GAIN ? xg[j] : x[j], ylo);
+            V[j + 2] = pack2(x[j], ylo);
             A[j] = ffma2(k[1], V[j + 1], V[j + 2]);
         }
         if (t + 2 >= 0 && t + 2 < TB) B[t + 2] = ffma2(k[2], V[t + 2], A[t + 2]);

@@ -75,7 +75,7 @@ __device__ __forceinline__ float sin_quarter(float x) {
 
 // trace (optional): 4 floats per voice-frame = oscillator output, amp envelope, filter envelope, phase after the tick
 __global__ void __launch_bounds__(128) k_voice(float *out, float *partial, float *trace, uint32_t frames, uint32_t V,
-                                               const float *__restrict__ par, float *state, uint32_t partial_ld) {
+                                               const float *__restrict__ par, float *retrig_flags, float *state, uint32_t partial_ld) {
     const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = v < V;
     const uint32_t vv = live ? v : V - 1;  // dead lanes shadow a live voice so the warp reductions stay convergent
@@ -84,7 +84,10 @@ __global__ void __launch_bounds__(128) k_voice(float *out, float *partial, float
     const float f_amount = P(VP_F_AMOUNT), a_amount = P(VP_A_AMOUNT), sr2 = P(VP_SR2), fc_max = P(VP_FC_MAX);
     const float damp_a = P(VP_DAMP_A), drive = P(VP_DRIVE);
     const int gate = (int) __float_as_uint(P(VP_GATE));
-    const bool retrig = __float_as_uint(P(VP_RETRIG)) != 0;
+    // the NoteOn retrigger is a one-shot: read through its own (writable) pointer and cleared by the voice that consumed it, so
+    // the host need not upload the table a second time to take it back
+    const bool retrig = live && __float_as_uint(retrig_flags[v]) != 0;
+    if (retrig) retrig_flags[v] = 0.0f;
     const EnvCoef ka{P(VP_A_D0), P(VP_A_TARGET), P(VP_A_DD0), P(VP_A_RD0), P(VP_A_SUS)};
     const EnvCoef kf{P(VP_F_D0), P(VP_F_TARGET), P(VP_F_DD0), P(VP_F_RD0), P(VP_F_SUS)};
     auto S = [&](int s) -> float & { return state[(size_t) s * V + vv]; };
@@ -188,8 +191,15 @@ struct olb_voice {
     int device = 0;
     uint32_t V = 0;
     std::vector<host::VoiceParams> voices;
-    bool dirty = true;
+    bool dirty = false;
+    uint32_t dirty_lo = 0, dirty_hi = 0;  // the voices whose parameters changed since the last upload: [lo, hi)
     bool retrig_pending = false;
+    uint32_t retrig_lo = 0, retrig_hi = 0;
+    void mark(uint32_t lo, uint32_t hi) {
+        if (!dirty) { dirty_lo = lo; dirty_hi = hi; }
+        else { dirty_lo = lo < dirty_lo ? lo : dirty_lo; dirty_hi = hi > dirty_hi ? hi : dirty_hi; }
+        dirty = true;
+    }
     float *d_par = nullptr, *d_state = nullptr, *d_partial = nullptr;
     uint32_t partial_ld = 0;  // frames capacity of the warp-partial buffer
     std::vector<float> stage;
@@ -202,11 +212,15 @@ static float vbits_f(uint32_t u) {
     return f;
 }
 
+// Uploads the columns of the voices whose parameters changed: one 2-D copy of [VP_COUNT][hi - lo] out of the [VP_COUNT][V]
+// table (a NoteOn of one voice is 22 floats, not the bank's 5.8 MB).
 static int voice_upload(olb_voice *h, cudaStream_t st) {
     const size_t V = h->V;
+    if (h->dirty_lo >= h->dirty_hi) { h->dirty_lo = 0; h->dirty_hi = h->V; }
+    const size_t lo = h->dirty_lo, hi = h->dirty_hi;
     h->stage.resize((size_t) VP_COUNT * V);
     float *s = h->stage.data();
-    for (size_t i = 0; i < V; i++) {
+    for (size_t i = lo; i < hi; i++) {
         const host::VoiceParams &u = h->voices[i];
         s[VP_FREQ * V + i] = u.freq;
         s[VP_GATE * V + i] = vbits_f((uint32_t) u.gate);
@@ -225,9 +239,11 @@ static int voice_upload(olb_voice *h, cudaStream_t st) {
         s[VP_F_D0 * V + i] = u.filter_env.a_d0; s[VP_F_TARGET * V + i] = u.filter_env.a_target; s[VP_F_DD0 * V + i] = u.filter_env.d_d0;
         s[VP_F_RD0 * V + i] = u.filter_env.r_d0; s[VP_F_SUS * V + i] = u.filter_env.sus;
     }
-    OLB_CUDA(cudaMemcpyAsync(h->d_par, s, h->stage.size() * sizeof(float), cudaMemcpyHostToDevice, st));
-    OLB_CUDA(cudaStreamSynchronize(st));
+    OLB_CUDA(cudaMemcpy2DAsync(h->d_par + lo, V * sizeof(float), s + lo, V * sizeof(float), (hi - lo) * sizeof(float), VP_COUNT,
+                               cudaMemcpyHostToDevice, st));
+    OLB_CUDA(cudaStreamSynchronize(st));  // the staging table is pageable and reused
     h->dirty = false;
+    h->dirty_lo = h->dirty_hi = 0;
     return OLB_OK;
 }
 
@@ -237,7 +253,7 @@ static int voice_init_all(olb_voice *h, float sr) {
         u.retrigger = false;
     }
     OLB_CUDA(h->order.memset0(h->d_state, (size_t) VS_COUNT * h->V * sizeof(float)));
-    h->dirty = true;
+    h->mark(0, h->V);
     return OLB_OK;
 }
 
@@ -295,7 +311,7 @@ OLB_API int olb_voice_update_midi(olb_voice *h, uint32_t first, uint32_t count, 
     OLB_VOICE_RANGE("olb_voice_update_midi");
     OLB_LOCK(h);
     for (uint32_t i = first; i < first + count; i++) h->voices[i].UpdateMidiControl(control, value);
-    h->dirty = true;
+    h->mark(first, first + count);
     return OLB_OK;
 }
 
@@ -304,7 +320,7 @@ OLB_API int olb_voice_update_hw(olb_voice *h, uint32_t first, uint32_t count, ui
     OLB_LOCK(h);
     OLB_ARG(values_host, "olb_voice_update_hw: values_host is NULL");
     for (uint32_t i = 0; i < count; i++) h->voices[first + i].UpdateHardwareControl(control, values_host[(size_t) i * stride]);
-    h->dirty = true;
+    h->mark(first, first + count);
     return OLB_OK;
 }
 
@@ -313,7 +329,7 @@ OLB_API int olb_voice_update_config(olb_voice *h, uint32_t first, uint32_t count
     OLB_LOCK(h);
     OLB_ARG(config16_host, "olb_voice_update_config: config is NULL");
     for (uint32_t i = first; i < first + count; i++) h->voices[i].UpdateConfig(config16_host);
-    h->dirty = true;
+    h->mark(first, first + count);
     return OLB_OK;
 }
 
@@ -323,7 +339,9 @@ OLB_API int olb_voice_note_on(olb_voice *h, uint32_t first, uint32_t count, cons
     OLB_ARG(notes_host, "olb_voice_note_on: notes_host is NULL");
     (void) velocity;  // the reference ignores it too (SynthVoice.h:245-251)
     for (uint32_t i = 0; i < count; i++) h->voices[first + i].NoteOn(notes_host[(size_t) i * stride]);
-    h->dirty = true;
+    h->mark(first, first + count);
+    if (!h->retrig_pending) { h->retrig_lo = first; h->retrig_hi = first + count; }
+    else { h->retrig_lo = first < h->retrig_lo ? first : h->retrig_lo; h->retrig_hi = first + count > h->retrig_hi ? first + count : h->retrig_hi; }
     h->retrig_pending = true;
     return OLB_OK;
 }
@@ -332,7 +350,7 @@ OLB_API int olb_voice_note_off(olb_voice *h, uint32_t first, uint32_t count) {
     OLB_VOICE_RANGE("olb_voice_note_off");
     OLB_LOCK(h);
     for (uint32_t i = first; i < first + count; i++) h->voices[i].NoteOff();
-    h->dirty = true;
+    h->mark(first, first + count);
     return OLB_OK;
 }
 
@@ -340,7 +358,7 @@ OLB_API int olb_voice_set_gate(olb_voice *h, uint32_t first, uint32_t count, int
     OLB_VOICE_RANGE("olb_voice_set_gate");
     OLB_LOCK(h);
     for (uint32_t i = first; i < first + count; i++) h->voices[i].gate = gate ? 1 : 0;
-    h->dirty = true;
+    h->mark(first, first + count);
     return OLB_OK;
 }
 
@@ -349,7 +367,7 @@ OLB_API int olb_voice_set_frequency(olb_voice *h, uint32_t first, uint32_t count
     OLB_LOCK(h);
     OLB_ARG(freqs_host, "olb_voice_set_frequency: freqs_host is NULL");
     for (uint32_t i = 0; i < count; i++) h->voices[first + i].freq = freqs_host[(size_t) i * stride];
-    h->dirty = true;
+    h->mark(first, first + count);
     return OLB_OK;
 }
 
@@ -387,17 +405,16 @@ OLB_API int olb_voice_process(olb_voice *h, float *out_dev, float *bus_dev, uint
         h->partial_ld = ld;
     }
     k_voice<<<(h->V + 127) / 128, 128, 0, st>>>(out_dev, bus_dev ? h->d_partial : nullptr, trace_dev, (uint32_t) frames, h->V, h->d_par,
-                                               h->d_state, h->partial_ld);
+                                               h->d_par + (size_t) VP_RETRIG * h->V, h->d_state, h->partial_ld);
     OLB_LAUNCHED();
     if (bus_dev) {
         k_bus_reduce<<<(unsigned) ((frames + 127) / 128), 128, 0, st>>>(h->d_partial, warps, h->partial_ld, bus_dev, (uint32_t) frames,
                                                                        bus_channels, accumulate, bus_gain);
         OLB_LAUNCHED();
     }
-    if (h->retrig_pending) {  // the retrigger was consumed by this launch
-        for (auto &u : h->voices) u.retrigger = false;
+    if (h->retrig_pending) {  // the retrigger was consumed by this launch: the kernel cleared the device flags, the host clears its own
+        for (uint32_t i = h->retrig_lo; i < h->retrig_hi; i++) h->voices[i].retrigger = false;
         h->retrig_pending = false;
-        h->dirty = true;
     }
     return OLB_OK;
 }

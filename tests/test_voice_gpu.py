@@ -173,6 +173,33 @@ def test_sample_accurate_event_list(orc):
     bank.close()
 
 
+def test_dense_event_list_on_a_wide_bank(orc):
+    """C4's 65 536 voices with a dense sample-accurate script: 64 NoteOn and 32 NoteOff at distinct frames of one 4 800-frame
+    block, each addressed to its own voice (a cut uploads the touched voices' parameter columns only, and the retrigger is
+    cleared by the voice that consumed it).  The touched voices against the oracle, an untouched one silent."""
+    from ol_dsp_b200.voice import process_events
+    V, frames = 65536, 4800
+    voices = [(i * 1021 + 7) % V for i in range(64)]
+    ev = [(13 + 61 * i, loader.EV_NOTE_ON, 40 + i, 100, v) for i, v in enumerate(voices)]
+    ev += [(2500 + 53 * i, loader.EV_NOTE_OFF, 40 + 2 * i, 0, voices[2 * i]) for i in range(32)]
+    bank = VoiceBank(V)
+    out = torch.empty((frames, V), dtype=torch.float32, device="cuda")
+    process_events(bank, ev, frames, out_ptr=out.data_ptr())
+    torch.cuda.synchronize()
+    for i in (0, 1, 2, 31, 62, 63):
+        script = [(13 + 61 * i, loader.EV_NOTE_ON, 40 + i, 100)]
+        if i % 2 == 0:
+            script.append((2500 + 53 * (i // 2), loader.EV_NOTE_OFF, 40 + i, 0))
+        want = orc.voice(frames, ev=script)
+        got = out[:, voices[i]].cpu().numpy()
+        assert np.abs(got - want).max() <= TOL, (i, float(np.abs(got - want).max()))
+        assert np.abs(want).max() > 0.01
+    assert float(out[:, 5].abs().max()) == 0.0  # a voice nobody played
+    playing = bank.Playing()
+    assert playing[voices[1]] == 41 and playing[voices[0]] == 0
+    bank.close()
+
+
 def test_voicemap_against_the_reference_golden():
     """ol::synth::VoiceMap over a bank (SURVEY.md section 8f item 2): tests/golden/synth.npz 'voicemap' is the reference's own
     VoiceMap<1> over six SynthVoices (pads on five notes, channel 3 set twice, unmapped notes / channels ignored)."""
