@@ -856,7 +856,8 @@ static SkewCfg skew_cfg_auto(uint32_t C, uint32_t frames) {
     // the first and the last tile of a launch run the frame-by-frame path: short blocks keep the short tiles
     if (per_sm <= 1)  // the SM to itself: 192 KiB (256 rows is the tallest TMA box)
         return frames >= 4096 ? SkewCfg{256, 6, 4, true} : frames >= 3072 ? SkewCfg{192, 8, 4, true} : SkewCfg{48, 32, 4, true};
-    if (per_sm <= 2) return frames >= 1536 ? SkewCfg{96, 8, 4, true} : SkewCfg{48, 16, 4, true};   // 96 KiB
+    if (per_sm <= 2)  // 96 KiB each
+        return frames >= 2048 ? SkewCfg{128, 6, 4, true} : frames >= 1536 ? SkewCfg{96, 8, 4, true} : SkewCfg{48, 16, 4, true};
     if (per_sm <= 4) return SkewCfg{48, 8, 4, false};  // 48 KiB
     if (per_sm <= 8) return SkewCfg{24, 8, 4, false};  // 24 KiB
     return SkewCfg{24, 4, 4, false};                   // 12 KiB: up to 18 CTAs per SM
@@ -874,6 +875,7 @@ static int launch_skew(olb_biquad *h, const float *in, float *out, uint32_t fram
     if (S != 8) c = SkewCfg{24, 8, 4, false};
     OLB_SKEW_TRY(8, 256, 6, 4, 4, true)
     OLB_SKEW_TRY(8, 192, 8, 4, 4, true)
+    OLB_SKEW_TRY(8, 128, 6, 4, 4, true)
     OLB_SKEW_TRY(8, 96, 8, 4, 4, true)
     OLB_SKEW_TRY(8, 96, 16, 4, 4, true)
     OLB_SKEW_TRY(8, 48, 32, 4, 4, true)

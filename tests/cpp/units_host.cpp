@@ -1,7 +1,7 @@
 // C++ callers written the way a reference user writes them (Init -> setters -> Process per frame, then per block), against
 // include/ol_gpu/{FxBank,DattorroBank,ChorusBank,VoiceBank}.hpp.  Built by tests/test_abi.py (link check, CPU) and run by
 // tests/test_cpp_hosts_gpu.py on the GPU box, where the outputs are compared with the oracle.
-//   usage: units_host <filter|delay|reverb|rack|plate|chorus|poly|voicemap|sampler> <instances> <frames> <in.f32> <out.f32> [out2.f32]
+//   usage: units_host <filter|delay|reverb|rack|rack2|delay2|plate|chorus|chorus2|poly|voicemap|sampler> <instances> <frames> <in.f32> <out.f32> [out2.f32]
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -28,8 +28,9 @@ static void dump(const char *path, const std::vector<float> &v) {
 
 // test/fx_test.cpp:25-55 shape: Init, a setter, per-frame Process in a loop -- then the rest of the block at once
 template <class Bank>
-static int run_fx(uint32_t I, uint32_t T, std::vector<float> &in, std::vector<float> &out) {
+static int run_fx(uint32_t I, uint32_t T, std::vector<float> &in, std::vector<float> &out, uint32_t width = 1) {
     Bank bank(I);
+    I *= width;  // floats per bank frame (stereo instances: 2 each)
     if (bank.Init(48000.f) != ol::gpu::Ok) {
         fprintf(stderr, "Init failed: %s\n", bank.error().c_str());
         return 4;
@@ -82,6 +83,19 @@ int main(int argc, char **argv) {
         if (t < T) plates.ProcessBlock(&in[(size_t) t * I], &out[(size_t) t * I], &out2[(size_t) t * I], T - t);
         rc = plates.status() == OLB_OK ? 0 : 5;
         if (rc) fprintf(stderr, "process failed: %s\n", plates.error().c_str());
+    } else if (!strcmp(unit, "rack2") || !strcmp(unit, "delay2")) {
+        // the stereo banks: `instances` here counts FLOATS per frame (2 per stereo instance), as the buffers are sized by it
+        rc = !strcmp(unit, "rack2") ? run_fx<ol::gpu::FxRack2Bank>(I / 2, T, in, out, 2) : run_fx<ol::gpu::DelayFx2Bank>(I / 2, T, in, out, 2);
+    } else if (!strcmp(unit, "chorus2")) {
+        ol::gpu::StereoChorusBank ch(I / 2);  // stereo-chorus.rnbopat: frames are [instances][2]
+        if (ch.Init(48000.f) != ol::gpu::Ok) return 4;
+        ch.SetRate(0.7f);
+        ch.SetDepth(0.9f);
+        ch.SetPitch(0.5f);
+        uint32_t t = 0;
+        for (; t < 3 && t < T; t++) ch.Process(&in[(size_t) t * I], &out[(size_t) t * I]);
+        if (t < T) ch.ProcessBlock(&in[(size_t) t * I], &out[(size_t) t * I], T - t);
+        rc = ch.status() == OLB_OK ? 0 : 5;
     } else if (!strcmp(unit, "chorus")) {
         ol::gpu::ChorusBank ch(I);
         if (ch.Init(48000.f) != ol::gpu::Ok) {

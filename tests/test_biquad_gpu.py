@@ -214,11 +214,11 @@ def test_skewed_pairs_bit_exact(orc, S, mode, C, chunks):
     assert np.array_equal(bits(st), bits(ost))
 
 
-@pytest.mark.parametrize("C,chunks,cfg", [(4096, [3500, 3100, 3072], None), (4096, [4100, 4096, 4353], None), (8192, [1600, 2000, 1536], None), (1024, [3333], None),
+@pytest.mark.parametrize("C,chunks,cfg", [(4096, [3500, 3100, 3072], None), (4096, [4100, 4096, 4353], None), (8192, [1600, 2000, 1536], None), (8192, [2048, 2300], None), (1024, [3333], None),
                                           (4096, [700], "24x8x4r"), (4096, [1000], "48x8x4r"), (4096, [2000], "96x16x4r")])
 def test_skewed_pairs_rolled_tile(orc, C, chunks, cfg, monkeypatch):
     """The FAST tier's rolled tile in every compiled height: 256 and 192 frames (<= 4 736 channels, blocks of 4 096 / 3 072 frames or more),
-    96 (<= 9 472 channels, 1 536 or more), 48 and 24; several calls so that the pipeline's fill from and drain into the
+    128 and 96 (<= 9 472 channels, 2 048 / 1 536 or more), 48 and 24; several calls so that the pipeline's fill from and drain into the
     bank's history format is exercised at tile boundaries that move from call to call."""
     if cfg:
         monkeypatch.setenv("OLB_BQ_SKEW_CFG", cfg)

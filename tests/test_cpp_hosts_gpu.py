@@ -58,6 +58,31 @@ def test_chorus_mirror(orc, tmp_path):
     assert np.array_equal(bits(y[:, 9]), bits(orc.chorus(x[:, 9], rate=0.7, depth=0.9)))
 
 
+@pytest.mark.parametrize("unit,name", [("rack2", "fxrack"), ("delay2", "delayfx")])
+def test_stereo_fx_mirrors(orc, tmp_path, unit, name):
+    """ol::gpu::FxRack2Bank / DelayFx2Bank: the reference's <2> templates, frames [instances][2]."""
+    I, T = 12, 900
+    x = orc.noise(54, 0, 2 * I, 0, T, 0.5)
+    run(unit, 2 * I, T, x, tmp_path)
+    y = np.fromfile(tmp_path / "out.f32", dtype=np.float32).reshape(T, I, 2)
+    ev = [(0, loader.EV_HW_CC, 35, 0.3), (0, loader.EV_MIDI_CC, 41, 90)]
+    for i in (0, 5, 11):
+        want = getattr(orc, name)(np.ascontiguousarray(x.reshape(T, I, 2)[:, i, :]), 48000.0, ev)
+        assert np.array_equal(bits(y[:, i, :]), bits(want)), (unit, i)
+
+
+def test_stereo_chorus_mirror(orc, tmp_path):
+    """ol::gpu::StereoChorusBank (stereo-chorus.rnbopat): left = phase 1, right = phase 0, shared rate / depth / pitch."""
+    I, T = 6, 2000
+    x = orc.noise(55, 0, 2 * I, 0, T, 0.5)
+    run("chorus2", 2 * I, T, x, tmp_path)
+    y = np.fromfile(tmp_path / "out.f32", dtype=np.float32).reshape(T, I, 2)
+    x3 = x.reshape(T, I, 2)
+    for i in (0, 5):
+        assert np.array_equal(bits(y[:, i, 0]), bits(orc.chorus(x3[:, i, 0], rate=0.7, depth=0.9, pitch=0.5, phase=1.0)))
+        assert np.array_equal(bits(y[:, i, 1]), bits(orc.chorus(x3[:, i, 1], rate=0.7, depth=0.9, pitch=0.5, phase=0.0)))
+
+
 def test_polyvoice_mirror(orc, tmp_path):
     V, T = 4, 3000
     out = run("poly", V, T, None, tmp_path)
