@@ -224,8 +224,10 @@ int olb_voice_set_frequency(olb_voice *h, uint32_t first, uint32_t count, const 
 int olb_voice_playing(olb_voice *h, uint32_t first, uint32_t count, uint8_t *playing_host);
 int olb_voice_process(olb_voice *h, float *out_dev, float *bus_dev, uint32_t bus_channels, int accumulate, float bus_gain,
                       float *trace_dev, uint64_t frames, void *stream);
-/* Sample-accurate control.  Events sorted by frame are applied BEFORE the frame they name; the
- * block is cut there.  voice < 0: Polyvoice's allocation (NoteOn -> first voice not playing, NoteOff -> first voice playing
+/* Sample-accurate control.  Events sorted by frame are applied BEFORE the frame they name.
+ * Events that address ONE voice (notes; CCs with voice >= 0) are applied ON THE DEVICE: the host runs the setter maths, the
+ * addressed voice's parameter column after each event is shipped with the launch, and the voice reloads it at that frame --
+ * one launch however many such events the block holds.  Only a CC that fans out to every voice cuts the block.  voice < 0: Polyvoice's allocation (NoteOn -> first voice not playing, NoteOff -> first voice playing
  * that note: Polyvoice.h:35-51; CCs fan out to every voice: Polyvoice.h:53-63); voice >= 0: that voice (Voice.h:33-57). */
 #define OLB_EV_MIDI_CC 0  /* UpdateMidiControl(cc = a, value = (uint8) v) */
 #define OLB_EV_HW_CC 1    /* UpdateHardwareControl(cc = a, value = v) */

@@ -18,6 +18,7 @@
 // WARP per frame written coalesced 32 frames at a time; k_bus_reduce then sums the warp partials in warp order:
 // deterministic run to run; differs from the reference's one sequential sum over all voices only by where the
 // partial sums are cut (float re-association, tolerance tier).
+#include <algorithm>
 #include <vector>
 
 #include "common.cuh"
@@ -73,23 +74,37 @@ __device__ __forceinline__ float sin_quarter(float x) {
     return __fmaf_rn(__fmul_rn(x, x2), p, x);
 }
 
+// Sample-accurate events ON THE DEVICE (EVENTS = true; olb_voice_process_events): the host has applied the block's per-voice
+// events to its parameter members in order and snapshotted, after each one, the addressed voice's parameter column; the
+// snapshots are sorted by voice (stably: frame order within a voice).  A voice finds its own with a binary search at the
+// start and, at the frame an event names, reloads its registers from the snapshot -- what the reference does when a setter
+// runs between two Process calls (SynthVoice.h:101-267), at frame instead of block granularity and in ONE launch.
+struct VoiceEvents {
+    const uint32_t *voice;  // [count] ascending
+    const uint32_t *frame;  // [count] block-relative
+    const float *par;       // [count][VP_COUNT]
+    uint32_t count;
+};
+
 // trace (optional): 4 floats per voice-frame = oscillator output, amp envelope, filter envelope, phase after the tick
+template <bool EVENTS>
 __global__ void __launch_bounds__(128) k_voice(float *out, float *partial, float *trace, uint32_t frames, uint32_t V,
-                                               const float *__restrict__ par, float *retrig_flags, float *state, uint32_t partial_ld) {
+                                               const float *__restrict__ par, float *retrig_flags, float *state, uint32_t partial_ld,
+                                               const VoiceEvents ev) {
     const uint32_t v = blockIdx.x * blockDim.x + threadIdx.x;
     const bool live = v < V;
     const uint32_t vv = live ? v : V - 1;  // dead lanes shadow a live voice so the warp reductions stay convergent
     auto P = [&](int p) { return par[(size_t) p * V + vv]; };
-    const float freq = P(VP_FREQ), port_coeff = P(VP_PORT_COEFF), sr_recip = P(VP_SR_RECIP), cutoff = P(VP_CUTOFF);
-    const float f_amount = P(VP_F_AMOUNT), a_amount = P(VP_A_AMOUNT), sr2 = P(VP_SR2), fc_max = P(VP_FC_MAX);
-    const float damp_a = P(VP_DAMP_A), drive = P(VP_DRIVE);
-    const int gate = (int) __float_as_uint(P(VP_GATE));
+    float freq = P(VP_FREQ), port_coeff = P(VP_PORT_COEFF), sr_recip = P(VP_SR_RECIP), cutoff = P(VP_CUTOFF);
+    float f_amount = P(VP_F_AMOUNT), a_amount = P(VP_A_AMOUNT), sr2 = P(VP_SR2), fc_max = P(VP_FC_MAX);
+    float damp_a = P(VP_DAMP_A), drive = P(VP_DRIVE);
+    int gate = (int) __float_as_uint(P(VP_GATE));
     // the NoteOn retrigger is a one-shot: read through its own (writable) pointer and cleared by the voice that consumed it, so
     // the host need not upload the table a second time to take it back
     const bool retrig = live && __float_as_uint(retrig_flags[v]) != 0;
     if (retrig) retrig_flags[v] = 0.0f;
-    const EnvCoef ka{P(VP_A_D0), P(VP_A_TARGET), P(VP_A_DD0), P(VP_A_RD0), P(VP_A_SUS)};
-    const EnvCoef kf{P(VP_F_D0), P(VP_F_TARGET), P(VP_F_DD0), P(VP_F_RD0), P(VP_F_SUS)};
+    EnvCoef ka{P(VP_A_D0), P(VP_A_TARGET), P(VP_A_DD0), P(VP_A_RD0), P(VP_A_SUS)};
+    EnvCoef kf{P(VP_F_D0), P(VP_F_TARGET), P(VP_F_DD0), P(VP_F_RD0), P(VP_F_SUS)};
     auto S = [&](int s) -> float & { return state[(size_t) s * V + vv]; };
     float phase = S(VS_PHASE), port_z = S(VS_PORT_Z), low = S(VS_LOW), band = S(VS_BAND), a_x = S(VS_A_X), f_x = S(VS_F_X);
     int a_mode = (int) __float_as_uint(S(VS_A_MODE)), a_gate = (int) __float_as_uint(S(VS_A_GATE));
@@ -101,11 +116,39 @@ __global__ void __launch_bounds__(128) k_voice(float *out, float *partial, float
     __shared__ float ytile[4][32][33];
     // Svf::SetFreq runs every sample and its result is a tolerance tier already (device sine): its two divisions are a
     // multiplication by 1 / (2 sr) and a fast division (<= 2 ulp each)
-    const float inv_sr2 = __frcp_rn(sr2);
+    float inv_sr2 = __frcp_rn(sr2);
     const int lane = threadIdx.x & 31, wic = threadIdx.x >> 5;
     const uint32_t warp_global = v >> 5;
+    uint32_t ev_cur = 0, ev_next = 0xffffffffu;  // this voice's next snapshot and the frame it takes effect at
+    if (EVENTS && live) {
+        uint32_t lo = 0, hi = ev.count;
+        while (lo < hi) {  // first snapshot with voice >= v
+            const uint32_t mid = (lo + hi) >> 1;
+            if (ev.voice[mid] < v) lo = mid + 1;
+            else hi = mid;
+        }
+        ev_cur = lo;
+        if (ev_cur < ev.count && ev.voice[ev_cur] == v) ev_next = ev.frame[ev_cur];
+    }
 
     for (uint32_t n = 0; n < frames; n++) {
+        if (EVENTS) {
+            while (n == ev_next) {  // rare and divergent: a setter ran "between two Process calls"
+                const float *q = ev.par + (size_t) ev_cur * VP_COUNT;
+                freq = q[VP_FREQ]; gate = (int) __float_as_uint(q[VP_GATE]); port_coeff = q[VP_PORT_COEFF]; sr_recip = q[VP_SR_RECIP];
+                cutoff = q[VP_CUTOFF]; f_amount = q[VP_F_AMOUNT]; a_amount = q[VP_A_AMOUNT]; sr2 = q[VP_SR2]; fc_max = q[VP_FC_MAX];
+                damp_a = q[VP_DAMP_A]; drive = q[VP_DRIVE];
+                ka = EnvCoef{q[VP_A_D0], q[VP_A_TARGET], q[VP_A_DD0], q[VP_A_RD0], q[VP_A_SUS]};
+                kf = EnvCoef{q[VP_F_D0], q[VP_F_TARGET], q[VP_F_DD0], q[VP_F_RD0], q[VP_F_SUS]};
+                inv_sr2 = __frcp_rn(sr2);
+                if (__float_as_uint(q[VP_RETRIG]) != 0) {  // NoteOn: Retrigger(hard) on both envelopes
+                    a_mode = 1; a_x = 0.f;
+                    f_mode = 1; f_x = 0.f;
+                }
+                ev_cur++;
+                ev_next = (ev_cur < ev.count && ev.voice[ev_cur] == v) ? ev.frame[ev_cur] : 0xffffffffu;
+            }
+        }
         const float amp_env = env_tick(a_x, a_mode, a_gate, gate, ka);
         const float amp = __fmul_rn(amp_env, a_amount);
         port_z = __fadd_rn(freq, __fmul_rn(port_coeff, __fsub_rn(port_z, freq)));  // Portamento.h:29-32
@@ -201,6 +244,9 @@ struct olb_voice {
         dirty = true;
     }
     float *d_par = nullptr, *d_state = nullptr, *d_partial = nullptr;
+    unsigned char *d_ev = nullptr;  // the device-resident event snapshots of olb_voice_process_events: [E] voice, [E] frame, [E][VP_COUNT]
+    size_t ev_cap = 0;
+    std::vector<unsigned char> ev_stage;
     uint32_t partial_ld = 0;  // frames capacity of the warp-partial buffer
     std::vector<float> stage;
     HostStage host;
@@ -212,6 +258,26 @@ static float vbits_f(uint32_t u) {
     return f;
 }
 
+// One voice's column of the device parameter table: element p goes to out[p * stride].
+static void voice_column(const host::VoiceParams &u, float *out, size_t stride) {
+    out[VP_FREQ * stride] = u.freq;
+    out[VP_GATE * stride] = vbits_f((uint32_t) u.gate);
+    out[VP_RETRIG * stride] = vbits_f(u.retrigger ? 1u : 0u);
+    out[VP_PORT_COEFF * stride] = u.port_coeff;
+    out[VP_SR_RECIP * stride] = 1.0f / u.sample_rate;  // Oscillator::Init
+    out[VP_CUTOFF * stride] = u.filter_cutoff;
+    out[VP_F_AMOUNT * stride] = u.filter_env_amount;
+    out[VP_A_AMOUNT * stride] = u.amp_env_amount;
+    out[VP_SR2 * stride] = u.svf.sr * 2.0f;
+    out[VP_FC_MAX * stride] = u.svf.fc_max;
+    out[VP_DAMP_A * stride] = 2.0f * (1.0f - powf(u.svf.res, 0.25f));
+    out[VP_DRIVE * stride] = u.svf.drive;
+    out[VP_A_D0 * stride] = u.amp_env.a_d0; out[VP_A_TARGET * stride] = u.amp_env.a_target; out[VP_A_DD0 * stride] = u.amp_env.d_d0;
+    out[VP_A_RD0 * stride] = u.amp_env.r_d0; out[VP_A_SUS * stride] = u.amp_env.sus;
+    out[VP_F_D0 * stride] = u.filter_env.a_d0; out[VP_F_TARGET * stride] = u.filter_env.a_target; out[VP_F_DD0 * stride] = u.filter_env.d_d0;
+    out[VP_F_RD0 * stride] = u.filter_env.r_d0; out[VP_F_SUS * stride] = u.filter_env.sus;
+}
+
 // Uploads the columns of the voices whose parameters changed: one 2-D copy of [VP_COUNT][hi - lo] out of the [VP_COUNT][V]
 // table (a NoteOn of one voice is 22 floats, not the bank's 5.8 MB).
 static int voice_upload(olb_voice *h, cudaStream_t st) {
@@ -220,25 +286,7 @@ static int voice_upload(olb_voice *h, cudaStream_t st) {
     const size_t lo = h->dirty_lo, hi = h->dirty_hi;
     h->stage.resize((size_t) VP_COUNT * V);
     float *s = h->stage.data();
-    for (size_t i = lo; i < hi; i++) {
-        const host::VoiceParams &u = h->voices[i];
-        s[VP_FREQ * V + i] = u.freq;
-        s[VP_GATE * V + i] = vbits_f((uint32_t) u.gate);
-        s[VP_RETRIG * V + i] = vbits_f(u.retrigger ? 1u : 0u);
-        s[VP_PORT_COEFF * V + i] = u.port_coeff;
-        s[VP_SR_RECIP * V + i] = 1.0f / u.sample_rate;  // Oscillator::Init
-        s[VP_CUTOFF * V + i] = u.filter_cutoff;
-        s[VP_F_AMOUNT * V + i] = u.filter_env_amount;
-        s[VP_A_AMOUNT * V + i] = u.amp_env_amount;
-        s[VP_SR2 * V + i] = u.svf.sr * 2.0f;
-        s[VP_FC_MAX * V + i] = u.svf.fc_max;
-        s[VP_DAMP_A * V + i] = 2.0f * (1.0f - powf(u.svf.res, 0.25f));
-        s[VP_DRIVE * V + i] = u.svf.drive;
-        s[VP_A_D0 * V + i] = u.amp_env.a_d0; s[VP_A_TARGET * V + i] = u.amp_env.a_target; s[VP_A_DD0 * V + i] = u.amp_env.d_d0;
-        s[VP_A_RD0 * V + i] = u.amp_env.r_d0; s[VP_A_SUS * V + i] = u.amp_env.sus;
-        s[VP_F_D0 * V + i] = u.filter_env.a_d0; s[VP_F_TARGET * V + i] = u.filter_env.a_target; s[VP_F_DD0 * V + i] = u.filter_env.d_d0;
-        s[VP_F_RD0 * V + i] = u.filter_env.r_d0; s[VP_F_SUS * V + i] = u.filter_env.sus;
-    }
+    for (size_t i = lo; i < hi; i++) voice_column(h->voices[i], s + i, V);
     OLB_CUDA(cudaMemcpy2DAsync(h->d_par + lo, V * sizeof(float), s + lo, V * sizeof(float), (hi - lo) * sizeof(float), VP_COUNT,
                                cudaMemcpyHostToDevice, st));
     OLB_CUDA(cudaStreamSynchronize(st));  // the staging table is pageable and reused
@@ -258,7 +306,7 @@ static int voice_init_all(olb_voice *h, float sr) {
 }
 
 static void voice_free(olb_voice *h) {
-    cudaFree(h->d_par); cudaFree(h->d_state); cudaFree(h->d_partial);
+    cudaFree(h->d_par); cudaFree(h->d_state); cudaFree(h->d_partial); cudaFree(h->d_ev);
     h->host.release();
     delete h;
 }
@@ -379,6 +427,42 @@ OLB_API int olb_voice_playing(olb_voice *h, uint32_t first, uint32_t count, uint
     return OLB_OK;
 }
 
+// The launch itself: the parameter table must be current (voice_upload) and `st` entered.  ev: the block's device-resident
+// per-voice events, or count == 0.
+static int voice_launch(olb_voice *h, float *out_dev, float *bus_dev, uint32_t bus_channels, int accumulate, float bus_gain, float *trace_dev,
+                        uint64_t frames, cudaStream_t st, const VoiceEvents &ev) {
+    const uint32_t warps = (h->V + 31) / 32;
+    if (bus_dev && h->partial_ld < frames) {
+        OLB_CUDA(cudaStreamSynchronize(st));
+        cudaFree(h->d_partial);
+        h->d_partial = nullptr;
+        h->partial_ld = 0;
+        const uint32_t ld = (uint32_t) ((frames + 31) / 32 * 32);
+        OLB_CUDA(cudaMalloc(&h->d_partial, (size_t) warps * ld * sizeof(float)));
+        h->partial_ld = ld;
+    }
+    if (ev.count)
+        k_voice<true><<<(h->V + 127) / 128, 128, 0, st>>>(out_dev, bus_dev ? h->d_partial : nullptr, trace_dev, (uint32_t) frames, h->V, h->d_par,
+                                                         h->d_par + (size_t) VP_RETRIG * h->V, h->d_state, h->partial_ld, ev);
+    else
+        k_voice<false><<<(h->V + 127) / 128, 128, 0, st>>>(out_dev, bus_dev ? h->d_partial : nullptr, trace_dev, (uint32_t) frames, h->V, h->d_par,
+                                                          h->d_par + (size_t) VP_RETRIG * h->V, h->d_state, h->partial_ld, ev);
+    OLB_LAUNCHED();
+    if (bus_dev) {
+        k_bus_reduce<<<(unsigned) ((frames + 127) / 128), 128, 0, st>>>(h->d_partial, warps, h->partial_ld, bus_dev, (uint32_t) frames,
+                                                                       bus_channels, accumulate, bus_gain);
+        OLB_LAUNCHED();
+    }
+    return OLB_OK;
+}
+
+// a pending NoteOn retrigger is consumed by the next launch (the kernel clears the device flags): the host clears its own
+static void voice_retrig_consumed(olb_voice *h) {
+    if (!h->retrig_pending) return;
+    for (uint32_t i = h->retrig_lo; i < h->retrig_hi; i++) h->voices[i].retrigger = false;
+    h->retrig_pending = false;
+}
+
 OLB_API int olb_voice_process(olb_voice *h, float *out_dev, float *bus_dev, uint32_t bus_channels, int accumulate, float bus_gain,
                               float *trace_dev, uint64_t frames, void *stream) {
     OLB_ARG(h, "olb_voice_process: NULL handle");
@@ -394,28 +478,9 @@ OLB_API int olb_voice_process(olb_voice *h, float *out_dev, float *bus_dev, uint
         int rc = voice_upload(h, st);
         if (rc) return rc;
     }
-    const uint32_t warps = (h->V + 31) / 32;
-    if (bus_dev && h->partial_ld < frames) {
-        OLB_CUDA(cudaStreamSynchronize(st));
-        cudaFree(h->d_partial);
-        h->d_partial = nullptr;
-        h->partial_ld = 0;
-        const uint32_t ld = (uint32_t) ((frames + 31) / 32 * 32);
-        OLB_CUDA(cudaMalloc(&h->d_partial, (size_t) warps * ld * sizeof(float)));
-        h->partial_ld = ld;
-    }
-    k_voice<<<(h->V + 127) / 128, 128, 0, st>>>(out_dev, bus_dev ? h->d_partial : nullptr, trace_dev, (uint32_t) frames, h->V, h->d_par,
-                                               h->d_par + (size_t) VP_RETRIG * h->V, h->d_state, h->partial_ld);
-    OLB_LAUNCHED();
-    if (bus_dev) {
-        k_bus_reduce<<<(unsigned) ((frames + 127) / 128), 128, 0, st>>>(h->d_partial, warps, h->partial_ld, bus_dev, (uint32_t) frames,
-                                                                       bus_channels, accumulate, bus_gain);
-        OLB_LAUNCHED();
-    }
-    if (h->retrig_pending) {  // the retrigger was consumed by this launch: the kernel cleared the device flags, the host clears its own
-        for (uint32_t i = h->retrig_lo; i < h->retrig_hi; i++) h->voices[i].retrigger = false;
-        h->retrig_pending = false;
-    }
+    int rc = voice_launch(h, out_dev, bus_dev, bus_channels, accumulate, bus_gain, trace_dev, frames, st, VoiceEvents{nullptr, nullptr, nullptr, 0});
+    if (rc) return rc;
+    voice_retrig_consumed(h);
     return OLB_OK;
 }
 
@@ -495,48 +560,137 @@ OLB_API int olb_voice_process_events(olb_voice *h, const olb_voice_event *events
         OLB_ARG(events[e].voice < 0 || (uint32_t) events[e].voice < h->V, "olb_voice_process_events: event %u addresses voice %d of %u", e,
                 events[e].voice, h->V);
     }
+    DeviceGuard g(h->device);
+    cudaStream_t st = (cudaStream_t) stream;
+    // One event, applied to the host-side members exactly as the public setters do.  Returns the voice it addressed, -1 for an
+    // event that was dropped (every voice busy / no voice plays the note), -2 for a fan-out to every voice.
+    auto apply = [&](const olb_voice_event &ev, int32_t &voice_out) -> int {
+        const uint8_t note = (uint8_t) ev.a;
+        int32_t voice = ev.voice;
+        switch (ev.kind) {
+            case OLB_EV_NOTE_ON:
+                if (voice < 0)
+                    for (uint32_t v = 0; v < h->V && voice < 0; v++)
+                        if (!h->voices[v].playing) voice = (int32_t) v;
+                if (voice >= 0) h->voices[voice].NoteOn(note);  // every voice busy: dropped, as in the reference
+                break;
+            case OLB_EV_NOTE_OFF:
+                if (voice < 0)
+                    for (uint32_t v = 0; v < h->V && voice < 0; v++)
+                        if (h->voices[v].playing == note) voice = (int32_t) v;
+                if (voice >= 0) h->voices[voice].NoteOff();
+                break;
+            case OLB_EV_MIDI_CC:
+                if (voice < 0) {
+                    for (auto &u : h->voices) u.UpdateMidiControl((uint8_t) ev.a, (uint8_t) ev.v);
+                    voice = -2;
+                } else {
+                    h->voices[voice].UpdateMidiControl((uint8_t) ev.a, (uint8_t) ev.v);
+                }
+                break;
+            case OLB_EV_HW_CC:
+                if (voice < 0) {
+                    for (auto &u : h->voices) u.UpdateHardwareControl((uint8_t) ev.a, ev.v);
+                    voice = -2;
+                } else {
+                    h->voices[voice].UpdateHardwareControl((uint8_t) ev.a, ev.v);
+                }
+                break;
+            default:
+                set_error("olb_voice_process_events: unknown event kind %u", ev.kind);
+                return OLB_E_ARG;
+        }
+        voice_out = voice;
+        return OLB_OK;
+    };
+    auto fans_out = [](const olb_voice_event &ev) { return ev.voice < 0 && (ev.kind == OLB_EV_MIDI_CC || ev.kind == OLB_EV_HW_CC); };
+
+    // The block is cut only where an event addresses EVERY voice (a Polyvoice-wide control change: the whole table changes);
+    // events that address one voice -- notes through Polyvoice's allocation, per-voice controls -- ride along with the launch.
     uint64_t pos = 0;
     uint32_t e = 0;
     while (pos < frames || e < n_events) {
+        // (1) events AT the segment's first frame change the table the launch starts from
         for (; e < n_events && events[e].frame == pos; e++) {
-            const olb_voice_event &ev = events[e];
-            const uint8_t note = (uint8_t) ev.a;
-            int rc = OLB_OK;
-            int32_t voice = ev.voice;
-            switch (ev.kind) {
-                case OLB_EV_NOTE_ON:
-                    if (voice < 0)
-                        for (uint32_t v = 0; v < h->V && voice < 0; v++)
-                            if (!h->voices[v].playing) voice = (int32_t) v;
-                    if (voice >= 0) rc = olb_voice_note_on(h, (uint32_t) voice, 1, &note, 0, (uint8_t) ev.v);
-                    break;  // every voice busy: dropped, as in the reference
-                case OLB_EV_NOTE_OFF:
-                    if (voice < 0)
-                        for (uint32_t v = 0; v < h->V && voice < 0; v++)
-                            if (h->voices[v].playing == note) voice = (int32_t) v;
-                    if (voice >= 0) rc = olb_voice_note_off(h, (uint32_t) voice, 1);
-                    break;
-                case OLB_EV_MIDI_CC:
-                    rc = voice < 0 ? olb_voice_update_midi(h, 0, h->V, (uint8_t) ev.a, (uint8_t) ev.v)
-                                   : olb_voice_update_midi(h, (uint32_t) voice, 1, (uint8_t) ev.a, (uint8_t) ev.v);
-                    break;
-                case OLB_EV_HW_CC:
-                    rc = voice < 0 ? olb_voice_update_hw(h, 0, h->V, (uint8_t) ev.a, &ev.v, 0)
-                                   : olb_voice_update_hw(h, (uint32_t) voice, 1, (uint8_t) ev.a, &ev.v, 0);
-                    break;
-                default:
-                    set_error("olb_voice_process_events: unknown event kind %u", ev.kind);
-                    return OLB_E_ARG;
-            }
+            int32_t voice;
+            int rc = apply(events[e], voice);
             if (rc) return rc;
+            if (voice == -2) {
+                h->mark(0, h->V);
+            } else if (voice >= 0) {
+                h->mark((uint32_t) voice, (uint32_t) voice + 1);
+                if (events[e].kind == OLB_EV_NOTE_ON) {
+                    if (!h->retrig_pending) { h->retrig_lo = (uint32_t) voice; h->retrig_hi = (uint32_t) voice + 1; }
+                    else { h->retrig_lo = std::min(h->retrig_lo, (uint32_t) voice); h->retrig_hi = std::max(h->retrig_hi, (uint32_t) voice + 1); }
+                    h->retrig_pending = true;
+                }
+            }
         }
         if (pos >= frames) break;
-        const uint64_t next = e < n_events ? events[e].frame : frames;
-        const uint64_t n = next - pos;
-        int rc = olb_voice_process(h, out_dev ? out_dev + pos * h->V : nullptr, bus_dev ? bus_dev + pos * bus_channels : nullptr, bus_channels,
-                                   accumulate, bus_gain, nullptr, n, stream);
+        uint64_t seg_end = frames;
+        uint32_t e_end = e;
+        for (; e_end < n_events; e_end++)
+            if (fans_out(events[e_end])) {
+                seg_end = events[e_end].frame;
+                break;
+            }
+        if (e_end == n_events) seg_end = frames;
+        // (2) the table as of `pos` goes to the device now: the members are about to move on
+        OLB_CUDA(h->order.enter(st));
+        if (h->dirty) {
+            int rc = voice_upload(h, st);
+            if (rc) return rc;
+        }
+        voice_retrig_consumed(h);  // the launch below consumes the device flags
+        // (3) the segment's per-voice events: apply in order, snapshot the addressed voice's column after each
+        struct Snap { uint32_t voice, frame, order; };
+        std::vector<Snap> snaps;
+        std::vector<float> cols;
+        uint32_t lo = h->V, hi = 0;
+        for (; e < e_end && events[e].frame < seg_end; e++) {  // an event AT seg_end starts the next segment (or ends the block)
+            int32_t voice;
+            int rc = apply(events[e], voice);
+            if (rc) return rc;
+            if (voice < 0) continue;  // dropped
+            snaps.push_back(Snap{(uint32_t) voice, (uint32_t) (events[e].frame - pos), (uint32_t) snaps.size()});
+            cols.resize(cols.size() + VP_COUNT);
+            voice_column(h->voices[voice], cols.data() + cols.size() - VP_COUNT, 1);
+            h->voices[voice].retrigger = false;  // carried by this snapshot alone
+            lo = std::min(lo, (uint32_t) voice);
+            hi = std::max(hi, (uint32_t) voice + 1);
+        }
+        VoiceEvents dev{nullptr, nullptr, nullptr, 0};
+        if (!snaps.empty()) {
+            std::stable_sort(snaps.begin(), snaps.end(), [](const Snap &a, const Snap &b) { return a.voice < b.voice; });
+            const size_t E = snaps.size(), bytes = E * (2 * sizeof(uint32_t) + VP_COUNT * sizeof(float));
+            h->ev_stage.resize(bytes);
+            uint32_t *hv = reinterpret_cast<uint32_t *>(h->ev_stage.data()), *hf = hv + E;
+            float *hp = reinterpret_cast<float *>(hf + E);
+            for (size_t i = 0; i < E; i++) {
+                hv[i] = snaps[i].voice;
+                hf[i] = snaps[i].frame;
+                memcpy(hp + i * VP_COUNT, cols.data() + (size_t) snaps[i].order * VP_COUNT, VP_COUNT * sizeof(float));
+            }
+            if (h->ev_cap < bytes) {
+                OLB_CUDA(cudaStreamSynchronize(st));
+                cudaFree(h->d_ev);
+                h->d_ev = nullptr;
+                h->ev_cap = 0;
+                OLB_CUDA(cudaMalloc(&h->d_ev, bytes * 2));
+                h->ev_cap = bytes * 2;
+            }
+            OLB_CUDA(cudaMemcpyAsync(h->d_ev, h->ev_stage.data(), bytes, cudaMemcpyHostToDevice, st));
+            OLB_CUDA(cudaStreamSynchronize(st));  // pageable staging, reused by the next segment
+            const uint32_t *dv = reinterpret_cast<const uint32_t *>(h->d_ev);
+            dev = VoiceEvents{dv, dv + E, reinterpret_cast<const float *>(dv + 2 * E), (uint32_t) E};
+        }
+        // (4) one launch for the segment
+        const uint64_t n = seg_end - pos;
+        int rc = voice_launch(h, out_dev ? out_dev + pos * h->V : nullptr, bus_dev ? bus_dev + pos * bus_channels : nullptr, bus_channels, accumulate,
+                              bus_gain, nullptr, n, st, dev);
         if (rc) return rc;
-        pos = next;
+        if (lo < hi) h->mark(lo, hi);  // the table on the device is the segment's FIRST frame's: bring it up to date at the next call
+        pos = seg_end;
     }
     return OLB_OK;
 }

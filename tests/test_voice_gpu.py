@@ -200,6 +200,37 @@ def test_dense_event_list_on_a_wide_bank(orc):
     bank.close()
 
 
+def test_event_list_mixed_with_fan_out_controls_and_same_frame_events(orc):
+    """Per-voice events ride along with the launch, a CC that fans out to every voice cuts the block, several events of one
+    voice may share a frame (NoteOn + CC; NoteOff + NoteOn), an event may sit exactly on a cut or on the block's end, and the
+    whole script may be split over two calls: all against the oracle replaying each voice's own script."""
+    from ol_dsp_b200.voice import process_events
+    V, frames = 96, 6000
+    per_voice = {3: [(0, loader.EV_NOTE_ON, 50, 100), (700, loader.EV_MIDI_CC, 41, 90), (700, loader.EV_NOTE_OFF, 50, 0), (700, loader.EV_NOTE_ON, 62, 100)],
+                 40: [(1, loader.EV_NOTE_ON, 45, 100), (2000, loader.EV_HW_CC, 42, 0.7), (4999, loader.EV_NOTE_OFF, 45, 0)],
+                 95: [(2000, loader.EV_NOTE_ON, 70, 100), (2000, loader.EV_MIDI_CC, 75, 20), (3000, loader.EV_NOTE_OFF, 70, 0), (6000, loader.EV_NOTE_ON, 71, 100)]}
+    fan = [(2000, loader.EV_MIDI_CC, 73, 30), (4000, loader.EV_HW_CC, 41, 0.4)]  # voice < 0: every voice
+    ev = [(f, k, a, v, voice) for voice, lst in per_voice.items() for (f, k, a, v) in lst] + [(f, k, a, v, -1) for (f, k, a, v) in fan]
+    ev.sort(key=lambda t: t[0])  # stable: list order within a frame is kept (per-voice events before the fan-out ones)
+    bank = VoiceBank(V)
+    out = torch.empty((frames, V), dtype=torch.float32, device="cuda")
+    cut = 2500
+    first = [t for t in ev if t[0] < cut]
+    second = [(t[0] - cut,) + t[1:] for t in ev if t[0] >= cut]
+    process_events(bank, first, cut, out_ptr=out.data_ptr())
+    process_events(bank, second, frames - cut, out_ptr=out[cut:].data_ptr())
+    torch.cuda.synchronize()
+    y = out.cpu().numpy()
+    for voice, lst in per_voice.items():
+        script = sorted([e for e in lst if e[0] < frames] + fan, key=lambda t: t[0])
+        want = orc.voice(frames, ev=script)
+        assert np.abs(y[:, voice] - want).max() <= TOL, (voice, float(np.abs(y[:, voice] - want).max()))
+        assert np.abs(want).max() > 0.01
+    assert not y[:, 7].any()
+    assert list(bank.Playing()[[3, 40, 95]]) == [62, 0, 71]
+    bank.close()
+
+
 def test_voicemap_against_the_reference_golden():
     """ol::synth::VoiceMap over a bank (SURVEY.md section 8f item 2): tests/golden/synth.npz 'voicemap' is the reference's own
     VoiceMap<1> over six SynthVoices (pads on five notes, channel 3 set twice, unmapped notes / channels ignored)."""
