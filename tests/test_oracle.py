@@ -329,6 +329,9 @@ def test_chorus_restatement_properties(orc):
     assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
     imp = np.zeros(4000, np.float32)
     imp[0] = 1.0
-    w = orc.chorus(imp, mix=1.0, depth=1.0, rate=0.0, phase=0.0)   # LFO starts at cos(0) = 1 -> delay ~ 2 d = 1 152 samples
+    w = orc.chorus(imp, mix=1.0, depth=1.0, rate=0.0, phase=0.0, pitch_stage=False)  # LFO starts at cos(0) = 1 -> delay ~ 2 d = 1 152 samples
     first = int(np.nonzero(w)[0][0])
     assert 1140 <= first <= 1153
+    # with the gen~ pitch shifter in front (pitch 0: the input half a 10 ms window late) the same impulse arrives 240 frames later
+    w = orc.chorus(imp, mix=1.0, depth=1.0, rate=0.0, phase=0.0)
+    assert int(np.nonzero(w)[0][0]) == first + 240
