@@ -125,6 +125,7 @@ public:
     int status() const { return status_; }
     std::string error() const { return olb_last_error(); }
     const char *LastKernel() { return olb_fx2_last_kernel(h_); }
+    olb_fx2 *handle() { return h_; }
 
 private:
     InitStatus note(int rc) {

@@ -18,7 +18,9 @@
 #include <vector>
 
 #include "ol_gpu/BiquadBank.hpp"
+#include "ol_gpu/ChorusBank.hpp"
 #include "ol_gpu/FxBank.hpp"
+#include "ol_gpu/VoiceBank.hpp"
 
 int main(int argc, char **argv) {
     const uint32_t C = argc > 1 ? (uint32_t) atoi(argv[1]) : 4096;
@@ -38,6 +40,11 @@ int main(int argc, char **argv) {
     bank.SetCoeffs(0, C, A.data());
     ol::gpu::FxBank<OLB_FX_FILTER> fx(256);
     if (fx.Init(48000.f) != ol::gpu::Ok) return 2;
+    // the banks of round 2 under the same race: a stereo rack, a chorus (with its pitch shifter), a voice bank fed event lists
+    ol::gpu::FxRack2Bank rack2(64);
+    ol::gpu::ChorusBank chorus(64);
+    ol::gpu::VoiceBank voices(128);
+    if (rack2.Init(48000.f) != ol::gpu::Ok || chorus.Init(48000.f) != ol::gpu::Ok || voices.Init(48000.f) != ol::gpu::Ok) return 2;
 
     std::atomic<bool> stop{false};
     std::atomic<long> flips{0};
@@ -50,17 +57,37 @@ int main(int argc, char **argv) {
             a = !a;
             const float cutoff = 0.25f + 0.5f * (float) (flips.load() & 1);
             if (rc == OLB_OK) rc = olb_fx_update_hw(fx.handle(), 0, 256, 41 /* CC_FILTER_CUTOFF */, &cutoff, 0);
+            if (rc == OLB_OK) rc = olb_fx2_update_midi(rack2.handle(), 0, 64, 35 /* CC_DELAY_TIME */, (uint8_t) (20 + (flips.load() & 63)));
+            if (rc == OLB_OK) rc = olb_chorus_set_param(chorus.handle(), 0, 64, OLB_CHORUS_PITCH, (float) (flips.load() & 3));
+            if (rc == OLB_OK) rc = olb_chorus_set_param(chorus.handle(), 0, 64, OLB_CHORUS_DEPTH, cutoff);
+            if (rc == OLB_OK) rc = olb_voice_update_midi(voices.handle(), 0, 128, 41 /* CC_FILTER_CUTOFF */, (uint8_t) (40 + (flips.load() & 63)));
             if (rc != OLB_OK) ctl_status = rc;
             flips.fetch_add(1);
         }
     });
 
     std::vector<float> x((size_t) F * C, 1.0f), y((size_t) F * C), fx_in((size_t) F * 256, 0.1f), fx_out((size_t) F * 256);
+    std::vector<float> st_in((size_t) F * 128, 0.1f), st_out((size_t) F * 128), ch_out((size_t) F * 64);
     long torn = 0, seen_a = 0, seen_b = 0;
     for (int b = 0; b < blocks; b++) {
         bank.ProcessBlock(x.data(), y.data(), F);
         fx.ProcessBlock(fx_in.data(), fx_out.data(), F);
-        if (bank.status() != OLB_OK || fx.status() != OLB_OK) {
+        rack2.ProcessBlock(st_in.data(), st_out.data(), F);
+        chorus.ProcessBlock(st_in.data(), ch_out.data(), F);
+        {   // a NoteOn / NoteOff pair on rotating voices, sample-accurate, applied on the device
+            const uint32_t vv = (uint32_t) b % 128u;
+            olb_voice_event ev[2] = {{(uint32_t) (F / 4), OLB_EV_NOTE_ON, 48u + vv % 24u, 100.f, (int32_t) vv},
+                                     {(uint32_t) (3 * F / 4), OLB_EV_NOTE_OFF, 48u + vv % 24u, 0.f, (int32_t) vv}};
+            // (device buffers only on this entry point; none given: the voices advance, which is all the race needs)
+            const int rc = olb_voice_process_events(voices.handle(), ev, 2, nullptr, nullptr, 1, 0, 1.0f, F, nullptr);
+            if (rc != OLB_OK) {
+                fprintf(stderr, "voices: %s\n", olb_last_error());
+                stop = true;
+                control.join();
+                return 3;
+            }
+        }
+        if (bank.status() != OLB_OK || fx.status() != OLB_OK || rack2.status() != OLB_OK || chorus.status() != OLB_OK) {
             fprintf(stderr, "process: %s\n", bank.error().c_str());
             stop = true;
             control.join();
@@ -79,6 +106,10 @@ int main(int argc, char **argv) {
         (y[0] == 1.0f ? seen_a : seen_b)++;
         for (size_t i = 0; i < fx_out.size(); i++)
             if (!std::isfinite(fx_out[i])) torn++;
+        for (size_t i = 0; i < st_out.size(); i++)
+            if (!std::isfinite(st_out[i])) torn++;
+        for (size_t i = 0; i < ch_out.size(); i++)
+            if (!std::isfinite(ch_out[i])) torn++;
     }
     stop = true;
     control.join();

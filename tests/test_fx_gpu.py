@@ -341,3 +341,19 @@ def test_stereo_rack_wide_bank_channel0_is_the_mono_rack(orc):
         assert np.array_equal(bits(y[:, i, :]), bits(w)), i
     b1.close()
     b2.close()
+
+
+@pytest.mark.parametrize("kind", [fx.FILTER, fx.DELAY, fx.RACK])
+def test_stereo_bank_with_an_odd_instance_count(orc, kind):
+    """7 stereo instances: the mono bank inside cannot use its tensor maps (instances % 4 != 0) and takes the plain-load kernel;
+    short and long delays mixed, so DelayFx<2>'s channel 1 walks time."""
+    I, T = 7, 5000
+    x = orc.noise(14, 0, 2 * I, 0, T, 0.5).reshape(T, I, 2)
+    evs = [[(0, loader.EV_HW_CC, 35, [0.0004, 0.3, 0.9, 0.05, 0.5, 0.0, 1.0][i]), (0, loader.EV_MIDI_CC, 36, 60 + 5 * i), (2000, loader.EV_MIDI_CC, 45, 30 + 10 * i)]
+           for i in range(I)]
+    prefill = 0.25 if kind == fx.FILTER else 0.0
+    y, _ = run_bank2(kind, x, evs, prefill=prefill)
+    for i in range(I):
+        kw = {"prefill": prefill} if kind == fx.FILTER else {}
+        w = getattr(orc, NAMES[kind])(np.ascontiguousarray(x[:, i, :]), 48000.0, evs[i], **kw)
+        assert np.array_equal(bits(y[:, i, :]), bits(w)), (kind, i)
