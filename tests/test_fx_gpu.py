@@ -357,3 +357,20 @@ def test_stereo_bank_with_an_odd_instance_count(orc, kind):
         kw = {"prefill": prefill} if kind == fx.FILTER else {}
         w = getattr(orc, NAMES[kind])(np.ascontiguousarray(x[:, i, :]), 48000.0, evs[i], **kw)
         assert np.array_equal(bits(y[:, i, :]), bits(w)), (kind, i)
+
+
+@pytest.mark.parametrize("kind", [fx.FILTER, fx.DELAY, fx.REVERB, fx.RACK])
+def test_cc_maps_sweep_every_controller_number(orc, kind):
+    """Row a10 on the library's side: libolbank restates the CC -> parameter maps in csrc/host_params.h.  Instance i of a
+    128-instance bank receives controller number i -- mapped or not -- with a spread of MIDI and hardware values; every instance
+    against the oracle (which tests/test_oracle.py pins to the reference's own classes over the same sweep)."""
+    T = 400
+    x1 = orc.noise(61, 0, 1, 0, T, 0.5)
+    x = np.ascontiguousarray(np.repeat(x1, 128, axis=1))
+    for evk, values in ((loader.EV_MIDI_CC, (0, 1, 17, 64, 100, 127)), (loader.EV_HW_CC, (0.0, 0.013, 0.5, 1.0))):
+        for v in values:
+            evs = [[(0, loader.EV_MIDI_CC, 35, 3), (100, evk, cc, v)] for cc in range(128)]
+            y = run_bank(kind, x, evs)
+            for cc in range(128):
+                want = getattr(orc, NAMES[kind])(x1, 48000.0, evs[cc])
+                assert np.array_equal(bits(y[:, cc]), bits(want[:, 0])), (NAMES[kind], cc, evk, v)

@@ -79,6 +79,45 @@ def test_fx_stereo_templates_match_reference_golden(orc, name):
         assert not np.array_equal(bits(ys[:, 1]), bits(y1[:, 0]))
 
 
+MIDI_VALUES = (0, 1, 17, 64, 100, 127)
+HW_VALUES = (0.0, 0.013, 0.5, 1.0)
+
+
+@pytest.mark.parametrize("name", ["filterfx", "delayfx", "reverbfx", "fxrack"])
+def test_cc_maps_sweep_against_the_compiled_reference(orc, ref, name):
+    """Row a10: the CC -> parameter maps (Fx.h:116-164, 219-266, 313-391, 443-491; ol::core::scale, ol_corelib.h:27-44) are
+    RESTATED in the oracle, not included from the reference.  So that the restatement cannot drift, EVERY controller number
+    0..127 -- mapped or not: an unmapped CC must be ignored the same way -- is applied with a spread of MIDI and hardware
+    values and the unit's output compared bit for bit with the reference's own class (compiled from where it lies)."""
+    x = orc.noise(61, 0, 1, 0, 400, 0.5)
+    checked = 0
+    for cc in range(128):
+        for kind, values in ((loader.EV_MIDI_CC, MIDI_VALUES), (loader.EV_HW_CC, HW_VALUES)):
+            for v in values:
+                ev = [(0, loader.EV_MIDI_CC, 35, 3), (100, kind, cc, v)]  # a short delay first, so that delay-path controls are heard
+                a, b = getattr(orc, name)(x, 48000.0, ev), getattr(ref, name)(x, 48000.0, ev)
+                assert np.array_equal(bits(a), bits(b)), (name, cc, kind, v)
+                checked += 1
+    assert checked == 128 * (len(MIDI_VALUES) + len(HW_VALUES))
+    # and the sweep is not vacuous: the unit's own controllers change its output, the others do not
+    heard = [cc for cc in range(128)
+             if not np.array_equal(getattr(orc, name)(x, 48000.0, [(0, loader.EV_MIDI_CC, 35, 3), (100, loader.EV_MIDI_CC, cc, 0)]),
+                                   getattr(orc, name)(x, 48000.0, [(0, loader.EV_MIDI_CC, 35, 3), (100, loader.EV_MIDI_CC, cc, 127)]))]
+    expect = {"filterfx": {41, 42}, "delayfx": {39}, "reverbfx": {34}, "fxrack": {7, 34, 39, 45, 46}}[name]  # cutoff / resonance, balances, volume
+    assert expect <= set(heard) and len(heard) <= 40, (name, heard)
+
+
+def test_voice_cc_map_sweep_against_the_compiled_reference(orc, ref):
+    """The same for SynthVoice's maps (SynthVoice.h:101-229): every controller number, MIDI and hardware, before and during a
+    note; the oracle's voice is bit-equal to the reference's (libm transcendentals on both sides)."""
+    for cc in range(128):
+        for kind, values in ((loader.EV_MIDI_CC, (0, 33, 127)), (loader.EV_HW_CC, (0.0, 0.37, 1.0))):
+            for v in values:
+                ev = [(0, kind, cc, v), (5, loader.EV_NOTE_ON, 57, 100), (300, kind, cc, values[1]), (500, loader.EV_NOTE_OFF, 57, 0)]
+                a, b = orc.voice(700, ev=ev), ref.voice(700, ev=ev)
+                assert np.array_equal(bits(a), bits(b)), (cc, kind, v)
+
+
 def test_pitch_shifter_restatement_properties(orc):
     """pitchshift.gendsp restated (no reference code, no golden: PARITY UNPINNED): at pitch 0 the phasor rests, tap 2 is the
     input half a window late at weight cos(0) = 1 and tap 1 carries weight cos(-pi/2) ~ -4e-8; the stage is linear in its

@@ -231,6 +231,27 @@ def test_event_list_mixed_with_fan_out_controls_and_same_frame_events(orc):
     bank.close()
 
 
+def test_cc_maps_sweep_every_controller_number(orc):
+    """SynthVoice's CC maps as restated in csrc/host_params.h: voice i of a 128-voice bank receives controller number i (MIDI and
+    hardware values, before and during a note); every voice against the oracle, which tests/test_oracle.py pins to the
+    reference's own SynthVoice over the same sweep."""
+    from ol_dsp_b200.voice import process_events
+    frames = 700
+    for kind, values in ((loader.EV_MIDI_CC, (0, 33, 127)), (loader.EV_HW_CC, (0.0, 0.37, 1.0))):
+        for v in values:
+            ev = [(0, kind, cc, v, cc) for cc in range(128)] + [(5, loader.EV_NOTE_ON, 57, 100, cc) for cc in range(128)]
+            ev += [(300, kind, cc, values[1], cc) for cc in range(128)] + [(500, loader.EV_NOTE_OFF, 57, 0, cc) for cc in range(128)]
+            bank = VoiceBank(128)
+            out = torch.empty((frames, 128), dtype=torch.float32, device="cuda")
+            process_events(bank, ev, frames, out_ptr=out.data_ptr())
+            torch.cuda.synchronize()
+            y = out.cpu().numpy()
+            bank.close()
+            for cc in range(128):
+                want = orc.voice(frames, ev=[(0, kind, cc, v), (5, loader.EV_NOTE_ON, 57, 100), (300, kind, cc, values[1]), (500, loader.EV_NOTE_OFF, 57, 0)])
+                assert np.abs(y[:, cc] - want).max() <= TOL, (cc, kind, v, float(np.abs(y[:, cc] - want).max()))
+
+
 def test_voicemap_against_the_reference_golden():
     """ol::synth::VoiceMap over a bank (SURVEY.md section 8f item 2): tests/golden/synth.npz 'voicemap' is the reference's own
     VoiceMap<1> over six SynthVoices (pads on five notes, channel 3 set twice, unmapped notes / channels ignored)."""
