@@ -1,0 +1,24 @@
+#!/bin/bash
+# round 2, run 41 (8-GPU box; run 29 again at HEAD): bench.py at N = 1, 2, 4, 8 (weak value, strong record, voices with the NCCL bus reduce, e2e), comm test
+set -u
+O=gpurun_out/r2_run41; mkdir -p $O
+nvidia-smi -L | head -8
+timeout 600 python -m pytest tests/test_comm_gpu.py tests/test_voice_gpu.py -m gpu -x -q > $O/pytest_comm.log 2>&1; echo "comm pytest rc=$?"; tail -3 $O/pytest_comm.log
+python bench.py --steps 50 --no-cpu-baseline > $O/bench_n1.json 2> $O/bench.err; echo "n1 rc=$?"
+p=29600
+for n in 2 4 8; do
+  p=$((p+1))
+  timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port $p bench.py --gpus $n --steps 50 > $O/bench_n$n.json 2>> $O/bench.err; echo "n$n rc=$?"
+done
+python - <<'PY'
+import json
+base=None
+for n in (1,2,4,8):
+    try: d=json.load(open(f'gpurun_out/r2_run41/bench_n{n}.json'))
+    except Exception as e: print(n, 'missing', e); continue
+    if n==1: base=d
+    s=d.get('strong',{}); v=d.get('voices',{}); e=d.get('e2e',{})
+    print(f"N={n} value {d['value']:.4e} ({d['value']/base['value']:.2f}x) strong {s.get('value',0):.4e} ({s.get('value',0)/base['value']:.2f}x, {s.get('kernel')}, frac {s.get('roofline_frac',0):.3f}) "
+          f"voices {v.get('value',0):.4e} ({v.get('value',0)/base['voices']['value']:.2f}x) e2e {e.get('value',0):.3e} pcie_frac {e.get('pcie_frac')}")
+PY
+tail -3 $O/bench.err
