@@ -46,6 +46,8 @@ public:
     // Update(): the reference pushes cached members to its primitives here (Fx.h:110-114); the bank does that at the
     // next Process call, so this is a no-op kept for source compatibility.
     void Update() {}
+    // Not in the reference: OLB_MODE_EXACT (default, bit-exact against it) or OLB_MODE_FMA (fused, olbank.h); after Init.
+    void SetMode(int mode) { note(olb_fx_set_mode(h_, mode)); }
     // UpdateMidiControl(control, value 0..127) -- every instance, or a range
     void UpdateMidiControl(uint8_t control, uint8_t value) { note(olb_fx_update_midi(h_, 0, instances_, control, value)); }
     void UpdateMidiControl(uint8_t control, uint8_t value, uint32_t first, uint32_t count) {
@@ -107,6 +109,7 @@ public:
         return note(olb_fx2_init(h_, sample_rate));
     }
     void Update() {}
+    void SetMode(int mode) { note(olb_fx2_set_mode(h_, mode)); }
     void UpdateMidiControl(uint8_t control, uint8_t value) { note(olb_fx2_update_midi(h_, 0, instances_, control, value)); }
     void UpdateMidiControl(uint8_t control, uint8_t value, uint32_t first, uint32_t count) {
         note(olb_fx2_update_midi(h_, first, count, control, value));

@@ -154,6 +154,21 @@ int olb_fx_update_midi(olb_fx *h, uint32_t first, uint32_t count, uint8_t contro
 /* UpdateHardwareControl(control, value 0..1), one value per instance at values_host[i * stride] (stride 0 = one value
  * for all)  (Fx.h:141-164, 219-237, 353-391, 470-492) */
 int olb_fx_update_hw(olb_fx *h, uint32_t first, uint32_t count, uint8_t control, const float *values_host, uint32_t stride);
+/* Arithmetic tier.  OLB_MODE_EXACT (the default) rounds every product and sum separately, in the reference's order: bit-exact
+ * against the reference built with -ffp-contract=off (oracle/Makefile).  OLB_MODE_FMA is the same signal flow with the
+ * contractions a compiler makes under -ffp-contract=fast, written out so that they are defined:
+ *     svf half-step   notch = fma(-damp, band, in); low = fma(freq, band, low); high = notch - low;
+ *                     band  = fma(-(drive*band)*band, band, fma(freq, high, band))
+ *     svf output      out   = fma(0.5, pick(second half), 0.5 * pick(first half))
+ *     delay line      read  = fma(b - a, frac, a);  write = fma(feedback, read, in)
+ *     dry/wet mixes   out   = fma(wet, balance, dry * (1 - balance))
+ * bit-exact against the oracle's restatement of exactly those forms (orc_fx_set_mode), and within 1e-4 of max(1, peak) of
+ * the EXACT tier over 10 s of 0.9-scale noise at five corners of the CC maps (tests/test_fx_gpu.py; measured on the device:
+ * 4.3e-7 wherever the output stays below 16, 2.2e-5 with every controller at 127, where the feedback loop peaks at 4 242).
+ * It is the throughput tier: FilterFx's EXACT kernel runs at the FP32 issue rate of its 100 separately rounded operations per four
+ * frames.  State carries over a switch.  OLB_FX_RACK_PLATE has OLB_MODE_EXACT only; any other mode
+ * value is OLB_E_ARG. */
+int olb_fx_set_mode(olb_fx *h, int mode);
 /* Block form of "for each frame: Process(frame_in, frame_out)"; in_dev == out_dev allowed. */
 int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream);
 /* Diagnostics: which kernel the last process call launched ("k_fx_split", "k_fx_tma", "k_fx_pf", "k_fx"). */
@@ -178,6 +193,8 @@ int olb_fx2_destroy(olb_fx2 *h);
 int olb_fx2_init(olb_fx2 *h, float sample_rate);
 int olb_fx2_update_midi(olb_fx2 *h, uint32_t first, uint32_t count, uint8_t control, uint8_t value);
 int olb_fx2_update_hw(olb_fx2 *h, uint32_t first, uint32_t count, uint8_t control, const float *values_host, uint32_t stride);
+/* Both channels in the tier (olb_fx_set_mode). */
+int olb_fx2_set_mode(olb_fx2 *h, int mode);
 int olb_fx2_process(olb_fx2 *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream);
 /* "k_fx2_put" (merge; DelayFx<2>'s channel 1 time-parallel) or "k_fx2_delay1" (channel 1 walking time: delays shorter than a cut) */
 const char *olb_fx2_last_kernel(olb_fx2 *h);

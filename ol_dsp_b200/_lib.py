@@ -69,6 +69,7 @@ def lib():
         "olb_fx_create": ([i32, i32, u32, f32, C.POINTER(vp)], i32),
         "olb_fx_destroy": ([vp], i32),
         "olb_fx_init": ([vp, f32], i32),
+        "olb_fx_set_mode": ([vp, i32], i32),
         "olb_fx_update_midi": ([vp, u32, u32, C.c_uint8, C.c_uint8], i32),
         "olb_fx_update_hw": ([vp, u32, u32, C.c_uint8, _F, u32], i32),
         "olb_fx_process": ([vp, vp, vp, u64, vp], i32),
@@ -77,6 +78,7 @@ def lib():
         "olb_fx2_create": ([i32, i32, u32, f32, C.POINTER(vp)], i32),
         "olb_fx2_destroy": ([vp], i32),
         "olb_fx2_init": ([vp, f32], i32),
+        "olb_fx2_set_mode": ([vp, i32], i32),
         "olb_fx2_update_midi": ([vp, u32, u32, C.c_uint8, C.c_uint8], i32),
         "olb_fx2_update_hw": ([vp, u32, u32, C.c_uint8, _F, u32], i32),
         "olb_fx2_process": ([vp, vp, vp, u64, vp], i32),

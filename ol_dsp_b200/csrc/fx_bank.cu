@@ -34,6 +34,15 @@ struct SvfCoef {
     int type;
 };
 
+// The arithmetic tier rides in the KIND template parameter: KIND | kFxFastBit = the FUSED tier of that kind
+// (olb_fx_set_mode(OLB_MODE_FAST); specification: oracle/olb_oracle.cpp svf_half / ring_read / delay_tick with g_fx_fast): the
+// same formulas with their multiply-adds fused -- the SVF's recurrence goes from 6 dependent operations per pass to 4, its
+// operation count from 11 to 7 -- a tolerance tier (north_star: fused variants state their tolerance; measured in the tests).
+// The default is the reference's separately rounded arithmetic.
+constexpr int kFxFastBit = 8;
+#define OLB_K(KIND) ((KIND) & 7)
+#define OLB_F(KIND) (((KIND) & olb::kFxFastBit) != 0)
+
 // daisysp::Svf::Process, two identical passes; returns the output FilterFx::Process selects (Fx.h:88-108).
 // Branch-free: the per-lane filter type picks its tap with selects (a switch here puts a divergent region in every
 // frame and keeps ptxas from overlapping consecutive frames); each output is 0.5 * pass1 + 0.5 * pass2 as in Svf.
@@ -46,17 +55,34 @@ __device__ __forceinline__ float svf_pick(int type, float low, float band, float
     s = type == 4 ? peak : s;
     return s;
 }
+// one pass of the recurrence
+template <bool F>
+__device__ __forceinline__ void svf_half(float in, float &low, float &band, const SvfCoef &k, float &notch, float &high) {
+    if (F) {
+        notch = __fmaf_rn(-k.damp, band, in);
+        low = __fmaf_rn(k.freq, band, low);
+        high = __fsub_rn(notch, low);
+        const float t = __fmaf_rn(k.freq, high, band);
+        const float c = __fmul_rn(__fmul_rn(k.drive, band), band);
+        band = __fmaf_rn(-c, band, t);
+    } else {
+        notch = __fsub_rn(in, __fmul_rn(k.damp, band));
+        low = __fadd_rn(low, __fmul_rn(k.freq, band));
+        high = __fsub_rn(notch, low);
+        band = __fsub_rn(__fadd_rn(__fmul_rn(k.freq, high), band), __fmul_rn(__fmul_rn(__fmul_rn(k.drive, band), band), band));
+    }
+}
+template <bool F>
+__device__ __forceinline__ float svf_half_sum(float o1, float pick2) {  // 0.5 * pass 1 (already halved) + 0.5 * pass 2
+    return F ? __fmaf_rn(0.5f, pick2, o1) : __fadd_rn(o1, __fmul_rn(0.5f, pick2));
+}
+template <bool F>
 __device__ __forceinline__ float svf_tick(float in, float &low, float &band, const SvfCoef &k) {
-    float notch = __fsub_rn(in, __fmul_rn(k.damp, band));
-    low = __fadd_rn(low, __fmul_rn(k.freq, band));
-    float high = __fsub_rn(notch, low);
-    band = __fsub_rn(__fadd_rn(__fmul_rn(k.freq, high), band), __fmul_rn(__fmul_rn(__fmul_rn(k.drive, band), band), band));
+    float notch, high;
+    svf_half<F>(in, low, band, k, notch, high);
     const float o1 = __fmul_rn(0.5f, svf_pick(k.type, low, band, high, notch));
-    notch = __fsub_rn(in, __fmul_rn(k.damp, band));
-    low = __fadd_rn(low, __fmul_rn(k.freq, band));
-    high = __fsub_rn(notch, low);
-    band = __fsub_rn(__fadd_rn(__fmul_rn(k.freq, high), band), __fmul_rn(__fmul_rn(__fmul_rn(k.drive, band), band), band));
-    return __fadd_rn(o1, __fmul_rn(0.5f, svf_pick(k.type, low, band, high, notch)));
+    svf_half<F>(in, low, band, k, notch, high);
+    return svf_half_sum<F>(o1, svf_pick(k.type, low, band, high, notch));
 }
 
 // The same filter with the output tap fixed at compile time (T = 0..4; T < 0: per-lane selects as above).  A bank whose
@@ -66,24 +92,31 @@ __device__ __forceinline__ float svf_pick_t(int type, float low, float band, flo
     if (T < 0) return svf_pick(type, low, band, high, notch);
     return T == 1 ? band : T == 2 ? high : T == 3 ? notch : T == 4 ? __fsub_rn(low, high) : low;
 }
-template <int T>
+template <int T, bool F>
 __device__ __forceinline__ float svf_tick_t(float in, float &low, float &band, const SvfCoef &k) {
-    float notch = __fsub_rn(in, __fmul_rn(k.damp, band));
-    low = __fadd_rn(low, __fmul_rn(k.freq, band));
-    float high = __fsub_rn(notch, low);
-    band = __fsub_rn(__fadd_rn(__fmul_rn(k.freq, high), band), __fmul_rn(__fmul_rn(__fmul_rn(k.drive, band), band), band));
+    float notch, high;
+    svf_half<F>(in, low, band, k, notch, high);
     const float o1 = __fmul_rn(0.5f, svf_pick_t<T>(k.type, low, band, high, notch));
-    notch = __fsub_rn(in, __fmul_rn(k.damp, band));
-    low = __fadd_rn(low, __fmul_rn(k.freq, band));
-    high = __fsub_rn(notch, low);
-    band = __fsub_rn(__fadd_rn(__fmul_rn(k.freq, high), band), __fmul_rn(__fmul_rn(__fmul_rn(k.drive, band), band), band));
-    return __fadd_rn(o1, __fmul_rn(0.5f, svf_pick_t<T>(k.type, low, band, high, notch)));
+    svf_half<F>(in, low, band, k, notch, high);
+    return svf_half_sum<F>(o1, svf_pick_t<T>(k.type, low, band, high, notch));
 }
 
 // Two independent SVFs advanced together, statement by statement: the same operations as two svf_tick calls, written
-// interleaved because ptxas keeps close to source order and each filter alone is one 12-deep dependent chain.
+// interleaved because ptxas keeps close to source order and each filter alone is one dependent chain.
+template <bool F>
 __device__ __forceinline__ void svf_tick_pair(float inA, float &lowA, float &bandA, const SvfCoef &kA, float &outA, float inB, float &lowB,
                                               float &bandB, const SvfCoef &kB, float &outB) {
+    if (F) {
+        float nA, hA, nB, hB;
+        svf_half<true>(inA, lowA, bandA, kA, nA, hA);
+        svf_half<true>(inB, lowB, bandB, kB, nB, hB);
+        const float o1A = __fmul_rn(0.5f, svf_pick(kA.type, lowA, bandA, hA, nA)), o1B = __fmul_rn(0.5f, svf_pick(kB.type, lowB, bandB, hB, nB));
+        svf_half<true>(inA, lowA, bandA, kA, nA, hA);
+        svf_half<true>(inB, lowB, bandB, kB, nB, hB);
+        outA = __fmaf_rn(0.5f, svf_pick(kA.type, lowA, bandA, hA, nA), o1A);
+        outB = __fmaf_rn(0.5f, svf_pick(kB.type, lowB, bandB, hB, nB), o1B);
+        return;
+    }
     float dA = __fmul_rn(kA.damp, bandA), dB = __fmul_rn(kB.damp, bandB);
     float gA = __fmul_rn(kA.freq, bandA), gB = __fmul_rn(kB.freq, bandB);
     float cA = __fmul_rn(__fmul_rn(__fmul_rn(kA.drive, bandA), bandA), bandA), cB = __fmul_rn(__fmul_rn(__fmul_rn(kB.drive, bandB), bandB), bandB);
@@ -107,13 +140,24 @@ __device__ __forceinline__ void svf_tick_pair(float inA, float &lowA, float &ban
     outB = __fadd_rn(o1B, __fmul_rn(0.5f, svf_pick(kB.type, lowB, bandB, highB, notchB)));
 }
 
+template <bool F>
 __device__ __forceinline__ float dry_wet(float wet, float dry, float balance) {  // Fx.h:205-207, 297-299
-    return __fadd_rn(__fmul_rn(wet, balance), __fmul_rn(dry, __fsub_rn(1.0f, balance)));
+    const float d = __fmul_rn(dry, __fsub_rn(1.0f, balance));
+    return F ? __fmaf_rn(wet, balance, d) : __fadd_rn(__fmul_rn(wet, balance), d);
+}
+template <bool F>
+__device__ __forceinline__ float dl_read(float a, float b, float frac) {  // DelayLine::Read: a + (b - a) * frac_ (Fx.h:198)
+    return F ? __fmaf_rn(__fsub_rn(b, a), frac, a) : __fadd_rn(a, __fmul_rn(__fsub_rn(b, a), frac));
+}
+template <bool F>
+__device__ __forceinline__ float dl_write(float x, float feedback, float rd) {  // Write(in + feedback * read) (Fx.h:199-200)
+    return F ? __fmaf_rn(feedback, rd, x) : __fadd_rn(x, __fmul_rn(feedback, rd));
 }
 
 template <int KIND>
 __global__ void __launch_bounds__(64) k_fx(const float *in, float *out, uint32_t frames, uint32_t I,
                                            const float *__restrict__ par, float *svf, float *ring_all, uint32_t wp0) {
+    constexpr bool FM = OLB_F(KIND);
     const uint32_t inst = blockIdx.x * blockDim.x + threadIdx.x;
     if (inst >= I) return;
     auto P = [&](int p) { return par[(size_t) p * I + inst]; };
@@ -128,22 +172,22 @@ __global__ void __launch_bounds__(64) k_fx(const float *in, float *out, uint32_t
 
     for (uint32_t n = 0; n < frames; n++) {
         float v = in[(size_t) n * I + inst];
-        if (KIND == OLB_FX_DELAY || KIND == OLB_FX_RACK) {
+        if (OLB_K(KIND) == OLB_FX_DELAY || OLB_K(KIND) == OLB_FX_RACK) {
             // DelayLine::Read then Write (Fx.h:198-200); the write pointer runs backwards
             uint32_t ia = wp + delay;
             ia = ia >= (uint32_t) kRing ? ia - kRing : ia;
             uint32_t ib = ia + 1;
             ib = ib >= (uint32_t) kRing ? ib - kRing : ib;
             const float a = ring[ia], b = ring[ib];
-            const float rd = __fadd_rn(a, __fmul_rn(__fsub_rn(b, a), frac));
-            ring[wp] = __fadd_rn(v, __fmul_rn(feedback, rd));
+            const float rd = dl_read<FM>(a, b, frac);
+            ring[wp] = dl_write<FM>(v, feedback, rd);
             wp = wp == 0 ? kRing - 1 : wp - 1;
-            const float wet = svf_tick(rd, w_low, w_band, kw);
-            v = dry_wet(wet, v, d_balance);
+            const float wet = svf_tick<FM>(rd, w_low, w_band, kw);
+            v = dry_wet<FM>(wet, v, d_balance);
         }
-        if (KIND == OLB_FX_REVERB || KIND == OLB_FX_RACK) v = dry_wet(__fmul_rn(v, 0.8f), v, r_balance);
-        if (KIND == OLB_FX_FILTER || KIND == OLB_FX_RACK) v = svf_tick(v, f_low, f_band, kf);
-        if (KIND == OLB_FX_RACK) v = __fmul_rn(v, master);
+        if (OLB_K(KIND) == OLB_FX_REVERB || OLB_K(KIND) == OLB_FX_RACK) v = dry_wet<FM>(__fmul_rn(v, 0.8f), v, r_balance);
+        if (OLB_K(KIND) == OLB_FX_FILTER || OLB_K(KIND) == OLB_FX_RACK) v = svf_tick<FM>(v, f_low, f_band, kf);
+        if (OLB_K(KIND) == OLB_FX_RACK) v = __fmul_rn(v, master);
         out[(size_t) n * I + inst] = v;
     }
     svf[inst] = f_low;
@@ -159,15 +203,16 @@ template <int KIND>
 __device__ __forceinline__ float fx_frame(float v, float ra, float rb, float &wr, float frac, float feedback, float d_balance,
                                           float r_balance, float master, float &w_low, float &w_band, const SvfCoef &kw,
                                           float &f_low, float &f_band, const SvfCoef &kf) {
-    if (KIND == OLB_FX_DELAY || KIND == OLB_FX_RACK) {
-        const float rd = __fadd_rn(ra, __fmul_rn(__fsub_rn(rb, ra), frac));  // DelayLine::Read (Fx.h:198)
-        wr = __fadd_rn(v, __fmul_rn(feedback, rd));                          // Write(in + feedback * read) (Fx.h:199-200)
-        const float wet = svf_tick(rd, w_low, w_band, kw);
-        v = dry_wet(wet, v, d_balance);
+    constexpr bool FM = OLB_F(KIND);
+    if (OLB_K(KIND) == OLB_FX_DELAY || OLB_K(KIND) == OLB_FX_RACK) {
+        const float rd = dl_read<FM>(ra, rb, frac);  // DelayLine::Read (Fx.h:198)
+        wr = dl_write<FM>(v, feedback, rd);                          // Write(in + feedback * read) (Fx.h:199-200)
+        const float wet = svf_tick<FM>(rd, w_low, w_band, kw);
+        v = dry_wet<FM>(wet, v, d_balance);
     }
-    if (KIND == OLB_FX_REVERB || KIND == OLB_FX_RACK) v = dry_wet(__fmul_rn(v, 0.8f), v, r_balance);
-    if (KIND == OLB_FX_FILTER || KIND == OLB_FX_RACK) v = svf_tick(v, f_low, f_band, kf);
-    if (KIND == OLB_FX_RACK) v = __fmul_rn(v, master);
+    if (OLB_K(KIND) == OLB_FX_REVERB || OLB_K(KIND) == OLB_FX_RACK) v = dry_wet<FM>(__fmul_rn(v, 0.8f), v, r_balance);
+    if (OLB_K(KIND) == OLB_FX_FILTER || OLB_K(KIND) == OLB_FX_RACK) v = svf_tick<FM>(v, f_low, f_band, kf);
+    if (OLB_K(KIND) == OLB_FX_RACK) v = __fmul_rn(v, master);
     return v;
 }
 
@@ -183,7 +228,8 @@ template <int KIND, int N>
 __device__ __forceinline__ void fx_batch(float *col, const float *tap, float *wcol, int wstride, float &prev_a, float frac, float feedback,
                                          float d_balance, float r_balance, float master, float &w_low, float &w_band, const SvfCoef &kw,
                                          float &f_low, float &f_band, const SvfCoef &kf) {
-    constexpr bool kHasRing = (KIND == OLB_FX_DELAY || KIND == OLB_FX_RACK);
+    constexpr bool kHasRing = (OLB_K(KIND) == OLB_FX_DELAY || OLB_K(KIND) == OLB_FX_RACK);
+    constexpr bool FM = OLB_F(KIND);
     float x[N], rd[N], v[N];
 #pragma unroll
     for (int r = 0; r < N; r++) x[r] = col[r * kFxLanes];
@@ -194,53 +240,53 @@ __device__ __forceinline__ void fx_batch(float *col, const float *tap, float *wc
 #pragma unroll
         for (int r = 0; r < N; r++) {
             const float rb = r == 0 ? prev_a : ra[r - 1];
-            rd[r] = __fadd_rn(ra[r], __fmul_rn(__fsub_rn(rb, ra[r]), frac));     // DelayLine::Read (Fx.h:198)
-            wcol[r * wstride] = __fadd_rn(x[r], __fmul_rn(feedback, rd[r]));    // Write(in + feedback * read) (Fx.h:199-200)
+            rd[r] = dl_read<FM>(ra[r], rb, frac);     // DelayLine::Read (Fx.h:198)
+            wcol[r * wstride] = dl_write<FM>(x[r], feedback, rd[r]);    // Write(in + feedback * read) (Fx.h:199-200)
         }
         prev_a = ra[N - 1];
-        if (KIND == OLB_FX_RACK) {
+        if (OLB_K(KIND) == OLB_FX_RACK) {
             // the two recurrences side by side, the main filter one frame behind the wet filter: in source order frame r of
             // chain B sits next to frame r-1 of chain D, which is where ptxas's in-order schedule needs them to overlap
             float u = 0.f;  // main filter input of frame r-1
 #pragma unroll
             for (int r = 0; r <= N; r++) {
                 float wet = 0.f, y = 0.f;
-                if (r > 0 && r < N) svf_tick_pair(rd[r], w_low, w_band, kw, wet, u, f_low, f_band, kf, y);
-                else if (r < N) wet = svf_tick(rd[r], w_low, w_band, kw);
-                else y = svf_tick(u, f_low, f_band, kf);
+                if (r > 0 && r < N) svf_tick_pair<FM>(rd[r], w_low, w_band, kw, wet, u, f_low, f_band, kf, y);
+                else if (r < N) wet = svf_tick<FM>(rd[r], w_low, w_band, kw);
+                else y = svf_tick<FM>(u, f_low, f_band, kf);
                 if (r > 0) v[r - 1] = y;
                 if (r < N) {
-                    u = dry_wet(wet, x[r], d_balance);
-                    u = dry_wet(__fmul_rn(u, 0.8f), u, r_balance);
+                    u = dry_wet<FM>(wet, x[r], d_balance);
+                    u = dry_wet<FM>(__fmul_rn(u, 0.8f), u, r_balance);
                 }
             }
         } else {
 #pragma unroll
-            for (int r = 0; r < N; r++) v[r] = svf_tick(rd[r], w_low, w_band, kw);
+            for (int r = 0; r < N; r++) v[r] = svf_tick<FM>(rd[r], w_low, w_band, kw);
 #pragma unroll
-            for (int r = 0; r < N; r++) v[r] = dry_wet(v[r], x[r], d_balance);
+            for (int r = 0; r < N; r++) v[r] = dry_wet<FM>(v[r], x[r], d_balance);
         }
     } else {
 #pragma unroll
         for (int r = 0; r < N; r++) v[r] = x[r];
     }
-    if (KIND == OLB_FX_REVERB) {
+    if (OLB_K(KIND) == OLB_FX_REVERB) {
 #pragma unroll
-        for (int r = 0; r < N; r++) v[r] = dry_wet(__fmul_rn(v[r], 0.8f), v[r], r_balance);
+        for (int r = 0; r < N; r++) v[r] = dry_wet<FM>(__fmul_rn(v[r], 0.8f), v[r], r_balance);
     }
-    if (KIND == OLB_FX_FILTER) {
+    if (OLB_K(KIND) == OLB_FX_FILTER) {
 #pragma unroll
-        for (int r = 0; r < N; r++) v[r] = svf_tick(v[r], f_low, f_band, kf);
+        for (int r = 0; r < N; r++) v[r] = svf_tick<FM>(v[r], f_low, f_band, kf);
     }
 #pragma unroll
-    for (int r = 0; r < N; r++) col[r * kFxLanes] = KIND == OLB_FX_RACK ? __fmul_rn(v[r], master) : v[r];
+    for (int r = 0; r < N; r++) col[r * kFxLanes] = OLB_K(KIND) == OLB_FX_RACK ? __fmul_rn(v[r], master) : v[r];
 }
 
 // The ring kinds cut into pipeline stages for k_fx_split, one warp each (same operations, same order per value):
 //   io_batch    DelayLine::Read + Write: taps -> interpolated read `rd` (to the rd tile) and the value written back
 //   wet_batch   the wet filter, the delay's dry/wet mix and (rack) the reverb slot's mix, in place in the audio tile
 //   tail_batch  (rack) the main filter and the master volume, in place
-template <int N>
+template <int N, bool FM>
 __device__ __forceinline__ void io_batch(const float *col, const float *tap, float *wcol, int wstride, float *rdcol, float &prev_a, float frac,
                                          float feedback) {
     float x[N], ra[N];
@@ -251,14 +297,14 @@ __device__ __forceinline__ void io_batch(const float *col, const float *tap, flo
 #pragma unroll
     for (int r = 0; r < N; r++) {
         const float rb = r == 0 ? prev_a : ra[r - 1];
-        const float rd = __fadd_rn(ra[r], __fmul_rn(__fsub_rn(rb, ra[r]), frac));  // DelayLine::Read (Fx.h:198)
+        const float rd = dl_read<FM>(ra[r], rb, frac);  // DelayLine::Read (Fx.h:198)
         rdcol[r * kFxLanes] = rd;
-        wcol[r * wstride] = __fadd_rn(x[r], __fmul_rn(feedback, rd));              // Write(in + feedback * read) (Fx.h:199-200)
+        wcol[r * wstride] = dl_write<FM>(x[r], feedback, rd);              // Write(in + feedback * read) (Fx.h:199-200)
     }
     prev_a = ra[N - 1];
 }
 
-template <int N, bool RACK>
+template <int N, bool RACK, bool FM>
 __device__ __forceinline__ void wet_batch(float *col, const float *rdcol, float d_balance, float r_balance, float &w_low, float &w_band,
                                           const SvfCoef &kw) {
     float x[N], v[N];
@@ -267,24 +313,24 @@ __device__ __forceinline__ void wet_batch(float *col, const float *rdcol, float 
 #pragma unroll
     for (int r = 0; r < N; r++) v[r] = rdcol[r * kFxLanes];
 #pragma unroll
-    for (int r = 0; r < N; r++) v[r] = svf_tick(v[r], w_low, w_band, kw);
+    for (int r = 0; r < N; r++) v[r] = svf_tick<FM>(v[r], w_low, w_band, kw);
 #pragma unroll
-    for (int r = 0; r < N; r++) v[r] = dry_wet(v[r], x[r], d_balance);                              // Fx.h:205-207
+    for (int r = 0; r < N; r++) v[r] = dry_wet<FM>(v[r], x[r], d_balance);                              // Fx.h:205-207
     if (RACK) {
 #pragma unroll
-        for (int r = 0; r < N; r++) v[r] = dry_wet(__fmul_rn(v[r], 0.8f), v[r], r_balance);         // Fx.h:294-300, stub reverb
+        for (int r = 0; r < N; r++) v[r] = dry_wet<FM>(__fmul_rn(v[r], 0.8f), v[r], r_balance);         // Fx.h:294-300, stub reverb
     }
 #pragma unroll
     for (int r = 0; r < N; r++) col[r * kFxLanes] = v[r];
 }
 
-template <int N>
+template <int N, bool FM>
 __device__ __forceinline__ void tail_batch(float *col, float master, float &f_low, float &f_band, const SvfCoef &kf) {
     float v[N];
 #pragma unroll
     for (int r = 0; r < N; r++) v[r] = col[r * kFxLanes];
 #pragma unroll
-    for (int r = 0; r < N; r++) v[r] = svf_tick(v[r], f_low, f_band, kf);                           // Fx.h:426-434
+    for (int r = 0; r < N; r++) v[r] = svf_tick<FM>(v[r], f_low, f_band, kf);                           // Fx.h:426-434
 #pragma unroll
     for (int r = 0; r < N; r++) col[r * kFxLanes] = __fmul_rn(v[r], master);
 }
@@ -299,7 +345,8 @@ constexpr int kFxB = 8;
 template <int KIND>
 __global__ void __launch_bounds__(64) k_fx_pf(const float *in, float *out, uint32_t frames, uint32_t I,
                                               const float *__restrict__ par, float *svf, float *ring_all, uint32_t wp0) {
-    constexpr bool kHasRing = (KIND == OLB_FX_DELAY || KIND == OLB_FX_RACK);
+    constexpr bool kHasRing = (OLB_K(KIND) == OLB_FX_DELAY || OLB_K(KIND) == OLB_FX_RACK);
+    constexpr bool FM = OLB_F(KIND);
     constexpr int B = kFxB;
     const uint32_t inst = blockIdx.x * blockDim.x + threadIdx.x;
     if (inst >= I) return;
@@ -420,7 +467,8 @@ template <int KIND, int TB, int STAGES>
 __global__ void __launch_bounds__(32) k_fx_tma(const __grid_constant__ TensorMap tm_in, const __grid_constant__ TensorMap tm_out,
                                                uint32_t frames, uint32_t I, const float *__restrict__ par, float *svf, float *ring_all,
                                                uint32_t wp0) {
-    constexpr bool kHasRing = (KIND == OLB_FX_DELAY || KIND == OLB_FX_RACK);
+    constexpr bool kHasRing = (OLB_K(KIND) == OLB_FX_DELAY || OLB_K(KIND) == OLB_FX_RACK);
+    constexpr bool FM = OLB_F(KIND);
     constexpr int L = kFxL;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const uint32_t lane = threadIdx.x, i0 = blockIdx.x * L, inst = i0 + lane;
@@ -508,12 +556,12 @@ __global__ void __launch_bounds__(32) k_fx_tma(const __grid_constant__ TensorMap
         const uint32_t rows = min((uint32_t) TB, frames - i * TB);
         float *col = tiles + (size_t) st * TB * L + lane;
         if (!kHasRing) {
-            if (KIND == OLB_FX_FILTER && uniform_type >= 0) {  // FilterFx::Process is the filter alone (Fx.h:88-108)
+            if (OLB_K(KIND) == OLB_FX_FILTER && uniform_type >= 0) {  // FilterFx::Process is the filter alone (Fx.h:88-108)
                 if (live) {
                     switch (uniform_type) {
 #define OLB_FX_TYPE_CASE(T_)                                                                             \
     case T_:                                                                                             \
-        _Pragma("unroll 4") for (uint32_t r = 0; r < rows; r++) col[r * L] = svf_tick_t<T_>(col[r * L], f_low, f_band, kf); \
+        _Pragma("unroll 4") for (uint32_t r = 0; r < rows; r++) col[r * L] = svf_tick_t<T_, FM>(col[r * L], f_low, f_band, kf); \
         break;
                         OLB_FX_TYPE_CASE(0)
                         OLB_FX_TYPE_CASE(1)
@@ -631,7 +679,7 @@ __host__ __device__ constexpr size_t fx_split_smem_floats() {
 constexpr int kFxIo = 0, kFxWet = 1, kFxTail = 2, kFxIdle = 3;
 template <int KIND, int G>
 __host__ __device__ constexpr int fx_split_warps() {
-    return G == 1 ? (KIND == OLB_FX_RACK ? 3 : 2) : G == 2 ? (KIND == OLB_FX_RACK ? 8 : 4) : (KIND == OLB_FX_RACK ? 12 : 8);
+    return G == 1 ? (OLB_K(KIND) == OLB_FX_RACK ? 3 : 2) : G == 2 ? (OLB_K(KIND) == OLB_FX_RACK ? 8 : 4) : (OLB_K(KIND) == OLB_FX_RACK ? 12 : 8);
 }
 template <int TB, int STAGES>
 __host__ __device__ constexpr size_t fx_split_pipe_bytes() {  // one pipeline's tiles + barriers, rounded for TMA alignment
@@ -643,9 +691,10 @@ __global__ void __launch_bounds__(32 * fx_split_warps<KIND, G>()) k_fx_split(con
                                                                               const __grid_constant__ TensorMap tm_out, uint32_t frames,
                                                                               uint32_t I, const float *__restrict__ par, float *svf,
                                                                               float *ring_all, uint32_t wp0) {
-    static_assert(KIND == OLB_FX_DELAY || KIND == OLB_FX_RACK, "ring kinds only");
+    static_assert(OLB_K(KIND) == OLB_FX_DELAY || OLB_K(KIND) == OLB_FX_RACK, "ring kinds only");
     static_assert(G == 1 || G == 2 || G == 4, "1, 2 or 4 pipelines per CTA");
-    constexpr bool kRack = KIND == OLB_FX_RACK;
+    constexpr bool kRack = OLB_K(KIND) == OLB_FX_RACK;
+    constexpr bool FM = OLB_F(KIND);
     constexpr int L = kFxL, RS = TB + 4, WS = L;
     extern __shared__ __align__(1024) unsigned char smem_all[];
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -712,8 +761,8 @@ __global__ void __launch_bounds__(32 * fx_split_warps<KIND, G>()) k_fx_split(con
             float *col = tiles + (size_t) st * TB * L + lane;
             if (live) {
                 uint32_t r = 0;
-                for (; r + kFxBatch <= rows; r += kFxBatch) tail_batch<kFxBatch>(col + r * L, master, f_low, f_band, kf);
-                for (; r < rows; r++) tail_batch<1>(col + r * L, master, f_low, f_band, kf);
+                for (; r + kFxBatch <= rows; r += kFxBatch) tail_batch<kFxBatch, FM>(col + r * L, master, f_low, f_band, kf);
+                for (; r < rows; r++) tail_batch<1, FM>(col + r * L, master, f_low, f_band, kf);
             }
             store_and_refill(i, st);
         }
@@ -737,8 +786,8 @@ __global__ void __launch_bounds__(32 * fx_split_warps<KIND, G>()) k_fx_split(con
             const float *rdcol = rdtiles + (size_t) st * TB * L + lane;
             if (live) {
                 uint32_t r = 0;
-                for (; r + kFxBatch <= rows; r += kFxBatch) wet_batch<kFxBatch, kRack>(col + r * L, rdcol + r * L, d_balance, r_balance, w_low, w_band, kw);
-                for (; r < rows; r++) wet_batch<1, kRack>(col + r * L, rdcol + r * L, d_balance, r_balance, w_low, w_band, kw);
+                for (; r + kFxBatch <= rows; r += kFxBatch) wet_batch<kFxBatch, kRack, FM>(col + r * L, rdcol + r * L, d_balance, r_balance, w_low, w_band, kw);
+                for (; r < rows; r++) wet_batch<1, kRack, FM>(col + r * L, rdcol + r * L, d_balance, r_balance, w_low, w_band, kw);
             }
             if (kRack) mbar_arrive(&mid[st]);
             else store_and_refill(i, st);
@@ -802,8 +851,8 @@ __global__ void __launch_bounds__(32 * fx_split_warps<KIND, G>()) k_fx_split(con
                 const float *tap = rtiles + (size_t) st * L * RS + lane * RS + ((int) lc - base4);
                 float *wcol = wtile + lane;
                 uint32_t r = 0;
-                for (; r + kFxBatch <= rows; r += kFxBatch) io_batch<kFxBatch>(col + r * L, tap - r, wcol + r * WS, WS, rdcol + r * L, prev_a, frac, feedback);
-                for (; r < rows; r++) io_batch<1>(col + r * L, tap - r, wcol + r * WS, WS, rdcol + r * L, prev_a, frac, feedback);
+                for (; r + kFxBatch <= rows; r += kFxBatch) io_batch<kFxBatch, FM>(col + r * L, tap - r, wcol + r * WS, WS, rdcol + r * L, prev_a, frac, feedback);
+                for (; r < rows; r++) io_batch<1, FM>(col + r * L, tap - r, wcol + r * WS, WS, rdcol + r * L, prev_a, frac, feedback);
                 lc = lc >= rows ? lc - rows : lc + kRing - rows;
             }
             mbar_arrive(&tapd[st]);  // the wet warp can start while the ring is written back
@@ -827,9 +876,9 @@ __global__ void __launch_bounds__(32 * fx_split_warps<KIND, G>()) k_fx_split(con
                     uint32_t ib = ia + 1;
                     ib = ib >= (uint32_t) kRing ? ib - kRing : ib;
                     const float ra = ring[ia], rb = ring[ib];
-                    const float rd = __fadd_rn(ra, __fmul_rn(__fsub_rn(rb, ra), frac));
+                    const float rd = dl_read<FM>(ra, rb, frac);
                     rdcol[r * L] = rd;
-                    ring[w] = __fadd_rn(col[r * L], __fmul_rn(feedback, rd));
+                    ring[w] = dl_write<FM>(col[r * L], feedback, rd);
                     w = w == 0 ? kRing - 1 : w - 1;
                 }
             }
@@ -849,6 +898,7 @@ __global__ void __launch_bounds__(32 * fx_split_warps<KIND, G>()) k_fx_split(con
 __global__ void __launch_bounds__(64) k_plate_tail(const float *wet, const float *dry, float *out, uint32_t frames, uint32_t I,
                                                    const float *__restrict__ par, float *svf) {
     constexpr int B = kFxB;
+    constexpr bool FM = false;  // the plate rack keeps the reference arithmetic
     const uint32_t inst = blockIdx.x * blockDim.x + threadIdx.x;
     if (inst >= I) return;
     auto P = [&](int p) { return par[(size_t) p * I + inst]; };
@@ -866,8 +916,8 @@ __global__ void __launch_bounds__(64) k_plate_tail(const float *wet, const float
 #pragma unroll
         for (int j = 0; j < B; j++)
             if (n0 + j < frames) {
-                float v = dry_wet(w[j], d[j], r_balance);
-                v = svf_tick(v, f_low, f_band, kf);
+                float v = dry_wet<FM>(w[j], d[j], r_balance);
+                v = svf_tick<FM>(v, f_low, f_band, kf);
                 out[(size_t) (n0 + j) * I + inst] = __fmul_rn(v, master);
             }
     }
@@ -886,6 +936,7 @@ struct olb_fx {
     std::recursive_mutex mu;
     StreamOrder order;
     int device = 0, kind = 0;
+    bool fast = false;  // olb_fx_set_mode: the fused arithmetic tier
     uint32_t I = 0;
     float sample_rate = 48000.f;
     std::vector<host::RackParams> units;
@@ -959,7 +1010,7 @@ static int fx_init(olb_fx *h, float sr) {
 // the delay-line reads).  OLB_FX_TMA_CFG="<TB>x<STAGES>" selects another compiled shape (tuning aid).
 template <int KIND, int TB, int STAGES>
 static int fx_launch_tma_cfg(olb_fx *h, const float *in, float *out, uint32_t frames, cudaStream_t st) {
-    constexpr bool has_ring = (KIND == OLB_FX_DELAY || KIND == OLB_FX_RACK);
+    constexpr bool has_ring = (OLB_K(KIND) == OLB_FX_DELAY || OLB_K(KIND) == OLB_FX_RACK);
     constexpr size_t smem = fx_tma_smem_floats<TB, STAGES>(has_ring) * sizeof(float) + (size_t) STAGES * sizeof(uint64_t);
     TensorMap tin, tout;
     int rc = make_tmap_frames(&tin, in, frames, h->I, kFxL, TB);
@@ -991,6 +1042,7 @@ static int fx_launch_split_cfg(olb_fx *h, const float *in, float *out, uint32_t 
 
 // The ring kinds run k_fx_split unless OLB_FX_SPLIT=0 asks for the one-warp k_fx_tma (test / tuning aid).
 static bool fx_use_split(int kind) {
+    kind &= 7;
     if (kind != OLB_FX_DELAY && kind != OLB_FX_RACK) return false;
     const char *e = getenv("OLB_FX_SPLIT");
     return !e || atoi(e) != 0;
@@ -1001,7 +1053,7 @@ static int fx_launch_tma(olb_fx *h, const float *in, float *out, uint32_t frames
     int tb = 64, stages = 4;
     if (const char *e = getenv("OLB_FX_TMA_CFG")) sscanf(e, "%dx%d", &tb, &stages);
     if (fx_use_split(KIND)) {
-        constexpr int SK = (KIND == OLB_FX_DELAY || KIND == OLB_FX_RACK) ? KIND : OLB_FX_DELAY;
+        constexpr int SK = (OLB_K(KIND) == OLB_FX_DELAY || OLB_K(KIND) == OLB_FX_RACK) ? KIND : (OLB_FX_DELAY | (KIND & kFxFastBit));
         // pipelines per CTA: as many as it takes to keep the bank on one CTA per SM (up to 4), so that the kernel places
         // every warp on a scheduler itself; OLB_FX_SPLIT_G / OLB_FX_TMA_CFG override (test / tuning aids)
         const uint32_t pipes = (h->I + kFxL - 1) / kFxL;
@@ -1105,6 +1157,18 @@ OLB_API int olb_fx_update_hw(olb_fx *h, uint32_t first, uint32_t count, uint8_t 
     return OLB_OK;
 }
 
+// The arithmetic tier of a bank (olbank.h): EXACT rounds every product and sum like the reference's -O3 build without
+// contraction; FMA contracts the svf, the ring's interpolation, the feedback write and the mixes into fused operations
+// (oracle: orc_fx_set_mode).  State carries over a switch -- the tiers differ in rounding only.
+OLB_API int olb_fx_set_mode(olb_fx *h, int mode) {
+    OLB_ARG(h, "olb_fx_set_mode: NULL handle");
+    OLB_LOCK(h);
+    OLB_ARG(mode == OLB_MODE_EXACT || mode == OLB_MODE_FMA, "olb_fx_set_mode: mode %d (the fx banks have OLB_MODE_EXACT and OLB_MODE_FMA)", mode);
+    OLB_ARG(h->kind != OLB_FX_RACK_PLATE || mode == OLB_MODE_EXACT, "olb_fx_set_mode: the plate rack has OLB_MODE_EXACT only");
+    h->fast = mode == OLB_MODE_FMA;
+    return OLB_OK;
+}
+
 OLB_API const char *olb_fx_last_kernel(olb_fx *h) { return h ? h->last_kernel : "none"; }
 
 // The plate rack's stages 2 and 3 (stage 1, the DelayFx kernel, has just written h->d_mid[0]).
@@ -1168,12 +1232,16 @@ OLB_API int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev_arg, u
     const int which = (ek && !strcmp(ek, "simple")) ? 0 : ((ek && !strcmp(ek, "pf")) || !tma_ok ? 1 : 2);
     const unsigned grid = (h->I + 63) / 64;
 #define OLB_FX_GO(KERNEL, KIND) KERNEL<KIND><<<grid, 64, 0, st>>>(in_dev, out_dev, F, h->I, h->d_par, h->d_svf, h->d_ring, h->wp)
-#define OLB_FX_KINDS(KERNEL)                                          \
-    switch (kind) {                                                   \
-        case OLB_FX_FILTER: OLB_FX_GO(KERNEL, OLB_FX_FILTER); break;  \
-        case OLB_FX_DELAY: OLB_FX_GO(KERNEL, OLB_FX_DELAY); break;    \
-        case OLB_FX_REVERB: OLB_FX_GO(KERNEL, OLB_FX_REVERB); break;  \
-        default: OLB_FX_GO(KERNEL, OLB_FX_RACK); break;               \
+#define OLB_FX_KINDS(KERNEL)                                                               \
+    switch (kind | (h->fast ? kFxFastBit : 0)) {                                           \
+        case OLB_FX_FILTER: OLB_FX_GO(KERNEL, OLB_FX_FILTER); break;                       \
+        case OLB_FX_DELAY: OLB_FX_GO(KERNEL, OLB_FX_DELAY); break;                         \
+        case OLB_FX_REVERB: OLB_FX_GO(KERNEL, OLB_FX_REVERB); break;                       \
+        case OLB_FX_RACK: OLB_FX_GO(KERNEL, OLB_FX_RACK); break;                           \
+        case OLB_FX_FILTER | kFxFastBit: OLB_FX_GO(KERNEL, OLB_FX_FILTER | kFxFastBit); break; \
+        case OLB_FX_DELAY | kFxFastBit: OLB_FX_GO(KERNEL, OLB_FX_DELAY | kFxFastBit); break;   \
+        case OLB_FX_REVERB | kFxFastBit: OLB_FX_GO(KERNEL, OLB_FX_REVERB | kFxFastBit); break; \
+        default: OLB_FX_GO(KERNEL, OLB_FX_RACK | kFxFastBit); break;                       \
     }
     if (which == 0) {
         OLB_FX_KINDS(k_fx);
@@ -1183,11 +1251,15 @@ OLB_API int olb_fx_process(olb_fx *h, const float *in_dev, float *out_dev_arg, u
         h->last_kernel = "k_fx_pf";
     } else {
         int rc = OLB_OK;
-        switch (kind) {
+        switch (kind | (h->fast ? kFxFastBit : 0)) {
             case OLB_FX_FILTER: rc = fx_launch_tma<OLB_FX_FILTER>(h, in_dev, out_dev, F, st); break;
             case OLB_FX_DELAY: rc = fx_launch_tma<OLB_FX_DELAY>(h, in_dev, out_dev, F, st); break;
             case OLB_FX_REVERB: rc = fx_launch_tma<OLB_FX_REVERB>(h, in_dev, out_dev, F, st); break;
-            default: rc = fx_launch_tma<OLB_FX_RACK>(h, in_dev, out_dev, F, st); break;
+            case OLB_FX_RACK: rc = fx_launch_tma<OLB_FX_RACK>(h, in_dev, out_dev, F, st); break;
+            case OLB_FX_FILTER | kFxFastBit: rc = fx_launch_tma<OLB_FX_FILTER | kFxFastBit>(h, in_dev, out_dev, F, st); break;
+            case OLB_FX_DELAY | kFxFastBit: rc = fx_launch_tma<OLB_FX_DELAY | kFxFastBit>(h, in_dev, out_dev, F, st); break;
+            case OLB_FX_REVERB | kFxFastBit: rc = fx_launch_tma<OLB_FX_REVERB | kFxFastBit>(h, in_dev, out_dev, F, st); break;
+            default: rc = fx_launch_tma<OLB_FX_RACK | kFxFastBit>(h, in_dev, out_dev, F, st); break;
         }
         if (rc) return rc;
         h->last_kernel = fx_use_split(kind) ? "k_fx_split" : "k_fx_tma";
@@ -1257,24 +1329,25 @@ __global__ void __launch_bounds__(256) k_fx2_take0(const float2 *__restrict__ in
 }
 
 // One thread per (frame, instance) of a time cut: merges channel 0 (already processed, `tmp`) with channel 1.
-// KIND == OLB_FX_DELAY here is the time-parallel form of channel 1's delay line, valid while no frame of the cut reads a
+// OLB_K(KIND) == OLB_FX_DELAY here is the time-parallel form of channel 1's delay line, valid while no frame of the cut reads a
 // ring position another frame of the cut writes (cut <= delay and delay + 1 <= 48 000 - cut for every instance; the host
 // checks).  in may alias out (each thread reads its frame before writing it).
 template <int KIND>
 __global__ void __launch_bounds__(256) k_fx2_put(const float2 *in, const float *__restrict__ tmp, float2 *out, uint32_t frames, uint32_t I,
                                                  const float *__restrict__ par, float *ring1, uint32_t wp0) {
+    constexpr bool FM = OLB_F(KIND);
     const size_t idx = (size_t) blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= (size_t) frames * I) return;
     const uint32_t n = (uint32_t) (idx / I), inst = (uint32_t) (idx - (size_t) n * I);
     auto P = [&](int p) { return par[(size_t) p * I + inst]; };
-    if (KIND == OLB_FX_FILTER) {
+    if (OLB_K(KIND) == OLB_FX_FILTER) {
         reinterpret_cast<float *>(out)[2 * idx] = tmp[idx];  // frame_out[1] stays what the caller had there
-    } else if (KIND == OLB_FX_RACK) {
+    } else if (OLB_K(KIND) == OLB_FX_RACK) {
         out[idx] = make_float2(tmp[idx], __fmul_rn(0.0f, P(P_MASTER)));  // buf_c[1] * master_volume, buf_c[1] == 0 for ever
-    } else if (KIND == OLB_FX_REVERB) {
+    } else if (OLB_K(KIND) == OLB_FX_REVERB) {
         const float2 v = in[idx];
         const float b = P(P_R_BALANCE);
-        out[idx] = make_float2(dry_wet(__fmul_rn(v.x, 0.8f), v.x, b), dry_wet(__fmul_rn(v.y, 0.8f), v.y, b));
+        out[idx] = make_float2(dry_wet<FM>(__fmul_rn(v.x, 0.8f), v.x, b), dry_wet<FM>(__fmul_rn(v.y, 0.8f), v.y, b));
     } else {
         const float x1 = in[idx].y;
         const uint32_t delay = __float_as_uint(P(P_D_DELAY));
@@ -1284,13 +1357,14 @@ __global__ void __launch_bounds__(256) k_fx2_put(const float2 *in, const float *
         uint32_t ib = ia + 1;
         ib = ib >= (uint32_t) kRing ? ib - kRing : ib;
         const float a = ring1[(size_t) ia * I + inst], b = ring1[(size_t) ib * I + inst];
-        const float rd = __fadd_rn(a, __fmul_rn(__fsub_rn(b, a), P(P_D_FRAC)));           // DelayLine::Read
-        ring1[(size_t) wp * I + inst] = __fadd_rn(x1, __fmul_rn(P(P_D_FEEDBACK), rd));   // Write(in + feedback * read)
-        out[idx] = make_float2(tmp[idx], dry_wet(rd, x1, P(P_D_BALANCE)));                // filter_.Process(buf, buf) left buf[1] alone
+        const float rd = dl_read<FM>(a, b, P(P_D_FRAC));           // DelayLine::Read
+        ring1[(size_t) wp * I + inst] = dl_write<FM>(x1, P(P_D_FEEDBACK), rd);   // Write(in + feedback * read)
+        out[idx] = make_float2(tmp[idx], dry_wet<FM>(rd, x1, P(P_D_BALANCE)));                // filter_.Process(buf, buf) left buf[1] alone
     }
 }
 
 // DelayFx<2> channel 1, one instance per thread walking time: any delay (a cut may read what it wrote).
+template <bool FM>
 __global__ void __launch_bounds__(64) k_fx2_delay1(const float2 *in, const float *__restrict__ tmp, float2 *out, uint32_t frames, uint32_t I,
                                                    const float *__restrict__ par, float *ring1, uint32_t wp0) {
     const uint32_t inst = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1307,10 +1381,10 @@ __global__ void __launch_bounds__(64) k_fx2_delay1(const float2 *in, const float
         uint32_t ib = ia + 1;
         ib = ib >= (uint32_t) kRing ? ib - kRing : ib;
         const float a = ring1[(size_t) ia * I + inst], b = ring1[(size_t) ib * I + inst];
-        const float rd = __fadd_rn(a, __fmul_rn(__fsub_rn(b, a), frac));
-        ring1[(size_t) wp * I + inst] = __fadd_rn(x1, __fmul_rn(feedback, rd));
+        const float rd = dl_read<FM>(a, b, frac);
+        ring1[(size_t) wp * I + inst] = dl_write<FM>(x1, feedback, rd);
         wp = wp == 0 ? kRing - 1 : wp - 1;
-        out[idx] = make_float2(tmp[idx], dry_wet(rd, x1, balance));
+        out[idx] = make_float2(tmp[idx], dry_wet<FM>(rd, x1, balance));
     }
 }
 
@@ -1383,7 +1457,34 @@ OLB_API int olb_fx2_update_hw(olb_fx2 *h, uint32_t first, uint32_t count, uint8_
     return olb_fx_update_hw(h->mono, first, count, control, values_host, stride);
 }
 
+OLB_API int olb_fx2_set_mode(olb_fx2 *h, int mode) {
+    OLB_ARG(h, "olb_fx2_set_mode: NULL handle");
+    OLB_LOCK(h);
+    return olb_fx_set_mode(h->mono, mode);
+}
+
 OLB_API const char *olb_fx2_last_kernel(olb_fx2 *h) { return h ? h->last_kernel : "none"; }
+
+// Channel 1 of one cut (and channel 0's interleave), in the bank's arithmetic tier.
+static void fx2_put(olb_fx2 *h, const float2 *in_c, const float *tmp, float2 *out_c, uint32_t n, unsigned grid, bool par_delay, cudaStream_t st) {
+    const float *par = h->mono->d_par;
+#define OLB_FX2_PUT(KIND, RING, WP) k_fx2_put<KIND><<<grid, 256, 0, st>>>(in_c, tmp, out_c, n, h->I, par, RING, WP)
+    if (h->mono->fast) {
+        constexpr int F = kFxFastBit;
+        if (h->kind == OLB_FX_REVERB) OLB_FX2_PUT(OLB_FX_REVERB | F, nullptr, 0);
+        else if (h->kind == OLB_FX_FILTER) OLB_FX2_PUT(OLB_FX_FILTER | F, nullptr, 0);
+        else if (h->kind == OLB_FX_RACK) OLB_FX2_PUT(OLB_FX_RACK | F, nullptr, 0);
+        else if (par_delay) OLB_FX2_PUT(OLB_FX_DELAY | F, h->d_ring1, h->wp1);
+        else k_fx2_delay1<true><<<(h->I + 63) / 64, 64, 0, st>>>(in_c, tmp, out_c, n, h->I, par, h->d_ring1, h->wp1);
+    } else {
+        if (h->kind == OLB_FX_REVERB) OLB_FX2_PUT(OLB_FX_REVERB, nullptr, 0);
+        else if (h->kind == OLB_FX_FILTER) OLB_FX2_PUT(OLB_FX_FILTER, nullptr, 0);
+        else if (h->kind == OLB_FX_RACK) OLB_FX2_PUT(OLB_FX_RACK, nullptr, 0);
+        else if (par_delay) OLB_FX2_PUT(OLB_FX_DELAY, h->d_ring1, h->wp1);
+        else k_fx2_delay1<false><<<(h->I + 63) / 64, 64, 0, st>>>(in_c, tmp, out_c, n, h->I, par, h->d_ring1, h->wp1);
+    }
+#undef OLB_FX2_PUT
+}
 
 OLB_API int olb_fx2_process(olb_fx2 *h, const float *in_dev, float *out_dev, uint64_t frames, void *stream) {
     OLB_ARG(h, "olb_fx2_process: NULL handle");
@@ -1439,7 +1540,7 @@ OLB_API int olb_fx2_process(olb_fx2 *h, const float *in_dev, float *out_dev, uin
                 int rc = fx_upload(h->mono, st);
                 if (rc) return rc;
             }
-            k_fx2_put<OLB_FX_REVERB><<<grid, 256, 0, st>>>(in_c, nullptr, out_c, n, h->I, h->mono->d_par, nullptr, 0);
+            fx2_put(h, in_c, nullptr, out_c, n, grid, false, st);
             OLB_LAUNCHED();
             h->last_kernel = "k_fx2_put";
             continue;
@@ -1448,10 +1549,7 @@ OLB_API int olb_fx2_process(olb_fx2 *h, const float *in_dev, float *out_dev, uin
         OLB_LAUNCHED();
         int rc = olb_fx_process(h->mono, h->d_tmp, h->d_tmp, n, st);
         if (rc) return rc;
-        if (h->kind == OLB_FX_FILTER) k_fx2_put<OLB_FX_FILTER><<<grid, 256, 0, st>>>(in_c, h->d_tmp, out_c, n, h->I, h->mono->d_par, nullptr, 0);
-        else if (h->kind == OLB_FX_RACK) k_fx2_put<OLB_FX_RACK><<<grid, 256, 0, st>>>(in_c, h->d_tmp, out_c, n, h->I, h->mono->d_par, nullptr, 0);
-        else if (par_delay) k_fx2_put<OLB_FX_DELAY><<<grid, 256, 0, st>>>(in_c, h->d_tmp, out_c, n, h->I, h->mono->d_par, h->d_ring1, h->wp1);
-        else k_fx2_delay1<<<(h->I + 63) / 64, 64, 0, st>>>(in_c, h->d_tmp, out_c, n, h->I, h->mono->d_par, h->d_ring1, h->wp1);
+        fx2_put(h, in_c, h->d_tmp, out_c, n, grid, par_delay, st);
         OLB_LAUNCHED();
         if (h->kind == OLB_FX_DELAY) h->wp1 = (uint32_t) ((h->wp1 + (uint64_t) kRing - n % kRing) % kRing);
         h->last_kernel = h->kind == OLB_FX_DELAY && !par_delay ? "k_fx2_delay1" : "k_fx2_put";
@@ -1561,7 +1659,7 @@ OLB_API int olb_fx2_process_static(olb_fx2 *h, const float *in_dev, float *out_d
         float2 *out_c = out2 + t0 * I;
         if (h->kind == OLB_FX_REVERB) {
             if (h->mono->dirty && (rc = fx_upload(h->mono, st))) return rc;
-            k_fx2_put<OLB_FX_REVERB><<<grid, 256, 0, st>>>(in_c, nullptr, out_c, n, h->I, h->mono->d_par, nullptr, 0);
+            fx2_put(h, in_c, nullptr, out_c, n, grid, false, st);
             OLB_LAUNCHED();
             h->last_kernel = "k_fx2_put";
             continue;
@@ -1570,10 +1668,7 @@ OLB_API int olb_fx2_process_static(olb_fx2 *h, const float *in_dev, float *out_d
         OLB_LAUNCHED();
         rc = olb_fx_process(h->mono, tmp, tmp, n, st);  // OLB_FX_FILTER / _DELAY / _RACK: launches only, no allocation
         if (rc) return rc;
-        if (h->kind == OLB_FX_FILTER) k_fx2_put<OLB_FX_FILTER><<<grid, 256, 0, st>>>(in_c, tmp, out_c, n, h->I, h->mono->d_par, nullptr, 0);
-        else if (h->kind == OLB_FX_RACK) k_fx2_put<OLB_FX_RACK><<<grid, 256, 0, st>>>(in_c, tmp, out_c, n, h->I, h->mono->d_par, nullptr, 0);
-        else if (par_delay) k_fx2_put<OLB_FX_DELAY><<<grid, 256, 0, st>>>(in_c, tmp, out_c, n, h->I, h->mono->d_par, h->d_ring1, h->wp1);
-        else k_fx2_delay1<<<(h->I + 63) / 64, 64, 0, st>>>(in_c, tmp, out_c, n, h->I, h->mono->d_par, h->d_ring1, h->wp1);
+        fx2_put(h, in_c, tmp, out_c, n, grid, par_delay, st);
         OLB_LAUNCHED();
         if (h->kind == OLB_FX_DELAY) h->wp1 = (uint32_t) ((h->wp1 + (uint64_t) kRing - n % kRing) % kRing);
         h->last_kernel = h->kind == OLB_FX_DELAY && !par_delay ? "k_fx2_delay1" : "k_fx2_put";

@@ -37,6 +37,10 @@ class FxBank:
     def Init(self, sample_rate):
         check(self._f("init")(self.h, sample_rate))
 
+    def SetMode(self, mode):
+        """MODE_EXACT (default; the reference's separately rounded arithmetic) or MODE_FMA (the fused tier, olbank.h)."""
+        check(self._f("set_mode")(self.h, int(mode)))
+
     def UpdateMidiControl(self, control, value, first=0, count=None):
         count = self.instances - first if count is None else count
         check(self._f("update_midi")(self.h, first, count, int(control), int(value)))

@@ -79,6 +79,14 @@ class _Fx:
         assert rc == 0
         return out
 
+    def fx_mode(self, fast):
+        """The fx units' arithmetic: False = the reference's separately rounded operations (default), True = the fused tier
+        (oracle only: the compiled reference has no such switch)."""
+        if self.prefix == "orc":
+            self.lib.orc_fx_set_mode(1 if fast else 0)
+        else:
+            assert not fast
+
     def filterfx(self, x, sr=48000.0, ev=None, prefill=0.0):
         return self._run("filterfx", x, sr, ev, prefill)
 

@@ -383,18 +383,39 @@ static void svf_set_drive(Svf *f, float d) {
     f->pre_drive = fclampf(d * 0.1f, 0.f, 1.f);
     f->drive = f->pre_drive * f->res;
 }
-static inline void svf_half(Svf *f, float in, float *notch, float *high) {
+// The fx banks' opt-in FUSED tier (olb_fx_set_mode(OLB_MODE_FMA); north_star: "fused or re-associated variants must state
+// their tolerance"): the same formulas with the multiply-adds fused (one rounding instead of two), which takes the SVF's
+// recurrence from 6 dependent operations per pass to 4 and its operation count from 11 to 7.  THIS FILE IS THE SPECIFICATION of
+// the fused forms (fmaf = one IEEE rounding); the default everywhere is the separately rounded reference arithmetic.  The
+// voice's filter is never fused.
+static int g_fx_fast = 0;
+ORC_API void orc_fx_set_mode(int fast) { g_fx_fast = fast ? 1 : 0; }
+static inline void svf_half(Svf *f, float in, float *notch, float *high, int fast) {
+    if (fast) {
+        *notch = fmaf(-f->damp, f->band, in);
+        f->low = fmaf(f->freq, f->band, f->low);
+        *high = *notch - f->low;
+        const float t = fmaf(f->freq, *high, f->band);
+        const float c = (f->drive * f->band) * f->band;
+        f->band = fmaf(-c, f->band, t);
+        return;
+    }
     *notch = in - f->damp * f->band;
     f->low = f->low + f->freq * f->band;
     *high = *notch - f->low;
     f->band = f->freq * *high + f->band - f->drive * f->band * f->band * f->band;
 }
-static void svf_tick(Svf *f, float in) {
+static void svf_tick(Svf *f, float in, int fast = 0) {
     float n, h;
-    svf_half(f, in, &n, &h);
+    svf_half(f, in, &n, &h, fast);
     f->o_low = 0.5f * f->low; f->o_high = 0.5f * h; f->o_band = 0.5f * f->band;
     f->o_peak = 0.5f * (f->low - h); f->o_notch = 0.5f * n;
-    svf_half(f, in, &n, &h);
+    svf_half(f, in, &n, &h, fast);
+    if (fast) {
+        f->o_low = fmaf(0.5f, f->low, f->o_low); f->o_high = fmaf(0.5f, h, f->o_high); f->o_band = fmaf(0.5f, f->band, f->o_band);
+        f->o_peak = fmaf(0.5f, f->low - h, f->o_peak); f->o_notch = fmaf(0.5f, n, f->o_notch);
+        return;
+    }
     f->o_low += 0.5f * f->low; f->o_high += 0.5f * h; f->o_band += 0.5f * f->band;
     f->o_peak += 0.5f * (f->low - h); f->o_notch += 0.5f * n;
 }
@@ -487,7 +508,7 @@ static void ring_set_delay(Ring *r, float d) {
 static inline float ring_read(const Ring *r) {
     float a = r->line[(r->wp + r->delay) % kMaxDelay];
     float b = r->line[(r->wp + r->delay + 1) % kMaxDelay];
-    return a + (b - a) * r->frac;
+    return g_fx_fast ? fmaf(b - a, r->frac, a) : a + (b - a) * r->frac;
 }
 static inline void ring_write(Ring *r, float s) { r->line[r->wp] = s; r->wp = (r->wp - 1 + kMaxDelay) % kMaxDelay; }
 
@@ -502,7 +523,7 @@ static void filter_update(FilterUnit *u) {  // Fx.h:110-114
 static void filter_defaults(FilterUnit *u) { u->cutoff = 20000.f; u->resonance = 0.f; u->drive = 0.f; u->type = 0; }
 static void filter_init(FilterUnit *u, float sr) { svf_init(&u->svf, sr); filter_update(u); }  // Fx.h:83-86
 static float filter_tick(FilterUnit *u, float in) {  // Fx.h:88-108; enum order LowPass, BandPass, HighPass, Notch, Peak
-    svf_tick(&u->svf, in);
+    svf_tick(&u->svf, in, g_fx_fast);
     switch (u->type) {
         case 2: return u->svf.o_high;
         case 1: return u->svf.o_band;
@@ -558,10 +579,11 @@ static void delay_tick(DelayUnit *d, const float *in, float *out) {  // Fx.h:194
     float buf[2];
     for (int i = 0; i < d->n; i++) {
         buf[i] = ring_read(&d->ring[i]);
-        ring_write(&d->ring[i], in[i] + (d->feedback * buf[i]));
+        ring_write(&d->ring[i], g_fx_fast ? fmaf(d->feedback, buf[i], in[i]) : in[i] + (d->feedback * buf[i]));
     }
     buf[0] = filter_tick(&d->wet, buf[0]);  // the wet filter is mono: only channel 0 passes through it
-    for (int i = 0; i < d->n; i++) out[i] = (buf[i] * d->balance) + (in[i] * (1 - d->balance));
+    for (int i = 0; i < d->n; i++)
+        out[i] = g_fx_fast ? fmaf(buf[i], d->balance, in[i] * (1 - d->balance)) : (buf[i] * d->balance) + (in[i] * (1 - d->balance));
 }
 static int delay_hw(DelayUnit *d, uint8_t cc, float v) {  // Fx.h:219-237
     switch (cc) {
@@ -603,7 +625,8 @@ static void reverb_tick(ReverbUnit *r, const float *in, float *out) {
     float in1 = in[0], in2 = r->n > 1 ? in[1] : in1;
     buf[0] = in1 * 0.8f;
     if (r->n > 1) buf[1] = in2 * 0.8f; else buf[0] = in2 * 0.8f;
-    for (int i = 0; i < r->n; i++) out[i] = (buf[i] * r->balance) + (in[i] * (1 - r->balance));
+    for (int i = 0; i < r->n; i++)
+        out[i] = g_fx_fast ? fmaf(buf[i], r->balance, in[i] * (1 - r->balance)) : (buf[i] * r->balance) + (in[i] * (1 - r->balance));
 }
 static int reverb_set(ReverbUnit *r, uint8_t cc, float scaled, float cutoff_scaled) {
     switch (cc) {

@@ -28,13 +28,14 @@ static void dump(const char *path, const std::vector<float> &v) {
 
 // test/fx_test.cpp:25-55 shape: Init, a setter, per-frame Process in a loop -- then the rest of the block at once
 template <class Bank>
-static int run_fx(uint32_t I, uint32_t T, std::vector<float> &in, std::vector<float> &out, uint32_t width = 1) {
+static int run_fx(uint32_t I, uint32_t T, std::vector<float> &in, std::vector<float> &out, uint32_t width = 1, int mode = OLB_MODE_EXACT) {
     Bank bank(I);
     I *= width;  // floats per bank frame (stereo instances: 2 each)
     if (bank.Init(48000.f) != ol::gpu::Ok) {
         fprintf(stderr, "Init failed: %s\n", bank.error().c_str());
         return 4;
     }
+    if (mode != OLB_MODE_EXACT) bank.SetMode(mode);  // the fused tier (not in the reference)
     bank.UpdateHardwareControl(35 /* CC_DELAY_TIME, cc_map.h */, 0.3f);
     bank.UpdateMidiControl(41 /* CC_FILTER_CUTOFF */, 90);
     uint32_t t = 0;
@@ -69,6 +70,7 @@ int main(int argc, char **argv) {
     else if (!strcmp(unit, "delay")) rc = run_fx<ol::gpu::DelayFxBank>(I, T, in, out);
     else if (!strcmp(unit, "reverb")) rc = run_fx<ol::gpu::ReverbFxBank>(I, T, in, out);
     else if (!strcmp(unit, "rack")) rc = run_fx<ol::gpu::FxRackBank>(I, T, in, out);
+    else if (!strcmp(unit, "rack_fma")) rc = run_fx<ol::gpu::FxRackBank>(I, T, in, out, 1, OLB_MODE_FMA);
     else if (!strcmp(unit, "plate")) {
         out2.resize((size_t) I * T);
         ol::gpu::DattorroBank plates(I);
@@ -83,6 +85,8 @@ int main(int argc, char **argv) {
         if (t < T) plates.ProcessBlock(&in[(size_t) t * I], &out[(size_t) t * I], &out2[(size_t) t * I], T - t);
         rc = plates.status() == OLB_OK ? 0 : 5;
         if (rc) fprintf(stderr, "process failed: %s\n", plates.error().c_str());
+    } else if (!strcmp(unit, "rack2_fma")) {
+        rc = run_fx<ol::gpu::FxRack2Bank>(I / 2, T, in, out, 2, OLB_MODE_FMA);
     } else if (!strcmp(unit, "rack2") || !strcmp(unit, "delay2")) {
         // the stereo banks: `instances` here counts FLOATS per frame (2 per stereo instance), as the buffers are sized by it
         rc = !strcmp(unit, "rack2") ? run_fx<ol::gpu::FxRack2Bank>(I / 2, T, in, out, 2) : run_fx<ol::gpu::DelayFx2Bank>(I / 2, T, in, out, 2);

@@ -71,6 +71,29 @@ def test_stereo_fx_mirrors(orc, tmp_path, unit, name):
         assert np.array_equal(bits(y[:, i, :]), bits(want)), (unit, i)
 
 
+def test_fx_mirrors_in_the_fused_tier(orc, tmp_path):
+    """FxRackBank::SetMode(OLB_MODE_FMA) / FxRack2Bank::SetMode: the C++ mirrors reach olb_fx_set_mode / olb_fx2_set_mode."""
+    I, T = 40, 700
+    ev = [(0, loader.EV_HW_CC, 35, 0.3), (0, loader.EV_MIDI_CC, 41, 90)]
+    x = orc.noise(55, 0, I, 0, T, 0.5)
+    run("rack_fma", I, T, x, tmp_path)
+    y = np.fromfile(tmp_path / "out.f32", dtype=np.float32).reshape(T, I)
+    run("rack2_fma", I, T, x, tmp_path)
+    y2 = np.fromfile(tmp_path / "out.f32", dtype=np.float32).reshape(T, I // 2, 2)
+    exact = orc.fxrack(np.ascontiguousarray(x[:, 7:8]), 48000.0, ev)
+    try:
+        orc.fx_mode(True)
+        for i in (0, 7, 39):
+            want = orc.fxrack(np.ascontiguousarray(x[:, i:i + 1]), 48000.0, ev)
+            assert np.array_equal(bits(y[:, i]), bits(want[:, 0])), i
+        for i in (0, 5, 19):
+            want = orc.fxrack(np.ascontiguousarray(x.reshape(T, I // 2, 2)[:, i, :]), 48000.0, ev)
+            assert np.array_equal(bits(y2[:, i, :]), bits(want)), i
+    finally:
+        orc.fx_mode(False)
+    assert not np.array_equal(bits(y[:, 7]), bits(exact[:, 0]))
+
+
 def test_stereo_chorus_mirror(orc, tmp_path):
     """ol::gpu::StereoChorusBank (stereo-chorus.rnbopat): left = phase 1, right = phase 0, shared rate / depth / pitch."""
     I, T = 6, 2000

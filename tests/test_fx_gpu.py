@@ -9,7 +9,7 @@ import pytest
 import torch
 
 from oracle import loader
-from ol_dsp_b200 import FxBank, fx
+from ol_dsp_b200 import MODE_EXACT, MODE_FMA, FxBank, _lib, fx
 from tests.golden import make_golden as mg
 
 pytestmark = pytest.mark.gpu
@@ -25,11 +25,13 @@ def sha(a):
     return hashlib.sha256(np.ascontiguousarray(a).tobytes()).hexdigest()
 
 
-def run_bank(kind, x, events_per_instance, sr=48000.0, extra_cuts=()):
+def run_bank(kind, x, events_per_instance, sr=48000.0, extra_cuts=(), mode=None):
     """x: [frames][instances].  events_per_instance[i] = list of (frame, kind, cc, value) applied before that frame;
     the block is cut at every event frame (setters take effect at the next Process call)."""
     T, I = x.shape
     b = FxBank(kind, I, sample_rate=sr)
+    if mode is not None:
+        b.SetMode(mode)
     cuts = sorted({0, T} | {e[0] for ev in events_per_instance for e in ev} | set(extra_cuts))
     dx = torch.from_numpy(np.ascontiguousarray(x)).cuda()
     dy = torch.empty_like(dx)
@@ -238,10 +240,12 @@ def test_plate_rack_bank_with_reverb_controls(orc):
 
 
 # ---- stereo instances: the reference's <2> templates (olb_fx2_*) ----------------------------------------------------------
-def run_bank2(kind, x, events_per_instance, sr=48000.0, extra_cuts=(), prefill=0.0, host=False, in_place=False):
+def run_bank2(kind, x, events_per_instance, sr=48000.0, extra_cuts=(), prefill=0.0, host=False, in_place=False, mode=None):
     """x: [frames][instances][2].  Same control-script convention as run_bank."""
     T, I, _ = x.shape
     b = FxBank(kind, I, sample_rate=sr, channels=2)
+    if mode is not None:
+        b.SetMode(mode)
     cuts = sorted(c for c in ({0, T} | {e[0] for ev in events_per_instance for e in ev} | set(extra_cuts)) if c <= T)  # later events never fire
     dx = torch.from_numpy(np.ascontiguousarray(x)).cuda()
     dy = dx if in_place else torch.full_like(dx, prefill)
@@ -374,3 +378,145 @@ def test_cc_maps_sweep_every_controller_number(orc, kind):
             for cc in range(128):
                 want = getattr(orc, NAMES[kind])(x1, 48000.0, evs[cc])
                 assert np.array_equal(bits(y[:, cc]), bits(want[:, 0])), (NAMES[kind], cc, evk, v)
+
+
+# ---- the fused tier: olb_fx_set_mode(OLB_MODE_FMA) ---------------------------------------------------------------------------
+@pytest.fixture
+def fused(orc):
+    """The oracle switched to the fused forms (orc_fx_set_mode) for one test."""
+    orc.fx_mode(True)
+    yield orc
+    orc.fx_mode(False)
+
+
+FMA_VARIANTS = [{"OLB_FX_KERNEL": "simple"}, {"OLB_FX_KERNEL": "pf"}, {"OLB_FX_KERNEL": "tma"},
+                {"OLB_FX_KERNEL": "tma", "OLB_FX_SPLIT": "0", "OLB_FX_TMA_CFG": "32x4"}, {"OLB_FX_KERNEL": "tma", "OLB_FX_SPLIT": "0", "OLB_FX_TMA_CFG": "64x8"},
+                {"OLB_FX_KERNEL": "tma", "OLB_FX_SPLIT_G": "1", "OLB_FX_TMA_CFG": "32x4"}, {"OLB_FX_KERNEL": "tma", "OLB_FX_SPLIT_G": "2", "OLB_FX_TMA_CFG": "64x4"},
+                {"OLB_FX_KERNEL": "tma", "OLB_FX_SPLIT_G": "4", "OLB_FX_TMA_CFG": "32x4"}]
+
+
+@pytest.mark.parametrize("env", FMA_VARIANTS, ids=lambda e: "-".join(e.values()))
+@pytest.mark.parametrize("kind", [fx.FILTER, fx.DELAY, fx.REVERB, fx.RACK])
+def test_fma_tier_every_kernel_variant_is_bit_exact_against_the_fused_oracle(fused, monkeypatch, env, kind):
+    """OLB_MODE_FMA is a DEFINED arithmetic, not "whatever the compiler contracts": every kernel variant computes the bits of
+    the oracle's fused forms (oracle/olb_oracle.cpp svf_half / ring_read / delay_tick / reverb_tick with fast = 1).  Same bank
+    as the EXACT variant test -- delays either side of the look-ahead thresholds, ragged cuts, pointer wrap -- with resonance,
+    drive and every filter type in play so that each fused operation carries signal."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    I, T = 84, 50000
+    x = fused.noise(13, 0, I, 0, T, 0.5)
+    times = [0.0, 1.0, 0.0001, 0.0002, 0.0003, 0.0004, 0.0005, 0.001, 0.0053, 0.0054, 0.0055, 0.0106, 0.0107, 0.0213, 0.0214]
+    evs = [[(0, loader.EV_HW_CC, 35, times[i] if i < len(times) else 0.05 + 0.9 * i / I), (0, loader.EV_MIDI_CC, 38, (i * 5) % 128),
+            (0, loader.EV_MIDI_CC, 36, 20 + i), (0, loader.EV_MIDI_CC, 39, 127 - i), (0, loader.EV_MIDI_CC, 40, (i * 3) % 100), (0, loader.EV_MIDI_CC, 41, (i * 7) % 128),
+            (0, loader.EV_MIDI_CC, 42, 30 + i), (0, loader.EV_MIDI_CC, 43, 50 + (i % 60)), (0, loader.EV_MIDI_CC, 45, (i * 11) % 128), (0, loader.EV_MIDI_CC, 46, i)]
+           for i in range(I)]
+    y = run_bank(kind, x, evs, extra_cuts=(1, 8, 17, 2000, 2001, 4097, 47990), mode=MODE_FMA)
+    name = NAMES[kind]
+    for i in list(range(16)) + [31, 32, 63, 64, 70, 83]:
+        want = getattr(fused, name)(np.ascontiguousarray(x[:, i:i + 1]), 48000.0, evs[i])
+        assert np.array_equal(bits(y[:, i]), bits(want[:, 0])), (env, name, i)
+
+
+def test_fma_tier_is_another_arithmetic_and_exact_is_untouched_by_the_switch(orc):
+    """Not vacuous, and reversible: on a resonant rack the FMA tier's bits differ from EXACT's; switching back mid-stream
+    continues in EXACT arithmetic from the FMA tier's state (the oracle does the same switch at the same frame)."""
+    I, T, cut = 40, 6000, 2500
+    x = orc.noise(14, 0, I, 0, T, 0.5)
+    ev = [(0, loader.EV_HW_CC, 35, 0.004), (0, loader.EV_MIDI_CC, 36, 90), (0, loader.EV_MIDI_CC, 39, 80), (0, loader.EV_MIDI_CC, 40, 90), (0, loader.EV_MIDI_CC, 41, 64)]
+    y_exact = run_bank(fx.RACK, x, [ev] * I, mode=MODE_EXACT)
+    y_fma = run_bank(fx.RACK, x, [ev] * I, mode=MODE_FMA)
+    assert np.array_equal(bits(y_exact[:, 3]), bits(orc.fxrack(np.ascontiguousarray(x[:, 3:4]), 48000.0, ev)[:, 0]))
+    assert not np.array_equal(bits(y_exact), bits(y_fma))
+    b = FxBank(fx.RACK, I)
+    for (_, k, cc, v) in ev:
+        b.UpdateHardwareControl(cc, v) if k == loader.EV_HW_CC else b.UpdateMidiControl(cc, int(v))
+    dx = torch.from_numpy(x).cuda()
+    dy = torch.empty_like(dx)
+    b.SetMode(MODE_FMA)
+    b.ProcessDevice(dx.data_ptr(), dy.data_ptr(), cut)
+    b.SetMode(MODE_EXACT)
+    b.ProcessDevice(dx[cut:].data_ptr(), dy[cut:].data_ptr(), T - cut)
+    torch.cuda.synchronize()
+    y = dy.cpu().numpy()
+    assert np.array_equal(bits(y[:cut]), bits(y_fma[:cut]))
+    assert not np.array_equal(bits(y[cut:]), bits(y_exact[cut:])) and not np.array_equal(bits(y[cut:]), bits(y_fma[cut:]))
+    np.testing.assert_allclose(y[cut:], y_exact[cut:], rtol=0, atol=1e-4)
+    L = _lib.lib()
+    assert L.olb_fx_set_mode(b.h, 2) == _lib.E_ARG and L.olb_fx_set_mode(b.h, -1) == _lib.E_ARG and L.olb_fx_set_mode(None, 0) == _lib.E_ARG
+    b.close()
+    p = FxBank(fx.RACK_PLATE, 2)
+    assert L.olb_fx_set_mode(p.h, MODE_FMA) == _lib.E_ARG and L.olb_fx_set_mode(p.h, MODE_EXACT) == _lib.OK
+    p.close()
+
+
+E, H = loader.EV_MIDI_CC, loader.EV_HW_CC
+FMA_CORNERS = {
+    "default": [],
+    "script": mg.FX_EVENTS,
+    "resonant": [(0, H, 35, 0.05), (0, E, 36, 120), (0, E, 38, 100), (0, E, 39, 110), (0, E, 40, 100), (0, E, 41, 60), (0, E, 42, 90), (0, E, 43, 90)],
+    "all controllers at maximum": [(0, H, 35, 0.0005)] + [(0, E, c, 127) for c in (36, 38, 39, 40, 41, 42, 43, 34)],
+    "middle": [(0, H, 35, 0.3)] + [(0, E, c, 64) for c in (36, 38, 39, 40, 41, 42, 43)],
+}
+FMA_TOL = 1e-4  # of max(1, peak of the EXACT output); include/olbank.h states it, DESIGN.md section 6 has the measured figures
+
+
+@pytest.mark.parametrize("kind", [fx.FILTER, fx.DELAY, fx.REVERB, fx.RACK])
+def test_fma_tier_stays_within_its_stated_tolerance_over_ten_seconds(fused, kind):
+    """The tolerance olbank.h states for OLB_MODE_FMA, measured on the device: 480 000 frames of 0.9-scale noise through five
+    corners of the CC maps (one instance each, 11 bystanders), FMA against EXACT from the same bank type.  The worst corner
+    -- every controller at 127: feedback at its maximum, the loop peaks in the thousands -- is where the two roundings
+    drift apart most (about 2e-5 of the peak); anywhere the output stays below 16 they agree to 5e-7."""
+    T, I = 480000, 16
+    names = list(FMA_CORNERS)
+    x = np.repeat(fused.noise(91, 0, 1, 0, T, 0.9), I, axis=1)
+    evs = [FMA_CORNERS[names[i % len(names)]] for i in range(I)]
+    y_exact = run_bank(kind, x, evs, mode=MODE_EXACT)
+    y_fma = run_bank(kind, x, evs, mode=MODE_FMA)
+    assert np.isfinite(y_exact).all() and np.isfinite(y_fma).all()
+    worst = {}
+    for i, n in enumerate(names):
+        peak = float(np.abs(y_exact[:, i]).max())
+        d = float(np.abs(y_fma[:, i] - y_exact[:, i]).max())
+        worst[n] = (d / max(1.0, peak), peak)
+        assert d <= FMA_TOL * max(1.0, peak), (NAMES[kind], n, d, peak)
+        if peak < 16.0:
+            assert d <= 2e-6 * max(1.0, peak), (NAMES[kind], n, d, peak)
+    print(f"\n{NAMES[kind]} |FMA - EXACT| / max(1, peak) over 10 s:", {k: f"{v[0]:.2e} (peak {v[1]:.1f})" for k, v in worst.items()})
+    i = names.index("resonant")  # and the long stream still equals the fused oracle bit for bit
+    want = getattr(fused, NAMES[kind])(np.ascontiguousarray(x[:, i:i + 1]), 48000.0, evs[i])
+    assert np.array_equal(bits(y_fma[:, i]), bits(want[:, 0]))
+
+
+@pytest.mark.parametrize("kind", [fx.FILTER, fx.DELAY, fx.REVERB, fx.RACK])
+def test_fma_tier_stereo_banks(fused, kind):
+    """olb_fx2_set_mode: both channels in the fused forms, through both of DelayFx<2>'s channel-1 kernels, the static-scratch
+    entry point included."""
+    I, T = 36, 9000
+    x = fused.noise(15, 0, 2 * I, 0, T, 0.5).reshape(T, I, 2)
+    for short in ((False, True) if kind == fx.DELAY else (False,)):
+        evs = []
+        for i in range(I):
+            t = 0.0004 if (short and i == 7) else 0.2 + 0.6 * i / I
+            evs.append([(0, H, 35, t), (0, E, 36, 40 + i), (0, E, 39, 30 + 2 * i), (0, E, 40, 20 + 2 * i), (0, E, 41, 10 * (i % 12)), (0, E, 42, 60), (0, E, 43, 70),
+                        (5000, loader.EV_INIT, 0, 44100.0)])
+        prefill = 0.25 if kind == fx.FILTER else 0.0
+        y, kernels = run_bank2(kind, x.copy(), evs, prefill=prefill, mode=MODE_FMA)
+        if kind == fx.DELAY:
+            assert kernels == ({"k_fx2_delay1"} if short else {"k_fx2_put"}), kernels
+        for i in (0, 7, 20, 35):
+            kw = {"prefill": prefill} if kind == fx.FILTER else {}
+            w = getattr(fused, NAMES[kind])(np.ascontiguousarray(x[:, i, :]), 48000.0, evs[i], **kw)
+            assert np.array_equal(bits(y[:, i, :]), bits(w)), (NAMES[kind], short, i)
+    b = FxBank(kind, I, channels=2)
+    b.SetMode(MODE_FMA)
+    for (_, k, cc, v) in evs[0][:-1]:
+        b.UpdateHardwareControl(cc, v) if k == H else b.UpdateMidiControl(cc, int(v))
+    dx = torch.from_numpy(np.ascontiguousarray(x)).cuda()
+    dy = torch.full_like(dx, 0.25 if kind == fx.FILTER else 0.0)
+    b.ProcessDeviceStatic(dx.data_ptr(), dy.data_ptr(), T)
+    torch.cuda.synchronize()
+    kw = {"prefill": 0.25} if kind == fx.FILTER else {}
+    w = getattr(fused, NAMES[kind])(np.ascontiguousarray(x[:, 5, :]), 48000.0, evs[0][:-1], **kw)
+    assert np.array_equal(bits(dy[:, 5, :].cpu().numpy()), bits(w))
+    b.close()

@@ -374,3 +374,27 @@ def test_chorus_restatement_properties(orc):
     # with the gen~ pitch shifter in front (pitch 0: the input half a 10 ms window late) the same impulse arrives 240 frames later
     w = orc.chorus(imp, mix=1.0, depth=1.0, rate=0.0, phase=0.0)
     assert int(np.nonzero(w)[0][0]) == first + 240
+
+
+def test_fx_fused_tier_of_the_oracle_is_opt_in_and_close(orc, ref):
+    """orc_fx_set_mode: the fused forms that specify the fx banks' OLB_MODE_FMA.  Off by default (the goldens above ran
+    without it), the compiled reference has no such switch, the voice's filter is never fused, and over a second of noise
+    through a resonant rack the tier stays within 1e-6 of the separately rounded arithmetic while differing in its bits."""
+    T = 48000
+    x = orc.noise(92, 0, 1, 0, T, 0.9)
+    ev = [(0, loader.EV_HW_CC, 35, 0.05)] + [(0, loader.EV_MIDI_CC, c, v) for c, v in ((36, 120), (38, 100), (39, 110), (40, 100), (41, 60), (42, 90), (43, 90))]
+    exact = {n: getattr(orc, n)(x, 48000.0, ev) for n in ("filterfx", "delayfx", "reverbfx", "fxrack")}
+    voice = orc.voice(2000, ev=[(0, loader.EV_NOTE_ON, 60, 100.0)])
+    try:
+        orc.fx_mode(True)
+        for n, a in exact.items():
+            b = getattr(orc, n)(x, 48000.0, ev)
+            assert not np.array_equal(a.view(np.uint32), b.view(np.uint32)), n
+            assert np.abs(a - b).max() <= 1e-6 * max(1.0, float(np.abs(a).max())), n
+        again = orc.voice(2000, ev=[(0, loader.EV_NOTE_ON, 60, 100.0)])
+        assert np.array_equal(np.asarray(voice).view(np.uint32), np.asarray(again).view(np.uint32)) and np.abs(voice).max() > 0
+    finally:
+        orc.fx_mode(False)
+    for n, a in exact.items():
+        assert np.array_equal(a.view(np.uint32), getattr(orc, n)(x, 48000.0, ev).view(np.uint32)), n
+        assert np.array_equal(a.view(np.uint32), getattr(ref, n)(x, 48000.0, ev).view(np.uint32)), n

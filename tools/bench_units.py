@@ -68,6 +68,7 @@ def bench_fx(a, kind, name, bytes_per_unit):
     from ol_dsp_b200 import FxBank, noise_device
     I, F = a.instances, a.frames
     b = FxBank(kind, I)
+    b.SetMode({"exact": 0, "fma": 1}[a.mode])
     b.UpdateHardwareControl(35, (0.05 + 0.9 * np.arange(I) / I).astype(np.float32))  # CC_DELAY_TIME sweep
     x = torch.empty((F, I), dtype=torch.float32, device="cuda")
     noise_device(x.data_ptr(), 0x01D5B200, 0, I, 0, F, 0.25)
@@ -75,7 +76,7 @@ def bench_fx(a, kind, name, bytes_per_unit):
     st = torch.cuda.current_stream().cuda_stream
     dt = timed(lambda: b.ProcessDevice(x.data_ptr(), y.data_ptr(), F, st), a.steps)
     units = I * F
-    line = {"unit": name, "metric": "instance-samples/s", "value": units / dt, "ms_per_step": dt * 1e3, "instances": I, "frames": F,
+    line = {"unit": name, "mode": a.mode, "metric": "instance-samples/s", "value": units / dt, "ms_per_step": dt * 1e3, "instances": I, "frames": F,
             "roofline": {"bound": "hbm", "algorithmic_bytes_per_unit": bytes_per_unit, "achieved": bytes_per_unit * units / dt / 1e9,
                          "peak": peaks(), "unit": "GB/s", "frac": bytes_per_unit * units / dt / 1e9 / peaks()},
             "kernel": b.LastKernel(), "env": {k: v for k, v in os.environ.items() if k.startswith("OLB_")},
@@ -231,6 +232,7 @@ if __name__ == "__main__":
     p.add_argument("--frames", type=int, default=48000)
     p.add_argument("--steps", type=int, default=3)
     p.add_argument("--cpu", action="store_true")
+    p.add_argument("--mode", choices=["exact", "fma"], default="exact", help="fx units: the arithmetic tier (olb_fx_set_mode)")
     a = p.parse_args()
     from ol_dsp_b200 import fx as _fx
     {"voices": bench_voices, "dattorro": bench_dattorro, "chorus": bench_chorus, "sampler": bench_sampler, "filterfx": lambda a: bench_fx(a, _fx.FILTER, "filterfx", 8),
