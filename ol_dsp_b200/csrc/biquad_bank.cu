@@ -31,7 +31,7 @@
 #include "common.cuh"
 #include "tmap.h"
 #include "biquad_sys.cuh"
-#include "biquad_skew.cuh"
+#include "biquad_roll.cuh"
 
 namespace olb {
 
@@ -841,18 +841,35 @@ static int launch_sys(olb_biquad *h, const float *in, float *out, uint32_t frame
 struct SkewCfg {
     int tb, nst, lag;
     bool roll;
+    int spw = 0;        // > 0: k_bq_roll, two channels per lane and spw sections per warp (FAST tier, 8 sections)
 };
-static SkewCfg skew_cfg_auto(uint32_t C, uint32_t frames) {
+static SkewCfg skew_cfg_auto(uint32_t C, uint32_t frames, bool fast8) {
     SkewCfg env{};
     if (const char *e = getenv("OLB_BQ_SKEW_CFG")) {  // read per call: a tuning aid, cheap next to a launch
         char r = 0;
-        const int n = sscanf(e, "%dx%dx%d%c", &env.tb, &env.nst, &env.lag, &r);
+        int spw = 2;
+        const int n = sscanf(e, "%dx%dx%d%c%d", &env.tb, &env.nst, &env.lag, &r, &spw);
         if (n >= 3) {
-            env.roll = n == 4 && r == 'r';
+            env.roll = n >= 4 && r == 'r';
+            env.spw = n >= 4 && r == 'c' ? spw : 0;
             return env;
         }
     }
     const uint32_t ctas = (C + 31) / 32, per_sm = (ctas + 147) / 148;
+    // FAST tier, 8 sections: k_bq_roll (64-channel CTAs, two channels per lane) where it puts ONE warp on a scheduler:
+    // 4 737 .. 9 472 channels with two sections per warp (8 192 channels: 37.6 cycles per frame against 40.2), 14 209 .. 18 944
+    // with four (16 384: 63.6 against 73.5); in between three 32-channel CTAs per SM are the finer fit (12 288: 55.1 against
+    // 66.7).  profiles/r02_run44_roll_sweep.txt.  lag: 4 = stores four positions late, 5 = and two blocks per trip.
+    if (fast8 && per_sm == 2 && frames >= 512) {
+        SkewCfg c = frames >= 1024 ? SkewCfg{128, 6, 4, false} : SkewCfg{64, 6, 4, false};
+        c.spw = 2;
+        return c;
+    }
+    if (fast8 && per_sm == 4 && ctas > 3 * 148 && frames >= 512) {
+        SkewCfg c{64, 6, 5, false};
+        c.spw = 4;
+        return c;
+    }
     // the first and the last tile of a launch run the frame-by-frame path: short blocks keep the short tiles
     if (per_sm <= 1)  // the SM to itself: 192 KiB (256 rows is the tallest TMA box)
         return frames >= 4096 ? SkewCfg{256, 6, 4, true} : frames >= 3072 ? SkewCfg{192, 8, 4, true} : SkewCfg{48, 32, 4, true};
@@ -870,9 +887,30 @@ static SkewCfg skew_cfg_auto(uint32_t C, uint32_t frames) {
 template <int MODE>
 static int launch_skew(olb_biquad *h, const float *in, float *out, uint32_t frames, cudaStream_t st) {
     const uint32_t S = h->S;
-    SkewCfg c = skew_cfg_auto(h->C, frames);
+    SkewCfg c = skew_cfg_auto(h->C, frames, MODE == OLB_MODE_FAST && h->S == 8);
     if (MODE != OLB_MODE_FAST) c.roll = false;  // the rolled tile is the FAST tier's
     if (S != 8) c = SkewCfg{24, 8, 4, false};
+    if (c.spw && MODE == OLB_MODE_FAST && S == 8) {
+        h->last_kernel = "k_bq_roll";
+#define OLB_ROLL_TRY(SPW_, TB_, NST_)                                                                                                                       \
+    if (c.spw == SPW_ && c.tb == TB_ && c.nst == NST_) {                                                                                                    \
+        if (c.lag == 0) return launch_roll_cfg<8, SPW_, TB_, NST_, 0, 1>(h->C, h->d_coef, h->d_hist, in, out, frames, st);                                  \
+        if (c.lag == 1) return launch_roll_cfg<8, SPW_, TB_, NST_, 0, 2>(h->C, h->d_coef, h->d_hist, in, out, frames, st);                                  \
+        if (c.lag == 5) return launch_roll_cfg<8, SPW_, TB_, NST_, 4, 2>(h->C, h->d_coef, h->d_hist, in, out, frames, st);                                  \
+        return launch_roll_cfg<8, SPW_, TB_, NST_, 4, 1>(h->C, h->d_coef, h->d_hist, in, out, frames, st);                                                  \
+    }
+        OLB_ROLL_TRY(2, 128, 6)
+        OLB_ROLL_TRY(2, 96, 8)
+        OLB_ROLL_TRY(2, 64, 6)
+        OLB_ROLL_TRY(2, 32, 6)
+        OLB_ROLL_TRY(4, 128, 3)
+        OLB_ROLL_TRY(4, 64, 6)
+        OLB_ROLL_TRY(4, 32, 6)
+#undef OLB_ROLL_TRY
+        set_error("olb_biquad_process: no compiled k_bq_roll shape spw=%d tb=%d nst=%d", c.spw, c.tb, c.nst);
+        return OLB_E_ARG;
+    }
+    c.spw = 0;
     OLB_SKEW_TRY(8, 256, 6, 4, 4, true)
     OLB_SKEW_TRY(8, 192, 8, 4, 4, true)
     OLB_SKEW_TRY(8, 128, 6, 4, 4, true)

@@ -187,8 +187,10 @@ __device__ __forceinline__ void skew_block8(float *colt, const u64 (&k)[5], floa
 #undef OLB_SKEW_POS
 }
 
-template <int TB, int D, int kSkewLag, bool GAIN, bool ROLL>
-__device__ __forceinline__ void skew_tile_fast(float *col, const u64 (&k)[5], float gain, u64 &x1, u64 &x2, u64 &y1, u64 &y2,
+// nb: the rolled form runs 8 * nb >= 16 rows from `col` on (any run of rows in which both halves carry real frames: whole
+// tiles in mid-stream, and what is left of the stream's first and last tiles); the unrolled form always runs TB rows.
+template <int TB, int D, int kSkewLag, bool GAIN, bool ROLL, bool WHOLE>
+__device__ __forceinline__ void skew_tile_fast(float *col, int nb, const u64 (&k)[5], float gain, u64 &x1, u64 &x2, u64 &y1, u64 &y2,
                                                float (&p)[kSkewLag], u64 one, u64 negzero) {
     if constexpr (!ROLL || kSkewLag != 4 || TB % 8 != 0 || TB < 24) {
         skew_tile_fast_unrolled<TB, D, kSkewLag, GAIN>(col, k, gain, x1, x2, y1, y2, p, one, negzero);
@@ -206,13 +208,15 @@ __device__ __forceinline__ void skew_tile_fast(float *col, const u64 (&k)[5], fl
 #pragma unroll
         for (int q = 0; q < 3; q++) xr[q] = col[(8 + q) * 32];  // frames 0 .. 2 are consumed: their slots take frames 8 .. 10
         float *colt = col;
-        constexpr int NS = TB / 8 - 2;  // steady-state blocks, two per trip (halves the copies that restore the loop's register names)
+        // steady-state blocks, two per trip (halves the copies that restore the loop's register names); WHOLE: a mid-stream
+        // tile, the count known at compile time
+        const int NS = (WHOLE ? TB / 8 : nb) - 2;
 #pragma unroll 1
         for (int i = 0; i < NS / 2; i++, colt += 16 * 32) {
             skew_block8<GAIN, 8, false, kSkewLag>(colt, k, gain, V, Y, A, B, C, xr, p);
             skew_block8<GAIN, 8, false, kSkewLag>(colt + 8 * 32, k, gain, V, Y, A, B, C, xr, p);
         }
-        if (NS % 2) {
+        if (NS & 1) {
             skew_block8<GAIN, 8, false, kSkewLag>(colt, k, gain, V, Y, A, B, C, xr, p);
             colt += 8 * 32;
         }
@@ -279,16 +283,10 @@ __global__ void __launch_bounds__((S / 2) * 32) k_bq_skew(const __grid_constant_
         mbar_wait(&bar[st * W + warp], par);
         float *col = tiles + (size_t) st * TB * CH + lane;
         const uint32_t m0 = i * TB;
-        if (m0 >= hi0 && m0 + TB <= lo0 + frames) {  // both halves carry real frames throughout the tile
-            if (MODE == OLB_MODE_FAST) {
-                if (with_gain) skew_tile_fast<TB, D, kSkewLag, true, ROLL>(col, k, gain, x1, x2, y1, y2, p, one, negzero);
-                else skew_tile_fast<TB, D, kSkewLag, false, ROLL>(col, k, gain, x1, x2, y1, y2, p, one, negzero);
-            } else {
-                skew_tile<MODE, TB, D, kSkewLag, false>(col, k, 0ull, x1, x2, y1, y2, p, one, negzero);
-            }
-        } else {
-            const uint32_t rows = min((uint32_t) TB, total - m0);
-            for (uint32_t r = 0; r < rows; r++) {
+        const uint32_t rows = min((uint32_t) TB, total - m0);
+        constexpr bool kRolled = ROLL && MODE == OLB_MODE_FAST && kSkewLag == 4 && TB % 8 == 0 && TB >= 24;
+        auto general = [&](uint32_t ra, uint32_t rb) {  // frame by frame, halves frozen outside their frames
+            for (uint32_t r = ra; r < rb; r++) {
                 const uint32_t m = m0 + r;
                 const bool lo_on = m >= lo0 && m < lo0 + frames, hi_on = m >= hi0 && m < hi0 + frames;
                 float xin = col[r * CH];
@@ -304,6 +302,30 @@ __global__ void __launch_bounds__((S / 2) * 32) k_bq_skew(const __grid_constant_
                 for (int q = kSkewLag - 1; q > 0; q--) p[q] = p[q - 1];
                 p[0] = ylo;
                 col[r * CH] = yhi;
+            }
+        };
+        if (m0 >= hi0 && m0 + TB <= lo0 + frames) {  // mid-stream: both halves carry real frames throughout the tile
+            if (MODE == OLB_MODE_FAST) {
+                if (with_gain) skew_tile_fast<TB, D, kSkewLag, true, ROLL, true>(col, TB / 8, k, gain, x1, x2, y1, y2, p, one, negzero);
+                else skew_tile_fast<TB, D, kSkewLag, false, ROLL, true>(col, TB / 8, k, gain, x1, x2, y1, y2, p, one, negzero);
+            } else {
+                skew_tile<MODE, TB, D, kSkewLag, false>(col, k, 0ull, x1, x2, y1, y2, p, one, negzero);
+            }
+        } else if constexpr (!kRolled) {
+            general(0, rows);  // (this branch as it was before the rolled tile learnt to run part of a tile: the unrolled
+                               // tiles' code is sensitive to what surrounds it, 12 288 channels 55.2 -> 60.5 cycles per frame otherwise)
+        } else {
+            // the rows of this tile at which both halves carry real frames: positions [hi0, lo0 + frames); the rolled tile
+            // takes them in blocks of eight, the frame-by-frame path the <= 7 + kSkewLag rows at either end
+            const int lo = min(max((int) hi0 - (int) m0, 0), (int) rows), hi = min(max((int) (lo0 + frames) - (int) m0, 0), (int) rows);
+            const int nb = hi > lo ? (hi - lo) / 8 : 0;
+            if (nb < 2) {
+                general(0, rows);
+            } else {
+                general(0, (uint32_t) lo);
+                if (with_gain) skew_tile_fast<TB, D, kSkewLag, true, true, false>(col + lo * CH, nb, k, gain, x1, x2, y1, y2, p, one, negzero);
+                else skew_tile_fast<TB, D, kSkewLag, false, true, false>(col + lo * CH, nb, k, gain, x1, x2, y1, y2, p, one, negzero);
+                general((uint32_t) (lo + 8 * nb), rows);
             }
         }
         if (warp < W - 1) {

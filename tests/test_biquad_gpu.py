@@ -214,11 +214,11 @@ def test_skewed_pairs_bit_exact(orc, S, mode, C, chunks):
     assert np.array_equal(bits(st), bits(ost))
 
 
-@pytest.mark.parametrize("C,chunks,cfg", [(4096, [3500, 3100, 3072], None), (4096, [4100, 4096, 4353], None), (8192, [1600, 2000, 1536], None), (8192, [2048, 2300], None), (1024, [3333], None),
+@pytest.mark.parametrize("C,chunks,cfg", [(4096, [3500, 3100, 3072], None), (4096, [4100, 4096, 4353], None), (8192, [1600, 2000, 1536], "96x8x4r"), (8192, [2048, 2300], "128x6x4r"), (1024, [3333], None),
                                           (4096, [700], "24x8x4r"), (4096, [1000], "48x8x4r"), (4096, [2000], "96x16x4r")])
 def test_skewed_pairs_rolled_tile(orc, C, chunks, cfg, monkeypatch):
     """The FAST tier's rolled tile in every compiled height: 256 and 192 frames (<= 4 736 channels, blocks of 4 096 / 3 072 frames or more),
-    128 and 96 (<= 9 472 channels, 2 048 / 1 536 or more), 48 and 24; several calls so that the pipeline's fill from and drain into the
+    128 and 96 (two CTAs per SM; since k_bq_roll took the 4 737 .. 9 472-channel banks these are reached by name), 48 and 24; several calls so that the pipeline's fill from and drain into the
     bank's history format is exercised at tile boundaries that move from call to call."""
     if cfg:
         monkeypatch.setenv("OLB_BQ_SKEW_CFG", cfg)
@@ -239,6 +239,44 @@ def test_skewed_pairs_rolled_tile(orc, C, chunks, cfg, monkeypatch):
         t0 += n
     torch.cuda.synchronize()
     pick = np.r_[0:34, C // 2 - 3:C // 2 + 30, C - 33:C]
+    x = dev[:, torch.as_tensor(pick, device="cuda")].cpu().numpy()
+    ost = np.zeros((len(pick), 8, 4), dtype=np.float32)
+    want = orc.biquad(x, np.ascontiguousarray(k[pick]), mode=loader.MODE_FAST, state=ost)
+    assert np.array_equal(bits(out.cpu().numpy()[:, pick]), bits(want))
+    assert np.array_equal(bits(b.GetState()[pick]), bits(ost))
+    b.close()
+
+
+@pytest.mark.parametrize("C,chunks,cfg", [
+    (8192, [1000, 700, 2049], "128x6x4c2"), (8192, [1000, 700, 2049], "128x6x5c2"), (8192, [1000, 700], "128x6x0c2"), (8192, [1000, 700], "128x6x1c2"),
+    (8192, [300, 90], "32x6x4c2"), (8192, [513, 64, 1], "64x6x4c2"), (16384, [1100, 1000], "128x3x4c4"), (8192, [400], "32x6x5c4"), (8188, [900, 333], "96x8x4c2"),
+    (4100, [500, 501], "64x6x4c4"), (8192, [1000, 700, 2049, 600, 100, 5000], None), (16384, [1100, 511, 1000], None), (6148, [3000], None)])
+def test_channel_pair_kernel(orc, C, chunks, cfg, monkeypatch):
+    """k_bq_roll (two channels per lane, 2 or 4 sections per warp chained in registers, rolled tile; stores in step or four
+    positions late, one or two blocks per trip) in its compiled shapes: several calls -- the pipeline fills from and drains
+    into the bank's history format at tile boundaries that move from call to call --, blocks shorter than a tile, a
+    one-frame block, a channel count that leaves the last CTA partly empty.  Without a named shape the automatic choice
+    takes it for blocks of 512 frames or more of 4 737 .. 9 472 and 14 209 .. 18 944-channel banks and k_bq_skew for the
+    shorter ones: the two alternate on ONE bank, through the bank's common history format."""
+    if cfg:
+        monkeypatch.setenv("OLB_BQ_SKEW_CFG", cfg)
+    T = sum(chunks)
+    dev = torch.empty((T, C), dtype=torch.float32, device="cuda")
+    noise_device(dev.data_ptr(), 25, 0, C, 0, T)
+    out = torch.empty_like(dev)
+    k = c2_coefs(C)
+    b = BiquadBank(C, 8)
+    b.SetMode(MODE_FAST)
+    if cfg:
+        b.SetVariant(V_SKEW)
+    b.SetCoeffs(k)
+    t0 = 0
+    for n in chunks:
+        b.ProcessDevice(dev[t0:].data_ptr(), out[t0:].data_ptr(), n)
+        assert b.LastKernel() == ("k_bq_roll" if cfg or n >= 512 else "k_bq_skew"), (n, b.LastKernel())
+        t0 += n
+    torch.cuda.synchronize()
+    pick = np.r_[0:66, C // 2 - 3:C // 2 + 30, C - 65:C]
     x = dev[:, torch.as_tensor(pick, device="cuda")].cpu().numpy()
     ost = np.zeros((len(pick), 8, 4), dtype=np.float32)
     want = orc.biquad(x, np.ascontiguousarray(k[pick]), mode=loader.MODE_FAST, state=ost)

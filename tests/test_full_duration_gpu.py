@@ -77,11 +77,12 @@ def test_headline_shape_one_block(orc, mode):
     _streamed_bank_vs_oracle(orc, 65536, mode, "k_bq_tma", 1, 24000, pick)
 
 
-@pytest.mark.parametrize("C,kernel,block", [(32768, "k_bq_tma", BLOCK), (8192, "k_bq_skew", BLOCK), (4096, "k_bq_skew", BLOCK), (4096, "k_bq_sys", 2400)])
+@pytest.mark.parametrize("C,kernel,block", [(32768, "k_bq_tma", BLOCK), (16384, "k_bq_roll", BLOCK), (12288, "k_bq_skew", BLOCK), (8192, "k_bq_roll", BLOCK), (4096, "k_bq_skew", BLOCK),
+                                               (4096, "k_bq_sys", 2400)])
 def test_wide_banks_10s_fast(orc, C, kernel, block):
     """The throughput tier over the full 10 s (20 blocks of 24 000 frames, or 200 of 2 400) at bank widths and block lengths
-    that reach each of the three TMA kernels through the automatic choice (k_bq_skew with its rolled tile in 96- and
-    192-frame tiles at 8 192 and 4 096 channels); 64 channels spread over the bank against the oracle, bit-exact."""
+    that reach each of the four TMA kernels through the automatic choice (k_bq_roll with two and four sections per warp at
+    8 192 and 16 384 channels, k_bq_skew with its unrolled and rolled tiles at 12 288 and 4 096); 64 channels spread over the bank against the oracle, bit-exact."""
     pick = sorted(set(list(range(0, 16)) + list(range(C // 2 - 8, C // 2 + 8)) + list(range(7, C, C // 16))[:16] + list(range(C - 16, C))))
     _streamed_bank_vs_oracle(orc, C, MODE_FAST, kernel, T // block, block, pick)
 
