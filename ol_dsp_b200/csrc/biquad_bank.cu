@@ -870,7 +870,11 @@ static SkewCfg skew_cfg_auto(uint32_t C, uint32_t frames, bool fast8) {
         c.spw = 4;
         return c;
     }
-    // the first and the last tile of a launch run the frame-by-frame path: short blocks keep the short tiles
+    if (!fast8) {  // EXACT / FMA tiers and other section counts: the unrolled tile (the rolled one is the FAST tier's)
+        if (per_sm <= 1) return SkewCfg{48, 32, 4, false};
+        if (per_sm <= 2) return SkewCfg{48, 16, 4, false};
+    }
+    // short blocks keep the short tiles (what is left of the stream's first and last tile beside whole 8-row blocks runs frame by frame)
     if (per_sm <= 1)  // the SM to itself: 192 KiB (256 rows is the tallest TMA box)
         return frames >= 4096 ? SkewCfg{256, 6, 4, true} : frames >= 3072 ? SkewCfg{192, 8, 4, true} : SkewCfg{48, 32, 4, true};
     if (per_sm <= 2)  // 96 KiB each
@@ -880,9 +884,11 @@ static SkewCfg skew_cfg_auto(uint32_t C, uint32_t frames, bool fast8) {
     return SkewCfg{24, 4, 4, false};                   // 12 KiB: up to 18 CTAs per SM
 }
 
-#define OLB_SKEW_TRY(S_, TB_, NST_, D_, LAG_, ROLL_)                                       \
-    if (S == S_ && c.tb == TB_ && c.nst == NST_ && c.lag == LAG_ && c.roll == ROLL_)       \
-        return launch_skew_cfg<S_, MODE, TB_, NST_, D_, LAG_, ROLL_>(h->C, h->d_coef, h->d_hist, in, out, frames, st);
+#define OLB_SKEW_TRY(S_, TB_, NST_, D_, LAG_, ROLL_)                                                                       \
+    if constexpr (!(ROLL_) || MODE == OLB_MODE_FAST) { /* no unrolled 256-frame EXACT tiles behind the rolled shapes' names */ \
+        if (S == S_ && c.tb == TB_ && c.nst == NST_ && c.lag == LAG_ && c.roll == ROLL_)                                   \
+            return launch_skew_cfg<S_, MODE, TB_, NST_, D_, LAG_, ROLL_>(h->C, h->d_coef, h->d_hist, in, out, frames, st); \
+    }
 
 template <int MODE>
 static int launch_skew(olb_biquad *h, const float *in, float *out, uint32_t frames, cudaStream_t st) {

@@ -285,6 +285,34 @@ def test_channel_pair_kernel(orc, C, chunks, cfg, monkeypatch):
     b.close()
 
 
+@pytest.mark.parametrize("mode", [MODE_EXACT, MODE_FMA])
+@pytest.mark.parametrize("C,chunks", [(8192, [2400, 1536]), (4096, [4096, 3100]), (2048, [5000]), (16384, [2400])])
+def test_mid_sized_banks_in_the_exact_and_fma_tiers_take_long_blocks(orc, mode, C, chunks):
+    """The automatic choice for 512 .. 32 767-channel banks is mode-independent (k_bq_skew), its tile shape is not: the rolled
+    tall tiles and k_bq_roll are the FAST tier's, EXACT and FMA run the unrolled 48-frame tiles whatever the block length."""
+    T = sum(chunks)
+    dev = torch.empty((T, C), dtype=torch.float32, device="cuda")
+    noise_device(dev.data_ptr(), 26, 0, C, 0, T)
+    out = torch.empty_like(dev)
+    k = c2_coefs(C)
+    b = BiquadBank(C, 8)
+    b.SetMode(mode)
+    b.SetCoeffs(k)
+    t0 = 0
+    for n in chunks:
+        b.ProcessDevice(dev[t0:].data_ptr(), out[t0:].data_ptr(), n)
+        assert b.LastKernel() == "k_bq_skew"
+        t0 += n
+    torch.cuda.synchronize()
+    pick = np.r_[0:34, C // 2 - 3:C // 2 + 30, C - 33:C]
+    x = dev[:, torch.as_tensor(pick, device="cuda")].cpu().numpy()
+    ost = np.zeros((len(pick), 8, 4), dtype=np.float32)
+    want = orc.biquad(x, np.ascontiguousarray(k[pick]), mode=mode, state=ost)
+    assert np.array_equal(bits(out.cpu().numpy()[:, pick]), bits(want))
+    assert np.array_equal(bits(b.GetState()[pick]), bits(ost))
+    b.close()
+
+
 def test_skewed_pairs_in_place(orc):
     C, T = 4096, 3000
     dev = torch.empty((T, C), dtype=torch.float32, device="cuda")
