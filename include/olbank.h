@@ -118,8 +118,9 @@ int olb_biquad_process_host(olb_biquad *h, const float *in_host, float *out_host
 /* State as the oracle lays it out: [channels][sections][4] = x1 x2 y1 y2 (host pointers). */
 int olb_biquad_get_state(olb_biquad *h, float *state_host);
 int olb_biquad_set_state(olb_biquad *h, const float *state_host);
-/* Diagnostics for bench.py: which kernel variant the last process call used, and kernel selection
- * override (0 = automatic). */
+/* Diagnostics for bench.py: which kernel the last process call used ("k_bq_tma", "k_bq_roll", "k_bq_skew", "k_bq_sys",
+ * "k_bq_direct", "k_bq_planar", "k_bq_runtime": DESIGN.md section 3 says which bank sizes take which), and kernel selection
+ * override (0 = automatic, 1 = direct, 2 = tma, 3 = sys, 4 = skew / roll).  Every kernel computes the same bits. */
 const char *olb_biquad_last_kernel(olb_biquad *h);
 int olb_biquad_set_variant(olb_biquad *h, int variant);
 
