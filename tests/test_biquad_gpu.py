@@ -313,6 +313,28 @@ def test_mid_sized_banks_in_the_exact_and_fma_tiers_take_long_blocks(orc, mode, 
     b.close()
 
 
+@pytest.mark.parametrize("C", [8192, 16384])
+def test_channel_pair_kernel_in_place(orc, C):
+    """k_bq_roll with in == out (main.cpp:82-85 calls Process in place): a tile is stored 16 or 24 frames behind where it was
+    loaded from, over rows the loader has already taken."""
+    T = 3000
+    dev = torch.empty((T, C), dtype=torch.float32, device="cuda")
+    noise_device(dev.data_ptr(), 27, 0, C, 0, T)
+    pick = np.r_[0:66, C // 2 - 3:C // 2 + 30, C - 65:C]
+    x = dev[:, torch.as_tensor(pick, device="cuda")].cpu().numpy()
+    k = c2_coefs(C)
+    b = BiquadBank(C, 8)
+    b.SetMode(MODE_FAST)
+    b.SetCoeffs(k)
+    b.ProcessDevice(dev.data_ptr(), dev.data_ptr(), 1700)
+    b.ProcessDevice(dev[1700:].data_ptr(), dev[1700:].data_ptr(), T - 1700)
+    torch.cuda.synchronize()
+    assert b.LastKernel() == "k_bq_roll"
+    want = orc.biquad(x, np.ascontiguousarray(k[pick]), mode=loader.MODE_FAST)
+    assert np.array_equal(bits(dev.cpu().numpy()[:, pick]), bits(want))
+    b.close()
+
+
 def test_skewed_pairs_in_place(orc):
     C, T = 4096, 3000
     dev = torch.empty((T, C), dtype=torch.float32, device="cuda")
