@@ -57,7 +57,9 @@ int main(int argc, char **argv) {
             a = !a;
             const float cutoff = 0.25f + 0.5f * (float) (flips.load() & 1);
             if (rc == OLB_OK) rc = olb_fx_update_hw(fx.handle(), 0, 256, 41 /* CC_FILTER_CUTOFF */, &cutoff, 0);
+            if (rc == OLB_OK) rc = olb_fx_set_mode(fx.handle(), (flips.load() & 2) ? OLB_MODE_FMA : OLB_MODE_EXACT);  // the tier of the NEXT block
             if (rc == OLB_OK) rc = olb_fx2_update_midi(rack2.handle(), 0, 64, 35 /* CC_DELAY_TIME */, (uint8_t) (20 + (flips.load() & 63)));
+            if (rc == OLB_OK) rc = olb_fx2_set_mode(rack2.handle(), (flips.load() & 4) ? OLB_MODE_FMA : OLB_MODE_EXACT);
             if (rc == OLB_OK) rc = olb_chorus_set_param(chorus.handle(), 0, 64, OLB_CHORUS_PITCH, (float) (flips.load() & 3));
             if (rc == OLB_OK) rc = olb_chorus_set_param(chorus.handle(), 0, 64, OLB_CHORUS_DEPTH, cutoff);
             if (rc == OLB_OK) rc = olb_voice_update_midi(voices.handle(), 0, 128, 41 /* CC_FILTER_CUTOFF */, (uint8_t) (40 + (flips.load() & 63)));
