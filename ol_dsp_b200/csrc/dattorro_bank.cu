@@ -699,10 +699,11 @@ struct olb_dattorro {
     HostStage host;
 };
 
-// banks up to this size take k_dattorro_smem for long blocks.  Measured (profiles/r02_run10_dattorro.txt, 48 000-frame blocks):
-// the resident kernel runs 1.5e10 instance-samples/s from 296 instances up (two plates per SM, bounded by the one-pole
-// recurrences), the HBM-ring kernel 1.8e9 at 296, 6.2e9 at 1 024, 2.4e10 from 4 736 up: they cross near 2 600 instances.
-constexpr uint32_t kSmemAutoMaxInstances = 2560;
+// banks up to this size take k_dattorro_smem for long blocks.  Measured (profiles/r02_run62_dattorro_sizes.txt, 48 000-frame
+// blocks): the resident kernel runs 1.9-2.2e10 instance-samples/s from 296 instances up (two plates per SM, bounded by the
+// one-pole recurrences), the HBM-ring kernel 1.8e9 at 296, 6.2e9 at 1 024, 1.48e10 at 2 560, 2.4e10 from 4 736 up: they cross
+// near 3 500 instances.
+constexpr uint32_t kSmemAutoMaxInstances = 3456;
 
 static void plate_geometry(PlateGeom *g, uint32_t *positions) {
     uint32_t n = 0;
@@ -861,7 +862,7 @@ OLB_API int olb_dattorro_process(olb_dattorro *h, const float *in_dev, float *ou
     if (smem_kernel) {
         OLB_CUDA(cudaFuncSetAttribute(k_dattorro_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) kSmBytes));
         OLB_CUDA(cudaFuncSetAttribute(k_dattorro_smem, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-        k_dattorro_smem<<<h->I, 96, kSmBytes, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I, h->d_slab, h->d_lp, h->d_par, h->geom,
+        k_dattorro_smem<<<h->I, kSmThreads, kSmBytes, st>>>(in_dev, out_l_dev, out_r_dev, (uint32_t) frames, h->I, h->d_slab, h->d_lp, h->d_par, h->geom,
                                                    h->t);
         h->last_kernel = "k_dattorro_smem";
     } else if (ek && !strcmp(ek, "simple")) {

@@ -4,16 +4,21 @@
 //
 // Why: the lane-per-instance kernels keep the rings in HBM ([ring position][instance]); every one of the 27 reads and 13
 // writes of a sample misses the L2 (1.4 GB of rings at 8 192 instances), 170 B of DRAM traffic per instance-sample against
-// 12 algorithmic.  Every delay of the network is >= 107 samples, so inside a block of 64 frames no ring read depends on a
+// 12 algorithmic.  Every delay of the network is >= 107 samples, so inside a block of 96 frames no ring read depends on a
 // ring write of the same block: the whole frame is ELEMENTWISE over the block -- except the three one-pole low-passes
 // (pre-filter, two damping filters), whose inputs (the pre-delay tap and the two 4 453 / 4 217-sample taps) are known
 // before the block starts.  So:
 //   one CTA = one plate, its rings in shared memory with EXACT lengths (27 390 floats = 107 KiB; two CTAs per SM)
-//   warp 0  ("scan")    loads the 64 input frames, runs the pre-delay ring, gathers the three low-pass inputs and runs the
-//                       three recurrences on lanes 0..2, 64 sequential steps (12 cycles each: sub, mul, add, all rounded
-//                       as in verb.cpp:131-134), one block AHEAD of the other warps
-//   warps 1-2 ("frame") lane = frame of the block: all tap reads, the four input all-passes, both tank halves, the 14 output
+//   warp 4  ("gather")  loads the 96 input frames (three blocks ahead), runs the pre-delay ring and gathers the inputs of the
+//                       three low-passes into a double-buffered table
+//   warp 0  ("scan")    runs the three recurrences on lanes 0..2, 96 sequential steps (12 cycles each: sub, mul, add, all
+//                       rounded as in verb.cpp:131-134) and NOTHING else: the chain is what bounds a plate, so everything
+//                       that is not the chain left this warp (with the gathering in it a block took 2 120 cycles, 768 of
+//                       them the chain: profiles/r02_run10_dattorro.txt)
+//   warps 1-3 ("frame") lane = frame of the block: all tap reads, the four input all-passes, both tank halves, the 14 output
 //                       taps, with the low-pass outputs handed over through shared memory
+// gather runs up to two blocks ahead of scan, scan up to two ahead of the frame warps (mbarrier pairs per buffer); the taps
+// the gatherer reads are >= 4 217 frames old, the pre-delay ring is its own.
 // Per-frame operation order inside every filter is the reference's, every operation rounded separately: bit-exact.
 // The one-pole chain bounds a plate at one frame per 12 cycles; an SM holds two plates.
 //
@@ -27,9 +32,11 @@
 
 namespace olb {
 
-constexpr int kSmB = 64;  // frames per block (every delay is >= 107)
+constexpr int kSmB = 96;  // frames per block (every delay is >= 107): one frame per lane of the three frame warps
+constexpr int kSmFrameWarps = kSmB / 32, kSmGatherWarp = 1 + kSmFrameWarps, kSmThreads = 32 * (2 + kSmFrameWarps);
+static_assert(kSmB % 32 == 0 && kSmB <= 106, "a block must stay shorter than the shortest delay (107) and fill whole warps");
 // exact ring lengths: the delay itself (a frame reads and then rewrites ITS OWN slot), the largest excursion for the two
-// modulated all-passes (672 + 16, 908 + 16), delay + block for the pre-delay (the scan warp WRITES the block's 64 inputs and
+// modulated all-passes (672 + 16, 908 + 16), delay + block for the pre-delay (the gather warp WRITES the block's inputs and
 // then reads: the oldest of the 4 800 samples a frame may ask for must survive the block's own writes)
 // (compile-time tables: every ring index below is a constant after unrolling, so the positions live in registers)
 struct SmGeom {
@@ -60,10 +67,17 @@ template <int I> struct SmTap {
     static constexpr int ring_l = (int) sm_geom().tap_l[I][0], ring_r = (int) sm_geom().tap_r[I][0];
     static constexpr uint32_t back_l = sm_geom().tap_l[I][1] - 1u, back_r = sm_geom().tap_r[I][1] - 1u;  // read after t++: one sample less far back
 };
-constexpr int kSmRingFloats = (int) sm_geom().total;  // 27 390
-static_assert(kSmRingFloats == 27390, "ring lengths changed");
+constexpr int kSmRingFloats = (int) sm_geom().total;  // 27 326 + block
+static_assert(kSmRingFloats == 27326 + kSmB, "ring lengths changed");
 constexpr int kSmLpStride = kSmB + 1;                                                                               // padded rows
-constexpr size_t kSmBytes = ((size_t) kSmRingFloats + 3 * kSmLpStride + 2 * 3 * kSmLpStride) * sizeof(float) + 4 * sizeof(uint64_t);
+constexpr size_t kSmBytes = ((size_t) kSmRingFloats + 2 * 3 * kSmLpStride + 2 * 3 * kSmLpStride) * sizeof(float) + 8 * sizeof(uint64_t);
+
+// a shared-memory load the compiler keeps in program order (it otherwise gathers the loads of an unrolled loop at its top)
+__device__ __forceinline__ float sm_lds(const float *p) {
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(smem_u32(p)) : "memory");
+    return v;
+}
 
 struct SmRings {
     float *base;
@@ -73,7 +87,7 @@ struct SmRings {
 #pragma unroll
         for (int r = 0; r < DV_RINGS; r++) pos[r] = 0;
     }
-    // slot of frame `n` of the block, `back` samples in the past (0 <= n < 64, 0 <= back <= len); R is a compile-time ring
+    // slot of frame `n` of the block, `back` samples in the past (0 <= n < kSmB, 0 <= back <= len); R is a compile-time ring
     template <int R>
     __device__ __forceinline__ float *at(uint32_t n, uint32_t back) const {
         constexpr uint32_t L = SmRing<R>::len;
@@ -102,15 +116,16 @@ __device__ __forceinline__ void SmRings::advance(uint32_t frames) {
     sm_for<0, DV_RINGS>([&](auto rc) { advance1<decltype(rc)::value>(frames); });
 }
 
-__global__ void __launch_bounds__(96, 2) k_dattorro_smem(const float *in, float *out_l, float *out_r, uint32_t frames, uint32_t I, float *slab,
+__global__ void __launch_bounds__(kSmThreads, 2) k_dattorro_smem(const float *in, float *out_l, float *out_r, uint32_t frames, uint32_t I, float *slab,
                                                           float *lp, const float *__restrict__ par, const __grid_constant__ PlateGeom g0,
                                                           uint32_t t0) {
     extern __shared__ __align__(16) unsigned char sm_raw[];
-    uint64_t *bars = reinterpret_cast<uint64_t *>(sm_raw);  // full[2], free[2] (first: 8-byte aligned whatever the ring lengths)
-    uint64_t *full = bars, *empty = bars + 2;
-    float *ring_base = reinterpret_cast<float *>(sm_raw + 4 * sizeof(uint64_t));
-    float *lp_in = ring_base + kSmRingFloats;        // [3][65]   inputs of the three low-passes for the block being scanned
-    float *lp_out = lp_in + 3 * kSmLpStride;         // [2][3][65] their outputs, double buffered
+    uint64_t *bars = reinterpret_cast<uint64_t *>(sm_raw);  // (first: 8-byte aligned whatever the ring lengths)
+    uint64_t *full = bars, *empty = bars + 2;         // scan -> frames: the low-pass outputs of a block; frames -> scan: done with them
+    uint64_t *in_full = bars + 4, *in_empty = bars + 6;  // gather -> scan: the low-pass inputs of a block; scan -> gather: taken
+    float *ring_base = reinterpret_cast<float *>(sm_raw + 8 * sizeof(uint64_t));
+    float *lp_in = ring_base + kSmRingFloats;        // [2][3][65] inputs of the three low-passes, double buffered
+    float *lp_out = lp_in + 2 * 3 * kSmLpStride;     // [2][3][65] their outputs, double buffered
     const uint32_t inst = blockIdx.x;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     SmRings R;
@@ -128,71 +143,100 @@ __global__ void __launch_bounds__(96, 2) k_dattorro_smem(const float *in, float 
     if (threadIdx.x == 0) {
         mbar_init(&full[0], 1);
         mbar_init(&full[1], 1);
-        mbar_init(&empty[0], 2);
-        mbar_init(&empty[1], 2);
+        mbar_init(&empty[0], kSmFrameWarps);
+        mbar_init(&empty[1], kSmFrameWarps);
+        mbar_init(&in_full[0], 1);
+        mbar_init(&in_full[1], 1);
+        mbar_init(&in_empty[0], 1);
+        mbar_init(&in_empty[1], 1);
         mbar_fence_init();
     }
     __syncthreads();
 
     const uint32_t nblocks = (frames + kSmB - 1) / kSmB;
-    if (warp == 0) {
-        // ================= scan warp: input, pre-delay ring, the three one-pole recurrences =================
-        const float f_pre = par[0 * (size_t) I + inst], f_damp = par[4 * (size_t) I + inst];
+    if (warp == kSmGatherWarp) {
+        // ================= gather warp: input, pre-delay ring, the inputs of the three one-poles =================
         const uint32_t pre_delay = (g0.mask[DV_PRE] + 1 - __float_as_uint(par[7 * (size_t) I + inst])) & 0xffffu;  // samples, 0..4800
-        float z = lane < 3 ? lp[(size_t) lane * I + inst] : 0.f;
-        const float f = lane == 0 ? f_pre : f_damp;
         // the input of a block is fetched THREE blocks ahead (one frame per lane and half block: two 4-byte loads per block,
         // each from its own DRAM sector -- the launch's input is [frames][instances] -- so their latency must stay off the path)
-        auto fetch = [&](uint32_t k, float &a, float &b) {
-            a = b = 0.f;
+        struct Xin { float v[kSmFrameWarps]; };
+        auto fetch = [&](uint32_t k, Xin &x) {
+#pragma unroll
+            for (int q = 0; q < kSmFrameWarps; q++) x.v[q] = 0.f;
             if (k < nblocks) {
                 const uint32_t nvk = min((uint32_t) kSmB, frames - k * kSmB);
-                if ((uint32_t) lane < nvk) a = in[((size_t) k * kSmB + lane) * I + inst];
-                if ((uint32_t) lane + 32 < nvk) b = in[((size_t) k * kSmB + lane + 32) * I + inst];
+#pragma unroll
+                for (int q = 0; q < kSmFrameWarps; q++)
+                    if ((uint32_t) lane + 32 * q < nvk) x.v[q] = in[((size_t) k * kSmB + lane + 32 * q) * I + inst];
             }
         };
-        float xa0, xb0, xa1, xb1, xa2, xb2;
-        fetch(0, xa0, xb0);
-        fetch(1, xa1, xb1);
-        fetch(2, xa2, xb2);
+        Xin x0, x1, x2;
+        fetch(0, x0);
+        fetch(1, x1);
+        fetch(2, x2);
         for (uint32_t k = 0; k < nblocks; k++) {
             const uint32_t buf = k & 1, nv = min((uint32_t) kSmB, frames - k * kSmB);
-            float xa3, xb3;
-            fetch(k + 3, xa3, xb3);
-            if (k >= 2) mbar_wait(&empty[buf], ((k >> 1) - 1) & 1);  // the frame warps are done with block k - 2's outputs
+            Xin x3;
+            fetch(k + 3, x3);
             // the block's input into the pre-delay ring (write, then read: verb.cpp:107-110)
-            if ((uint32_t) lane < nv) *R.at<DV_PRE>(lane, 0) = xa0;
-            if ((uint32_t) lane + 32 < nv) *R.at<DV_PRE>(lane + 32, 0) = xb0;
-            xa0 = xa1; xb0 = xb1; xa1 = xa2; xb1 = xb2; xa2 = xa3; xb2 = xb3;
+#pragma unroll
+            for (int q = 0; q < kSmFrameWarps; q++)
+                if ((uint32_t) lane + 32 * q < nv) *R.at<DV_PRE>(lane + 32 * q, 0) = x0.v[q];
+            x0 = x1; x1 = x2; x2 = x3;
             __syncwarp();
+            if (k >= 2) mbar_wait(&in_empty[buf], ((k >> 1) - 1) & 1);  // the scan warp has taken block k - 2's inputs
+            float *xi = lp_in + buf * 3 * kSmLpStride;
             for (uint32_t n = lane; n < nv; n += 32) {
-                lp_in[0 * kSmLpStride + n] = *R.at<DV_PRE>(n, pre_delay);
-                lp_in[1 * kSmLpStride + n] = *R.at<DV_PDA>(n, SmRing<DV_PDA>::delay);
-                lp_in[2 * kSmLpStride + n] = *R.at<DV_PDB>(n, SmRing<DV_PDB>::delay);
+                xi[0 * kSmLpStride + n] = *R.at<DV_PRE>(n, pre_delay);
+                xi[1 * kSmLpStride + n] = *R.at<DV_PDA>(n, SmRing<DV_PDA>::delay);
+                xi[2 * kSmLpStride + n] = *R.at<DV_PDB>(n, SmRing<DV_PDB>::delay);
             }
             __syncwarp();
-            if (lane < 3) {
-                const float *xi = lp_in + lane * kSmLpStride;
-                float *zo = lp_out + (buf * 3 + lane) * kSmLpStride;
-                if (nv == (uint32_t) kSmB) {  // a full block: all 64 inputs into registers first, then the dependent chain alone
-                    float x[kSmB];
+            if (lane == 0) mbar_arrive(&in_full[buf]);
+            R.advance(nv);
+        }
+    } else if (warp == 0) {
+        // ================= scan warp: the three one-pole recurrences, lanes 0..2 =================
+        const float f_pre = par[0 * (size_t) I + inst], f_damp = par[4 * (size_t) I + inst];
+        float z = lane < 3 ? lp[(size_t) lane * I + inst] : 0.f;
+        const float f = lane == 0 ? f_pre : f_damp;
+        for (uint32_t k = 0; k < nblocks; k++) {
+            const uint32_t buf = k & 1, nv = min((uint32_t) kSmB, frames - k * kSmB);
+            mbar_wait(&in_full[buf], (k >> 1) & 1);
+            const float *xi = lp_in + (buf * 3 + (lane < 3 ? lane : 0)) * kSmLpStride;
+            float *zo = lp_out + (buf * 3 + (lane < 3 ? lane : 0)) * kSmLpStride;
+            if (nv == (uint32_t) kSmB) {
+                // a full block: the dependent chain alone, its inputs fetched eight steps ahead in program order (a step
+                // leaves three of its four issue slots free; loading the whole block first cost 460 of a block's 1 700
+                // cycles, profiles/r02_run61_ncu_k_dattorro_smem.txt)
+                if (k >= 2) mbar_wait(&empty[buf], ((k >> 1) - 1) & 1);  // the frame warps are done with block k - 2's outputs
+                if (lane < 3) {
+                    float xw[8];
 #pragma unroll
-                    for (int j = 0; j < kSmB; j++) x[j] = xi[j];
+                    for (int j = 0; j < 8; j++) xw[j] = sm_lds(xi + j);
 #pragma unroll
                     for (int j = 0; j < kSmB; j++) {
-                        z = __fadd_rn(z, __fmul_rn(__fsub_rn(x[j], z), f));  // LowPassFilter_process, verb.cpp:131-134
+                        const float xj = xw[j & 7];
+                        if (j + 8 < kSmB) xw[j & 7] = sm_lds(xi + j + 8);
+                        z = __fadd_rn(z, __fmul_rn(__fsub_rn(xj, z), f));  // LowPassFilter_process, verb.cpp:131-134
                         zo[j] = z;
                     }
-                } else {
+                }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&in_empty[buf]);
+            } else {
+                if (k >= 2) mbar_wait(&empty[buf], ((k >> 1) - 1) & 1);
+                if (lane < 3) {
                     for (uint32_t n = 0; n < nv; n++) {
                         z = __fadd_rn(z, __fmul_rn(__fsub_rn(xi[n], z), f));
                         zo[n] = z;
                     }
                 }
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&in_empty[buf]);
             }
             __syncwarp();
             if (lane == 0) mbar_arrive(&full[buf]);
-            R.advance(nv);
         }
         if (lane < 3) lp[(size_t) lane * I + inst] = z;
     } else {
@@ -236,7 +280,7 @@ __global__ void __launch_bounds__(96, 2) k_dattorro_smem(const float *in, float 
                 z_b = lp_out[(buf * 3 + 2) * kSmLpStride + n];
             }
             // the modulated all-passes read slots that OTHER frames of the block rewrite: all reads before any write
-            asm volatile("bar.sync 1, 64;" ::: "memory");
+            asm volatile("bar.sync 1, %0;" ::"n"(32 * kSmFrameWarps) : "memory");
             if (live) {
                 float w;
                 float x = z_pre;
