@@ -19,6 +19,8 @@
 
 #include <vector>
 
+#include <type_traits>
+
 #include "common.cuh"
 #include "host_params.h"
 #include "tmap.h"
@@ -304,7 +306,7 @@ __device__ __forceinline__ void io_batch(const float *col, const float *tap, flo
     prev_a = ra[N - 1];
 }
 
-template <int N, bool RACK, bool FM>
+template <int N, bool RACK, bool FM, int T = -1>
 __device__ __forceinline__ void wet_batch(float *col, const float *rdcol, float d_balance, float r_balance, float &w_low, float &w_band,
                                           const SvfCoef &kw) {
     float x[N], v[N];
@@ -313,7 +315,7 @@ __device__ __forceinline__ void wet_batch(float *col, const float *rdcol, float 
 #pragma unroll
     for (int r = 0; r < N; r++) v[r] = rdcol[r * kFxLanes];
 #pragma unroll
-    for (int r = 0; r < N; r++) v[r] = svf_tick<FM>(v[r], w_low, w_band, kw);
+    for (int r = 0; r < N; r++) v[r] = svf_tick_t<T, FM>(v[r], w_low, w_band, kw);  // T < 0: the tap picked per lane
 #pragma unroll
     for (int r = 0; r < N; r++) v[r] = dry_wet<FM>(v[r], x[r], d_balance);                              // Fx.h:205-207
     if (RACK) {
@@ -324,13 +326,13 @@ __device__ __forceinline__ void wet_batch(float *col, const float *rdcol, float 
     for (int r = 0; r < N; r++) col[r * kFxLanes] = v[r];
 }
 
-template <int N, bool FM>
+template <int N, bool FM, int T = -1>
 __device__ __forceinline__ void tail_batch(float *col, float master, float &f_low, float &f_band, const SvfCoef &kf) {
     float v[N];
 #pragma unroll
     for (int r = 0; r < N; r++) v[r] = col[r * kFxLanes];
 #pragma unroll
-    for (int r = 0; r < N; r++) v[r] = svf_tick<FM>(v[r], f_low, f_band, kf);                           // Fx.h:426-434
+    for (int r = 0; r < N; r++) v[r] = svf_tick_t<T, FM>(v[r], f_low, f_band, kf);                      // Fx.h:426-434
 #pragma unroll
     for (int r = 0; r < N; r++) col[r * kFxLanes] = __fmul_rn(v[r], master);
 }
@@ -677,6 +679,16 @@ __host__ __device__ constexpr size_t fx_split_smem_floats() {
 // the two tail warps get a sub-partition each, the light I/O warps share with the tails (warps 4, 5 exit at once);
 // G = 4: pipeline p is warps p, p + 4, p + 8 -- all three of its stages on sub-partition p, 99 issue slots per frame each.
 constexpr int kFxIo = 0, kFxWet = 1, kFxTail = 2, kFxIdle = 3;
+// run(std::integral_constant<int, type>) for a warp-uniform filter type 0..4, run(<-1>) otherwise
+#define OLB_FX_BY_TYPE(TYPE, RUN)                                  \
+    switch (TYPE) {                                                \
+        case 0: RUN(std::integral_constant<int, 0>{}); break;      \
+        case 1: RUN(std::integral_constant<int, 1>{}); break;      \
+        case 2: RUN(std::integral_constant<int, 2>{}); break;      \
+        case 3: RUN(std::integral_constant<int, 3>{}); break;      \
+        case 4: RUN(std::integral_constant<int, 4>{}); break;      \
+        default: RUN(std::integral_constant<int, -1>{}); break;    \
+    }
 template <int KIND, int G>
 __host__ __device__ constexpr int fx_split_warps() {
     return G == 1 ? (OLB_K(KIND) == OLB_FX_RACK ? 3 : 2) : G == 2 ? (OLB_K(KIND) == OLB_FX_RACK ? 8 : 4) : (OLB_K(KIND) == OLB_FX_RACK ? 12 : 8);
@@ -690,7 +702,7 @@ template <int KIND, int TB, int STAGES, int G>
 __global__ void __launch_bounds__(32 * fx_split_warps<KIND, G>()) k_fx_split(const __grid_constant__ TensorMap tm_in,
                                                                               const __grid_constant__ TensorMap tm_out, uint32_t frames,
                                                                               uint32_t I, const float *__restrict__ par, float *svf,
-                                                                              float *ring_all, uint32_t wp0) {
+                                                                              float *ring_all, uint32_t wp0, uint32_t type_mask) {
     static_assert(OLB_K(KIND) == OLB_FX_DELAY || OLB_K(KIND) == OLB_FX_RACK, "ring kinds only");
     static_assert(G == 1 || G == 2 || G == 4, "1, 2 or 4 pipelines per CTA");
     constexpr bool kRack = OLB_K(KIND) == OLB_FX_RACK;
@@ -754,18 +766,26 @@ __global__ void __launch_bounds__(32 * fx_split_warps<KIND, G>()) k_fx_split(con
         const SvfCoef kf{P(P_F_FREQ), P(P_F_DAMP), P(P_F_DRIVE), (int) __float_as_uint(P(P_F_TYPE))};
         const float master = P(P_MASTER);
         float f_low = svf[ci], f_band = svf[(size_t) I + ci];
-        for (uint32_t i = 0; i < ntiles; i++) {
-            const uint32_t st = i % STAGES, ph = (i / STAGES) & 1;
-            mbar_wait(&mid[st], ph);
-            const uint32_t rows = min((uint32_t) TB, frames - i * TB);
-            float *col = tiles + (size_t) st * TB * L + lane;
-            if (live) {
-                uint32_t r = 0;
-                for (; r + kFxBatch <= rows; r += kFxBatch) tail_batch<kFxBatch, FM>(col + r * L, master, f_low, f_band, kf);
-                for (; r < rows; r++) tail_batch<1, FM>(col + r * L, master, f_low, f_band, kf);
+        // one filter type for the whole warp (idle lanes carry instance 0's)?  then the tap is picked at compile time: 8 selects
+        // and the peak subtractions of a frame less on the warps that set the pipeline's pace
+        const int type0 = __shfl_sync(0xffffffffu, kf.type, 0);
+        const int uniform_type = ((type_mask & 2u) && __all_sync(0xffffffffu, kf.type == type0 || !live) && type0 >= 0 && type0 <= 4) ? type0 : -1;
+        auto run = [&](auto tc) {  // (the whole tile loop per type: one switch per launch, the loops as plain as without it)
+            constexpr int T_ = decltype(tc)::value;
+            for (uint32_t i = 0; i < ntiles; i++) {
+                const uint32_t st = i % STAGES, ph = (i / STAGES) & 1;
+                mbar_wait(&mid[st], ph);
+                const uint32_t rows = min((uint32_t) TB, frames - i * TB);
+                float *col = tiles + (size_t) st * TB * L + lane;
+                if (live) {
+                    uint32_t r = 0;
+                    for (; r + kFxBatch <= rows; r += kFxBatch) tail_batch<kFxBatch, FM, T_>(col + r * L, master, f_low, f_band, kf);
+                    for (; r < rows; r++) tail_batch<1, FM, T_>(col + r * L, master, f_low, f_band, kf);
+                }
+                store_and_refill(i, st);
             }
-            store_and_refill(i, st);
-        }
+        };
+        OLB_FX_BY_TYPE(uniform_type, run)
         if (lane == 0) tma_wait_all<0>();
         if (live) {
             svf[inst] = f_low;
@@ -777,21 +797,28 @@ __global__ void __launch_bounds__(32 * fx_split_warps<KIND, G>()) k_fx_split(con
         const SvfCoef kw{P(P_W_FREQ), P(P_W_DAMP), P(P_W_DRIVE), (int) __float_as_uint(P(P_W_TYPE))};
         const float d_balance = P(P_D_BALANCE), r_balance = P(P_R_BALANCE);
         float w_low = svf[2 * (size_t) I + ci], w_band = svf[3 * (size_t) I + ci];
-        for (uint32_t i = 0; i < ntiles; i++) {
-            const uint32_t st = i % STAGES, ph = (i / STAGES) & 1;
-            mbar_wait(&full[st], ph);  // the inputs (async proxy) ...
-            mbar_wait(&tapd[st], ph);  // ... and warp 0's reads of the delay line
-            const uint32_t rows = min((uint32_t) TB, frames - i * TB);
-            float *col = tiles + (size_t) st * TB * L + lane;
-            const float *rdcol = rdtiles + (size_t) st * TB * L + lane;
-            if (live) {
-                uint32_t r = 0;
-                for (; r + kFxBatch <= rows; r += kFxBatch) wet_batch<kFxBatch, kRack, FM>(col + r * L, rdcol + r * L, d_balance, r_balance, w_low, w_band, kw);
-                for (; r < rows; r++) wet_batch<1, kRack, FM>(col + r * L, rdcol + r * L, d_balance, r_balance, w_low, w_band, kw);
+        const int type0 = __shfl_sync(0xffffffffu, kw.type, 0);
+        const int uniform_type = ((type_mask & 1u) && __all_sync(0xffffffffu, kw.type == type0 || !live) && type0 >= 0 && type0 <= 4) ? type0 : -1;
+        auto run = [&](auto tc) {
+            constexpr int T_ = decltype(tc)::value;
+            for (uint32_t i = 0; i < ntiles; i++) {
+                const uint32_t st = i % STAGES, ph = (i / STAGES) & 1;
+                mbar_wait(&full[st], ph);  // the inputs (async proxy) ...
+                mbar_wait(&tapd[st], ph);  // ... and warp 0's reads of the delay line
+                const uint32_t rows = min((uint32_t) TB, frames - i * TB);
+                float *col = tiles + (size_t) st * TB * L + lane;
+                const float *rdcol = rdtiles + (size_t) st * TB * L + lane;
+                if (live) {
+                    uint32_t r = 0;
+                    for (; r + kFxBatch <= rows; r += kFxBatch)
+                        wet_batch<kFxBatch, kRack, FM, T_>(col + r * L, rdcol + r * L, d_balance, r_balance, w_low, w_band, kw);
+                    for (; r < rows; r++) wet_batch<1, kRack, FM, T_>(col + r * L, rdcol + r * L, d_balance, r_balance, w_low, w_band, kw);
+                }
+                if (kRack) mbar_arrive(&mid[st]);
+                else store_and_refill(i, st);
             }
-            if (kRack) mbar_arrive(&mid[st]);
-            else store_and_refill(i, st);
-        }
+        };
+        OLB_FX_BY_TYPE(uniform_type, run)
         if (!kRack && lane == 0) tma_wait_all<0>();
         if (live) {
             svf[2 * (size_t) I + inst] = w_low;
@@ -1036,7 +1063,13 @@ static int fx_launch_split_cfg(olb_fx *h, const float *in, float *out, uint32_t 
     auto kern = k_fx_split<KIND, TB, STAGES, G>;
     OLB_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
     const uint32_t pipes = (h->I + kFxL - 1) / kFxL;
-    kern<<<(pipes + G - 1) / G, 32 * fx_split_warps<KIND, G>(), smem, st>>>(tin, tout, frames, h->I, h->d_par, h->d_svf, h->d_ring, h->wp);
+    // which warps pick the filter's output tap at compile time when their instances share a type: bit 0 wet, bit 1 tail
+    // (OLB_FX_SPLIT_TYPES: tuning aid).  Default: the wet warp, the pipeline's heaviest -- 8 192 instances, of the roof:
+    // delay 0.391 -> 0.410 (fused tier 0.446 -> 0.467); rack unchanged; with the tail warp specialised too the rack's fused
+    // tier LOSES 6 % (profiles/r02_run70_fx_split_types.txt)
+    const char *et = getenv("OLB_FX_SPLIT_TYPES");
+    const uint32_t type_mask = et ? (uint32_t) atoi(et) : 1u;
+    kern<<<(pipes + G - 1) / G, 32 * fx_split_warps<KIND, G>(), smem, st>>>(tin, tout, frames, h->I, h->d_par, h->d_svf, h->d_ring, h->wp, type_mask);
     return OLB_OK;
 }
 
