@@ -799,26 +799,49 @@ __global__ void __launch_bounds__(32 * fx_split_warps<KIND, G>()) k_fx_split(con
         float w_low = svf[2 * (size_t) I + ci], w_band = svf[3 * (size_t) I + ci];
         const int type0 = __shfl_sync(0xffffffffu, kw.type, 0);
         const int uniform_type = ((type_mask & 1u) && __all_sync(0xffffffffu, kw.type == type0 || !live) && type0 >= 0 && type0 <= 4) ? type0 : -1;
-        auto run = [&](auto tc) {
-            constexpr int T_ = decltype(tc)::value;
+        if constexpr (kRack) {
+            auto run = [&](auto tc) {  // the whole tile loop per type: one switch per launch
+                constexpr int T_ = decltype(tc)::value;
+                for (uint32_t i = 0; i < ntiles; i++) {
+                    const uint32_t st = i % STAGES, ph = (i / STAGES) & 1;
+                    mbar_wait(&full[st], ph);  // the inputs (async proxy) ...
+                    mbar_wait(&tapd[st], ph);  // ... and warp 0's reads of the delay line
+                    const uint32_t rows = min((uint32_t) TB, frames - i * TB);
+                    float *col = tiles + (size_t) st * TB * L + lane;
+                    const float *rdcol = rdtiles + (size_t) st * TB * L + lane;
+                    if (live) {
+                        uint32_t r = 0;
+                        for (; r + kFxBatch <= rows; r += kFxBatch)
+                            wet_batch<kFxBatch, true, FM, T_>(col + r * L, rdcol + r * L, d_balance, r_balance, w_low, w_band, kw);
+                        for (; r < rows; r++) wet_batch<1, true, FM, T_>(col + r * L, rdcol + r * L, d_balance, r_balance, w_low, w_band, kw);
+                    }
+                    mbar_arrive(&mid[st]);
+                }
+            };
+            OLB_FX_BY_TYPE(uniform_type, run)
+        } else {
+            // (the delay's two-warp pipeline runs 6 % faster with the switch INSIDE the tile loop, the rack's three-warp one 4 %
+            // faster with it outside: profiles/r02_run70_fx_split_types.txt -- these warps' code is that sensitive to its shape)
             for (uint32_t i = 0; i < ntiles; i++) {
                 const uint32_t st = i % STAGES, ph = (i / STAGES) & 1;
-                mbar_wait(&full[st], ph);  // the inputs (async proxy) ...
-                mbar_wait(&tapd[st], ph);  // ... and warp 0's reads of the delay line
+                mbar_wait(&full[st], ph);
+                mbar_wait(&tapd[st], ph);
                 const uint32_t rows = min((uint32_t) TB, frames - i * TB);
                 float *col = tiles + (size_t) st * TB * L + lane;
                 const float *rdcol = rdtiles + (size_t) st * TB * L + lane;
                 if (live) {
-                    uint32_t r = 0;
-                    for (; r + kFxBatch <= rows; r += kFxBatch)
-                        wet_batch<kFxBatch, kRack, FM, T_>(col + r * L, rdcol + r * L, d_balance, r_balance, w_low, w_band, kw);
-                    for (; r < rows; r++) wet_batch<1, kRack, FM, T_>(col + r * L, rdcol + r * L, d_balance, r_balance, w_low, w_band, kw);
+                    auto run = [&](auto tc) {
+                        constexpr int T_ = decltype(tc)::value;
+                        uint32_t r = 0;
+                        for (; r + kFxBatch <= rows; r += kFxBatch)
+                            wet_batch<kFxBatch, false, FM, T_>(col + r * L, rdcol + r * L, d_balance, r_balance, w_low, w_band, kw);
+                        for (; r < rows; r++) wet_batch<1, false, FM, T_>(col + r * L, rdcol + r * L, d_balance, r_balance, w_low, w_band, kw);
+                    };
+                    OLB_FX_BY_TYPE(uniform_type, run)
                 }
-                if (kRack) mbar_arrive(&mid[st]);
-                else store_and_refill(i, st);
+                store_and_refill(i, st);
             }
-        };
-        OLB_FX_BY_TYPE(uniform_type, run)
+        }
         if (!kRack && lane == 0) tma_wait_all<0>();
         if (live) {
             svf[2 * (size_t) I + inst] = w_low;
@@ -1065,8 +1088,8 @@ static int fx_launch_split_cfg(olb_fx *h, const float *in, float *out, uint32_t 
     const uint32_t pipes = (h->I + kFxL - 1) / kFxL;
     // which warps pick the filter's output tap at compile time when their instances share a type: bit 0 wet, bit 1 tail
     // (OLB_FX_SPLIT_TYPES: tuning aid).  Default: the wet warp, the pipeline's heaviest -- 8 192 instances, of the roof:
-    // delay 0.391 -> 0.410 (fused tier 0.446 -> 0.467); rack unchanged; with the tail warp specialised too the rack's fused
-    // tier LOSES 6 % (profiles/r02_run70_fx_split_types.txt)
+    // delay 0.402 -> 0.435 (fused tier 0.441 -> 0.478), rack 0.386 -> 0.400 (0.464 -> 0.466); with the tail warp specialised
+    // too the rack's fused tier LOSES 6 % (profiles/r02_run70_fx_split_types.txt, r02_run73_fx_split_final.txt)
     const char *et = getenv("OLB_FX_SPLIT_TYPES");
     const uint32_t type_mask = et ? (uint32_t) atoi(et) : 1u;
     kern<<<(pipes + G - 1) / G, 32 * fx_split_warps<KIND, G>(), smem, st>>>(tin, tout, frames, h->I, h->d_par, h->d_svf, h->d_ring, h->wp, type_mask);
